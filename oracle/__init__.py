@@ -1,0 +1,166 @@
+"""ctypes loader for the CPU oracle (oracle/*.c).
+
+TEST INFRASTRUCTURE ONLY — PARITY UNPINNED. Only tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs may import this package; the product
+(docker-nvidia-glx-desktop_b200/) never does. The oracle restates GStreamer videoconvert /
+videoscale from SURVEY.md Appendix A/B: the reference (/root/reference Dockerfile:467-471)
+installs GStreamer as an unpinned binary and holds neither its source nor any test vector.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SRCS = ["convert.c", "scale.c", "damage_synth.c"]
+
+FMT_I420, FMT_NV12 = 0, 1
+MATRIX_BT601, MATRIX_BT709 = 0, 1
+RANGE_LIMITED, RANGE_FULL = 0, 1
+SITE_NONE, SITE_H_COSITED = 0, 1
+SCALE_GST_LQ, SCALE_BOX_2X2 = 0, 1
+
+
+def build(native: bool = False, out_dir: str | None = None) -> str:
+    """Compile the oracle with gcc. native=True builds -march=native into a temp dir (used by the
+    timed CPU arm so the baseline gets the host's full ISA); otherwise oracle/_build/."""
+    march = "native" if native else "x86-64-v3"
+    if out_dir is None:
+        out_dir = tempfile.mkdtemp(prefix="b200vc_oracle_") if native else os.path.join(_HERE, "_build")
+    os.makedirs(out_dir, exist_ok=True)
+    out = os.path.join(out_dir, "liboracle.so")
+    srcs = [os.path.join(_HERE, s) for s in _SRCS]
+    newest = max(os.path.getmtime(p) for p in srcs + [os.path.join(_HERE, "oracle.h")])
+    if os.path.exists(out) and os.path.getmtime(out) >= newest:
+        return out
+    cmd = [os.environ.get("CC", "gcc"), "-O3", f"-march={march}", "-fPIC", "-std=c11", "-D_GNU_SOURCE",
+           "-shared", "-o", out] + srcs + ["-lm", "-lpthread"]
+    subprocess.run(cmd, check=True)
+    return out
+
+
+class Oracle:
+    """Thin typed wrapper over liboracle.so working on numpy uint8 arrays."""
+
+    def __init__(self, path: str | None = None, native: bool = False):
+        self.path = path or build(native=native)
+        L = self.lib = C.CDLL(self.path)
+        u8p, sz, i = C.c_void_p, C.c_size_t, C.c_int
+        pl, pi = C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)
+        L.orc_build_matrix.argtypes = [i, i, C.POINTER(C.c_int32 * 12)]
+        L.orc_default_layout.argtypes = [i, i, i, pi, pi]
+        L.orc_default_layout.restype = sz
+        L.orc_convert_mt.argtypes = [u8p, sz, i, i, i, i, i, i, pl, pi, i]
+        L.orc_convert_rows.argtypes = [u8p, sz, i, i, i, i, i, i, pl, pi, i, i]
+        L.orc_scale_plane.argtypes = [u8p, sz, i, i, u8p, sz, i, i, i, i]
+        L.orc_convert_scale_mt.argtypes = [u8p, sz, i, i, i, i, i, i, i, i, i, pl, pi, i]
+        L.orc_scale_h_taps.argtypes = [i, i, u8p, u8p]
+        L.orc_scale_v_taps.argtypes = [i, i, u8p, u8p]
+        L.orc_damage_map.argtypes = [u8p, sz, u8p, sz, i, i, u8p]
+        L.orc_synth_rand.argtypes = [u8p, sz, i, i, C.c_uint64]
+        L.orc_synth_bars.argtypes = [u8p, sz, i, i]
+        L.orc_synth_desk.argtypes = [u8p, sz, i, i, C.c_uint64]
+
+    # -- spec tables ---------------------------------------------------------------------------
+    def matrix(self, matrix: int, rng: int) -> np.ndarray:
+        m = (C.c_int32 * 12)()
+        self.lib.orc_build_matrix(matrix, rng, C.byref(m))
+        return np.array(list(m), dtype=np.int32).reshape(3, 4)
+
+    def default_layout(self, fmt: int, w: int, h: int):
+        off, pit = (C.c_size_t * 3)(), (C.c_size_t * 3)()
+        total = self.lib.orc_default_layout(fmt, w, h, off, pit)
+        return int(total), [int(x) for x in off], [int(x) for x in pit]
+
+    def h_taps(self, in_w: int, out_w: int):
+        idx, fr = np.zeros(out_w, np.int32), np.zeros(out_w, np.int32)
+        self.lib.orc_scale_h_taps(in_w, out_w, idx.ctypes.data, fr.ctypes.data)
+        return idx, fr
+
+    def v_taps(self, in_h: int, out_h: int):
+        idx, p1 = np.zeros(out_h, np.int32), np.zeros(out_h, np.int32)
+        self.lib.orc_scale_v_taps(in_h, out_h, idx.ctypes.data, p1.ctypes.data)
+        return idx, p1
+
+    # -- the path ------------------------------------------------------------------------------
+    def _planes(self, fmt, w, h, pitches):
+        if pitches is None:
+            total, off, pit = self.default_layout(fmt, w, h)
+        else:
+            pit = list(pitches) + [0] * (3 - len(pitches))
+            rows = [h, h // 2, h // 2]
+            off, total = [], 0
+            for p in range(3 if fmt == FMT_I420 else 2):
+                off.append(total)
+                total += pit[p] * rows[p]
+            off += [0] * (3 - len(off))
+        buf = np.zeros(total, np.uint8)
+        ptrs = (C.c_void_p * 3)(*[buf.ctypes.data + o for o in off])
+        pits = (C.c_size_t * 3)(*pit)
+        return buf, off, pit, ptrs, pits
+
+    def convert(self, frame: np.ndarray, fmt=FMT_I420, matrix=MATRIX_BT601, rng=RANGE_LIMITED,
+                site=SITE_NONE, out_size=None, scale_mode=SCALE_GST_LQ, pitches=None, threads=1):
+        """frame: (h, w, 4) uint8 BGRx (may be a strided view). Returns (buf, offsets, pitches)."""
+        h, w = frame.shape[:2]
+        assert frame.dtype == np.uint8 and frame.shape[2] == 4 and frame.strides[2] == 1 and frame.strides[1] == 4
+        ow, oh = out_size if out_size else (w, h)
+        buf, off, pit, ptrs, pits = self._planes(fmt, ow, oh, pitches)
+        rc = self.lib.orc_convert_scale_mt(frame.ctypes.data, frame.strides[0], w, h, ow, oh, fmt, matrix,
+                                           rng, site, scale_mode, ptrs, pits, threads)
+        if rc:
+            raise ValueError("oracle rejected the arguments")
+        return buf, off, pit
+
+    def convert_into(self, frame_ptr: int, in_pitch: int, w: int, h: int, ow: int, oh: int, fmt, matrix, rng,
+                     site, scale_mode, ptrs, pits, threads: int) -> int:
+        """Raw-pointer variant for the timed CPU arm (no allocation inside the timed region)."""
+        return self.lib.orc_convert_scale_mt(frame_ptr, in_pitch, w, h, ow, oh, fmt, matrix, rng, site,
+                                             scale_mode, ptrs, pits, threads)
+
+    def scale_plane(self, src: np.ndarray, out_w: int, out_h: int, comps=1, scale_mode=SCALE_GST_LQ):
+        in_h, in_w = src.shape[0], src.shape[1] // comps
+        dst = np.zeros((out_h, out_w * comps), np.uint8)
+        rc = self.lib.orc_scale_plane(src.ctypes.data, src.strides[0], in_w, in_h, dst.ctypes.data,
+                                      dst.strides[0], out_w, out_h, comps, scale_mode)
+        if rc:
+            raise ValueError("oracle rejected the arguments")
+        return dst
+
+    def damage_map(self, cur: np.ndarray, prev: np.ndarray | None) -> np.ndarray:
+        h, w = cur.shape[:2]
+        m = np.zeros(((h + 15) // 16, (w + 15) // 16), np.uint8)
+        self.lib.orc_damage_map(cur.ctypes.data, cur.strides[0], prev.ctypes.data if prev is not None else None,
+                                prev.strides[0] if prev is not None else 0, w, h, m.ctypes.data)
+        return m
+
+    # -- synthetic frames ------------------------------------------------------------------------
+    def synth(self, kind: str, w: int, h: int, frame_index: int = 0, pitch: int | None = None,
+              out: np.ndarray | None = None) -> np.ndarray:
+        pitch = pitch or w * 4
+        if out is None:
+            out = np.zeros((h, pitch), np.uint8)
+        ptr = out.ctypes.data
+        if kind == "rand":
+            self.lib.orc_synth_rand(ptr, pitch, w, h, frame_index)
+        elif kind == "bars":
+            self.lib.orc_synth_bars(ptr, pitch, w, h)
+        elif kind == "desk":
+            self.lib.orc_synth_desk(ptr, pitch, w, h, frame_index)
+        else:
+            raise ValueError(kind)
+        return np.ndarray((h, w, 4), np.uint8, buffer=out, strides=(pitch, 4, 1))
+
+
+_default: Oracle | None = None
+
+
+def get() -> Oracle:
+    global _default
+    if _default is None:
+        _default = Oracle()
+    return _default

@@ -1,0 +1,135 @@
+"""Independent NumPy restatement of SURVEY.md Appendix A/B (vectorised, plain formulas).
+
+TEST INFRASTRUCTURE ONLY — PARITY UNPINNED (see oracle.h). It exists so that two separately
+written implementations of one spec (this file and oracle/*.c) can be compared: agreement catches
+transcription slips in either, not errors in the spec itself. It shares no code with the C oracle:
+the matrix comes from the table printed in SURVEY A.2 (the C side derives it from Kr/Kb), the
+conversion uses the plain per-pixel formula (the C side uses upstream's packed int64 tables).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+# (matrix, range) -> rows Y,U,V of (cR, cG, cB, off)
+MATRICES = {
+    (0, 0): [(66, 129, 25, 4096), (-38, -74, 112, 32768), (112, -94, -18, 32768)],
+    (0, 1): [(77, 150, 29, 0), (-43, -85, 128, 32768), (128, -107, -21, 32768)],
+    (1, 0): [(47, 157, 16, 4096), (-26, -87, 112, 32768), (112, -102, -10, 32768)],
+    (1, 1): [(54, 183, 18, 0), (-29, -99, 128, 32768), (128, -116, -12, 32768)],
+}
+
+
+def yuv444(frame: np.ndarray, matrix: int, rng: int):
+    """(h,w,4) BGRx -> three (h,w) uint8 arrays, (c.RGB + off) >> 8 with no rounding term."""
+    b = frame[..., 0].astype(np.int32)
+    g = frame[..., 1].astype(np.int32)
+    r = frame[..., 2].astype(np.int32)
+    out = []
+    for cr, cg, cb, off in MATRICES[(matrix, rng)]:
+        s = cr * r + cg * g + cb * b + off
+        assert s.min() >= 0 and s.max() <= 65535
+        out.append((s >> 8).astype(np.uint8))
+    return out
+
+
+def chroma_down(c: np.ndarray, site: int) -> np.ndarray:
+    """(h,w) 4:4:4 chroma -> (h/2,w/2): horizontal (rounded) on each line, then vertical (rounded)."""
+    h, w = c.shape
+    c = c.astype(np.int32)
+    if site == 0:  # NONE / JPEG: h2
+        hz = (c[:, 0::2] + c[:, 1::2] + 1) >> 1
+    else:  # H_COSITED: h2_cs
+        hz = np.empty((h, w // 2), np.int32)
+        hz[:, 0] = (3 * c[:, 0] + c[:, 1] + 2) >> 2
+        if w >= 4:
+            mid = np.arange(2, w - 2, 2)
+            hz[:, 1 : w // 2 - 1] = (c[:, mid - 1] + 2 * c[:, mid] + c[:, mid + 1] + 2) >> 2
+            hz[:, w // 2 - 1] = (c[:, w - 3] + 3 * c[:, w - 2] + 2) >> 2
+    return ((hz[0::2] + hz[1::2] + 1) >> 1).astype(np.uint8)
+
+
+def convert(frame: np.ndarray, fmt: int, matrix: int, rng: int, site: int):
+    """Returns (Y, U, V) planes for I420 or (Y, UV) for NV12 at the input size."""
+    y, u, v = yuv444(frame, matrix, rng)
+    u2, v2 = chroma_down(u, site), chroma_down(v, site)
+    if fmt == 1:
+        uv = np.empty((u2.shape[0], u2.shape[1] * 2), np.uint8)
+        uv[:, 0::2], uv[:, 1::2] = u2, v2
+        return y, uv
+    return y, u2, v2
+
+
+def h_taps(in_w: int, out_w: int):
+    inc = max(0, ((in_w - 1) << 16) // (out_w - 1) - 1) if out_w > 1 else 0
+    p = np.arange(out_w, dtype=np.int64) * inc
+    return (p >> 16).astype(np.int64), ((p >> 8) & 0xFF).astype(np.int64)
+
+
+def v_taps(in_h: int, out_h: int):
+    y = np.arange(out_h, dtype=np.int64)
+    num, den = (2 * y + 1) * in_h - out_h, 2 * out_h
+    i = np.floor_divide(num, den)
+    rem = num - i * den
+    return i, (128 * rem + den) // (2 * den)
+
+
+def scale_plane(src: np.ndarray, out_w: int, out_h: int, comps: int = 1, mode: int = 0) -> np.ndarray:
+    in_h, in_w = src.shape[0], src.shape[1] // comps
+    s = src.reshape(in_h, in_w, comps).astype(np.int64)
+    if mode == 1:
+        assert in_w == 2 * out_w and in_h == 2 * out_h
+        d = (s[0::2, 0::2] + s[0::2, 1::2] + s[1::2, 0::2] + s[1::2, 1::2] + 2) >> 2
+        return d.astype(np.uint8).reshape(out_h, out_w * comps)
+    hi, hf = h_taps(in_w, out_w)
+    i0, i1 = np.clip(hi, 0, in_w - 1), np.clip(hi + 1, 0, in_w - 1)
+    f = hf[None, :, None]
+    hz = (s[:, i0] * (256 - f) + s[:, i1] * f) >> 8
+    vi, vp = v_taps(in_h, out_h)
+    a, b = hz[np.clip(vi, 0, in_h - 1)], hz[np.clip(vi + 1, 0, in_h - 1)]
+    d = a + (((b - a) * vp[:, None, None] + 32) >> 6)
+    return np.clip(d, 0, 255).astype(np.uint8).reshape(out_h, out_w * comps)
+
+
+def convert_scale(frame, out_w, out_h, fmt, matrix, rng, site, mode=0):
+    planes = convert(frame, fmt, matrix, rng, site)
+    if out_w == frame.shape[1] and out_h == frame.shape[0]:
+        return planes
+    out = [scale_plane(planes[0], out_w, out_h, 1, mode)]
+    if fmt == 1:
+        out.append(scale_plane(planes[1], out_w // 2, out_h // 2, 2, mode))
+    else:
+        out.append(scale_plane(planes[1], out_w // 2, out_h // 2, 1, mode))
+        out.append(scale_plane(planes[2], out_w // 2, out_h // 2, 1, mode))
+    return tuple(out)
+
+
+def damage_map(cur: np.ndarray, prev: np.ndarray | None) -> np.ndarray:
+    h, w = cur.shape[:2]
+    mh, mw = (h + 15) // 16, (w + 15) // 16
+    if prev is None:
+        return np.ones((mh, mw), np.uint8)
+    diff = np.any(cur[..., :3] != prev[..., :3], axis=2)
+    pad = np.zeros((mh * 16, mw * 16), bool)
+    pad[:h, :w] = diff
+    return pad.reshape(mh, 16, mw, 16).any(axis=(1, 3)).astype(np.uint8)
+
+
+def splitmix64(state: int):
+    state = (state + 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
+    z = state
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & 0xFFFFFFFFFFFFFFFF
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & 0xFFFFFFFFFFFFFFFF
+    return state, z ^ (z >> 31)
+
+
+def synth_rand(w: int, h: int, frame_index: int) -> np.ndarray:
+    """Python mirror of orc_synth_rand (small frames only: pure-Python generator)."""
+    out = np.zeros((h, w * 4), np.uint8)
+    for y in range(h):
+        st = (0x9E3779B97F4A7C15 + frame_index * 0x100000001B3 + y * 0xD6E8FEB86659FD93) & 0xFFFFFFFFFFFFFFFF
+        row = bytearray()
+        while len(row) < w * 4:
+            st, v = splitmix64(st)
+            row += v.to_bytes(8, "little")
+        out[y] = np.frombuffer(bytes(row[: w * 4]), np.uint8)
+    return out.reshape(h, w, 4)

@@ -1,0 +1,907 @@
+// api.cu — the C ABI of libb200vc.so (include/b200vc.h) and the host runtime behind it:
+// negotiation checks, per-session device frames, pinned staging, the three-stream PCIe pipeline
+// (H2D / kernel / D2H with events), tap tables and TMA descriptors for the fused scaler.
+//
+// Mirrors what GstVideoConvert/GstVideoScale do around gst_video_converter_frame on the
+// reference's x264enc fallback (/root/reference Dockerfile:467-471, README.md:21): set_info builds
+// the converter once, transform_frame runs it per buffer (b). No CPU fallback
+// exists anywhere in this file: without a usable sm_100 device every call fails.
+#include "../../include/b200vc.h"
+#include "kernels.cuh"
+
+#include <cudaTypedefs.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+using namespace b200vc;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct Session {
+    uint8_t *d_in[2] = { nullptr, nullptr };   // ping-pong: current and previous frame stay in HBM
+    int cur = 0;
+    bool have_prev = false;
+    cudaEvent_t ev_kernel = nullptr;          // last kernel that read this session's frames
+    bool ev_valid = false;
+};
+
+struct Slot {
+    uint8_t *d_out = nullptr;                 // device output frame (+ damage map at d_dmg)
+    uint8_t *d_dmg = nullptr;
+    uint8_t *h_in = nullptr;                  // pinned staging, allocated on first pageable frame
+    uint8_t *h_out = nullptr;
+    cudaEvent_t done = nullptr;
+    bool busy = false;
+    uint64_t ticket = 0;
+    // deferred host copy out of h_out when the caller's planes are pageable
+    bool staged_out = false;
+    b200vc_frame frame;
+};
+
+struct HostReg { const void *base; size_t bytes; };
+
+}  // namespace
+
+struct b200vc_ctx {
+    b200vc_config cfg;
+    bool scaling = false;
+    int path = 0;                              // 0 convert, 1 fused scale, 2 two-pass scale
+    Matrix mx;
+    cudaDeviceProp prop;
+    cudaStream_t s_h2d = nullptr, s_k = nullptr, s_d2h = nullptr;
+    std::vector<cudaEvent_t> ev_band_h2d, ev_band_k;
+
+    // device geometry (library-owned buffers: pitches padded so every row is 16-byte aligned)
+    size_t d_in_pitch = 0, d_in_size = 0;
+    size_t d_off[3] = { 0, 0, 0 }, d_pitch[3] = { 0, 0, 0 }, d_out_size = 0;
+    int mb_w = 0, mb_h = 0;
+
+    std::vector<Session> sessions;
+    std::vector<Slot> slots;
+    uint64_t next_ticket = 1;
+    int next_slot = 0;
+
+    // scaling
+    Tap *d_taps = nullptr;
+    ScaleTables tab = { nullptr, nullptr, nullptr, nullptr };
+    int box_w = 0, box_h = 0;
+    size_t smem_bytes = 0;
+    uint8_t *d_mid = nullptr;                  // two-pass: full-size intermediate I420
+    size_t mid_off[3] = { 0, 0, 0 }, mid_pitch[3] = { 0, 0, 0 }, mid_size = 0;
+    int mid_frames = 0;
+    PFN_cuTensorMapEncodeTiled_v12000 encode_tiled = nullptr;
+
+    std::vector<HostReg> registered;
+    b200vc_stats stats;
+    mutable std::mutex mu;
+    std::string err;
+};
+
+namespace {
+
+int fail(b200vc_ctx *c, int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf; else g_create_error = buf;
+    return code;
+}
+
+#define CU_TRY(c, call)                                                                          \
+    do {                                                                                         \
+        cudaError_t e_ = (call);                                                                 \
+        if (e_ != cudaSuccess)                                                                   \
+            return fail((c), e_ == cudaErrorMemoryAllocation ? B200VC_ERR_NOMEM : B200VC_ERR_CUDA, \
+                        "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+size_t ru(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// SURVEY A.2 table; rows Y,U,V of (cR, cG, cB, off). The oracle derives the same numbers from
+// Kr/Kb in double precision; tests compare the two.
+const int kMatrix[2][2][3][4] = {
+    { { { 66, 129, 25, 4096 }, { -38, -74, 112, 32768 }, { 112, -94, -18, 32768 } },      // 601 limited
+      { { 77, 150, 29, 0 }, { -43, -85, 128, 32768 }, { 128, -107, -21, 32768 } } },      // 601 full
+    { { { 47, 157, 16, 4096 }, { -26, -87, 112, 32768 }, { 112, -102, -10, 32768 } },     // 709 limited
+      { { 54, 183, 18, 0 }, { -29, -99, 128, 32768 }, { 128, -116, -12, 32768 } } },      // 709 full
+};
+
+uint32_t pack_coef(int cb, int cg, int cr)
+{
+    return (uint32_t)(cb & 0xff) | ((uint32_t)(cg & 0xff) << 8) | ((uint32_t)(cr & 0xff) << 16);
+}
+
+Matrix make_matrix(int matrix, int range)
+{
+    const int (*m)[4] = kMatrix[matrix][range];
+    Matrix r;
+    r.cy = pack_coef(m[0][2], m[0][1], m[0][0]);
+    r.oy = (uint32_t)m[0][3];
+    bool neg = false;
+    for (int row = 1; row < 3; row++)
+        for (int c = 0; c < 3; c++)
+            if (m[row][c] > 127) neg = true;
+    r.neg = neg ? 1 : 0;
+    if (!neg) {
+        r.cu = pack_coef(m[1][2], m[1][1], m[1][0]);  r.ou = (uint32_t)m[1][3];
+        r.cv = pack_coef(m[2][2], m[2][1], m[2][0]);  r.ov = (uint32_t)m[2][3];
+    } else {
+        r.cu = pack_coef(-m[1][2], -m[1][1], -m[1][0]);  r.ou = (uint32_t)(65535 - m[1][3]);
+        r.cv = pack_coef(-m[2][2], -m[2][1], -m[2][0]);  r.ov = (uint32_t)(65535 - m[2][3]);
+    }
+    return r;
+}
+
+// ---- scaler taps, integer arithmetic only -------------------------------------------
+void build_h_taps(int in_n, int out_n, std::vector<Tap> &t)
+{
+    long long inc = 0;
+    if (out_n > 1) {
+        inc = (((long long)(in_n - 1)) << 16) / (out_n - 1) - 1;
+        if (inc < 0) inc = 0;
+    }
+    t.resize(ru(out_n, 4));
+    for (int x = 0; x < out_n; x++) {
+        long long p = (long long)x * inc;
+        int i = (int)(p >> 16), f = (int)((p >> 8) & 0xff);
+        int i0 = std::min(std::max(i, 0), in_n - 1), i1 = std::min(std::max(i + 1, 0), in_n - 1);
+        t[x] = (Tap)i0 | ((Tap)f << 16) | ((Tap)(i1 - i0) << 24);
+    }
+    for (size_t x = out_n; x < t.size(); x++) t[x] = t[out_n - 1];
+}
+
+void build_v_taps(int in_n, int out_n, std::vector<Tap> &t)
+{
+    const long long den = 2LL * out_n;
+    t.resize(ru(out_n, 4));
+    for (int y = 0; y < out_n; y++) {
+        long long num = (2LL * y + 1) * in_n - out_n;
+        long long i = num / den, rem = num - i * den;
+        if (rem < 0) { i -= 1; rem += den; }
+        int p1 = (int)((128 * rem + den) / (2 * den));
+        int i0 = (int)std::min<long long>(std::max<long long>(i, 0), in_n - 1);
+        int i1 = (int)std::min<long long>(std::max<long long>(i + 1, 0), in_n - 1);
+        t[y] = (Tap)i0 | ((Tap)p1 << 16) | ((Tap)(i1 - i0) << 24);
+    }
+    for (size_t y = out_n; y < t.size(); y++) t[y] = t[out_n - 1];
+}
+
+// BOX_2X2 reuses the tables as plain index maps: entry k = source index 2k.
+void build_box_taps(int out_n, std::vector<Tap> &t)
+{
+    t.resize(ru(out_n, 4));
+    for (int k = 0; k < out_n; k++) t[k] = (Tap)(2 * k) | ((Tap)1 << 24);
+    for (size_t k = out_n; k < t.size(); k++) t[k] = t[out_n - 1];
+}
+
+inline int tidx(Tap t) { return (int)(t & 0xffff); }
+inline int tstep(Tap t) { return (int)((t >> 24) & 1); }
+
+// Source window per output tile, mirrored from k2_fused_scale_kernel phase 0; returns the box that
+// covers every tile.
+void fused_box(const b200vc_config &c, const std::vector<Tap> &hy, const std::vector<Tap> &vy,
+               const std::vector<Tap> &hc, const std::vector<Tap> &vc, int &box_w, int &box_h)
+{
+    const int site = c.chroma_site == B200VC_SITE_H_COSITED ? 1 : 0;
+    box_w = box_h = 0;
+    for (int x0 = 0; x0 < c.out_w; x0 += K2_TILE_W) {
+        const int x1 = std::min(x0 + K2_TILE_W, c.out_w) - 1;
+        int sx = std::min(tidx(hy[x0]), 2 * tidx(hc[x0 >> 1]) - site) & ~1;
+        int last = std::max(tidx(hy[x1]) + tstep(hy[x1]), 2 * (tidx(hc[x1 >> 1]) + tstep(hc[x1 >> 1])) + 1);
+        box_w = std::max(box_w, last - sx + 1);
+    }
+    for (int y0 = 0; y0 < c.out_h; y0 += K2_TILE_H) {
+        const int y1 = std::min(y0 + K2_TILE_H, c.out_h) - 1;
+        int sy = std::min(tidx(vy[y0]), 2 * tidx(vc[y0 >> 1])) & ~1;
+        int last = std::max(tidx(vy[y1]) + tstep(vy[y1]), 2 * (tidx(vc[y1 >> 1]) + tstep(vc[y1 >> 1])) + 1);
+        box_h = std::max(box_h, last - sy + 1);
+    }
+    box_w = (int)ru(box_w, 4);
+    box_h = (int)ru(box_h, 2);
+}
+
+int check_config(const b200vc_config *c, std::string *why)
+{
+    auto bad = [&](int code, const char *msg) { if (why) *why = msg; return code; };
+    if (!c) return bad(B200VC_ERR_INVALID_ARG, "config is NULL");
+    if (c->in_w < 2 || c->in_h < 2 || c->out_w < 2 || c->out_h < 2)
+        return bad(B200VC_ERR_INVALID_ARG, "width/height must be >= 2");
+    if (c->in_w > 16384 || c->in_h > 16384 || c->out_w > 16384 || c->out_h > 16384)
+        return bad(B200VC_ERR_UNSUPPORTED, "width/height above 16384");
+    if ((c->in_w | c->in_h | c->out_w | c->out_h) & 1)
+        return bad(B200VC_ERR_UNSUPPORTED, "odd widths/heights are not negotiated (4:2:0 needs even sizes)");
+    if (c->out_format != B200VC_FMT_I420 && c->out_format != B200VC_FMT_NV12)
+        return bad(B200VC_ERR_UNSUPPORTED, "output format must be I420 or NV12");
+    if (c->matrix != B200VC_MATRIX_BT601 && c->matrix != B200VC_MATRIX_BT709)
+        return bad(B200VC_ERR_UNSUPPORTED, "colorimetry matrix must be bt601 or bt709");
+    if (c->range != B200VC_RANGE_LIMITED && c->range != B200VC_RANGE_FULL)
+        return bad(B200VC_ERR_UNSUPPORTED, "range must be limited (16-235) or full (0-255)");
+    if (c->chroma_site != B200VC_SITE_NONE && c->chroma_site != B200VC_SITE_H_COSITED)
+        return bad(B200VC_ERR_UNSUPPORTED, "chroma-site must be none/jpeg or mpeg2 (h-cosited)");
+    if (c->scale_mode != B200VC_SCALE_GST_LQ && c->scale_mode != B200VC_SCALE_BOX_2X2)
+        return bad(B200VC_ERR_UNSUPPORTED, "unknown scale mode");
+    const bool scaling = c->in_w != c->out_w || c->in_h != c->out_h;
+    if (scaling && c->scale_mode == B200VC_SCALE_BOX_2X2 && (c->in_w != 2 * c->out_w || c->in_h != 2 * c->out_h))
+        return bad(B200VC_ERR_UNSUPPORTED, "BOX_2X2 needs an exact 2:1 downscale");
+    if (scaling && (c->flags & B200VC_FLAG_DAMAGE_MAP))
+        return bad(B200VC_ERR_UNSUPPORTED, "the damage map is produced on the unscaled path only");
+    if (c->max_sessions < 0 || c->max_sessions > 1024 || c->n_inflight < 0 || c->n_inflight > 64 ||
+        c->n_bands < 0 || c->n_bands > 64)
+        return bad(B200VC_ERR_INVALID_ARG, "max_sessions/n_inflight/n_bands out of range");
+    return B200VC_OK;
+}
+
+bool is_pinned(const void *p)
+{
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost;
+}
+
+int collect_slot(b200vc_ctx *c, Slot &s);
+
+// Page-lock a caller buffer once (B200VC_FLAG_REGISTER_HOST); false = fall back to staging.
+bool ensure_registered(b200vc_ctx *c, const void *p, size_t bytes)
+{
+    for (const HostReg &r : c->registered)
+        if (p >= r.base && (const uint8_t *)p + bytes <= (const uint8_t *)r.base + r.bytes) return true;
+    if (c->registered.size() >= 64) return false;
+    if (cudaHostRegister(const_cast<void *>(p), bytes, cudaHostRegisterDefault) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    c->registered.push_back({ p, bytes });
+    return true;
+}
+
+int make_tensor_map(b200vc_ctx *c, const void *base, size_t pitch, size_t frame_stride, int n_frames,
+                    CUtensorMap *map)
+{
+    cuuint64_t dims[3] = { (cuuint64_t)c->cfg.in_w, (cuuint64_t)c->cfg.in_h, (cuuint64_t)n_frames };
+    cuuint64_t strides[2] = { (cuuint64_t)pitch, (cuuint64_t)(frame_stride ? frame_stride : pitch * c->cfg.in_h) };
+    cuuint32_t box[3] = { (cuuint32_t)c->box_w, (cuuint32_t)c->box_h, 1 };
+    cuuint32_t estr[3] = { 1, 1, 1 };
+    CUresult r = c->encode_tiled(map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, const_cast<void *>(base), dims, strides,
+                                 box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail(c, B200VC_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return B200VC_OK;
+}
+
+PlaneSet plane_set(uint8_t *base, const size_t off[3], const size_t pitch[3], size_t frame_stride, int fmt)
+{
+    PlaneSet ps;
+    for (int i = 0; i < 3; i++) {
+        ps.p[i] = (fmt == B200VC_FMT_NV12 && i == 2) ? nullptr : base + off[i];
+        ps.pitch[i] = (long long)pitch[i];
+    }
+    ps.frame_stride = (long long)frame_stride;
+    return ps;
+}
+
+// Enqueue the kernels for n_frames frames on `st`. Input rows [row0,row0+rows) (unscaled path) or
+// whole frames (scaled paths).
+int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_t src_fstride,
+                    const uint8_t *d_prev, size_t prev_pitch, size_t prev_fstride,
+                    const PlaneSet &out, uint8_t *d_dmg, size_t dmg_fstride,
+                    int row0, int rows, int n_frames, cudaStream_t st)
+{
+    const b200vc_config &g = c->cfg;
+    const int site = g.chroma_site == B200VC_SITE_H_COSITED ? 1 : 0;
+    if (c->path == 0) {
+        ConvertParams p;
+        memset(&p, 0, sizeof p);
+        p.src = d_src + (size_t)row0 * src_pitch;  p.src_pitch = (long long)src_pitch;  p.src_frame_stride = (long long)src_fstride;
+        if (d_prev && d_dmg) {
+            p.prev = d_prev + (size_t)row0 * prev_pitch;  p.prev_pitch = (long long)prev_pitch;  p.prev_frame_stride = (long long)prev_fstride;
+            p.damage = d_dmg + (size_t)(row0 / 16) * c->mb_w;  p.damage_frame_stride = (long long)dmg_fstride;
+        }
+        p.mb_w = c->mb_w;
+        p.out = out;
+        p.out.p[0] += (size_t)row0 * out.pitch[0];
+        p.out.p[1] += (size_t)(row0 / 2) * out.pitch[1];
+        if (p.out.p[2]) p.out.p[2] += (size_t)(row0 / 2) * out.pitch[2];
+        p.w = g.in_w;  p.h = rows;  p.n_frames = n_frames;  p.mx = c->mx;
+        CU_TRY(c, launch_convert(p, g.out_format, site, st));
+        c->stats.kernel_launches += 1;
+        return B200VC_OK;
+    }
+    if (c->path == 1) {
+        CUtensorMap map;
+        int rc = make_tensor_map(c, d_src, src_pitch, src_fstride, n_frames, &map);
+        if (rc) return rc;
+        FusedScaleParams p;
+        memset(&p, 0, sizeof p);
+        p.out = out;  p.tab = c->tab;
+        p.in_w = g.in_w;  p.in_h = g.in_h;  p.out_w = g.out_w;  p.out_h = g.out_h;
+        p.box_w = c->box_w;  p.box_h = c->box_h;  p.n_frames = n_frames;
+        p.box2x2 = g.scale_mode == B200VC_SCALE_BOX_2X2;  p.mx = c->mx;
+        CU_TRY(c, launch_fused_scale(map, p, g.out_format, site, st));
+        c->stats.kernel_launches += 1;
+        return B200VC_OK;
+    }
+    // two-pass: K1 into the full-size intermediate (always planar), then the plane scaler
+    for (int f0 = 0; f0 < n_frames; f0 += c->mid_frames) {
+        const int nf = std::min(c->mid_frames, n_frames - f0);
+        ConvertParams p;
+        memset(&p, 0, sizeof p);
+        p.src = d_src + (size_t)f0 * src_fstride;  p.src_pitch = (long long)src_pitch;  p.src_frame_stride = (long long)src_fstride;
+        p.out = plane_set(c->d_mid, c->mid_off, c->mid_pitch, c->mid_size, B200VC_FMT_I420);
+        p.w = g.in_w;  p.h = g.in_h;  p.n_frames = nf;  p.mx = c->mx;
+        CU_TRY(c, launch_convert(p, B200VC_FMT_I420, site, st));
+        PlaneScaleParams q;
+        memset(&q, 0, sizeof q);
+        for (int i = 0; i < 3; i++) { q.src[i] = c->d_mid + c->mid_off[i];  q.src_pitch[i] = (long long)c->mid_pitch[i]; }
+        q.src_frame_stride = (long long)c->mid_size;
+        q.out = out;
+        for (int i = 0; i < 3; i++) if (q.out.p[i]) q.out.p[i] += (size_t)f0 * out.frame_stride;
+        q.tab = c->tab;
+        q.in_w = g.in_w;  q.in_h = g.in_h;  q.out_w = g.out_w;  q.out_h = g.out_h;  q.n_frames = nf;
+        q.box2x2 = g.scale_mode == B200VC_SCALE_BOX_2X2;
+        CU_TRY(c, launch_plane_scale(q, g.out_format, st));
+        c->stats.kernel_launches += 2;
+    }
+    return B200VC_OK;
+}
+
+void destroy_locked(b200vc_ctx *c)
+{
+    cudaSetDevice(c->cfg.device);
+    if (c->s_h2d) cudaStreamSynchronize(c->s_h2d);
+    if (c->s_k) cudaStreamSynchronize(c->s_k);
+    if (c->s_d2h) cudaStreamSynchronize(c->s_d2h);
+    for (Session &s : c->sessions) {
+        cudaFree(s.d_in[0]);  cudaFree(s.d_in[1]);
+        if (s.ev_kernel) cudaEventDestroy(s.ev_kernel);
+    }
+    for (Slot &s : c->slots) {
+        cudaFree(s.d_out);
+        if (s.h_in) cudaFreeHost(s.h_in);
+        if (s.h_out) cudaFreeHost(s.h_out);
+        if (s.done) cudaEventDestroy(s.done);
+    }
+    for (cudaEvent_t e : c->ev_band_h2d) cudaEventDestroy(e);
+    for (cudaEvent_t e : c->ev_band_k) cudaEventDestroy(e);
+    for (const HostReg &r : c->registered) cudaHostUnregister(const_cast<void *>(r.base));
+    cudaFree(c->d_taps);
+    cudaFree(c->d_mid);
+    if (c->s_h2d) cudaStreamDestroy(c->s_h2d);
+    if (c->s_k) cudaStreamDestroy(c->s_k);
+    if (c->s_d2h) cudaStreamDestroy(c->s_d2h);
+    cudaGetLastError();
+}
+
+int create_impl(b200vc_ctx *c)
+{
+    b200vc_config &g = c->cfg;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(c, B200VC_ERR_NO_DEVICE, "no CUDA device is visible; libb200vc has no CPU fallback");
+    }
+    if (g.device < 0 || g.device >= ndev)
+        return fail(c, B200VC_ERR_INVALID_ARG, "device %d out of range (0..%d)", g.device, ndev - 1);
+    CU_TRY(c, cudaSetDevice(g.device));
+    CU_TRY(c, cudaGetDeviceProperties(&c->prop, g.device));
+    if (c->prop.major != 10)
+        return fail(c, B200VC_ERR_NO_DEVICE, "device %d (%s, sm_%d%d) is not sm_100: this library carries sm_100a code only",
+                    g.device, c->prop.name, c->prop.major, c->prop.minor);
+
+    c->mx = make_matrix(g.matrix, g.range);
+    c->scaling = g.in_w != g.out_w || g.in_h != g.out_h;
+    c->mb_w = (g.in_w + 15) / 16;
+    c->mb_h = (g.in_h + 15) / 16;
+
+    CU_TRY(c, cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));
+    CU_TRY(c, cudaStreamCreateWithFlags(&c->s_k, cudaStreamNonBlocking));
+    CU_TRY(c, cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking));
+    c->ev_band_h2d.resize(g.n_bands);
+    c->ev_band_k.resize(g.n_bands);
+    for (int i = 0; i < g.n_bands; i++) {
+        CU_TRY(c, cudaEventCreateWithFlags(&c->ev_band_h2d[i], cudaEventDisableTiming));
+        CU_TRY(c, cudaEventCreateWithFlags(&c->ev_band_k[i], cudaEventDisableTiming));
+    }
+
+    // library-owned device frames: rows padded to 256 bytes
+    c->d_in_pitch = ru((size_t)g.in_w * 4, 256);
+    c->d_in_size = c->d_in_pitch * g.in_h;
+    {
+        const size_t yp = ru(g.out_w, 256), cp = g.out_format == B200VC_FMT_NV12 ? yp : ru(g.out_w / 2, 256);
+        c->d_pitch[0] = yp;  c->d_pitch[1] = cp;  c->d_pitch[2] = g.out_format == B200VC_FMT_NV12 ? 0 : cp;
+        c->d_off[0] = 0;  c->d_off[1] = yp * g.out_h;
+        c->d_off[2] = g.out_format == B200VC_FMT_NV12 ? 0 : c->d_off[1] + cp * (g.out_h / 2);
+        c->d_out_size = ru(c->d_off[1] + cp * (g.out_h / 2) * (g.out_format == B200VC_FMT_NV12 ? 1 : 2), 256);
+    }
+    const size_t dmg_bytes = ru((size_t)c->mb_w * c->mb_h, 256);
+
+    c->sessions.resize(g.max_sessions);
+    for (Session &s : c->sessions) {
+        CU_TRY(c, cudaMalloc(&s.d_in[0], c->d_in_size));
+        CU_TRY(c, cudaMalloc(&s.d_in[1], c->d_in_size));
+        CU_TRY(c, cudaEventCreateWithFlags(&s.ev_kernel, cudaEventDisableTiming));
+    }
+    c->slots.resize(std::max(g.n_inflight, g.max_sessions));
+    for (Slot &s : c->slots) {
+        CU_TRY(c, cudaMalloc(&s.d_out, c->d_out_size + dmg_bytes));
+        s.d_dmg = s.d_out + c->d_out_size;
+        CU_TRY(c, cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+    }
+
+    if (c->scaling) {
+        std::vector<Tap> hy, vy, hc, vc;
+        if (g.scale_mode == B200VC_SCALE_BOX_2X2) {
+            build_box_taps(g.out_w, hy);  build_box_taps(g.out_h, vy);
+            build_box_taps(g.out_w / 2, hc);  build_box_taps(g.out_h / 2, vc);
+        } else {
+            build_h_taps(g.in_w, g.out_w, hy);  build_v_taps(g.in_h, g.out_h, vy);
+            build_h_taps(g.in_w / 2, g.out_w / 2, hc);  build_v_taps(g.in_h / 2, g.out_h / 2, vc);
+        }
+        const size_t n = hy.size() + vy.size() + hc.size() + vc.size();
+        CU_TRY(c, cudaMalloc(&c->d_taps, n * sizeof(Tap)));
+        Tap *d = c->d_taps;
+        c->tab.hy = d;  CU_TRY(c, cudaMemcpy(d, hy.data(), hy.size() * sizeof(Tap), cudaMemcpyHostToDevice));  d += hy.size();
+        c->tab.vy = d;  CU_TRY(c, cudaMemcpy(d, vy.data(), vy.size() * sizeof(Tap), cudaMemcpyHostToDevice));  d += vy.size();
+        c->tab.hc = d;  CU_TRY(c, cudaMemcpy(d, hc.data(), hc.size() * sizeof(Tap), cudaMemcpyHostToDevice));  d += hc.size();
+        c->tab.vc = d;  CU_TRY(c, cudaMemcpy(d, vc.data(), vc.size() * sizeof(Tap), cudaMemcpyHostToDevice));
+
+        fused_box(g, hy, vy, hc, vc, c->box_w, c->box_h);
+        c->smem_bytes = fused_scale_smem_bytes(c->box_w, c->box_h);
+        const bool fits = c->box_w <= 256 && c->box_h <= 256 &&
+                          c->smem_bytes + 1024 <= (size_t)c->prop.sharedMemPerBlockOptin;
+        c->path = (fits && !(g.flags & B200VC_FLAG_FORCE_TWO_PASS)) ? 1 : 2;
+        if (c->path == 1) {
+            void *fn = nullptr;
+            cudaDriverEntryPointQueryResult qres;
+            CU_TRY(c, cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+            if (!fn || qres != cudaDriverEntryPointSuccess)
+                return fail(c, B200VC_ERR_CUDA, "the driver does not export cuTensorMapEncodeTiled");
+            c->encode_tiled = (PFN_cuTensorMapEncodeTiled_v12000)fn;
+            CU_TRY(c, fused_scale_prepare(c->smem_bytes));
+        } else {
+            const size_t yp = ru(g.in_w, 256), cp = ru(g.in_w / 2, 256);
+            c->mid_pitch[0] = yp;  c->mid_pitch[1] = cp;  c->mid_pitch[2] = cp;
+            c->mid_off[0] = 0;  c->mid_off[1] = yp * g.in_h;  c->mid_off[2] = c->mid_off[1] + cp * (g.in_h / 2);
+            c->mid_size = ru(c->mid_off[2] + cp * (g.in_h / 2), 256);
+            c->mid_frames = std::max(1, std::min(g.max_sessions, 8));
+            CU_TRY(c, cudaMalloc(&c->d_mid, c->mid_size * c->mid_frames));
+        }
+    }
+    CU_TRY(c, cudaDeviceSynchronize());
+    return B200VC_OK;
+}
+
+// Copy `rows` rows of `bytes` each between host buffers with different pitches.
+void copy_rows(uint8_t *dst, size_t dpitch, const uint8_t *src, size_t spitch, size_t bytes, int rows)
+{
+    if (dpitch == bytes && spitch == bytes) {
+        memcpy(dst, src, bytes * rows);
+        return;
+    }
+    for (int r = 0; r < rows; r++) memcpy(dst + r * dpitch, src + r * spitch, bytes);
+}
+
+int validate_frame(b200vc_ctx *c, const b200vc_frame *f)
+{
+    const b200vc_config &g = c->cfg;
+    if (!f || !f->bgrx || !f->planes[0] || !f->planes[1] || (g.out_format == B200VC_FMT_I420 && !f->planes[2]))
+        return fail(c, B200VC_ERR_INVALID_ARG, "frame, input or plane pointer is NULL");
+    if (f->session < 0 || f->session >= g.max_sessions)
+        return fail(c, B200VC_ERR_INVALID_ARG, "session %d out of range (max_sessions %d)", f->session, g.max_sessions);
+    if (f->in_pitch < (size_t)g.in_w * 4)
+        return fail(c, B200VC_ERR_INVALID_ARG, "input pitch %zu is smaller than a row (%d bytes)", f->in_pitch, g.in_w * 4);
+    const size_t cw = g.out_format == B200VC_FMT_NV12 ? (size_t)g.out_w : (size_t)g.out_w / 2;
+    if (f->pitches[0] < (size_t)g.out_w || f->pitches[1] < cw || (g.out_format == B200VC_FMT_I420 && f->pitches[2] < cw))
+        return fail(c, B200VC_ERR_INVALID_ARG, "an output pitch is smaller than its row");
+    if (f->damage && !(g.flags & B200VC_FLAG_DAMAGE_MAP))
+        return fail(c, B200VC_ERR_INVALID_ARG, "a damage map was requested but the context was created without B200VC_FLAG_DAMAGE_MAP");
+    return B200VC_OK;
+}
+
+// Enqueue one frame on the three streams. bands > 1 pipelines H2D / kernel / D2H inside the frame.
+int submit_locked(b200vc_ctx *c, const b200vc_frame *f, int bands, uint64_t *ticket)
+{
+    int rc = validate_frame(c, f);
+    if (rc) return rc;
+    const b200vc_config &g = c->cfg;
+    Slot &slot = c->slots[c->next_slot];
+    if (slot.busy && (rc = collect_slot(c, slot)) != 0) return rc;
+    c->next_slot = (c->next_slot + 1) % (int)c->slots.size();
+    Session &ss = c->sessions[f->session];
+
+    const size_t row_bytes = (size_t)g.in_w * 4;
+    const int n_planes = g.out_format == B200VC_FMT_NV12 ? 2 : 3;
+    const size_t out_row_bytes[3] = { (size_t)g.out_w, g.out_format == B200VC_FMT_NV12 ? (size_t)g.out_w : (size_t)g.out_w / 2,
+                                      (size_t)g.out_w / 2 };
+    const int out_rows[3] = { g.out_h, g.out_h / 2, g.out_h / 2 };
+
+    // where do the host sides live?
+    bool in_pinned = is_pinned(f->bgrx);
+    if (!in_pinned && (g.flags & B200VC_FLAG_REGISTER_HOST))
+        in_pinned = ensure_registered(c, f->bgrx, f->in_pitch * (g.in_h - 1) + row_bytes);
+    bool out_pinned = true;
+    for (int i = 0; i < n_planes; i++) {
+        bool pin = is_pinned(f->planes[i]);
+        if (!pin && (g.flags & B200VC_FLAG_REGISTER_HOST))
+            pin = ensure_registered(c, f->planes[i], f->pitches[i] * (out_rows[i] - 1) + out_row_bytes[i]);
+        out_pinned = out_pinned && pin;
+    }
+    if (f->damage && !is_pinned(f->damage)) out_pinned = false;
+    if (!in_pinned && !slot.h_in) CU_TRY(c, cudaMallocHost(&slot.h_in, c->d_in_size));
+    if (!out_pinned && !slot.h_out) CU_TRY(c, cudaMallocHost(&slot.h_out, c->d_out_size + ru((size_t)c->mb_w * c->mb_h, 256)));
+
+    if (c->path != 0 || bands < 1) bands = 1;
+    bands = std::min(bands, (int)c->ev_band_h2d.size());
+    bands = std::min(bands, std::max(1, c->mb_h));
+
+    uint8_t *d_cur = ss.d_in[ss.cur];
+    const uint8_t *d_prev = (f->damage && ss.have_prev) ? ss.d_in[ss.cur ^ 1] : nullptr;
+    const PlaneSet out = plane_set(slot.d_out, c->d_off, c->d_pitch, 0, g.out_format);
+
+    // the copy engine must not overwrite a frame the previous kernel of this session still reads
+    if (ss.ev_valid) CU_TRY(c, cudaStreamWaitEvent(c->s_h2d, ss.ev_kernel, 0));
+    if (f->damage && !d_prev)
+        CU_TRY(c, cudaMemsetAsync(slot.d_dmg, 1, (size_t)c->mb_w * c->mb_h, c->s_k));
+
+    const int mb_rows_per_band = (c->mb_h + bands - 1) / bands;
+    for (int b = 0; b < bands; b++) {
+        const int row0 = b * mb_rows_per_band * 16;
+        if (row0 >= g.in_h) break;
+        const int rows = std::min(mb_rows_per_band * 16, g.in_h - row0);
+        // host -> pinned (only for pageable input), then H2D
+        const uint8_t *hsrc = (const uint8_t *)f->bgrx + (size_t)row0 * f->in_pitch;
+        size_t hpitch = f->in_pitch;
+        if (!in_pinned) {
+            copy_rows(slot.h_in + (size_t)row0 * row_bytes, row_bytes, hsrc, f->in_pitch, row_bytes, rows);
+            hsrc = slot.h_in + (size_t)row0 * row_bytes;
+            hpitch = row_bytes;
+            c->stats.staged_in_bytes += row_bytes * rows;
+        }
+        CU_TRY(c, cudaMemcpy2DAsync(d_cur + (size_t)row0 * c->d_in_pitch, c->d_in_pitch, hsrc, hpitch, row_bytes, rows,
+                                    cudaMemcpyHostToDevice, c->s_h2d));
+        c->stats.h2d_bytes += row_bytes * rows;
+        if (c->path != 0) continue;      // scaled paths launch once, after the whole frame is up
+        CU_TRY(c, cudaEventRecord(c->ev_band_h2d[b], c->s_h2d));
+        CU_TRY(c, cudaStreamWaitEvent(c->s_k, c->ev_band_h2d[b], 0));
+        rc = enqueue_kernels(c, d_cur, c->d_in_pitch, 0, d_prev, c->d_in_pitch, 0, out, d_prev ? slot.d_dmg : nullptr, 0,
+                             row0, rows, 1, c->s_k);
+        if (rc) return rc;
+        CU_TRY(c, cudaEventRecord(c->ev_band_k[b], c->s_k));
+        CU_TRY(c, cudaStreamWaitEvent(c->s_d2h, c->ev_band_k[b], 0));
+        // D2H of this band's rows of every plane
+        for (int i = 0; i < n_planes; i++) {
+            const int pr0 = i ? row0 / 2 : row0, prs = i ? rows / 2 : rows;
+            uint8_t *hdst = out_pinned ? (uint8_t *)f->planes[i] + (size_t)pr0 * f->pitches[i]
+                                       : slot.h_out + c->d_off[i] + (size_t)pr0 * c->d_pitch[i];
+            const size_t hp = out_pinned ? f->pitches[i] : c->d_pitch[i];
+            CU_TRY(c, cudaMemcpy2DAsync(hdst, hp, slot.d_out + c->d_off[i] + (size_t)pr0 * c->d_pitch[i], c->d_pitch[i],
+                                        out_row_bytes[i], prs, cudaMemcpyDeviceToHost, c->s_d2h));
+            c->stats.d2h_bytes += out_row_bytes[i] * prs;
+        }
+    }
+    if (c->path != 0) {
+        CU_TRY(c, cudaEventRecord(c->ev_band_h2d[0], c->s_h2d));
+        CU_TRY(c, cudaStreamWaitEvent(c->s_k, c->ev_band_h2d[0], 0));
+        rc = enqueue_kernels(c, d_cur, c->d_in_pitch, 0, nullptr, 0, 0, out, nullptr, 0, 0, g.in_h, 1, c->s_k);
+        if (rc) return rc;
+        CU_TRY(c, cudaEventRecord(c->ev_band_k[0], c->s_k));
+        CU_TRY(c, cudaStreamWaitEvent(c->s_d2h, c->ev_band_k[0], 0));
+        for (int i = 0; i < n_planes; i++) {
+            uint8_t *hdst = out_pinned ? (uint8_t *)f->planes[i] : slot.h_out + c->d_off[i];
+            const size_t hp = out_pinned ? f->pitches[i] : c->d_pitch[i];
+            CU_TRY(c, cudaMemcpy2DAsync(hdst, hp, slot.d_out + c->d_off[i], c->d_pitch[i], out_row_bytes[i], out_rows[i],
+                                        cudaMemcpyDeviceToHost, c->s_d2h));
+            c->stats.d2h_bytes += out_row_bytes[i] * out_rows[i];
+        }
+    }
+    CU_TRY(c, cudaEventRecord(ss.ev_kernel, c->s_k));
+    ss.ev_valid = true;
+    if (f->damage) {
+        uint8_t *hdst = out_pinned ? f->damage : slot.h_out + c->d_out_size;
+        CU_TRY(c, cudaStreamWaitEvent(c->s_d2h, ss.ev_kernel, 0));
+        CU_TRY(c, cudaMemcpyAsync(hdst, slot.d_dmg, (size_t)c->mb_w * c->mb_h, cudaMemcpyDeviceToHost, c->s_d2h));
+        c->stats.d2h_bytes += (size_t)c->mb_w * c->mb_h;
+    }
+    CU_TRY(c, cudaEventRecord(slot.done, c->s_d2h));
+
+    if (g.flags & B200VC_FLAG_DAMAGE_MAP) {
+        ss.cur ^= 1;               // this frame becomes the next one's "previous"; no copy
+        ss.have_prev = true;
+    }
+    slot.busy = true;
+    slot.staged_out = !out_pinned;
+    slot.frame = *f;
+    slot.ticket = c->next_ticket++;
+    if (ticket) *ticket = slot.ticket;
+    c->stats.frames += 1;
+    return B200VC_OK;
+}
+
+int collect_slot(b200vc_ctx *c, Slot &s)
+{
+    if (!s.busy) return B200VC_OK;
+    CU_TRY(c, cudaEventSynchronize(s.done));
+    s.busy = false;
+    if (s.staged_out) {
+        const b200vc_config &g = c->cfg;
+        const int n_planes = g.out_format == B200VC_FMT_NV12 ? 2 : 3;
+        const size_t rb[3] = { (size_t)g.out_w, g.out_format == B200VC_FMT_NV12 ? (size_t)g.out_w : (size_t)g.out_w / 2,
+                               (size_t)g.out_w / 2 };
+        const int rows[3] = { g.out_h, g.out_h / 2, g.out_h / 2 };
+        for (int i = 0; i < n_planes; i++) {
+            copy_rows((uint8_t *)s.frame.planes[i], s.frame.pitches[i], s.h_out + c->d_off[i], c->d_pitch[i], rb[i], rows[i]);
+            c->stats.staged_out_bytes += rb[i] * rows[i];
+        }
+        if (s.frame.damage) memcpy(s.frame.damage, s.h_out + c->d_out_size, (size_t)c->mb_w * c->mb_h);
+    }
+    return B200VC_OK;
+}
+
+bool aligned16(const void *p) { return ((uintptr_t)p & 15) == 0; }
+
+}  // namespace
+
+// ================================================================================================
+// C ABI
+// ================================================================================================
+extern "C" {
+
+int b200vc_version(void) { return B200VC_VERSION_MAJOR * 100 + B200VC_VERSION_MINOR; }
+
+const char *b200vc_status_string(int s)
+{
+    switch (s) {
+    case B200VC_OK: return "ok";
+    case B200VC_ERR_INVALID_ARG: return "invalid argument";
+    case B200VC_ERR_UNSUPPORTED: return "caps not supported";
+    case B200VC_ERR_NOT_NEGOTIATED: return "not negotiated";
+    case B200VC_ERR_CUDA: return "CUDA error";
+    case B200VC_ERR_NO_DEVICE: return "no usable sm_100 device";
+    case B200VC_ERR_ALIGNMENT: return "pointer or pitch not 16-byte aligned";
+    case B200VC_ERR_NOMEM: return "out of memory";
+    case B200VC_ERR_BAD_TICKET: return "unknown ticket";
+    default: return "unknown status";
+    }
+}
+
+int b200vc_default_colorimetry(int out_h, int *matrix, int *range, int *chroma_site)
+{
+    if (out_h <= 0) return B200VC_ERR_INVALID_ARG;
+    // > 576 lines -> bt709 limited, chroma-site mpeg2; else bt601 limited, jpeg.
+    // (bt2020 for >= 2160 lines exists only in newer GStreamer and is not offered by this element.)
+    const bool hd = out_h > 576;
+    if (matrix) *matrix = hd ? B200VC_MATRIX_BT709 : B200VC_MATRIX_BT601;
+    if (range) *range = B200VC_RANGE_LIMITED;
+    if (chroma_site) *chroma_site = hd ? B200VC_SITE_H_COSITED : B200VC_SITE_NONE;
+    return B200VC_OK;
+}
+
+size_t b200vc_default_layout(int format, int w, int h, size_t offsets[3], size_t pitches[3])
+{
+    if (w <= 0 || h <= 0 || !offsets || !pitches) return 0;
+    const size_t h2 = ru(h, 2), yp = ru(w, 4);
+    offsets[0] = 0;  pitches[0] = yp;  offsets[1] = yp * h2;
+    if (format == B200VC_FMT_NV12) {
+        pitches[1] = yp;  offsets[2] = 0;  pitches[2] = 0;
+        return offsets[1] + yp * (h2 / 2);
+    }
+    if (format != B200VC_FMT_I420) return 0;
+    const size_t cp = ru(ru(w, 2) / 2, 4);
+    pitches[1] = pitches[2] = cp;
+    offsets[2] = offsets[1] + cp * (h2 / 2);
+    return offsets[2] + cp * (h2 / 2);
+}
+
+int b200vc_check_config(const b200vc_config *cfg)
+{
+    std::string why;
+    int rc = check_config(cfg, &why);
+    if (rc) g_create_error = why;
+    return rc;
+}
+
+int b200vc_create(const b200vc_config *cfg, b200vc_ctx **out)
+{
+    if (!out) return fail(nullptr, B200VC_ERR_INVALID_ARG, "out pointer is NULL");
+    *out = nullptr;
+    std::string why;
+    int rc = check_config(cfg, &why);
+    if (rc) return fail(nullptr, rc, "%s", why.c_str());
+    b200vc_ctx *c = new (std::nothrow) b200vc_ctx();
+    if (!c) return fail(nullptr, B200VC_ERR_NOMEM, "out of host memory");
+    c->cfg = *cfg;
+    if (c->cfg.max_sessions == 0) c->cfg.max_sessions = 1;
+    if (c->cfg.n_inflight == 0) c->cfg.n_inflight = 3;
+    if (c->cfg.n_bands == 0) c->cfg.n_bands = 4;
+    memset(&c->stats, 0, sizeof c->stats);
+    rc = create_impl(c);
+    if (rc) {
+        g_create_error = c->err;
+        destroy_locked(c);
+        delete c;
+        return rc;
+    }
+    *out = c;
+    return B200VC_OK;
+}
+
+int b200vc_destroy(b200vc_ctx *c)
+{
+    if (!c) return B200VC_ERR_INVALID_ARG;
+    {
+        std::lock_guard<std::mutex> lk(c->mu);
+        for (Slot &s : c->slots) collect_slot(c, s);
+        destroy_locked(c);
+    }
+    delete c;
+    return B200VC_OK;
+}
+
+const char *b200vc_last_error(const b200vc_ctx *c)
+{
+    return c ? c->err.c_str() : g_create_error.c_str();
+}
+
+int b200vc_get_info(const b200vc_ctx *c, b200vc_info *info)
+{
+    if (!c || !info) return B200VC_ERR_INVALID_ARG;
+    memset(info, 0, sizeof *info);
+    info->path = c->path;
+    info->tile_w = c->path == 1 ? K2_TILE_W : K1_TILE_W;
+    info->tile_h = c->path == 1 ? K2_TILE_H : K1_TILE_H;
+    info->box_w = c->box_w;  info->box_h = c->box_h;
+    info->smem_bytes = c->path == 1 ? (int)c->smem_bytes : 3 * 1024 + 32;
+    info->sm_count = c->prop.multiProcessorCount;
+    info->cc_major = c->prop.major;  info->cc_minor = c->prop.minor;
+    snprintf(info->device_name, sizeof info->device_name, "%.63s", c->prop.name);
+    return B200VC_OK;
+}
+
+int b200vc_get_stats(const b200vc_ctx *c, b200vc_stats *st)
+{
+    if (!c || !st) return B200VC_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(c->mu);
+    *st = c->stats;
+    return B200VC_OK;
+}
+
+int b200vc_reset(b200vc_ctx *c, int session)
+{
+    if (!c) return B200VC_ERR_NOT_NEGOTIATED;
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (session >= (int)c->sessions.size()) return fail(c, B200VC_ERR_INVALID_ARG, "session %d out of range", session);
+    for (int i = 0; i < (int)c->sessions.size(); i++)
+        if (session < 0 || session == i) c->sessions[i].have_prev = false;
+    return B200VC_OK;
+}
+
+int b200vc_submit(b200vc_ctx *c, const b200vc_frame *f, uint64_t *ticket)
+{
+    if (!c) return B200VC_ERR_NOT_NEGOTIATED;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU_TRY(c, cudaSetDevice(c->cfg.device));
+    return submit_locked(c, f, 1, ticket);
+}
+
+int b200vc_collect(b200vc_ctx *c, uint64_t ticket)
+{
+    if (!c) return B200VC_ERR_NOT_NEGOTIATED;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU_TRY(c, cudaSetDevice(c->cfg.device));
+    if (ticket == 0 || ticket >= c->next_ticket) return fail(c, B200VC_ERR_BAD_TICKET, "ticket %llu was never issued", (unsigned long long)ticket);
+    for (Slot &s : c->slots)
+        if (s.busy && s.ticket == ticket) return collect_slot(c, s);
+    return B200VC_OK;   // already collected (its slot was reused or collected before)
+}
+
+int b200vc_convert(b200vc_ctx *c, const void *bgrx, size_t in_pitch, void *const planes[3], const size_t pitches[3],
+                   uint8_t *damage)
+{
+    if (!c) return B200VC_ERR_NOT_NEGOTIATED;
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (!planes || !pitches) return fail(c, B200VC_ERR_INVALID_ARG, "planes/pitches is NULL");
+    CU_TRY(c, cudaSetDevice(c->cfg.device));
+    b200vc_frame f;
+    memset(&f, 0, sizeof f);
+    f.bgrx = bgrx;  f.in_pitch = in_pitch;
+    const int np = c->cfg.out_format == B200VC_FMT_NV12 ? 2 : 3;
+    for (int i = 0; i < np; i++) { f.planes[i] = planes[i];  f.pitches[i] = pitches[i]; }
+    f.damage = damage;  f.session = 0;
+    int rc = submit_locked(c, &f, c->cfg.n_bands, nullptr);
+    if (rc) return rc;
+    for (Slot &s : c->slots)
+        if ((rc = collect_slot(c, s)) != 0) return rc;
+    return B200VC_OK;
+}
+
+int b200vc_convert_batch(b200vc_ctx *c, const b200vc_frame *frames, int n)
+{
+    if (!c) return B200VC_ERR_NOT_NEGOTIATED;
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (!frames || n < 0) return fail(c, B200VC_ERR_INVALID_ARG, "frames is NULL or n < 0");
+    CU_TRY(c, cudaSetDevice(c->cfg.device));
+    int rc;
+    for (int i = 0; i < n; i++)
+        if ((rc = submit_locked(c, &frames[i], 1, nullptr)) != 0) return rc;
+    for (Slot &s : c->slots)
+        if ((rc = collect_slot(c, s)) != 0) return rc;
+    return B200VC_OK;
+}
+
+int b200vc_host_alloc(size_t bytes, void **out)
+{
+    if (!out || !bytes) return B200VC_ERR_INVALID_ARG;
+    *out = nullptr;
+    cudaError_t e = cudaMallocHost(out, bytes);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        g_create_error = std::string("cudaMallocHost failed: ") + cudaGetErrorString(e);
+        return e == cudaErrorMemoryAllocation ? B200VC_ERR_NOMEM : B200VC_ERR_CUDA;
+    }
+    return B200VC_OK;
+}
+
+int b200vc_host_free(void *p)
+{
+    if (!p) return B200VC_OK;
+    return cudaFreeHost(p) == cudaSuccess ? B200VC_OK : B200VC_ERR_CUDA;
+}
+
+int b200vc_convert_device(b200vc_ctx *c, const b200vc_device_frames *d, void *cuda_stream)
+{
+    if (!c) return B200VC_ERR_NOT_NEGOTIATED;
+    std::lock_guard<std::mutex> lk(c->mu);
+    const b200vc_config &g = c->cfg;
+    if (!d || !d->bgrx || !d->planes[0] || !d->planes[1] || (g.out_format == B200VC_FMT_I420 && !d->planes[2]) || d->n_frames < 1)
+        return fail(c, B200VC_ERR_INVALID_ARG, "device frame set is NULL, has a NULL plane or n_frames < 1");
+    if (d->n_frames > 65535) return fail(c, B200VC_ERR_INVALID_ARG, "at most 65535 frames per launch");
+    if (d->damage && (!(g.flags & B200VC_FLAG_DAMAGE_MAP) || c->path != 0))
+        return fail(c, B200VC_ERR_INVALID_ARG, "a damage map was requested but the context was created without B200VC_FLAG_DAMAGE_MAP");
+    const int np = g.out_format == B200VC_FMT_NV12 ? 2 : 3;
+    bool ok = aligned16(d->bgrx) && d->in_pitch % 16 == 0 && d->in_frame_stride % 16 == 0 && d->out_frame_stride % 16 == 0;
+    for (int i = 0; i < np; i++) ok = ok && aligned16(d->planes[i]) && d->pitches[i] % 16 == 0;
+    if (d->prev) ok = ok && aligned16(d->prev) && d->prev_pitch % 16 == 0 && d->prev_frame_stride % 16 == 0;
+    if (!ok) return fail(c, B200VC_ERR_ALIGNMENT, "device pointers, pitches and frame strides must be multiples of 16 bytes");
+    const size_t cw = g.out_format == B200VC_FMT_NV12 ? (size_t)g.out_w : (size_t)g.out_w / 2;
+    if (d->in_pitch < (size_t)g.in_w * 4 || d->pitches[0] < (size_t)g.out_w || d->pitches[1] < cw ||
+        (np == 3 && d->pitches[2] < cw))
+        return fail(c, B200VC_ERR_INVALID_ARG, "a pitch is smaller than its row");
+    if (d->n_frames > 1 && (d->in_frame_stride == 0 || d->out_frame_stride == 0))
+        return fail(c, B200VC_ERR_INVALID_ARG, "frame strides are required for n_frames > 1");
+
+    CU_TRY(c, cudaSetDevice(g.device));
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    PlaneSet out;
+    for (int i = 0; i < 3; i++) { out.p[i] = i < np ? (uint8_t *)d->planes[i] : nullptr;  out.pitch[i] = i < np ? (long long)d->pitches[i] : 0; }
+    out.frame_stride = (long long)d->out_frame_stride;
+    if (d->damage && !d->prev) {
+        if (d->n_frames > 1 && d->damage_frame_stride != (size_t)c->mb_w * c->mb_h) {
+            for (int i = 0; i < d->n_frames; i++)
+                CU_TRY(c, cudaMemsetAsync(d->damage + (size_t)i * d->damage_frame_stride, 1, (size_t)c->mb_w * c->mb_h, st));
+        } else {
+            CU_TRY(c, cudaMemsetAsync(d->damage, 1, (size_t)c->mb_w * c->mb_h * d->n_frames, st));
+        }
+    }
+    int rc = enqueue_kernels(c, (const uint8_t *)d->bgrx, d->in_pitch, d->in_frame_stride,
+                             (const uint8_t *)d->prev, d->prev_pitch, d->prev_frame_stride, out,
+                             d->prev ? d->damage : nullptr, d->damage_frame_stride, 0, g.in_h, d->n_frames, st);
+    if (rc) return rc;
+    c->stats.frames += d->n_frames;
+    return B200VC_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,92 @@
+// device_utils.cuh — per-pixel arithmetic shared by the kernels (sm_100a).
+//
+// Bit-exact restatement, for the GPU, of the integer steps in SURVEY.md Appendix A:
+//   A.2  (c . [R,G,B] + off) >> 8 with no rounding term     -> dp4a, result taken from byte 1
+//   A.4  chroma 4:4:4 -> 4:2:0, horizontal then vertical, two roundings -> 2x16-bit SIMD in a word
+#pragma once
+
+#include <stdint.h>
+#include "kernels.cuh"
+
+namespace b200vc {
+
+__device__ __forceinline__ uint32_t dp4a_uu(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d;
+    asm("dp4a.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+// a: four unsigned bytes (the pixel), b: four signed bytes (coefficients)
+__device__ __forceinline__ uint32_t dp4a_us(uint32_t a, uint32_t b, uint32_t c)
+{
+    int32_t d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"((int32_t)c));
+    return (uint32_t)d;
+}
+
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel)
+{
+    return __byte_perm(a, b, sel);
+}
+
+// streaming 16-byte load: read once, do not keep in L1
+__device__ __forceinline__ uint4 ldg_stream_v4(const void *p)
+{
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+
+__device__ __forceinline__ uint2 ldg_stream_v2(const void *p)
+{
+    uint2 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+    return r;
+}
+
+__device__ __forceinline__ uint32_t ldg_stream_u32(const void *p)
+{
+    uint32_t r;
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
+    return r;
+}
+
+// Y sum of one pixel; the 8-bit result is byte 1 of the return value (sum is in 0..65535).
+__device__ __forceinline__ uint32_t luma_sum(uint32_t pix, const Matrix &m)
+{
+    return dp4a_uu(pix, m.cy, m.oy);
+}
+
+// Four luma sums -> four Y bytes in pixel order.
+__device__ __forceinline__ uint32_t pack_luma4(uint32_t s0, uint32_t s1, uint32_t s2, uint32_t s3)
+{
+    return prmt(prmt(s0, s1, 0x0051), prmt(s2, s3, 0x0051), 0x5410);
+}
+
+// (u,v) of one pixel as two 16-bit lanes: u in bits 0..7, v in bits 16..23.
+template <bool NEG>
+__device__ __forceinline__ uint32_t chroma_pair(uint32_t pix, const Matrix &m)
+{
+    uint32_t su = dp4a_us(pix, m.cu, m.ou);
+    uint32_t sv = dp4a_us(pix, m.cv, m.ov);
+    uint32_t p = prmt(su, sv, 0x6521);      // bytes: su.1, su.2 (=0), sv.1, sv.2 (=0)
+    return NEG ? (p ^ 0x00FF00FFu) : p;
+}
+
+constexpr uint32_t LANES8 = 0x00FF00FFu;
+
+// video_chroma_down_h2_u8 / v2: (a + b + 1) >> 1 on both lanes
+__device__ __forceinline__ uint32_t avg2(uint32_t a, uint32_t b)
+{
+    return ((a + b + 0x00010001u) >> 1) & LANES8;
+}
+
+// video_chroma_down_h2_cs_u8: (l + 2c + r + 2) >> 2 on both lanes
+__device__ __forceinline__ uint32_t filt121(uint32_t l, uint32_t c, uint32_t r)
+{
+    return ((l + 2u * c + r + 0x00020002u) >> 2) & LANES8;
+}
+
+}  // namespace b200vc

@@ -1,0 +1,322 @@
+// k2_scale.cu — K2: BGRx -> I420/NV12 with the bilinear downscale fused into the same pass, and
+// the general two-pass plane scaler (sm_100a).
+//
+// Replaces `videoconvert ! videoscale` (GstVideoScale -> GstVideoScaler 2-tap "lq" path) on the
+// reference's software-encoder fallback (/root/reference Dockerfile:467-471, README.md:21).
+// Semantics, SURVEY.md Appendix B.1: conversion and chroma downsampling happen at the INPUT size,
+// then every plane is scaled on its own (horizontal 2-tap with an 8-bit fraction, then vertical
+// 2-tap with a 6-bit tap). The fused kernel reproduces that two-stage result bit for bit without
+// ever writing the full-size I420 intermediate to HBM:
+//
+//   phase 0  one thread issues a TMA tiled load (cp.async.bulk.tensor.3d) of the tile's source
+//            window — the rows and columns its output pixels depend on, halo included; pixels
+//            outside the frame are zero-filled by the TMA unit and never consumed — and the CTA
+//            waits on an mbarrier for the bytes to land in shared memory
+//   phase 1  convert the window: Y per pixel and the 4:2:0 (u,v) pair per 2x2 block, kept in
+//            shared memory (this is the "intermediate frame", tile-sized)
+//   phase 2  scale out of shared memory with host-built tap tables, store the output tile
+//
+// HBM roofline: algorithmic bytes per output frame = in_w*in_h*4 + out_w*out_h*1.5.
+#include "device_utils.cuh"
+
+namespace b200vc {
+
+namespace {
+
+constexpr int TW = K2_TILE_W;
+constexpr int TH = K2_TILE_H;
+
+__device__ __forceinline__ int tap_idx(Tap t) { return (int)(t & 0xffffu); }
+__device__ __forceinline__ int tap_frac(Tap t) { return (int)((t >> 16) & 0xffu); }
+__device__ __forceinline__ int tap_step(Tap t) { return (int)((t >> 24) & 1u); }
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p)
+{
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+// video_scale_h_2tap_1u8 (lq) then video_scale_v_2tap_u8 (lq) on one component
+__device__ __forceinline__ int lerp_h(int a, int b, int f) { return (a * (256 - f) + b * f) >> 8; }
+__device__ __forceinline__ int lerp_v(int a, int b, int p1)
+{
+    int d = a + (((b - a) * p1 + 32) >> 6);
+    return d < 0 ? 0 : (d > 255 ? 255 : d);
+}
+
+template <int FMT, int SITE, bool NEG>
+__global__ void __launch_bounds__(256)
+k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedScaleParams p)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ __align__(8) uint64_t s_bar;
+    __shared__ int s_org[2];
+
+    const int bw = p.box_w, bh = p.box_h;
+    uint32_t *s_src = reinterpret_cast<uint32_t *>(smem);                 // [bh][bw] pixels
+    uint8_t *s_yf = smem + (size_t)bw * bh * 4;                           // [bh][bw] luma
+    uint32_t *s_cf = reinterpret_cast<uint32_t *>(s_yf + (size_t)bw * bh); // [bh/2][bw/2] (u,v) pairs
+
+    const int tid = threadIdx.x;
+    const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH;
+    const int frame = blockIdx.z;
+
+    // ---- phase 0: source window origin, TMA load -------------------------------------------
+    if (tid == 0) {
+        const int hy0 = tap_idx(p.tab.hy[x0]);
+        const int uc0 = tap_idx(p.tab.hc[x0 >> 1]);
+        int sx = min(hy0, 2 * uc0 - (SITE ? 1 : 0));
+        sx &= ~1;                                         // even, may be -2 at the left frame edge
+        const int vy0 = tap_idx(p.tab.vy[y0]);
+        const int vc0 = tap_idx(p.tab.vc[y0 >> 1]);
+        const int sy = min(vy0, 2 * vc0) & ~1;
+        s_org[0] = sx;
+        s_org[1] = sy;
+
+        const uint32_t bar = smem_u32(&s_bar);
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        const uint32_t bytes = (uint32_t)bw * bh * 4;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+        asm volatile(
+            "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+            " [%0], [%1, {%2, %3, %4}], [%5];"
+            ::"r"(smem_u32(s_src)), "l"(reinterpret_cast<uint64_t>(&src_map)), "r"(sx), "r"(sy), "r"(frame), "r"(bar)
+            : "memory");
+    }
+    __syncthreads();
+    const int sx0 = s_org[0], sy0 = s_org[1];
+    {
+        const uint32_t bar = smem_u32(&s_bar);
+        uint32_t done = 0;
+        while (!done) {
+            asm volatile(
+                "{\n\t.reg .pred q;\n\t"
+                "mbarrier.try_wait.parity.shared::cta.b64 q, [%1], %2;\n\t"
+                "selp.u32 %0, 1, 0, q;\n\t}"
+                : "=r"(done) : "r"(bar), "r"(0u) : "memory");
+        }
+    }
+
+    // ---- phase 1: convert the window (4 columns x 2 lines per item) ------------------------------
+    const Matrix &m = p.mx;
+    const int items_x = bw >> 2, n_items = items_x * (bh >> 1);
+    for (int it = tid; it < n_items; it += 256) {
+        const int kx = it % items_x, ky = it / items_x;
+        const uint32_t *ra = s_src + (size_t)(2 * ky) * bw + 4 * kx;
+        const uint32_t *rb = ra + bw;
+        const uint4 a = *reinterpret_cast<const uint4 *>(ra);
+        const uint4 b = *reinterpret_cast<const uint4 *>(rb);
+
+        uint32_t ya4 = pack_luma4(luma_sum(a.x, m), luma_sum(a.y, m), luma_sum(a.z, m), luma_sum(a.w, m));
+        uint32_t yb4 = pack_luma4(luma_sum(b.x, m), luma_sum(b.y, m), luma_sum(b.z, m), luma_sum(b.w, m));
+        *reinterpret_cast<uint32_t *>(s_yf + (size_t)(2 * ky) * bw + 4 * kx) = ya4;
+        *reinterpret_cast<uint32_t *>(s_yf + (size_t)(2 * ky + 1) * bw + 4 * kx) = yb4;
+
+        const uint32_t pa0 = chroma_pair<NEG>(a.x, m), pa1 = chroma_pair<NEG>(a.y, m);
+        const uint32_t pa2 = chroma_pair<NEG>(a.z, m), pa3 = chroma_pair<NEG>(a.w, m);
+        const uint32_t pb0 = chroma_pair<NEG>(b.x, m), pb1 = chroma_pair<NEG>(b.y, m);
+        const uint32_t pb2 = chroma_pair<NEG>(b.z, m), pb3 = chroma_pair<NEG>(b.w, m);
+        uint32_t c0, c1;
+        if (SITE == 0) {
+            c0 = avg2(avg2(pa0, pa1), avg2(pb0, pb1));
+            c1 = avg2(avg2(pa2, pa3), avg2(pb2, pb3));
+        } else {
+            const int ac = sx0 + 4 * kx;                  // absolute column of pixel 0 (even)
+            // left neighbours: column 0 takes itself; the window's first item has none (its
+            // first chroma column is halo and is never consumed)
+            uint32_t la = pa0, lb = pb0;
+            if (ac != 0 && kx > 0) {
+                la = chroma_pair<NEG>(ra[-1], m);
+                lb = chroma_pair<NEG>(rb[-1], m);
+            }
+            uint32_t l2a = (ac + 2 == 0) ? pa2 : pa1, l2b = (ac + 2 == 0) ? pb2 : pb1;
+            // right neighbours: the last even column (in_w-2, in_w > 2) takes itself
+            const bool e0 = (p.in_w > 2) && (ac == p.in_w - 2);
+            const bool e2 = (p.in_w > 2) && (ac + 2 == p.in_w - 2);
+            c0 = avg2(filt121(la, pa0, e0 ? pa0 : pa1), filt121(lb, pb0, e0 ? pb0 : pb1));
+            c1 = avg2(filt121(l2a, pa2, e2 ? pa2 : pa3), filt121(l2b, pb2, e2 ? pb2 : pb3));
+        }
+        *reinterpret_cast<uint2 *>(s_cf + (size_t)ky * (bw >> 1) + 2 * kx) = make_uint2(c0, c1);
+    }
+    __syncthreads();
+
+    // ---- phase 2a: luma, 4 output pixels per thread ------------------------------------------
+    const long long fo = (long long)frame * p.out.frame_stride;
+    {
+        const int r = tid >> 4, c4 = (tid & 15) * 4;
+        const int y = y0 + r, x = x0 + c4;
+        if (y < p.out_h && x < p.out_w) {
+            const Tap tv = p.tab.vy[y];
+            const int i0 = tap_idx(tv) - sy0, i1 = i0 + tap_step(tv), p1 = tap_frac(tv);
+            const uint8_t *row0 = s_yf + (size_t)i0 * bw, *row1 = s_yf + (size_t)i1 * bw;
+            const uint4 th4 = *reinterpret_cast<const uint4 *>(p.tab.hy + x);   // table padded to 4
+            const Tap th[4] = { th4.x, th4.y, th4.z, th4.w };
+            uint32_t out = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const int j0 = tap_idx(th[k]) - sx0, j1 = j0 + tap_step(th[k]), f = tap_frac(th[k]);
+                int d;
+                if (p.box2x2)
+                    d = (row0[j0] + row0[j0 + 1] + row1[j0] + row1[j0 + 1] + 2) >> 2;
+                else
+                    d = lerp_v(lerp_h(row0[j0], row0[j1], f), lerp_h(row1[j0], row1[j1], f), p1);
+                out |= (uint32_t)d << (8 * k);
+            }
+            uint8_t *dst = p.out.p[0] + fo + (long long)y * p.out.pitch[0] + x;
+            if (x + 4 <= p.out_w) {
+                *reinterpret_cast<uint32_t *>(dst) = out;
+            } else {
+                for (int k = 0; k < p.out_w - x; k++) dst[k] = (uint8_t)(out >> (8 * k));
+            }
+        }
+    }
+
+    // ---- phase 2b: chroma, one (u,v) sample per thread ---------------------------------------
+    {
+        const int cr = tid >> 5, cc = tid & 31;
+        const int cy = (y0 >> 1) + cr, cx = (x0 >> 1) + cc;
+        if (cy < (p.out_h >> 1) && cx < (p.out_w >> 1)) {
+            const Tap tv = p.tab.vc[cy], th = p.tab.hc[cx];
+            const int cw = bw >> 1;
+            const int i0 = tap_idx(tv) - (sy0 >> 1), i1 = i0 + tap_step(tv), p1 = tap_frac(tv);
+            const int j0 = tap_idx(th) - (sx0 >> 1), j1 = j0 + tap_step(th), f = tap_frac(th);
+            const uint32_t *row0 = s_cf + (size_t)i0 * cw, *row1 = s_cf + (size_t)i1 * cw;
+            int du, dv;
+            if (p.box2x2) {
+                uint32_t s = ((row0[j0] + row0[j0 + 1] + row1[j0] + row1[j0 + 1] + 0x00020002u) >> 2) & LANES8;
+                du = (int)(s & 0xff);
+                dv = (int)(s >> 16);
+            } else {
+                // both lanes at once: each lane's weighted sum is <= 255*256
+                const uint32_t ha = ((row0[j0] * (uint32_t)(256 - f) + row0[j1] * (uint32_t)f) >> 8) & LANES8;
+                const uint32_t hb = ((row1[j0] * (uint32_t)(256 - f) + row1[j1] * (uint32_t)f) >> 8) & LANES8;
+                du = lerp_v((int)(ha & 0xff), (int)(hb & 0xff), p1);
+                dv = lerp_v((int)(ha >> 16), (int)(hb >> 16), p1);
+            }
+            if (FMT == 0) {
+                p.out.p[1][fo + (long long)cy * p.out.pitch[1] + cx] = (uint8_t)du;
+                p.out.p[2][fo + (long long)cy * p.out.pitch[2] + cx] = (uint8_t)dv;
+            } else {
+                *reinterpret_cast<uint16_t *>(p.out.p[1] + fo + (long long)cy * p.out.pitch[1] + 2 * cx) =
+                    (uint16_t)(du | (dv << 8));
+            }
+        }
+    }
+}
+
+// ---- two-pass, pass 2: scale the planes of a full-size intermediate I420 -----------------------
+template <int FMT>
+__global__ void __launch_bounds__(256) k2_plane_scale_kernel(const PlaneScaleParams p)
+{
+    const int tx = blockIdx.x * 64 + (threadIdx.x & 63);
+    const int ry = blockIdx.y * 4 + (threadIdx.x >> 6);
+    const int frame = blockIdx.z;
+    const long long fi = (long long)frame * p.src_frame_stride;
+    const long long fo = (long long)frame * p.out.frame_stride;
+    const int x = tx * 4;
+
+    if (ry < p.out_h) {                                    // luma row
+        if (x >= p.out_w) return;
+        const Tap tv = p.tab.vy[ry];
+        const uint8_t *row0 = p.src[0] + fi + (long long)tap_idx(tv) * p.src_pitch[0];
+        const uint8_t *row1 = row0 + (long long)tap_step(tv) * p.src_pitch[0];
+        const int p1 = tap_frac(tv);
+        uint8_t *dst = p.out.p[0] + fo + (long long)ry * p.out.pitch[0] + x;
+        for (int k = 0; k < 4 && x + k < p.out_w; k++) {
+            const Tap th = p.tab.hy[x + k];
+            const int j0 = tap_idx(th), j1 = j0 + tap_step(th), f = tap_frac(th);
+            int d;
+            if (p.box2x2)
+                d = (__ldg(row0 + j0) + __ldg(row0 + j0 + 1) + __ldg(row1 + j0) + __ldg(row1 + j0 + 1) + 2) >> 2;
+            else
+                d = lerp_v(lerp_h(__ldg(row0 + j0), __ldg(row0 + j1), f),
+                           lerp_h(__ldg(row1 + j0), __ldg(row1 + j1), f), p1);
+            dst[k] = (uint8_t)d;
+        }
+        return;
+    }
+    const int cy = ry - p.out_h;                           // chroma row
+    if (cy >= (p.out_h >> 1) || x >= (p.out_w >> 1)) return;
+    const Tap tv = p.tab.vc[cy];
+    const int p1 = tap_frac(tv);
+#pragma unroll
+    for (int pl = 1; pl <= 2; pl++) {
+        const uint8_t *row0 = p.src[pl] + fi + (long long)tap_idx(tv) * p.src_pitch[pl];
+        const uint8_t *row1 = row0 + (long long)tap_step(tv) * p.src_pitch[pl];
+        for (int k = 0; k < 4 && x + k < (p.out_w >> 1); k++) {
+            const Tap th = p.tab.hc[x + k];
+            const int j0 = tap_idx(th), j1 = j0 + tap_step(th), f = tap_frac(th);
+            int d;
+            if (p.box2x2)
+                d = (__ldg(row0 + j0) + __ldg(row0 + j0 + 1) + __ldg(row1 + j0) + __ldg(row1 + j0 + 1) + 2) >> 2;
+            else
+                d = lerp_v(lerp_h(__ldg(row0 + j0), __ldg(row0 + j1), f),
+                           lerp_h(__ldg(row1 + j0), __ldg(row1 + j1), f), p1);
+            if (FMT == 0)
+                p.out.p[pl][fo + (long long)cy * p.out.pitch[pl] + x + k] = (uint8_t)d;
+            else
+                p.out.p[1][fo + (long long)cy * p.out.pitch[1] + 2 * (x + k) + (pl - 1)] = (uint8_t)d;
+        }
+    }
+}
+
+template <int FMT, int SITE>
+cudaError_t launch_fused2(const CUtensorMap &map, const FusedScaleParams &p, dim3 grid, size_t smem, cudaStream_t st)
+{
+    if (p.mx.neg)
+        k2_fused_scale_kernel<FMT, SITE, true><<<grid, 256, smem, st>>>(map, p);
+    else
+        k2_fused_scale_kernel<FMT, SITE, false><<<grid, 256, smem, st>>>(map, p);
+    return cudaGetLastError();
+}
+
+template <typename K>
+cudaError_t set_smem(K kernel, size_t bytes)
+{
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+}
+
+}  // namespace
+
+size_t fused_scale_smem_bytes(int box_w, int box_h)
+{
+    return (size_t)box_w * box_h * 6;
+}
+
+cudaError_t fused_scale_prepare(size_t smem_bytes)
+{
+    cudaError_t e;
+#define B200VC_SET(F, S, N) \
+    if ((e = set_smem(k2_fused_scale_kernel<F, S, N>, smem_bytes)) != cudaSuccess) return e;
+    B200VC_SET(0, 0, false) B200VC_SET(0, 0, true) B200VC_SET(0, 1, false) B200VC_SET(0, 1, true)
+    B200VC_SET(1, 0, false) B200VC_SET(1, 0, true) B200VC_SET(1, 1, false) B200VC_SET(1, 1, true)
+#undef B200VC_SET
+    return cudaSuccess;
+}
+
+cudaError_t launch_fused_scale(const CUtensorMap &src_map, const FusedScaleParams &p, int fmt, int site,
+                               cudaStream_t st)
+{
+    if (p.out_w <= 0 || p.out_h <= 0 || p.n_frames <= 0)
+        return cudaErrorInvalidValue;
+    dim3 grid((p.out_w + TW - 1) / TW, (p.out_h + TH - 1) / TH, p.n_frames);
+    const size_t smem = fused_scale_smem_bytes(p.box_w, p.box_h);
+    if (fmt == 0)
+        return site ? launch_fused2<0, 1>(src_map, p, grid, smem, st) : launch_fused2<0, 0>(src_map, p, grid, smem, st);
+    return site ? launch_fused2<1, 1>(src_map, p, grid, smem, st) : launch_fused2<1, 0>(src_map, p, grid, smem, st);
+}
+
+cudaError_t launch_plane_scale(const PlaneScaleParams &p, int fmt, cudaStream_t st)
+{
+    if (p.out_w <= 0 || p.out_h <= 0 || p.n_frames <= 0)
+        return cudaErrorInvalidValue;
+    const int rows = p.out_h + (p.out_h >> 1);
+    dim3 grid(((p.out_w + 3) / 4 + 63) / 64, (rows + 3) / 4, p.n_frames);
+    if (fmt == 0)
+        k2_plane_scale_kernel<0><<<grid, 256, 0, st>>>(p);
+    else
+        k2_plane_scale_kernel<1><<<grid, 256, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+}  // namespace b200vc

@@ -1,0 +1,86 @@
+// kernels.cuh — parameter blocks and launchers shared by the sm_100a kernels and the C-ABI layer.
+//
+// Path replaced: GStreamer videoconvert ! videoscale on the reference's x264enc fallback
+// (/root/reference Dockerfile:467-471, README.md:21); arithmetic per SURVEY.md Appendix A/B.
+#pragma once
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200vc {
+
+// Matrix in the form the kernels consume. Coefficients are packed as four bytes in
+// pixel byte order B,G,R,x for dp4a; x's coefficient is 0 so the pad byte never matters.
+//   Y = dp4a.u32.u32(pix, cy, oy) >> 8
+//   U = dp4a.u32.s32(pix, cu, ou) >> 8            (neg == 0)
+// Full-range rows hold a +128 coefficient, which does not fit a signed byte. Those matrices are
+// evaluated negated (neg == 1): T = dp4a(pix, -c, 65535 - o) = 65535 - S, whose byte 1 is the
+// one's complement of byte 1 of S; the kernel undoes it with one XOR on the packed (u,v) word.
+struct Matrix {
+    uint32_t cy, cu, cv;
+    uint32_t oy, ou, ov;
+    int32_t neg;
+};
+
+struct PlaneSet {
+    uint8_t *p[3];          // Y,U,V (I420) or Y,UV (NV12)
+    long long pitch[3];
+    long long frame_stride; // bytes between consecutive frames, same for every plane pointer
+};
+
+// K1 (+K3): convert a band of rows of n_frames frames.
+struct ConvertParams {
+    const uint8_t *src;  long long src_pitch;  long long src_frame_stride;
+    const uint8_t *prev; long long prev_pitch; long long prev_frame_stride;   // K3 only
+    PlaneSet out;
+    uint8_t *damage; long long damage_frame_stride; int mb_w;                  // K3 only
+    int w, h;               // pixels covered by this launch (h = rows of the band, even)
+    int n_frames;
+    Matrix mx;
+};
+
+// Packed scaler tap: bits 0..15 first source index (clamped), bits 16..23 fraction (H: 0..255,
+// V: 0..64), bit 24 set when the second tap is index+1 (clear when clamped onto the first).
+typedef uint32_t Tap;
+
+struct ScaleTables {
+    const Tap *hy, *vy;     // luma: out_w / out_h entries
+    const Tap *hc, *vc;     // chroma: out_w/2, out_h/2 entries
+};
+
+// K2 fused: TMA-staged source window -> convert -> chroma down -> 2-tap scale, one pass.
+struct FusedScaleParams {
+    PlaneSet out;
+    ScaleTables tab;
+    int in_w, in_h, out_w, out_h;
+    int box_w, box_h;       // source window per tile (pixels); box_w % 4 == 0, box_h even
+    int n_frames;
+    int box2x2;             // scale_mode == BOX_2X2
+    Matrix mx;
+};
+
+// Two-pass scale, pass 2: plane scaler reading the full-size intermediate I420.
+struct PlaneScaleParams {
+    const uint8_t *src[3]; long long src_pitch[3]; long long src_frame_stride;
+    PlaneSet out;
+    ScaleTables tab;
+    int in_w, in_h, out_w, out_h;
+    int n_frames;
+    int box2x2;
+};
+
+constexpr int K1_TILE_W = 128;   // pixels per CTA tile (one LDG.128 per lane per row)
+constexpr int K1_TILE_H = 16;    // one macroblock row: 8 warps x 2 lines
+constexpr int K2_TILE_W = 64;    // output pixels per CTA tile
+constexpr int K2_TILE_H = 16;
+
+// Launchers return the cudaError_t of the launch. fmt/site as in b200vc.h.
+cudaError_t launch_convert(const ConvertParams &p, int fmt, int site, cudaStream_t st);
+cudaError_t launch_fused_scale(const CUtensorMap &src_map, const FusedScaleParams &p, int fmt, int site,
+                               cudaStream_t st);
+cudaError_t launch_plane_scale(const PlaneScaleParams &p, int fmt, cudaStream_t st);
+size_t fused_scale_smem_bytes(int box_w, int box_h);
+cudaError_t fused_scale_prepare(size_t smem_bytes);   // opt in to > 48 KB dynamic shared memory
+
+}  // namespace b200vc

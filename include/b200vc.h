@@ -1,0 +1,191 @@
+/*
+ * b200vc.h — C ABI of libb200vc.so: BGRx -> I420/NV12 conversion, fused bilinear downscale and
+ * 16x16 damage map on NVIDIA B200 (sm_100a).
+ *
+ * This is the drop-in boundary for the one data-parallel hot path of
+ * COx2/docker-nvidia-glx-desktop: the `videoconvert ! videoscale` stage of the selkies-gstreamer
+ * pipeline on the WEBRTC_ENCODER=x264enc fallback. The reference holds no source for that stage;
+ * it installs it as a binary (Dockerfile:467-471), sources its environment
+ * (selkies-gstreamer-entrypoint.sh:8), starts the application that instantiates it
+ * (selkies-gstreamer-entrypoint.sh:44-47) and selects the software-encoder path that uses it
+ * (README.md:21,35,58; xgl.yml:61-63). Each entry point below names the GStreamer
+ * GstBaseTransform/GstVideoFilter virtual method (SURVEY.md §8 b) whose work it carries; the
+ * element that binds them is docker-nvidia-glx-desktop_b200/gst/gstb200convert.c and the binding
+ * is shown in INTEGRATION.md.
+ *
+ * Plain C types only: no GLib, no CUDA, no torch types cross this boundary. There is no CPU
+ * fallback: every entry point that does work fails with B200VC_ERR_NO_DEVICE / B200VC_ERR_CUDA
+ * when no sm_100 device can be used.
+ *
+ * Threading: a context is internally locked; entry points may be called from any thread (the
+ * GStreamer streaming thread is not ours), one frame stream per session index.
+ */
+#ifndef B200VC_H
+#define B200VC_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200VC_VERSION_MAJOR 0
+#define B200VC_VERSION_MINOR 1
+
+/* ---- status codes ------------------------------------------------------------------------- */
+enum {
+    B200VC_OK = 0,
+    B200VC_ERR_INVALID_ARG = 1,   /* NULL pointer, bad enum, odd size, ...                        */
+    B200VC_ERR_UNSUPPORTED = 2,   /* caps this element does not accept (refuse at negotiation)    */
+    B200VC_ERR_NOT_NEGOTIATED = 3,/* called before a successful create (GST_FLOW_NOT_NEGOTIATED)  */
+    B200VC_ERR_CUDA = 4,          /* a CUDA call failed (GST_FLOW_ERROR); see b200vc_last_error   */
+    B200VC_ERR_NO_DEVICE = 5,     /* no usable sm_100 GPU                                          */
+    B200VC_ERR_ALIGNMENT = 6,     /* device pointers/pitches must be 16-byte multiples             */
+    B200VC_ERR_NOMEM = 7,
+    B200VC_ERR_BAD_TICKET = 8
+};
+
+/* ---- negotiated caps, as plain enums ------------------------------------------------------- */
+enum { B200VC_FMT_I420 = 0, B200VC_FMT_NV12 = 1 };                  /* src pad format          */
+enum { B200VC_MATRIX_BT601 = 0, B200VC_MATRIX_BT709 = 1 };          /* colorimetry matrix      */
+enum { B200VC_RANGE_LIMITED = 0, B200VC_RANGE_FULL = 1 };           /* colorimetry range       */
+enum { B200VC_SITE_NONE = 0 /* "jpeg" */, B200VC_SITE_H_COSITED = 1 /* "mpeg2" */ };
+enum { B200VC_SCALE_GST_LQ = 0 /* videoscale bilinear, SURVEY B.2 */, B200VC_SCALE_BOX_2X2 = 1 };
+
+/* flags */
+#define B200VC_FLAG_DAMAGE_MAP      0x1u  /* keep the previous frame per session and emit the map */
+#define B200VC_FLAG_FORCE_TWO_PASS  0x2u  /* scaling: convert to a full-size intermediate, then
+                                             scale the planes (the general path), never the fused
+                                             kernel                                               */
+#define B200VC_FLAG_REGISTER_HOST   0x4u  /* page-lock caller buffers on first sight (XShm pool)
+                                             instead of staging them through a pinned ring        */
+
+typedef struct b200vc_config {
+    int32_t device;        /* CUDA device ordinal                                                  */
+    int32_t in_w, in_h;    /* sink caps: video/x-raw,format=BGRx                                   */
+    int32_t out_w, out_h;  /* src caps; equal to in_* = videoconvert only                          */
+    int32_t out_format;    /* B200VC_FMT_*                                                         */
+    int32_t matrix;        /* B200VC_MATRIX_*                                                      */
+    int32_t range;         /* B200VC_RANGE_*                                                       */
+    int32_t chroma_site;   /* B200VC_SITE_*                                                        */
+    int32_t scale_mode;    /* B200VC_SCALE_*                                                       */
+    uint32_t flags;        /* B200VC_FLAG_*                                                        */
+    int32_t max_sessions;  /* independent desktop sessions served by this context (>=1; 0 -> 1)   */
+    int32_t n_inflight;    /* frames that may be in flight between submit and collect (0 -> 3)    */
+    int32_t n_bands;       /* row bands a single synchronous convert is pipelined in (0 -> 4)     */
+} b200vc_config;
+
+typedef struct b200vc_ctx b200vc_ctx;
+
+/* One frame crossing the boundary in host memory. Mirrors what transform_frame receives: the
+ * mapped input GstVideoFrame (data[0], stride[0]) and the mapped output frame (data[p],
+ * stride[p]); strides are always honoured. planes[2]/pitches[2] unused for NV12. */
+typedef struct b200vc_frame {
+    const void *bgrx;
+    size_t in_pitch;
+    void *planes[3];
+    size_t pitches[3];
+    uint8_t *damage;       /* ceil(in_w/16)*ceil(in_h/16) bytes, or NULL                           */
+    int32_t session;       /* 0 .. max_sessions-1                                                  */
+    int32_t reserved;
+} b200vc_frame;
+
+/* A batch of frames already resident in device memory (kernel-only path; also what a
+ * memory:CUDAMemory caps feature would hand over). Frame i lives at base + i*stride. All
+ * pointers, pitches and strides must be multiples of 16 bytes. */
+typedef struct b200vc_device_frames {
+    const void *bgrx;  size_t in_pitch;   size_t in_frame_stride;
+    const void *prev;  size_t prev_pitch; size_t prev_frame_stride;   /* NULL: map is all ones    */
+    void *planes[3];   size_t pitches[3]; size_t out_frame_stride;
+    uint8_t *damage;   size_t damage_frame_stride;                    /* NULL: no map             */
+    int32_t n_frames;
+    int32_t reserved;
+} b200vc_device_frames;
+
+typedef struct b200vc_stats {
+    uint64_t frames;            /* frames converted                                                */
+    uint64_t kernel_launches;   /* kernels launched by this context                                */
+    uint64_t h2d_bytes, d2h_bytes;
+    uint64_t staged_in_bytes;   /* bytes copied host->pinned because the caller's buffer was pageable */
+    uint64_t staged_out_bytes;
+} b200vc_stats;
+
+typedef struct b200vc_info {
+    int32_t path;               /* 0 convert only, 1 fused scale (TMA), 2 two-pass scale           */
+    int32_t tile_w, tile_h;     /* output tile of the main kernel                                   */
+    int32_t box_w, box_h;       /* fused scale: source window loaded per tile (pixels)              */
+    int32_t smem_bytes;         /* dynamic + static shared memory of the main kernel                */
+    int32_t sm_count;
+    int32_t cc_major, cc_minor;
+    char device_name[64];
+} b200vc_info;
+
+/* ---- negotiation helpers (no GPU needed) -------------------------------------------------- */
+
+/* GstVideoConvert/GstVideoScale fixate_caps + video-info.c set_default_colorimetry:
+ * colorimetry and chroma-site implied by the output height when the caps leave them open. */
+int b200vc_default_colorimetry(int out_h, int *matrix, int *range, int *chroma_site);
+
+/* video-info.c default strides/offsets for I420/NV12. Returns the frame size. */
+size_t b200vc_default_layout(int format, int w, int h, size_t offsets[3], size_t pitches[3]);
+
+/* transform_caps/set_caps acceptance test: B200VC_OK, or the reason the caps are refused. */
+int b200vc_check_config(const b200vc_config *cfg);
+
+const char *b200vc_status_string(int status);
+int b200vc_version(void);
+
+/* ---- lifecycle ----------------------------------------------------------------------------- */
+
+/* GstBaseTransform::start + GstVideoFilter::set_info: build every CUDA resource for the
+ * negotiated caps. Renegotiation = destroy + create. */
+int b200vc_create(const b200vc_config *cfg, b200vc_ctx **out);
+
+/* GstBaseTransform::stop. Waits for work in flight. */
+int b200vc_destroy(b200vc_ctx *ctx);
+
+/* Text of the last failure on this context (ctx == NULL: of the last failed create on this
+ * thread). What the element posts through GST_ELEMENT_ERROR. */
+const char *b200vc_last_error(const b200vc_ctx *ctx);
+
+int b200vc_get_info(const b200vc_ctx *ctx, b200vc_info *info);
+int b200vc_get_stats(const b200vc_ctx *ctx, b200vc_stats *stats);
+
+/* Stream discontinuity (flush, seek, caps change on the same geometry): forget the previous
+ * frame of `session` (-1: all); its next damage map is all ones. */
+int b200vc_reset(b200vc_ctx *ctx, int session);
+
+/* ---- the hot path, host buffers ------------------------------------------------------------ */
+
+/* GstVideoFilter::transform_frame -> gst_video_converter_frame: one frame of session 0,
+ * synchronous; the planes are complete on return. H2D, kernel and D2H are pipelined over row
+ * bands inside the call. damage may be NULL. */
+int b200vc_convert(b200vc_ctx *ctx, const void *bgrx, size_t in_pitch,
+                   void *const planes[3], const size_t pitches[3], uint8_t *damage_or_null);
+
+/* One tick of n sessions (config "64 sessions, 8 per GPU"): frames are pipelined against each
+ * other (H2D of frame i+1 under kernel and D2H of frame i); all complete on return. */
+int b200vc_convert_batch(b200vc_ctx *ctx, const b200vc_frame *frames, int n);
+
+/* One-frame-latency mode (GstBaseTransform::submit_input_buffer / generate_output): enqueue a
+ * frame and return at once; b200vc_collect blocks until that frame's planes are complete.
+ * The caller's buffers must stay valid and untouched until collect returns. */
+int b200vc_submit(b200vc_ctx *ctx, const b200vc_frame *frame, uint64_t *ticket);
+int b200vc_collect(b200vc_ctx *ctx, uint64_t ticket);
+
+/* propose_allocation/decide_allocation: page-locked host memory for buffer pools either side of
+ * the element, so frames cross PCIe without a staging copy. */
+int b200vc_host_alloc(size_t bytes, void **out);
+int b200vc_host_free(void *p);
+
+/* ---- the hot path, device buffers ---------------------------------------------------------- */
+
+/* Same transform on frames already in HBM, one batched launch on `cuda_stream` (a cudaStream_t
+ * passed as void*; NULL = the default stream). Asynchronous: returns after enqueueing. */
+int b200vc_convert_device(b200vc_ctx *ctx, const b200vc_device_frames *frames, void *cuda_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200VC_H */

@@ -1,0 +1,56 @@
+"""Generates tests/golden/vectors.npz.
+
+The reference holds no golden vector for this path, and GStreamer is not available
+to produce any, so these vectors are made from this repo's own spec: inputs come from a fixed
+NumPy RNG, expected outputs from oracle/np_oracle.py (the plain-formula restatement of SURVEY
+Appendix A/B). They pin the restatement — the C oracle and the CUDA path must both reproduce them
+— not GStreamer itself. Re-run:  python tests/golden/make_golden.py
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from oracle import np_oracle as N  # noqa: E402
+
+# (name, in_w, in_h, out_w, out_h, fmt, matrix, range, site, scale_mode)
+CASES = [
+    ("c1_601l_i420_jpeg", 36, 20, 36, 20, 0, 0, 0, 0, 0),
+    ("601l_i420_mpeg2", 36, 20, 36, 20, 0, 0, 0, 1, 0),
+    ("c2_709f_nv12_mpeg2", 40, 18, 40, 18, 1, 1, 1, 1, 0),
+    ("709l_i420_mpeg2_ragged", 134, 34, 134, 34, 0, 1, 0, 1, 0),
+    ("601f_nv12_jpeg_w2", 2, 2, 2, 2, 1, 0, 1, 0, 0),
+    ("c3_2to1_709l_i420", 64, 36, 32, 18, 0, 1, 0, 1, 0),
+    ("scale_3to2_601l_nv12", 96, 48, 64, 32, 1, 0, 0, 0, 0),
+    ("scale_box_709l_i420", 64, 36, 32, 18, 0, 1, 0, 1, 1),
+    ("scale_odd_ratio", 100, 60, 46, 26, 0, 1, 0, 1, 0),
+]
+
+
+def main():
+    rng = np.random.default_rng(20261106)
+    out = {}
+    for name, iw, ih, ow, oh, fmt, mat, rg, site, mode in CASES:
+        frame = rng.integers(0, 256, size=(ih, iw, 4), dtype=np.uint8)
+        planes = N.convert_scale(frame, ow, oh, fmt, mat, rg, site, mode)
+        out[name + "/in"] = frame
+        out[name + "/cfg"] = np.array([iw, ih, ow, oh, fmt, mat, rg, site, mode], np.int32)
+        for i, p in enumerate(planes):
+            out[f"{name}/p{i}"] = p
+    # damage map: two frames differing in a few places (one of them only in the x byte)
+    a = rng.integers(0, 256, size=(40, 70, 4), dtype=np.uint8)
+    b = a.copy()
+    b[3, 5, 0] ^= 1      # B of a pixel in MB (0,0)
+    b[17, 33, 2] ^= 128  # R in MB (1,2)
+    b[39, 69, 1] ^= 4    # G in the ragged corner MB (2,4)
+    b[20, 50, 3] ^= 255  # x byte only: not damage
+    out["damage/a"], out["damage/b"], out["damage/map"] = a, b, N.damage_map(b, a)
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "vectors.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path), "bytes;", len(CASES), "cases")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,115 @@
+"""CPU tests of the C-ABI boundary: the library loads, exports what include/b200vc.h declares,
+negotiates like `videoconvert ! videoscale` for these formats, and refuses to work without a GPU.
+No compute entry point is called here."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+import b200vc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _has_gpu():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+def test_header_and_library_agree(lib):
+    hdr = open(os.path.join(ROOT, "include", "b200vc.h")).read()
+    declared = sorted(set(re.findall(r"\b(b200vc_[a-z_0-9]+)\s*\(", hdr)))
+    assert declared == sorted(b200vc.SYMBOLS)
+    for name in declared:
+        assert hasattr(lib, name), f"libb200vc.so does not export {name}"
+
+
+def test_struct_sizes_match_the_header():
+    # the header's structs, laid out by hand (LP64): catches a drifting ctypes mirror
+    assert C.sizeof(b200vc.Config) == 14 * 4
+    assert C.sizeof(b200vc.Frame) == 8 + 8 + 24 + 24 + 8 + 4 + 4
+    assert C.sizeof(b200vc.DeviceFrames) == 3 * 8 + 3 * 8 + 24 + 24 + 8 + 8 + 8 + 4 + 4
+    assert C.sizeof(b200vc.Stats) == 6 * 8
+    assert C.sizeof(b200vc.Info) == 9 * 4 + 64
+
+
+def test_version_and_status_strings(lib):
+    assert lib.b200vc_version() == 1
+    assert lib.b200vc_status_string(0) == b"ok"
+    assert b"sm_100" in lib.b200vc_status_string(b200vc.ERR_NO_DEVICE)
+
+
+def test_default_colorimetry_by_height():
+    # > 576 lines -> bt709 limited + mpeg2 siting; else bt601 limited + jpeg siting
+    assert b200vc.default_colorimetry(1080) == (b200vc.MATRIX_BT709, b200vc.RANGE_LIMITED, b200vc.SITE_H_COSITED)
+    assert b200vc.default_colorimetry(577)[0] == b200vc.MATRIX_BT709
+    assert b200vc.default_colorimetry(576) == (b200vc.MATRIX_BT601, b200vc.RANGE_LIMITED, b200vc.SITE_NONE)
+    assert b200vc.default_colorimetry(480)[2] == b200vc.SITE_NONE
+
+
+@pytest.mark.parametrize("fmt,w,h", [(0, 1920, 1080), (1, 2560, 1440), (0, 1366, 768), (1, 1366, 768), (0, 2, 2)])
+def test_default_layout_matches_oracle(orc, fmt, w, h):
+    assert b200vc.default_layout(fmt, w, h) == orc.default_layout(fmt, w, h)
+
+
+def _cfg(**kw):
+    base = dict(device=0, in_w=1920, in_h=1080, out_w=1920, out_h=1080, out_format=0, matrix=0, range=0,
+                chroma_site=0, scale_mode=0, flags=0, max_sessions=1, n_inflight=0, n_bands=0)
+    base.update(kw)
+    return b200vc.Config(**base)
+
+
+def test_caps_acceptance(lib):
+    ok = [_cfg(), _cfg(out_format=1, matrix=1, range=1, chroma_site=1, in_w=2560, in_h=1440, out_w=2560, out_h=1440),
+          _cfg(in_w=3840, in_h=2160), _cfg(in_w=3840, in_h=2160, scale_mode=1), _cfg(flags=b200vc.FLAG_DAMAGE_MAP),
+          _cfg(in_w=1366, in_h=768, out_w=1366, out_h=768), _cfg(max_sessions=8, n_inflight=4)]
+    for c in ok:
+        assert lib.b200vc_check_config(C.byref(c)) == b200vc.OK
+    refused = [(_cfg(in_w=1921, out_w=1921), b200vc.ERR_UNSUPPORTED),      # odd width
+               (_cfg(out_format=2), b200vc.ERR_UNSUPPORTED),               # not I420/NV12
+               (_cfg(matrix=2), b200vc.ERR_UNSUPPORTED),                   # bt2020 not offered
+               (_cfg(chroma_site=3), b200vc.ERR_UNSUPPORTED),              # v-cosited not offered
+               (_cfg(in_w=3840, in_h=2160, out_w=1280, out_h=720, scale_mode=1), b200vc.ERR_UNSUPPORTED),
+               (_cfg(in_w=3840, in_h=2160, flags=b200vc.FLAG_DAMAGE_MAP), b200vc.ERR_UNSUPPORTED),
+               (_cfg(in_w=0), b200vc.ERR_INVALID_ARG), (_cfg(max_sessions=-1), b200vc.ERR_INVALID_ARG),
+               (_cfg(in_w=32768, out_w=32768), b200vc.ERR_UNSUPPORTED)]
+    for c, want in refused:
+        assert lib.b200vc_check_config(C.byref(c)) == want
+        assert lib.b200vc_last_error(None)          # a reason is always given
+    assert lib.b200vc_check_config(None) == b200vc.ERR_INVALID_ARG
+
+
+def test_calls_before_negotiation_fail(lib):
+    assert lib.b200vc_convert(None, None, 0, None, None, None) == b200vc.ERR_NOT_NEGOTIATED
+    assert lib.b200vc_convert_batch(None, None, 0) == b200vc.ERR_NOT_NEGOTIATED
+    assert lib.b200vc_submit(None, None, None) == b200vc.ERR_NOT_NEGOTIATED
+    assert lib.b200vc_convert_device(None, None, None) == b200vc.ERR_NOT_NEGOTIATED
+    assert lib.b200vc_destroy(None) == b200vc.ERR_INVALID_ARG
+    with pytest.raises(b200vc.B200vcError):
+        b200vc.Converter().transform_frame(None)
+
+
+@pytest.mark.skipif(_has_gpu(), reason="this box has a GPU")
+def test_no_gpu_means_loud_failure_not_fallback(lib):
+    ctx = C.c_void_p()
+    c = _cfg()
+    assert lib.b200vc_create(C.byref(c), C.byref(ctx)) == b200vc.ERR_NO_DEVICE
+    assert not ctx.value
+    assert b"no CPU fallback" in lib.b200vc_last_error(None)
+    with pytest.raises(b200vc.B200vcError) as e:
+        b200vc.Converter().set_info(1920, 1080)
+    assert e.value.status == b200vc.ERR_NO_DEVICE
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "docker-nvidia-glx-desktop_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".c", ".h", ".cpp")):
+                src = open(os.path.join(dirpath, f), errors="ignore").read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), f
+                assert "oracle.h" not in src and "liboracle" not in src, f

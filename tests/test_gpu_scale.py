@@ -1,0 +1,101 @@
+"""GPU parity tests, K2: conversion with the bilinear downscale fused in (TMA-staged tiles), and the
+general two-pass scaler, against the oracle's `videoconvert ! videoscale` restatement. Bit-exact."""
+import numpy as np
+import pytest
+
+import b200vc
+from helpers import assert_planes_equal, plane_checksums, plane_views
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def conv():
+    c = b200vc.Converter(0)
+    yield c
+    c.stop()
+
+
+def _want(orc, frame, ow, oh, fmt, m, rg, site, mode=0):
+    buf, off, pit = orc.convert(frame, fmt, m, rg, site, out_size=(ow, oh), scale_mode=mode)
+    return plane_views(buf, off, pit, fmt, ow, oh)
+
+
+GEOS = [(3840, 2160, 1920, 1080), (64, 36, 32, 18), (128, 64, 64, 32), (260, 132, 130, 66), (96, 48, 64, 32),
+        (100, 60, 46, 26), (1920, 1080, 1280, 720), (1280, 720, 854, 480), (200, 120, 150, 90), (640, 360, 212, 120)]
+
+
+@pytest.mark.parametrize("geo", GEOS)
+@pytest.mark.parametrize("two_pass", [False, True])
+def test_scale_parity(conv, orc, geo, two_pass):
+    iw, ih, ow, oh = geo
+    frame = orc.synth("rand", iw, ih, 9)
+    flags = b200vc.FLAG_FORCE_TWO_PASS if two_pass else 0
+    for fmt, m, rg, site in [(0, 1, 0, 1), (1, 0, 1, 0), (0, 0, 0, 0), (1, 1, 1, 1)]:
+        conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=m, range_=rg, chroma_site=site, flags=flags)
+        assert conv.info().path == (2 if two_pass else 1)
+        buf, off, pit = conv.transform_frame(frame)
+        assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), _want(orc, frame, ow, oh, fmt, m, rg, site),
+                            f"{geo} fmt{fmt} m{m} r{rg} s{site} two_pass={two_pass}")
+
+
+@pytest.mark.parametrize("two_pass", [False, True])
+def test_box_mode(conv, orc, two_pass):
+    iw, ih, ow, oh = 516, 260, 258, 130
+    frame = orc.synth("rand", iw, ih, 2)
+    flags = b200vc.FLAG_FORCE_TWO_PASS if two_pass else 0
+    for fmt in (0, 1):
+        conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=1, range_=0, chroma_site=1, scale_mode=1, flags=flags)
+        buf, off, pit = conv.transform_frame(frame)
+        assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), _want(orc, frame, ow, oh, fmt, 1, 0, 1, 1))
+
+
+def test_structured_frames_4k(conv, orc):
+    # C3 on bars/ramp/checkerboard: the ramp exercises every horizontal fraction 0..247
+    frame = orc.synth("desk", 3840, 2160, 3)
+    conv.set_info(3840, 2160, 1920, 1080, matrix=1, range_=0, chroma_site=1)
+    inf = conv.info()
+    assert inf.path == 1 and inf.box_w >= 130 and inf.box_h >= 32
+    buf, off, pit = conv.transform_frame(frame)
+    want = _want(orc, frame, 1920, 1080, 0, 1, 0, 1)
+    assert_planes_equal(plane_views(buf, off, pit, 0, 1920, 1080), want)
+    assert plane_checksums(plane_views(buf, off, pit, 0, 1920, 1080)) == plane_checksums(want)
+
+
+def test_large_ratio_falls_back_to_two_pass(conv, orc):
+    # 6:1 needs a source window wider than one TMA box: negotiated onto the general path
+    frame = orc.synth("rand", 1920, 1080, 4)
+    conv.set_info(1920, 1080, 320, 180, matrix=0, range_=0, chroma_site=0)
+    assert conv.info().path == 2
+    buf, off, pit = conv.transform_frame(frame)
+    assert_planes_equal(plane_views(buf, off, pit, 0, 320, 180), _want(orc, frame, 320, 180, 0, 0, 0, 0))
+
+
+def test_upscale_uses_the_same_taps(conv, orc):
+    frame = orc.synth("rand", 160, 90, 4)
+    for flags in (0, b200vc.FLAG_FORCE_TWO_PASS):
+        conv.set_info(160, 90, 320, 180, matrix=0, range_=0, chroma_site=1, flags=flags)
+        buf, off, pit = conv.transform_frame(frame)
+        assert_planes_equal(plane_views(buf, off, pit, 0, 320, 180), _want(orc, frame, 320, 180, 0, 0, 0, 1))
+
+
+def test_device_entry_point_scaled_batch(conv, orc):
+    import torch
+    iw, ih, ow, oh, n = 1280, 720, 640, 360, 5
+    total, off, pit = b200vc.default_layout(0, ow, oh)
+    host = np.stack([orc.synth("rand", iw, ih, 60 + i) for i in range(n)])
+    d_in = torch.from_numpy(host.reshape(n, -1)).cuda()
+    for flags in (0, b200vc.FLAG_FORCE_TWO_PASS):
+        d_out = torch.zeros((n, total), dtype=torch.uint8, device="cuda")
+        conv.set_info(iw, ih, ow, oh, matrix=1, range_=0, chroma_site=1, flags=flags, max_sessions=2)
+        df = b200vc.DeviceFrames()
+        df.bgrx, df.in_pitch, df.in_frame_stride = d_in.data_ptr(), iw * 4, iw * ih * 4
+        for i in range(3):
+            df.planes[i], df.pitches[i] = d_out.data_ptr() + off[i], pit[i]
+        df.out_frame_stride, df.n_frames = total, n
+        conv.convert_device(df, 0)
+        torch.cuda.synchronize()
+        got = d_out.cpu().numpy()
+        for i in range(n):
+            assert_planes_equal(plane_views(got[i], off, pit, 0, ow, oh), _want(orc, host[i], ow, oh, 0, 1, 0, 1),
+                                f"frame {i} flags {flags}")

@@ -1,0 +1,175 @@
+"""CPU tests of the oracle: known answers, golden vectors, C vs NumPy agreement.
+
+These pin the repo's restatement of videoconvert/videoscale. Parity with GStreamer itself is
+unpinned: the reference (/root/reference) has no test or vector for this path and GStreamer is not
+installed here.
+"""
+import os
+
+import numpy as np
+import pytest
+from hypothesis import given, settings, strategies as st
+
+from helpers import assert_planes_equal, plane_views
+from oracle import np_oracle as N
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "vectors.npz")
+
+# (R,G,B) -> (Y,U,V) for [601 limited, 601 full, 709 limited, 709 full]
+KNOWN = {
+    (0, 0, 0): [(16, 128, 128), (0, 128, 128), (16, 128, 128), (0, 128, 128)],
+    (255, 255, 255): [(235, 128, 128), (255, 128, 128), (235, 127, 128), (254, 128, 128)],
+    (255, 0, 0): [(81, 90, 239), (76, 85, 255), (62, 102, 239), (53, 99, 255)],
+    (0, 255, 0): [(144, 54, 34), (149, 43, 21), (172, 41, 26), (182, 29, 12)],
+    (0, 0, 255): [(40, 239, 110), (28, 255, 107), (31, 239, 118), (17, 255, 116)],
+    (128, 128, 128): [(126, 128, 128), (128, 128, 128), (126, 127, 128), (127, 128, 128)],
+}
+COMBOS = [(0, 0), (0, 1), (1, 0), (1, 1)]
+
+
+def test_matrix_table_matches_survey(orc):
+    for (m, r), rows in N.MATRICES.items():
+        assert np.array_equal(orc.matrix(m, r), np.array(rows, np.int32))
+
+
+@pytest.mark.parametrize("site", [0, 1])
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_known_answers_uniform_frames(orc, fmt, site):
+    for (r, g, b), expect in KNOWN.items():
+        frame = np.zeros((4, 8, 4), np.uint8)
+        frame[..., 0], frame[..., 1], frame[..., 2], frame[..., 3] = b, g, r, 0x5A
+        for k, (m, rg) in enumerate(COMBOS):
+            buf, off, pit = orc.convert(frame, fmt, m, rg, site)
+            pl = plane_views(buf, off, pit, fmt, 8, 4)
+            y, u, v = expect[k]
+            assert (pl[0] == y).all(), (r, g, b, m, rg)
+            if fmt == 0:
+                assert (pl[1] == u).all() and (pl[2] == v).all(), (r, g, b, m, rg)
+            else:
+                assert (pl[1][:, 0::2] == u).all() and (pl[1][:, 1::2] == v).all()
+
+
+def test_golden_vectors(orc):
+    z = np.load(GOLDEN)
+    names = sorted({k.split("/")[0] for k in z.files if k.endswith("/cfg")})
+    assert len(names) >= 9
+    for name in names:
+        iw, ih, ow, oh, fmt, mat, rg, site, mode = [int(v) for v in z[name + "/cfg"]]
+        frame = np.ascontiguousarray(z[name + "/in"])
+        buf, off, pit = orc.convert(frame, fmt, mat, rg, site, out_size=(ow, oh), scale_mode=mode)
+        want = [z[f"{name}/p{i}"] for i in range(2 if fmt else 3)]
+        assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), want, name)
+    assert np.array_equal(orc.damage_map(np.ascontiguousarray(z["damage/b"]), np.ascontiguousarray(z["damage/a"])),
+                          z["damage/map"])
+    assert z["damage/map"].sum() == 3
+
+
+def test_cosited_edges_by_hand(orc):
+    # one line pair, w = 6, hand-computed from SURVEY A.4 on the U channel of a BT.601-full frame
+    frame = np.zeros((2, 6, 4), np.uint8)
+    frame[..., 0] = np.array([0, 40, 80, 120, 160, 200], np.uint8)  # B ramp
+    y, u, v = N.yuv444(frame, 0, 1)
+    u = u.astype(int)
+    h = [(3 * u[0, 0] + u[0, 1] + 2) >> 2, (u[0, 1] + 2 * u[0, 2] + u[0, 3] + 2) >> 2, (u[0, 3] + 3 * u[0, 4] + 2) >> 2]
+    buf, off, pit = orc.convert(frame, 0, 0, 1, 1)
+    pl = plane_views(buf, off, pit, 0, 6, 2)
+    assert list(pl[1][0]) == h   # both lines equal, so the vertical mean is the identity
+
+
+@pytest.mark.parametrize("size", [(2, 2), (4, 2), (6, 4), (130, 18), (258, 34), (1920, 1080)])
+def test_c_equals_numpy_convert(orc, size):
+    w, h = size
+    for kind in ("rand", "bars", "desk"):
+        frame = orc.synth(kind, w, h, 7)
+        for fmt in (0, 1):
+            for m, rg in COMBOS:
+                for site in (0, 1):
+                    buf, off, pit = orc.convert(frame, fmt, m, rg, site)
+                    assert_planes_equal(plane_views(buf, off, pit, fmt, w, h), list(N.convert(frame, fmt, m, rg, site)),
+                                        f"{kind} {size} fmt{fmt} m{m} r{rg} s{site}")
+
+
+def test_threads_and_pitch_do_not_change_results(orc):
+    w, h = 322, 50
+    frame = orc.synth("rand", w, h, 1, pitch=w * 4 + 64)
+    ref = orc.convert(np.ascontiguousarray(frame), 0, 1, 0, 1)[0]
+    for t in (1, 2, 3, 5):
+        assert np.array_equal(orc.convert(frame, 0, 1, 0, 1, threads=t)[0], ref)
+    buf, off, pit = orc.convert(frame, 0, 1, 0, 1, pitches=[384, 192, 192])
+    buf0, off0, pit0 = orc.convert(frame, 0, 1, 0, 1)
+    assert_planes_equal(plane_views(buf, off, pit, 0, w, h), plane_views(buf0, off0, pit0, 0, w, h))
+
+
+@pytest.mark.parametrize("geo", [(3840, 2160, 1920, 1080), (64, 32, 32, 16), (100, 60, 64, 36), (64, 48, 30, 22),
+                                 (32, 16, 64, 32), (1920, 1080, 1280, 720), (200, 120, 50, 30)])
+def test_c_equals_numpy_scale(orc, geo):
+    iw, ih, ow, oh = geo
+    frame = orc.synth("rand", iw, ih, 5)
+    for fmt in (0, 1):
+        for mode in (0, 1):
+            if mode == 1 and (iw != 2 * ow or ih != 2 * oh):
+                continue
+            buf, off, pit = orc.convert(frame, fmt, 1, 0, 1, out_size=(ow, oh), scale_mode=mode)
+            assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh),
+                                list(N.convert_scale(frame, ow, oh, fmt, 1, 0, 1, mode)), f"{geo} fmt{fmt} mode{mode}")
+
+
+def test_scaler_taps_survey_b2(orc):
+    hi, hf = orc.h_taps(3840, 1920)   # inc = 131105: i = 2x for every x, f grows 0..247
+    assert np.array_equal(hi, 2 * np.arange(1920)) and hf[0] == 0 and hf[-1] == 247
+    assert np.array_equal(hf, (33 * np.arange(1920)) >> 8)
+    hi, hf = orc.h_taps(1920, 960)    # inc = 131139
+    assert np.array_equal(hi, 2 * np.arange(960)) and np.array_equal(hf, (67 * np.arange(960)) >> 8)
+    vi, vp = orc.v_taps(2160, 1080)   # exact 2:1 -> w = 0.5 -> p1 = 32 -> (a+b+1)>>1
+    assert np.array_equal(vi, 2 * np.arange(1080)) and (vp == 32).all()
+    for a, b in [(in_, out) for in_ in (7, 16, 33) for out in (2, 5, 16, 40)]:
+        assert np.array_equal(orc.h_taps(a, b)[0], N.h_taps(a, b)[0])
+        assert np.array_equal(orc.v_taps(a, b)[0], N.v_taps(a, b)[0])
+        assert np.array_equal(orc.v_taps(a, b)[1], N.v_taps(a, b)[1])
+
+
+def test_default_layout_survey_a5(orc):
+    total, off, pit = orc.default_layout(0, 1920, 1080)
+    assert (total, off, pit) == (3110400, [0, 2073600, 2592000], [1920, 960, 960])
+    total, off, pit = orc.default_layout(1, 2560, 1440)
+    assert (total, off[:2], pit[:2]) == (5529600, [0, 3686400], [2560, 2560])
+    assert orc.default_layout(0, 1366, 768)[2] == [1368, 684, 684]
+
+
+def test_damage_map_properties(orc):
+    a = orc.synth("desk", 1920, 1080, 10)
+    b = orc.synth("desk", 1920, 1080, 11)
+    m = orc.damage_map(b, a)
+    assert m.shape == (68, 120) and np.array_equal(m, N.damage_map(b, a))
+    assert 0.01 < m.mean() < 0.06                      # "mostly static desktop": ~3 % dirty
+    assert orc.damage_map(a, a).sum() == 0 and orc.damage_map(a, None).all()
+    c = a.copy()
+    c[..., 3] ^= 0xFF                                   # only the pad byte changes: no damage
+    assert orc.damage_map(c, a).sum() == 0
+    c[1079, 1919, 1] ^= 1                               # last pixel: the 8-line macroblock row
+    m = orc.damage_map(c, a)
+    assert m.sum() == 1 and m[67, 119] == 1
+
+
+def test_synth_python_mirror(orc):
+    assert np.array_equal(orc.synth("rand", 37, 5, 9), N.synth_rand(37, 5, 9))
+    assert not np.array_equal(orc.synth("rand", 16, 4, 0), orc.synth("rand", 16, 4, 1))
+
+
+def test_oracle_rejects_what_the_element_rejects(orc):
+    with pytest.raises(ValueError):
+        orc.convert(np.zeros((4, 5, 4), np.uint8))     # odd width
+    with pytest.raises(ValueError):
+        orc.convert(np.zeros((4, 8, 4), np.uint8), out_size=(2, 2), scale_mode=1)  # BOX needs 2:1
+
+
+@settings(max_examples=40, deadline=None)
+@given(w=st.integers(1, 40).map(lambda v: 2 * v), h=st.integers(1, 12).map(lambda v: 2 * v),
+       fmt=st.integers(0, 1), m=st.integers(0, 1), rg=st.integers(0, 1), site=st.integers(0, 1),
+       seed=st.integers(0, 2**31))
+def test_property_c_equals_numpy(w, h, fmt, m, rg, site, seed):
+    import oracle
+    orc = oracle.get()
+    frame = np.random.default_rng(seed).integers(0, 256, (h, w, 4), dtype=np.uint8)
+    buf, off, pit = orc.convert(frame, fmt, m, rg, site)
+    assert_planes_equal(plane_views(buf, off, pit, fmt, w, h), list(N.convert(frame, fmt, m, rg, site)))

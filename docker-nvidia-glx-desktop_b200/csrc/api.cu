@@ -197,7 +197,7 @@ void fused_box(const b200vc_config &c, const std::vector<Tap> &hy, const std::ve
     box_w = box_h = 0;
     for (int x0 = 0; x0 < c.out_w; x0 += K2_TILE_W) {
         const int x1 = std::min(x0 + K2_TILE_W, c.out_w) - 1;
-        int sx = std::min(tidx(hy[x0]), 2 * tidx(hc[x0 >> 1]) - site) & ~1;
+        int sx = std::min(tidx(hy[x0]), 2 * tidx(hc[x0 >> 1]) - site) & ~3;   // 16-byte aligned box start
         int last = std::max(tidx(hy[x1]) + tstep(hy[x1]), 2 * (tidx(hc[x1 >> 1]) + tstep(hc[x1 >> 1])) + 1);
         box_w = std::max(box_w, last - sx + 1);
     }

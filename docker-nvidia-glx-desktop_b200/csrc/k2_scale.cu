@@ -65,7 +65,7 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
         const int hy0 = tap_idx(p.tab.hy[x0]);
         const int uc0 = tap_idx(p.tab.hc[x0 >> 1]);
         int sx = min(hy0, 2 * uc0 - (SITE ? 1 : 0));
-        sx &= ~1;                                         // even, may be -2 at the left frame edge
+        sx &= ~3;     // TMA needs the box's first byte 16-byte aligned (4 pixels); -4 at the left frame edge
         const int vy0 = tap_idx(p.tab.vy[y0]);
         const int vc0 = tap_idx(p.tab.vc[y0 >> 1]);
         const int sy = min(vy0, 2 * vc0) & ~1;
@@ -121,7 +121,7 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
             c0 = avg2(avg2(pa0, pa1), avg2(pb0, pb1));
             c1 = avg2(avg2(pa2, pa3), avg2(pb2, pb3));
         } else {
-            const int ac = sx0 + 4 * kx;                  // absolute column of pixel 0 (even)
+            const int ac = sx0 + 4 * kx;                  // absolute column of pixel 0 (multiple of 4)
             // left neighbours: column 0 takes itself; the window's first item has none (its
             // first chroma column is halo and is never consumed)
             uint32_t la = pa0, lb = pb0;
@@ -129,7 +129,7 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
                 la = chroma_pair<NEG>(ra[-1], m);
                 lb = chroma_pair<NEG>(rb[-1], m);
             }
-            uint32_t l2a = (ac + 2 == 0) ? pa2 : pa1, l2b = (ac + 2 == 0) ? pb2 : pb1;
+            const uint32_t l2a = pa1, l2b = pb1;          // ac % 4 == 0, so pixel 2 is never column 0
             // right neighbours: the last even column (in_w-2, in_w > 2) takes itself
             const bool e0 = (p.in_w > 2) && (ac == p.in_w - 2);
             const bool e2 = (p.in_w > 2) && (ac + 2 == p.in_w - 2);

@@ -1,0 +1,85 @@
+"""Kernel-only timing of every BASELINE.json config (C1..C4) through b200vc_convert_device:
+frames resident in HBM as a ring larger than L2, CUDA events on the launching stream.
+Prints one JSON line per config; used for tuning and for the tables in DESIGN.md."""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "docker-nvidia-glx-desktop_b200")]
+import torch  # noqa: E402
+
+import b200vc  # noqa: E402
+
+PEAK = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(
+    os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+
+CONFIGS = [
+    # name, in_w, in_h, out_w, out_h, fmt, matrix, range, site, flags, damage
+    ("C1 1080p I420 601L mpeg2", 1920, 1080, 1920, 1080, 0, 0, 0, 1, 0, False),
+    ("C1 1080p I420 601L jpeg", 1920, 1080, 1920, 1080, 0, 0, 0, 0, 0, False),
+    ("C2 1440p NV12 709F mpeg2", 2560, 1440, 2560, 1440, 1, 1, 1, 1, 0, False),
+    ("C3 4K->1080p I420 709L fused", 3840, 2160, 1920, 1080, 0, 1, 0, 1, 0, False),
+    ("C3 4K->1080p I420 709L two-pass", 3840, 2160, 1920, 1080, 0, 1, 0, 1, b200vc.FLAG_FORCE_TWO_PASS, False),
+    ("C4 1080p I420 601L mpeg2 +damage", 1920, 1080, 1920, 1080, 0, 0, 0, 1, b200vc.FLAG_DAMAGE_MAP, True),
+]
+
+
+def main():
+    reps = int(sys.argv[1]) if len(sys.argv) > 1 else 50
+    only = sys.argv[2] if len(sys.argv) > 2 else None
+    conv = b200vc.Converter(0)
+    stream = torch.cuda.Stream()
+    for name, iw, ih, ow, oh, fmt, m, rg, site, flags, damage in CONFIGS:
+        if only and only not in name:
+            continue
+        in_b, (total, off, pit) = iw * ih * 4, b200vc.default_layout(fmt, ow, oh)
+        n = max(8, min(64, int(600e6 // in_b)))                 # ring >= ~600 MB of input
+        conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=m, range_=rg, chroma_site=site, flags=flags, max_sessions=8)
+        d_in = torch.randint(0, 256, (n, in_b), dtype=torch.uint8, device="cuda")
+        d_out = torch.zeros((n, total), dtype=torch.uint8, device="cuda")
+        mb = ((iw + 15) // 16) * ((ih + 15) // 16)
+        d_dmg = torch.zeros((n, mb), dtype=torch.uint8, device="cuda")
+        df = b200vc.DeviceFrames()
+        df.bgrx, df.in_pitch, df.in_frame_stride = d_in.data_ptr(), iw * 4, in_b
+        for i in range(3):
+            df.planes[i], df.pitches[i] = d_out.data_ptr() + off[i], pit[i]
+        df.out_frame_stride, df.n_frames = total, n
+        algo = in_b + total
+        if damage:
+            d_prev = torch.roll(d_in, 1, 0).contiguous()
+            df.prev, df.prev_pitch, df.prev_frame_stride = d_prev.data_ptr(), iw * 4, in_b
+            df.damage, df.damage_frame_stride = d_dmg.data_ptr(), mb
+            algo += in_b + mb
+        with torch.cuda.stream(stream):
+            for _ in range(5):
+                conv.convert_device(df, stream.cuda_stream)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(reps):
+                conv.convert_device(df, stream.cuda_stream)
+            e1.record(stream)
+        stream.synchronize()
+        sec = e0.elapsed_time(e1) / 1e3 / reps
+        # single-frame launch (L2-resident, launch-latency bound), reported separately
+        df.n_frames = 1
+        with torch.cuda.stream(stream):
+            for _ in range(20):
+                conv.convert_device(df, stream.cuda_stream)
+            e0.record(stream)
+            for _ in range(200):
+                conv.convert_device(df, stream.cuda_stream)
+            e1.record(stream)
+        stream.synchronize()
+        one = e0.elapsed_time(e1) / 1e3 / 200
+        inf = conv.info()
+        print(json.dumps({"config": name, "ring_frames": n, "fps": round(n / sec, 1), "ms_per_launch": round(sec * 1e3, 4),
+                          "algo_GBs": round(algo * n / sec / 1e9, 1), "frac_of_measured_peak": round(algo * n / sec / 1e9 / PEAK, 4),
+                          "single_frame_us": round(one * 1e6, 2), "path": inf.path, "box": [inf.box_w, inf.box_h]}), flush=True)
+        del d_in, d_out, d_dmg
+        torch.cuda.empty_cache()
+    conv.stop()
+
+
+if __name__ == "__main__":
+    main()

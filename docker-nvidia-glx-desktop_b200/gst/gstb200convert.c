@@ -1,0 +1,212 @@
+/*
+ * gstb200convert.c — GStreamer element "b200convert": drop-in for `videoconvert ! videoscale` on
+ * the BGRx -> I420/NV12 path of the selkies-gstreamer pipeline (reference call sites:
+ * /root/reference Dockerfile:467-471, selkies-gstreamer-entrypoint.sh:8,44-47, README.md:21).
+ *
+ * NEVER COMPILED HERE. GStreamer, GLib and their headers are absent from the build image and the
+ * GPU box, so this file has not been through a compiler. It is a thin shim: every
+ * piece of work is a call into libb200vc.so (include/b200vc.h), which is what is tested and timed.
+ * Build, on a machine that has GStreamer:
+ *   gcc -shared -fPIC gstb200convert.c -o libgstb200convert.so \
+ *       $(pkg-config --cflags --libs gstreamer-video-1.0) -I../../include -L.. -lb200vc
+ * then put it on GST_PLUGIN_PATH (the reference wipes the registry cache at every start,
+ * selkies-gstreamer-entrypoint.sh:41, so it is picked up) and replace `videoconvert ! videoscale`
+ * by `b200convert` in the pipeline string.
+ */
+#include <gst/gst.h>
+#include <gst/video/video.h>
+#include <gst/video/gstvideofilter.h>
+
+#include "b200vc.h"
+
+#define GST_TYPE_B200_CONVERT (gst_b200_convert_get_type())
+G_DECLARE_FINAL_TYPE(GstB200Convert, gst_b200_convert, GST, B200_CONVERT, GstVideoFilter)
+
+struct _GstB200Convert {
+    GstVideoFilter parent;
+    b200vc_ctx *ctx;
+    gint device_id;
+    gboolean damage_map;
+    gint n_bands;
+};
+
+G_DEFINE_TYPE(GstB200Convert, gst_b200_convert, GST_TYPE_VIDEO_FILTER)
+
+GST_DEBUG_CATEGORY_STATIC(b200convert_debug);
+#define GST_CAT_DEFAULT b200convert_debug
+
+enum { PROP_0, PROP_DEVICE_ID, PROP_DAMAGE_MAP, PROP_N_BANDS };
+
+static GstStaticPadTemplate sink_tmpl = GST_STATIC_PAD_TEMPLATE("sink", GST_PAD_SINK, GST_PAD_ALWAYS,
+    GST_STATIC_CAPS("video/x-raw, format=(string)BGRx, width=(int)[2,16384], height=(int)[2,16384], "
+                    "framerate=(fraction)[0/1,2147483647/1]"));
+static GstStaticPadTemplate src_tmpl = GST_STATIC_PAD_TEMPLATE("src", GST_PAD_SRC, GST_PAD_ALWAYS,
+    GST_STATIC_CAPS("video/x-raw, format=(string){I420,NV12}, width=(int)[2,16384], height=(int)[2,16384], "
+                    "framerate=(fraction)[0/1,2147483647/1]"));
+
+/* transform_caps: what videoconvert and videoscale do combined — drop format, colorimetry and
+ * chroma-site, open width/height/pixel-aspect-ratio to ranges; the pad templates then restrict. */
+static GstCaps *
+gst_b200_convert_transform_caps(GstBaseTransform *trans, GstPadDirection direction, GstCaps *caps, GstCaps *filter)
+{
+    GstCaps *out = gst_caps_new_empty();
+    for (guint i = 0; i < gst_caps_get_size(caps); i++) {
+        GstStructure *s = gst_structure_copy(gst_caps_get_structure(caps, i));
+        gst_structure_remove_fields(s, "format", "colorimetry", "chroma-site", NULL);
+        gst_structure_set(s, "width", GST_TYPE_INT_RANGE, 2, 16384, "height", GST_TYPE_INT_RANGE, 2, 16384, NULL);
+        if (gst_structure_has_field(s, "pixel-aspect-ratio"))
+            gst_structure_set(s, "pixel-aspect-ratio", GST_TYPE_FRACTION_RANGE, 1, G_MAXINT, G_MAXINT, 1, NULL);
+        gst_caps_append_structure(out, s);
+    }
+    GstCaps *tmpl = gst_pad_get_pad_template_caps(direction == GST_PAD_SINK ? trans->srcpad : trans->sinkpad);
+    GstCaps *res = gst_caps_intersect_full(out, tmpl, GST_CAPS_INTERSECT_FIRST);
+    gst_caps_unref(out);
+    gst_caps_unref(tmpl);
+    if (filter) {
+        GstCaps *f = gst_caps_intersect_full(filter, res, GST_CAPS_INTERSECT_FIRST);
+        gst_caps_unref(res);
+        res = f;
+    }
+    return res;
+}
+
+/* fixate_caps: takes ownership of othercaps; prefer the input size (no scaling unless asked). */
+static GstCaps *
+gst_b200_convert_fixate_caps(GstBaseTransform *trans, GstPadDirection direction, GstCaps *caps, GstCaps *othercaps)
+{
+    othercaps = gst_caps_truncate(gst_caps_make_writable(othercaps));
+    GstStructure *in = gst_caps_get_structure(caps, 0), *out = gst_caps_get_structure(othercaps, 0);
+    gint w, h;
+    if (gst_structure_get_int(in, "width", &w)) gst_structure_fixate_field_nearest_int(out, "width", w);
+    if (gst_structure_get_int(in, "height", &h)) gst_structure_fixate_field_nearest_int(out, "height", h);
+    if (direction == GST_PAD_SINK) gst_structure_fixate_field_string(out, "format", "I420");
+    return gst_caps_fixate(othercaps);
+}
+
+static int matrix_of(const GstVideoInfo *i)
+{
+    return i->colorimetry.matrix == GST_VIDEO_COLOR_MATRIX_BT601 ? B200VC_MATRIX_BT601 : B200VC_MATRIX_BT709;
+}
+
+/* set_info: (re)build the converter for the negotiated caps. FALSE = not negotiated. */
+static gboolean
+gst_b200_convert_set_info(GstVideoFilter *filter, GstCaps *incaps, GstVideoInfo *in, GstCaps *outcaps, GstVideoInfo *out)
+{
+    GstB200Convert *self = GST_B200_CONVERT(filter);
+    b200vc_config cfg = { 0 };
+    int m, r, s;
+    b200vc_default_colorimetry(GST_VIDEO_INFO_HEIGHT(out), &m, &r, &s);
+    cfg.device = self->device_id;
+    cfg.in_w = GST_VIDEO_INFO_WIDTH(in);    cfg.in_h = GST_VIDEO_INFO_HEIGHT(in);
+    cfg.out_w = GST_VIDEO_INFO_WIDTH(out);  cfg.out_h = GST_VIDEO_INFO_HEIGHT(out);
+    cfg.out_format = GST_VIDEO_INFO_FORMAT(out) == GST_VIDEO_FORMAT_NV12 ? B200VC_FMT_NV12 : B200VC_FMT_I420;
+    /* honour the caps, do not assume */
+    cfg.matrix = out->colorimetry.matrix == GST_VIDEO_COLOR_MATRIX_UNKNOWN ? m : matrix_of(out);
+    cfg.range = out->colorimetry.range == GST_VIDEO_COLOR_RANGE_UNKNOWN ? r
+              : (out->colorimetry.range == GST_VIDEO_COLOR_RANGE_0_255 ? B200VC_RANGE_FULL : B200VC_RANGE_LIMITED);
+    cfg.chroma_site = out->chroma_site == GST_VIDEO_CHROMA_SITE_UNKNOWN ? s
+                    : ((out->chroma_site & GST_VIDEO_CHROMA_SITE_H_COSITED) ? B200VC_SITE_H_COSITED : B200VC_SITE_NONE);
+    cfg.flags = (self->damage_map && cfg.in_w == cfg.out_w && cfg.in_h == cfg.out_h) ? B200VC_FLAG_DAMAGE_MAP : 0;
+    cfg.flags |= B200VC_FLAG_REGISTER_HOST;           /* ximagesrc hands out a small pool of XShm images */
+    cfg.n_bands = self->n_bands;
+    if (self->ctx) { b200vc_destroy(self->ctx); self->ctx = NULL; }
+    int rc = b200vc_create(&cfg, &self->ctx);
+    if (rc != B200VC_OK) {
+        GST_ELEMENT_ERROR(self, LIBRARY, INIT, ("b200vc_create: %s", b200vc_status_string(rc)), ("%s", b200vc_last_error(NULL)));
+        return FALSE;
+    }
+    return TRUE;
+}
+
+/* transform_frame: one synchronous conversion; `out` is complete on return. */
+static GstFlowReturn
+gst_b200_convert_transform_frame(GstVideoFilter *filter, GstVideoFrame *in, GstVideoFrame *out)
+{
+    GstB200Convert *self = GST_B200_CONVERT(filter);
+    if (!self->ctx) return GST_FLOW_NOT_NEGOTIATED;
+    void *planes[3] = { GST_VIDEO_FRAME_PLANE_DATA(out, 0), GST_VIDEO_FRAME_PLANE_DATA(out, 1),
+                        GST_VIDEO_FRAME_N_PLANES(out) > 2 ? GST_VIDEO_FRAME_PLANE_DATA(out, 2) : NULL };
+    size_t pitches[3] = { (size_t)GST_VIDEO_FRAME_PLANE_STRIDE(out, 0), (size_t)GST_VIDEO_FRAME_PLANE_STRIDE(out, 1),
+                          GST_VIDEO_FRAME_N_PLANES(out) > 2 ? (size_t)GST_VIDEO_FRAME_PLANE_STRIDE(out, 2) : 0 };
+    int rc = b200vc_convert(self->ctx, GST_VIDEO_FRAME_PLANE_DATA(in, 0), (size_t)GST_VIDEO_FRAME_PLANE_STRIDE(in, 0),
+                            planes, pitches, NULL /* the map would travel as a custom GstMeta */);
+    if (rc != B200VC_OK) {
+        GST_ELEMENT_ERROR(self, LIBRARY, FAILED, ("b200vc_convert: %s", b200vc_status_string(rc)), ("%s", b200vc_last_error(self->ctx)));
+        return GST_FLOW_ERROR;
+    }
+    return GST_FLOW_OK;
+}
+
+static gboolean gst_b200_convert_stop(GstBaseTransform *trans)
+{
+    GstB200Convert *self = GST_B200_CONVERT(trans);
+    if (self->ctx) { b200vc_destroy(self->ctx); self->ctx = NULL; }
+    return TRUE;
+}
+
+static void gst_b200_convert_set_property(GObject *obj, guint id, const GValue *v, GParamSpec *ps)
+{
+    GstB200Convert *self = GST_B200_CONVERT(obj);
+    GST_OBJECT_LOCK(self);
+    switch (id) {
+    case PROP_DEVICE_ID: self->device_id = g_value_get_int(v); break;
+    case PROP_DAMAGE_MAP: self->damage_map = g_value_get_boolean(v); break;
+    case PROP_N_BANDS: self->n_bands = g_value_get_int(v); break;
+    default: G_OBJECT_WARN_INVALID_PROPERTY_ID(obj, id, ps);
+    }
+    GST_OBJECT_UNLOCK(self);
+}
+
+static void gst_b200_convert_get_property(GObject *obj, guint id, GValue *v, GParamSpec *ps)
+{
+    GstB200Convert *self = GST_B200_CONVERT(obj);
+    switch (id) {
+    case PROP_DEVICE_ID: g_value_set_int(v, self->device_id); break;
+    case PROP_DAMAGE_MAP: g_value_set_boolean(v, self->damage_map); break;
+    case PROP_N_BANDS: g_value_set_int(v, self->n_bands); break;
+    default: G_OBJECT_WARN_INVALID_PROPERTY_ID(obj, id, ps);
+    }
+}
+
+static void gst_b200_convert_class_init(GstB200ConvertClass *klass)
+{
+    GObjectClass *go = G_OBJECT_CLASS(klass);
+    GstElementClass *el = GST_ELEMENT_CLASS(klass);
+    GstBaseTransformClass *bt = GST_BASE_TRANSFORM_CLASS(klass);
+    GstVideoFilterClass *vf = GST_VIDEO_FILTER_CLASS(klass);
+    go->set_property = gst_b200_convert_set_property;
+    go->get_property = gst_b200_convert_get_property;
+    g_object_class_install_property(go, PROP_DEVICE_ID, g_param_spec_int("device-id", "Device", "CUDA device ordinal", 0, 63, 0, G_PARAM_READWRITE));
+    g_object_class_install_property(go, PROP_DAMAGE_MAP, g_param_spec_boolean("damage-map", "Damage map", "Emit the 16x16 damage map", FALSE, G_PARAM_READWRITE));
+    g_object_class_install_property(go, PROP_N_BANDS, g_param_spec_int("n-bands", "Bands", "Row bands a frame is pipelined in", 0, 64, 0, G_PARAM_READWRITE));
+    gst_element_class_add_static_pad_template(el, &sink_tmpl);
+    gst_element_class_add_static_pad_template(el, &src_tmpl);
+    gst_element_class_set_static_metadata(el, "B200 BGRx converter/scaler", "Filter/Converter/Video/Scaler",
+                                          "BGRx to I420/NV12 with bilinear scale on NVIDIA B200", "b200vc");
+    bt->transform_caps = GST_DEBUG_FUNCPTR(gst_b200_convert_transform_caps);
+    bt->fixate_caps = GST_DEBUG_FUNCPTR(gst_b200_convert_fixate_caps);
+    bt->stop = GST_DEBUG_FUNCPTR(gst_b200_convert_stop);
+    bt->passthrough_on_same_caps = FALSE;
+    vf->set_info = GST_DEBUG_FUNCPTR(gst_b200_convert_set_info);
+    vf->transform_frame = GST_DEBUG_FUNCPTR(gst_b200_convert_transform_frame);
+}
+
+static void gst_b200_convert_init(GstB200Convert *self)
+{
+    self->ctx = NULL;
+    self->device_id = 0;
+    self->damage_map = FALSE;
+    self->n_bands = 0;
+}
+
+static gboolean plugin_init(GstPlugin *plugin)
+{
+    GST_DEBUG_CATEGORY_INIT(b200convert_debug, "b200convert", 0, "B200 BGRx converter");
+    return gst_element_register(plugin, "b200convert", GST_RANK_NONE, GST_TYPE_B200_CONVERT);
+}
+
+#ifndef PACKAGE
+#define PACKAGE "b200vc"
+#endif
+GST_PLUGIN_DEFINE(GST_VERSION_MAJOR, GST_VERSION_MINOR, b200convert, "BGRx to I420/NV12 on NVIDIA B200",
+                  plugin_init, "0.1", "MPL", PACKAGE, "https://example.invalid/b200vc")

@@ -1,0 +1,37 @@
+"""Boundary test: the headless C harness drives libb200vc.so in GstVideoFilter call order
+(set_info -> transform_frame xN -> renegotiation in mid-stream -> stop) from plain C, with no Python
+and no torch in the process; its output file is compared with the oracle."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from helpers import assert_planes_equal, plane_views
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HARNESS = os.path.join(ROOT, "docker-nvidia-glx-desktop_b200", "harness", "filter_harness")
+
+
+@pytest.mark.parametrize("geo", [(1920, 1080, 1920, 1080), (1280, 720, 640, 360)])
+def test_c_harness_in_gstvideofilter_call_order(orc, tmp_path, geo):
+    w, h, ow, oh = geo
+    n = 4
+    out = tmp_path / "frames.bin"
+    r = subprocess.run([HARNESS, str(w), str(h), str(ow), str(oh), str(n), str(out)], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    assert f"frames {n // 2}" in r.stdout          # stats are per negotiated context: the NV12 half
+    data = np.fromfile(out, np.uint8)
+    import b200vc
+    m, rg, site = b200vc.default_colorimetry(oh)   # caps left colorimetry open: defaults by height
+    pos = 0
+    for k in range(n):
+        fmt = 0 if k < n // 2 else 1
+        total, off, pit = orc.default_layout(fmt, ow, oh)
+        frame = orc.synth("rand", w, h, k)
+        buf, ooff, opit = orc.convert(frame, fmt, m, rg, site, out_size=(ow, oh))
+        assert_planes_equal(plane_views(data[pos:pos + total], off, pit, fmt, ow, oh),
+                            plane_views(buf, ooff, opit, fmt, ow, oh), f"frame {k}")
+        pos += total
+    assert pos == data.size

@@ -33,7 +33,9 @@ SYMBOLS = [
     "b200vc_version", "b200vc_create", "b200vc_destroy", "b200vc_last_error", "b200vc_get_info",
     "b200vc_get_stats", "b200vc_reset", "b200vc_convert", "b200vc_convert_batch", "b200vc_submit",
     "b200vc_collect", "b200vc_host_alloc", "b200vc_host_free", "b200vc_convert_device",
+    "b200vc_convert_scale_device_static",
 ]
+STATIC_SCRATCH_BYTES = 3133440
 
 
 class Config(C.Structure):
@@ -105,6 +107,7 @@ def load() -> C.CDLL:
     L.b200vc_host_alloc.argtypes = [sz, C.POINTER(vp)]
     L.b200vc_host_free.argtypes = [vp]
     L.b200vc_convert_device.argtypes = [vp, C.POINTER(DeviceFrames), vp]
+    L.b200vc_convert_scale_device_static.argtypes = [C.POINTER(Config), C.POINTER(DeviceFrames), vp, C.c_char_p, sz]
     _lib = L
     return L
 

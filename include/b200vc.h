@@ -185,6 +185,37 @@ int b200vc_host_free(void *p);
  * passed as void*; NULL = the default stream). Asynchronous: returns after enqueueing. */
 int b200vc_convert_device(b200vc_ctx *ctx, const b200vc_device_frames *frames, void *cuda_stream);
 
+/* ---- no-allocation variant ----------------------------------------------------------------- */
+
+/* Maximum intermediate frame the entry point below can hold: an I420 frame of a 1920x1088 source. */
+#define B200VC_STATIC_SCRATCH_BYTES 3133440
+
+/* This entry point has no counterpart in the reference.
+ *
+ * Convert + scale (the general two-pass path: conversion at the source size into an intermediate
+ * I420 frame, then the 2-tap plane scaler) for callers that must not allocate memory: a streaming
+ * thread following a caps change mid-stream cannot afford cudaMalloc/cudaFree, which serialise
+ * against everything in flight on the device and would stall the other sessions on that GPU; and a
+ * process that gave all GPU memory to another pool at start-up has none left to ask for. It takes
+ * no context (creating one allocates): `cfg` carries the negotiated caps (max_sessions, n_inflight,
+ * n_bands are ignored; in and out sizes must differ; no damage map), `frames` the device buffers as
+ * for b200vc_convert_device (input pointer/pitch/stride multiples of 16 bytes, output pointers and
+ * pitches multiples of 4), `cuda_stream` the stream to enqueue on. It calls no cudaMalloc, cudaFree
+ * or any other allocating routine.
+ *
+ * The intermediate frame lives in a fixed device array inside the library, B200VC_STATIC_SCRATCH_BYTES
+ * long, which every GPU that runs this library keeps until the process exits. Sources whose
+ * intermediate frame would not fit (anything above 1920x1088 pixels) are refused with
+ * B200VC_ERR_UNSUPPORTED and a message in `errbuf`. The work runs on the calling thread's current
+ * device, which cfg->device must name. The first call on each device also looks up that device's
+ * address of the array; make that first call before any stream capture begins. All calls on a device
+ * share the one array: nothing in it needs clearing between calls (each call overwrites what it
+ * reads), but two calls that overlap on the GPU race on it, so order them (one stream, or events).
+ *
+ * errbuf (may be NULL) receives the reason when the result is not B200VC_OK. */
+int b200vc_convert_scale_device_static(const b200vc_config *cfg, const b200vc_device_frames *frames,
+                                       void *cuda_stream, char *errbuf, size_t errbuf_len);
+
 #ifdef __cplusplus
 }
 #endif

@@ -53,6 +53,16 @@ __device__ __forceinline__ uint32_t ldg_stream_u32(const void *p)
     return r;
 }
 
+// predicated 4-byte streaming load (no branch): 0 when pred is false
+__device__ __forceinline__ uint32_t ldg_stream_u32_if(const void *p, bool pred)
+{
+    uint32_t r;
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %2, 0;\n\tmov.u32 %0, 0;\n\t"
+                 "@q ld.global.nc.L1::no_allocate.u32 %0, [%1];\n\t}"
+                 : "=r"(r) : "l"(p), "r"((uint32_t)pred));
+    return r;
+}
+
 // Y sum of one pixel; the 8-bit result is byte 1 of the return value (sum is in 0..65535).
 __device__ __forceinline__ uint32_t luma_sum(uint32_t pix, const Matrix &m)
 {

@@ -4,17 +4,19 @@
 // the reference's x264enc fallback (/root/reference Dockerfile:467-471, README.md:21); the line
 // chain it restates is SURVEY.md §8 (a2)-(a5) / Appendix A, the damage map is §8 (a7).
 //
-// Layout of the work. One CTA (8 warps) owns a 128 x 16 pixel tile = 8 macroblocks of one
-// macroblock row. Warp w owns the line pair (2w, 2w+1); lane l owns pixels 4l..4l+3 of both lines,
-// fetched as one coalesced 16-byte streaming load per line (512 contiguous bytes per warp
-// request). Everything per pixel happens in registers:
+// Layout of the work. A warp owns one 128 x 16 pixel stripe = 8 macroblocks of one macroblock row,
+// and walks it in two steps of 8 lines. Lane l owns pixels 4l..4l+3 of every line: one coalesced
+// 16-byte streaming load per line (512 contiguous bytes per warp request), eight in flight per
+// step. Everything per pixel happens in registers:
 //   Y      one dp4a per pixel, four results packed to a word with PRMT
 //   U,V    two dp4a per pixel, kept as 2x16-bit lanes in one word; the horizontal filter
-//          (h2 or cosited 1-2-1, neighbours across lanes by one shuffle, tile halo by one
+//          (h2 or cosited 1-2-1, neighbours across lanes by one shuffle, stripe halo by one
 //          extra 4-byte load in lane 0) and the vertical rounded mean run on both lanes at once
-//   damage XOR against the previous frame (x byte masked), warp ballot, 4 lanes = 1 macroblock
-// The tile's planar output is staged in 3 KB of shared memory so that every plane leaves the SM
-// as full 16-byte stores of contiguous row segments.
+//   damage XOR against the previous frame (x byte masked) accumulated over the 16 lines, one warp
+//          ballot at the end, 4 lanes = 1 macroblock, 8 map bytes per warp
+// Each step's planar output is staged in the warp's own 1.5 KB of shared memory (no block-level
+// barrier anywhere) and leaves the SM as 16-byte stores of contiguous 128-byte row segments.
+// A CTA is four independent warps covering 512 x 16 pixels.
 //
 // HBM roofline: algorithmic bytes per pixel = 4 (read) + 1.5 (write) [+ 4 previous frame].
 #include "device_utils.cuh"
@@ -23,179 +25,191 @@ namespace b200vc {
 
 namespace {
 
-constexpr int TW = K1_TILE_W;
-constexpr int TH = K1_TILE_H;
+constexpr int TW = K1_TILE_W;            // 128 pixels per warp stripe
+constexpr int TH = K1_TILE_H;            // 16 lines per warp stripe
+constexpr int WARPS = K1_WARPS_PER_CTA;  // 4
 constexpr uint32_t FULL = 0xffffffffu;
 
-template <int FMT, int SITE, bool NEG, bool DMG>
-__global__ void __launch_bounds__(256) k1_convert_kernel(const ConvertParams p)
+// HR = lines a warp loads, converts and stores per step (4 or 8); a stripe takes 16 / HR steps.
+template <int HR>
+struct WarpStage {
+    uint8_t y[HR][TW];                   // HR x 128 B
+    uint8_t c[HR / 2][TW];               // I420: [0..63] U, [64..127] V; NV12: UVUV..
+};
+
+__device__ __noinline__ void store_tail(uint8_t *dst, const uint8_t *src, int valid)
 {
-    __shared__ __align__(16) uint8_t s_y[TH][TW];
-    __shared__ __align__(16) uint8_t s_c[TH / 2][TW];   // I420: [0..63] U, [64..127] V; NV12: UVUV..
-    __shared__ uint32_t s_dmg[8];
+    for (int i = 0; i < valid; i++) dst[i] = src[i];
+}
+
+// 16 bytes from shared to global, or the leading `valid` bytes when the row ends inside them
+__device__ __forceinline__ void store16(uint8_t *dst, const uint8_t *src, int valid)
+{
+    if (valid >= 16)
+        *reinterpret_cast<uint4 *>(dst) = *reinterpret_cast<const uint4 *>(src);
+    else
+        store_tail(dst, src, valid);
+}
+
+template <int FMT, int SITE, bool NEG, bool DMG, int HR>
+__global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertParams p)
+{
+    __shared__ __align__(16) WarpStage<HR> s_stage[WARPS];
+    constexpr int PAIRS = HR / 2;
 
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    const int x0 = blockIdx.x * TW;
+    const int x0 = (blockIdx.x * WARPS + warp) * TW;      // first column of this warp's stripe
     const int y0 = blockIdx.y * TH;
     const int frame = blockIdx.z;
+    if (x0 >= p.w) return;                                 // warp-uniform: whole warp leaves
 
-    const int x = x0 + lane * 4;          // first pixel of this thread
-    const int ya = y0 + warp * 2;         // even line of this warp's pair
-    const bool row_ok = ya < p.h;         // h is even, so ya + 1 < h as well
-    int nvalid = p.w - x;                 // w even, x % 4 == 0  ->  <=0, 2, or >= 4
-    nvalid = nvalid < 0 ? 0 : (nvalid > 4 ? 4 : nvalid);
-
-    const uint8_t *src = p.src + (long long)frame * p.src_frame_stride + (long long)ya * p.src_pitch;
-    uint4 a = make_uint4(0, 0, 0, 0), b = make_uint4(0, 0, 0, 0);
-    uint32_t halo_a = 0, halo_b = 0;
-
-    if (row_ok) {
-        if (nvalid == 4) {
-            a = ldg_stream_v4(src + (long long)x * 4);
-            b = ldg_stream_v4(src + p.src_pitch + (long long)x * 4);
-        } else if (nvalid == 2) {
-            uint2 t = ldg_stream_v2(src + (long long)x * 4);
-            a = make_uint4(t.x, t.y, t.y, t.y);
-            t = ldg_stream_v2(src + p.src_pitch + (long long)x * 4);
-            b = make_uint4(t.x, t.y, t.y, t.y);
-        }
-        if (SITE == 1 && lane == 0 && x > 0 && nvalid) {       // left halo pixel of the tile
-            halo_a = ldg_stream_u32(src + (long long)(x - 1) * 4);
-            halo_b = ldg_stream_u32(src + p.src_pitch + (long long)(x - 1) * 4);
-        }
-    }
-
-    // ---- K3: damage -----------------------------------------------------------------------
-    if (DMG) {
-        uint32_t diff = 0;
-        if (row_ok && nvalid) {
-            const uint8_t *prv = p.prev + (long long)frame * p.prev_frame_stride + (long long)ya * p.prev_pitch;
-            uint4 pa, pb;
-            if (nvalid == 4) {
-                pa = ldg_stream_v4(prv + (long long)x * 4);
-                pb = ldg_stream_v4(prv + p.prev_pitch + (long long)x * 4);
-            } else {
-                uint2 t = ldg_stream_v2(prv + (long long)x * 4);
-                pa = make_uint4(t.x, t.y, t.y, t.y);
-                t = ldg_stream_v2(prv + p.prev_pitch + (long long)x * 4);
-                pb = make_uint4(t.x, t.y, t.y, t.y);
-            }
-            diff = ((a.x ^ pa.x) | (a.y ^ pa.y) | (a.z ^ pa.z) | (a.w ^ pa.w) |
-                    (b.x ^ pb.x) | (b.y ^ pb.y) | (b.z ^ pb.z) | (b.w ^ pb.w)) & 0x00FFFFFFu;
-        }
-        const uint32_t ballot = __ballot_sync(FULL, diff != 0);
-        if (lane == 0)
-            s_dmg[warp] = ballot;
-    }
-
-    // ---- luma --------------------------------------------------------------------------------
+    WarpStage<HR> &st = s_stage[warp];
     const Matrix &m = p.mx;
-    {
-        uint32_t ya4 = pack_luma4(luma_sum(a.x, m), luma_sum(a.y, m), luma_sum(a.z, m), luma_sum(a.w, m));
-        uint32_t yb4 = pack_luma4(luma_sum(b.x, m), luma_sum(b.y, m), luma_sum(b.z, m), luma_sum(b.w, m));
-        *reinterpret_cast<uint32_t *>(&s_y[warp * 2][lane * 4]) = ya4;
-        *reinterpret_cast<uint32_t *>(&s_y[warp * 2 + 1][lane * 4]) = yb4;
-    }
+    const int x = x0 + lane * 4;                           // first pixel of this thread
+    const int remain = p.w - x;                            // w even, x % 4 == 0  ->  <= 0, 2, or >= 4
+    const bool v4 = remain >= 4, v2 = remain == 2;         // this lane holds 4 / 2 / no valid pixels
+    const bool interior_x = x0 + TW <= p.w;                // warp-uniform
+    const bool halo = SITE == 1 && lane == 0 && x0 > 0;    // lane 0 fetches the stripe's left neighbour
+    // cosited right edge: the last even column (w-2, when w > 2) takes itself as right neighbour
+    const bool edge3 = SITE == 1 && p.w > 2 && x + 4 == p.w;
+    const bool edge1 = SITE == 1 && p.w > 2 && x + 2 == p.w;
 
-    // ---- chroma: 4:4:4 (u,v) pairs, horizontal filter per line, vertical mean ------------------
-    uint32_t pa0 = chroma_pair<NEG>(a.x, m), pa1 = chroma_pair<NEG>(a.y, m);
-    uint32_t pa2 = chroma_pair<NEG>(a.z, m), pa3 = chroma_pair<NEG>(a.w, m);
-    uint32_t pb0 = chroma_pair<NEG>(b.x, m), pb1 = chroma_pair<NEG>(b.y, m);
-    uint32_t pb2 = chroma_pair<NEG>(b.z, m), pb3 = chroma_pair<NEG>(b.w, m);
-    uint32_t c0, c1;
-    if (SITE == 0) {
-        c0 = avg2(avg2(pa0, pa1), avg2(pb0, pb1));
-        c1 = avg2(avg2(pa2, pa3), avg2(pb2, pb3));
-    } else {
-        // left neighbour of pixel 0: previous lane's pixel 3, the tile halo, or (column 0) itself
-        uint32_t la = __shfl_up_sync(FULL, pa3, 1);
-        uint32_t lb = __shfl_up_sync(FULL, pb3, 1);
-        if (lane == 0) {
-            la = (x > 0) ? chroma_pair<NEG>(halo_a, m) : pa0;
-            lb = (x > 0) ? chroma_pair<NEG>(halo_b, m) : pb0;
-        }
-        // last even column (w-2, when w > 2) takes itself as right neighbour: FILT_1_3
-        uint32_t ra1 = pa1, rb1 = pb1, ra3 = pa3, rb3 = pb3;
-        if (p.w > 2) {
-            if (x + 4 == p.w) { ra3 = pa2; rb3 = pb2; }
-            if (x + 2 == p.w) { ra1 = pa0; rb1 = pb0; }
-        }
-        c0 = avg2(filt121(la, pa0, ra1), filt121(lb, pb0, rb1));
-        c1 = avg2(filt121(pa1, pa2, ra3), filt121(pb1, pb2, rb3));
-    }
-    if (FMT == 0) {
-        uint32_t uuvv = prmt(c0, c1, 0x6240);                 // u0 u1 v0 v1
-        *reinterpret_cast<uint16_t *>(&s_c[warp][lane * 2]) = (uint16_t)(uuvv & 0xffffu);
-        *reinterpret_cast<uint16_t *>(&s_c[warp][64 + lane * 2]) = (uint16_t)(uuvv >> 16);
-    } else {
-        *reinterpret_cast<uint32_t *>(&s_c[warp][lane * 4]) = prmt(c0, c1, 0x6420);   // u0 v0 u1 v1
-    }
-
-    __syncthreads();
-
-    // ---- planar stores, 16 bytes per thread -------------------------------------------------------
-    const int t = threadIdx.x;
+    const uint8_t *src = p.src + (long long)frame * p.src_frame_stride + (long long)y0 * p.src_pitch + (long long)x * 4;
+    const uint8_t *prv = DMG ? p.prev + (long long)frame * p.prev_frame_stride + (long long)y0 * p.prev_pitch + (long long)x * 4
+                             : nullptr;
     const long long fo = (long long)frame * p.out.frame_stride;
-    if (t < 128) {                                         // Y: 16 rows x 8 segments
-        const int row = t >> 3, seg = t & 7;
-        const int gy = y0 + row, gx = x0 + seg * 16;
-        if (gy < p.h && gx < p.w) {
-            uint8_t *dst = p.out.p[0] + fo + (long long)gy * p.out.pitch[0] + gx;
-            if (gx + 16 <= p.w) {
-                *reinterpret_cast<uint4 *>(dst) = *reinterpret_cast<const uint4 *>(&s_y[row][seg * 16]);
-            } else {
-                for (int i = 0; i < p.w - gx; i++) dst[i] = s_y[row][seg * 16 + i];
-            }
-        }
-    } else if (t < 192) {                                  // chroma: 8 rows x 8 segments
-        const int idx = t - 128, row = idx >> 3, s = idx & 7;
-        const int gy = (y0 >> 1) + row;
-        if (gy < (p.h >> 1)) {
-            if (FMT == 0) {
-                const int plane = 1 + (s >> 2), seg = s & 3;
-                const int gx = (x0 >> 1) + seg * 16, cw = p.w >> 1;
-                if (gx < cw) {
-                    uint8_t *dst = p.out.p[plane] + fo + (long long)gy * p.out.pitch[plane] + gx;
-                    const uint8_t *sp = &s_c[row][(plane - 1) * 64 + seg * 16];
-                    if (gx + 16 <= cw) {
-                        *reinterpret_cast<uint4 *>(dst) = *reinterpret_cast<const uint4 *>(sp);
-                    } else {
-                        for (int i = 0; i < cw - gx; i++) dst[i] = sp[i];
-                    }
-                }
-            } else {
-                const int gx = x0 + s * 16;
-                if (gx < p.w) {
-                    uint8_t *dst = p.out.p[1] + fo + (long long)gy * p.out.pitch[1] + gx;
-                    const uint8_t *sp = &s_c[row][s * 16];
-                    if (gx + 16 <= p.w) {
-                        *reinterpret_cast<uint4 *>(dst) = *reinterpret_cast<const uint4 *>(sp);
-                    } else {
-                        for (int i = 0; i < p.w - gx; i++) dst[i] = sp[i];
-                    }
-                }
-            }
-        }
-    } else if (DMG && t < 200) {                           // damage: 8 macroblocks of this tile
-        const int k = t - 192;
-        const int mbx = (x0 >> 4) + k;
-        if (mbx < p.mb_w) {
-            uint32_t any = 0;
+    const int seg = lane & 7, gx = x0 + seg * 16;          // this lane's 16-byte segment in the store phase
+    uint32_t diff = 0;
+
+#pragma unroll 1
+    for (int step = 0; step < TH / HR; step++) {
+        const int yh = y0 + step * HR;
+        if (yh >= p.h) break;                              // warp-uniform
+        const int rows = min(HR, p.h - yh);                // even
+
+        // ---- loads: HR lines x 16 bytes per thread in flight ------------------------------------
+        uint4 px[HR];
+        uint32_t hl[HR];
+        if (rows == HR && interior_x) {                    // warp-uniform: straight-line loads
 #pragma unroll
-            for (int w = 0; w < 8; w++) any |= (s_dmg[w] >> (4 * k)) & 0xFu;
-            p.damage[(long long)frame * p.damage_frame_stride + (long long)(y0 >> 4) * p.mb_w + mbx] = any ? 1 : 0;
+            for (int r = 0; r < HR; r++) {
+                px[r] = ldg_stream_v4(src);
+                hl[r] = SITE == 1 ? ldg_stream_u32_if(src - 4, halo) : 0;
+                if (DMG) {
+                    const uint4 q = ldg_stream_v4(prv);
+                    diff |= (px[r].x ^ q.x) | (px[r].y ^ q.y) | (px[r].z ^ q.z) | (px[r].w ^ q.w);
+                    prv += p.prev_pitch;
+                }
+                src += p.src_pitch;
+            }
+        } else {                                           // right/bottom frame edge: per-lane validity
+#pragma unroll
+            for (int r = 0; r < HR; r++) {
+                px[r] = make_uint4(0, 0, 0, 0);            // pixels past the edge: never stored, never damage
+                hl[r] = 0;
+                if (r < rows) {
+                    uint4 q = make_uint4(0, 0, 0, 0);
+                    if (v4) {
+                        px[r] = ldg_stream_v4(src);
+                        if (DMG) q = ldg_stream_v4(prv);
+                    } else if (v2) {
+                        const uint2 t = ldg_stream_v2(src);
+                        px[r].x = t.x;  px[r].y = t.y;
+                        if (DMG) { const uint2 u = ldg_stream_v2(prv);  q.x = u.x;  q.y = u.y; }
+                    }
+                    if (SITE == 1) hl[r] = ldg_stream_u32_if(src - 4, halo);
+                    if (DMG) diff |= (px[r].x ^ q.x) | (px[r].y ^ q.y) | (px[r].z ^ q.z) | (px[r].w ^ q.w);
+                }
+                src += p.src_pitch;
+                if (DMG) prv += p.prev_pitch;
+            }
         }
+
+        // ---- per line pair: luma, chroma ---------------------------------------------------------
+#pragma unroll
+        for (int k = 0; k < PAIRS; k++) {
+            const uint4 a = px[2 * k], b = px[2 * k + 1];
+            *reinterpret_cast<uint32_t *>(&st.y[2 * k][lane * 4]) =
+                pack_luma4(luma_sum(a.x, m), luma_sum(a.y, m), luma_sum(a.z, m), luma_sum(a.w, m));
+            *reinterpret_cast<uint32_t *>(&st.y[2 * k + 1][lane * 4]) =
+                pack_luma4(luma_sum(b.x, m), luma_sum(b.y, m), luma_sum(b.z, m), luma_sum(b.w, m));
+
+            const uint32_t pa0 = chroma_pair<NEG>(a.x, m), pa1 = chroma_pair<NEG>(a.y, m);
+            const uint32_t pa2 = chroma_pair<NEG>(a.z, m), pa3 = chroma_pair<NEG>(a.w, m);
+            const uint32_t pb0 = chroma_pair<NEG>(b.x, m), pb1 = chroma_pair<NEG>(b.y, m);
+            const uint32_t pb2 = chroma_pair<NEG>(b.z, m), pb3 = chroma_pair<NEG>(b.w, m);
+            uint32_t c0, c1;
+            if (SITE == 0) {
+                c0 = avg2(avg2(pa0, pa1), avg2(pb0, pb1));
+                c1 = avg2(avg2(pa2, pa3), avg2(pb2, pb3));
+            } else {
+                // left neighbour of pixel 0: previous lane's pixel 3, the stripe halo, or (column 0) itself
+                uint32_t la = __shfl_up_sync(FULL, pa3, 1);
+                uint32_t lb = __shfl_up_sync(FULL, pb3, 1);
+                if (lane == 0) {
+                    la = halo ? chroma_pair<NEG>(hl[2 * k], m) : pa0;
+                    lb = halo ? chroma_pair<NEG>(hl[2 * k + 1], m) : pb0;
+                }
+                const uint32_t ra1 = edge1 ? pa0 : pa1, rb1 = edge1 ? pb0 : pb1;
+                const uint32_t ra3 = edge3 ? pa2 : pa3, rb3 = edge3 ? pb2 : pb3;
+                c0 = avg2(filt121(la, pa0, ra1), filt121(lb, pb0, rb1));
+                c1 = avg2(filt121(pa1, pa2, ra3), filt121(pb1, pb2, rb3));
+            }
+            if (FMT == 0) {
+                const uint32_t uuvv = prmt(c0, c1, 0x6240);                 // u0 u1 v0 v1
+                *reinterpret_cast<uint16_t *>(&st.c[k][lane * 2]) = (uint16_t)(uuvv & 0xffffu);
+                *reinterpret_cast<uint16_t *>(&st.c[k][64 + lane * 2]) = (uint16_t)(uuvv >> 16);
+            } else {
+                *reinterpret_cast<uint32_t *>(&st.c[k][lane * 4]) = prmt(c0, c1, 0x6420);   // u0 v0 u1 v1
+            }
+        }
+        __syncwarp();
+
+        // ---- planar stores: 16 bytes per lane, 128-byte row segments -----------------------------
+#pragma unroll
+        for (int i = 0; i < HR / 4; i++) {                // Y: HR rows x 8 segments
+            const int r = i * 4 + (lane >> 3);
+            if (r < rows && gx < p.w)
+                store16(p.out.p[0] + fo + (long long)(yh + r) * p.out.pitch[0] + gx, &st.y[r][seg * 16], p.w - gx);
+        }
+        {
+            const int r = lane >> 3;                       // chroma: HR/2 rows x 8 segments
+            if (r < PAIRS && 2 * r < rows) {
+                const long long cy = (yh >> 1) + r;
+                if (FMT == 0) {
+                    const int plane = 1 + (seg >> 2), cx = (x0 >> 1) + (seg & 3) * 16, cw = p.w >> 1;
+                    if (cx < cw)
+                        store16(p.out.p[plane] + fo + cy * p.out.pitch[plane] + cx, &st.c[r][seg * 16], cw - cx);
+                } else if (gx < p.w) {
+                    store16(p.out.p[1] + fo + cy * p.out.pitch[1] + gx, &st.c[r][seg * 16], p.w - gx);
+                }
+            }
+        }
+        __syncwarp();                                      // the stage is reused by the next step
+    }
+
+    // ---- K3: one ballot per stripe, 4 lanes = 1 macroblock ---------------------------------------
+    if (DMG) {
+        const uint32_t ballot = __ballot_sync(FULL, (diff & 0x00FFFFFFu) != 0);
+        const int mbx = (x0 >> 4) + lane;
+        if (lane < 8 && mbx < p.mb_w)
+            p.damage[(long long)frame * p.damage_frame_stride + (long long)(y0 >> 4) * p.mb_w + mbx] =
+                ((ballot >> (4 * lane)) & 0xFu) ? 1 : 0;
     }
 }
+
+// Measured on B200 (profiles/README.md): 8 lines per step (8 x 16 bytes in flight per thread,
+// 63-96 registers) runs at 0.99 of the copy roofline; 4 lines per step (48-56 registers) at 0.93-0.99.
+constexpr int K1_ROWS_PER_STEP = 8;
 
 template <int FMT, int SITE, bool NEG>
 cudaError_t launch3(const ConvertParams &p, dim3 grid, cudaStream_t st)
 {
     if (p.prev && p.damage)
-        k1_convert_kernel<FMT, SITE, NEG, true><<<grid, 256, 0, st>>>(p);
+        k1_convert_kernel<FMT, SITE, NEG, true, K1_ROWS_PER_STEP><<<grid, WARPS * 32, 0, st>>>(p);
     else
-        k1_convert_kernel<FMT, SITE, NEG, false><<<grid, 256, 0, st>>>(p);
+        k1_convert_kernel<FMT, SITE, NEG, false, K1_ROWS_PER_STEP><<<grid, WARPS * 32, 0, st>>>(p);
     return cudaGetLastError();
 }
 
@@ -211,7 +225,7 @@ cudaError_t launch_convert(const ConvertParams &p, int fmt, int site, cudaStream
 {
     if (p.w <= 0 || p.h <= 0 || p.n_frames <= 0)
         return cudaErrorInvalidValue;
-    dim3 grid((p.w + TW - 1) / TW, (p.h + TH - 1) / TH, p.n_frames);
+    dim3 grid((p.w + TW * WARPS - 1) / (TW * WARPS), (p.h + TH - 1) / TH, p.n_frames);
     if (fmt == 0)
         return site ? launch2<0, 1>(p, grid, st) : launch2<0, 0>(p, grid, st);
     return site ? launch2<1, 1>(p, grid, st) : launch2<1, 0>(p, grid, st);

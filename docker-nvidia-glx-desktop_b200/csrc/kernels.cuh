@@ -70,8 +70,9 @@ struct PlaneScaleParams {
     int box2x2;
 };
 
-constexpr int K1_TILE_W = 128;   // pixels per CTA tile (one LDG.128 per lane per row)
-constexpr int K1_TILE_H = 16;    // one macroblock row: 8 warps x 2 lines
+constexpr int K1_TILE_W = 128;   // pixels per warp stripe (one LDG.128 per lane per line)
+constexpr int K1_TILE_H = 16;    // one macroblock row per warp stripe
+constexpr int K1_WARPS_PER_CTA = 4;
 constexpr int K2_TILE_W = 64;    // output pixels per CTA tile
 constexpr int K2_TILE_H = 16;
 

@@ -25,7 +25,7 @@ MATRIX_BT601, MATRIX_BT709 = 0, 1
 RANGE_LIMITED, RANGE_FULL = 0, 1
 SITE_NONE, SITE_H_COSITED = 0, 1
 SCALE_GST_LQ, SCALE_BOX_2X2 = 0, 1
-FLAG_DAMAGE_MAP, FLAG_FORCE_TWO_PASS, FLAG_REGISTER_HOST = 1, 2, 4
+FLAG_DAMAGE_MAP, FLAG_FORCE_TWO_PASS, FLAG_REGISTER_HOST, FLAG_FORCE_GENERIC_FUSED = 1, 2, 4, 8
 
 # every symbol include/b200vc.h declares
 SYMBOLS = [
@@ -66,7 +66,7 @@ class Stats(C.Structure):
 class Info(C.Structure):
     _fields_ = [("path", C.c_int32), ("tile_w", C.c_int32), ("tile_h", C.c_int32), ("box_w", C.c_int32),
                 ("box_h", C.c_int32), ("smem_bytes", C.c_int32), ("sm_count", C.c_int32), ("cc_major", C.c_int32),
-                ("cc_minor", C.c_int32), ("device_name", C.c_char * 64)]
+                ("cc_minor", C.c_int32), ("fused_2to1", C.c_int32), ("device_name", C.c_char * 64)]
 
 
 class B200vcError(RuntimeError):

@@ -74,6 +74,8 @@ struct b200vc_ctx {
     ScaleTables tab = { nullptr, nullptr, nullptr, nullptr };
     int box_w = 0, box_h = 0;
     size_t smem_bytes = 0;
+    bool fused2x = false;                      // path 1 runs the exact-2:1 register kernel
+    uint32_t inc_y = 0, inc_c = 0;
     uint8_t *d_mid = nullptr;                  // two-pass: full-size intermediate I420
     size_t mid_off[3] = { 0, 0, 0 }, mid_pitch[3] = { 0, 0, 0 }, mid_size = 0;
     int mid_frames = 0;
@@ -211,6 +213,24 @@ void fused_box(const b200vc_config &c, const std::vector<Tap> &hy, const std::ve
     box_h = (int)ru(box_h, 2);
 }
 
+// True when every tap of an (in_n -> out_n) scaler starts at 2k with the second tap at 2k+1 and,
+// for vertical taps, weighs both lines equally (p1 == 32): the pattern k2_fused_2x_kernel assumes.
+bool taps_are_2to1(const std::vector<Tap> &t, int out_n, bool vertical)
+{
+    for (int k = 0; k < out_n; k++) {
+        if (tidx(t[k]) != 2 * k || tstep(t[k]) != 1) return false;
+        if (vertical && ((t[k] >> 16) & 0xff) != 32) return false;
+    }
+    return true;
+}
+
+uint32_t h_inc(int in_n, int out_n)
+{
+    if (out_n <= 1) return 0;
+    long long inc = (((long long)(in_n - 1)) << 16) / (out_n - 1) - 1;
+    return (uint32_t)(inc < 0 ? 0 : inc);
+}
+
 int check_config(const b200vc_config *c, std::string *why)
 {
     auto bad = [&](int code, const char *msg) { if (why) *why = msg; return code; };
@@ -325,6 +345,15 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         CUtensorMap map;
         int rc = make_tensor_map(c, d_src, src_pitch, src_fstride, n_frames, &map);
         if (rc) return rc;
+        if (c->fused2x) {
+            Fused2xParams q;
+            memset(&q, 0, sizeof q);
+            q.out = out;  q.in_w = g.in_w;  q.in_h = g.in_h;  q.inc_y = c->inc_y;  q.inc_c = c->inc_c;
+            q.n_frames = n_frames;  q.mx = c->mx;
+            CU_TRY(c, launch_fused_2x(map, q, g.out_format, site, g.scale_mode == B200VC_SCALE_BOX_2X2, st));
+            c->stats.kernel_launches += 1;
+            return B200VC_OK;
+        }
         FusedScaleParams p;
         memset(&p, 0, sizeof p);
         p.out = out;  p.tab = c->tab;
@@ -464,6 +493,18 @@ int create_impl(b200vc_ctx *c)
         const bool fits = c->box_w <= 256 && c->box_h <= 256 &&
                           c->smem_bytes + 1024 <= (size_t)c->prop.sharedMemPerBlockOptin;
         c->path = (fits && !(g.flags & B200VC_FLAG_FORCE_TWO_PASS)) ? 1 : 2;
+        const bool exact2 = g.in_w == 2 * g.out_w && g.in_h == 2 * g.out_h && (g.in_w % 4) == 0 && (g.in_h % 4) == 0;
+        c->fused2x = c->path == 1 && exact2 && !(g.flags & B200VC_FLAG_FORCE_GENERIC_FUSED) &&
+                     (g.scale_mode == B200VC_SCALE_BOX_2X2 ||
+                      (taps_are_2to1(hy, g.out_w, false) && taps_are_2to1(vy, g.out_h, true) &&
+                       taps_are_2to1(hc, g.out_w / 2, false) && taps_are_2to1(vc, g.out_h / 2, true)));
+        if (c->fused2x) {
+            c->box_w = K2X_SRC_W + K2X_HALO;
+            c->box_h = K2X_SRC_H;
+            c->smem_bytes = (size_t)c->box_w * c->box_h * 4;
+            c->inc_y = h_inc(g.in_w, g.out_w);
+            c->inc_c = h_inc(g.in_w / 2, g.out_w / 2);
+        }
         if (c->path == 1) {
             void *fn = nullptr;
             cudaDriverEntryPointQueryResult qres;
@@ -471,7 +512,7 @@ int create_impl(b200vc_ctx *c)
             if (!fn || qres != cudaDriverEntryPointSuccess)
                 return fail(c, B200VC_ERR_CUDA, "the driver does not export cuTensorMapEncodeTiled");
             c->encode_tiled = (PFN_cuTensorMapEncodeTiled_v12000)fn;
-            CU_TRY(c, fused_scale_prepare(c->smem_bytes));
+            if (!c->fused2x) CU_TRY(c, fused_scale_prepare(c->smem_bytes));
         } else {
             const size_t yp = ru(g.in_w, 256), cp = ru(g.in_w / 2, 256);
             c->mid_pitch[0] = yp;  c->mid_pitch[1] = cp;  c->mid_pitch[2] = cp;
@@ -763,6 +804,7 @@ int b200vc_get_info(const b200vc_ctx *c, b200vc_info *info)
     info->path = c->path;
     info->tile_w = c->path == 1 ? K2_TILE_W : K1_TILE_W;
     info->tile_h = c->path == 1 ? K2_TILE_H : K1_TILE_H;
+    info->fused_2to1 = c->fused2x ? 1 : 0;
     info->box_w = c->box_w;  info->box_h = c->box_h;
     info->smem_bytes = c->path == 1 ? (int)c->smem_bytes : 3 * 1024 + 32;
     info->sm_count = c->prop.multiProcessorCount;

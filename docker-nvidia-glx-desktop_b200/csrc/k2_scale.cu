@@ -204,6 +204,131 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
     }
 }
 
+
+// ---- K2, exact 2:1 ------------------------------------------------------------------------------
+// When every horizontal tap starts at source index 2x and every vertical tap is the rounded mean of
+// lines 2y, 2y+1 (an exact 2:1 downscale up to ~3970 output columns; 4K -> 1080p is the case that
+// matters), one thread's 4x4 source block plus one halo column holds everything two output line
+// pairs need: 2x2 luma outputs and one (u,v) output. The tile still arrives by TMA (132 x 32 box,
+// halo columns included, zero fill outside the frame), but the intermediate frame never exists
+// even in shared memory: conversion, both chroma roundings, the fractional horizontal tap and the
+// vertical mean all run in registers on 2x16-bit lanes.
+template <int FMT, int SITE, bool NEG, bool BOX>
+__global__ void __launch_bounds__(256)
+k2_fused_2x_kernel(const __grid_constant__ CUtensorMap src_map, const Fused2xParams p)
+{
+    constexpr int BW = K2X_SRC_W + K2X_HALO;               // 132
+    __shared__ __align__(128) uint32_t s_src[K2X_SRC_H][BW];
+    __shared__ __align__(8) uint64_t s_bar;
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int frame = blockIdx.z;
+    const int tx = blockIdx.x * K2X_SRC_W, ty = blockIdx.y * K2X_SRC_H;   // source tile origin
+
+    if (threadIdx.x == 0) {
+        const uint32_t bar = smem_u32(&s_bar);
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)sizeof(s_src)) : "memory");
+        asm volatile(
+            "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+            " [%0], [%1, {%2, %3, %4}], [%5];"
+            ::"r"(smem_u32(&s_src[0][0])), "l"(reinterpret_cast<uint64_t>(&src_map)), "r"(tx - K2X_HALO), "r"(ty), "r"(frame),
+              "r"(bar) : "memory");
+    }
+    __syncthreads();
+    {
+        const uint32_t bar = smem_u32(&s_bar);
+        uint32_t done = 0;
+        while (!done) {
+            asm volatile(
+                "{\n\t.reg .pred q;\n\t"
+                "mbarrier.try_wait.parity.shared::cta.b64 q, [%1], %2;\n\t"
+                "selp.u32 %0, 1, 0, q;\n\t}"
+                : "=r"(done) : "r"(bar), "r"(0u) : "memory");
+        }
+    }
+
+    const Matrix &m = p.mx;
+    const int c = tx + lane * 4;                           // absolute source column of this thread's pixel 0
+    const int r = ty + warp * 4;                           // absolute source line of this thread's line 0
+    uint4 a[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+        a[i] = *reinterpret_cast<const uint4 *>(&s_src[warp * 4 + i][K2X_HALO + lane * 4]);
+
+    // ---- chroma: 4:4:4 pairs, horizontal filter per line, vertical means, 2:1 scale --------------
+    uint32_t h0[4], h1[4];                                 // filtered chroma at columns c and c+2, per line
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const uint32_t q0 = chroma_pair<NEG>(a[i].x, m), q1 = chroma_pair<NEG>(a[i].y, m);
+        const uint32_t q2 = chroma_pair<NEG>(a[i].z, m), q3 = chroma_pair<NEG>(a[i].w, m);
+        if (SITE == 0) {
+            h0[i] = avg2(q0, q1);
+            h1[i] = avg2(q2, q3);
+        } else {
+            uint32_t l = __shfl_up_sync(0xffffffffu, q3, 1);
+            if (lane == 0)                                 // tile halo column, or (frame column 0) itself
+                l = c > 0 ? chroma_pair<NEG>(s_src[warp * 4 + i][K2X_HALO - 1], m) : q0;
+            const uint32_t rr = (c + 4 == p.in_w) ? q2 : q3;   // last even column takes itself (FILT_1_3)
+            h0[i] = filt121(l, q0, q1);
+            h1[i] = filt121(q1, q2, rr);
+        }
+    }
+    // intermediate chroma plane samples: lines (r/2, r/2+1) x columns (c/2, c/2+1)
+    const uint32_t v00 = avg2(h0[0], h0[1]), v01 = avg2(h1[0], h1[1]);
+    const uint32_t v10 = avg2(h0[2], h0[3]), v11 = avg2(h1[2], h1[3]);
+    uint32_t cuv;
+    if (BOX) {
+        cuv = ((v00 + v01 + v10 + v11 + 0x00020002u) >> 2) & LANES8;
+    } else {
+        const uint32_t f = (((uint32_t)(c >> 2) * p.inc_c) >> 8) & 0xffu;
+        const uint32_t ha = ((v00 * (256u - f) + v01 * f) >> 8) & LANES8;
+        const uint32_t hb = ((v10 * (256u - f) + v11 * f) >> 8) & LANES8;
+        cuv = avg2(ha, hb);
+    }
+
+    // ---- luma: lines (2i, 2i+1) ride in the two 16-bit lanes --------------------------------------
+    uint32_t yout[2];
+#pragma unroll
+    for (int ii = 0; ii < 2; ii++) {
+        const uint4 t = a[2 * ii], b = a[2 * ii + 1];
+        const uint32_t w0 = prmt(luma_sum(t.x, m), luma_sum(b.x, m), 0x6521);
+        const uint32_t w1 = prmt(luma_sum(t.y, m), luma_sum(b.y, m), 0x6521);
+        const uint32_t w2 = prmt(luma_sum(t.z, m), luma_sum(b.z, m), 0x6521);
+        const uint32_t w3 = prmt(luma_sum(t.w, m), luma_sum(b.w, m), 0x6521);
+        uint32_t d0, d1;
+        if (BOX) {
+            const uint32_t s0 = w0 + w1, s1 = w2 + w3;
+            d0 = ((s0 & 0xffffu) + (s0 >> 16) + 2u) >> 2;
+            d1 = ((s1 & 0xffffu) + (s1 >> 16) + 2u) >> 2;
+        } else {
+            const uint32_t ox = (uint32_t)(c >> 1);
+            const uint32_t f0 = ((ox * p.inc_y) >> 8) & 0xffu, f1 = (((ox + 1u) * p.inc_y) >> 8) & 0xffu;
+            const uint32_t s0 = ((w0 * (256u - f0) + w1 * f0) >> 8) & LANES8;
+            const uint32_t s1 = ((w2 * (256u - f1) + w3 * f1) >> 8) & LANES8;
+            d0 = ((s0 & 0xffffu) + (s0 >> 16) + 1u) >> 1;
+            d1 = ((s1 & 0xffffu) + (s1 >> 16) + 1u) >> 1;
+        }
+        yout[ii] = d0 | (d1 << 8);
+    }
+
+    // ---- stores ---------------------------------------------------------------------------------------
+    if (c < p.in_w && r < p.in_h) {
+        const long long fo = (long long)frame * p.out.frame_stride;
+        const int ox = c >> 1, oy = r >> 1, cx = c >> 2, cy = r >> 2;
+        *reinterpret_cast<uint16_t *>(p.out.p[0] + fo + (long long)oy * p.out.pitch[0] + ox) = (uint16_t)yout[0];
+        *reinterpret_cast<uint16_t *>(p.out.p[0] + fo + (long long)(oy + 1) * p.out.pitch[0] + ox) = (uint16_t)yout[1];
+        if (FMT == 0) {
+            p.out.p[1][fo + (long long)cy * p.out.pitch[1] + cx] = (uint8_t)(cuv & 0xffu);
+            p.out.p[2][fo + (long long)cy * p.out.pitch[2] + cx] = (uint8_t)(cuv >> 16);
+        } else {
+            *reinterpret_cast<uint16_t *>(p.out.p[1] + fo + (long long)cy * p.out.pitch[1] + 2 * cx) =
+                (uint16_t)((cuv & 0xffu) | ((cuv >> 16) << 8));
+        }
+    }
+}
+
 // ---- two-pass, pass 2: scale the planes of a full-size intermediate I420 -----------------------
 template <int FMT>
 __global__ void __launch_bounds__(256) k2_plane_scale_kernel(const PlaneScaleParams p)
@@ -276,6 +401,37 @@ cudaError_t set_smem(K kernel, size_t bytes)
     return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
 }
 
+
+template <int FMT, int SITE, bool NEG>
+cudaError_t launch_2x3(const CUtensorMap &map, const Fused2xParams &p, int box, dim3 grid, cudaStream_t st)
+{
+    if (box)
+        k2_fused_2x_kernel<FMT, SITE, NEG, true><<<grid, 256, 0, st>>>(map, p);
+    else
+        k2_fused_2x_kernel<FMT, SITE, NEG, false><<<grid, 256, 0, st>>>(map, p);
+    return cudaGetLastError();
+}
+
+template <int FMT, int SITE>
+cudaError_t launch_2x2(const CUtensorMap &map, const Fused2xParams &p, int box, dim3 grid, cudaStream_t st)
+{
+    return p.mx.neg ? launch_2x3<FMT, SITE, true>(map, p, box, grid, st) : launch_2x3<FMT, SITE, false>(map, p, box, grid, st);
+}
+
+}  // namespace
+
+cudaError_t launch_fused_2x(const CUtensorMap &src_map, const Fused2xParams &p, int fmt, int site, int box2x2,
+                            cudaStream_t st)
+{
+    if (p.in_w <= 0 || p.in_h <= 0 || p.n_frames <= 0 || (p.in_w & 3) || (p.in_h & 3))
+        return cudaErrorInvalidValue;
+    dim3 grid((p.in_w + K2X_SRC_W - 1) / K2X_SRC_W, (p.in_h + K2X_SRC_H - 1) / K2X_SRC_H, p.n_frames);
+    if (fmt == 0)
+        return site ? launch_2x2<0, 1>(src_map, p, box2x2, grid, st) : launch_2x2<0, 0>(src_map, p, box2x2, grid, st);
+    return site ? launch_2x2<1, 1>(src_map, p, box2x2, grid, st) : launch_2x2<1, 0>(src_map, p, box2x2, grid, st);
+}
+
+namespace {
 }  // namespace
 
 size_t fused_scale_smem_bytes(int box_w, int box_h)

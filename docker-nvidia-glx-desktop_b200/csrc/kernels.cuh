@@ -60,6 +60,15 @@ struct FusedScaleParams {
     Matrix mx;
 };
 
+// K2 exact 2:1: TMA-staged 128x32 source tile (+4 halo columns), everything else in registers.
+struct Fused2xParams {
+    PlaneSet out;
+    int in_w, in_h;         // in = 2 * out exactly; in_w % 4 == 0, in_h % 4 == 0
+    uint32_t inc_y, inc_c;  // 16.16 horizontal steps of the luma / chroma plane scalers
+    int n_frames;
+    Matrix mx;
+};
+
 // Two-pass scale, pass 2: plane scaler reading the full-size intermediate I420.
 struct PlaneScaleParams {
     const uint8_t *src[3]; long long src_pitch[3]; long long src_frame_stride;
@@ -75,11 +84,16 @@ constexpr int K1_TILE_H = 16;    // one macroblock row per warp stripe
 constexpr int K1_WARPS_PER_CTA = 4;
 constexpr int K2_TILE_W = 64;    // output pixels per CTA tile
 constexpr int K2_TILE_H = 16;
+constexpr int K2X_SRC_W = 128;   // exact-2:1 kernel: source tile per CTA (8 warps x 4 lines, 32 lanes x 4 pixels)
+constexpr int K2X_SRC_H = 32;
+constexpr int K2X_HALO = 4;      // columns loaded left of the tile (TMA boxes start 16-byte aligned)
 
 // Launchers return the cudaError_t of the launch. fmt/site as in b200vc.h.
 cudaError_t launch_convert(const ConvertParams &p, int fmt, int site, cudaStream_t st);
 cudaError_t launch_fused_scale(const CUtensorMap &src_map, const FusedScaleParams &p, int fmt, int site,
                                cudaStream_t st);
+cudaError_t launch_fused_2x(const CUtensorMap &src_map, const Fused2xParams &p, int fmt, int site, int box2x2,
+                            cudaStream_t st);
 cudaError_t launch_plane_scale(const PlaneScaleParams &p, int fmt, cudaStream_t st);
 size_t fused_scale_smem_bytes(int box_w, int box_h);
 cudaError_t fused_scale_prepare(size_t smem_bytes);   // opt in to > 48 KB dynamic shared memory

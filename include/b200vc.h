@@ -58,6 +58,8 @@ enum { B200VC_SCALE_GST_LQ = 0 /* videoscale bilinear, SURVEY B.2 */, B200VC_SCA
 #define B200VC_FLAG_FORCE_TWO_PASS  0x2u  /* scaling: convert to a full-size intermediate, then
                                              scale the planes (the general path), never the fused
                                              kernel                                               */
+#define B200VC_FLAG_FORCE_GENERIC_FUSED 0x8u /* scaling: never the exact-2:1 kernel, always the
+                                             general fused kernel (any ratio that fits a tile)    */
 #define B200VC_FLAG_REGISTER_HOST   0x4u  /* page-lock caller buffers on first sight (XShm pool)
                                              instead of staging them through a pinned ring        */
 
@@ -118,6 +120,7 @@ typedef struct b200vc_info {
     int32_t smem_bytes;         /* dynamic + static shared memory of the main kernel                */
     int32_t sm_count;
     int32_t cc_major, cc_minor;
+    int32_t fused_2to1;         /* path 1 only: the exact-2:1 register kernel is in use              */
     char device_name[64];
 } b200vc_info;
 

@@ -34,7 +34,7 @@ def test_struct_sizes_match_the_header():
     assert C.sizeof(b200vc.Frame) == 8 + 8 + 24 + 24 + 8 + 4 + 4
     assert C.sizeof(b200vc.DeviceFrames) == 3 * 8 + 3 * 8 + 24 + 24 + 8 + 8 + 8 + 4 + 4
     assert C.sizeof(b200vc.Stats) == 6 * 8
-    assert C.sizeof(b200vc.Info) == 9 * 4 + 64
+    assert C.sizeof(b200vc.Info) == 10 * 4 + 64
 
 
 def test_version_and_status_strings(lib):

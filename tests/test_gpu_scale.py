@@ -21,29 +21,33 @@ def _want(orc, frame, ow, oh, fmt, m, rg, site, mode=0):
     return plane_views(buf, off, pit, fmt, ow, oh)
 
 
-GEOS = [(3840, 2160, 1920, 1080), (64, 36, 32, 18), (128, 64, 64, 32), (260, 132, 130, 66), (96, 48, 64, 32),
+GEOS = [(3840, 2160, 1920, 1080), (64, 36, 32, 18), (128, 64, 64, 32), (260, 132, 130, 66), (4, 4, 2, 2), (96, 48, 64, 32),
         (100, 60, 46, 26), (1920, 1080, 1280, 720), (1280, 720, 854, 480), (200, 120, 150, 90), (640, 360, 212, 120)]
 
 
 @pytest.mark.parametrize("geo", GEOS)
-@pytest.mark.parametrize("two_pass", [False, True])
-def test_scale_parity(conv, orc, geo, two_pass):
+@pytest.mark.parametrize("variant", ["fused", "fused_generic", "two_pass"])
+def test_scale_parity(conv, orc, geo, variant):
+    """Three implementations of the same two-stage semantics: the exact-2:1 register kernel (where
+    the taps allow it), the general fused kernel, and convert-then-scale through an intermediate."""
     iw, ih, ow, oh = geo
+    two_pass = variant == "two_pass"
     frame = orc.synth("rand", iw, ih, 9)
-    flags = b200vc.FLAG_FORCE_TWO_PASS if two_pass else 0
+    flags = {"fused": 0, "fused_generic": b200vc.FLAG_FORCE_GENERIC_FUSED, "two_pass": b200vc.FLAG_FORCE_TWO_PASS}[variant]
     for fmt, m, rg, site in [(0, 1, 0, 1), (1, 0, 1, 0), (0, 0, 0, 0), (1, 1, 1, 1)]:
         conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=m, range_=rg, chroma_site=site, flags=flags)
-        assert conv.info().path == (2 if two_pass else 1)
+        inf = conv.info()
+        assert inf.path == (2 if two_pass else 1)
+        assert inf.fused_2to1 == (1 if variant == "fused" and iw == 2 * ow and ih == 2 * oh and iw % 4 == 0 and ih % 4 == 0 else 0)
         buf, off, pit = conv.transform_frame(frame)
         assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), _want(orc, frame, ow, oh, fmt, m, rg, site),
                             f"{geo} fmt{fmt} m{m} r{rg} s{site} two_pass={two_pass}")
 
 
-@pytest.mark.parametrize("two_pass", [False, True])
-def test_box_mode(conv, orc, two_pass):
+@pytest.mark.parametrize("flags", [0, b200vc.FLAG_FORCE_GENERIC_FUSED, b200vc.FLAG_FORCE_TWO_PASS])
+def test_box_mode(conv, orc, flags):
     iw, ih, ow, oh = 516, 260, 258, 130
     frame = orc.synth("rand", iw, ih, 2)
-    flags = b200vc.FLAG_FORCE_TWO_PASS if two_pass else 0
     for fmt in (0, 1):
         conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=1, range_=0, chroma_site=1, scale_mode=1, flags=flags)
         buf, off, pit = conv.transform_frame(frame)
@@ -55,7 +59,7 @@ def test_structured_frames_4k(conv, orc):
     frame = orc.synth("desk", 3840, 2160, 3)
     conv.set_info(3840, 2160, 1920, 1080, matrix=1, range_=0, chroma_site=1)
     inf = conv.info()
-    assert inf.path == 1 and inf.box_w >= 130 and inf.box_h >= 32
+    assert inf.path == 1 and inf.fused_2to1 == 1 and inf.box_w >= 130 and inf.box_h >= 32
     buf, off, pit = conv.transform_frame(frame)
     want = _want(orc, frame, 1920, 1080, 0, 1, 0, 1)
     assert_planes_equal(plane_views(buf, off, pit, 0, 1920, 1080), want)

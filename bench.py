@@ -312,6 +312,27 @@ def run_gpu(args, rank: int, local_rank: int, world: int):
         conv.lib.b200vc_convert(conv.ctx, h_in.ptr + (i % RING) * IN_BYTES, W * 4, planes, pits, None)
     sync_fps = n_sync / (time.perf_counter() - t0)
 
+    # PCIe ceiling for the e2e number: raw pinned copies of the same frames, both directions at once,
+    # no kernel (what the link gives for this traffic pattern on this box)
+    s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
+    h_out_t = torch.from_numpy(h_out.array)
+    d_in_flat, d_out_flat = d_in.reshape(-1), d_out.reshape(-1)
+
+    def raw_copies(n):
+        for k in range(n):
+            i = k % RING
+            with torch.cuda.stream(s_up):
+                d_in_flat[i * IN_BYTES:(i + 1) * IN_BYTES].copy_(h_in_t[i * IN_BYTES:(i + 1) * IN_BYTES], non_blocking=True)
+            with torch.cuda.stream(s_dn):
+                h_out_t[i * OUT_BYTES:(i + 1) * OUT_BYTES].copy_(d_out_flat[i * OUT_BYTES:(i + 1) * OUT_BYTES], non_blocking=True)
+
+    raw_copies(32)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    raw_copies(256)
+    torch.cuda.synchronize()
+    pcie_fps = 256 / (time.perf_counter() - t0)
+
     clocks = sampler.finish() if rank == 0 else None
 
 
@@ -334,6 +355,9 @@ def run_gpu(args, rank: int, local_rank: int, world: int):
                     "d2h_bytes_per_step": int((st1.d2h_bytes - st0.d2h_bytes) // args.steps),
                     "api": "b200vc_convert_batch, 8 sessions per call, pinned host buffers",
                     "pcie_h2d_gbs": round(e2e_fps / world * IN_BYTES / 1e9, 2),
+                    "pcie_ceiling_fps_per_gpu": round(pcie_fps, 1),
+                    "frac_of_pcie_ceiling": round(e2e_fps / world / pcie_fps, 4),
+                    "pcie_ceiling_how": "raw pinned H2D 8.3 MB + D2H 3.1 MB copies in flight together, no kernel, rank 0",
                     "sync_single_session_fps": round(sync_fps, 1)},
             "gpu_launches": gpu_launches,
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",

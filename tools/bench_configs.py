@@ -22,6 +22,12 @@ CONFIGS = [
     ("C3 4K->1080p I420 709L fused", 3840, 2160, 1920, 1080, 0, 1, 0, 1, 0, False),
     ("C3 4K->1080p I420 709L two-pass", 3840, 2160, 1920, 1080, 0, 1, 0, 1, b200vc.FLAG_FORCE_TWO_PASS, False),
     ("C4 1080p I420 601L mpeg2 +damage", 1920, 1080, 1920, 1080, 0, 0, 0, 1, b200vc.FLAG_DAMAGE_MAP, True),
+    # ratios other than 2:1 run the general fused kernel
+    ("G 4K->1080p generic fused", 3840, 2160, 1920, 1080, 0, 1, 0, 1, b200vc.FLAG_FORCE_GENERIC_FUSED, False),
+    ("G 4K->1440p 3:2", 3840, 2160, 2560, 1440, 0, 1, 0, 1, 0, False),
+    ("G 1440p->1080p 4:3", 2560, 1440, 1920, 1080, 0, 1, 0, 1, 0, False),
+    ("G 1080p->720p 3:2", 1920, 1080, 1280, 720, 0, 1, 0, 1, 0, False),
+    ("G 4K->720p 3:1", 3840, 2160, 1280, 720, 0, 1, 0, 1, 0, False),
 ]
 
 

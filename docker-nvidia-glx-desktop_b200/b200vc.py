@@ -25,6 +25,7 @@ MATRIX_BT601, MATRIX_BT709 = 0, 1
 RANGE_LIMITED, RANGE_FULL = 0, 1
 SITE_NONE, SITE_H_COSITED = 0, 1
 SCALE_GST_LQ, SCALE_BOX_2X2 = 0, 1
+IN_BGRX, IN_RGBX, IN_XRGB, IN_XBGR = 0, 1, 2, 3
 FLAG_DAMAGE_MAP, FLAG_FORCE_TWO_PASS, FLAG_REGISTER_HOST, FLAG_FORCE_GENERIC_FUSED = 1, 2, 4, 8
 
 # every symbol include/b200vc.h declares
@@ -42,7 +43,7 @@ class Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("in_w", C.c_int32), ("in_h", C.c_int32), ("out_w", C.c_int32),
                 ("out_h", C.c_int32), ("out_format", C.c_int32), ("matrix", C.c_int32), ("range", C.c_int32),
                 ("chroma_site", C.c_int32), ("scale_mode", C.c_int32), ("flags", C.c_uint32),
-                ("max_sessions", C.c_int32), ("n_inflight", C.c_int32), ("n_bands", C.c_int32)]
+                ("max_sessions", C.c_int32), ("n_inflight", C.c_int32), ("n_bands", C.c_int32), ("in_format", C.c_int32)]
 
 
 class Frame(C.Structure):
@@ -162,7 +163,7 @@ class Converter:
     def set_info(self, in_w: int, in_h: int, out_w: int | None = None, out_h: int | None = None,
                  out_format: int = FMT_I420, matrix: int | None = None, range_: int | None = None,
                  chroma_site: int | None = None, scale_mode: int = SCALE_GST_LQ, flags: int = 0,
-                 max_sessions: int = 1, n_inflight: int = 0, n_bands: int = 0) -> None:
+                 max_sessions: int = 1, n_inflight: int = 0, n_bands: int = 0, in_format: int = IN_BGRX) -> None:
         out_w, out_h = out_w or in_w, out_h or in_h
         if matrix is None or range_ is None or chroma_site is None:
             dm, dr, ds = default_colorimetry(out_h)   # caps left colorimetry open: defaults by height
@@ -171,7 +172,7 @@ class Converter:
             chroma_site = ds if chroma_site is None else chroma_site
         self.stop()
         cfg = Config(self.device, in_w, in_h, out_w, out_h, out_format, matrix, range_, chroma_site, scale_mode,
-                     flags, max_sessions, n_inflight, n_bands)
+                     flags, max_sessions, n_inflight, n_bands, in_format)
         ctx = C.c_void_p()
         rc = self.lib.b200vc_create(C.byref(cfg), C.byref(ctx))
         if rc:

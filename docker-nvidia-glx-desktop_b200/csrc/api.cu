@@ -119,15 +119,22 @@ const int kMatrix[2][2][3][4] = {
       { { 54, 183, 18, 0 }, { -29, -99, 128, 32768 }, { 128, -116, -12, 32768 } } },      // 709 full
 };
 
-uint32_t pack_coef(int cb, int cg, int cr)
+// byte position of B, G, R in one pixel, per B200VC_IN_* (unpack_BGRA / _RGBA / _ARGB / _ABGR)
+const int kBytePos[4][3] = { { 0, 1, 2 }, { 2, 1, 0 }, { 3, 2, 1 }, { 1, 2, 3 } };
+
+uint32_t pack_coef_at(const int pos[3], int cb, int cg, int cr)
 {
-    return (uint32_t)(cb & 0xff) | ((uint32_t)(cg & 0xff) << 8) | ((uint32_t)(cr & 0xff) << 16);
+    return ((uint32_t)(cb & 0xff) << (8 * pos[0])) | ((uint32_t)(cg & 0xff) << (8 * pos[1])) |
+           ((uint32_t)(cr & 0xff) << (8 * pos[2]));
 }
 
-Matrix make_matrix(int matrix, int range)
+Matrix make_matrix(int matrix, int range, int in_format)
 {
     const int (*m)[4] = kMatrix[matrix][range];
+    const int *pos = kBytePos[in_format];
+    auto pack_coef = [pos](int cb, int cg, int cr) { return pack_coef_at(pos, cb, cg, cr); };
     Matrix r;
+    r.rgb_mask = pack_coef_at(pos, 0xff, 0xff, 0xff);
     r.cy = pack_coef(m[0][2], m[0][1], m[0][0]);
     r.oy = (uint32_t)m[0][3];
     bool neg = false;
@@ -243,6 +250,8 @@ int check_config(const b200vc_config *c, std::string *why)
         return bad(B200VC_ERR_UNSUPPORTED, "odd widths/heights are not negotiated (4:2:0 needs even sizes)");
     if (c->out_format != B200VC_FMT_I420 && c->out_format != B200VC_FMT_NV12)
         return bad(B200VC_ERR_UNSUPPORTED, "output format must be I420 or NV12");
+    if (c->in_format < B200VC_IN_BGRX || c->in_format > B200VC_IN_XBGR)
+        return bad(B200VC_ERR_UNSUPPORTED, "input format must be BGRx/BGRA, RGBx/RGBA, xRGB/ARGB or xBGR/ABGR");
     if (c->matrix != B200VC_MATRIX_BT601 && c->matrix != B200VC_MATRIX_BT709)
         return bad(B200VC_ERR_UNSUPPORTED, "colorimetry matrix must be bt601 or bt709");
     if (c->range != B200VC_RANGE_LIMITED && c->range != B200VC_RANGE_FULL)
@@ -431,7 +440,7 @@ int create_impl(b200vc_ctx *c)
         return fail(c, B200VC_ERR_NO_DEVICE, "device %d (%s, sm_%d%d) is not sm_100: this library carries sm_100a code only",
                     g.device, c->prop.name, c->prop.major, c->prop.minor);
 
-    c->mx = make_matrix(g.matrix, g.range);
+    c->mx = make_matrix(g.matrix, g.range, g.in_format);
     c->scaling = g.in_w != g.out_w || g.in_h != g.out_h;
     c->mb_w = (g.in_w + 15) / 16;
     c->mb_h = (g.in_h + 15) / 16;

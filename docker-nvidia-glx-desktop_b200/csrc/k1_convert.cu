@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
 
     // ---- K3: one ballot per stripe, 4 lanes = 1 macroblock ---------------------------------------
     if (DMG) {
-        const uint32_t ballot = __ballot_sync(FULL, (diff & 0x00FFFFFFu) != 0);
+        const uint32_t ballot = __ballot_sync(FULL, (diff & p.mx.rgb_mask) != 0);
         const int mbx = (x0 >> 4) + lane;
         if (lane < 8 && mbx < p.mb_w)
             p.damage[(long long)frame * p.damage_frame_stride + (long long)(y0 >> 4) * p.mb_w + mbx] =

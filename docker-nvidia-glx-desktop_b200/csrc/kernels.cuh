@@ -11,7 +11,8 @@
 namespace b200vc {
 
 // Matrix in the form the kernels consume. Coefficients are packed as four bytes in
-// pixel byte order B,G,R,x for dp4a; x's coefficient is 0 so the pad byte never matters.
+// the pixel's byte order (B,G,R,x for BGRx; any of the four sink formats) for dp4a; x's coefficient
+// is 0 so the pad byte never matters.
 //   Y = dp4a.u32.u32(pix, cy, oy) >> 8
 //   U = dp4a.u32.s32(pix, cu, ou) >> 8            (neg == 0)
 // Full-range rows hold a +128 coefficient, which does not fit a signed byte. Those matrices are
@@ -21,6 +22,7 @@ struct Matrix {
     uint32_t cy, cu, cv;
     uint32_t oy, ou, ov;
     int32_t neg;
+    uint32_t rgb_mask;      // the three bytes of a pixel word that are B, G, R (damage ignores the 4th)
 };
 
 struct PlaneSet {

@@ -144,8 +144,10 @@ long long h_inc(int in_n, int out_n)
 }
 
 // Same numbers as the table in api.cu; kept here so that this file stands alone.
-Matrix static_matrix(int matrix, int range)
+Matrix static_matrix(int matrix, int range, int in_format)
 {
+    static const int pos_tab[4][3] = { { 0, 1, 2 }, { 2, 1, 0 }, { 3, 2, 1 }, { 1, 2, 3 } };   // byte of B, G, R
+    const int *pos = pos_tab[in_format];
     static const int t[2][2][3][4] = {
         { { { 66, 129, 25, 4096 }, { -38, -74, 112, 32768 }, { 112, -94, -18, 32768 } },
           { { 77, 150, 29, 0 }, { -43, -85, 128, 32768 }, { 128, -107, -21, 32768 } } },
@@ -153,10 +155,12 @@ Matrix static_matrix(int matrix, int range)
           { { 54, 183, 18, 0 }, { -29, -99, 128, 32768 }, { 128, -116, -12, 32768 } } },
     };
     const int (*m)[4] = t[matrix][range];
-    auto pack = [](int cb, int cg, int cr) {
-        return (uint32_t)(cb & 0xff) | ((uint32_t)(cg & 0xff) << 8) | ((uint32_t)(cr & 0xff) << 16);
+    auto pack = [pos](int cb, int cg, int cr) {
+        return ((uint32_t)(cb & 0xff) << (8 * pos[0])) | ((uint32_t)(cg & 0xff) << (8 * pos[1])) |
+               ((uint32_t)(cr & 0xff) << (8 * pos[2]));
     };
     Matrix r;
+    r.rgb_mask = pack(0xff, 0xff, 0xff);
     r.cy = pack(m[0][2], m[0][1], m[0][0]);
     r.oy = (uint32_t)m[0][3];
     r.neg = range == B200VC_RANGE_FULL ? 1 : 0;      // the full-range rows hold the +128 coefficient
@@ -236,7 +240,7 @@ extern "C" int b200vc_convert_scale_device_static(const b200vc_config *cfg, cons
 
     cudaStream_t st = (cudaStream_t)cuda_stream;
     const int site = cfg->chroma_site == B200VC_SITE_H_COSITED ? 1 : 0;
-    const Matrix mx = static_matrix(cfg->matrix, cfg->range);
+    const Matrix mx = static_matrix(cfg->matrix, cfg->range, cfg->in_format);
     for (int f = 0; f < d->n_frames; f++) {
         // pass 1: K1 at the source size into the static intermediate (always planar)
         ConvertParams p1 = {};

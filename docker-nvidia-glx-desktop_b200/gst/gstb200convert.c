@@ -38,7 +38,7 @@ GST_DEBUG_CATEGORY_STATIC(b200convert_debug);
 enum { PROP_0, PROP_DEVICE_ID, PROP_DAMAGE_MAP, PROP_N_BANDS };
 
 static GstStaticPadTemplate sink_tmpl = GST_STATIC_PAD_TEMPLATE("sink", GST_PAD_SINK, GST_PAD_ALWAYS,
-    GST_STATIC_CAPS("video/x-raw, format=(string)BGRx, width=(int)[2,16384], height=(int)[2,16384], "
+    GST_STATIC_CAPS("video/x-raw, format=(string){BGRx,BGRA,RGBx,RGBA,xRGB,ARGB,xBGR,ABGR}, width=(int)[2,16384], height=(int)[2,16384], "
                     "framerate=(fraction)[0/1,2147483647/1]"));
 static GstStaticPadTemplate src_tmpl = GST_STATIC_PAD_TEMPLATE("src", GST_PAD_SRC, GST_PAD_ALWAYS,
     GST_STATIC_CAPS("video/x-raw, format=(string){I420,NV12}, width=(int)[2,16384], height=(int)[2,16384], "
@@ -83,6 +83,16 @@ gst_b200_convert_fixate_caps(GstBaseTransform *trans, GstPadDirection direction,
     return gst_caps_fixate(othercaps);
 }
 
+static int in_format_of(const GstVideoInfo *i)
+{
+    switch (GST_VIDEO_INFO_FORMAT(i)) {
+    case GST_VIDEO_FORMAT_RGBx: case GST_VIDEO_FORMAT_RGBA: return B200VC_IN_RGBX;
+    case GST_VIDEO_FORMAT_xRGB: case GST_VIDEO_FORMAT_ARGB: return B200VC_IN_XRGB;
+    case GST_VIDEO_FORMAT_xBGR: case GST_VIDEO_FORMAT_ABGR: return B200VC_IN_XBGR;
+    default: return B200VC_IN_BGRX;   /* BGRx, BGRA: what ximagesrc delivers at depth 24/32 */
+    }
+}
+
 static int matrix_of(const GstVideoInfo *i)
 {
     return i->colorimetry.matrix == GST_VIDEO_COLOR_MATRIX_BT601 ? B200VC_MATRIX_BT601 : B200VC_MATRIX_BT709;
@@ -99,6 +109,7 @@ gst_b200_convert_set_info(GstVideoFilter *filter, GstCaps *incaps, GstVideoInfo 
     cfg.device = self->device_id;
     cfg.in_w = GST_VIDEO_INFO_WIDTH(in);    cfg.in_h = GST_VIDEO_INFO_HEIGHT(in);
     cfg.out_w = GST_VIDEO_INFO_WIDTH(out);  cfg.out_h = GST_VIDEO_INFO_HEIGHT(out);
+    cfg.in_format = in_format_of(in);
     cfg.out_format = GST_VIDEO_INFO_FORMAT(out) == GST_VIDEO_FORMAT_NV12 ? B200VC_FMT_NV12 : B200VC_FMT_I420;
     /* honour the caps, do not assume */
     cfg.matrix = out->colorimetry.matrix == GST_VIDEO_COLOR_MATRIX_UNKNOWN ? m : matrix_of(out);

@@ -52,6 +52,10 @@ enum { B200VC_MATRIX_BT601 = 0, B200VC_MATRIX_BT709 = 1 };          /* colorimet
 enum { B200VC_RANGE_LIMITED = 0, B200VC_RANGE_FULL = 1 };           /* colorimetry range       */
 enum { B200VC_SITE_NONE = 0 /* "jpeg" */, B200VC_SITE_H_COSITED = 1 /* "mpeg2" */ };
 enum { B200VC_SCALE_GST_LQ = 0 /* videoscale bilinear, SURVEY B.2 */, B200VC_SCALE_BOX_2X2 = 1 };
+/* sink pad format: byte order of one pixel in memory; x is a pad or alpha byte and never matters
+ * (BGRA, RGBA, ARGB, ABGR negotiate as their x twins: I420/NV12 carry no alpha). BGRx is what
+ * ximagesrc delivers at the reference's default depth 24 (Dockerfile:206, entrypoint.sh:102). */
+enum { B200VC_IN_BGRX = 0, B200VC_IN_RGBX = 1, B200VC_IN_XRGB = 2, B200VC_IN_XBGR = 3 };
 
 /* flags */
 #define B200VC_FLAG_DAMAGE_MAP      0x1u  /* keep the previous frame per session and emit the map */
@@ -65,7 +69,7 @@ enum { B200VC_SCALE_GST_LQ = 0 /* videoscale bilinear, SURVEY B.2 */, B200VC_SCA
 
 typedef struct b200vc_config {
     int32_t device;        /* CUDA device ordinal                                                  */
-    int32_t in_w, in_h;    /* sink caps: video/x-raw,format=BGRx                                   */
+    int32_t in_w, in_h;    /* sink caps: video/x-raw,format=BGRx (or in_format below)              */
     int32_t out_w, out_h;  /* src caps; equal to in_* = videoconvert only                          */
     int32_t out_format;    /* B200VC_FMT_*                                                         */
     int32_t matrix;        /* B200VC_MATRIX_*                                                      */
@@ -76,6 +80,7 @@ typedef struct b200vc_config {
     int32_t max_sessions;  /* independent desktop sessions served by this context (>=1; 0 -> 1)   */
     int32_t n_inflight;    /* frames that may be in flight between submit and collect (0 -> 3)    */
     int32_t n_bands;       /* row bands a single synchronous convert is pipelined in (0 -> 4)     */
+    int32_t in_format;     /* B200VC_IN_* (0 = BGRx)                                               */
 } b200vc_config;
 
 typedef struct b200vc_ctx b200vc_ctx;

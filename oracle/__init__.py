@@ -23,6 +23,7 @@ MATRIX_BT601, MATRIX_BT709 = 0, 1
 RANGE_LIMITED, RANGE_FULL = 0, 1
 SITE_NONE, SITE_H_COSITED = 0, 1
 SCALE_GST_LQ, SCALE_BOX_2X2 = 0, 1
+IN_BGRX, IN_RGBX, IN_XRGB, IN_XBGR = 0, 1, 2, 3
 
 
 def build(native: bool = False, out_dir: str | None = None) -> str:
@@ -58,6 +59,8 @@ class Oracle:
         L.orc_convert_rows.argtypes = [u8p, sz, i, i, i, i, i, i, pl, pi, i, i]
         L.orc_scale_plane.argtypes = [u8p, sz, i, i, u8p, sz, i, i, i, i]
         L.orc_convert_scale_mt.argtypes = [u8p, sz, i, i, i, i, i, i, i, i, i, pl, pi, i]
+        L.orc_convert_scale_mt_ex.argtypes = [u8p, sz, i, i, i, i, i, i, i, i, i, i, pl, pi, i]
+        L.orc_damage_map_ex.argtypes = [u8p, sz, u8p, sz, i, i, i, u8p]
         L.orc_scale_h_taps.argtypes = [i, i, u8p, u8p]
         L.orc_scale_v_taps.argtypes = [i, i, u8p, u8p]
         L.orc_damage_map.argtypes = [u8p, sz, u8p, sz, i, i, u8p]
@@ -104,14 +107,14 @@ class Oracle:
         return buf, off, pit, ptrs, pits
 
     def convert(self, frame: np.ndarray, fmt=FMT_I420, matrix=MATRIX_BT601, rng=RANGE_LIMITED,
-                site=SITE_NONE, out_size=None, scale_mode=SCALE_GST_LQ, pitches=None, threads=1):
+                site=SITE_NONE, out_size=None, scale_mode=SCALE_GST_LQ, pitches=None, threads=1, in_format=IN_BGRX):
         """frame: (h, w, 4) uint8 BGRx (may be a strided view). Returns (buf, offsets, pitches)."""
         h, w = frame.shape[:2]
         assert frame.dtype == np.uint8 and frame.shape[2] == 4 and frame.strides[2] == 1 and frame.strides[1] == 4
         ow, oh = out_size if out_size else (w, h)
         buf, off, pit, ptrs, pits = self._planes(fmt, ow, oh, pitches)
-        rc = self.lib.orc_convert_scale_mt(frame.ctypes.data, frame.strides[0], w, h, ow, oh, fmt, matrix,
-                                           rng, site, scale_mode, ptrs, pits, threads)
+        rc = self.lib.orc_convert_scale_mt_ex(frame.ctypes.data, frame.strides[0], in_format, w, h, ow, oh, fmt, matrix,
+                                              rng, site, scale_mode, ptrs, pits, threads)
         if rc:
             raise ValueError("oracle rejected the arguments")
         return buf, off, pit
@@ -131,11 +134,11 @@ class Oracle:
             raise ValueError("oracle rejected the arguments")
         return dst
 
-    def damage_map(self, cur: np.ndarray, prev: np.ndarray | None) -> np.ndarray:
+    def damage_map(self, cur: np.ndarray, prev: np.ndarray | None, in_format=IN_BGRX) -> np.ndarray:
         h, w = cur.shape[:2]
         m = np.zeros(((h + 15) // 16, (w + 15) // 16), np.uint8)
-        self.lib.orc_damage_map(cur.ctypes.data, cur.strides[0], prev.ctypes.data if prev is not None else None,
-                                prev.strides[0] if prev is not None else 0, w, h, m.ctypes.data)
+        self.lib.orc_damage_map_ex(cur.ctypes.data, cur.strides[0], prev.ctypes.data if prev is not None else None,
+                                   prev.strides[0] if prev is not None else 0, in_format, w, h, m.ctypes.data)
         return m
 
     # -- synthetic frames ------------------------------------------------------------------------

@@ -71,14 +71,17 @@ size_t orc_default_layout(int format, int w, int h, size_t offsets[3], size_t pi
 
 /* ---- line stages ---------------------------------------------------------------------------- */
 
-/* unpack_BGRA: B,G,R,x -> A,R,G,B temp line (A forced to 0xff like the BGRx unpack). */
-static void unpack_bgrx(const uint8_t *s, uint8_t *d, int w)
+/* unpack_BGRA / unpack_RGBA / unpack_ARGB / unpack_ABGR: 4-byte pixel -> A,R,G,B temp line
+ * (A forced to 0xff like the x-format unpacks; it is dropped again by the pack stage). */
+static void unpack_line(const uint8_t *s, uint8_t *d, int w, int in_format)
 {
+    static const int pos[4][3] = { { 2, 1, 0 }, { 0, 1, 2 }, { 1, 2, 3 }, { 3, 2, 1 } };   /* byte of R, G, B */
+    const int pr = pos[in_format][0], pg = pos[in_format][1], pb = pos[in_format][2];
     for (int i = 0; i < w; i++) {
         d[4 * i + 0] = 0xff;
-        d[4 * i + 1] = s[4 * i + 2];
-        d[4 * i + 2] = s[4 * i + 1];
-        d[4 * i + 3] = s[4 * i + 0];
+        d[4 * i + 1] = s[4 * i + pr];
+        d[4 * i + 2] = s[4 * i + pg];
+        d[4 * i + 3] = s[4 * i + pb];
     }
 }
 
@@ -186,11 +189,13 @@ static void pack_uv_interleaved(const uint8_t *p, uint8_t *uv, int w)
 
 /* ---- frame entry points ------------------------------------------------------------------- */
 
-int orc_convert_rows(const uint8_t *bgrx, size_t in_pitch, int w, int h,
-                     int format, int matrix, int range, int site,
-                     uint8_t *const planes[3], const size_t pitches[3],
-                     int row0, int row1)
+static int convert_rows_ex(const uint8_t *bgrx, size_t in_pitch, int in_format, int w, int h,
+                           int format, int matrix, int range, int site,
+                           uint8_t *const planes[3], const size_t pitches[3],
+                           int row0, int row1)
 {
+    if (in_format < ORC_IN_BGRX || in_format > ORC_IN_XBGR)
+        return -1;
     if (!bgrx || !planes || !pitches || w < 2 || h < 2 || (w & 1) || (h & 1))
         return -1;
     if (row0 < 0 || row1 > h || row0 > row1 || (row0 & 1) || (row1 & 1))
@@ -212,8 +217,8 @@ int orc_convert_rows(const uint8_t *bgrx, size_t in_pitch, int w, int h,
     init_tables(&mx, tab);
 
     for (int y = row0; y < row1; y += 2) {
-        unpack_bgrx(bgrx + (size_t)y * in_pitch, l0, w);
-        unpack_bgrx(bgrx + (size_t)(y + 1) * in_pitch, l1, w);
+        unpack_line(bgrx + (size_t)y * in_pitch, l0, w, in_format);
+        unpack_line(bgrx + (size_t)(y + 1) * in_pitch, l1, w, in_format);
         matrix8_table(tab, l0, w);
         matrix8_table(tab, l1, w);
         pack_y(l0, planes[0] + (size_t)y * pitches[0], w);
@@ -229,6 +234,14 @@ int orc_convert_rows(const uint8_t *bgrx, size_t in_pitch, int w, int h,
     return 0;
 }
 
+int orc_convert_rows(const uint8_t *bgrx, size_t in_pitch, int w, int h,
+                     int format, int matrix, int range, int site,
+                     uint8_t *const planes[3], const size_t pitches[3],
+                     int row0, int row1)
+{
+    return convert_rows_ex(bgrx, in_pitch, ORC_IN_BGRX, w, h, format, matrix, range, site, planes, pitches, row0, row1);
+}
+
 int orc_convert(const uint8_t *bgrx, size_t in_pitch, int w, int h,
                 int format, int matrix, int range, int site,
                 uint8_t *const planes[3], const size_t pitches[3])
@@ -237,25 +250,36 @@ int orc_convert(const uint8_t *bgrx, size_t in_pitch, int w, int h,
 }
 
 typedef struct {
-    const uint8_t *bgrx; size_t in_pitch; int w, h, format, matrix, range, site;
+    const uint8_t *bgrx; size_t in_pitch; int in_format, w, h, format, matrix, range, site;
     uint8_t *const *planes; const size_t *pitches; int row0, row1, rc;
 } band_job;
 
 static void *band_main(void *arg)
 {
     band_job *j = (band_job *)arg;
-    j->rc = orc_convert_rows(j->bgrx, j->in_pitch, j->w, j->h, j->format, j->matrix, j->range,
-                             j->site, j->planes, j->pitches, j->row0, j->row1);
+    j->rc = convert_rows_ex(j->bgrx, j->in_pitch, j->in_format, j->w, j->h, j->format, j->matrix, j->range,
+                            j->site, j->planes, j->pitches, j->row0, j->row1);
     return NULL;
 }
 
 /* n-threads > 1: horizontal bands aligned to 2 lines. */
+int orc_convert_mt_ex(const uint8_t *bgrx, size_t in_pitch, int in_format, int w, int h,
+                      int format, int matrix, int range, int site,
+                      uint8_t *const planes[3], const size_t pitches[3], int n_threads);
+
 int orc_convert_mt(const uint8_t *bgrx, size_t in_pitch, int w, int h,
                    int format, int matrix, int range, int site,
                    uint8_t *const planes[3], const size_t pitches[3], int n_threads)
 {
+    return orc_convert_mt_ex(bgrx, in_pitch, ORC_IN_BGRX, w, h, format, matrix, range, site, planes, pitches, n_threads);
+}
+
+int orc_convert_mt_ex(const uint8_t *bgrx, size_t in_pitch, int in_format, int w, int h,
+                      int format, int matrix, int range, int site,
+                      uint8_t *const planes[3], const size_t pitches[3], int n_threads)
+{
     if (n_threads <= 1)
-        return orc_convert(bgrx, in_pitch, w, h, format, matrix, range, site, planes, pitches);
+        return convert_rows_ex(bgrx, in_pitch, in_format, w, h, format, matrix, range, site, planes, pitches, 0, h);
     if (n_threads > 64)
         n_threads = 64;
     pthread_t th[64];
@@ -264,7 +288,7 @@ int orc_convert_mt(const uint8_t *bgrx, size_t in_pitch, int w, int h,
     int pairs = h / 2, rc = 0;
     for (int t = 0; t < n_threads; t++) {
         band_job *j = &jobs[t];
-        j->bgrx = bgrx; j->in_pitch = in_pitch; j->w = w; j->h = h; j->format = format;
+        j->bgrx = bgrx; j->in_pitch = in_pitch; j->in_format = in_format; j->w = w; j->h = h; j->format = format;
         j->matrix = matrix; j->range = range; j->site = site; j->planes = planes; j->pitches = pitches;
         j->row0 = 2 * (int)((long)pairs * t / n_threads);
         j->row1 = 2 * (int)((long)pairs * (t + 1) / n_threads);

@@ -14,8 +14,15 @@
 int orc_damage_map(const uint8_t *cur, size_t cur_pitch, const uint8_t *prev, size_t prev_pitch,
                    int w, int h, uint8_t *map)
 {
-    if (!cur || !map || w < 1 || h < 1)
+    return orc_damage_map_ex(cur, cur_pitch, prev, prev_pitch, ORC_IN_BGRX, w, h, map);
+}
+
+int orc_damage_map_ex(const uint8_t *cur, size_t cur_pitch, const uint8_t *prev, size_t prev_pitch,
+                      int in_format, int w, int h, uint8_t *map)
+{
+    if (!cur || !map || w < 1 || h < 1 || in_format < ORC_IN_BGRX || in_format > ORC_IN_XBGR)
         return -1;
+    const int c0 = (in_format == ORC_IN_XRGB || in_format == ORC_IN_XBGR) ? 1 : 0;   /* first colour byte */
     const int mb_w = (w + 15) / 16, mb_h = (h + 15) / 16;
     if (!prev) {
         memset(map, 1, (size_t)mb_w * mb_h);
@@ -27,7 +34,8 @@ int orc_damage_map(const uint8_t *cur, size_t cur_pitch, const uint8_t *prev, si
         const uint8_t *b = prev + (size_t)y * prev_pitch;
         for (int x = 0; x < w; x++) {
             /* the x byte cannot change the converted output, so it is not damage */
-            if (a[4 * x] != b[4 * x] || a[4 * x + 1] != b[4 * x + 1] || a[4 * x + 2] != b[4 * x + 2])
+            if (a[4 * x + c0] != b[4 * x + c0] || a[4 * x + c0 + 1] != b[4 * x + c0 + 1] ||
+                a[4 * x + c0 + 2] != b[4 * x + c0 + 2])
                 map[(y / 16) * mb_w + (x / 16)] = 1;
         }
     }

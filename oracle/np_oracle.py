@@ -19,11 +19,16 @@ MATRICES = {
 }
 
 
-def yuv444(frame: np.ndarray, matrix: int, rng: int):
-    """(h,w,4) BGRx -> three (h,w) uint8 arrays, (c.RGB + off) >> 8 with no rounding term."""
-    b = frame[..., 0].astype(np.int32)
-    g = frame[..., 1].astype(np.int32)
-    r = frame[..., 2].astype(np.int32)
+# byte index of (R, G, B) in a pixel: BGRx, RGBx, xRGB, xBGR
+CHANNELS = {0: (2, 1, 0), 1: (0, 1, 2), 2: (1, 2, 3), 3: (3, 2, 1)}
+
+
+def yuv444(frame: np.ndarray, matrix: int, rng: int, in_format: int = 0):
+    """(h,w,4) pixels -> three (h,w) uint8 arrays, (c.RGB + off) >> 8 with no rounding term."""
+    ir, ig, ib = CHANNELS[in_format]
+    b = frame[..., ib].astype(np.int32)
+    g = frame[..., ig].astype(np.int32)
+    r = frame[..., ir].astype(np.int32)
     out = []
     for cr, cg, cb, off in MATRICES[(matrix, rng)]:
         s = cr * r + cg * g + cb * b + off
@@ -48,9 +53,9 @@ def chroma_down(c: np.ndarray, site: int) -> np.ndarray:
     return ((hz[0::2] + hz[1::2] + 1) >> 1).astype(np.uint8)
 
 
-def convert(frame: np.ndarray, fmt: int, matrix: int, rng: int, site: int):
+def convert(frame: np.ndarray, fmt: int, matrix: int, rng: int, site: int, in_format: int = 0):
     """Returns (Y, U, V) planes for I420 or (Y, UV) for NV12 at the input size."""
-    y, u, v = yuv444(frame, matrix, rng)
+    y, u, v = yuv444(frame, matrix, rng, in_format)
     u2, v2 = chroma_down(u, site), chroma_down(v, site)
     if fmt == 1:
         uv = np.empty((u2.shape[0], u2.shape[1] * 2), np.uint8)
@@ -90,8 +95,8 @@ def scale_plane(src: np.ndarray, out_w: int, out_h: int, comps: int = 1, mode: i
     return np.clip(d, 0, 255).astype(np.uint8).reshape(out_h, out_w * comps)
 
 
-def convert_scale(frame, out_w, out_h, fmt, matrix, rng, site, mode=0):
-    planes = convert(frame, fmt, matrix, rng, site)
+def convert_scale(frame, out_w, out_h, fmt, matrix, rng, site, mode=0, in_format=0):
+    planes = convert(frame, fmt, matrix, rng, site, in_format)
     if out_w == frame.shape[1] and out_h == frame.shape[0]:
         return planes
     out = [scale_plane(planes[0], out_w, out_h, 1, mode)]
@@ -103,12 +108,13 @@ def convert_scale(frame, out_w, out_h, fmt, matrix, rng, site, mode=0):
     return tuple(out)
 
 
-def damage_map(cur: np.ndarray, prev: np.ndarray | None) -> np.ndarray:
+def damage_map(cur: np.ndarray, prev: np.ndarray | None, in_format: int = 0) -> np.ndarray:
     h, w = cur.shape[:2]
     mh, mw = (h + 15) // 16, (w + 15) // 16
     if prev is None:
         return np.ones((mh, mw), np.uint8)
-    diff = np.any(cur[..., :3] != prev[..., :3], axis=2)
+    ch = list(CHANNELS[in_format])
+    diff = np.any(cur[..., ch] != prev[..., ch], axis=2)
     pad = np.zeros((mh * 16, mw * 16), bool)
     pad[:h, :w] = diff
     return pad.reshape(mh, 16, mw, 16).any(axis=(1, 3)).astype(np.uint8)

@@ -27,6 +27,8 @@ enum { ORC_MATRIX_BT601 = 0, ORC_MATRIX_BT709 = 1 };
 enum { ORC_RANGE_LIMITED = 0, ORC_RANGE_FULL = 1 };
 enum { ORC_SITE_NONE = 0 /* "jpeg" */, ORC_SITE_H_COSITED = 1 /* "mpeg2" */ };
 enum { ORC_SCALE_GST_LQ = 0, ORC_SCALE_BOX_2X2 = 1 };
+/* input byte orders: unpack_BGRA, unpack_RGBA, unpack_ARGB, unpack_ABGR (alpha/pad byte ignored) */
+enum { ORC_IN_BGRX = 0, ORC_IN_RGBX = 1, ORC_IN_XRGB = 2, ORC_IN_XBGR = 3 };
 
 /* 3x4 matrix in 8.8 fixed point: rows Y,U,V; columns cR,cG,cB,offset. */
 typedef struct {
@@ -71,6 +73,14 @@ int orc_convert_scale_mt(const uint8_t *bgrx, size_t in_pitch, int in_w, int in_
                          int out_w, int out_h, int format, int matrix, int range, int site,
                          int scale_mode, uint8_t *const planes[3], const size_t pitches[3],
                          int n_threads);
+
+/* The same entry points for the other 4-byte input formats (in_format = ORC_IN_*). */
+int orc_convert_scale_mt_ex(const uint8_t *src, size_t in_pitch, int in_format, int in_w, int in_h,
+                            int out_w, int out_h, int format, int matrix, int range, int site,
+                            int scale_mode, uint8_t *const planes[3], const size_t pitches[3],
+                            int n_threads);
+int orc_damage_map_ex(const uint8_t *cur, size_t cur_pitch, const uint8_t *prev, size_t prev_pitch,
+                      int in_format, int w, int h, uint8_t *map);
 
 /* Scaler taps, exposed so tests can pin them. */
 void orc_scale_h_taps(int in_w, int out_w, int32_t *idx, int32_t *frac);   /* frac 0..255 */

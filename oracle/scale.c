@@ -130,13 +130,17 @@ int orc_scale_plane(const uint8_t *src, size_t src_pitch, int in_w, int in_h,
     return 0;
 }
 
-static int convert_scale_impl(const uint8_t *bgrx, size_t in_pitch, int in_w, int in_h,
+int orc_convert_mt_ex(const uint8_t *bgrx, size_t in_pitch, int in_format, int w, int h,
+                      int format, int matrix, int range, int site,
+                      uint8_t *const planes[3], const size_t pitches[3], int n_threads);
+
+static int convert_scale_impl(const uint8_t *bgrx, size_t in_pitch, int in_format, int in_w, int in_h,
                               int out_w, int out_h, int format, int matrix, int range, int site,
                               int scale_mode, uint8_t *const planes[3], const size_t pitches[3],
                               int n_threads)
 {
     if (in_w == out_w && in_h == out_h)
-        return orc_convert_mt(bgrx, in_pitch, in_w, in_h, format, matrix, range, site, planes, pitches, n_threads);
+        return orc_convert_mt_ex(bgrx, in_pitch, in_format, in_w, in_h, format, matrix, range, site, planes, pitches, n_threads);
     if ((out_w & 1) || (out_h & 1) || out_w < 2 || out_h < 2)
         return -1;
 
@@ -147,7 +151,7 @@ static int convert_scale_impl(const uint8_t *bgrx, size_t in_pitch, int in_w, in
     if (!tmp)
         return -1;
     uint8_t *tp[3] = { tmp + off[0], tmp + off[1], tmp + off[2] };
-    int rc = orc_convert_mt(bgrx, in_pitch, in_w, in_h, format, matrix, range, site, tp, pit, n_threads);
+    int rc = orc_convert_mt_ex(bgrx, in_pitch, in_format, in_w, in_h, format, matrix, range, site, tp, pit, n_threads);
 
     /* stage 2: videoscale, each plane independently */
     if (!rc)
@@ -167,7 +171,7 @@ int orc_convert_scale(const uint8_t *bgrx, size_t in_pitch, int in_w, int in_h,
                       int out_w, int out_h, int format, int matrix, int range, int site,
                       int scale_mode, uint8_t *const planes[3], const size_t pitches[3])
 {
-    return convert_scale_impl(bgrx, in_pitch, in_w, in_h, out_w, out_h, format, matrix, range, site,
+    return convert_scale_impl(bgrx, in_pitch, ORC_IN_BGRX, in_w, in_h, out_w, out_h, format, matrix, range, site,
                               scale_mode, planes, pitches, 1);
 }
 
@@ -177,6 +181,15 @@ int orc_convert_scale_mt(const uint8_t *bgrx, size_t in_pitch, int in_w, int in_
                          int scale_mode, uint8_t *const planes[3], const size_t pitches[3],
                          int n_threads)
 {
-    return convert_scale_impl(bgrx, in_pitch, in_w, in_h, out_w, out_h, format, matrix, range, site,
+    return convert_scale_impl(bgrx, in_pitch, ORC_IN_BGRX, in_w, in_h, out_w, out_h, format, matrix, range, site,
+                              scale_mode, planes, pitches, n_threads);
+}
+
+int orc_convert_scale_mt_ex(const uint8_t *src, size_t in_pitch, int in_format, int in_w, int in_h,
+                            int out_w, int out_h, int format, int matrix, int range, int site,
+                            int scale_mode, uint8_t *const planes[3], const size_t pitches[3],
+                            int n_threads)
+{
+    return convert_scale_impl(src, in_pitch, in_format, in_w, in_h, out_w, out_h, format, matrix, range, site,
                               scale_mode, planes, pitches, n_threads);
 }

@@ -15,7 +15,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 from oracle import np_oracle as N  # noqa: E402
 
-# (name, in_w, in_h, out_w, out_h, fmt, matrix, range, site, scale_mode)
+# (name, in_w, in_h, out_w, out_h, fmt, matrix, range, site, scale_mode[, in_format])
 CASES = [
     ("c1_601l_i420_jpeg", 36, 20, 36, 20, 0, 0, 0, 0, 0),
     ("601l_i420_mpeg2", 36, 20, 36, 20, 0, 0, 0, 1, 0),
@@ -26,17 +26,22 @@ CASES = [
     ("scale_3to2_601l_nv12", 96, 48, 64, 32, 1, 0, 0, 0, 0),
     ("scale_box_709l_i420", 64, 36, 32, 18, 0, 1, 0, 1, 1),
     ("scale_odd_ratio", 100, 60, 46, 26, 0, 1, 0, 1, 0),
+    ("in_rgbx_709l_i420", 38, 20, 38, 20, 0, 1, 0, 1, 0, 1),
+    ("in_xrgb_601f_nv12", 38, 20, 38, 20, 1, 0, 1, 0, 0, 2),
+    ("in_xbgr_2to1_709l_i420", 64, 36, 32, 18, 0, 1, 0, 1, 0, 3),
 ]
 
 
 def main():
     rng = np.random.default_rng(20261106)
     out = {}
-    for name, iw, ih, ow, oh, fmt, mat, rg, site, mode in CASES:
+    for case in CASES:
+        name, iw, ih, ow, oh, fmt, mat, rg, site, mode = case[:10]
+        inf = case[10] if len(case) > 10 else 0
         frame = rng.integers(0, 256, size=(ih, iw, 4), dtype=np.uint8)
-        planes = N.convert_scale(frame, ow, oh, fmt, mat, rg, site, mode)
+        planes = N.convert_scale(frame, ow, oh, fmt, mat, rg, site, mode, inf)
         out[name + "/in"] = frame
-        out[name + "/cfg"] = np.array([iw, ih, ow, oh, fmt, mat, rg, site, mode], np.int32)
+        out[name + "/cfg"] = np.array([iw, ih, ow, oh, fmt, mat, rg, site, mode, inf], np.int32)
         for i, p in enumerate(planes):
             out[f"{name}/p{i}"] = p
     # damage map: two frames differing in a few places (one of them only in the x byte)

@@ -30,7 +30,7 @@ def test_header_and_library_agree(lib):
 
 def test_struct_sizes_match_the_header():
     # the header's structs, laid out by hand (LP64): catches a drifting ctypes mirror
-    assert C.sizeof(b200vc.Config) == 14 * 4
+    assert C.sizeof(b200vc.Config) == 15 * 4
     assert C.sizeof(b200vc.Frame) == 8 + 8 + 24 + 24 + 8 + 4 + 4
     assert C.sizeof(b200vc.DeviceFrames) == 3 * 8 + 3 * 8 + 24 + 24 + 8 + 8 + 8 + 4 + 4
     assert C.sizeof(b200vc.Stats) == 6 * 8
@@ -58,7 +58,7 @@ def test_default_layout_matches_oracle(orc, fmt, w, h):
 
 def _cfg(**kw):
     base = dict(device=0, in_w=1920, in_h=1080, out_w=1920, out_h=1080, out_format=0, matrix=0, range=0,
-                chroma_site=0, scale_mode=0, flags=0, max_sessions=1, n_inflight=0, n_bands=0)
+                chroma_site=0, scale_mode=0, flags=0, max_sessions=1, n_inflight=0, n_bands=0, in_format=0)
     base.update(kw)
     return b200vc.Config(**base)
 
@@ -66,11 +66,12 @@ def _cfg(**kw):
 def test_caps_acceptance(lib):
     ok = [_cfg(), _cfg(out_format=1, matrix=1, range=1, chroma_site=1, in_w=2560, in_h=1440, out_w=2560, out_h=1440),
           _cfg(in_w=3840, in_h=2160), _cfg(in_w=3840, in_h=2160, scale_mode=1), _cfg(flags=b200vc.FLAG_DAMAGE_MAP),
-          _cfg(in_w=1366, in_h=768, out_w=1366, out_h=768), _cfg(max_sessions=8, n_inflight=4)]
+          _cfg(in_w=1366, in_h=768, out_w=1366, out_h=768), _cfg(max_sessions=8, n_inflight=4), _cfg(in_format=3)]
     for c in ok:
         assert lib.b200vc_check_config(C.byref(c)) == b200vc.OK
     refused = [(_cfg(in_w=1921, out_w=1921), b200vc.ERR_UNSUPPORTED),      # odd width
                (_cfg(out_format=2), b200vc.ERR_UNSUPPORTED),               # not I420/NV12
+               (_cfg(in_format=4), b200vc.ERR_UNSUPPORTED),                # not a 4-byte RGB order
                (_cfg(matrix=2), b200vc.ERR_UNSUPPORTED),                   # bt2020 not offered
                (_cfg(chroma_site=3), b200vc.ERR_UNSUPPORTED),              # v-cosited not offered
                (_cfg(in_w=3840, in_h=2160, out_w=1280, out_h=720, scale_mode=1), b200vc.ERR_UNSUPPORTED),

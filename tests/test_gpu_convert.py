@@ -78,8 +78,9 @@ def test_golden_vectors_on_gpu(conv):
     z = np.load(GOLDEN)
     names = sorted({k.split("/")[0] for k in z.files if k.endswith("/cfg")})
     for name in names:
-        iw, ih, ow, oh, fmt, mat, rg, site, mode = [int(v) for v in z[name + "/cfg"]]
-        conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=mat, range_=rg, chroma_site=site, scale_mode=mode)
+        iw, ih, ow, oh, fmt, mat, rg, site, mode, inf = [int(v) for v in z[name + "/cfg"]]
+        conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=mat, range_=rg, chroma_site=site, scale_mode=mode,
+                      in_format=inf)
         buf, off, pit = conv.transform_frame(np.ascontiguousarray(z[name + "/in"]))
         want = [z[f"{name}/p{i}"] for i in range(2 if fmt else 3)]
         assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), want, name)
@@ -283,3 +284,27 @@ def test_errors_at_run_time(conv):
     with pytest.raises(b200vc.B200vcError) as e:      # caps the element does not offer
         conv.set_info(63, 32)
     assert e.value.status == b200vc.ERR_UNSUPPORTED
+
+
+@pytest.mark.parametrize("inf", [1, 2, 3])
+def test_input_formats_on_gpu(conv, orc, inf):
+    """RGBx/RGBA, xRGB/ARGB, xBGR/ABGR sink formats: conversion, fused scale and damage map."""
+    for (w, h) in [(1920, 1080), (134, 34)]:
+        f = orc.synth("rand", w, h, 21)
+        for fmt, m, rg, site in [(0, 1, 0, 1), (1, 0, 1, 0)]:
+            conv.set_info(w, h, out_format=fmt, matrix=m, range_=rg, chroma_site=site, in_format=inf,
+                          flags=b200vc.FLAG_DAMAGE_MAP)
+            buf, off, pit, dm = conv.transform_frame(f, damage=True)
+            assert_planes_equal(plane_views(buf, off, pit, fmt, w, h),
+                                plane_views(*orc.convert(f, fmt, m, rg, site, in_format=inf), fmt, w, h), f"in{inf} {w}x{h}")
+            g = f.copy()
+            g[5, 7, 0] ^= 1
+            g[h - 1, w - 1, 3] ^= 1
+            dm = conv.transform_frame(g, damage=True)[3]
+            assert np.array_equal(dm, orc.damage_map(g, f, inf)) and dm.sum() == 1
+    f = orc.synth("rand", 1280, 720, 22)
+    for flags in (0, b200vc.FLAG_FORCE_GENERIC_FUSED, b200vc.FLAG_FORCE_TWO_PASS):
+        conv.set_info(1280, 720, 640, 360, matrix=1, range_=0, chroma_site=1, in_format=inf, flags=flags)
+        buf, off, pit = conv.transform_frame(f)
+        want = orc.convert(f, 0, 1, 0, 1, in_format=inf, out_size=(640, 360))
+        assert_planes_equal(plane_views(buf, off, pit, 0, 640, 360), plane_views(*want, 0, 640, 360), f"in{inf} scaled {flags}")

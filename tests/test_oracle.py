@@ -52,11 +52,11 @@ def test_known_answers_uniform_frames(orc, fmt, site):
 def test_golden_vectors(orc):
     z = np.load(GOLDEN)
     names = sorted({k.split("/")[0] for k in z.files if k.endswith("/cfg")})
-    assert len(names) >= 9
+    assert len(names) >= 12
     for name in names:
-        iw, ih, ow, oh, fmt, mat, rg, site, mode = [int(v) for v in z[name + "/cfg"]]
+        iw, ih, ow, oh, fmt, mat, rg, site, mode, inf = [int(v) for v in z[name + "/cfg"]]
         frame = np.ascontiguousarray(z[name + "/in"])
-        buf, off, pit = orc.convert(frame, fmt, mat, rg, site, out_size=(ow, oh), scale_mode=mode)
+        buf, off, pit = orc.convert(frame, fmt, mat, rg, site, out_size=(ow, oh), scale_mode=mode, in_format=inf)
         want = [z[f"{name}/p{i}"] for i in range(2 if fmt else 3)]
         assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), want, name)
     assert np.array_equal(orc.damage_map(np.ascontiguousarray(z["damage/b"]), np.ascontiguousarray(z["damage/a"])),
@@ -173,3 +173,20 @@ def test_property_c_equals_numpy(w, h, fmt, m, rg, site, seed):
     frame = np.random.default_rng(seed).integers(0, 256, (h, w, 4), dtype=np.uint8)
     buf, off, pit = orc.convert(frame, fmt, m, rg, site)
     assert_planes_equal(plane_views(buf, off, pit, fmt, w, h), list(N.convert(frame, fmt, m, rg, site)))
+
+
+def test_input_formats(orc):
+    """RGBx / xRGB / xBGR (and their alpha twins) are byte permutations of BGRx: same output."""
+    f = orc.synth("rand", 134, 34, 3)
+    base = orc.convert(f, 0, 1, 0, 1)[0]
+    for inf, perm in {1: [2, 1, 0, 3], 2: [3, 2, 1, 0], 3: [3, 0, 1, 2]}.items():
+        g = np.ascontiguousarray(f[..., perm])
+        assert np.array_equal(orc.convert(g, 0, 1, 0, 1, in_format=inf)[0], base)
+        for fmt in (0, 1):
+            buf, off, pit = orc.convert(f, fmt, 0, 1, 0, in_format=inf, out_size=(66, 16))
+            assert_planes_equal(plane_views(buf, off, pit, fmt, 66, 16), list(N.convert_scale(f, 66, 16, fmt, 0, 1, 0, 0, inf)))
+        h = f.copy()
+        h[5, 7, 0] ^= 1      # byte 0 is the pad byte for xRGB/xBGR, a colour for BGRx/RGBx
+        h[20, 100, 3] ^= 1   # and the other way round for byte 3
+        assert np.array_equal(orc.damage_map(h, f, inf), N.damage_map(h, f, inf))
+        assert orc.damage_map(h, f, inf).sum() == 1

@@ -305,10 +305,12 @@ k2_fused_2x_kernel(const __grid_constant__ CUtensorMap src_map, const Fused2xPar
         } else {
             const uint32_t ox = (uint32_t)(c >> 1);
             const uint32_t f0 = ((ox * p.inc_y) >> 8) & 0xffu, f1 = (((ox + 1u) * p.inc_y) >> 8) & 0xffu;
-            const uint32_t s0 = ((w0 * (256u - f0) + w1 * f0) >> 8) & LANES8;
-            const uint32_t s1 = ((w2 * (256u - f1) + w3 * f1) >> 8) & LANES8;
-            d0 = ((s0 & 0xffffu) + (s0 >> 16) + 1u) >> 1;
-            d1 = ((s1 & 0xffffu) + (s1 >> 16) + 1u) >> 1;
+            // per 16-bit lane the weighted sum is < 65536 and its high byte is the horizontally
+            // scaled pixel (the >> 8); dp4a with weights on bytes 1 and 3 adds the two lines + 1
+            const uint32_t s0 = w0 * (256u - f0) + w1 * f0;
+            const uint32_t s1 = w2 * (256u - f1) + w3 * f1;
+            d0 = dp4a_uu(s0, 0x01000100u, 1u) >> 1;
+            d1 = dp4a_uu(s1, 0x01000100u, 1u) >> 1;
         }
         yout[ii] = d0 | (d1 << 8);
     }

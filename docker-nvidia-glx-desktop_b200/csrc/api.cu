@@ -776,7 +776,7 @@ int b200vc_create(const b200vc_config *cfg, b200vc_ctx **out)
     c->cfg = *cfg;
     if (c->cfg.max_sessions == 0) c->cfg.max_sessions = 1;
     if (c->cfg.n_inflight == 0) c->cfg.n_inflight = 3;
-    if (c->cfg.n_bands == 0) c->cfg.n_bands = 4;
+    if (c->cfg.n_bands == 0) c->cfg.n_bands = 2;   // measured best for 1080p (tools/sync_latency.py)
     memset(&c->stats, 0, sizeof c->stats);
     rc = create_impl(c);
     if (rc) {

@@ -79,7 +79,7 @@ typedef struct b200vc_config {
     uint32_t flags;        /* B200VC_FLAG_*                                                        */
     int32_t max_sessions;  /* independent desktop sessions served by this context (>=1; 0 -> 1)   */
     int32_t n_inflight;    /* frames that may be in flight between submit and collect (0 -> 3)    */
-    int32_t n_bands;       /* row bands a single synchronous convert is pipelined in (0 -> 4)     */
+    int32_t n_bands;       /* row bands a single synchronous convert is pipelined in (0 -> 2)     */
     int32_t in_format;     /* B200VC_IN_* (0 = BGRx)                                               */
 } b200vc_config;
 

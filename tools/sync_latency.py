@@ -1,0 +1,22 @@
+"""Synchronous single-frame call (b200vc_convert, GstBaseTransform's default mode): frames/s vs n_bands."""
+import ctypes as C, os, sys, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "docker-nvidia-glx-desktop_b200")]
+import b200vc
+W, H = 1920, 1080
+total, off, pit = b200vc.default_layout(0, W, H)
+h_in, h_out = b200vc.PinnedBuffer(8 * W * H * 4), b200vc.PinnedBuffer(total)
+h_in.array[:] = 77
+planes = (C.c_void_p * 3)(*[h_out.ptr + o for o in off]); pits = (C.c_size_t * 3)(*pit)
+conv = b200vc.Converter(0)
+for bands in (1, 2, 3, 4, 6, 8, 12, 17):
+    conv.set_info(W, H, matrix=0, range_=0, chroma_site=1, n_bands=bands)
+    for i in range(20):
+        conv.lib.b200vc_convert(conv.ctx, h_in.ptr + (i % 8) * W * H * 4, W * 4, planes, pits, None)
+    n = 400
+    t0 = time.perf_counter()
+    for i in range(n):
+        conv.lib.b200vc_convert(conv.ctx, h_in.ptr + (i % 8) * W * H * 4, W * 4, planes, pits, None)
+    dt = time.perf_counter() - t0
+    print(f"bands={bands:2d}: {n / dt:8.1f} frames/s  {dt / n * 1e6:7.1f} us/frame", flush=True)
+conv.stop()

@@ -213,7 +213,7 @@ class Converter:
             total, off, pit = self.out_layout()
         else:
             pit = list(pitches) + [0] * (3 - len(pitches))
-            rows = [g.out_h, g.out_h // 2, g.out_h // 2]
+            rows = [g.out_h, (g.out_h + 1) // 2, (g.out_h + 1) // 2]
             off, total = [], 0
             for p in range(2 if g.out_format == FMT_NV12 else 3):
                 off.append(total)

@@ -246,8 +246,9 @@ int check_config(const b200vc_config *c, std::string *why)
         return bad(B200VC_ERR_INVALID_ARG, "width/height must be >= 2");
     if (c->in_w > 16384 || c->in_h > 16384 || c->out_w > 16384 || c->out_h > 16384)
         return bad(B200VC_ERR_UNSUPPORTED, "width/height above 16384");
-    if ((c->in_w | c->in_h | c->out_w | c->out_h) & 1)
-        return bad(B200VC_ERR_UNSUPPORTED, "odd widths/heights are not negotiated (4:2:0 needs even sizes)");
+    const bool scaling_req = c->in_w != c->out_w || c->in_h != c->out_h;
+    if (scaling_req && ((c->in_w | c->in_h | c->out_w | c->out_h) & 1))
+        return bad(B200VC_ERR_UNSUPPORTED, "scaling is negotiated for even widths and heights only");
     if (c->out_format != B200VC_FMT_I420 && c->out_format != B200VC_FMT_NV12)
         return bad(B200VC_ERR_UNSUPPORTED, "output format must be I420 or NV12");
     if (c->in_format < B200VC_IN_BGRX || c->in_format > B200VC_IN_XBGR)
@@ -459,11 +460,12 @@ int create_impl(b200vc_ctx *c)
     c->d_in_pitch = ru((size_t)g.in_w * 4, 256);
     c->d_in_size = c->d_in_pitch * g.in_h;
     {
-        const size_t yp = ru(g.out_w, 256), cp = g.out_format == B200VC_FMT_NV12 ? yp : ru(g.out_w / 2, 256);
+        const size_t ch = (size_t)(g.out_h + 1) / 2, cw = (size_t)(g.out_w + 1) / 2;   // chroma lines / samples
+        const size_t yp = ru(g.out_w + 1, 256), cp = g.out_format == B200VC_FMT_NV12 ? yp : ru(cw, 256);
         c->d_pitch[0] = yp;  c->d_pitch[1] = cp;  c->d_pitch[2] = g.out_format == B200VC_FMT_NV12 ? 0 : cp;
         c->d_off[0] = 0;  c->d_off[1] = yp * g.out_h;
-        c->d_off[2] = g.out_format == B200VC_FMT_NV12 ? 0 : c->d_off[1] + cp * (g.out_h / 2);
-        c->d_out_size = ru(c->d_off[1] + cp * (g.out_h / 2) * (g.out_format == B200VC_FMT_NV12 ? 1 : 2), 256);
+        c->d_off[2] = g.out_format == B200VC_FMT_NV12 ? 0 : c->d_off[1] + cp * ch;
+        c->d_out_size = ru(c->d_off[1] + cp * ch * (g.out_format == B200VC_FMT_NV12 ? 1 : 2), 256);
     }
     const size_t dmg_bytes = ru((size_t)c->mb_w * c->mb_h, 256);
 
@@ -554,7 +556,7 @@ int validate_frame(b200vc_ctx *c, const b200vc_frame *f)
         return fail(c, B200VC_ERR_INVALID_ARG, "session %d out of range (max_sessions %d)", f->session, g.max_sessions);
     if (f->in_pitch < (size_t)g.in_w * 4)
         return fail(c, B200VC_ERR_INVALID_ARG, "input pitch %zu is smaller than a row (%d bytes)", f->in_pitch, g.in_w * 4);
-    const size_t cw = g.out_format == B200VC_FMT_NV12 ? (size_t)g.out_w : (size_t)g.out_w / 2;
+    const size_t cs = (size_t)(g.out_w + 1) / 2, cw = g.out_format == B200VC_FMT_NV12 ? 2 * cs : cs;
     if (f->pitches[0] < (size_t)g.out_w || f->pitches[1] < cw || (g.out_format == B200VC_FMT_I420 && f->pitches[2] < cw))
         return fail(c, B200VC_ERR_INVALID_ARG, "an output pitch is smaller than its row");
     if (f->damage && !(g.flags & B200VC_FLAG_DAMAGE_MAP))
@@ -575,9 +577,9 @@ int submit_locked(b200vc_ctx *c, const b200vc_frame *f, int bands, uint64_t *tic
 
     const size_t row_bytes = (size_t)g.in_w * 4;
     const int n_planes = g.out_format == B200VC_FMT_NV12 ? 2 : 3;
-    const size_t out_row_bytes[3] = { (size_t)g.out_w, g.out_format == B200VC_FMT_NV12 ? (size_t)g.out_w : (size_t)g.out_w / 2,
-                                      (size_t)g.out_w / 2 };
-    const int out_rows[3] = { g.out_h, g.out_h / 2, g.out_h / 2 };
+    const size_t cs = (size_t)(g.out_w + 1) / 2;           // chroma samples per line
+    const size_t out_row_bytes[3] = { (size_t)g.out_w, g.out_format == B200VC_FMT_NV12 ? 2 * cs : cs, cs };
+    const int out_rows[3] = { g.out_h, (g.out_h + 1) / 2, (g.out_h + 1) / 2 };
 
     // where do the host sides live?
     bool in_pinned = is_pinned(f->bgrx);
@@ -634,7 +636,7 @@ int submit_locked(b200vc_ctx *c, const b200vc_frame *f, int bands, uint64_t *tic
         CU_TRY(c, cudaStreamWaitEvent(c->s_d2h, c->ev_band_k[b], 0));
         // D2H of this band's rows of every plane
         for (int i = 0; i < n_planes; i++) {
-            const int pr0 = i ? row0 / 2 : row0, prs = i ? rows / 2 : rows;
+            const int pr0 = i ? row0 / 2 : row0, prs = i ? (rows + 1) / 2 : rows;
             uint8_t *hdst = out_pinned ? (uint8_t *)f->planes[i] + (size_t)pr0 * f->pitches[i]
                                        : slot.h_out + c->d_off[i] + (size_t)pr0 * c->d_pitch[i];
             const size_t hp = out_pinned ? f->pitches[i] : c->d_pitch[i];
@@ -689,9 +691,9 @@ int collect_slot(b200vc_ctx *c, Slot &s)
     if (s.staged_out) {
         const b200vc_config &g = c->cfg;
         const int n_planes = g.out_format == B200VC_FMT_NV12 ? 2 : 3;
-        const size_t rb[3] = { (size_t)g.out_w, g.out_format == B200VC_FMT_NV12 ? (size_t)g.out_w : (size_t)g.out_w / 2,
-                               (size_t)g.out_w / 2 };
-        const int rows[3] = { g.out_h, g.out_h / 2, g.out_h / 2 };
+        const size_t cs = (size_t)(g.out_w + 1) / 2;
+        const size_t rb[3] = { (size_t)g.out_w, g.out_format == B200VC_FMT_NV12 ? 2 * cs : cs, cs };
+        const int rows[3] = { g.out_h, (g.out_h + 1) / 2, (g.out_h + 1) / 2 };
         for (int i = 0; i < n_planes; i++) {
             copy_rows((uint8_t *)s.frame.planes[i], s.frame.pitches[i], s.h_out + c->d_off[i], c->d_pitch[i], rb[i], rows[i]);
             c->stats.staged_out_bytes += rb[i] * rows[i];
@@ -927,7 +929,7 @@ int b200vc_convert_device(b200vc_ctx *c, const b200vc_device_frames *d, void *cu
     for (int i = 0; i < np; i++) ok = ok && aligned16(d->planes[i]) && d->pitches[i] % 16 == 0;
     if (d->prev) ok = ok && aligned16(d->prev) && d->prev_pitch % 16 == 0 && d->prev_frame_stride % 16 == 0;
     if (!ok) return fail(c, B200VC_ERR_ALIGNMENT, "device pointers, pitches and frame strides must be multiples of 16 bytes");
-    const size_t cw = g.out_format == B200VC_FMT_NV12 ? (size_t)g.out_w : (size_t)g.out_w / 2;
+    const size_t cs2 = (size_t)(g.out_w + 1) / 2, cw = g.out_format == B200VC_FMT_NV12 ? 2 * cs2 : cs2;
     if (d->in_pitch < (size_t)g.in_w * 4 || d->pitches[0] < (size_t)g.out_w || d->pitches[1] < cw ||
         (np == 3 && d->pitches[2] < cw))
         return fail(c, B200VC_ERR_INVALID_ARG, "a pitch is smaller than its row");

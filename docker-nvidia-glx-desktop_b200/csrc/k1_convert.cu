@@ -67,13 +67,14 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
     WarpStage<HR> &st = s_stage[warp];
     const Matrix &m = p.mx;
     const int x = x0 + lane * 4;                           // first pixel of this thread
-    const int remain = p.w - x;                            // w even, x % 4 == 0  ->  <= 0, 2, or >= 4
-    const bool v4 = remain >= 4, v2 = remain == 2;         // this lane holds 4 / 2 / no valid pixels
+    const int remain = p.w - x;                            // pixels of this lane inside the frame: <= 0, 1..3, >= 4
     const bool interior_x = x0 + TW <= p.w;                // warp-uniform
     const bool halo = SITE == 1 && lane == 0 && x0 > 0;    // lane 0 fetches the stripe's left neighbour
-    // cosited right edge: the last even column (w-2, when w > 2) takes itself as right neighbour
-    const bool edge3 = SITE == 1 && p.w > 2 && x + 4 == p.w;
-    const bool edge1 = SITE == 1 && p.w > 2 && x + 2 == p.w;
+    // Right frame edge, cosited: the last chroma site (column w-2 of an even width, w-1 of an odd
+    // one; w > 2) takes itself as right neighbour (FILT_1_3). (Jpeg siting needs no flag: the edge
+    // loader duplicates an unpaired last pixel, and avg2(p, p) = p.)
+    const bool edge1 = SITE == 1 && p.w > 2 && remain <= 2;   // site at pixel 0
+    const bool edge3 = SITE == 1 && p.w > 2 && remain <= 4;   // site at pixel 2
 
     const uint8_t *src = p.src + (long long)frame * p.src_frame_stride + (long long)y0 * p.src_pitch + (long long)x * 4;
     const uint8_t *prv = DMG ? p.prev + (long long)frame * p.prev_frame_stride + (long long)y0 * p.prev_pitch + (long long)x * 4
@@ -110,19 +111,33 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
                 hl[r] = 0;
                 if (r < rows) {
                     uint4 q = make_uint4(0, 0, 0, 0);
-                    if (v4) {
+                    if (remain >= 4) {
                         px[r] = ldg_stream_v4(src);
                         if (DMG) q = ldg_stream_v4(prv);
-                    } else if (v2) {
-                        const uint2 t = ldg_stream_v2(src);
-                        px[r].x = t.x;  px[r].y = t.y;
-                        if (DMG) { const uint2 u = ldg_stream_v2(prv);  q.x = u.x;  q.y = u.y; }
+                    } else if (remain > 0) {               // 1..3 pixels: odd widths and widths % 4 != 0
+                        px[r].x = ldg_stream_u32(src);
+                        if (remain > 1) px[r].y = ldg_stream_u32(src + 4);
+                        if (remain > 2) px[r].z = ldg_stream_u32(src + 8);
+                        if (DMG) {
+                            q.x = ldg_stream_u32(prv);
+                            if (remain > 1) q.y = ldg_stream_u32(prv + 4);
+                            if (remain > 2) q.z = ldg_stream_u32(prv + 8);
+                        }
                     }
                     if (SITE == 1) hl[r] = ldg_stream_u32_if(src - 4, halo);
                     if (DMG) diff |= (px[r].x ^ q.x) | (px[r].y ^ q.y) | (px[r].z ^ q.z) | (px[r].w ^ q.w);
+                    if (SITE == 0) {                       // odd width: the unpaired last pixel pairs with itself
+                        if (remain == 1) px[r].y = px[r].x;
+                        if (remain == 3) px[r].w = px[r].z;
+                    }
                 }
                 src += p.src_pitch;
                 if (DMG) prv += p.prev_pitch;
+            }
+            if (rows & 1) {                                // odd height: the last line pairs with itself
+#pragma unroll
+                for (int r = 1; r < HR; r += 2)
+                    if (r == rows) { px[r] = px[r - 1]; hl[r] = hl[r - 1]; }
             }
         }
 
@@ -177,12 +192,13 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
             const int r = lane >> 3;                       // chroma: HR/2 rows x 8 segments
             if (r < PAIRS && 2 * r < rows) {
                 const long long cy = (yh >> 1) + r;
+                const int cw = (p.w + 1) >> 1;             // chroma samples per line (odd widths round up)
                 if (FMT == 0) {
-                    const int plane = 1 + (seg >> 2), cx = (x0 >> 1) + (seg & 3) * 16, cw = p.w >> 1;
+                    const int plane = 1 + (seg >> 2), cx = (x0 >> 1) + (seg & 3) * 16;
                     if (cx < cw)
                         store16(p.out.p[plane] + fo + cy * p.out.pitch[plane] + cx, &st.c[r][seg * 16], cw - cx);
-                } else if (gx < p.w) {
-                    store16(p.out.p[1] + fo + cy * p.out.pitch[1] + gx, &st.c[r][seg * 16], p.w - gx);
+                } else if (gx < 2 * cw) {
+                    store16(p.out.p[1] + fo + cy * p.out.pitch[1] + gx, &st.c[r][seg * 16], 2 * cw - gx);
                 }
             }
         }

@@ -36,7 +36,7 @@ extern "C" {
 /* ---- status codes ------------------------------------------------------------------------- */
 enum {
     B200VC_OK = 0,
-    B200VC_ERR_INVALID_ARG = 1,   /* NULL pointer, bad enum, odd size, ...                        */
+    B200VC_ERR_INVALID_ARG = 1,   /* NULL pointer, bad enum, size out of range, ...               */
     B200VC_ERR_UNSUPPORTED = 2,   /* caps this element does not accept (refuse at negotiation)    */
     B200VC_ERR_NOT_NEGOTIATED = 3,/* called before a successful create (GST_FLOW_NOT_NEGOTIATED)  */
     B200VC_ERR_CUDA = 4,          /* a CUDA call failed (GST_FLOW_ERROR); see b200vc_last_error   */

@@ -95,7 +95,7 @@ class Oracle:
             total, off, pit = self.default_layout(fmt, w, h)
         else:
             pit = list(pitches) + [0] * (3 - len(pitches))
-            rows = [h, h // 2, h // 2]
+            rows = [h, (h + 1) // 2, (h + 1) // 2]
             off, total = [], 0
             for p in range(3 if fmt == FMT_I420 else 2):
                 off.append(total)

@@ -171,9 +171,10 @@ static void pack_y(const uint8_t *p, uint8_t *y, int w)
         y[i] = p[4 * i + 1];
 }
 
+/* odd widths: the last pixel is a chroma site of its own (pack_I420's `if (width & 1)` tail) */
 static void pack_uv_planar(const uint8_t *p, uint8_t *u, uint8_t *v, int w)
 {
-    for (int i = 0; i < w / 2; i++) {
+    for (int i = 0; i < (w + 1) / 2; i++) {
         u[i] = p[8 * i + 2];
         v[i] = p[8 * i + 3];
     }
@@ -181,7 +182,7 @@ static void pack_uv_planar(const uint8_t *p, uint8_t *u, uint8_t *v, int w)
 
 static void pack_uv_interleaved(const uint8_t *p, uint8_t *uv, int w)
 {
-    for (int i = 0; i < w / 2; i++) {
+    for (int i = 0; i < (w + 1) / 2; i++) {
         uv[2 * i + 0] = p[8 * i + 2];
         uv[2 * i + 1] = p[8 * i + 3];
     }
@@ -196,9 +197,9 @@ static int convert_rows_ex(const uint8_t *bgrx, size_t in_pitch, int in_format, 
 {
     if (in_format < ORC_IN_BGRX || in_format > ORC_IN_XBGR)
         return -1;
-    if (!bgrx || !planes || !pitches || w < 2 || h < 2 || (w & 1) || (h & 1))
+    if (!bgrx || !planes || !pitches || w < 2 || h < 2)
         return -1;
-    if (row0 < 0 || row1 > h || row0 > row1 || (row0 & 1) || (row1 & 1))
+    if (row0 < 0 || row1 > h || row0 > row1 || (row0 & 1) || ((row1 & 1) && row1 != h))
         return -1;
     if (format != ORC_FMT_I420 && format != ORC_FMT_NV12)
         return -1;
@@ -217,12 +218,15 @@ static int convert_rows_ex(const uint8_t *bgrx, size_t in_pitch, int in_format, 
     init_tables(&mx, tab);
 
     for (int y = row0; y < row1; y += 2) {
+        /* do_unpack_lines clamps the line index: below an odd frame's last line comes that line again */
+        const int y1 = (y + 1 < h) ? y + 1 : y;
         unpack_line(bgrx + (size_t)y * in_pitch, l0, w, in_format);
-        unpack_line(bgrx + (size_t)(y + 1) * in_pitch, l1, w, in_format);
+        unpack_line(bgrx + (size_t)y1 * in_pitch, l1, w, in_format);
         matrix8_table(tab, l0, w);
         matrix8_table(tab, l1, w);
         pack_y(l0, planes[0] + (size_t)y * pitches[0], w);
-        pack_y(l1, planes[0] + (size_t)(y + 1) * pitches[0], w);
+        if (y1 != y)
+            pack_y(l1, planes[0] + (size_t)y1 * pitches[0], w);
         chroma_down_v2(l0, l1, w, site);
         if (format == ORC_FMT_NV12)
             pack_uv_interleaved(l0, planes[1] + (size_t)(y / 2) * pitches[1], w);
@@ -285,13 +289,14 @@ int orc_convert_mt_ex(const uint8_t *bgrx, size_t in_pitch, int in_format, int w
     pthread_t th[64];
     int started[64];
     band_job jobs[64];
-    int pairs = h / 2, rc = 0;
+    int pairs = (h + 1) / 2, rc = 0;
     for (int t = 0; t < n_threads; t++) {
         band_job *j = &jobs[t];
         j->bgrx = bgrx; j->in_pitch = in_pitch; j->in_format = in_format; j->w = w; j->h = h; j->format = format;
         j->matrix = matrix; j->range = range; j->site = site; j->planes = planes; j->pitches = pitches;
         j->row0 = 2 * (int)((long)pairs * t / n_threads);
         j->row1 = 2 * (int)((long)pairs * (t + 1) / n_threads);
+        if (j->row1 > h) j->row1 = h;
         j->rc = 0;
         started[t] = (pthread_create(&th[t], NULL, band_main, j) == 0);
         if (!started[t])

@@ -38,18 +38,27 @@ def yuv444(frame: np.ndarray, matrix: int, rng: int, in_format: int = 0):
 
 
 def chroma_down(c: np.ndarray, site: int) -> np.ndarray:
-    """(h,w) 4:4:4 chroma -> (h/2,w/2): horizontal (rounded) on each line, then vertical (rounded)."""
+    """(h,w) 4:4:4 chroma -> (ceil(h/2),ceil(w/2)): horizontal (rounded) on each line, then vertical
+    (rounded). Odd widths: the last pixel is a site of its own; odd heights: the last line pairs with
+    itself."""
     h, w = c.shape
     c = c.astype(np.int32)
-    if site == 0:  # NONE / JPEG: h2
-        hz = (c[:, 0::2] + c[:, 1::2] + 1) >> 1
+    n = (w + 1) // 2
+    hz = np.empty((h, n), np.int32)
+    if site == 0:  # NONE / JPEG: h2 on full pairs, an unpaired last pixel stays as it is
+        hz[:, : w // 2] = (c[:, 0 : 2 * (w // 2) : 2] + c[:, 1 : 2 * (w // 2) : 2] + 1) >> 1
+        if w & 1:
+            hz[:, n - 1] = c[:, w - 1]
     else:  # H_COSITED: h2_cs
-        hz = np.empty((h, w // 2), np.int32)
         hz[:, 0] = (3 * c[:, 0] + c[:, 1] + 2) >> 2
-        if w >= 4:
-            mid = np.arange(2, w - 2, 2)
-            hz[:, 1 : w // 2 - 1] = (c[:, mid - 1] + 2 * c[:, mid] + c[:, mid + 1] + 2) >> 2
-            hz[:, w // 2 - 1] = (c[:, w - 3] + 3 * c[:, w - 2] + 2) >> 2
+        i = 2
+        while i < w - 2:
+            hz[:, i // 2] = (c[:, i - 1] + 2 * c[:, i] + c[:, i + 1] + 2) >> 2
+            i += 2
+        if i < w:
+            hz[:, i // 2] = (c[:, i - 1] + 3 * c[:, i] + 2) >> 2
+    if h & 1:
+        hz = np.concatenate([hz, hz[-1:]], axis=0)
     return ((hz[0::2] + hz[1::2] + 1) >> 1).astype(np.uint8)
 
 

@@ -141,8 +141,8 @@ static int convert_scale_impl(const uint8_t *bgrx, size_t in_pitch, int in_forma
 {
     if (in_w == out_w && in_h == out_h)
         return orc_convert_mt_ex(bgrx, in_pitch, in_format, in_w, in_h, format, matrix, range, site, planes, pitches, n_threads);
-    if ((out_w & 1) || (out_h & 1) || out_w < 2 || out_h < 2)
-        return -1;
+    if (((in_w | in_h | out_w | out_h) & 1) || out_w < 2 || out_h < 2)
+        return -1;            /* scaling is restated for even sizes only */
 
     /* stage 1: videoconvert at input size into a default-layout intermediate frame */
     size_t off[3], pit[3];

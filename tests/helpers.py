@@ -6,10 +6,10 @@ def plane_views(buf, off, pit, fmt, w, h):
     """Return the output planes of a frame buffer as 2-D views: [Y, U, V] or [Y, UV]."""
     y = np.ndarray((h, w), np.uint8, buffer=buf, offset=off[0], strides=(pit[0], 1))
     if fmt == 1:
-        uv = np.ndarray((h // 2, w), np.uint8, buffer=buf, offset=off[1], strides=(pit[1], 1))
+        uv = np.ndarray(((h + 1) // 2, 2 * ((w + 1) // 2)), np.uint8, buffer=buf, offset=off[1], strides=(pit[1], 1))
         return [y, uv]
-    u = np.ndarray((h // 2, w // 2), np.uint8, buffer=buf, offset=off[1], strides=(pit[1], 1))
-    v = np.ndarray((h // 2, w // 2), np.uint8, buffer=buf, offset=off[2], strides=(pit[2], 1))
+    u = np.ndarray(((h + 1) // 2, (w + 1) // 2), np.uint8, buffer=buf, offset=off[1], strides=(pit[1], 1))
+    v = np.ndarray(((h + 1) // 2, (w + 1) // 2), np.uint8, buffer=buf, offset=off[2], strides=(pit[2], 1))
     return [y, u, v]
 
 

@@ -282,7 +282,7 @@ def test_errors_at_run_time(conv):
     with pytest.raises(b200vc.B200vcError):           # pitch smaller than a row
         conv.transform_frame(np.zeros((32, 64, 4), np.uint8), pitches=[32, 32, 32])
     with pytest.raises(b200vc.B200vcError) as e:      # caps the element does not offer
-        conv.set_info(63, 32)
+        conv.set_info(63, 32, 32, 16)
     assert e.value.status == b200vc.ERR_UNSUPPORTED
 
 
@@ -308,3 +308,23 @@ def test_input_formats_on_gpu(conv, orc, inf):
         buf, off, pit = conv.transform_frame(f)
         want = orc.convert(f, 0, 1, 0, 1, in_format=inf, out_size=(640, 360))
         assert_planes_equal(plane_views(buf, off, pit, 0, 640, 360), plane_views(*want, 0, 640, 360), f"in{inf} scaled {flags}")
+
+
+@pytest.mark.parametrize("size", [(3, 3), (5, 2), (2, 5), (7, 9), (131, 35), (1365, 767), (1919, 1079), (129, 17), (127, 15)])
+def test_odd_sizes(conv, orc, size):
+    """Odd widths and heights (unscaled path): the last pixel / last line is a chroma site of its own."""
+    w, h = size
+    f = orc.synth("rand", w, h, 31)
+    g = f.copy()
+    g[h - 1, w - 1, 1] ^= 2
+    for fmt in (0, 1):
+        for m, rg, site in [(0, 0, 0), (1, 0, 1), (1, 1, 1), (0, 1, 0)]:
+            conv.set_info(w, h, out_format=fmt, matrix=m, range_=rg, chroma_site=site, flags=b200vc.FLAG_DAMAGE_MAP)
+            buf, off, pit, dm = conv.transform_frame(f, damage=True)
+            assert_planes_equal(plane_views(buf, off, pit, fmt, w, h), _oracle_planes(orc, f, fmt, m, rg, site),
+                                f"{size} fmt{fmt} m{m} r{rg} s{site}")
+            dm = conv.transform_frame(g, damage=True)[3]
+            assert np.array_equal(dm, orc.damage_map(g, f)) and dm.sum() == 1
+    with pytest.raises(b200vc.B200vcError) as e:      # scaling stays even-only
+        conv.set_info(w | 1, h | 1, 64, 36)
+    assert e.value.status == b200vc.ERR_UNSUPPORTED

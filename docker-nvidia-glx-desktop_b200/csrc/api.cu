@@ -529,7 +529,7 @@ int create_impl(b200vc_ctx *c)
             c->mid_pitch[0] = yp;  c->mid_pitch[1] = cp;  c->mid_pitch[2] = cp;
             c->mid_off[0] = 0;  c->mid_off[1] = yp * g.in_h;  c->mid_off[2] = c->mid_off[1] + cp * (g.in_h / 2);
             c->mid_size = ru(c->mid_off[2] + cp * (g.in_h / 2), 256);
-            c->mid_frames = std::max(1, std::min(g.max_sessions, 8));
+            c->mid_frames = std::max(1, std::min(g.max_sessions, 8));   // measured: groups of 8 beat groups of 2
             CU_TRY(c, cudaMalloc(&c->d_mid, c->mid_size * c->mid_frames));
         }
     }

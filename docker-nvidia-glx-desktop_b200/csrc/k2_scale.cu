@@ -332,57 +332,87 @@ k2_fused_2x_kernel(const __grid_constant__ CUtensorMap src_map, const Fused2xPar
 }
 
 // ---- two-pass, pass 2: scale the planes of a full-size intermediate I420 -----------------------
-template <int FMT>
-__global__ void __launch_bounds__(256) k2_plane_scale_kernel(const PlaneScaleParams p)
+// The intermediate was written by K1 a moment ago and is read out of L2. A thread owns four
+// consecutive output samples of one line of one plane; the two source lines ride in the two 16-bit
+// lanes of a word, so one multiply-add pair applies the horizontal tap to both.
+__device__ __forceinline__ uint32_t scale4(const uint8_t *r0, const uint8_t *r1, const uint4 th4, int p1, int box)
 {
-    const int tx = blockIdx.x * 64 + (threadIdx.x & 63);
-    const int ry = blockIdx.y * 4 + (threadIdx.x >> 6);
-    const int frame = blockIdx.z;
-    const long long fi = (long long)frame * p.src_frame_stride;
-    const long long fo = (long long)frame * p.out.frame_stride;
-    const int x = tx * 4;
+    const Tap th[4] = { th4.x, th4.y, th4.z, th4.w };
+    uint32_t out = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int j0 = tap_idx(th[k]), j1 = j0 + tap_step(th[k]);
+        const uint32_t f = (uint32_t)tap_frac(th[k]);
+        const uint32_t w0 = (uint32_t)__ldg(r0 + j0) | ((uint32_t)__ldg(r1 + j0) << 16);
+        const uint32_t w1 = (uint32_t)__ldg(r0 + j1) | ((uint32_t)__ldg(r1 + j1) << 16);
+        int d;
+        if (box) {
+            const uint32_t q = w0 + w1;
+            d = (int)(((q & 0xffffu) + (q >> 16) + 2u) >> 2);
+        } else {
+            const uint32_t h = w0 * (256u - f) + w1 * f;   // per lane < 65536; its high byte is the scaled pixel
+            d = lerp_v((int)((h >> 8) & 0xffu), (int)(h >> 24), p1);
+        }
+        out |= (uint32_t)d << (8 * k);
+    }
+    return out;
+}
 
-    if (ry < p.out_h) {                                    // luma row
+template <int FMT>
+__global__ void __launch_bounds__(128) k2_plane_scale_kernel(const PlaneScaleParams p)
+{
+    const int x = (blockIdx.x * 128 + threadIdx.x) * 4;
+    const int row = blockIdx.y;
+    const long long fi = (long long)blockIdx.z * p.src_frame_stride;
+    const long long fo = (long long)blockIdx.z * p.out.frame_stride;
+    const int ch = p.out_h >> 1, cw = p.out_w >> 1;
+
+    if (row < p.out_h) {                                   // luma line
         if (x >= p.out_w) return;
-        const Tap tv = p.tab.vy[ry];
-        const uint8_t *row0 = p.src[0] + fi + (long long)tap_idx(tv) * p.src_pitch[0];
-        const uint8_t *row1 = row0 + (long long)tap_step(tv) * p.src_pitch[0];
-        const int p1 = tap_frac(tv);
-        uint8_t *dst = p.out.p[0] + fo + (long long)ry * p.out.pitch[0] + x;
-        for (int k = 0; k < 4 && x + k < p.out_w; k++) {
-            const Tap th = p.tab.hy[x + k];
-            const int j0 = tap_idx(th), j1 = j0 + tap_step(th), f = tap_frac(th);
-            int d;
-            if (p.box2x2)
-                d = (__ldg(row0 + j0) + __ldg(row0 + j0 + 1) + __ldg(row1 + j0) + __ldg(row1 + j0 + 1) + 2) >> 2;
-            else
-                d = lerp_v(lerp_h(__ldg(row0 + j0), __ldg(row0 + j1), f),
-                           lerp_h(__ldg(row1 + j0), __ldg(row1 + j1), f), p1);
-            dst[k] = (uint8_t)d;
+        const Tap tv = p.tab.vy[row];
+        const uint8_t *r0 = p.src[0] + fi + (long long)tap_idx(tv) * p.src_pitch[0];
+        const uint8_t *r1 = r0 + (long long)tap_step(tv) * p.src_pitch[0];
+        const uint32_t out = scale4(r0, r1, *reinterpret_cast<const uint4 *>(p.tab.hy + x), tap_frac(tv), p.box2x2);
+        uint8_t *dst = p.out.p[0] + fo + (long long)row * p.out.pitch[0] + x;
+        if (x + 4 <= p.out_w) {
+            *reinterpret_cast<uint32_t *>(dst) = out;
+        } else {
+            for (int k = 0; k < p.out_w - x; k++) dst[k] = (uint8_t)(out >> (8 * k));
         }
         return;
     }
-    const int cy = ry - p.out_h;                           // chroma row
-    if (cy >= (p.out_h >> 1) || x >= (p.out_w >> 1)) return;
-    const Tap tv = p.tab.vc[cy];
-    const int p1 = tap_frac(tv);
+    if (FMT == 0) {                                        // I420: lines of U, then lines of V
+        const int pl = row < p.out_h + ch ? 1 : 2, cy = row - p.out_h - (pl - 1) * ch;
+        if (cy >= ch || x >= cw) return;
+        const Tap tv = p.tab.vc[cy];
+        const uint8_t *r0 = p.src[pl] + fi + (long long)tap_idx(tv) * p.src_pitch[pl];
+        const uint8_t *r1 = r0 + (long long)tap_step(tv) * p.src_pitch[pl];
+        const uint32_t out = scale4(r0, r1, *reinterpret_cast<const uint4 *>(p.tab.hc + x), tap_frac(tv), p.box2x2);
+        uint8_t *dst = p.out.p[pl] + fo + (long long)cy * p.out.pitch[pl] + x;
+        if (x + 4 <= cw) {
+            *reinterpret_cast<uint32_t *>(dst) = out;
+        } else {
+            for (int k = 0; k < cw - x; k++) dst[k] = (uint8_t)(out >> (8 * k));
+        }
+    } else {                                               // NV12: U and V of four samples, interleaved
+        const int cy = row - p.out_h;
+        if (cy >= ch || x >= cw) return;
+        const Tap tv = p.tab.vc[cy];
+        const uint4 th4 = *reinterpret_cast<const uint4 *>(p.tab.hc + x);
+        uint32_t o[2];
 #pragma unroll
-    for (int pl = 1; pl <= 2; pl++) {
-        const uint8_t *row0 = p.src[pl] + fi + (long long)tap_idx(tv) * p.src_pitch[pl];
-        const uint8_t *row1 = row0 + (long long)tap_step(tv) * p.src_pitch[pl];
-        for (int k = 0; k < 4 && x + k < (p.out_w >> 1); k++) {
-            const Tap th = p.tab.hc[x + k];
-            const int j0 = tap_idx(th), j1 = j0 + tap_step(th), f = tap_frac(th);
-            int d;
-            if (p.box2x2)
-                d = (__ldg(row0 + j0) + __ldg(row0 + j0 + 1) + __ldg(row1 + j0) + __ldg(row1 + j0 + 1) + 2) >> 2;
-            else
-                d = lerp_v(lerp_h(__ldg(row0 + j0), __ldg(row0 + j1), f),
-                           lerp_h(__ldg(row1 + j0), __ldg(row1 + j1), f), p1);
-            if (FMT == 0)
-                p.out.p[pl][fo + (long long)cy * p.out.pitch[pl] + x + k] = (uint8_t)d;
-            else
-                p.out.p[1][fo + (long long)cy * p.out.pitch[1] + 2 * (x + k) + (pl - 1)] = (uint8_t)d;
+        for (int pl = 1; pl <= 2; pl++) {
+            const uint8_t *r0 = p.src[pl] + fi + (long long)tap_idx(tv) * p.src_pitch[pl];
+            const uint8_t *r1 = r0 + (long long)tap_step(tv) * p.src_pitch[pl];
+            o[pl - 1] = scale4(r0, r1, th4, tap_frac(tv), p.box2x2);
+        }
+        const uint32_t lo = prmt(o[0], o[1], 0x5140), hi = prmt(o[0], o[1], 0x7362);   // u0 v0 u1 v1 | u2 v2 u3 v3
+        uint8_t *dst = p.out.p[1] + fo + (long long)cy * p.out.pitch[1] + 2 * x;
+        if (x + 4 <= cw) {
+            *reinterpret_cast<uint2 *>(dst) = make_uint2(lo, hi);
+        } else {
+            const unsigned long long both = (unsigned long long)lo | ((unsigned long long)hi << 32);
+            for (int k = 0; k < 2 * (cw - x); k++) dst[k] = (uint8_t)(both >> (8 * k));
         }
     }
 }
@@ -468,12 +498,13 @@ cudaError_t launch_plane_scale(const PlaneScaleParams &p, int fmt, cudaStream_t 
 {
     if (p.out_w <= 0 || p.out_h <= 0 || p.n_frames <= 0)
         return cudaErrorInvalidValue;
-    const int rows = p.out_h + (p.out_h >> 1);
-    dim3 grid(((p.out_w + 3) / 4 + 63) / 64, (rows + 3) / 4, p.n_frames);
+    // one block row per output line: luma lines, then chroma lines (I420: U lines then V lines)
+    const int rows = p.out_h + (fmt == 0 ? 2 : 1) * (p.out_h >> 1);
+    dim3 grid(((p.out_w + 3) / 4 + 127) / 128, rows, p.n_frames);
     if (fmt == 0)
-        k2_plane_scale_kernel<0><<<grid, 256, 0, st>>>(p);
+        k2_plane_scale_kernel<0><<<grid, 128, 0, st>>>(p);
     else
-        k2_plane_scale_kernel<1><<<grid, 256, 0, st>>>(p);
+        k2_plane_scale_kernel<1><<<grid, 128, 0, st>>>(p);
     return cudaGetLastError();
 }
 

@@ -12,6 +12,10 @@ for p in (ROOT, PKG):
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a real B200 (run with -m gpu through gpurun)")
+    # the built libraries are not in git: a fresh checkout builds them before the first test
+    if not os.path.exists(os.path.join(PKG, "libb200vc.so")):
+        import __graft_entry__
+        __graft_entry__.build()
 
 
 @pytest.fixture(scope="session")

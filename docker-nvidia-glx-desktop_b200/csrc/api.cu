@@ -272,15 +272,20 @@ int check_config(const b200vc_config *c, std::string *why)
     return B200VC_OK;
 }
 
-bool is_pinned(const void *p)
+// 1 = page-locked host memory (cudaMallocHost / cudaHostRegister), 0 = pageable host memory,
+// -1 = device or managed memory (belongs to b200vc_convert_device, not to the host entry points)
+int host_kind(const void *p)
 {
     cudaPointerAttributes a;
     if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
         cudaGetLastError();
-        return false;
+        return 0;
     }
-    return a.type == cudaMemoryTypeHost;
+    if (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) return -1;
+    return a.type == cudaMemoryTypeHost ? 1 : 0;
 }
+
+bool is_pinned(const void *p) { return host_kind(p) == 1; }
 
 int collect_slot(b200vc_ctx *c, Slot &s);
 
@@ -582,6 +587,9 @@ int submit_locked(b200vc_ctx *c, const b200vc_frame *f, int bands, uint64_t *tic
     const int out_rows[3] = { g.out_h, (g.out_h + 1) / 2, (g.out_h + 1) / 2 };
 
     // where do the host sides live?
+    if (host_kind(f->bgrx) < 0 || host_kind(f->planes[0]) < 0)
+        return fail(c, B200VC_ERR_INVALID_ARG, "a device pointer was passed to a host-buffer entry point; "
+                                               "frames already on the GPU go through b200vc_convert_device");
     bool in_pinned = is_pinned(f->bgrx);
     if (!in_pinned && (g.flags & B200VC_FLAG_REGISTER_HOST))
         in_pinned = ensure_registered(c, f->bgrx, f->in_pitch * (g.in_h - 1) + row_bytes);

@@ -109,3 +109,39 @@ def test_context_survives_a_refused_call(orc):
     buf, off, pit = conv.transform_frame(f)               # still works
     assert_planes_equal(plane_views(buf, off, pit, 0, 320, 180), plane_views(*orc.convert(f, 0, 0, 0, 0), 0, 320, 180))
     conv.stop()
+
+
+def test_device_pointer_on_the_host_entry_point_is_refused():
+    import torch
+    conv = b200vc.Converter(0)
+    conv.set_info(64, 32)
+    d = torch.zeros(64 * 32 * 4, dtype=torch.uint8, device="cuda")
+    total, off, pit = b200vc.default_layout(0, 64, 32)
+    out = np.zeros(total, np.uint8)
+    planes = (C.c_void_p * 3)(*[out.ctypes.data + o for o in off])
+    pits = (C.c_size_t * 3)(*pit)
+    assert conv.lib.b200vc_convert(conv.ctx, d.data_ptr(), 256, planes, pits, None) == b200vc.ERR_INVALID_ARG
+    assert b"b200vc_convert_device" in conv.lib.b200vc_last_error(conv.ctx)
+    conv.stop()
+
+
+def test_8k_frame(orc):
+    """7680x4320 (133 MB in): offsets beyond 2^27 bytes, 480 x 270 macroblocks."""
+    w, h = 7680, 4320
+    f = orc.synth("rand", w, h, 2)
+    conv = b200vc.Converter(0)
+    conv.set_info(w, h, out_format=1, matrix=1, range_=0, chroma_site=1, flags=b200vc.FLAG_DAMAGE_MAP)
+    buf, off, pit, dm = conv.transform_frame(f, damage=True)
+    want = orc.convert(f, 1, 1, 0, 1, threads=8)
+    assert_planes_equal(plane_views(buf, off, pit, 1, w, h), plane_views(*want, 1, w, h), "8K NV12")
+    g = f.copy()
+    g[h - 1, w - 1, 0] ^= 1
+    g[0, 0, 2] ^= 1
+    dm = conv.transform_frame(g, damage=True)[3]
+    assert dm.shape == (270, 480) and dm.sum() == 2 and dm[0, 0] == 1 and dm[269, 479] == 1
+    conv.set_info(w, h, w // 2, h // 2, matrix=1, range_=0, chroma_site=1)
+    assert conv.info().fused_2to1 == 1
+    buf, off, pit = conv.transform_frame(f)
+    want = orc.convert(f, 0, 1, 0, 1, out_size=(w // 2, h // 2), threads=8)
+    assert_planes_equal(plane_views(buf, off, pit, 0, w // 2, h // 2), plane_views(*want, 0, w // 2, h // 2), "8K -> 4K")
+    conv.stop()

@@ -109,6 +109,7 @@ int fail(b200vc_ctx *c, int code, const char *fmt, ...)
     } while (0)
 
 size_t ru(size_t v, size_t a) { return (v + a - 1) / a * a; }
+bool aligned16(const void *p) { return ((uintptr_t)p & 15) == 0; }
 
 // SURVEY A.2 table; rows Y,U,V of (cR, cG, cB, off). The oracle derives the same numbers from
 // Kr/Kb in double precision; tests compare the two.
@@ -604,6 +605,30 @@ int submit_locked(b200vc_ctx *c, const b200vc_frame *f, int bands, uint64_t *tic
     if (!in_pinned && !slot.h_in) CU_TRY(c, cudaMallocHost(&slot.h_in, c->d_in_size));
     if (!out_pinned && !slot.h_out) CU_TRY(c, cudaMallocHost(&slot.h_out, c->d_out_size + ru((size_t)c->mb_w * c->mb_h, 256)));
 
+    // zero-copy: K1 reads the page-locked frame over PCIe and writes the planes back itself
+    if ((g.flags & B200VC_FLAG_ZERO_COPY) && c->path == 0 && !f->damage && in_pinned && out_pinned) {
+        void *d_src = nullptr, *d_pl[3] = { nullptr, nullptr, nullptr };
+        bool ok = cudaHostGetDevicePointer(&d_src, const_cast<void *>(f->bgrx), 0) == cudaSuccess;
+        for (int i = 0; i < n_planes && ok; i++) ok = cudaHostGetDevicePointer(&d_pl[i], f->planes[i], 0) == cudaSuccess;
+        if (!ok) cudaGetLastError();
+        ok = ok && aligned16(d_src) && f->in_pitch % 16 == 0;
+        for (int i = 0; i < n_planes; i++) ok = ok && aligned16(d_pl[i]) && f->pitches[i] % 16 == 0;
+        if (ok) {
+            PlaneSet zout;
+            for (int i = 0; i < 3; i++) { zout.p[i] = (uint8_t *)d_pl[i];  zout.pitch[i] = i < n_planes ? (long long)f->pitches[i] : 0; }
+            zout.frame_stride = 0;
+            rc = enqueue_kernels(c, (const uint8_t *)d_src, f->in_pitch, 0, nullptr, 0, 0, zout, nullptr, 0, 0, g.in_h, 1, c->s_k);
+            if (rc) return rc;
+            CU_TRY(c, cudaEventRecord(slot.done, c->s_k));
+            c->stats.h2d_bytes += row_bytes * g.in_h;
+            for (int i = 0; i < n_planes; i++) c->stats.d2h_bytes += out_row_bytes[i] * out_rows[i];
+            slot.busy = true;  slot.staged_out = false;  slot.frame = *f;  slot.ticket = c->next_ticket++;
+            if (ticket) *ticket = slot.ticket;
+            c->stats.frames += 1;
+            return B200VC_OK;
+        }
+    }
+
     if (c->path != 0 || bands < 1) bands = 1;
     bands = std::min(bands, (int)c->ev_band_h2d.size());
     bands = std::min(bands, std::max(1, c->mb_h));
@@ -710,8 +735,6 @@ int collect_slot(b200vc_ctx *c, Slot &s)
     }
     return B200VC_OK;
 }
-
-bool aligned16(const void *p) { return ((uintptr_t)p & 15) == 0; }
 
 }  // namespace
 

@@ -64,6 +64,10 @@ enum { B200VC_IN_BGRX = 0, B200VC_IN_RGBX = 1, B200VC_IN_XRGB = 2, B200VC_IN_XBG
                                              kernel                                               */
 #define B200VC_FLAG_FORCE_GENERIC_FUSED 0x8u /* scaling: never the exact-2:1 kernel, always the
                                              general fused kernel (any ratio that fits a tile)    */
+#define B200VC_FLAG_ZERO_COPY       0x10u /* unscaled path, page-locked buffers, no damage map: the
+                                             kernel reads the frame from host memory and writes the
+                                             planes to host memory itself (one launch, no copy
+                                             engine, both PCIe directions busy at once)           */
 #define B200VC_FLAG_REGISTER_HOST   0x4u  /* page-lock caller buffers on first sight (XShm pool)
                                              instead of staging them through a pinned ring        */
 

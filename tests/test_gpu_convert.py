@@ -328,3 +328,25 @@ def test_odd_sizes(conv, orc, size):
     with pytest.raises(b200vc.B200vcError) as e:      # scaling stays even-only
         conv.set_info(w | 1, h | 1, 64, 36)
     assert e.value.status == b200vc.ERR_UNSUPPORTED
+
+
+def test_zero_copy_mode(conv, orc):
+    """B200VC_FLAG_ZERO_COPY: the kernel reads the page-locked frame and writes the planes itself."""
+    w, h = 1920, 1080
+    total, off, pit = b200vc.default_layout(1, w, h)
+    pin_in, pin_out = b200vc.PinnedBuffer(w * h * 4), b200vc.PinnedBuffer(total)
+    f = orc.synth("desk", w, h, 5, out=pin_in.array.reshape(h, w * 4))
+    conv.set_info(w, h, out_format=1, matrix=1, range_=0, chroma_site=1, flags=b200vc.FLAG_ZERO_COPY)
+    pin_out.array[:] = 0
+    buf, off, pit = conv.transform_frame(f, out=pin_out.array)
+    want = _oracle_planes(orc, f, 1, 1, 0, 1)
+    assert_planes_equal(plane_views(buf, off, pit, 1, w, h), want, "zero-copy")
+    st = conv.stats()
+    assert st.kernel_launches == 1 and st.h2d_bytes == w * h * 4 and st.d2h_bytes == total
+    # pageable buffers cannot be read by the kernel: the call falls back to the copy pipeline
+    buf, off, pit = conv.transform_frame(np.array(f))
+    assert_planes_equal(plane_views(buf, off, pit, 1, w, h), want, "zero-copy flag, pageable buffers")
+    assert conv.stats().staged_in_bytes == w * h * 4
+    conv.stop()
+    pin_in.free()
+    pin_out.free()

@@ -247,9 +247,9 @@ int check_config(const b200vc_config *c, std::string *why)
         return bad(B200VC_ERR_INVALID_ARG, "width/height must be >= 2");
     if (c->in_w > 16384 || c->in_h > 16384 || c->out_w > 16384 || c->out_h > 16384)
         return bad(B200VC_ERR_UNSUPPORTED, "width/height above 16384");
-    const bool scaling_req = c->in_w != c->out_w || c->in_h != c->out_h;
-    if (scaling_req && ((c->in_w | c->in_h | c->out_w | c->out_h) & 1))
-        return bad(B200VC_ERR_UNSUPPORTED, "scaling is negotiated for even widths and heights only");
+    if (c->scale_mode == B200VC_SCALE_BOX_2X2 && ((c->in_w | c->in_h | c->out_w | c->out_h) & 1) &&
+        (c->in_w != c->out_w || c->in_h != c->out_h))
+        return bad(B200VC_ERR_UNSUPPORTED, "BOX_2X2 needs even widths and heights");
     if (c->out_format != B200VC_FMT_I420 && c->out_format != B200VC_FMT_NV12)
         return bad(B200VC_ERR_UNSUPPORTED, "output format must be I420 or NV12");
     if (c->in_format < B200VC_IN_BGRX || c->in_format > B200VC_IN_XBGR)
@@ -492,10 +492,11 @@ int create_impl(b200vc_ctx *c)
         std::vector<Tap> hy, vy, hc, vc;
         if (g.scale_mode == B200VC_SCALE_BOX_2X2) {
             build_box_taps(g.out_w, hy);  build_box_taps(g.out_h, vy);
-            build_box_taps(g.out_w / 2, hc);  build_box_taps(g.out_h / 2, vc);
+            build_box_taps(g.out_w / 2, hc);  build_box_taps(g.out_h / 2, vc);   // BOX: even sizes only
         } else {
             build_h_taps(g.in_w, g.out_w, hy);  build_v_taps(g.in_h, g.out_h, vy);
-            build_h_taps(g.in_w / 2, g.out_w / 2, hc);  build_v_taps(g.in_h / 2, g.out_h / 2, vc);
+            // chroma planes of odd frames round up, like the intermediate frame's own layout
+            build_h_taps((g.in_w + 1) / 2, (g.out_w + 1) / 2, hc);  build_v_taps((g.in_h + 1) / 2, (g.out_h + 1) / 2, vc);
         }
         const size_t n = hy.size() + vy.size() + hc.size() + vc.size();
         CU_TRY(c, cudaMalloc(&c->d_taps, n * sizeof(Tap)));
@@ -509,7 +510,8 @@ int create_impl(b200vc_ctx *c)
         c->smem_bytes = fused_scale_smem_bytes(c->box_w, c->box_h);
         const bool fits = c->box_w <= 256 && c->box_h <= 256 &&
                           c->smem_bytes + 1024 <= (size_t)c->prop.sharedMemPerBlockOptin;
-        c->path = (fits && !(g.flags & B200VC_FLAG_FORCE_TWO_PASS)) ? 1 : 2;
+        const bool all_even = !((g.in_w | g.in_h | g.out_w | g.out_h) & 1);      // the fused kernels assume it
+        c->path = (fits && all_even && !(g.flags & B200VC_FLAG_FORCE_TWO_PASS)) ? 1 : 2;
         const bool exact2 = g.in_w == 2 * g.out_w && g.in_h == 2 * g.out_h && (g.in_w % 4) == 0 && (g.in_h % 4) == 0;
         c->fused2x = c->path == 1 && exact2 && !(g.flags & B200VC_FLAG_FORCE_GENERIC_FUSED) &&
                      (g.scale_mode == B200VC_SCALE_BOX_2X2 ||
@@ -531,10 +533,10 @@ int create_impl(b200vc_ctx *c)
             c->encode_tiled = (PFN_cuTensorMapEncodeTiled_v12000)fn;
             if (!c->fused2x) CU_TRY(c, fused_scale_prepare(c->smem_bytes));
         } else {
-            const size_t yp = ru(g.in_w, 256), cp = ru(g.in_w / 2, 256);
+            const size_t yp = ru(g.in_w + 1, 256), cp = ru((g.in_w + 1) / 2, 256), mch = (size_t)(g.in_h + 1) / 2;
             c->mid_pitch[0] = yp;  c->mid_pitch[1] = cp;  c->mid_pitch[2] = cp;
-            c->mid_off[0] = 0;  c->mid_off[1] = yp * g.in_h;  c->mid_off[2] = c->mid_off[1] + cp * (g.in_h / 2);
-            c->mid_size = ru(c->mid_off[2] + cp * (g.in_h / 2), 256);
+            c->mid_off[0] = 0;  c->mid_off[1] = yp * g.in_h;  c->mid_off[2] = c->mid_off[1] + cp * mch;
+            c->mid_size = ru(c->mid_off[2] + cp * mch, 256);
             c->mid_frames = std::max(1, std::min(g.max_sessions, 8));   // measured: groups of 8 beat groups of 2
             CU_TRY(c, cudaMalloc(&c->d_mid, c->mid_size * c->mid_frames));
         }

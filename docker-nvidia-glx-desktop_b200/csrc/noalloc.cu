@@ -187,6 +187,8 @@ extern "C" int b200vc_convert_scale_device_static(const b200vc_config *cfg, cons
                       "no scaling requested: the unscaled path needs no scratch, use b200vc_convert_device");
     if (cfg->flags & B200VC_FLAG_DAMAGE_MAP)
         return report(errbuf, errbuf_len, B200VC_ERR_UNSUPPORTED, "the damage map is produced on the unscaled path only");
+    if ((cfg->in_w | cfg->in_h | cfg->out_w | cfg->out_h) & 1)
+        return report(errbuf, errbuf_len, B200VC_ERR_UNSUPPORTED, "this entry point scales even widths and heights only");
 
     // intermediate I420 at the source size, rows padded to 16 bytes for K1's vector stores
     const size_t yp = ((size_t)cfg->in_w + 15) / 16 * 16, cp = ((size_t)cfg->in_w / 2 + 15) / 16 * 16;

@@ -109,11 +109,12 @@ def convert_scale(frame, out_w, out_h, fmt, matrix, rng, site, mode=0, in_format
     if out_w == frame.shape[1] and out_h == frame.shape[0]:
         return planes
     out = [scale_plane(planes[0], out_w, out_h, 1, mode)]
+    ocw, och = (out_w + 1) // 2, (out_h + 1) // 2      # chroma planes of odd frames round up
     if fmt == 1:
-        out.append(scale_plane(planes[1], out_w // 2, out_h // 2, 2, mode))
+        out.append(scale_plane(planes[1], ocw, och, 2, mode))
     else:
-        out.append(scale_plane(planes[1], out_w // 2, out_h // 2, 1, mode))
-        out.append(scale_plane(planes[2], out_w // 2, out_h // 2, 1, mode))
+        out.append(scale_plane(planes[1], ocw, och, 1, mode))
+        out.append(scale_plane(planes[2], ocw, och, 1, mode))
     return tuple(out)
 
 

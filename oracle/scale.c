@@ -141,8 +141,12 @@ static int convert_scale_impl(const uint8_t *bgrx, size_t in_pitch, int in_forma
 {
     if (in_w == out_w && in_h == out_h)
         return orc_convert_mt_ex(bgrx, in_pitch, in_format, in_w, in_h, format, matrix, range, site, planes, pitches, n_threads);
-    if (((in_w | in_h | out_w | out_h) & 1) || out_w < 2 || out_h < 2)
-        return -1;            /* scaling is restated for even sizes only */
+    if (out_w < 2 || out_h < 2)
+        return -1;
+    if (scale_mode == ORC_SCALE_BOX_2X2 && ((in_w | in_h | out_w | out_h) & 1))
+        return -1;
+    /* odd sizes: the chroma planes of both frames round up (video-info.c), and are scaled as such */
+    const int icw = (in_w + 1) / 2, ich = (in_h + 1) / 2, ocw = (out_w + 1) / 2, och = (out_h + 1) / 2;
 
     /* stage 1: videoconvert at input size into a default-layout intermediate frame */
     size_t off[3], pit[3];
@@ -157,11 +161,11 @@ static int convert_scale_impl(const uint8_t *bgrx, size_t in_pitch, int in_forma
     if (!rc)
         rc = orc_scale_plane(tp[0], pit[0], in_w, in_h, planes[0], pitches[0], out_w, out_h, 1, scale_mode);
     if (!rc && format == ORC_FMT_NV12) {
-        rc = orc_scale_plane(tp[1], pit[1], in_w / 2, in_h / 2, planes[1], pitches[1], out_w / 2, out_h / 2, 2, scale_mode);
+        rc = orc_scale_plane(tp[1], pit[1], icw, ich, planes[1], pitches[1], ocw, och, 2, scale_mode);
     } else if (!rc) {
-        rc = orc_scale_plane(tp[1], pit[1], in_w / 2, in_h / 2, planes[1], pitches[1], out_w / 2, out_h / 2, 1, scale_mode);
+        rc = orc_scale_plane(tp[1], pit[1], icw, ich, planes[1], pitches[1], ocw, och, 1, scale_mode);
         if (!rc)
-            rc = orc_scale_plane(tp[2], pit[2], in_w / 2, in_h / 2, planes[2], pitches[2], out_w / 2, out_h / 2, 1, scale_mode);
+            rc = orc_scale_plane(tp[2], pit[2], icw, ich, planes[2], pitches[2], ocw, och, 1, scale_mode);
     }
     free(tmp);
     return rc;

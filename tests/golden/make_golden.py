@@ -29,6 +29,9 @@ CASES = [
     ("in_rgbx_709l_i420", 38, 20, 38, 20, 0, 1, 0, 1, 0, 1),
     ("in_xrgb_601f_nv12", 38, 20, 38, 20, 1, 0, 1, 0, 0, 2),
     ("in_xbgr_2to1_709l_i420", 64, 36, 32, 18, 0, 1, 0, 1, 0, 3),
+    ("odd_709l_i420_mpeg2", 37, 21, 37, 21, 0, 1, 0, 1, 0),
+    ("odd_601f_nv12_jpeg", 35, 19, 35, 19, 1, 0, 1, 0, 0),
+    ("odd_scale_709l_i420", 71, 39, 36, 21, 0, 1, 0, 1, 0),
 ]
 
 

@@ -67,10 +67,10 @@ def test_caps_acceptance(lib):
     ok = [_cfg(), _cfg(out_format=1, matrix=1, range=1, chroma_site=1, in_w=2560, in_h=1440, out_w=2560, out_h=1440),
           _cfg(in_w=3840, in_h=2160), _cfg(in_w=3840, in_h=2160, scale_mode=1), _cfg(flags=b200vc.FLAG_DAMAGE_MAP),
           _cfg(in_w=1366, in_h=768, out_w=1366, out_h=768), _cfg(max_sessions=8, n_inflight=4), _cfg(in_format=3),
-          _cfg(in_w=1365, in_h=767, out_w=1365, out_h=767)]
+          _cfg(in_w=1365, in_h=767, out_w=1365, out_h=767), _cfg(in_w=3841, in_h=2161)]
     for c in ok:
         assert lib.b200vc_check_config(C.byref(c)) == b200vc.OK
-    refused = [(_cfg(in_w=3841, in_h=2160), b200vc.ERR_UNSUPPORTED),       # odd width with scaling
+    refused = [(_cfg(in_w=3842, in_h=2162, out_w=1921, out_h=1081, scale_mode=1), b200vc.ERR_UNSUPPORTED),   # BOX, odd
                (_cfg(out_format=2), b200vc.ERR_UNSUPPORTED),               # not I420/NV12
                (_cfg(in_format=4), b200vc.ERR_UNSUPPORTED),                # not a 4-byte RGB order
                (_cfg(matrix=2), b200vc.ERR_UNSUPPORTED),                   # bt2020 not offered

@@ -282,7 +282,7 @@ def test_errors_at_run_time(conv):
     with pytest.raises(b200vc.B200vcError):           # pitch smaller than a row
         conv.transform_frame(np.zeros((32, 64, 4), np.uint8), pitches=[32, 32, 32])
     with pytest.raises(b200vc.B200vcError) as e:      # caps the element does not offer
-        conv.set_info(63, 32, 32, 16)
+        conv.set_info(64, 32, out_format=5)
     assert e.value.status == b200vc.ERR_UNSUPPORTED
 
 
@@ -325,8 +325,8 @@ def test_odd_sizes(conv, orc, size):
                                 f"{size} fmt{fmt} m{m} r{rg} s{site}")
             dm = conv.transform_frame(g, damage=True)[3]
             assert np.array_equal(dm, orc.damage_map(g, f)) and dm.sum() == 1
-    with pytest.raises(b200vc.B200vcError) as e:      # scaling stays even-only
-        conv.set_info(w | 1, h | 1, 64, 36)
+    with pytest.raises(b200vc.B200vcError) as e:      # the 2x2 box mean needs even sizes
+        conv.set_info(65, 37, 32, 18, scale_mode=1)
     assert e.value.status == b200vc.ERR_UNSUPPORTED
 
 

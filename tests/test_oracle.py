@@ -52,7 +52,7 @@ def test_known_answers_uniform_frames(orc, fmt, site):
 def test_golden_vectors(orc):
     z = np.load(GOLDEN)
     names = sorted({k.split("/")[0] for k in z.files if k.endswith("/cfg")})
-    assert len(names) >= 12
+    assert len(names) >= 15
     for name in names:
         iw, ih, ow, oh, fmt, mat, rg, site, mode, inf = [int(v) for v in z[name + "/cfg"]]
         frame = np.ascontiguousarray(z[name + "/in"])
@@ -102,7 +102,8 @@ def test_threads_and_pitch_do_not_change_results(orc):
 
 
 @pytest.mark.parametrize("geo", [(3840, 2160, 1920, 1080), (64, 32, 32, 16), (100, 60, 64, 36), (64, 48, 30, 22),
-                                 (32, 16, 64, 32), (1920, 1080, 1280, 720), (200, 120, 50, 30)])
+                                 (32, 16, 64, 32), (1920, 1080, 1280, 720), (200, 120, 50, 30), (7, 9, 4, 5),
+                                 (131, 35, 65, 17), (1365, 767, 683, 384)])
 def test_c_equals_numpy_scale(orc, geo):
     iw, ih, ow, oh = geo
     frame = orc.synth("rand", iw, ih, 5)
@@ -159,7 +160,7 @@ def test_synth_python_mirror(orc):
 
 def test_oracle_rejects_what_the_element_rejects(orc):
     with pytest.raises(ValueError):
-        orc.convert(np.zeros((4, 5, 4), np.uint8), out_size=(2, 2))     # odd width with scaling
+        orc.convert(np.zeros((4, 6, 4), np.uint8), out_size=(3, 2), scale_mode=1)     # BOX with an odd size
     with pytest.raises(ValueError):
         orc.convert(np.zeros((4, 8, 4), np.uint8), out_size=(2, 2), scale_mode=1)  # BOX needs 2:1
 

@@ -95,8 +95,8 @@ def test_static_scratch_limits_and_errors(lib):
     cfg = b200vc.Config(7, 640, 360, 320, 180, 0, 1, 0, 1, 0, 0, 0, 0, 0)
     rc, msg = _static(lib, cfg, _device_frames(d_in, d_out, 640, 360, 320, 180, 0, 1))
     assert rc == b200vc.ERR_INVALID_ARG and "current device" in msg
-    # caps the element does not offer
-    cfg = b200vc.Config(0, 641, 360, 320, 180, 0, 1, 0, 1, 0, 0, 0, 0, 0)   # odd width with scaling
+    # odd sizes are scaled by the context-based path only
+    cfg = b200vc.Config(0, 641, 360, 320, 180, 0, 1, 0, 1, 0, 0, 0, 0, 0)
     rc, msg = _static(lib, cfg, _device_frames(d_in, d_out, 641, 360, 320, 180, 0, 1))
     assert rc == b200vc.ERR_UNSUPPORTED and msg
     assert lib.b200vc_convert_scale_device_static(None, None, None, None, 0) == b200vc.ERR_INVALID_ARG

@@ -35,3 +35,14 @@ def test_c_harness_in_gstvideofilter_call_order(orc, tmp_path, geo):
                             plane_views(buf, ooff, opit, fmt, ow, oh), f"frame {k}")
         pos += total
     assert pos == data.size
+
+
+def test_session_bench_keeps_60hz():
+    """C5's per-GPU share in real time: 8 sessions at 60 Hz, every tick far inside its 16.7 ms budget."""
+    import json
+    exe = os.path.join(ROOT, "docker-nvidia-glx-desktop_b200", "harness", "session_bench")
+    r = subprocess.run([exe, "--gpus", "1", "--sessions", "8", "--seconds", "1.5", "--damage"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    d = json.loads(r.stdout.strip().splitlines()[-1])
+    assert d["late_ticks"] == 0 and d["ticks"] >= 80 and d["frames"] == 8 * d["ticks"]
+    assert d["tick_ms_p99"] < d["tick_budget_ms"] / 2

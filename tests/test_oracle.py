@@ -192,3 +192,14 @@ def test_input_formats(orc):
         h[20, 100, 3] ^= 1   # and the other way round for byte 3
         assert np.array_equal(orc.damage_map(h, f, inf), N.damage_map(h, f, inf))
         assert orc.damage_map(h, f, inf).sum() == 1
+
+
+def test_oracle_clean_under_sanitizers():
+    """The C oracle, rebuilt with -fsanitize=address,undefined, over ragged sizes and every format."""
+    import shutil
+    import subprocess
+    if not shutil.which("gcc"):
+        pytest.skip("no gcc")
+    r = subprocess.run(["make", "-C", os.path.join(os.path.dirname(os.path.dirname(__file__)), "oracle"), "asan"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "oracle clean" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

@@ -202,4 +202,6 @@ def test_oracle_clean_under_sanitizers():
         pytest.skip("no gcc")
     r = subprocess.run(["make", "-C", os.path.join(os.path.dirname(os.path.dirname(__file__)), "oracle"), "asan"],
                        capture_output=True, text=True, timeout=300)
+    if "cannot find -lasan" in r.stderr or "cannot find -lubsan" in r.stderr:
+        pytest.skip("this gcc has no sanitizer runtime")
     assert r.returncode == 0 and "oracle clean" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

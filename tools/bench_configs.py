@@ -82,8 +82,29 @@ def main():
             e1.record(stream)
         stream.synchronize()
         one = e0.elapsed_time(e1) / 1e3 / 200
+        # one launch per frame, 1024 launches back to back over the ring (HBM traffic, launch overhead included)
+        per = None
+        if not damage:
+            frames_df = []
+            for i in range(n):
+                d1 = b200vc.DeviceFrames()
+                d1.bgrx, d1.in_pitch, d1.in_frame_stride = d_in.data_ptr() + i * in_b, iw * 4, in_b
+                for k in range(3):
+                    d1.planes[k], d1.pitches[k] = d_out.data_ptr() + i * total + off[k], pit[k]
+                d1.out_frame_stride, d1.n_frames = total, 1
+                frames_df.append(d1)
+            with torch.cuda.stream(stream):
+                for i in range(64):
+                    conv.convert_device(frames_df[i % n], stream.cuda_stream)
+                e0.record(stream)
+                for i in range(1024):
+                    conv.convert_device(frames_df[i % n], stream.cuda_stream)
+                e1.record(stream)
+            stream.synchronize()
+            per = e0.elapsed_time(e1) / 1e3 / 1024
         inf = conv.info()
-        print(json.dumps({"config": name, "ring_frames": n, "fps": round(n / sec, 1), "ms_per_launch": round(sec * 1e3, 4),
+        print(json.dumps({"config": name, "per_frame_launch_ring_us": round(per * 1e6, 2) if per else None,
+                          "per_frame_launch_ring_fps": round(1 / per, 1) if per else None, "ring_frames": n, "fps": round(n / sec, 1), "ms_per_launch": round(sec * 1e3, 4),
                           "algo_GBs": round(algo * n / sec / 1e9, 1), "frac_of_measured_peak": round(algo * n / sec / 1e9 / PEAK, 4),
                           "single_frame_us": round(one * 1e6, 2), "path": inf.path, "box": [inf.box_w, inf.box_h]}), flush=True)
         del d_in, d_out, d_dmg

@@ -369,6 +369,7 @@ def run_gpu(args, rank: int, local_rank: int, world: int):
                     "pcie_h2d_gbs": round(e2e_fps / world * IN_BYTES / 1e9, 2),
                     "pcie_ceiling_fps_per_gpu": round(pcie_fps, 1),
                     "frac_of_pcie_ceiling": round(e2e_fps / world / pcie_fps, 4),
+                    "frac_of_pcie_gen5_x16_raw_63GBs": round(e2e_fps / world * IN_BYTES / 63.02e9, 4),
                     "pcie_ceiling_how": "raw pinned H2D 8.3 MB + D2H 3.1 MB copies in flight together, no kernel, rank 0",
                     "sync_single_session_fps": round(sync_fps, 1)},
             "gpu_launches": gpu_launches,

@@ -35,7 +35,45 @@ CONFIGS = [
 ]
 
 
+def e2e(only):
+    """End to end through b200vc_convert_batch (8 sessions per call, pinned host buffers) per config."""
+    import ctypes as C
+    import time
+    conv = b200vc.Converter(0)
+    for name, iw, ih, ow, oh, fmt, m, rg, site, flags, damage in CONFIGS:
+        if (only and only not in name) or "two-pass" in name or name.startswith("G "):
+            continue
+        ns = 8
+        in_b, (total, off, pit) = iw * ih * 4, b200vc.default_layout(fmt, ow, oh)
+        mb = ((iw + 15) // 16) * ((ih + 15) // 16)
+        conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=m, range_=rg, chroma_site=site, flags=flags, max_sessions=ns, n_inflight=ns)
+        h_in, h_out = b200vc.PinnedBuffer(2 * ns * in_b), b200vc.PinnedBuffer(ns * (total + mb))
+        h_in.array[:] = 99
+        h_in.array[ns * in_b::977] = 7                    # the second set of frames differs a little
+        ticks = []
+        for t in range(2):
+            fr = [conv.make_frame(h_in.ptr + (t * ns + s) * in_b, iw * 4, h_out.ptr + s * (total + mb), off, pit, session=s,
+                                  damage_ptr=(h_out.ptr + s * (total + mb) + total) if damage else None) for s in range(ns)]
+            ticks.append((b200vc.Frame * ns)(*fr))
+        for k in range(6):
+            conv.lib.b200vc_convert_batch(conv.ctx, ticks[k & 1], ns)
+        n = max(10, int(2e9 // (ns * in_b)))
+        t0 = time.perf_counter()
+        for k in range(n):
+            rc = conv.lib.b200vc_convert_batch(conv.ctx, ticks[k & 1], ns)
+            assert rc == 0
+        dt = time.perf_counter() - t0
+        fps = n * ns / dt
+        print(json.dumps({"config": name, "e2e_fps": round(fps, 1), "h2d_GBs": round(fps * in_b / 1e9, 2),
+                          "d2h_GBs": round(fps * total / 1e9, 2), "frac_of_pcie_gen5_x16_raw_63GBs": round(fps * in_b / 63.02e9, 4)}), flush=True)
+        conv.stop()
+        h_in.free()
+        h_out.free()
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "e2e":
+        return e2e(sys.argv[2] if len(sys.argv) > 2 else None)
     reps = int(sys.argv[1]) if len(sys.argv) > 1 else 50
     only = sys.argv[2] if len(sys.argv) > 2 else None
     conv = b200vc.Converter(0)

@@ -210,7 +210,7 @@ int b200vc_convert_device(b200vc_ctx *ctx, const b200vc_device_frames *frames, v
  * against everything in flight on the device and would stall the other sessions on that GPU; and a
  * process that gave all GPU memory to another pool at start-up has none left to ask for. It takes
  * no context (creating one allocates): `cfg` carries the negotiated caps (max_sessions, n_inflight,
- * n_bands are ignored; in and out sizes must differ; no damage map), `frames` the device buffers as
+ * n_bands are ignored; in and out sizes must differ and be even; no damage map), `frames` the device buffers as
  * for b200vc_convert_device (input pointer/pitch/stride multiples of 16 bytes, output pointers and
  * pitches multiples of 4), `cuda_stream` the stream to enqueue on. It calls no cudaMalloc, cudaFree
  * or any other allocating routine.

@@ -21,7 +21,7 @@ LIB_PATH = os.path.join(_HERE, "libb200vc.so")
 OK = 0
 ERR_INVALID_ARG, ERR_UNSUPPORTED, ERR_NOT_NEGOTIATED, ERR_CUDA, ERR_NO_DEVICE, ERR_ALIGNMENT, ERR_NOMEM, ERR_BAD_TICKET = range(1, 9)
 FMT_I420, FMT_NV12 = 0, 1
-MATRIX_BT601, MATRIX_BT709 = 0, 1
+MATRIX_BT601, MATRIX_BT709, MATRIX_BT2020 = 0, 1, 2
 RANGE_LIMITED, RANGE_FULL = 0, 1
 SITE_NONE, SITE_H_COSITED = 0, 1
 SCALE_GST_LQ, SCALE_BOX_2X2 = 0, 1

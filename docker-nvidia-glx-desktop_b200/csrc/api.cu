@@ -113,11 +113,13 @@ bool aligned16(const void *p) { return ((uintptr_t)p & 15) == 0; }
 
 // SURVEY A.2 table; rows Y,U,V of (cR, cG, cB, off). The oracle derives the same numbers from
 // Kr/Kb in double precision; tests compare the two.
-const int kMatrix[2][2][3][4] = {
+const int kMatrix[3][2][3][4] = {
     { { { 66, 129, 25, 4096 }, { -38, -74, 112, 32768 }, { 112, -94, -18, 32768 } },      // 601 limited
       { { 77, 150, 29, 0 }, { -43, -85, 128, 32768 }, { 128, -107, -21, 32768 } } },      // 601 full
     { { { 47, 157, 16, 4096 }, { -26, -87, 112, 32768 }, { 112, -102, -10, 32768 } },     // 709 limited
       { { 54, 183, 18, 0 }, { -29, -99, 128, 32768 }, { 128, -116, -12, 32768 } } },      // 709 full
+    { { { 58, 149, 13, 4096 }, { -31, -81, 112, 32768 }, { 112, -103, -9, 32768 } },      // 2020 limited
+      { { 67, 174, 15, 0 }, { -36, -92, 128, 32768 }, { 128, -118, -10, 32768 } } },      // 2020 full
 };
 
 // byte position of B, G, R in one pixel, per B200VC_IN_* (unpack_BGRA / _RGBA / _ARGB / _ABGR)
@@ -254,8 +256,8 @@ int check_config(const b200vc_config *c, std::string *why)
         return bad(B200VC_ERR_UNSUPPORTED, "output format must be I420 or NV12");
     if (c->in_format < B200VC_IN_BGRX || c->in_format > B200VC_IN_XBGR)
         return bad(B200VC_ERR_UNSUPPORTED, "input format must be BGRx/BGRA, RGBx/RGBA, xRGB/ARGB or xBGR/ABGR");
-    if (c->matrix != B200VC_MATRIX_BT601 && c->matrix != B200VC_MATRIX_BT709)
-        return bad(B200VC_ERR_UNSUPPORTED, "colorimetry matrix must be bt601 or bt709");
+    if (c->matrix < B200VC_MATRIX_BT601 || c->matrix > B200VC_MATRIX_BT2020)
+        return bad(B200VC_ERR_UNSUPPORTED, "colorimetry matrix must be bt601, bt709 or bt2020");
     if (c->range != B200VC_RANGE_LIMITED && c->range != B200VC_RANGE_FULL)
         return bad(B200VC_ERR_UNSUPPORTED, "range must be limited (16-235) or full (0-255)");
     if (c->chroma_site != B200VC_SITE_NONE && c->chroma_site != B200VC_SITE_H_COSITED)
@@ -766,10 +768,10 @@ const char *b200vc_status_string(int s)
 int b200vc_default_colorimetry(int out_h, int *matrix, int *range, int *chroma_site)
 {
     if (out_h <= 0) return B200VC_ERR_INVALID_ARG;
-    // > 576 lines -> bt709 limited, chroma-site mpeg2; else bt601 limited, jpeg.
-    // (bt2020 for >= 2160 lines exists only in newer GStreamer and is not offered by this element.)
+    // >= 2160 lines -> bt2020 (GStreamer >= 1.18; the bundle the reference downloads is
+    // recent), > 576 lines -> bt709, else bt601; limited range; chroma-site mpeg2 above 576 lines, else jpeg.
     const bool hd = out_h > 576;
-    if (matrix) *matrix = hd ? B200VC_MATRIX_BT709 : B200VC_MATRIX_BT601;
+    if (matrix) *matrix = out_h >= 2160 ? B200VC_MATRIX_BT2020 : hd ? B200VC_MATRIX_BT709 : B200VC_MATRIX_BT601;
     if (range) *range = B200VC_RANGE_LIMITED;
     if (chroma_site) *chroma_site = hd ? B200VC_SITE_H_COSITED : B200VC_SITE_NONE;
     return B200VC_OK;

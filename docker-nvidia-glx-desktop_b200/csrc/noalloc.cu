@@ -148,11 +148,13 @@ Matrix static_matrix(int matrix, int range, int in_format)
 {
     static const int pos_tab[4][3] = { { 0, 1, 2 }, { 2, 1, 0 }, { 3, 2, 1 }, { 1, 2, 3 } };   // byte of B, G, R
     const int *pos = pos_tab[in_format];
-    static const int t[2][2][3][4] = {
+    static const int t[3][2][3][4] = {
         { { { 66, 129, 25, 4096 }, { -38, -74, 112, 32768 }, { 112, -94, -18, 32768 } },
           { { 77, 150, 29, 0 }, { -43, -85, 128, 32768 }, { 128, -107, -21, 32768 } } },
         { { { 47, 157, 16, 4096 }, { -26, -87, 112, 32768 }, { 112, -102, -10, 32768 } },
           { { 54, 183, 18, 0 }, { -29, -99, 128, 32768 }, { 128, -116, -12, 32768 } } },
+        { { { 58, 149, 13, 4096 }, { -31, -81, 112, 32768 }, { 112, -103, -9, 32768 } },
+          { { 67, 174, 15, 0 }, { -36, -92, 128, 32768 }, { 128, -118, -10, 32768 } } },
     };
     const int (*m)[4] = t[matrix][range];
     auto pack = [pos](int cb, int cg, int cr) {

@@ -95,7 +95,11 @@ static int in_format_of(const GstVideoInfo *i)
 
 static int matrix_of(const GstVideoInfo *i)
 {
-    return i->colorimetry.matrix == GST_VIDEO_COLOR_MATRIX_BT601 ? B200VC_MATRIX_BT601 : B200VC_MATRIX_BT709;
+    switch (i->colorimetry.matrix) {
+    case GST_VIDEO_COLOR_MATRIX_BT601: return B200VC_MATRIX_BT601;
+    case GST_VIDEO_COLOR_MATRIX_BT2020: return B200VC_MATRIX_BT2020;
+    default: return B200VC_MATRIX_BT709;
+    }
 }
 
 /* set_info: (re)build the converter for the negotiated caps. FALSE = not negotiated. */

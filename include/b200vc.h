@@ -48,7 +48,7 @@ enum {
 
 /* ---- negotiated caps, as plain enums ------------------------------------------------------- */
 enum { B200VC_FMT_I420 = 0, B200VC_FMT_NV12 = 1 };                  /* src pad format          */
-enum { B200VC_MATRIX_BT601 = 0, B200VC_MATRIX_BT709 = 1 };          /* colorimetry matrix      */
+enum { B200VC_MATRIX_BT601 = 0, B200VC_MATRIX_BT709 = 1, B200VC_MATRIX_BT2020 = 2 };   /* colorimetry matrix */
 enum { B200VC_RANGE_LIMITED = 0, B200VC_RANGE_FULL = 1 };           /* colorimetry range       */
 enum { B200VC_SITE_NONE = 0 /* "jpeg" */, B200VC_SITE_H_COSITED = 1 /* "mpeg2" */ };
 enum { B200VC_SCALE_GST_LQ = 0 /* videoscale bilinear, SURVEY B.2 */, B200VC_SCALE_BOX_2X2 = 1 };

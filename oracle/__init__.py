@@ -19,7 +19,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _SRCS = ["convert.c", "scale.c", "damage_synth.c"]
 
 FMT_I420, FMT_NV12 = 0, 1
-MATRIX_BT601, MATRIX_BT709 = 0, 1
+MATRIX_BT601, MATRIX_BT709, MATRIX_BT2020 = 0, 1, 2
 RANGE_LIMITED, RANGE_FULL = 0, 1
 SITE_NONE, SITE_H_COSITED = 0, 1
 SCALE_GST_LQ, SCALE_BOX_2X2 = 0, 1

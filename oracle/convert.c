@@ -20,8 +20,8 @@
 void orc_build_matrix(int matrix, int range, orc_matrix *out)
 {
     /* gst_video_color_matrix_get_Kr_Kb */
-    const double Kr = (matrix == ORC_MATRIX_BT709) ? 0.2126 : 0.299;
-    const double Kb = (matrix == ORC_MATRIX_BT709) ? 0.0722 : 0.114;
+    const double Kr = (matrix == ORC_MATRIX_BT2020) ? 0.2627 : (matrix == ORC_MATRIX_BT709) ? 0.2126 : 0.299;
+    const double Kb = (matrix == ORC_MATRIX_BT2020) ? 0.0593 : (matrix == ORC_MATRIX_BT709) ? 0.0722 : 0.114;
     const double Kg = 1.0 - Kr - Kb;
     double m[3][4];
 
@@ -195,7 +195,7 @@ static int convert_rows_ex(const uint8_t *bgrx, size_t in_pitch, int in_format, 
                            uint8_t *const planes[3], const size_t pitches[3],
                            int row0, int row1)
 {
-    if (in_format < ORC_IN_BGRX || in_format > ORC_IN_XBGR)
+    if (in_format < ORC_IN_BGRX || in_format > ORC_IN_XBGR || matrix < ORC_MATRIX_BT601 || matrix > ORC_MATRIX_BT2020)
         return -1;
     if (!bgrx || !planes || !pitches || w < 2 || h < 2)
         return -1;

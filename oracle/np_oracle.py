@@ -16,6 +16,10 @@ MATRICES = {
     (0, 1): [(77, 150, 29, 0), (-43, -85, 128, 32768), (128, -107, -21, 32768)],
     (1, 0): [(47, 157, 16, 4096), (-26, -87, 112, 32768), (112, -102, -10, 32768)],
     (1, 1): [(54, 183, 18, 0), (-29, -99, 128, 32768), (128, -116, -12, 32768)],
+    # BT.2020 non-constant luminance (Kr 0.2627, Kb 0.0593), same procedure; what GStreamer >= 1.18
+    # picks by default for >= 2160 lines
+    (2, 0): [(58, 149, 13, 4096), (-31, -81, 112, 32768), (112, -103, -9, 32768)],
+    (2, 1): [(67, 174, 15, 0), (-36, -92, 128, 32768), (128, -118, -10, 32768)],
 }
 
 

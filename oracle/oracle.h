@@ -23,7 +23,7 @@ extern "C" {
 #endif
 
 enum { ORC_FMT_I420 = 0, ORC_FMT_NV12 = 1 };
-enum { ORC_MATRIX_BT601 = 0, ORC_MATRIX_BT709 = 1 };
+enum { ORC_MATRIX_BT601 = 0, ORC_MATRIX_BT709 = 1, ORC_MATRIX_BT2020 = 2 };
 enum { ORC_RANGE_LIMITED = 0, ORC_RANGE_FULL = 1 };
 enum { ORC_SITE_NONE = 0 /* "jpeg" */, ORC_SITE_H_COSITED = 1 /* "mpeg2" */ };
 enum { ORC_SCALE_GST_LQ = 0, ORC_SCALE_BOX_2X2 = 1 };

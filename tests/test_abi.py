@@ -44,8 +44,10 @@ def test_version_and_status_strings(lib):
 
 
 def test_default_colorimetry_by_height():
-    # > 576 lines -> bt709 limited + mpeg2 siting; else bt601 limited + jpeg siting
+    # >= 2160 lines -> bt2020, > 576 lines -> bt709 limited + mpeg2 siting; else bt601 limited + jpeg
     assert b200vc.default_colorimetry(1080) == (b200vc.MATRIX_BT709, b200vc.RANGE_LIMITED, b200vc.SITE_H_COSITED)
+    assert b200vc.default_colorimetry(2160) == (b200vc.MATRIX_BT2020, b200vc.RANGE_LIMITED, b200vc.SITE_H_COSITED)
+    assert b200vc.default_colorimetry(2159)[0] == b200vc.MATRIX_BT709
     assert b200vc.default_colorimetry(577)[0] == b200vc.MATRIX_BT709
     assert b200vc.default_colorimetry(576) == (b200vc.MATRIX_BT601, b200vc.RANGE_LIMITED, b200vc.SITE_NONE)
     assert b200vc.default_colorimetry(480)[2] == b200vc.SITE_NONE
@@ -73,7 +75,7 @@ def test_caps_acceptance(lib):
     refused = [(_cfg(in_w=3842, in_h=2162, out_w=1921, out_h=1081, scale_mode=1), b200vc.ERR_UNSUPPORTED),   # BOX, odd
                (_cfg(out_format=2), b200vc.ERR_UNSUPPORTED),               # not I420/NV12
                (_cfg(in_format=4), b200vc.ERR_UNSUPPORTED),                # not a 4-byte RGB order
-               (_cfg(matrix=2), b200vc.ERR_UNSUPPORTED),                   # bt2020 not offered
+               (_cfg(matrix=3), b200vc.ERR_UNSUPPORTED),                   # not bt601/bt709/bt2020
                (_cfg(chroma_site=3), b200vc.ERR_UNSUPPORTED),              # v-cosited not offered
                (_cfg(in_w=3840, in_h=2160, out_w=1280, out_h=720, scale_mode=1), b200vc.ERR_UNSUPPORTED),
                (_cfg(in_w=3840, in_h=2160, flags=b200vc.FLAG_DAMAGE_MAP), b200vc.ERR_UNSUPPORTED),

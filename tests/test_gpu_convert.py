@@ -13,7 +13,7 @@ from helpers import assert_planes_equal, plane_checksums, plane_views
 
 pytestmark = pytest.mark.gpu
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "vectors.npz")
-COMBOS = [(0, 0), (0, 1), (1, 0), (1, 1)]
+COMBOS = [(0, 0), (0, 1), (1, 0), (1, 1), (2, 0), (2, 1)]
 
 
 @pytest.fixture(scope="module")

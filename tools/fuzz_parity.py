@@ -37,6 +37,7 @@ def main():
             oh = max(2, int(ih * rng.uniform(0.3, 1.6)))
         fmt, m, rg, site, inf = (int(rng.integers(0, 2)) for _ in range(5))
         inf = int(rng.integers(0, 4))
+        m = int(rng.integers(0, 3))
         scaling = (ow, oh) != (iw, ih)
         flags = int(rng.choice([0, b200vc.FLAG_FORCE_TWO_PASS, b200vc.FLAG_FORCE_GENERIC_FUSED])) if scaling else \
             int(rng.choice([0, b200vc.FLAG_DAMAGE_MAP, b200vc.FLAG_ZERO_COPY]))

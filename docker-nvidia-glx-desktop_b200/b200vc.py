@@ -34,7 +34,7 @@ SYMBOLS = [
     "b200vc_version", "b200vc_create", "b200vc_destroy", "b200vc_last_error", "b200vc_get_info",
     "b200vc_get_stats", "b200vc_reset", "b200vc_convert", "b200vc_convert_batch", "b200vc_submit",
     "b200vc_collect", "b200vc_host_alloc", "b200vc_host_free", "b200vc_convert_device",
-    "b200vc_convert_scale_device_static",
+    "b200vc_convert_scale_device_static", "b200vc_damage_to_rects",
 ]
 STATIC_SCRATCH_BYTES = 3133440
 
@@ -68,6 +68,10 @@ class Info(C.Structure):
     _fields_ = [("path", C.c_int32), ("tile_w", C.c_int32), ("tile_h", C.c_int32), ("box_w", C.c_int32),
                 ("box_h", C.c_int32), ("smem_bytes", C.c_int32), ("sm_count", C.c_int32), ("cc_major", C.c_int32),
                 ("cc_minor", C.c_int32), ("fused_2to1", C.c_int32), ("device_name", C.c_char * 64)]
+
+
+class Rect(C.Structure):
+    _fields_ = [("x", C.c_int32), ("y", C.c_int32), ("w", C.c_int32), ("h", C.c_int32)]
 
 
 class B200vcError(RuntimeError):
@@ -109,6 +113,7 @@ def load() -> C.CDLL:
     L.b200vc_host_free.argtypes = [vp]
     L.b200vc_convert_device.argtypes = [vp, C.POINTER(DeviceFrames), vp]
     L.b200vc_convert_scale_device_static.argtypes = [C.POINTER(Config), C.POINTER(DeviceFrames), vp, C.c_char_p, sz]
+    L.b200vc_damage_to_rects.argtypes = [vp, i, i, C.POINTER(Rect), i]
     _lib = L
     return L
 
@@ -125,6 +130,16 @@ def default_layout(fmt: int, w: int, h: int):
     off, pit = (C.c_size_t * 3)(), (C.c_size_t * 3)()
     total = load().b200vc_default_layout(fmt, w, h, off, pit)
     return int(total), [int(x) for x in off], [int(x) for x in pit]
+
+
+def damage_rects(dmg: np.ndarray, frame_w: int, frame_h: int, max_rects: int = 4096):
+    """Dirty macroblocks of a damage map as a list of (x, y, w, h) pixel rectangles."""
+    dmg = np.ascontiguousarray(dmg, np.uint8)
+    arr = (Rect * max_rects)()
+    n = load().b200vc_damage_to_rects(dmg.ctypes.data, frame_w, frame_h, arr, max_rects)
+    if n < 0:
+        raise B200vcError(ERR_INVALID_ARG, "bad damage map arguments")
+    return [(r.x, r.y, r.w, r.h) for r in arr[: min(n, max_rects)]], n
 
 
 class PinnedBuffer:

@@ -793,6 +793,47 @@ size_t b200vc_default_layout(int format, int w, int h, size_t offsets[3], size_t
     return offsets[2] + cp * (h2 / 2);
 }
 
+int b200vc_damage_to_rects(const uint8_t *map, int frame_w, int frame_h, b200vc_rect *rects, int max_rects)
+{
+    if (!map || frame_w < 1 || frame_h < 1 || max_rects < 0 || (max_rects > 0 && !rects)) return -1;
+    const int mb_w = (frame_w + 15) / 16, mb_h = (frame_h + 15) / 16;
+    struct Open { int x0, x1, y0; };                       // runs of the previous row still growing downwards
+    std::vector<Open> open, next;
+    int n = 0;
+    auto emit = [&](const Open &o, int y1) {
+        if (n < max_rects) {
+            b200vc_rect &r = rects[n];
+            r.x = o.x0 * 16;  r.y = o.y0 * 16;
+            r.w = std::min(o.x1 * 16, frame_w) - r.x;
+            r.h = std::min(y1 * 16, frame_h) - r.y;
+        }
+        n++;
+    };
+    for (int y = 0; y <= mb_h; y++) {
+        next.clear();
+        if (y < mb_h) {
+            const uint8_t *row = map + (size_t)y * mb_w;
+            for (int x = 0; x < mb_w;) {
+                if (!row[x]) { x++; continue; }
+                int x1 = x;
+                while (x1 < mb_w && row[x1]) x1++;
+                int y0 = y;
+                for (const Open &o : open)
+                    if (o.x0 == x && o.x1 == x1) y0 = o.y0;   // same run as in the row above: keep growing
+                next.push_back({ x, x1, y0 });
+                x = x1;
+            }
+        }
+        for (const Open &o : open) {                       // runs that did not continue are complete
+            bool cont = false;
+            for (const Open &q : next) cont = cont || (q.x0 == o.x0 && q.x1 == o.x1 && q.y0 == o.y0);
+            if (!cont) emit(o, y);
+        }
+        open.swap(next);
+    }
+    return n;
+}
+
 int b200vc_check_config(const b200vc_config *cfg)
 {
     std::string why;

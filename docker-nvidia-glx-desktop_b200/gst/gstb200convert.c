@@ -143,8 +143,20 @@ gst_b200_convert_transform_frame(GstVideoFilter *filter, GstVideoFrame *in, GstV
                         GST_VIDEO_FRAME_N_PLANES(out) > 2 ? GST_VIDEO_FRAME_PLANE_DATA(out, 2) : NULL };
     size_t pitches[3] = { (size_t)GST_VIDEO_FRAME_PLANE_STRIDE(out, 0), (size_t)GST_VIDEO_FRAME_PLANE_STRIDE(out, 1),
                           GST_VIDEO_FRAME_N_PLANES(out) > 2 ? (size_t)GST_VIDEO_FRAME_PLANE_STRIDE(out, 2) : 0 };
+    guint8 *map = NULL;
+    const gint fw = GST_VIDEO_FRAME_WIDTH(in), fh = GST_VIDEO_FRAME_HEIGHT(in);
+    if (self->damage_map && fw == GST_VIDEO_FRAME_WIDTH(out) && fh == GST_VIDEO_FRAME_HEIGHT(out))
+        map = g_malloc(((fw + 15) / 16) * ((fh + 15) / 16));
     int rc = b200vc_convert(self->ctx, GST_VIDEO_FRAME_PLANE_DATA(in, 0), (size_t)GST_VIDEO_FRAME_PLANE_STRIDE(in, 0),
-                            planes, pitches, NULL /* the map would travel as a custom GstMeta */);
+                            planes, pitches, map);
+    if (rc == B200VC_OK && map) {
+        /* dirty macroblocks travel downstream as regions of interest */
+        b200vc_rect rects[256];
+        int n = b200vc_damage_to_rects(map, fw, fh, rects, 256);
+        for (int i = 0; i < n && i < 256; i++)
+            gst_buffer_add_video_region_of_interest_meta(out->buffer, "damage", rects[i].x, rects[i].y, rects[i].w, rects[i].h);
+    }
+    g_free(map);
     if (rc != B200VC_OK) {
         GST_ELEMENT_ERROR(self, LIBRARY, FAILED, ("b200vc_convert: %s", b200vc_status_string(rc)), ("%s", b200vc_last_error(self->ctx)));
         return GST_FLOW_ERROR;

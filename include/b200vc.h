@@ -145,6 +145,14 @@ size_t b200vc_default_layout(int format, int w, int h, size_t offsets[3], size_t
 /* transform_caps/set_caps acceptance test: B200VC_OK, or the reason the caps are refused. */
 int b200vc_check_config(const b200vc_config *cfg);
 
+/* Damage-map consumer (no GPU needed): merge the dirty 16x16 macroblocks of a map into pixel
+ * rectangles — runs of dirty macroblocks along a row, stacked while consecutive rows hold the same
+ * run — clipped to the frame. What the element attaches downstream as GstVideoRegionOfInterestMeta
+ * (x264enc does not read it today). Returns the number of rectangles the map needs;
+ * at most max_rects of them are written. */
+typedef struct b200vc_rect { int32_t x, y, w, h; } b200vc_rect;
+int b200vc_damage_to_rects(const uint8_t *map, int frame_w, int frame_h, b200vc_rect *rects, int max_rects);
+
 const char *b200vc_status_string(int status);
 int b200vc_version(void);
 

@@ -117,3 +117,31 @@ def test_product_never_imports_the_oracle():
                 src = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), f
                 assert "oracle.h" not in src and "liboracle" not in src, f
+
+
+def test_damage_map_to_rectangles(orc):
+    """The damage-map consumer: rectangles cover exactly the dirty macroblocks, clipped to the frame."""
+    import numpy as np
+    w, h = 1920, 1080
+    a, b = orc.synth("desk", w, h, 29), orc.synth("desk", w, h, 30)
+    dm = orc.damage_map(b, a)
+    rects, n = b200vc.damage_rects(dm, w, h)
+    assert n == len(rects) and 0 < n < 40
+    cover = np.zeros_like(dm)
+    for x, y, rw, rh in rects:
+        assert x % 16 == 0 and y % 16 == 0 and rw > 0 and rh > 0 and x + rw <= w and y + rh <= h
+        sub = cover[y // 16:(y + rh + 15) // 16, x // 16:(x + rw + 15) // 16]
+        assert not sub.any()                             # rectangles do not overlap
+        sub[:] = 1
+    assert np.array_equal(cover, dm)
+    # the last macroblock row of 1080p is 8 lines high
+    full = np.ones_like(dm)
+    assert b200vc.damage_rects(full, w, h)[0] == [(0, 0, 1920, 1080)]
+    assert b200vc.damage_rects(np.zeros_like(dm), w, h) == ([], 0)
+    lone = np.zeros_like(dm)
+    lone[67, 119] = 1
+    assert b200vc.damage_rects(lone, w, h)[0] == [(1904, 1072, 16, 8)]
+    # more rectangles than room: the count is still reported
+    chk = (np.indices(dm.shape).sum(0) & 1).astype(np.uint8)
+    got, need = b200vc.damage_rects(chk, w, h, max_rects=10)
+    assert len(got) == 10 and need == int(chk.sum())

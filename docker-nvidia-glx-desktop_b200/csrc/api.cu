@@ -378,6 +378,9 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         p.in_w = g.in_w;  p.in_h = g.in_h;  p.out_w = g.out_w;  p.out_h = g.out_h;
         p.box_w = c->box_w;  p.box_h = c->box_h;  p.n_frames = n_frames;
         p.box2x2 = g.scale_mode == B200VC_SCALE_BOX_2X2;  p.mx = c->mx;
+        const uint32_t items_x = (uint32_t)c->box_w / 4;
+        p.inv_items_x = (65536u + items_x - 1) / items_x;
+        p.inv_items_x1 = items_x > 1 ? (65536u + items_x - 2) / (items_x - 1) : 65536u;
         CU_TRY(c, launch_fused_scale(map, p, g.out_format, site, st));
         c->stats.kernel_launches += 1;
         return B200VC_OK;

@@ -49,7 +49,7 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
 {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t s_bar;
-    __shared__ int s_org[2];
+    __shared__ int s_org[3];               // window origin x, y; first 4-column item that is not pure halo
 
     const int bw = p.box_w, bh = p.box_h;
     uint32_t *s_src = reinterpret_cast<uint32_t *>(smem);                 // [bh][bw] pixels
@@ -71,6 +71,7 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
         const int sy = min(vy0, 2 * vc0) & ~1;
         s_org[0] = sx;
         s_org[1] = sy;
+        s_org[2] = min(min(hy0, 2 * uc0) - sx, 4) >> 2;   // 1 when the window's first 4 columns are halo only
 
         const uint32_t bar = smem_u32(&s_bar);
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
@@ -84,7 +85,7 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
             : "memory");
     }
     __syncthreads();
-    const int sx0 = s_org[0], sy0 = s_org[1];
+    const int sx0 = s_org[0], sy0 = s_org[1], kfirst = s_org[2];
     {
         const uint32_t bar = smem_u32(&s_bar);
         uint32_t done = 0;
@@ -99,9 +100,15 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
 
     // ---- phase 1: convert the window (4 columns x 2 lines per item) ------------------------------
     const Matrix &m = p.mx;
-    const int items_x = bw >> 2, n_items = items_x * (bh >> 1);
-    for (int it = tid; it < n_items; it += 256) {
-        const int kx = it % items_x, ky = it / items_x;
+    // items are walked without divisions (host-made reciprocal for the start, increments after),
+    // and a first item column that holds nothing but halo is skipped
+    const int items_x = (bw >> 2) - kfirst, n_items = items_x * (bh >> 1);
+    const uint32_t inv = kfirst ? p.inv_items_x1 : p.inv_items_x;
+    int ky = (int)(((uint32_t)tid * inv) >> 16), kxr = tid - ky * items_x;
+    const int dky = (int)((256u * inv) >> 16), dkx = 256 - dky * items_x;
+    for (int it = tid; it < n_items; it += 256, kxr += dkx, ky += dky) {
+        if (kxr >= items_x) { kxr -= items_x; ky++; }
+        const int kx = kxr + kfirst;
         const uint32_t *ra = s_src + (size_t)(2 * ky) * bw + 4 * kx;
         const uint32_t *rb = ra + bw;
         const uint4 a = *reinterpret_cast<const uint4 *>(ra);

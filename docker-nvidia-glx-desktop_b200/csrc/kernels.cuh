@@ -59,6 +59,8 @@ struct FusedScaleParams {
     int box_w, box_h;       // source window per tile (pixels); box_w % 4 == 0, box_h even
     int n_frames;
     int box2x2;             // scale_mode == BOX_2X2
+    uint32_t inv_items_x;   // ceil(65536 / (box_w/4)) and the same for box_w/4 - 1: tid / items_x
+    uint32_t inv_items_x1;  // without a division (exact for tid <= 256, up to 64 items)
     Matrix mx;
 };
 

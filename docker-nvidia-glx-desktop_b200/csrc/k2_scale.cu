@@ -35,8 +35,8 @@ __device__ __forceinline__ uint32_t smem_u32(const void *p)
     return (uint32_t)__cvta_generic_to_shared(p);
 }
 
-// video_scale_h_2tap_1u8 (lq) then video_scale_v_2tap_u8 (lq) on one component
-__device__ __forceinline__ int lerp_h(int a, int b, int f) { return (a * (256 - f) + b * f) >> 8; }
+// video_scale_v_2tap_u8 (lq) on one component (the horizontal tap, video_scale_h_2tap_1u8 (lq), is
+// (a*(256-f) + b*f) >> 8 and is applied to two lines at once on 16-bit lanes where it is used)
 __device__ __forceinline__ int lerp_v(int a, int b, int p1)
 {
     int d = a + (((b - a) * p1 + 32) >> 6);
@@ -158,16 +158,24 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
             const uint8_t *row0 = s_yf + (size_t)i0 * bw, *row1 = s_yf + (size_t)i1 * bw;
             const uint4 th4 = *reinterpret_cast<const uint4 *>(p.tab.hy + x);   // table padded to 4
             const Tap th[4] = { th4.x, th4.y, th4.z, th4.w };
+            // vertical tap as dp4a weights on bytes 1 and 3 (the two lines' horizontally scaled pixels
+            // are the high bytes of the two 16-bit lanes): a + (((b-a)*p1 + 32) >> 6) equals
+            // (a*(64-p1) + b*p1 + 32) >> 6, which needs no clamp
+            const uint32_t wv = ((uint32_t)(64 - p1) << 8) | ((uint32_t)p1 << 24);
             uint32_t out = 0;
 #pragma unroll
             for (int k = 0; k < 4; k++) {
-                const int j0 = tap_idx(th[k]) - sx0, j1 = j0 + tap_step(th[k]), f = tap_frac(th[k]);
-                int d;
-                if (p.box2x2)
-                    d = (row0[j0] + row0[j0 + 1] + row1[j0] + row1[j0 + 1] + 2) >> 2;
-                else
-                    d = lerp_v(lerp_h(row0[j0], row0[j1], f), lerp_h(row1[j0], row1[j1], f), p1);
-                out |= (uint32_t)d << (8 * k);
+                const int j0 = tap_idx(th[k]) - sx0, j1 = j0 + tap_step(th[k]);
+                const uint32_t f = (uint32_t)tap_frac(th[k]);
+                uint32_t d;
+                if (p.box2x2) {
+                    d = (uint32_t)(row0[j0] + row0[j0 + 1] + row1[j0] + row1[j0 + 1] + 2) >> 2;
+                } else {
+                    const uint32_t w0 = (uint32_t)row0[j0] | ((uint32_t)row1[j0] << 16);   // both lines, 16-bit lanes
+                    const uint32_t w1 = (uint32_t)row0[j1] | ((uint32_t)row1[j1] << 16);
+                    d = dp4a_uu(w0 * (256u - f) + w1 * f, wv, 32u) >> 6;
+                }
+                out |= d << (8 * k);
             }
             uint8_t *dst = p.out.p[0] + fo + (long long)y * p.out.pitch[0] + x;
             if (x + 4 <= p.out_w) {
@@ -195,10 +203,11 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
                 dv = (int)(s >> 16);
             } else {
                 // both lanes at once: each lane's weighted sum is <= 255*256
-                const uint32_t ha = ((row0[j0] * (uint32_t)(256 - f) + row0[j1] * (uint32_t)f) >> 8) & LANES8;
-                const uint32_t hb = ((row1[j0] * (uint32_t)(256 - f) + row1[j1] * (uint32_t)f) >> 8) & LANES8;
-                du = lerp_v((int)(ha & 0xff), (int)(hb & 0xff), p1);
-                dv = lerp_v((int)(ha >> 16), (int)(hb >> 16), p1);
+                const uint32_t ha = row0[j0] * (uint32_t)(256 - f) + row0[j1] * (uint32_t)f;   // high bytes of the
+                const uint32_t hb = row1[j0] * (uint32_t)(256 - f) + row1[j1] * (uint32_t)f;   // lanes: scaled u, v
+                const uint32_t uv = prmt(ha, hb, 0x7351);          // u(line 0), u(line 1), v(line 0), v(line 1)
+                du = (int)(dp4a_uu(uv, (uint32_t)(64 - p1) | ((uint32_t)p1 << 8), 32u) >> 6);
+                dv = (int)(dp4a_uu(uv, ((uint32_t)(64 - p1) << 16) | ((uint32_t)p1 << 24), 32u) >> 6);
             }
             if (FMT == 0) {
                 p.out.p[1][fo + (long long)cy * p.out.pitch[1] + cx] = (uint8_t)du;

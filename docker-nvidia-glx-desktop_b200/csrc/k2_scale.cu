@@ -35,13 +35,10 @@ __device__ __forceinline__ uint32_t smem_u32(const void *p)
     return (uint32_t)__cvta_generic_to_shared(p);
 }
 
-// video_scale_v_2tap_u8 (lq) on one component (the horizontal tap, video_scale_h_2tap_1u8 (lq), is
-// (a*(256-f) + b*f) >> 8 and is applied to two lines at once on 16-bit lanes where it is used)
-__device__ __forceinline__ int lerp_v(int a, int b, int p1)
-{
-    int d = a + (((b - a) * p1 + 32) >> 6);
-    return d < 0 ? 0 : (d > 255 ? 255 : d);
-}
+// Scaler arithmetic used below. Horizontal, video_scale_h_2tap_1u8 (lq):
+// (a*(256-f) + b*f) >> 8, applied to two lines at once on 16-bit lanes. Vertical,
+// video_scale_v_2tap_u8 (lq): a + (((b-a)*p1 + 32) >> 6), which equals (a*(64-p1) + b*p1 + 32) >> 6
+// (no clamp needed for 0 <= p1 <= 64) and is evaluated as one dp4a on the lanes' high bytes.
 
 template <int FMT, int SITE, bool NEG>
 __global__ void __launch_bounds__(256)
@@ -299,9 +296,10 @@ k2_fused_2x_kernel(const __grid_constant__ CUtensorMap src_map, const Fused2xPar
         cuv = ((v00 + v01 + v10 + v11 + 0x00020002u) >> 2) & LANES8;
     } else {
         const uint32_t f = (((uint32_t)(c >> 2) * p.inc_c) >> 8) & 0xffu;
-        const uint32_t ha = ((v00 * (256u - f) + v01 * f) >> 8) & LANES8;
-        const uint32_t hb = ((v10 * (256u - f) + v11 * f) >> 8) & LANES8;
-        cuv = avg2(ha, hb);
+        const uint32_t ha = v00 * (256u - f) + v01 * f;    // high bytes of the lanes: scaled u, v of line 0
+        const uint32_t hb = v10 * (256u - f) + v11 * f;    // ... of line 1
+        const uint32_t uv = prmt(ha, hb, 0x7351);          // u0 u1 v0 v1 (line 0 / line 1)
+        cuv = (dp4a_uu(uv, 0x00000101u, 1u) >> 1) | ((dp4a_uu(uv, 0x01010000u, 1u) >> 1) << 16);
     }
 
     // ---- luma: lines (2i, 2i+1) ride in the two 16-bit lanes --------------------------------------
@@ -361,15 +359,16 @@ __device__ __forceinline__ uint32_t scale4(const uint8_t *r0, const uint8_t *r1,
         const uint32_t f = (uint32_t)tap_frac(th[k]);
         const uint32_t w0 = (uint32_t)__ldg(r0 + j0) | ((uint32_t)__ldg(r1 + j0) << 16);
         const uint32_t w1 = (uint32_t)__ldg(r0 + j1) | ((uint32_t)__ldg(r1 + j1) << 16);
-        int d;
+        uint32_t d;
         if (box) {
             const uint32_t q = w0 + w1;
-            d = (int)(((q & 0xffffu) + (q >> 16) + 2u) >> 2);
+            d = ((q & 0xffffu) + (q >> 16) + 2u) >> 2;
         } else {
-            const uint32_t h = w0 * (256u - f) + w1 * f;   // per lane < 65536; its high byte is the scaled pixel
-            d = lerp_v((int)((h >> 8) & 0xffu), (int)(h >> 24), p1);
+            // per lane the sum is < 65536 and its high byte is the scaled pixel; the vertical tap
+            // a + (((b-a)*p1 + 32) >> 6) == (a*(64-p1) + b*p1 + 32) >> 6 is one dp4a on bytes 1 and 3
+            d = dp4a_uu(w0 * (256u - f) + w1 * f, ((uint32_t)(64 - p1) << 8) | ((uint32_t)p1 << 24), 32u) >> 6;
         }
-        out |= (uint32_t)d << (8 * k);
+        out |= d << (8 * k);
     }
     return out;
 }

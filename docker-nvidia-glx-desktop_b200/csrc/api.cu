@@ -613,7 +613,8 @@ int submit_locked(b200vc_ctx *c, const b200vc_frame *f, int bands, uint64_t *tic
     if (!out_pinned && !slot.h_out) CU_TRY(c, cudaMallocHost(&slot.h_out, c->d_out_size + ru((size_t)c->mb_w * c->mb_h, 256)));
 
     // zero-copy: K1 reads the page-locked frame over PCIe and writes the planes back itself
-    if ((g.flags & B200VC_FLAG_ZERO_COPY) && c->path == 0 && !f->damage && in_pinned && out_pinned) {
+    // (not on contexts that keep previous frames for the damage map: those need the frame in HBM)
+    if ((g.flags & B200VC_FLAG_ZERO_COPY) && !(g.flags & B200VC_FLAG_DAMAGE_MAP) && c->path == 0 && in_pinned && out_pinned) {
         void *d_src = nullptr, *d_pl[3] = { nullptr, nullptr, nullptr };
         bool ok = cudaHostGetDevicePointer(&d_src, const_cast<void *>(f->bgrx), 0) == cudaSuccess;
         for (int i = 0; i < n_planes && ok; i++) ok = cudaHostGetDevicePointer(&d_pl[i], f->planes[i], 0) == cudaSuccess;

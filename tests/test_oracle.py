@@ -210,3 +210,23 @@ def test_oracle_clean_under_sanitizers():
     if "cannot find -lasan" in r.stderr or "cannot find -lubsan" in r.stderr:
         pytest.skip("this gcc has no sanitizer runtime")
     assert r.returncode == 0 and "oracle clean" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_sanity_against_opencv(orc):
+    """Non-gating cross-check: OpenCV's BGRA->I420 uses other coefficients, rounding and
+    chroma sampling, so it is not an oracle — but on a smooth frame it must agree within a few LSB,
+    which catches gross plane-layout or channel-order mistakes in the restatement."""
+    cv2 = pytest.importorskip("cv2")
+    w, h = 640, 360
+    yy, xx = np.mgrid[0:h, 0:w]
+    frame = np.zeros((h, w, 4), np.uint8)
+    frame[..., 0] = (xx * 255 // (w - 1))                  # B ramps left to right
+    frame[..., 1] = (yy * 255 // (h - 1))                  # G ramps top to bottom
+    frame[..., 2] = ((xx + yy) * 255 // (w + h - 2))       # R ramps along the diagonal
+    frame[..., 3] = 0x77
+    buf, off, pit = orc.convert(frame, 0, 0, 0, 0)         # BT.601 limited, like OpenCV
+    y, u, v = plane_views(buf, off, pit, 0, w, h)
+    ref = cv2.cvtColor(frame, cv2.COLOR_BGRA2YUV_I420)
+    ry, ru, rv = ref[:h], ref[h:h + h // 4].reshape(h // 2, w // 2), ref[h + h // 4:].reshape(h // 2, w // 2)
+    assert np.abs(y.astype(int) - ry).max() <= 2
+    assert np.abs(u.astype(int) - ru).max() <= 3 and np.abs(v.astype(int) - rv).max() <= 3

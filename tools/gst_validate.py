@@ -42,7 +42,7 @@ MATRIX = {0: "bt601", 1: "bt709", 2: "bt2020"}
 
 def colorimetry(matrix: int, rng: int) -> str:
     # explicit form so that range is pinned too: "1:4:..." = full, "2:..." = limited (16-235)
-    m = {0: 4, 1: 3, 2: 9}[matrix]        # GstVideoColorMatrix: BT709=3, BT601=4, BT2020=9 (enum order FCC=2)
+    m = {0: 4, 1: 3, 2: 6}[matrix]        # GstVideoColorMatrix: RGB=1, FCC=2, BT709=3, BT601=4, SMPTE240M=5, BT2020=6
     r = 1 if rng == 1 else 2              # GstVideoColorRange: 0_255=1, 16_235=2
     return f"{r}:{m}:0:0"                 # transfer and primaries unknown: no gamma/primaries conversion
 

@@ -16,7 +16,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200vc.so")
+LIB_PATH = os.environ.get("B200VC_LIB") or os.path.join(_HERE, "libb200vc.so")   # (override: A/B builds of the library)
 
 OK = 0
 ERR_INVALID_ARG, ERR_UNSUPPORTED, ERR_NOT_NEGOTIATED, ERR_CUDA, ERR_NO_DEVICE, ERR_ALIGNMENT, ERR_NOMEM, ERR_BAD_TICKET = range(1, 9)

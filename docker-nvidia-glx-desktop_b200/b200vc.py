@@ -26,7 +26,7 @@ RANGE_LIMITED, RANGE_FULL = 0, 1
 SITE_NONE, SITE_H_COSITED = 0, 1
 SCALE_GST_LQ, SCALE_BOX_2X2 = 0, 1
 IN_BGRX, IN_RGBX, IN_XRGB, IN_XBGR = 0, 1, 2, 3
-FLAG_DAMAGE_MAP, FLAG_FORCE_TWO_PASS, FLAG_REGISTER_HOST, FLAG_FORCE_GENERIC_FUSED, FLAG_ZERO_COPY = 1, 2, 4, 8, 16
+FLAG_DAMAGE_MAP, FLAG_FORCE_TWO_PASS, FLAG_REGISTER_HOST, FLAG_FORCE_GENERIC_FUSED, FLAG_ZERO_COPY, FLAG_ZERO_COPY_OUT = 1, 2, 4, 8, 16, 32
 
 # every symbol include/b200vc.h declares
 SYMBOLS = [

@@ -643,12 +643,29 @@ int submit_locked(b200vc_ctx *c, const b200vc_frame *f, int bands, uint64_t *tic
 
     uint8_t *d_cur = ss.d_in[ss.cur];
     const uint8_t *d_prev = (f->damage && ss.have_prev) ? ss.d_in[ss.cur ^ 1] : nullptr;
-    const PlaneSet out = plane_set(slot.d_out, c->d_off, c->d_pitch, 0, g.out_format);
+    PlaneSet out = plane_set(slot.d_out, c->d_off, c->d_pitch, 0, g.out_format);
+    uint8_t *d_dmg = slot.d_dmg;
+
+    // B200VC_FLAG_ZERO_COPY_OUT: kernels store planes (and map) into the caller's page-locked memory
+    bool direct_out = false;
+    if ((g.flags & B200VC_FLAG_ZERO_COPY_OUT) && out_pinned) {
+        void *d_pl[3] = { nullptr, nullptr, nullptr }, *d_map = nullptr;
+        bool ok = true;
+        for (int i = 0; i < n_planes && ok; i++)
+            ok = cudaHostGetDevicePointer(&d_pl[i], f->planes[i], 0) == cudaSuccess && aligned16(d_pl[i]) && f->pitches[i] % 16 == 0;
+        if (ok && f->damage) ok = cudaHostGetDevicePointer(&d_map, f->damage, 0) == cudaSuccess;
+        if (!ok) cudaGetLastError();
+        if (ok) {
+            for (int i = 0; i < n_planes; i++) { out.p[i] = (uint8_t *)d_pl[i];  out.pitch[i] = (long long)f->pitches[i]; }
+            if (f->damage) d_dmg = (uint8_t *)d_map;
+            direct_out = true;
+        }
+    }
 
     // the copy engine must not overwrite a frame the previous kernel of this session still reads
     if (ss.ev_valid) CU_TRY(c, cudaStreamWaitEvent(c->s_h2d, ss.ev_kernel, 0));
     if (f->damage && !d_prev)
-        CU_TRY(c, cudaMemsetAsync(slot.d_dmg, 1, (size_t)c->mb_w * c->mb_h, c->s_k));
+        CU_TRY(c, cudaMemsetAsync(d_dmg, 1, (size_t)c->mb_w * c->mb_h, c->s_k));
 
     const int mb_rows_per_band = (c->mb_h + bands - 1) / bands;
     for (int b = 0; b < bands; b++) {
@@ -670,9 +687,13 @@ int submit_locked(b200vc_ctx *c, const b200vc_frame *f, int bands, uint64_t *tic
         if (c->path != 0) continue;      // scaled paths launch once, after the whole frame is up
         CU_TRY(c, cudaEventRecord(c->ev_band_h2d[b], c->s_h2d));
         CU_TRY(c, cudaStreamWaitEvent(c->s_k, c->ev_band_h2d[b], 0));
-        rc = enqueue_kernels(c, d_cur, c->d_in_pitch, 0, d_prev, c->d_in_pitch, 0, out, d_prev ? slot.d_dmg : nullptr, 0,
+        rc = enqueue_kernels(c, d_cur, c->d_in_pitch, 0, d_prev, c->d_in_pitch, 0, out, d_prev ? d_dmg : nullptr, 0,
                              row0, rows, 1, c->s_k);
         if (rc) return rc;
+        if (direct_out) {                               // the kernel's own stores are the D2H traffic
+            for (int i = 0; i < n_planes; i++) c->stats.d2h_bytes += out_row_bytes[i] * (i ? (rows + 1) / 2 : rows);
+            continue;
+        }
         CU_TRY(c, cudaEventRecord(c->ev_band_k[b], c->s_k));
         CU_TRY(c, cudaStreamWaitEvent(c->s_d2h, c->ev_band_k[b], 0));
         // D2H of this band's rows of every plane
@@ -693,7 +714,7 @@ int submit_locked(b200vc_ctx *c, const b200vc_frame *f, int bands, uint64_t *tic
         if (rc) return rc;
         CU_TRY(c, cudaEventRecord(c->ev_band_k[0], c->s_k));
         CU_TRY(c, cudaStreamWaitEvent(c->s_d2h, c->ev_band_k[0], 0));
-        for (int i = 0; i < n_planes; i++) {
+        for (int i = 0; i < n_planes && !direct_out; i++) {
             uint8_t *hdst = out_pinned ? (uint8_t *)f->planes[i] : slot.h_out + c->d_off[i];
             const size_t hp = out_pinned ? f->pitches[i] : c->d_pitch[i];
             CU_TRY(c, cudaMemcpy2DAsync(hdst, hp, slot.d_out + c->d_off[i], c->d_pitch[i], out_row_bytes[i], out_rows[i],
@@ -703,7 +724,11 @@ int submit_locked(b200vc_ctx *c, const b200vc_frame *f, int bands, uint64_t *tic
     }
     CU_TRY(c, cudaEventRecord(ss.ev_kernel, c->s_k));
     ss.ev_valid = true;
-    if (f->damage) {
+    if (direct_out) {
+        for (int i = 0; i < n_planes && c->path != 0; i++) c->stats.d2h_bytes += out_row_bytes[i] * out_rows[i];
+        if (f->damage) c->stats.d2h_bytes += (size_t)c->mb_w * c->mb_h;
+        CU_TRY(c, cudaStreamWaitEvent(c->s_d2h, ss.ev_kernel, 0));      // "done" is recorded on the D2H stream
+    } else if (f->damage) {
         uint8_t *hdst = out_pinned ? f->damage : slot.h_out + c->d_out_size;
         CU_TRY(c, cudaStreamWaitEvent(c->s_d2h, ss.ev_kernel, 0));
         CU_TRY(c, cudaMemcpyAsync(hdst, slot.d_dmg, (size_t)c->mb_w * c->mb_h, cudaMemcpyDeviceToHost, c->s_d2h));

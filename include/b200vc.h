@@ -68,6 +68,10 @@ enum { B200VC_IN_BGRX = 0, B200VC_IN_RGBX = 1, B200VC_IN_XRGB = 2, B200VC_IN_XBG
                                              kernel reads the frame from host memory and writes the
                                              planes to host memory itself (one launch, no copy
                                              engine, both PCIe directions busy at once)           */
+#define B200VC_FLAG_ZERO_COPY_OUT   0x20u /* page-locked output planes: the kernels store the planes
+                                             (and the damage map) straight into host memory; the
+                                             input still arrives through the copy engine. Saves the
+                                             D2H copies and their per-band set-up cost            */
 #define B200VC_FLAG_REGISTER_HOST   0x4u  /* page-lock caller buffers on first sight (XShm pool)
                                              instead of staging them through a pinned ring        */
 

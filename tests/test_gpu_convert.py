@@ -350,3 +350,37 @@ def test_zero_copy_mode(conv, orc):
     conv.stop()
     pin_in.free()
     pin_out.free()
+
+
+def test_zero_copy_out_mode(conv, orc):
+    """B200VC_FLAG_ZERO_COPY_OUT: input through the copy engine, planes and damage map stored by the
+    kernels straight into page-locked host memory — unscaled with damage, and scaled."""
+    w, h = 1920, 1080
+    total, off, pit = b200vc.default_layout(0, w, h)
+    mbh, mbw = (h + 15) // 16, (w + 15) // 16
+    pin_in, pin_out = b200vc.PinnedBuffer(w * h * 4), b200vc.PinnedBuffer(total + mbh * mbw)
+    planes = (C.c_void_p * 3)(*[pin_out.ptr + o for o in off])
+    pits = (C.c_size_t * 3)(*pit)
+    conv.set_info(w, h, matrix=0, range_=0, chroma_site=1, n_bands=4, flags=b200vc.FLAG_ZERO_COPY_OUT | b200vc.FLAG_DAMAGE_MAP)
+    prev = None
+    for k in range(3):
+        f = orc.synth("desk", w, h, 70 + k, out=pin_in.array.reshape(h, w * 4))
+        host = np.array(f)
+        pin_out.array[:] = 0
+        assert conv.lib.b200vc_convert(conv.ctx, pin_in.ptr, w * 4, planes, pits, pin_out.ptr + total) == 0
+        assert_planes_equal(plane_views(pin_out.array[:total], off, pit, 0, w, h), _oracle_planes(orc, host, 0, 0, 0, 1), f"frame {k}")
+        assert np.array_equal(pin_out.array[total:].reshape(mbh, mbw), orc.damage_map(host, prev)), f"frame {k} damage"
+        prev = host
+    st = conv.stats()
+    assert st.d2h_bytes == 3 * (total + mbh * mbw) and st.h2d_bytes == 3 * w * h * 4
+    conv.set_info(w, h, w // 2, h // 2, out_format=1, matrix=1, range_=0, chroma_site=1, flags=b200vc.FLAG_ZERO_COPY_OUT)
+    t2, o2, p2 = b200vc.default_layout(1, w // 2, h // 2)
+    f = orc.synth("rand", w, h, 3, out=pin_in.array.reshape(h, w * 4))
+    pl = (C.c_void_p * 3)(pin_out.ptr + o2[0], pin_out.ptr + o2[1], None)
+    pt = (C.c_size_t * 3)(*p2)
+    assert conv.lib.b200vc_convert(conv.ctx, pin_in.ptr, w * 4, pl, pt, None) == 0
+    want = orc.convert(np.array(f), 1, 1, 0, 1, out_size=(w // 2, h // 2))
+    assert_planes_equal(plane_views(pin_out.array[:t2], o2, p2, 1, w // 2, h // 2), plane_views(*want, 1, w // 2, h // 2), "scaled")
+    conv.stop()
+    pin_in.free()
+    pin_out.free()

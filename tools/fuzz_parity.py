@@ -40,7 +40,7 @@ def main():
         m = int(rng.integers(0, 3))
         scaling = (ow, oh) != (iw, ih)
         flags = int(rng.choice([0, b200vc.FLAG_FORCE_TWO_PASS, b200vc.FLAG_FORCE_GENERIC_FUSED])) if scaling else \
-            int(rng.choice([0, b200vc.FLAG_DAMAGE_MAP, b200vc.FLAG_ZERO_COPY]))
+            int(rng.choice([0, b200vc.FLAG_DAMAGE_MAP, b200vc.FLAG_ZERO_COPY, b200vc.FLAG_ZERO_COPY_OUT]))
         f = rng.integers(0, 256, (ih, iw, 4), dtype=np.uint8)
         try:
             conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=m, range_=rg, chroma_site=site, scale_mode=mode, flags=flags,

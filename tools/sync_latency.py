@@ -9,7 +9,8 @@ h_in, h_out = b200vc.PinnedBuffer(8 * W * H * 4), b200vc.PinnedBuffer(total)
 h_in.array[:] = 77
 planes = (C.c_void_p * 3)(*[h_out.ptr + o for o in off]); pits = (C.c_size_t * 3)(*pit)
 conv = b200vc.Converter(0)
-for bands, flags in [(1, 0), (2, 0), (4, 0), (2, b200vc.FLAG_ZERO_COPY)]:
+for bands, flags in [(1, 0), (2, 0), (4, 0), (2, b200vc.FLAG_ZERO_COPY), (1, b200vc.FLAG_ZERO_COPY_OUT), (2, b200vc.FLAG_ZERO_COPY_OUT),
+                     (4, b200vc.FLAG_ZERO_COPY_OUT), (8, b200vc.FLAG_ZERO_COPY_OUT), (17, b200vc.FLAG_ZERO_COPY_OUT)]:
     conv.set_info(W, H, matrix=0, range_=0, chroma_site=1, n_bands=bands, flags=flags)
     for i in range(20):
         conv.lib.b200vc_convert(conv.ctx, h_in.ptr + (i % 8) * W * H * 4, W * 4, planes, pits, None)
@@ -20,7 +21,7 @@ for bands, flags in [(1, 0), (2, 0), (4, 0), (2, b200vc.FLAG_ZERO_COPY)]:
     dt = time.perf_counter() - t0
     print(f"bands={bands:2d} flags={flags:2d}: {n / dt:8.1f} frames/s  {dt / n * 1e6:7.1f} us/frame", flush=True)
 # batch of 8 sessions, copy engines vs zero-copy
-for flags in (0, b200vc.FLAG_ZERO_COPY):
+for flags in (0, b200vc.FLAG_ZERO_COPY, b200vc.FLAG_ZERO_COPY_OUT):
     conv.set_info(W, H, matrix=0, range_=0, chroma_site=1, max_sessions=8, n_inflight=8, flags=flags)
     outs = b200vc.PinnedBuffer(8 * total)
     frames = (b200vc.Frame * 8)(*[conv.make_frame(h_in.ptr + s * W * H * 4, W * 4, outs.ptr + s * total, off, pit, session=s) for s in range(8)])

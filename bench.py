@@ -204,6 +204,9 @@ def run_gpu(args, rank: int, local_rank: int, world: int):
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the GPU arm has no CPU fallback")
+    import sessions
+    # before any pinned allocation: put this rank on the cores (and so the memory) next to its GPU
+    numa = sessions.bind_to_gpu_numa(local_rank) if os.environ.get("B200VC_NUMA_BIND", "1") != "0" else {"bound": False, "off": True}
     torch.cuda.set_device(local_rank)
     dist = None
     if world > 1:
@@ -227,8 +230,6 @@ def run_gpu(args, rank: int, local_rank: int, world: int):
         if dist is not None:
             dist.barrier()
         torch.cuda.synchronize()
-
-    import sessions
 
     def max_over_ranks(seconds: float) -> float:
         return sessions.job_throughput(FRAMES_PER_STEP * args.steps, seconds, dist, "cuda")[1]
@@ -371,7 +372,7 @@ def run_gpu(args, rank: int, local_rank: int, world: int):
                     "frac_of_pcie_ceiling": round(e2e_fps / world / pcie_fps, 4),
                     "frac_of_pcie_gen5_x16_raw_63GBs": round(e2e_fps / world * IN_BYTES / 63.02e9, 4),
                     "pcie_ceiling_how": "raw pinned H2D 8.3 MB + D2H 3.1 MB copies in flight together, no kernel, rank 0",
-                    "sync_single_session_fps": round(sync_fps, 1)},
+                    "sync_single_session_fps": round(sync_fps, 1), "numa": numa},
             "gpu_launches": gpu_launches,
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                          "frac": round(achieved / peak, 4), "traffic": committed_traffic(),

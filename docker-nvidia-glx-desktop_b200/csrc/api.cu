@@ -72,6 +72,8 @@ struct b200vc_ctx {
     // scaling
     Tap *d_taps = nullptr;
     ScaleTables tab = { nullptr, nullptr, nullptr, nullptr };
+    FusedTaps ft = { nullptr, nullptr, nullptr, nullptr, nullptr };
+    int tile_h = K2_TILE_H;
     int box_w = 0, box_h = 0;
     size_t smem_bytes = 0;
     bool fused2x = false;                      // path 1 runs the exact-2:1 register kernel
@@ -199,11 +201,46 @@ void build_box_taps(int out_n, std::vector<Tap> &t)
 
 inline int tidx(Tap t) { return (int)(t & 0xffff); }
 inline int tstep(Tap t) { return (int)((t >> 24) & 1); }
+inline int tfrac(Tap t) { return (int)((t >> 16) & 0xff); }
+
+// The general fused kernel's form of the tables (FusedTaps, kernels.cuh), as one blob of 32-bit words:
+// [hy_i | hy_w | vy pairs | vc pairs | hc quads], every section a multiple of 4 words.
+struct FusedTapBlob { std::vector<uint32_t> w; size_t hy_i, hy_w, vy, vc, hc; };
+
+uint32_t v_weights(Tap t)
+{
+    const int p1 = tstep(t) ? tfrac(t) : 0;          // clamped second line: all weight on the first
+    const int a = 256 - 4 * p1, b = 4 * p1;
+    const int a1 = std::min(a, 255), b1 = std::min(b, 255);
+    return (uint32_t)a1 | ((uint32_t)(a - a1) << 8) | ((uint32_t)b1 << 16) | ((uint32_t)(b - b1) << 24);
+}
+
+void build_fused_taps(const std::vector<Tap> &hy, const std::vector<Tap> &vy, const std::vector<Tap> &hc,
+                      const std::vector<Tap> &vc, FusedTapBlob &o)
+{
+    o.w.clear();
+    o.hy_i = o.w.size();
+    for (Tap t : hy) o.w.push_back((uint32_t)tidx(t));
+    o.hy_w = o.w.size();
+    for (Tap t : hy) {
+        const uint32_t f = tstep(t) ? (uint32_t)tfrac(t) : 0u;
+        o.w.push_back((255u - f) | (1u << 8) | (f << 16));
+    }
+    o.vy = o.w.size();
+    for (Tap t : vy) { o.w.push_back((uint32_t)tidx(t));  o.w.push_back(v_weights(t)); }
+    o.vc = o.w.size();
+    for (Tap t : vc) { o.w.push_back((uint32_t)tidx(t));  o.w.push_back(v_weights(t)); }
+    o.hc = o.w.size();
+    for (Tap t : hc) {
+        const uint32_t f = tstep(t) ? (uint32_t)tfrac(t) : 0u;
+        o.w.push_back((uint32_t)tidx(t));  o.w.push_back(256u - f);  o.w.push_back(f);  o.w.push_back(0u);
+    }
+}
 
 // Source window per output tile, mirrored from k2_fused_scale_kernel phase 0; returns the box that
 // covers every tile.
 void fused_box(const b200vc_config &c, const std::vector<Tap> &hy, const std::vector<Tap> &vy,
-               const std::vector<Tap> &hc, const std::vector<Tap> &vc, int &box_w, int &box_h)
+               const std::vector<Tap> &hc, const std::vector<Tap> &vc, int tile_h, int &box_w, int &box_h)
 {
     const int site = c.chroma_site == B200VC_SITE_H_COSITED ? 1 : 0;
     box_w = box_h = 0;
@@ -213,8 +250,8 @@ void fused_box(const b200vc_config &c, const std::vector<Tap> &hy, const std::ve
         int last = std::max(tidx(hy[x1]) + tstep(hy[x1]), 2 * (tidx(hc[x1 >> 1]) + tstep(hc[x1 >> 1])) + 1);
         box_w = std::max(box_w, last - sx + 1);
     }
-    for (int y0 = 0; y0 < c.out_h; y0 += K2_TILE_H) {
-        const int y1 = std::min(y0 + K2_TILE_H, c.out_h) - 1;
+    for (int y0 = 0; y0 < c.out_h; y0 += tile_h) {
+        const int y1 = std::min(y0 + tile_h, c.out_h) - 1;
         int sy = std::min(tidx(vy[y0]), 2 * tidx(vc[y0 >> 1])) & ~1;
         int last = std::max(tidx(vy[y1]) + tstep(vy[y1]), 2 * (tidx(vc[y1 >> 1]) + tstep(vc[y1 >> 1])) + 1);
         box_h = std::max(box_h, last - sy + 1);
@@ -374,13 +411,16 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         }
         FusedScaleParams p;
         memset(&p, 0, sizeof p);
-        p.out = out;  p.tab = c->tab;
+        p.out = out;  p.tab = c->tab;  p.ft = c->ft;
         p.in_w = g.in_w;  p.in_h = g.in_h;  p.out_w = g.out_w;  p.out_h = g.out_h;
-        p.box_w = c->box_w;  p.box_h = c->box_h;  p.n_frames = n_frames;
+        p.box_w = c->box_w;  p.box_h = c->box_h;  p.tile_h = c->tile_h;  p.n_frames = n_frames;
         p.box2x2 = g.scale_mode == B200VC_SCALE_BOX_2X2;  p.mx = c->mx;
-        const uint32_t items_x = (uint32_t)c->box_w / 4;
+        // items per line pair of the window: 8-column items over box_w/4 groups, or one group fewer
+        // when a tile's first group is pure halo
+        const uint32_t groups_x = (uint32_t)c->box_w / 4;
+        const uint32_t items_x = groups_x, items_x1 = std::max(groups_x - 1, 1u);
         p.inv_items_x = (65536u + items_x - 1) / items_x;
-        p.inv_items_x1 = items_x > 1 ? (65536u + items_x - 2) / (items_x - 1) : 65536u;
+        p.inv_items_x1 = (65536u + items_x1 - 1) / items_x1;
         CU_TRY(c, launch_fused_scale(map, p, g.out_format, site, st));
         c->stats.kernel_launches += 1;
         return B200VC_OK;
@@ -503,16 +543,34 @@ int create_impl(b200vc_ctx *c)
             // chroma planes of odd frames round up, like the intermediate frame's own layout
             build_h_taps((g.in_w + 1) / 2, (g.out_w + 1) / 2, hc);  build_v_taps((g.in_h + 1) / 2, (g.out_h + 1) / 2, vc);
         }
-        const size_t n = hy.size() + vy.size() + hc.size() + vc.size();
-        CU_TRY(c, cudaMalloc(&c->d_taps, n * sizeof(Tap)));
+        FusedTapBlob blob;
+        build_fused_taps(hy, vy, hc, vc, blob);
+        const size_t n = hy.size() + vy.size() + hc.size() + vc.size();       // every size a multiple of 4
+        CU_TRY(c, cudaMalloc(&c->d_taps, (n + blob.w.size()) * sizeof(Tap)));
         Tap *d = c->d_taps;
+        {
+            const uint32_t *b = d + n;                                        // 16-byte aligned: n % 4 == 0
+            CU_TRY(c, cudaMemcpy(d + n, blob.w.data(), blob.w.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+            c->ft.hy_i = b + blob.hy_i;  c->ft.hy_w = b + blob.hy_w;
+            c->ft.vy = reinterpret_cast<const uint2 *>(b + blob.vy);
+            c->ft.vc = reinterpret_cast<const uint2 *>(b + blob.vc);
+            c->ft.hc = reinterpret_cast<const uint4 *>(b + blob.hc);
+        }
         c->tab.hy = d;  CU_TRY(c, cudaMemcpy(d, hy.data(), hy.size() * sizeof(Tap), cudaMemcpyHostToDevice));  d += hy.size();
         c->tab.vy = d;  CU_TRY(c, cudaMemcpy(d, vy.data(), vy.size() * sizeof(Tap), cudaMemcpyHostToDevice));  d += vy.size();
         c->tab.hc = d;  CU_TRY(c, cudaMemcpy(d, hc.data(), hc.size() * sizeof(Tap), cudaMemcpyHostToDevice));  d += hc.size();
         c->tab.vc = d;  CU_TRY(c, cudaMemcpy(d, vc.data(), vc.size() * sizeof(Tap), cudaMemcpyHostToDevice));
 
-        fused_box(g, hy, vy, hc, vc, c->box_w, c->box_h);
+        c->tile_h = K2_TILE_H;
+        fused_box(g, hy, vy, hc, vc, c->tile_h, c->box_w, c->box_h);
         c->smem_bytes = fused_scale_smem_bytes(c->box_w, c->box_h);
+        // the kernel is register-limited to 6 CTAs per SM; a window that leaves room for fewer (ratios
+        // towards 3:1 and beyond) is halved in height instead
+        if (c->smem_bytes + 4096 > (size_t)c->prop.sharedMemPerMultiprocessor / 6) {
+            c->tile_h = K2_TILE_H / 2;
+            fused_box(g, hy, vy, hc, vc, c->tile_h, c->box_w, c->box_h);
+            c->smem_bytes = fused_scale_smem_bytes(c->box_w, c->box_h);
+        }
         const bool fits = c->box_w <= 256 && c->box_h <= 256 &&
                           c->smem_bytes + 1024 <= (size_t)c->prop.sharedMemPerBlockOptin;
         const bool all_even = !((g.in_w | g.in_h | g.out_w | g.out_h) & 1);      // the fused kernels assume it
@@ -919,7 +977,7 @@ int b200vc_get_info(const b200vc_ctx *c, b200vc_info *info)
     memset(info, 0, sizeof *info);
     info->path = c->path;
     info->tile_w = c->path == 1 ? K2_TILE_W : K1_TILE_W;
-    info->tile_h = c->path == 1 ? K2_TILE_H : K1_TILE_H;
+    info->tile_h = c->path == 1 ? (c->fused2x ? K2_TILE_H : c->tile_h) : K1_TILE_H;
     info->fused_2to1 = c->fused2x ? 1 : 0;
     info->box_w = c->box_w;  info->box_h = c->box_h;
     info->smem_bytes = c->path == 1 ? (int)c->smem_bytes : 3 * 1024 + 32;

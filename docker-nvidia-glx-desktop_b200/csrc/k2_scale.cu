@@ -24,7 +24,6 @@ namespace b200vc {
 namespace {
 
 constexpr int TW = K2_TILE_W;
-constexpr int TH = K2_TILE_H;
 
 __device__ __forceinline__ int tap_idx(Tap t) { return (int)(t & 0xffffu); }
 __device__ __forceinline__ int tap_frac(Tap t) { return (int)((t >> 16) & 0xffu); }
@@ -40,13 +39,69 @@ __device__ __forceinline__ uint32_t smem_u32(const void *p)
 // video_scale_v_2tap_u8 (lq): a + (((b-a)*p1 + 32) >> 6), which equals (a*(64-p1) + b*p1 + 32) >> 6
 // (no clamp needed for 0 <= p1 <= 64) and is evaluated as one dp4a on the lanes' high bytes.
 
-template <int FMT, int SITE, bool NEG>
+// Phase 1 of the general fused kernel: one item = 8 columns x 2 lines of the window (two 4-column
+// groups; `two` false: only the first), BGRx in s_src -> Y bytes in s_yf and filtered, vertically
+// averaged (u,v) pairs in s_cf. kx = first group's index in the line pair, sx0 = window's frame column.
+template <int SITE, bool NEG, bool EDGE>
+__device__ __forceinline__ void convert_item(const uint32_t *s_src, uint8_t *s_yf, uint32_t *s_cf, int bw, int kx, int ky,
+                                             int sx0, int in_w, bool two, const Matrix &m)
+{
+    const uint32_t *ra = s_src + (2 * ky) * bw + 4 * kx, *rb = ra + bw;
+    uint8_t *ya = s_yf + (2 * ky) * bw + 4 * kx;
+    uint32_t *cf = s_cf + ky * (bw >> 1) + 2 * kx;
+    const int ac = sx0 + 4 * kx;                          // frame column of pixel 0 (multiple of 4)
+    uint32_t la = 0, lb = 0;                              // left chroma neighbours of the group
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        if (h == 1 && !two) break;
+        const uint4 a = *reinterpret_cast<const uint4 *>(ra + 4 * h);
+        const uint4 b = *reinterpret_cast<const uint4 *>(rb + 4 * h);
+        *reinterpret_cast<uint32_t *>(ya + 4 * h) =
+            pack_luma4(luma_sum(a.x, m), luma_sum(a.y, m), luma_sum(a.z, m), luma_sum(a.w, m));
+        *reinterpret_cast<uint32_t *>(ya + bw + 4 * h) =
+            pack_luma4(luma_sum(b.x, m), luma_sum(b.y, m), luma_sum(b.z, m), luma_sum(b.w, m));
+
+        const uint32_t pa0 = chroma_pair<NEG>(a.x, m), pa1 = chroma_pair<NEG>(a.y, m);
+        const uint32_t pa2 = chroma_pair<NEG>(a.z, m), pa3 = chroma_pair<NEG>(a.w, m);
+        const uint32_t pb0 = chroma_pair<NEG>(b.x, m), pb1 = chroma_pair<NEG>(b.y, m);
+        const uint32_t pb2 = chroma_pair<NEG>(b.z, m), pb3 = chroma_pair<NEG>(b.w, m);
+        uint32_t c0, c1;
+        if (SITE == 0) {
+            c0 = avg2(avg2(pa0, pa1), avg2(pb0, pb1));
+            c1 = avg2(avg2(pa2, pa3), avg2(pb2, pb3));
+        } else {
+            if (h == 0) {
+                // frame column 0 takes itself; the window's first group has no left neighbour (its
+                // first chroma column is halo and is never consumed)
+                la = pa0;  lb = pb0;
+                if (ac != 0 && kx > 0) {
+                    la = chroma_pair<NEG>(ra[-1], m);
+                    lb = chroma_pair<NEG>(rb[-1], m);
+                }
+            }
+            // right neighbours: the frame's last even column (in_w - 2, in_w > 2) takes itself
+            const bool e0 = EDGE && in_w > 2 && ac + 4 * h == in_w - 2;
+            const bool e2 = EDGE && in_w > 2 && ac + 4 * h + 2 == in_w - 2;
+            c0 = avg2(filt121(la, pa0, e0 ? pa0 : pa1), filt121(lb, pb0, e0 ? pb0 : pb1));
+            c1 = avg2(filt121(pa1, pa2, e2 ? pa2 : pa3), filt121(pb1, pb2, e2 ? pb2 : pb3));
+            la = pa3;  lb = pb3;
+        }
+        *reinterpret_cast<uint2 *>(cf + 2 * h) = make_uint2(c0, c1);
+    }
+}
+
+template <int FMT, int SITE, bool NEG, int TILE_H>
 __global__ void __launch_bounds__(256)
 k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedScaleParams p)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ int s_org[3];               // window origin x, y; first 4-column item that is not pure halo
+    // this tile's taps (FusedTaps) as offsets into the window's planes, staged while the TMA load flies
+    __shared__ uint32_t s_hyo[TW], s_hyw[TW];
+    __shared__ uint2 s_vy[TILE_H], s_vc[TILE_H / 2];
+    __shared__ __align__(16) uint4 s_hc[TW / 2];
+    __shared__ __align__(16) uint8_t s_out[TW * TILE_H * 3 / 2];   // output tile: Y, then U and V (or UV) tiles
 
     const int bw = p.box_w, bh = p.box_h;
     uint32_t *s_src = reinterpret_cast<uint32_t *>(smem);                 // [bh][bw] pixels
@@ -54,7 +109,7 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
     uint32_t *s_cf = reinterpret_cast<uint32_t *>(s_yf + (size_t)bw * bh); // [bh/2][bw/2] (u,v) pairs
 
     const int tid = threadIdx.x;
-    const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH;
+    const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TILE_H;
     const int frame = blockIdx.z;
 
     // ---- phase 0: source window origin, TMA load -------------------------------------------
@@ -84,6 +139,30 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
     __syncthreads();
     const int sx0 = s_org[0], sy0 = s_org[1], kfirst = s_org[2];
     {
+        // warps 0-1: luma columns, warp 2: luma rows, warp 3: chroma columns, warp 4: chroma rows
+        // (indices clamped to the tables; entries past the frame edge are never consumed)
+        const int t = tid & 31, w = tid >> 5;
+        if (w < 2) {
+            const int x = min(x0 + tid, p.out_w - 1);
+            s_hyo[tid] = p.ft.hy_i[x] - (uint32_t)sx0;
+            s_hyw[tid] = p.ft.hy_w[x];
+        } else if (w == 2) {
+            if (t < TILE_H) {
+                const uint2 v = p.ft.vy[min(y0 + t, p.out_h - 1)];
+                s_vy[t] = make_uint2((uint32_t)(((int)v.x - sy0) * bw), v.y);
+            }
+        } else if (w == 3) {
+            uint4 h = p.ft.hc[min((x0 >> 1) + t, (p.out_w >> 1) - 1)];
+            h.x -= (uint32_t)(sx0 >> 1);
+            s_hc[t] = h;
+        } else if (w == 4) {
+            if (t < TILE_H / 2) {
+                const uint2 v = p.ft.vc[min((y0 >> 1) + t, (p.out_h >> 1) - 1)];
+                s_vc[t] = make_uint2((uint32_t)(((int)v.x - (sy0 >> 1)) * (bw >> 1)), v.y);
+            }
+        }
+    }
+    {
         const uint32_t bar = smem_u32(&s_bar);
         uint32_t done = 0;
         while (!done) {
@@ -95,123 +174,116 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
         }
     }
 
-    // ---- phase 1: convert the window (4 columns x 2 lines per item) ------------------------------
-    const Matrix &m = p.mx;
-    // items are walked without divisions (host-made reciprocal for the start, increments after),
-    // and a first item column that holds nothing but halo is skipped
-    const int items_x = (bw >> 2) - kfirst, n_items = items_x * (bh >> 1);
-    const uint32_t inv = kfirst ? p.inv_items_x1 : p.inv_items_x;
-    int ky = (int)(((uint32_t)tid * inv) >> 16), kxr = tid - ky * items_x;
-    const int dky = (int)((256u * inv) >> 16), dkx = 256 - dky * items_x;
-    for (int it = tid; it < n_items; it += 256, kxr += dkx, ky += dky) {
-        if (kxr >= items_x) { kxr -= items_x; ky++; }
-        const int kx = kxr + kfirst;
-        const uint32_t *ra = s_src + (size_t)(2 * ky) * bw + 4 * kx;
-        const uint32_t *rb = ra + bw;
-        const uint4 a = *reinterpret_cast<const uint4 *>(ra);
-        const uint4 b = *reinterpret_cast<const uint4 *>(rb);
-
-        uint32_t ya4 = pack_luma4(luma_sum(a.x, m), luma_sum(a.y, m), luma_sum(a.z, m), luma_sum(a.w, m));
-        uint32_t yb4 = pack_luma4(luma_sum(b.x, m), luma_sum(b.y, m), luma_sum(b.z, m), luma_sum(b.w, m));
-        *reinterpret_cast<uint32_t *>(s_yf + (size_t)(2 * ky) * bw + 4 * kx) = ya4;
-        *reinterpret_cast<uint32_t *>(s_yf + (size_t)(2 * ky + 1) * bw + 4 * kx) = yb4;
-
-        const uint32_t pa0 = chroma_pair<NEG>(a.x, m), pa1 = chroma_pair<NEG>(a.y, m);
-        const uint32_t pa2 = chroma_pair<NEG>(a.z, m), pa3 = chroma_pair<NEG>(a.w, m);
-        const uint32_t pb0 = chroma_pair<NEG>(b.x, m), pb1 = chroma_pair<NEG>(b.y, m);
-        const uint32_t pb2 = chroma_pair<NEG>(b.z, m), pb3 = chroma_pair<NEG>(b.w, m);
-        uint32_t c0, c1;
-        if (SITE == 0) {
-            c0 = avg2(avg2(pa0, pa1), avg2(pb0, pb1));
-            c1 = avg2(avg2(pa2, pa3), avg2(pb2, pb3));
-        } else {
-            const int ac = sx0 + 4 * kx;                  // absolute column of pixel 0 (multiple of 4)
-            // left neighbours: column 0 takes itself; the window's first item has none (its
-            // first chroma column is halo and is never consumed)
-            uint32_t la = pa0, lb = pb0;
-            if (ac != 0 && kx > 0) {
-                la = chroma_pair<NEG>(ra[-1], m);
-                lb = chroma_pair<NEG>(rb[-1], m);
-            }
-            const uint32_t l2a = pa1, l2b = pb1;          // ac % 4 == 0, so pixel 2 is never column 0
-            // right neighbours: the last even column (in_w-2, in_w > 2) takes itself
-            const bool e0 = (p.in_w > 2) && (ac == p.in_w - 2);
-            const bool e2 = (p.in_w > 2) && (ac + 2 == p.in_w - 2);
-            c0 = avg2(filt121(la, pa0, e0 ? pa0 : pa1), filt121(lb, pb0, e0 ? pb0 : pb1));
-            c1 = avg2(filt121(l2a, pa2, e2 ? pa2 : pa3), filt121(l2b, pb2, e2 ? pb2 : pb3));
+    // ---- phase 1: convert the window (8 columns x 2 lines per item, as two halves) ---------------
+    // Items are walked without divisions (host-made reciprocal for the start, increments after); a
+    // first 4-column group that holds nothing but halo is skipped. The second half takes its left
+    // chroma neighbours from the first half's registers. Only tiles whose window reaches the frame's
+    // last column pay for the right-edge rule of the cosited filter (uniform branch).
+    {
+        const int items_x = (bw >> 2) - kfirst, n_items = items_x * (bh >> 1);   // 4-column groups
+        const uint32_t inv = kfirst ? p.inv_items_x1 : p.inv_items_x;
+        int ky = (int)(((uint32_t)tid * inv) >> 16), kxr = tid - ky * items_x;
+        const int dky = (int)((256u * inv) >> 16), dkx = 256 - dky * items_x;
+        const bool redge = SITE != 0 && sx0 + bw >= p.in_w;
+        for (int it = tid; it < n_items; it += 256, kxr += dkx, ky += dky) {
+            if (kxr >= items_x) { kxr -= items_x; ky++; }
+            const int kx = kxr + kfirst;
+            if (redge)
+                convert_item<SITE, NEG, true>(s_src, s_yf, s_cf, bw, kx, ky, sx0, p.in_w, false, p.mx);
+            else
+                convert_item<SITE, NEG, false>(s_src, s_yf, s_cf, bw, kx, ky, sx0, p.in_w, false, p.mx);
         }
-        *reinterpret_cast<uint2 *>(s_cf + (size_t)ky * (bw >> 1) + 2 * kx) = make_uint2(c0, c1);
     }
     __syncthreads();
 
-    // ---- phase 2a: luma, 4 output pixels per thread ------------------------------------------
-    const long long fo = (long long)frame * p.out.frame_stride;
+    // ---- phase 2: scale out of the planes into an output tile in shared memory ----------------
+    // Taps come ready to use (FusedTaps, staged above as offsets into the planes): nothing is decoded
+    // here. Both taps are always read (a clamped one has weight 0; the byte or line after the window
+    // is inside this CTA's shared memory, see fused_scale_smem_bytes). A warp covers 32 consecutive
+    // output columns of one row at a time: its byte loads fall into at most 32 consecutive words
+    // (ratio < 4), free of bank conflicts, and the row's vertical tap is a uniform load. Every sample of
+    // the tile is computed (the staged taps of columns and rows past the frame edge are clamped copies);
+    // the frame edge is applied when the tile is stored.
+    const int lane = tid & 31, wrp = tid >> 5;
     {
-        const int r = tid >> 4, c4 = (tid & 15) * 4;
-        const int y = y0 + r, x = x0 + c4;
-        if (y < p.out_h && x < p.out_w) {
-            const Tap tv = p.tab.vy[y];
-            const int i0 = tap_idx(tv) - sy0, i1 = i0 + tap_step(tv), p1 = tap_frac(tv);
-            const uint8_t *row0 = s_yf + (size_t)i0 * bw, *row1 = s_yf + (size_t)i1 * bw;
-            const uint4 th4 = *reinterpret_cast<const uint4 *>(p.tab.hy + x);   // table padded to 4
-            const Tap th[4] = { th4.x, th4.y, th4.z, th4.w };
-            // vertical tap as dp4a weights on bytes 1 and 3 (the two lines' horizontally scaled pixels
-            // are the high bytes of the two 16-bit lanes): a + (((b-a)*p1 + 32) >> 6) equals
-            // (a*(64-p1) + b*p1 + 32) >> 6, which needs no clamp
-            const uint32_t wv = ((uint32_t)(64 - p1) << 8) | ((uint32_t)p1 << 24);
-            uint32_t out = 0;
+        // luma: one output column x 4 rows per thread
+        constexpr int RPT = TILE_H / 4;           // rows per thread: 8 warps = 2 column halves x 4 row groups
+        const int c = (wrp & 1) * 32 + lane, rb = (wrp >> 1) * RPT;
+        const uint32_t wh = s_hyw[c];
+        const uint8_t *col = s_yf + (int)s_hyo[c];
 #pragma unroll
-            for (int k = 0; k < 4; k++) {
-                const int j0 = tap_idx(th[k]) - sx0, j1 = j0 + tap_step(th[k]);
-                const uint32_t f = (uint32_t)tap_frac(th[k]);
-                uint32_t d;
-                if (p.box2x2) {
-                    d = (uint32_t)(row0[j0] + row0[j0 + 1] + row1[j0] + row1[j0 + 1] + 2) >> 2;
-                } else {
-                    const uint32_t w0 = (uint32_t)row0[j0] | ((uint32_t)row1[j0] << 16);   // both lines, 16-bit lanes
-                    const uint32_t w1 = (uint32_t)row0[j1] | ((uint32_t)row1[j1] << 16);
-                    d = dp4a_uu(w0 * (256u - f) + w1 * f, wv, 32u) >> 6;
-                }
-                out |= d << (8 * k);
-            }
-            uint8_t *dst = p.out.p[0] + fo + (long long)y * p.out.pitch[0] + x;
-            if (x + 4 <= p.out_w) {
-                *reinterpret_cast<uint32_t *>(dst) = out;
+        for (int k = 0; k < RPT; k++) {
+            const uint2 tv = s_vy[rb + k];
+            const uint8_t *r0 = col + (int)tv.x, *r1 = r0 + bw;
+            uint32_t d;
+            if (p.box2x2) {
+                d = (uint32_t)(r0[0] + r0[1] + r1[0] + r1[1] + 2) << 6;
             } else {
-                for (int k = 0; k < p.out_w - x; k++) dst[k] = (uint8_t)(out >> (8 * k));
+                // [a,a,b,_] . (255-f, 1, f, 0) per line, then [A,A,B,B] . (wa1,wa2,wb1,wb2) + 128 on
+                // the two sums' high bytes; the sample is byte 1 of the result
+                const uint32_t s0 = dp4a_uu(prmt(r0[0], r0[1], 0x1400), wh, 0u);
+                const uint32_t s1 = dp4a_uu(prmt(r1[0], r1[1], 0x1400), wh, 0u);
+                d = dp4a_uu(prmt(s0, s1, 0x5511), tv.y, 128u);
             }
+            s_out[(rb + k) * TW + c] = (uint8_t)(d >> 8);
         }
     }
+    if (wrp < TILE_H / 2) {
+        // chroma: one (u,v) sample per thread, warp w does chroma row w
+        const uint4 th = s_hc[lane];
+        const uint2 tv = s_vc[wrp];
+        const int cw = bw >> 1;
+        const uint32_t *r0 = s_cf + (int)th.x + (int)tv.x, *r1 = r0 + cw;
+        uint32_t uv;                              // u in byte 1, v in byte 3
+        if (p.box2x2) {
+            uv = (((r0[0] + r0[1] + r1[0] + r1[1] + 0x00020002u) >> 2) & LANES8) << 8;
+        } else {
+            // both lanes at once: each lane's weighted sum is <= 255*256, its high byte the sample
+            const uint32_t ha = r0[0] * th.y + r0[1] * th.z;
+            const uint32_t hb = r1[0] * th.y + r1[1] * th.z;
+            const uint32_t du = dp4a_uu(prmt(ha, hb, 0x5511), tv.y, 128u);
+            const uint32_t dv = dp4a_uu(prmt(ha, hb, 0x7733), tv.y, 128u);
+            uv = prmt(du, dv, 0x5010);            // du.0, du.1, dv.0, dv.1
+        }
+        uint8_t *oc = s_out + TW * TILE_H;
+        if (FMT == 0) {
+            oc[wrp * (TW / 2) + lane] = (uint8_t)(uv >> 8);                            // U tile, then V tile
+            oc[(TW / 2) * (TILE_H / 2) + wrp * (TW / 2) + lane] = (uint8_t)(uv >> 24);
+        } else {
+            reinterpret_cast<uint16_t *>(oc)[wrp * (TW / 2) + lane] = (uint16_t)prmt(uv, 0, 0x4431);   // u, v
+        }
+    }
+    __syncthreads();
 
-    // ---- phase 2b: chroma, one (u,v) sample per thread ---------------------------------------
-    {
-        const int cr = tid >> 5, cc = tid & 31;
-        const int cy = (y0 >> 1) + cr, cx = (x0 >> 1) + cc;
-        if (cy < (p.out_h >> 1) && cx < (p.out_w >> 1)) {
-            const Tap tv = p.tab.vc[cy], th = p.tab.hc[cx];
-            const int cw = bw >> 1;
-            const int i0 = tap_idx(tv) - (sy0 >> 1), i1 = i0 + tap_step(tv), p1 = tap_frac(tv);
-            const int j0 = tap_idx(th) - (sx0 >> 1), j1 = j0 + tap_step(th), f = tap_frac(th);
-            const uint32_t *row0 = s_cf + (size_t)i0 * cw, *row1 = s_cf + (size_t)i1 * cw;
-            int du, dv;
-            if (p.box2x2) {
-                uint32_t s = ((row0[j0] + row0[j0 + 1] + row1[j0] + row1[j0 + 1] + 0x00020002u) >> 2) & LANES8;
-                du = (int)(s & 0xff);
-                dv = (int)(s >> 16);
+    // ---- phase 3: the tile leaves as 16-byte stores (4 chunks per luma row, 4 per chroma row pair) --
+    if (tid < TILE_H * 6) {
+        const long long fo = (long long)frame * p.out.frame_stride;
+        const uint8_t *src = s_out + tid * 16;
+        uint8_t *dst;
+        int n;                                    // valid bytes of this chunk, <= 0: none
+        bool row_ok;
+        if (tid < TILE_H * 4) {
+            const int r = tid >> 2, xb = x0 + (tid & 3) * 16;
+            row_ok = y0 + r < p.out_h;
+            n = p.out_w - xb;
+            dst = p.out.p[0] + fo + (long long)(y0 + r) * p.out.pitch[0] + xb;
+        } else if (FMT == 0) {
+            const int i = tid - TILE_H * 4;
+            const int pl = i / TILE_H, r = (i >> 1) & (TILE_H / 2 - 1), xb = (x0 >> 1) + (tid & 1) * 16;
+            row_ok = (y0 >> 1) + r < (p.out_h >> 1);
+            n = (p.out_w >> 1) - xb;
+            dst = p.out.p[1 + pl] + fo + (long long)((y0 >> 1) + r) * p.out.pitch[1 + pl] + xb;
+        } else {
+            const int r = (tid - TILE_H * 4) >> 2, xb = x0 + (tid & 3) * 16;
+            row_ok = (y0 >> 1) + r < (p.out_h >> 1);
+            n = p.out_w - xb;
+            dst = p.out.p[1] + fo + (long long)((y0 >> 1) + r) * p.out.pitch[1] + xb;
+        }
+        if (row_ok) {
+            if (n >= 16) {
+                *reinterpret_cast<uint4 *>(dst) = *reinterpret_cast<const uint4 *>(src);
             } else {
-                // both lanes at once: each lane's weighted sum is <= 255*256
-                const uint32_t ha = row0[j0] * (uint32_t)(256 - f) + row0[j1] * (uint32_t)f;   // high bytes of the
-                const uint32_t hb = row1[j0] * (uint32_t)(256 - f) + row1[j1] * (uint32_t)f;   // lanes: scaled u, v
-                const uint32_t uv = prmt(ha, hb, 0x7351);          // u(line 0), u(line 1), v(line 0), v(line 1)
-                du = (int)(dp4a_uu(uv, (uint32_t)(64 - p1) | ((uint32_t)p1 << 8), 32u) >> 6);
-                dv = (int)(dp4a_uu(uv, ((uint32_t)(64 - p1) << 16) | ((uint32_t)p1 << 24), 32u) >> 6);
-            }
-            if (FMT == 0) {
-                p.out.p[1][fo + (long long)cy * p.out.pitch[1] + cx] = (uint8_t)du;
-                p.out.p[2][fo + (long long)cy * p.out.pitch[2] + cx] = (uint8_t)dv;
-            } else {
-                *reinterpret_cast<uint16_t *>(p.out.p[1] + fo + (long long)cy * p.out.pitch[1] + 2 * cx) =
-                    (uint16_t)(du | (dv << 8));
+                for (int k = 0; k < n; k++) dst[k] = src[k];
             }
         }
     }
@@ -435,10 +507,17 @@ __global__ void __launch_bounds__(128) k2_plane_scale_kernel(const PlaneScalePar
 template <int FMT, int SITE>
 cudaError_t launch_fused2(const CUtensorMap &map, const FusedScaleParams &p, dim3 grid, size_t smem, cudaStream_t st)
 {
-    if (p.mx.neg)
-        k2_fused_scale_kernel<FMT, SITE, true><<<grid, 256, smem, st>>>(map, p);
-    else
-        k2_fused_scale_kernel<FMT, SITE, false><<<grid, 256, smem, st>>>(map, p);
+    if (p.tile_h == 8) {
+        if (p.mx.neg)
+            k2_fused_scale_kernel<FMT, SITE, true, 8><<<grid, 256, smem, st>>>(map, p);
+        else
+            k2_fused_scale_kernel<FMT, SITE, false, 8><<<grid, 256, smem, st>>>(map, p);
+    } else {
+        if (p.mx.neg)
+            k2_fused_scale_kernel<FMT, SITE, true, 16><<<grid, 256, smem, st>>>(map, p);
+        else
+            k2_fused_scale_kernel<FMT, SITE, false, 16><<<grid, 256, smem, st>>>(map, p);
+    }
     return cudaGetLastError();
 }
 
@@ -483,14 +562,17 @@ namespace {
 
 size_t fused_scale_smem_bytes(int box_w, int box_h)
 {
-    return (size_t)box_w * box_h * 6;
+    // source pixels + Y plane + (u,v) plane, and one spare chroma line: a clamped second tap still
+    // reads index+1 (with weight 0), which for the last chroma line lies just behind the plane
+    return (size_t)box_w * box_h * 6 + (size_t)box_w * 2 + 16;
 }
 
 cudaError_t fused_scale_prepare(size_t smem_bytes)
 {
     cudaError_t e;
 #define B200VC_SET(F, S, N) \
-    if ((e = set_smem(k2_fused_scale_kernel<F, S, N>, smem_bytes)) != cudaSuccess) return e;
+    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 8>, smem_bytes)) != cudaSuccess) return e; \
+    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 16>, smem_bytes)) != cudaSuccess) return e;
     B200VC_SET(0, 0, false) B200VC_SET(0, 0, true) B200VC_SET(0, 1, false) B200VC_SET(0, 1, true)
     B200VC_SET(1, 0, false) B200VC_SET(1, 0, true) B200VC_SET(1, 1, false) B200VC_SET(1, 1, true)
 #undef B200VC_SET
@@ -502,7 +584,9 @@ cudaError_t launch_fused_scale(const CUtensorMap &src_map, const FusedScaleParam
 {
     if (p.out_w <= 0 || p.out_h <= 0 || p.n_frames <= 0)
         return cudaErrorInvalidValue;
-    dim3 grid((p.out_w + TW - 1) / TW, (p.out_h + TH - 1) / TH, p.n_frames);
+    if (p.tile_h != 8 && p.tile_h != 16)
+        return cudaErrorInvalidValue;
+    dim3 grid((p.out_w + TW - 1) / TW, (p.out_h + p.tile_h - 1) / p.tile_h, p.n_frames);
     const size_t smem = fused_scale_smem_bytes(p.box_w, p.box_h);
     if (fmt == 0)
         return site ? launch_fused2<0, 1>(src_map, p, grid, smem, st) : launch_fused2<0, 0>(src_map, p, grid, smem, st);

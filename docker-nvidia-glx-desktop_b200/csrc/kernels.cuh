@@ -51,16 +51,31 @@ struct ScaleTables {
     const Tap *hc, *vc;     // chroma: out_w/2, out_h/2 entries
 };
 
+// The same taps in the form the general fused kernel consumes without decoding: plain indices and
+// ready-made dp4a weight words. A clamped second tap (step 0) has weight 0, so the kernel always
+// reads index+1.
+//   horizontal luma   hy_i[x] = index, hy_w[x] = (255-f) | 1<<8 | f<<16 : [a,a,b,_] . w = a*(256-f) + b*f
+//   vertical          {index, wa1 | wa2<<8 | wb1<<16 | wb2<<24} with wa1+wa2 = 256-4*p1, wb1+wb2 = 4*p1:
+//                     ([a,a,b,b] . w + 128) >> 8 == (a*(64-p1) + b*p1 + 32) >> 6
+//   horizontal chroma {index, 256-f, f, 0}: multipliers for (u,v) pairs on 2x16-bit lanes
+struct FusedTaps {
+    const uint32_t *hy_i, *hy_w;
+    const uint2 *vy, *vc;
+    const uint4 *hc;
+};
+
 // K2 fused: TMA-staged source window -> convert -> chroma down -> 2-tap scale, one pass.
 struct FusedScaleParams {
     PlaneSet out;
     ScaleTables tab;
+    FusedTaps ft;
     int in_w, in_h, out_w, out_h;
     int box_w, box_h;       // source window per tile (pixels); box_w % 4 == 0, box_h even
+    int tile_h;             // output rows per tile: 16, or 8 when a 16-row window would leave too few CTAs per SM
     int n_frames;
     int box2x2;             // scale_mode == BOX_2X2
-    uint32_t inv_items_x;   // ceil(65536 / (box_w/4)) and the same for box_w/4 - 1: tid / items_x
-    uint32_t inv_items_x1;  // without a division (exact for tid <= 256, up to 64 items)
+    uint32_t inv_items_x;   // ceil(65536 / items per line pair), for box_w/4 and box_w/4 - 1 groups:
+    uint32_t inv_items_x1;  // tid / items_x without a division (exact for tid <= 256, up to 64 items)
     Matrix mx;
 };
 
@@ -87,7 +102,7 @@ constexpr int K1_TILE_W = 128;   // pixels per warp stripe (one LDG.128 per lane
 constexpr int K1_TILE_H = 16;    // one macroblock row per warp stripe
 constexpr int K1_WARPS_PER_CTA = 4;
 constexpr int K2_TILE_W = 64;    // output pixels per CTA tile
-constexpr int K2_TILE_H = 16;
+constexpr int K2_TILE_H = 16;    // (8 for large ratios, FusedScaleParams::tile_h)
 constexpr int K2X_SRC_W = 128;   // exact-2:1 kernel: source tile per CTA (8 warps x 4 lines, 32 lanes x 4 pixels)
 constexpr int K2X_SRC_H = 32;
 constexpr int K2X_HALO = 4;      // columns loaded left of the tile (TMA boxes start 16-byte aligned)

@@ -82,3 +82,16 @@ def test_two_ranks_gloo(orc):
         f = orc.synth("desk", 64, 32, 100 * s)
         buf, off, pit = orc.convert(f, 0, 0, 0, 1)
         assert merged[s] == plane_checksums(plane_views(buf, off, pit, 0, 64, 32))
+
+
+def test_cpulist_and_numa_lookup(tmp_path):
+    assert sessions.parse_cpulist("0-3,8,10-11\n") == [0, 1, 2, 3, 8, 10, 11]
+    assert sessions.parse_cpulist("") == []
+    d = tmp_path / "bus/pci/devices/0000:1b:00.0"
+    d.mkdir(parents=True)
+    (d / "numa_node").write_text("1\n")
+    assert sessions.gpu_numa_node("00000000:1B:00.0", str(tmp_path)) == 1
+    assert sessions.gpu_numa_node("00000000:9F:00.0", str(tmp_path)) == -1
+    # no GPU / no NVML here: the binder reports instead of raising
+    info = sessions.bind_to_gpu_numa(0, str(tmp_path))
+    assert info["bound"] is False

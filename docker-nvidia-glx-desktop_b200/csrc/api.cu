@@ -72,7 +72,8 @@ struct b200vc_ctx {
     // scaling
     Tap *d_taps = nullptr;
     ScaleTables tab = { nullptr, nullptr, nullptr, nullptr };
-    FusedTaps ft = { nullptr, nullptr, nullptr, nullptr, nullptr };
+    uint32_t *d_ftaps = nullptr;               // the general fused kernel's per-tile tap records
+    FusedTaps ft = { nullptr, nullptr, nullptr, nullptr };
     int tile_h = K2_TILE_H;
     int box_w = 0, box_h = 0;
     size_t smem_bytes = 0;
@@ -203,9 +204,9 @@ inline int tidx(Tap t) { return (int)(t & 0xffff); }
 inline int tstep(Tap t) { return (int)((t >> 24) & 1); }
 inline int tfrac(Tap t) { return (int)((t >> 16) & 0xff); }
 
-// The general fused kernel's form of the tables (FusedTaps, kernels.cuh), as one blob of 32-bit words:
-// [hy_i | hy_w | vy pairs | vc pairs | hc quads], every section a multiple of 4 words.
-struct FusedTapBlob { std::vector<uint32_t> w; size_t hy_i, hy_w, vy, vc, hc; };
+// The general fused kernel's form of the tables (FusedTaps, kernels.cuh) as one blob of 32-bit words:
+// [tile_x pairs | tile_y | col_rec | row_rec], every section padded to a multiple of 4 words.
+struct FusedTapBlob { std::vector<uint32_t> w; size_t tile_x, tile_y, col_rec, row_rec; };
 
 uint32_t v_weights(Tap t)
 {
@@ -215,25 +216,64 @@ uint32_t v_weights(Tap t)
     return (uint32_t)a1 | ((uint32_t)(a - a1) << 8) | ((uint32_t)b1 << 16) | ((uint32_t)(b - b1) << 24);
 }
 
-void build_fused_taps(const std::vector<Tap> &hy, const std::vector<Tap> &vy, const std::vector<Tap> &hc,
-                      const std::vector<Tap> &vc, FusedTapBlob &o)
+// Window origin of a tile column / tile row: the first source column (line) any of its taps reads,
+// the cosited chroma filter's left neighbour included, rounded down to what the TMA box (16-byte
+// aligned start) and the 2x2 chroma sites need.
+inline int tile_org_x(const std::vector<Tap> &hy, const std::vector<Tap> &hc, int x0, int site)
 {
+    return std::min(tidx(hy[x0]), 2 * tidx(hc[x0 >> 1]) - site) & ~3;
+}
+inline int tile_org_y(const std::vector<Tap> &vy, const std::vector<Tap> &vc, int y0)
+{
+    return std::min(tidx(vy[y0]), 2 * tidx(vc[y0 >> 1])) & ~1;
+}
+
+void build_fused_taps(const b200vc_config &c, const std::vector<Tap> &hy, const std::vector<Tap> &vy,
+                      const std::vector<Tap> &hc, const std::vector<Tap> &vc, int tile_h, int box_w, FusedTapBlob &o)
+{
+    const int site = c.chroma_site == B200VC_SITE_H_COSITED ? 1 : 0;
+    const int tiles_x = (c.out_w + K2_TILE_W - 1) / K2_TILE_W, tiles_y = (c.out_h + tile_h - 1) / tile_h;
+    const int cw_out = c.out_w / 2, ch_out = c.out_h / 2;                      // fused path: even sizes
+    auto pad4 = [&] { while (o.w.size() % 4) o.w.push_back(0u); };
     o.w.clear();
-    o.hy_i = o.w.size();
-    for (Tap t : hy) o.w.push_back((uint32_t)tidx(t));
-    o.hy_w = o.w.size();
-    for (Tap t : hy) {
-        const uint32_t f = tstep(t) ? (uint32_t)tfrac(t) : 0u;
-        o.w.push_back((255u - f) | (1u << 8) | (f << 16));
+    o.tile_x = o.w.size();
+    for (int bx = 0; bx < tiles_x; bx++) {
+        const int x0 = bx * K2_TILE_W, sx = tile_org_x(hy, hc, x0, site);
+        const int first = std::min(tidx(hy[x0]), 2 * tidx(hc[x0 >> 1]));
+        o.w.push_back((uint32_t)sx);
+        o.w.push_back((uint32_t)(std::min(first - sx, 4) >> 2));               // first 4 columns halo only
     }
-    o.vy = o.w.size();
-    for (Tap t : vy) { o.w.push_back((uint32_t)tidx(t));  o.w.push_back(v_weights(t)); }
-    o.vc = o.w.size();
-    for (Tap t : vc) { o.w.push_back((uint32_t)tidx(t));  o.w.push_back(v_weights(t)); }
-    o.hc = o.w.size();
-    for (Tap t : hc) {
-        const uint32_t f = tstep(t) ? (uint32_t)tfrac(t) : 0u;
-        o.w.push_back((uint32_t)tidx(t));  o.w.push_back(256u - f);  o.w.push_back(f);  o.w.push_back(0u);
+    pad4();
+    o.tile_y = o.w.size();
+    for (int by = 0; by < tiles_y; by++) o.w.push_back((uint32_t)tile_org_y(vy, vc, by * tile_h));
+    pad4();
+    o.col_rec = o.w.size();
+    for (int bx = 0; bx < tiles_x; bx++) {
+        const int x0 = bx * K2_TILE_W, sx = tile_org_x(hy, hc, x0, site);
+        for (int k = 0; k < K2_TILE_W; k++)
+            o.w.push_back((uint32_t)(tidx(hy[std::min(x0 + k, c.out_w - 1)]) - sx));
+        for (int k = 0; k < K2_TILE_W; k++) {
+            const Tap t = hy[std::min(x0 + k, c.out_w - 1)];
+            const uint32_t f = tstep(t) ? (uint32_t)tfrac(t) : 0u;
+            o.w.push_back((255u - f) | (1u << 8) | (f << 16));
+        }
+        for (int k = 0; k < K2_TILE_W / 2; k++) {
+            const Tap t = hc[std::min(x0 / 2 + k, cw_out - 1)];
+            const uint32_t f = tstep(t) ? (uint32_t)tfrac(t) : 0u;
+            o.w.push_back((uint32_t)(tidx(t) - sx / 2));  o.w.push_back(256u - f);  o.w.push_back(f);  o.w.push_back(0u);
+        }
+    }
+    o.row_rec = o.w.size();
+    for (int by = 0; by < tiles_y; by++) {
+        const int y0 = by * tile_h, sy = tile_org_y(vy, vc, y0);
+        for (int k = 0; k < tile_h; k++) {
+            const Tap t = vy[std::min(y0 + k, c.out_h - 1)];
+            o.w.push_back((uint32_t)((tidx(t) - sy) * box_w));  o.w.push_back(v_weights(t));
+        }
+        for (int k = 0; k < tile_h / 2; k++) {
+            const Tap t = vc[std::min(y0 / 2 + k, ch_out - 1)];
+            o.w.push_back((uint32_t)((tidx(t) - sy / 2) * (box_w / 2)));  o.w.push_back(v_weights(t));
+        }
     }
 }
 
@@ -246,13 +286,13 @@ void fused_box(const b200vc_config &c, const std::vector<Tap> &hy, const std::ve
     box_w = box_h = 0;
     for (int x0 = 0; x0 < c.out_w; x0 += K2_TILE_W) {
         const int x1 = std::min(x0 + K2_TILE_W, c.out_w) - 1;
-        int sx = std::min(tidx(hy[x0]), 2 * tidx(hc[x0 >> 1]) - site) & ~3;   // 16-byte aligned box start
+        int sx = tile_org_x(hy, hc, x0, site);                                   // 16-byte aligned box start
         int last = std::max(tidx(hy[x1]) + tstep(hy[x1]), 2 * (tidx(hc[x1 >> 1]) + tstep(hc[x1 >> 1])) + 1);
         box_w = std::max(box_w, last - sx + 1);
     }
     for (int y0 = 0; y0 < c.out_h; y0 += tile_h) {
         const int y1 = std::min(y0 + tile_h, c.out_h) - 1;
-        int sy = std::min(tidx(vy[y0]), 2 * tidx(vc[y0 >> 1])) & ~1;
+        int sy = tile_org_y(vy, vc, y0);
         int last = std::max(tidx(vy[y1]) + tstep(vy[y1]), 2 * (tidx(vc[y1 >> 1]) + tstep(vc[y1 >> 1])) + 1);
         box_h = std::max(box_h, last - sy + 1);
     }
@@ -411,7 +451,7 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         }
         FusedScaleParams p;
         memset(&p, 0, sizeof p);
-        p.out = out;  p.tab = c->tab;  p.ft = c->ft;
+        p.out = out;  p.ft = c->ft;
         p.in_w = g.in_w;  p.in_h = g.in_h;  p.out_w = g.out_w;  p.out_h = g.out_h;
         p.box_w = c->box_w;  p.box_h = c->box_h;  p.tile_h = c->tile_h;  p.n_frames = n_frames;
         p.box2x2 = g.scale_mode == B200VC_SCALE_BOX_2X2;  p.mx = c->mx;
@@ -469,6 +509,7 @@ void destroy_locked(b200vc_ctx *c)
     for (cudaEvent_t e : c->ev_band_k) cudaEventDestroy(e);
     for (const HostReg &r : c->registered) cudaHostUnregister(const_cast<void *>(r.base));
     cudaFree(c->d_taps);
+    cudaFree(c->d_ftaps);
     cudaFree(c->d_mid);
     if (c->s_h2d) cudaStreamDestroy(c->s_h2d);
     if (c->s_k) cudaStreamDestroy(c->s_k);
@@ -543,33 +584,24 @@ int create_impl(b200vc_ctx *c)
             // chroma planes of odd frames round up, like the intermediate frame's own layout
             build_h_taps((g.in_w + 1) / 2, (g.out_w + 1) / 2, hc);  build_v_taps((g.in_h + 1) / 2, (g.out_h + 1) / 2, vc);
         }
-        FusedTapBlob blob;
-        build_fused_taps(hy, vy, hc, vc, blob);
         const size_t n = hy.size() + vy.size() + hc.size() + vc.size();       // every size a multiple of 4
-        CU_TRY(c, cudaMalloc(&c->d_taps, (n + blob.w.size()) * sizeof(Tap)));
+        CU_TRY(c, cudaMalloc(&c->d_taps, n * sizeof(Tap)));
         Tap *d = c->d_taps;
-        {
-            const uint32_t *b = d + n;                                        // 16-byte aligned: n % 4 == 0
-            CU_TRY(c, cudaMemcpy(d + n, blob.w.data(), blob.w.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
-            c->ft.hy_i = b + blob.hy_i;  c->ft.hy_w = b + blob.hy_w;
-            c->ft.vy = reinterpret_cast<const uint2 *>(b + blob.vy);
-            c->ft.vc = reinterpret_cast<const uint2 *>(b + blob.vc);
-            c->ft.hc = reinterpret_cast<const uint4 *>(b + blob.hc);
-        }
         c->tab.hy = d;  CU_TRY(c, cudaMemcpy(d, hy.data(), hy.size() * sizeof(Tap), cudaMemcpyHostToDevice));  d += hy.size();
         c->tab.vy = d;  CU_TRY(c, cudaMemcpy(d, vy.data(), vy.size() * sizeof(Tap), cudaMemcpyHostToDevice));  d += vy.size();
         c->tab.hc = d;  CU_TRY(c, cudaMemcpy(d, hc.data(), hc.size() * sizeof(Tap), cudaMemcpyHostToDevice));  d += hc.size();
         c->tab.vc = d;  CU_TRY(c, cudaMemcpy(d, vc.data(), vc.size() * sizeof(Tap), cudaMemcpyHostToDevice));
 
-        c->tile_h = K2_TILE_H;
-        fused_box(g, hy, vy, hc, vc, c->tile_h, c->box_w, c->box_h);
-        c->smem_bytes = fused_scale_smem_bytes(c->box_w, c->box_h);
-        // the kernel is register-limited to 6 CTAs per SM; a window that leaves room for fewer (ratios
-        // towards 3:1 and beyond) is halved in height instead
-        if (c->smem_bytes + 4096 > (size_t)c->prop.sharedMemPerMultiprocessor / 6) {
-            c->tile_h = K2_TILE_H / 2;
+        // Output rows per tile of the general fused kernel: the tallest of 32, 16, 8 whose window
+        // leaves room for 6 CTAs per SM. Tall tiles amortise the per-tile set-up, the halo lines and
+        // the rounding of phase 1's work to whole warps (measured: 4:3 and 3:2 gain 13-22 % from
+        // 16 -> 32 rows); a window too large for 6 resident CTAs no longer hides its TMA wait
+        // (4K -> 720p: 0.78 of the roofline with 8 rows, 0.67 with 16, 0.37 with 32).
+        for (c->tile_h = 32; ; c->tile_h /= 2) {
             fused_box(g, hy, vy, hc, vc, c->tile_h, c->box_w, c->box_h);
             c->smem_bytes = fused_scale_smem_bytes(c->box_w, c->box_h);
+            if (c->tile_h == 8 || c->smem_bytes + 4096 <= (size_t)c->prop.sharedMemPerMultiprocessor / 6)
+                break;
         }
         const bool fits = c->box_w <= 256 && c->box_h <= 256 &&
                           c->smem_bytes + 1024 <= (size_t)c->prop.sharedMemPerBlockOptin;
@@ -586,6 +618,16 @@ int create_impl(b200vc_ctx *c)
             c->smem_bytes = (size_t)c->box_w * c->box_h * 4;
             c->inc_y = h_inc(g.in_w, g.out_w);
             c->inc_c = h_inc(g.in_w / 2, g.out_w / 2);
+        }
+        if (c->path == 1 && !c->fused2x) {
+            FusedTapBlob blob;
+            build_fused_taps(g, hy, vy, hc, vc, c->tile_h, c->box_w, blob);
+            CU_TRY(c, cudaMalloc(&c->d_ftaps, blob.w.size() * sizeof(uint32_t)));
+            CU_TRY(c, cudaMemcpy(c->d_ftaps, blob.w.data(), blob.w.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+            c->ft.tile_x = reinterpret_cast<const int2 *>(c->d_ftaps + blob.tile_x);
+            c->ft.tile_y = reinterpret_cast<const int *>(c->d_ftaps + blob.tile_y);
+            c->ft.col_rec = c->d_ftaps + blob.col_rec;
+            c->ft.row_rec = c->d_ftaps + blob.row_rec;
         }
         if (c->path == 1) {
             void *fn = nullptr;

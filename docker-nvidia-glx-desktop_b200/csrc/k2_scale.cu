@@ -39,6 +39,23 @@ __device__ __forceinline__ uint32_t smem_u32(const void *p)
 // video_scale_v_2tap_u8 (lq): a + (((b-a)*p1 + 32) >> 6), which equals (a*(64-p1) + b*p1 + 32) >> 6
 // (no clamp needed for 0 <= p1 <= 64) and is evaluated as one dp4a on the lanes' high bytes.
 
+// mbarrier init + TMA tiled load of the tile's source window, by one thread. Kept out of line: inlined,
+// the sequence's uniform-datapath instructions are stepped through by all eight warps (~40 issue slots
+// each); as a call only the calling warp pays.
+__device__ __noinline__ void issue_window_load(uint64_t *s_bar, void *dst, const CUtensorMap *map, int x, int y, int z,
+                                               uint32_t bytes)
+{
+    const uint32_t bar = smem_u32(s_bar);
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%2, %3, %4}], [%5];"
+        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(x), "r"(y), "r"(z), "r"(bar)
+        : "memory");
+}
+
 // Phase 1 of the general fused kernel: one item = 8 columns x 2 lines of the window (two 4-column
 // groups; `two` false: only the first), BGRx in s_src -> Y bytes in s_yf and filtered, vertically
 // averaged (u,v) pairs in s_cf. kx = first group's index in the line pair, sx0 = window's frame column.
@@ -91,17 +108,19 @@ __device__ __forceinline__ void convert_item(const uint32_t *s_src, uint8_t *s_y
 }
 
 template <int FMT, int SITE, bool NEG, int TILE_H>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 8)
 k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedScaleParams p)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t s_bar;
-    __shared__ int s_org[3];               // window origin x, y; first 4-column item that is not pure halo
-    // this tile's taps (FusedTaps) as offsets into the window's planes, staged while the TMA load flies
-    __shared__ uint32_t s_hyo[TW], s_hyw[TW];
-    __shared__ uint2 s_vy[TILE_H], s_vc[TILE_H / 2];
-    __shared__ __align__(16) uint4 s_hc[TW / 2];
+    // this tile's taps, ready to use (FusedTaps): copied from the host-made records while the TMA
+    // load is in flight
+    __shared__ __align__(16) uint32_t s_col[4 * TW];           // hyo[TW] | hyw[TW] | hc[TW/2] quads
+    __shared__ __align__(8) uint32_t s_row[3 * TILE_H];        // vy[TILE_H] pairs | vc[TILE_H/2] pairs
     __shared__ __align__(16) uint8_t s_out[TW * TILE_H * 3 / 2];   // output tile: Y, then U and V (or UV) tiles
+    const uint32_t *s_hyo = s_col, *s_hyw = s_col + TW;
+    const uint4 *s_hc = reinterpret_cast<const uint4 *>(s_col + 2 * TW);
+    const uint2 *s_vy = reinterpret_cast<const uint2 *>(s_row), *s_vc = s_vy + TILE_H;
 
     const int bw = p.box_w, bh = p.box_h;
     uint32_t *s_src = reinterpret_cast<uint32_t *>(smem);                 // [bh][bw] pixels
@@ -112,56 +131,15 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
     const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TILE_H;
     const int frame = blockIdx.z;
 
-    // ---- phase 0: source window origin, TMA load -------------------------------------------
-    if (tid == 0) {
-        const int hy0 = tap_idx(p.tab.hy[x0]);
-        const int uc0 = tap_idx(p.tab.hc[x0 >> 1]);
-        int sx = min(hy0, 2 * uc0 - (SITE ? 1 : 0));
-        sx &= ~3;     // TMA needs the box's first byte 16-byte aligned (4 pixels); -4 at the left frame edge
-        const int vy0 = tap_idx(p.tab.vy[y0]);
-        const int vc0 = tap_idx(p.tab.vc[y0 >> 1]);
-        const int sy = min(vy0, 2 * vc0) & ~1;
-        s_org[0] = sx;
-        s_org[1] = sy;
-        s_org[2] = min(min(hy0, 2 * uc0) - sx, 4) >> 2;   // 1 when the window's first 4 columns are halo only
-
-        const uint32_t bar = smem_u32(&s_bar);
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        const uint32_t bytes = (uint32_t)bw * bh * 4;
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-        asm volatile(
-            "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
-            " [%0], [%1, {%2, %3, %4}], [%5];"
-            ::"r"(smem_u32(s_src)), "l"(reinterpret_cast<uint64_t>(&src_map)), "r"(sx), "r"(sy), "r"(frame), "r"(bar)
-            : "memory");
-    }
+    // ---- phase 0: source window origin (host-made, per tile column / tile row), TMA load --------
+    const int2 org_x = p.ft.tile_x[blockIdx.x];          // window's frame column (multiple of 4), kfirst
+    const int sx0 = org_x.x, kfirst = org_x.y, sy0 = p.ft.tile_y[blockIdx.y];
+    if (tid == 0)
+        issue_window_load(&s_bar, s_src, &src_map, sx0, sy0, frame, (uint32_t)bw * bh * 4);
+    s_col[tid] = p.ft.col_rec[blockIdx.x * (4 * TW) + tid];               // 4 * TW == 256 == blockDim.x
+    if (tid < 3 * TILE_H)
+        s_row[tid] = p.ft.row_rec[blockIdx.y * (3 * TILE_H) + tid];
     __syncthreads();
-    const int sx0 = s_org[0], sy0 = s_org[1], kfirst = s_org[2];
-    {
-        // warps 0-1: luma columns, warp 2: luma rows, warp 3: chroma columns, warp 4: chroma rows
-        // (indices clamped to the tables; entries past the frame edge are never consumed)
-        const int t = tid & 31, w = tid >> 5;
-        if (w < 2) {
-            const int x = min(x0 + tid, p.out_w - 1);
-            s_hyo[tid] = p.ft.hy_i[x] - (uint32_t)sx0;
-            s_hyw[tid] = p.ft.hy_w[x];
-        } else if (w == 2) {
-            if (t < TILE_H) {
-                const uint2 v = p.ft.vy[min(y0 + t, p.out_h - 1)];
-                s_vy[t] = make_uint2((uint32_t)(((int)v.x - sy0) * bw), v.y);
-            }
-        } else if (w == 3) {
-            uint4 h = p.ft.hc[min((x0 >> 1) + t, (p.out_w >> 1) - 1)];
-            h.x -= (uint32_t)(sx0 >> 1);
-            s_hc[t] = h;
-        } else if (w == 4) {
-            if (t < TILE_H / 2) {
-                const uint2 v = p.ft.vc[min((y0 >> 1) + t, (p.out_h >> 1) - 1)];
-                s_vc[t] = make_uint2((uint32_t)(((int)v.x - (sy0 >> 1)) * (bw >> 1)), v.y);
-            }
-        }
-    }
     {
         const uint32_t bar = smem_u32(&s_bar);
         uint32_t done = 0;
@@ -228,53 +206,57 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
             s_out[(rb + k) * TW + c] = (uint8_t)(d >> 8);
         }
     }
-    if (wrp < TILE_H / 2) {
-        // chroma: one (u,v) sample per thread, warp w does chroma row w
+    {
+        // chroma: one (u,v) sample per thread and row, warp w does chroma rows w, w + 8, ...
         const uint4 th = s_hc[lane];
-        const uint2 tv = s_vc[wrp];
         const int cw = bw >> 1;
-        const uint32_t *r0 = s_cf + (int)th.x + (int)tv.x, *r1 = r0 + cw;
-        uint32_t uv;                              // u in byte 1, v in byte 3
-        if (p.box2x2) {
-            uv = (((r0[0] + r0[1] + r1[0] + r1[1] + 0x00020002u) >> 2) & LANES8) << 8;
-        } else {
-            // both lanes at once: each lane's weighted sum is <= 255*256, its high byte the sample
-            const uint32_t ha = r0[0] * th.y + r0[1] * th.z;
-            const uint32_t hb = r1[0] * th.y + r1[1] * th.z;
-            const uint32_t du = dp4a_uu(prmt(ha, hb, 0x5511), tv.y, 128u);
-            const uint32_t dv = dp4a_uu(prmt(ha, hb, 0x7733), tv.y, 128u);
-            uv = prmt(du, dv, 0x5010);            // du.0, du.1, dv.0, dv.1
-        }
         uint8_t *oc = s_out + TW * TILE_H;
-        if (FMT == 0) {
-            oc[wrp * (TW / 2) + lane] = (uint8_t)(uv >> 8);                            // U tile, then V tile
-            oc[(TW / 2) * (TILE_H / 2) + wrp * (TW / 2) + lane] = (uint8_t)(uv >> 24);
-        } else {
-            reinterpret_cast<uint16_t *>(oc)[wrp * (TW / 2) + lane] = (uint16_t)prmt(uv, 0, 0x4431);   // u, v
+#pragma unroll
+        for (int r = wrp; r < TILE_H / 2; r += 8) {
+            const uint2 tv = s_vc[r];
+            const uint32_t *r0 = s_cf + (int)th.x + (int)tv.x, *r1 = r0 + cw;
+            uint32_t uv;                              // u in byte 1, v in byte 3
+            if (p.box2x2) {
+                uv = (((r0[0] + r0[1] + r1[0] + r1[1] + 0x00020002u) >> 2) & LANES8) << 8;
+            } else {
+                // both lanes at once: each lane's weighted sum is <= 255*256, its high byte the sample
+                const uint32_t ha = r0[0] * th.y + r0[1] * th.z;
+                const uint32_t hb = r1[0] * th.y + r1[1] * th.z;
+                const uint32_t du = dp4a_uu(prmt(ha, hb, 0x5511), tv.y, 128u);
+                const uint32_t dv = dp4a_uu(prmt(ha, hb, 0x7733), tv.y, 128u);
+                uv = prmt(du, dv, 0x5010);            // du.0, du.1, dv.0, dv.1
+            }
+            if (FMT == 0) {
+                oc[r * (TW / 2) + lane] = (uint8_t)(uv >> 8);                            // U tile, then V tile
+                oc[(TW / 2) * (TILE_H / 2) + r * (TW / 2) + lane] = (uint8_t)(uv >> 24);
+            } else {
+                reinterpret_cast<uint16_t *>(oc)[r * (TW / 2) + lane] = (uint16_t)prmt(uv, 0, 0x4431);   // u, v
+            }
         }
     }
     __syncthreads();
 
     // ---- phase 3: the tile leaves as 16-byte stores (4 chunks per luma row, 4 per chroma row pair) --
-    if (tid < TILE_H * 6) {
-        const long long fo = (long long)frame * p.out.frame_stride;
-        const uint8_t *src = s_out + tid * 16;
+    const long long fo = (long long)frame * p.out.frame_stride;
+#pragma unroll
+    for (int c = tid; c < TILE_H * 6; c += 256) {
+        const uint8_t *src = s_out + c * 16;
         uint8_t *dst;
         int n;                                    // valid bytes of this chunk, <= 0: none
         bool row_ok;
-        if (tid < TILE_H * 4) {
-            const int r = tid >> 2, xb = x0 + (tid & 3) * 16;
+        if (c < TILE_H * 4) {
+            const int r = c >> 2, xb = x0 + (c & 3) * 16;
             row_ok = y0 + r < p.out_h;
             n = p.out_w - xb;
             dst = p.out.p[0] + fo + (long long)(y0 + r) * p.out.pitch[0] + xb;
         } else if (FMT == 0) {
-            const int i = tid - TILE_H * 4;
-            const int pl = i / TILE_H, r = (i >> 1) & (TILE_H / 2 - 1), xb = (x0 >> 1) + (tid & 1) * 16;
+            const int i = c - TILE_H * 4;
+            const int pl = i / TILE_H, r = (i >> 1) & (TILE_H / 2 - 1), xb = (x0 >> 1) + (c & 1) * 16;
             row_ok = (y0 >> 1) + r < (p.out_h >> 1);
             n = (p.out_w >> 1) - xb;
             dst = p.out.p[1 + pl] + fo + (long long)((y0 >> 1) + r) * p.out.pitch[1 + pl] + xb;
         } else {
-            const int r = (tid - TILE_H * 4) >> 2, xb = x0 + (tid & 3) * 16;
+            const int r = (c - TILE_H * 4) >> 2, xb = x0 + (c & 3) * 16;
             row_ok = (y0 >> 1) + r < (p.out_h >> 1);
             n = p.out_w - xb;
             dst = p.out.p[1] + fo + (long long)((y0 >> 1) + r) * p.out.pitch[1] + xb;
@@ -512,6 +494,12 @@ cudaError_t launch_fused2(const CUtensorMap &map, const FusedScaleParams &p, dim
             k2_fused_scale_kernel<FMT, SITE, true, 8><<<grid, 256, smem, st>>>(map, p);
         else
             k2_fused_scale_kernel<FMT, SITE, false, 8><<<grid, 256, smem, st>>>(map, p);
+    } else if (p.tile_h == 32) {
+        if (p.mx.neg)
+            k2_fused_scale_kernel<FMT, SITE, true, 32><<<grid, 256, smem, st>>>(map, p);
+        else
+            k2_fused_scale_kernel<FMT, SITE, false, 32><<<grid, 256, smem, st>>>(map, p);
+
     } else {
         if (p.mx.neg)
             k2_fused_scale_kernel<FMT, SITE, true, 16><<<grid, 256, smem, st>>>(map, p);
@@ -572,7 +560,8 @@ cudaError_t fused_scale_prepare(size_t smem_bytes)
     cudaError_t e;
 #define B200VC_SET(F, S, N) \
     if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 8>, smem_bytes)) != cudaSuccess) return e; \
-    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 16>, smem_bytes)) != cudaSuccess) return e;
+    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 16>, smem_bytes)) != cudaSuccess) return e; \
+    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 32>, smem_bytes)) != cudaSuccess) return e;
     B200VC_SET(0, 0, false) B200VC_SET(0, 0, true) B200VC_SET(0, 1, false) B200VC_SET(0, 1, true)
     B200VC_SET(1, 0, false) B200VC_SET(1, 0, true) B200VC_SET(1, 1, false) B200VC_SET(1, 1, true)
 #undef B200VC_SET
@@ -584,7 +573,7 @@ cudaError_t launch_fused_scale(const CUtensorMap &src_map, const FusedScaleParam
 {
     if (p.out_w <= 0 || p.out_h <= 0 || p.n_frames <= 0)
         return cudaErrorInvalidValue;
-    if (p.tile_h != 8 && p.tile_h != 16)
+    if (p.tile_h != 8 && p.tile_h != 16 && p.tile_h != 32)
         return cudaErrorInvalidValue;
     dim3 grid((p.out_w + TW - 1) / TW, (p.out_h + p.tile_h - 1) / p.tile_h, p.n_frames);
     const size_t smem = fused_scale_smem_bytes(p.box_w, p.box_h);

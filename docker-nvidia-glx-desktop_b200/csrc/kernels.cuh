@@ -51,27 +51,32 @@ struct ScaleTables {
     const Tap *hc, *vc;     // chroma: out_w/2, out_h/2 entries
 };
 
-// The same taps in the form the general fused kernel consumes without decoding: plain indices and
-// ready-made dp4a weight words. A clamped second tap (step 0) has weight 0, so the kernel always
-// reads index+1.
-//   horizontal luma   hy_i[x] = index, hy_w[x] = (255-f) | 1<<8 | f<<16 : [a,a,b,_] . w = a*(256-f) + b*f
-//   vertical          {index, wa1 | wa2<<8 | wb1<<16 | wb2<<24} with wa1+wa2 = 256-4*p1, wb1+wb2 = 4*p1:
-//                     ([a,a,b,b] . w + 128) >> 8 == (a*(64-p1) + b*p1 + 32) >> 6
-//   horizontal chroma {index, 256-f, f, 0}: multipliers for (u,v) pairs on 2x16-bit lanes
+// The taps in the form the general fused kernel consumes without decoding, as one record per tile
+// column and one per tile row (host-made, api.cu build_fused_taps). Indices are offsets into the
+// tile's source window; a clamped second tap (step 0) has weight 0, so the kernel always reads index+1.
+//   tile_x[bx] = {window's first frame column (multiple of 4, may be -4), 1 if its first 4 columns
+//                 are pure halo}, tile_y[by] = window's first frame line (even)
+//   col_rec[bx][256]: 64 x hyo (byte offset of the first tap in a Y line of the window)
+//                     64 x hyw = (255-f) | 1<<8 | f<<16 : [a,a,b,_] . hyw = a*(256-f) + b*f
+//                     32 x {offset of the first tap in a (u,v) line, 256-f, f, 0}
+//   row_rec[by][3*tile_h]: tile_h x {byte offset of the first line in the Y plane, wv}
+//                          tile_h/2 x {word offset of the first line in the (u,v) plane, wv}
+//       wv = wa1 | wa2<<8 | wb1<<16 | wb2<<24 with wa1+wa2 = 256-4*p1, wb1+wb2 = 4*p1:
+//       ([a,a,b,b] . wv + 128) >> 8 == (a*(64-p1) + b*p1 + 32) >> 6
+// Columns and rows past the frame edge repeat the last valid entry.
 struct FusedTaps {
-    const uint32_t *hy_i, *hy_w;
-    const uint2 *vy, *vc;
-    const uint4 *hc;
+    const int2 *tile_x;
+    const int *tile_y;
+    const uint32_t *col_rec, *row_rec;
 };
 
 // K2 fused: TMA-staged source window -> convert -> chroma down -> 2-tap scale, one pass.
 struct FusedScaleParams {
     PlaneSet out;
-    ScaleTables tab;
     FusedTaps ft;
     int in_w, in_h, out_w, out_h;
     int box_w, box_h;       // source window per tile (pixels); box_w % 4 == 0, box_h even
-    int tile_h;             // output rows per tile: 16, or 8 when a 16-row window would leave too few CTAs per SM
+    int tile_h;             // output rows per tile: 32, 16 or 8 (the tallest whose window leaves 6 CTAs per SM)
     int n_frames;
     int box2x2;             // scale_mode == BOX_2X2
     uint32_t inv_items_x;   // ceil(65536 / items per line pair), for box_w/4 and box_w/4 - 1 groups:
@@ -102,7 +107,7 @@ constexpr int K1_TILE_W = 128;   // pixels per warp stripe (one LDG.128 per lane
 constexpr int K1_TILE_H = 16;    // one macroblock row per warp stripe
 constexpr int K1_WARPS_PER_CTA = 4;
 constexpr int K2_TILE_W = 64;    // output pixels per CTA tile
-constexpr int K2_TILE_H = 16;    // (8 for large ratios, FusedScaleParams::tile_h)
+constexpr int K2_TILE_H = 16;    // exact-2:1 kernel; the general kernel's is FusedScaleParams::tile_h
 constexpr int K2X_SRC_W = 128;   // exact-2:1 kernel: source tile per CTA (8 warps x 4 lines, 32 lanes x 4 pixels)
 constexpr int K2X_SRC_H = 32;
 constexpr int K2X_HALO = 4;      // columns loaded left of the tile (TMA boxes start 16-byte aligned)

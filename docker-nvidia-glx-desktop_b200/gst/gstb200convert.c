@@ -25,10 +25,67 @@ G_DECLARE_FINAL_TYPE(GstB200Convert, gst_b200_convert, GST, B200_CONVERT, GstVid
 struct _GstB200Convert {
     GstVideoFilter parent;
     b200vc_ctx *ctx;
+    GstAllocator *allocator;      /* page-locked host memory (b200vc_host_alloc) for the output pool */
     gint device_id;
     gboolean damage_map;
     gint n_bands;
 };
+
+/* ---- allocator over b200vc_host_alloc: buffers the copy engines reach without staging -------------
+ * Output buffers come from a GstVideoBufferPool configured with this allocator (decide_allocation), so
+ * the planes x264enc reads are page-locked and the library copies device -> host straight into them.
+ * The same allocator and a pool are offered upstream (propose_allocation); ximagesrc ignores the offer
+ * (it wraps XShm images), which is what B200VC_FLAG_REGISTER_HOST is for. */
+typedef struct { GstMemory mem; gpointer data; } GstB200PinnedMemory;
+typedef struct { GstAllocator parent; } GstB200PinnedAllocator;
+typedef struct { GstAllocatorClass parent_class; } GstB200PinnedAllocatorClass;
+GType gst_b200_pinned_allocator_get_type(void);
+G_DEFINE_TYPE(GstB200PinnedAllocator, gst_b200_pinned_allocator, GST_TYPE_ALLOCATOR)
+
+static GstMemory *gst_b200_pinned_alloc(GstAllocator *allocator, gsize size, GstAllocationParams *params)
+{
+    const gsize maxsize = size + params->prefix + params->padding;
+    void *data = NULL;
+    if (b200vc_host_alloc(maxsize, &data) != B200VC_OK)     /* page-aligned: satisfies any params->align */
+        return NULL;
+    GstB200PinnedMemory *m = g_slice_new0(GstB200PinnedMemory);
+    gst_memory_init(GST_MEMORY_CAST(m), params->flags, allocator, NULL, maxsize, params->align, params->prefix, size);
+    m->data = data;
+    return GST_MEMORY_CAST(m);
+}
+
+static void gst_b200_pinned_free(GstAllocator *allocator, GstMemory *mem)
+{
+    GstB200PinnedMemory *m = (GstB200PinnedMemory *)mem;
+    (void)allocator;
+    b200vc_host_free(m->data);
+    g_slice_free(GstB200PinnedMemory, m);
+}
+
+static gpointer gst_b200_pinned_map(GstMemory *mem, gsize maxsize, GstMapFlags flags)
+{
+    (void)maxsize; (void)flags;
+    return ((GstB200PinnedMemory *)mem)->data;
+}
+
+static void gst_b200_pinned_unmap(GstMemory *mem) { (void)mem; }
+
+static void gst_b200_pinned_allocator_class_init(GstB200PinnedAllocatorClass *klass)
+{
+    GstAllocatorClass *ac = GST_ALLOCATOR_CLASS(klass);
+    ac->alloc = gst_b200_pinned_alloc;
+    ac->free = gst_b200_pinned_free;
+}
+
+static void gst_b200_pinned_allocator_init(GstB200PinnedAllocator *self)
+{
+    GstAllocator *a = GST_ALLOCATOR_CAST(self);
+    a->mem_type = "B200PinnedMemory";
+    a->mem_map = gst_b200_pinned_map;
+    a->mem_unmap = gst_b200_pinned_unmap;
+    /* no mem_share/mem_copy: the defaults copy into system memory, which is always correct */
+    GST_OBJECT_FLAG_SET(a, GST_ALLOCATOR_FLAG_CUSTOM_ALLOC);
+}
 
 G_DEFINE_TYPE(GstB200Convert, gst_b200_convert, GST_TYPE_VIDEO_FILTER)
 
@@ -164,6 +221,80 @@ gst_b200_convert_transform_frame(GstVideoFilter *filter, GstVideoFrame *in, GstV
     return GST_FLOW_OK;
 }
 
+/* A video buffer pool over the pinned allocator for `caps` (transfer full), or NULL. */
+static GstBufferPool *gst_b200_convert_new_pool(GstB200Convert *self, GstCaps *caps, guint size, guint min, guint max,
+                                                gboolean video_meta)
+{
+    GstBufferPool *pool = gst_video_buffer_pool_new();
+    GstStructure *cfg = gst_buffer_pool_get_config(pool);
+    GstAllocationParams params;
+    gst_allocation_params_init(&params);
+    gst_buffer_pool_config_set_params(cfg, caps, size, min, max);
+    gst_buffer_pool_config_set_allocator(cfg, self->allocator, &params);
+    if (video_meta)
+        gst_buffer_pool_config_add_option(cfg, GST_BUFFER_POOL_OPTION_VIDEO_META);
+    if (!gst_buffer_pool_set_config(pool, cfg)) {
+        gst_object_unref(pool);
+        return NULL;
+    }
+    return pool;
+}
+
+/* decide_allocation: where our output buffers come from. A pool proposed by downstream is kept
+ * (x264enc proposes none); otherwise the output pool is ours, in page-locked memory. */
+static gboolean gst_b200_convert_decide_allocation(GstBaseTransform *trans, GstQuery *query)
+{
+    GstB200Convert *self = GST_B200_CONVERT(trans);
+    GstCaps *caps = NULL;
+    GstVideoInfo info;
+    gst_query_parse_allocation(query, &caps, NULL);
+    if (caps && gst_video_info_from_caps(&info, caps) && gst_query_get_n_allocation_pools(query) == 0) {
+        const gboolean vmeta = gst_query_find_allocation_meta(query, GST_VIDEO_META_API_TYPE, NULL);
+        GstBufferPool *pool = gst_b200_convert_new_pool(self, caps, (guint)GST_VIDEO_INFO_SIZE(&info), 2, 0, vmeta);
+        if (pool) {
+            gst_query_add_allocation_pool(query, pool, (guint)GST_VIDEO_INFO_SIZE(&info), 2, 0);
+            gst_object_unref(pool);
+        }
+    }
+    return GST_BASE_TRANSFORM_CLASS(gst_b200_convert_parent_class)->decide_allocation(trans, query);
+}
+
+/* propose_allocation: tell upstream we read strides from GstVideoMeta, and offer it page-locked buffers. */
+static gboolean gst_b200_convert_propose_allocation(GstBaseTransform *trans, GstQuery *decide_query, GstQuery *query)
+{
+    GstB200Convert *self = GST_B200_CONVERT(trans);
+    GstCaps *caps = NULL;
+    gboolean need_pool = FALSE;
+    GstVideoInfo info;
+    if (!GST_BASE_TRANSFORM_CLASS(gst_b200_convert_parent_class)->propose_allocation(trans, decide_query, query))
+        return FALSE;
+    if (decide_query == NULL)          /* passthrough: the base class forwarded the query */
+        return TRUE;
+    gst_query_add_allocation_meta(query, GST_VIDEO_META_API_TYPE, NULL);
+    gst_query_parse_allocation(query, &caps, &need_pool);
+    if (caps && gst_video_info_from_caps(&info, caps)) {
+        GstAllocationParams params;
+        gst_allocation_params_init(&params);
+        gst_query_add_allocation_param(query, self->allocator, &params);
+        if (need_pool) {
+            GstBufferPool *pool = gst_b200_convert_new_pool(self, caps, (guint)GST_VIDEO_INFO_SIZE(&info), 2, 0, TRUE);
+            if (pool) {
+                gst_query_add_allocation_pool(query, pool, (guint)GST_VIDEO_INFO_SIZE(&info), 2, 0);
+                gst_object_unref(pool);
+            }
+        }
+    }
+    return TRUE;
+}
+
+static void gst_b200_convert_finalize(GObject *obj)
+{
+    GstB200Convert *self = GST_B200_CONVERT(obj);
+    if (self->ctx) { b200vc_destroy(self->ctx); self->ctx = NULL; }
+    gst_clear_object(&self->allocator);
+    G_OBJECT_CLASS(gst_b200_convert_parent_class)->finalize(obj);
+}
+
 static gboolean gst_b200_convert_stop(GstBaseTransform *trans)
 {
     GstB200Convert *self = GST_B200_CONVERT(trans);
@@ -203,6 +334,7 @@ static void gst_b200_convert_class_init(GstB200ConvertClass *klass)
     GstVideoFilterClass *vf = GST_VIDEO_FILTER_CLASS(klass);
     go->set_property = gst_b200_convert_set_property;
     go->get_property = gst_b200_convert_get_property;
+    go->finalize = gst_b200_convert_finalize;
     g_object_class_install_property(go, PROP_DEVICE_ID, g_param_spec_int("device-id", "Device", "CUDA device ordinal", 0, 63, 0, G_PARAM_READWRITE));
     g_object_class_install_property(go, PROP_DAMAGE_MAP, g_param_spec_boolean("damage-map", "Damage map", "Emit the 16x16 damage map", FALSE, G_PARAM_READWRITE));
     g_object_class_install_property(go, PROP_N_BANDS, g_param_spec_int("n-bands", "Bands", "Row bands a frame is pipelined in", 0, 64, 0, G_PARAM_READWRITE));
@@ -213,6 +345,8 @@ static void gst_b200_convert_class_init(GstB200ConvertClass *klass)
     bt->transform_caps = GST_DEBUG_FUNCPTR(gst_b200_convert_transform_caps);
     bt->fixate_caps = GST_DEBUG_FUNCPTR(gst_b200_convert_fixate_caps);
     bt->stop = GST_DEBUG_FUNCPTR(gst_b200_convert_stop);
+    bt->decide_allocation = GST_DEBUG_FUNCPTR(gst_b200_convert_decide_allocation);
+    bt->propose_allocation = GST_DEBUG_FUNCPTR(gst_b200_convert_propose_allocation);
     bt->passthrough_on_same_caps = FALSE;
     vf->set_info = GST_DEBUG_FUNCPTR(gst_b200_convert_set_info);
     vf->transform_frame = GST_DEBUG_FUNCPTR(gst_b200_convert_transform_frame);
@@ -221,6 +355,8 @@ static void gst_b200_convert_class_init(GstB200ConvertClass *klass)
 static void gst_b200_convert_init(GstB200Convert *self)
 {
     self->ctx = NULL;
+    self->allocator = g_object_new(gst_b200_pinned_allocator_get_type(), NULL);
+    gst_object_ref_sink(self->allocator);
     self->device_id = 0;
     self->damage_map = FALSE;
     self->n_bands = 0;

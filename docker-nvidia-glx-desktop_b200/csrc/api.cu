@@ -75,6 +75,9 @@ struct b200vc_ctx {
     uint32_t *d_ftaps = nullptr;               // the general fused kernel's per-tile tap records
     FusedTaps ft = { nullptr, nullptr, nullptr, nullptr };
     int tile_h = K2_TILE_H;
+    uint32_t *d_ptaps = nullptr;               // tiled plane scaler's records (two-pass path)
+    PlaneTileKind pt[2] = {};
+    bool plane_tiled = false;                  // two-pass path: pass 2 is the tiled kernel, not the gather kernel
     int box_w = 0, box_h = 0;
     size_t smem_bytes = 0;
     bool fused2x = false;                      // path 1 runs the exact-2:1 register kernel
@@ -277,6 +280,57 @@ void build_fused_taps(const b200vc_config &c, const std::vector<Tap> &hy, const 
     }
 }
 
+// Per-tile tap records of the tiled plane scaler (PlaneTileKind, kernels.cuh) for one plane kind:
+// in_w x in_h -> out_w x out_h through the taps th (horizontal) and tv (vertical). Returns the blob
+// [tile_x | tile_y | col_rec | row_rec] (sections padded to 4 words) and fills everything of `k` but
+// the pointers; `off` receives the sections' word offsets.
+void build_plane_tile_taps(const std::vector<Tap> &th, const std::vector<Tap> &tv, int in_h, int out_w, int out_h,
+                           PlaneTileKind &k, std::vector<uint32_t> &w, size_t off[4])
+{
+    const int tiles_x = (out_w + KPT_TILE_W - 1) / KPT_TILE_W, tiles_y = (out_h + KPT_TILE_H - 1) / KPT_TILE_H;
+    int bw = 0, bh = 0;
+    std::vector<int> sx(tiles_x), sy(tiles_y);
+    for (int bx = 0; bx < tiles_x; bx++) {
+        const int x0 = bx * KPT_TILE_W, x1 = std::min(x0 + KPT_TILE_W, out_w) - 1;
+        sx[bx] = tidx(th[x0]) & ~15;                                       // 16-byte loads
+        bw = std::max(bw, tidx(th[x1]) + 1 - sx[bx] + 1);                  // index+1 is always read
+    }
+    for (int by = 0; by < tiles_y; by++) {
+        const int y0 = by * KPT_TILE_H, y1 = std::min(y0 + KPT_TILE_H, out_h) - 1;
+        sy[by] = tidx(tv[y0]);
+        bh = std::max(bh, tidx(tv[y1]) + 1 - sy[by] + 1);
+    }
+    k.tiles_x = tiles_x;  k.tiles_y = tiles_y;
+    k.bwp = (int)ru(bw, 16);  k.bh = bh;
+    k.src_h = in_h;  k.out_w = out_w;  k.out_h = out_h;
+    auto pad4 = [&] { while (w.size() % 4) w.push_back(0u); };
+    off[0] = w.size();
+    for (int v : sx) w.push_back((uint32_t)v);
+    pad4();
+    off[1] = w.size();
+    for (int v : sy) w.push_back((uint32_t)v);
+    pad4();
+    off[2] = w.size();
+    for (int bx = 0; bx < tiles_x; bx++) {
+        const int x0 = bx * KPT_TILE_W;
+        for (int i = 0; i < KPT_TILE_W; i++) w.push_back((uint32_t)(tidx(th[std::min(x0 + i, out_w - 1)]) - sx[bx]));
+        for (int i = 0; i < KPT_TILE_W; i++) {
+            const Tap t = th[std::min(x0 + i, out_w - 1)];
+            const uint32_t f = tstep(t) ? (uint32_t)tfrac(t) : 0u;
+            w.push_back((255u - f) | (1u << 8) | (f << 16));
+        }
+    }
+    off[3] = w.size();
+    for (int by = 0; by < tiles_y; by++) {
+        const int y0 = by * KPT_TILE_H;
+        for (int i = 0; i < KPT_TILE_H; i++) {
+            const Tap t = tv[std::min(y0 + i, out_h - 1)];
+            w.push_back((uint32_t)((tidx(t) - sy[by]) * k.bwp));  w.push_back(v_weights(t));
+        }
+    }
+    pad4();
+}
+
 // Source window per output tile, mirrored from k2_fused_scale_kernel phase 0; returns the box that
 // covers every tile.
 void fused_box(const b200vc_config &c, const std::vector<Tap> &hy, const std::vector<Tap> &vy,
@@ -474,6 +528,19 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         p.out = plane_set(c->d_mid, c->mid_off, c->mid_pitch, c->mid_size, B200VC_FMT_I420);
         p.w = g.in_w;  p.h = g.in_h;  p.n_frames = nf;  p.mx = c->mx;
         CU_TRY(c, launch_convert(p, B200VC_FMT_I420, site, st));
+        if (c->plane_tiled) {
+            PlaneTileParams t;
+            memset(&t, 0, sizeof t);
+            for (int i = 0; i < 3; i++) { t.src[i] = c->d_mid + c->mid_off[i];  t.src_pitch[i] = (long long)c->mid_pitch[i]; }
+            t.src_frame_stride = (long long)c->mid_size;
+            t.out = out;
+            for (int i = 0; i < 3; i++) if (t.out.p[i]) t.out.p[i] += (size_t)f0 * out.frame_stride;
+            t.k[0] = c->pt[0];  t.k[1] = c->pt[1];
+            t.n_frames = nf;  t.box2x2 = g.scale_mode == B200VC_SCALE_BOX_2X2;
+            CU_TRY(c, launch_plane_tile(t, g.out_format, st));
+            c->stats.kernel_launches += 2;
+            continue;
+        }
         PlaneScaleParams q;
         memset(&q, 0, sizeof q);
         for (int i = 0; i < 3; i++) { q.src[i] = c->d_mid + c->mid_off[i];  q.src_pitch[i] = (long long)c->mid_pitch[i]; }
@@ -510,6 +577,7 @@ void destroy_locked(b200vc_ctx *c)
     for (const HostReg &r : c->registered) cudaHostUnregister(const_cast<void *>(r.base));
     cudaFree(c->d_taps);
     cudaFree(c->d_ftaps);
+    cudaFree(c->d_ptaps);
     cudaFree(c->d_mid);
     if (c->s_h2d) cudaStreamDestroy(c->s_h2d);
     if (c->s_k) cudaStreamDestroy(c->s_k);
@@ -644,6 +712,29 @@ int create_impl(b200vc_ctx *c)
             c->mid_size = ru(c->mid_off[2] + cp * mch, 256);
             c->mid_frames = std::max(1, std::min(g.max_sessions, 8));   // measured: groups of 8 beat groups of 2
             CU_TRY(c, cudaMalloc(&c->d_mid, c->mid_size * c->mid_frames));
+            // pass 2 as 64x32 tiles out of shared memory when every tile's window fits (any ratio up to
+            // about 8:1); larger ratios keep the gather kernel
+            std::vector<uint32_t> w;
+            size_t o0[4], o1[4];
+            build_plane_tile_taps(hy, vy, g.in_h, g.out_w, g.out_h, c->pt[0], w, o0);
+            build_plane_tile_taps(hc, vc, (g.in_h + 1) / 2, (g.out_w + 1) / 2, (g.out_h + 1) / 2, c->pt[1], w, o1);
+            PlaneTileParams probe;
+            memset(&probe, 0, sizeof probe);
+            probe.k[0] = c->pt[0];  probe.k[1] = c->pt[1];
+            const size_t pt_smem = plane_tile_smem_bytes(probe, g.out_format);
+            if (pt_smem <= 64 * 1024) {
+                CU_TRY(c, cudaMalloc(&c->d_ptaps, w.size() * sizeof(uint32_t)));
+                CU_TRY(c, cudaMemcpy(c->d_ptaps, w.data(), w.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+                const size_t *o[2] = { o0, o1 };
+                for (int i = 0; i < 2; i++) {
+                    c->pt[i].tile_x = reinterpret_cast<const int *>(c->d_ptaps + o[i][0]);
+                    c->pt[i].tile_y = reinterpret_cast<const int *>(c->d_ptaps + o[i][1]);
+                    c->pt[i].col_rec = c->d_ptaps + o[i][2];
+                    c->pt[i].row_rec = c->d_ptaps + o[i][3];
+                }
+                CU_TRY(c, plane_tile_prepare(pt_smem));
+                c->plane_tiled = true;
+            }
         }
     }
     CU_TRY(c, cudaDeviceSynchronize());

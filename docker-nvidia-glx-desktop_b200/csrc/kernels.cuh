@@ -103,6 +103,33 @@ struct PlaneScaleParams {
     int box2x2;
 };
 
+// Two-pass scale, pass 2, tiled form: 64 x 32 output tiles of one plane (NV12 chroma: of U and V
+// together), the source window staged in shared memory by coalesced 16-byte loads, taps ready-made in
+// per-tile records like FusedTaps. Kind 0 = luma plane, kind 1 = chroma planes.
+//   tile_x[bx] = window's first source column (multiple of 16), tile_y[by] = its first source line
+//   col_rec[bx][128]: 64 x byte offset of the first tap in a window line, 64 x (255-f) | 1<<8 | f<<16
+//   row_rec[by][64]:  32 x {byte offset of the first line in the window, wv}   (wv as in FusedTaps)
+constexpr int KPT_TILE_W = 128;
+constexpr int KPT_TILE_H = 64;
+struct PlaneTileKind {
+    const int *tile_x, *tile_y;
+    const uint32_t *col_rec, *row_rec;
+    int tiles_x, tiles_y;
+    int bwp, bh;            // window pitch in shared memory (bytes, multiple of 16) and lines (without the spare one)
+    int src_h;              // lines of the source plane (window lines past the last one repeat it)
+    int out_w, out_h;       // samples of the output plane
+};
+struct PlaneTileParams {
+    const uint8_t *src[3]; long long src_pitch[3]; long long src_frame_stride;
+    PlaneSet out;
+    PlaneTileKind k[2];
+    int n_frames;
+    int box2x2;
+};
+size_t plane_tile_smem_bytes(const PlaneTileParams &p, int fmt);
+cudaError_t plane_tile_prepare(size_t smem_bytes);
+cudaError_t launch_plane_tile(const PlaneTileParams &p, int fmt, cudaStream_t st);
+
 constexpr int K1_TILE_W = 128;   // pixels per warp stripe (one LDG.128 per lane per line)
 constexpr int K1_TILE_H = 16;    // one macroblock row per warp stripe
 constexpr int K1_WARPS_PER_CTA = 4;

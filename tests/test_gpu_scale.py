@@ -116,3 +116,19 @@ def test_odd_sizes_with_scaling(conv, orc, geo):
         assert conv.info().path == 2
         buf, off, pit = conv.transform_frame(frame)
         assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), _want(orc, frame, ow, oh, fmt, m, rg, site), f"{geo} fmt{fmt}")
+
+
+@pytest.mark.parametrize("geo,flags,tile_h", [((2560, 1440, 1920, 1080), 0, 32),
+                                              ((3840, 2160, 1920, 1080), b200vc.FLAG_FORCE_GENERIC_FUSED, 16),
+                                              ((3840, 2160, 1280, 720), 0, 8)])
+def test_general_kernel_tile_heights(conv, orc, geo, flags, tile_h):
+    """The general fused kernel picks 32-, 16- or 8-row tiles by window size; each height is its own
+    instantiation, so each is checked at the geometry that selects it (bars: every fraction occurs)."""
+    iw, ih, ow, oh = geo
+    frame = orc.synth("bars", iw, ih, 4)
+    for fmt, site in [(0, 1), (1, 0)]:
+        conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=1, range_=0, chroma_site=site, flags=flags)
+        inf = conv.info()
+        assert inf.path == 1 and inf.fused_2to1 == 0 and inf.tile_h == tile_h
+        buf, off, pit = conv.transform_frame(frame)
+        assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), _want(orc, frame, ow, oh, fmt, 1, 0, site), f"{geo} fmt{fmt}")

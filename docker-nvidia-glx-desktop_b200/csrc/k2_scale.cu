@@ -285,27 +285,41 @@ __global__ void __launch_bounds__(256)
 k2_fused_2x_kernel(const __grid_constant__ CUtensorMap src_map, const Fused2xParams p)
 {
     constexpr int BW = K2X_SRC_W + K2X_HALO;               // 132
-    __shared__ __align__(128) uint32_t s_src[K2X_SRC_H][BW];
-    __shared__ __align__(8) uint64_t s_bar;
+    constexpr int NT = K2X_TILES_PER_CTA;                  // vertically adjacent tiles per CTA, all loads issued up front
+    __shared__ __align__(128) uint32_t s_tiles[NT][K2X_SRC_H][BW];
+    __shared__ __align__(8) uint64_t s_bar[NT];
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int frame = blockIdx.z;
-    const int tx = blockIdx.x * K2X_SRC_W, ty = blockIdx.y * K2X_SRC_H;   // source tile origin
+    const int tx = blockIdx.x * K2X_SRC_W, ty0 = blockIdx.y * (K2X_SRC_H * NT);   // source origin of the first tile
 
     if (threadIdx.x == 0) {
-        const uint32_t bar = smem_u32(&s_bar);
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+#pragma unroll
+        for (int t = 0; t < NT; t++)
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_bar[t])));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)sizeof(s_src)) : "memory");
-        asm volatile(
-            "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
-            " [%0], [%1, {%2, %3, %4}], [%5];"
-            ::"r"(smem_u32(&s_src[0][0])), "l"(reinterpret_cast<uint64_t>(&src_map)), "r"(tx - K2X_HALO), "r"(ty), "r"(frame),
-              "r"(bar) : "memory");
+#pragma unroll
+        for (int t = 0; t < NT; t++) {
+            if (ty0 + t * K2X_SRC_H < p.in_h) {
+                const uint32_t bar = smem_u32(&s_bar[t]);
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+                             ::"r"(bar), "r"((uint32_t)sizeof(s_tiles[0])) : "memory");
+                asm volatile(
+                    "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+                    " [%0], [%1, {%2, %3, %4}], [%5];"
+                    ::"r"(smem_u32(&s_tiles[t][0][0])), "l"(reinterpret_cast<uint64_t>(&src_map)), "r"(tx - K2X_HALO),
+                      "r"(ty0 + t * K2X_SRC_H), "r"(frame), "r"(bar) : "memory");
+            }
+        }
     }
     __syncthreads();
+#pragma unroll 1
+    for (int t = 0; t < NT; t++) {
+    const int ty = ty0 + t * K2X_SRC_H;
+    if (ty >= p.in_h) break;
+    const uint32_t (*s_src)[BW] = s_tiles[t];
     {
-        const uint32_t bar = smem_u32(&s_bar);
+        const uint32_t bar = smem_u32(&s_bar[t]);
         uint32_t done = 0;
         while (!done) {
             asm volatile(
@@ -397,6 +411,7 @@ k2_fused_2x_kernel(const __grid_constant__ CUtensorMap src_map, const Fused2xPar
                 (uint16_t)((cuv & 0xffu) | ((cuv >> 16) << 8));
         }
     }
+    }   // tiles of this CTA
 }
 
 // ---- two-pass, pass 2: scale the planes of a full-size intermediate I420 -----------------------
@@ -539,7 +554,7 @@ cudaError_t launch_fused_2x(const CUtensorMap &src_map, const Fused2xParams &p, 
 {
     if (p.in_w <= 0 || p.in_h <= 0 || p.n_frames <= 0 || (p.in_w & 3) || (p.in_h & 3))
         return cudaErrorInvalidValue;
-    dim3 grid((p.in_w + K2X_SRC_W - 1) / K2X_SRC_W, (p.in_h + K2X_SRC_H - 1) / K2X_SRC_H, p.n_frames);
+    dim3 grid((p.in_w + K2X_SRC_W - 1) / K2X_SRC_W, (p.in_h + K2X_SRC_H * K2X_TILES_PER_CTA - 1) / (K2X_SRC_H * K2X_TILES_PER_CTA), p.n_frames);
     if (fmt == 0)
         return site ? launch_2x2<0, 1>(src_map, p, box2x2, grid, st) : launch_2x2<0, 0>(src_map, p, box2x2, grid, st);
     return site ? launch_2x2<1, 1>(src_map, p, box2x2, grid, st) : launch_2x2<1, 0>(src_map, p, box2x2, grid, st);

@@ -137,6 +137,7 @@ constexpr int K2_TILE_W = 64;    // output pixels per CTA tile
 constexpr int K2_TILE_H = 16;    // exact-2:1 kernel; the general kernel's is FusedScaleParams::tile_h
 constexpr int K2X_SRC_W = 128;   // exact-2:1 kernel: source tile per CTA (8 warps x 4 lines, 32 lanes x 4 pixels)
 constexpr int K2X_SRC_H = 32;
+constexpr int K2X_TILES_PER_CTA = 2;   // exact-2:1 kernel: tiles per CTA (the later loads hide behind the first tile's work)
 constexpr int K2X_HALO = 4;      // columns loaded left of the tile (TMA boxes start 16-byte aligned)
 
 // Launchers return the cudaError_t of the launch. fmt/site as in b200vc.h.

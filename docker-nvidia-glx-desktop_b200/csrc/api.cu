@@ -236,7 +236,7 @@ void build_fused_taps(const b200vc_config &c, const std::vector<Tap> &hy, const 
 {
     const int site = c.chroma_site == B200VC_SITE_H_COSITED ? 1 : 0;
     const int tiles_x = (c.out_w + K2_TILE_W - 1) / K2_TILE_W, tiles_y = (c.out_h + tile_h - 1) / tile_h;
-    const int cw_out = c.out_w / 2, ch_out = c.out_h / 2;                      // fused path: even sizes
+    const int cw_out = (c.out_w + 1) / 2, ch_out = (c.out_h + 1) / 2;          // odd frames: chroma planes round up
     auto pad4 = [&] { while (o.w.size() % 4) o.w.push_back(0u); };
     o.w.clear();
     o.tile_x = o.w.size();
@@ -673,8 +673,8 @@ int create_impl(b200vc_ctx *c)
         }
         const bool fits = c->box_w <= 256 && c->box_h <= 256 &&
                           c->smem_bytes + 1024 <= (size_t)c->prop.sharedMemPerBlockOptin;
-        const bool all_even = !((g.in_w | g.in_h | g.out_w | g.out_h) & 1);      // the fused kernels assume it
-        c->path = (fits && all_even && !(g.flags & B200VC_FLAG_FORCE_TWO_PASS)) ? 1 : 2;
+        // (odd sizes run the general fused kernel; the exact-2:1 kernel needs multiples of 4, BOX even sizes)
+        c->path = (fits && !(g.flags & B200VC_FLAG_FORCE_TWO_PASS)) ? 1 : 2;
         const bool exact2 = g.in_w == 2 * g.out_w && g.in_h == 2 * g.out_h && (g.in_w % 4) == 0 && (g.in_h % 4) == 0;
         c->fused2x = c->path == 1 && exact2 && !(g.flags & B200VC_FLAG_FORCE_GENERIC_FUSED) &&
                      (g.scale_mode == B200VC_SCALE_BOX_2X2 ||

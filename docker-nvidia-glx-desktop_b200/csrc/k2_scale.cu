@@ -152,6 +152,22 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
         }
     }
 
+    // ---- odd frames: the pixel column / line just past the frame repeats the last one --------------
+    // (an odd frame's last pixel and last line are chroma sites of their own: h2 averages it with itself,
+    // the cosited filter gives it l + 3c, the vertical mean pairs the line with itself — SURVEY A.4.
+    // The TMA unit zero-filled those cells; after this, phase 1 needs no special case.)
+    if ((p.in_w | p.in_h) & 1) {
+        const int dupx = p.in_w - sx0, dupy = p.in_h - p.ft.tile_y[blockIdx.y];
+        const bool fixx = (p.in_w & 1) && dupx > 0 && dupx < bw, fixy = (p.in_h & 1) && dupy > 0 && dupy < bh;
+        if (fixx)
+            for (int r = tid; r < bh; r += 256)
+                s_src[r * bw + dupx] = s_src[((fixy && r == dupy) ? dupy - 1 : r) * bw + dupx - 1];
+        if (fixy)
+            for (int c = tid; c < bw; c += 256)
+                if (!(fixx && c == dupx)) s_src[dupy * bw + c] = s_src[(dupy - 1) * bw + c];
+        __syncthreads();
+    }
+
     // ---- phase 1: convert the window (8 columns x 2 lines per item, as two halves) ---------------
     // Items are walked without divisions (host-made reciprocal for the start, increments after); a
     // first 4-column group that holds nothing but halo is skipped. The second half takes its left
@@ -252,13 +268,13 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
         } else if (FMT == 0) {
             const int i = c - TILE_H * 4;
             const int pl = i / TILE_H, r = (i >> 1) & (TILE_H / 2 - 1), xb = (x0 >> 1) + (c & 1) * 16;
-            row_ok = (y0 >> 1) + r < (p.out_h >> 1);
-            n = (p.out_w >> 1) - xb;
+            row_ok = (y0 >> 1) + r < ((p.out_h + 1) >> 1);
+            n = ((p.out_w + 1) >> 1) - xb;
             dst = p.out.p[1 + pl] + fo + (long long)((y0 >> 1) + r) * p.out.pitch[1 + pl] + xb;
         } else {
             const int r = (c - TILE_H * 4) >> 2, xb = x0 + (c & 3) * 16;
-            row_ok = (y0 >> 1) + r < (p.out_h >> 1);
-            n = p.out_w - xb;
+            row_ok = (y0 >> 1) + r < ((p.out_h + 1) >> 1);
+            n = 2 * ((p.out_w + 1) >> 1) - xb;
             dst = p.out.p[1] + fo + (long long)((y0 >> 1) + r) * p.out.pitch[1] + xb;
         }
         if (row_ok) {

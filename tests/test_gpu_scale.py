@@ -107,15 +107,20 @@ def test_device_entry_point_scaled_batch(conv, orc):
 
 @pytest.mark.parametrize("geo", [(7, 9, 4, 5), (131, 35, 65, 17), (1365, 767, 683, 384), (100, 61, 47, 26), (64, 36, 33, 19),
                                  (1919, 1079, 1280, 720), (1920, 1080, 1281, 721)])
-def test_odd_sizes_with_scaling(conv, orc, geo):
-    """Any odd width or height sends scaling onto the general two-pass path; chroma planes round up."""
+@pytest.mark.parametrize("two_pass", [False, True])
+def test_odd_sizes_with_scaling(conv, orc, geo, two_pass):
+    """Odd widths and heights: chroma planes round up, the last pixel / line is a chroma site of its own.
+    The general fused kernel takes them (it repeats the last column / line inside its window) and so does
+    the two-pass path."""
     iw, ih, ow, oh = geo
     frame = orc.synth("rand", iw, ih, 17)
     for fmt, m, rg, site in [(0, 1, 0, 1), (1, 0, 1, 0)]:
-        conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=m, range_=rg, chroma_site=site)
-        assert conv.info().path == 2
+        conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=m, range_=rg, chroma_site=site,
+                      flags=b200vc.FLAG_FORCE_TWO_PASS if two_pass else 0)
+        assert conv.info().path == (2 if two_pass else 1)
         buf, off, pit = conv.transform_frame(frame)
-        assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), _want(orc, frame, ow, oh, fmt, m, rg, site), f"{geo} fmt{fmt}")
+        assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), _want(orc, frame, ow, oh, fmt, m, rg, site),
+                            f"{geo} fmt{fmt} two_pass={two_pass}")
 
 
 @pytest.mark.parametrize("geo,flags,tile_h", [((2560, 1440, 1920, 1080), 0, 32),

@@ -117,6 +117,12 @@ int fail(b200vc_ctx *c, int code, const char *fmt, ...)
 size_t ru(size_t v, size_t a) { return (v + a - 1) / a * a; }
 bool aligned16(const void *p) { return ((uintptr_t)p & 15) == 0; }
 
+// Dynamic shared memory the general fused kernel may ask for: the device's opt-in limit less room for
+// its static arrays. The kernels' function attribute is set to the device limit (*_prepare), never to one
+// geometry's need: the kernels are shared by every context of the process, and a later, smaller
+// negotiation must not shrink an earlier one's.
+size_t dyn_smem_cap(const b200vc_ctx *c) { return (size_t)c->prop.sharedMemPerBlockOptin - 8192; }
+
 // SURVEY A.2 table; rows Y,U,V of (cR, cG, cB, off). The oracle derives the same numbers from
 // Kr/Kb in double precision; tests compare the two.
 const int kMatrix[3][2][3][4] = {
@@ -672,7 +678,7 @@ int create_impl(b200vc_ctx *c)
                 break;
         }
         const bool fits = c->box_w <= 256 && c->box_h <= 256 &&
-                          c->smem_bytes + 1024 <= (size_t)c->prop.sharedMemPerBlockOptin;
+                          c->smem_bytes <= dyn_smem_cap(c);
         // (odd sizes run the general fused kernel; the exact-2:1 kernel needs multiples of 4, BOX even sizes)
         c->path = (fits && !(g.flags & B200VC_FLAG_FORCE_TWO_PASS)) ? 1 : 2;
         const bool exact2 = g.in_w == 2 * g.out_w && g.in_h == 2 * g.out_h && (g.in_w % 4) == 0 && (g.in_h % 4) == 0;
@@ -704,7 +710,7 @@ int create_impl(b200vc_ctx *c)
             if (!fn || qres != cudaDriverEntryPointSuccess)
                 return fail(c, B200VC_ERR_CUDA, "the driver does not export cuTensorMapEncodeTiled");
             c->encode_tiled = (PFN_cuTensorMapEncodeTiled_v12000)fn;
-            if (!c->fused2x) CU_TRY(c, fused_scale_prepare(c->smem_bytes));
+            if (!c->fused2x) CU_TRY(c, fused_scale_prepare((size_t)c->prop.sharedMemPerBlockOptin));
         } else {
             const size_t yp = ru(g.in_w + 1, 256), cp = ru((g.in_w + 1) / 2, 256), mch = (size_t)(g.in_h + 1) / 2;
             c->mid_pitch[0] = yp;  c->mid_pitch[1] = cp;  c->mid_pitch[2] = cp;
@@ -732,7 +738,7 @@ int create_impl(b200vc_ctx *c)
                     c->pt[i].col_rec = c->d_ptaps + o[i][2];
                     c->pt[i].row_rec = c->d_ptaps + o[i][3];
                 }
-                CU_TRY(c, plane_tile_prepare(pt_smem));
+                CU_TRY(c, plane_tile_prepare((size_t)c->prop.sharedMemPerBlockOptin));
                 c->plane_tiled = true;
             }
         }

@@ -145,11 +145,16 @@ size_t plane_tile_smem_bytes(const PlaneTileParams &p, int fmt)
     return (luma > chroma ? luma : chroma) + 16;             // a clamped tap reads one byte past its window line
 }
 
-cudaError_t plane_tile_prepare(size_t smem_bytes)
+cudaError_t plane_tile_prepare(size_t optin_bytes)
 {
-    cudaError_t e = cudaFuncSetAttribute(k2_plane_tile_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+    cudaFuncAttributes a;
+    cudaError_t e = cudaFuncGetAttributes(&a, k2_plane_tile_kernel<0>);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(k2_plane_tile_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+    e = cudaFuncSetAttribute(k2_plane_tile_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(optin_bytes - a.sharedSizeBytes));
+    if (e != cudaSuccess) return e;
+    e = cudaFuncGetAttributes(&a, k2_plane_tile_kernel<1>);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(k2_plane_tile_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(optin_bytes - a.sharedSizeBytes));
 }
 
 cudaError_t launch_plane_tile(const PlaneTileParams &p, int fmt, cudaStream_t st)

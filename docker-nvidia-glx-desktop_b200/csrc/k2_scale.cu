@@ -56,6 +56,20 @@ __device__ __noinline__ void issue_window_load(uint64_t *s_bar, void *dst, const
         : "memory");
 }
 
+// Odd frames, edge tiles of the general fused kernel: window column dupx / line dupy (the ones just past
+// the frame, zero-filled by the TMA unit) become copies of the column / line before them.
+__device__ __forceinline__ void repeat_last_column_and_line(uint32_t *s_src, int bw, int bh, int dupx, int dupy, int odd_w,
+                                                         int odd_h, int tid)
+{
+    const bool fixx = odd_w && dupx > 0 && dupx < bw, fixy = odd_h && dupy > 0 && dupy < bh;
+    if (fixx)
+        for (int r = tid; r < bh; r += 256)
+            s_src[r * bw + dupx] = s_src[((fixy && r == dupy) ? dupy - 1 : r) * bw + dupx - 1];
+    if (fixy)
+        for (int c = tid; c < bw; c += 256)
+            if (!(fixx && c == dupx)) s_src[dupy * bw + c] = s_src[(dupy - 1) * bw + c];
+}
+
 // Phase 1 of the general fused kernel: one item = 8 columns x 2 lines of the window (two 4-column
 // groups; `two` false: only the first), BGRx in s_src -> Y bytes in s_yf and filtered, vertically
 // averaged (u,v) pairs in s_cf. kx = first group's index in the line pair, sx0 = window's frame column.
@@ -107,7 +121,7 @@ __device__ __forceinline__ void convert_item(const uint32_t *s_src, uint8_t *s_y
     }
 }
 
-template <int FMT, int SITE, bool NEG, int TILE_H>
+template <int FMT, int SITE, bool NEG, int TILE_H, bool ODD>
 __global__ void __launch_bounds__(256, 8)
 k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedScaleParams p)
 {
@@ -156,15 +170,8 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
     // (an odd frame's last pixel and last line are chroma sites of their own: h2 averages it with itself,
     // the cosited filter gives it l + 3c, the vertical mean pairs the line with itself — SURVEY A.4.
     // The TMA unit zero-filled those cells; after this, phase 1 needs no special case.)
-    if ((p.in_w | p.in_h) & 1) {
-        const int dupx = p.in_w - sx0, dupy = p.in_h - p.ft.tile_y[blockIdx.y];
-        const bool fixx = (p.in_w & 1) && dupx > 0 && dupx < bw, fixy = (p.in_h & 1) && dupy > 0 && dupy < bh;
-        if (fixx)
-            for (int r = tid; r < bh; r += 256)
-                s_src[r * bw + dupx] = s_src[((fixy && r == dupy) ? dupy - 1 : r) * bw + dupx - 1];
-        if (fixy)
-            for (int c = tid; c < bw; c += 256)
-                if (!(fixx && c == dupx)) s_src[dupy * bw + c] = s_src[(dupy - 1) * bw + c];
+    if (ODD) {                                         // instantiated apart: even frames pay nothing
+        repeat_last_column_and_line(s_src, bw, bh, p.in_w - sx0, p.in_h - p.ft.tile_y[blockIdx.y], p.in_w & 1, p.in_h & 1, tid);
         __syncthreads();
     }
 
@@ -517,33 +524,35 @@ __global__ void __launch_bounds__(128) k2_plane_scale_kernel(const PlaneScalePar
     }
 }
 
-template <int FMT, int SITE>
-cudaError_t launch_fused2(const CUtensorMap &map, const FusedScaleParams &p, dim3 grid, size_t smem, cudaStream_t st)
+template <int FMT, int SITE, bool NEG, bool ODD>
+cudaError_t launch_fused4(const CUtensorMap &map, const FusedScaleParams &p, dim3 grid, size_t smem, cudaStream_t st)
 {
-    if (p.tile_h == 8) {
-        if (p.mx.neg)
-            k2_fused_scale_kernel<FMT, SITE, true, 8><<<grid, 256, smem, st>>>(map, p);
-        else
-            k2_fused_scale_kernel<FMT, SITE, false, 8><<<grid, 256, smem, st>>>(map, p);
-    } else if (p.tile_h == 32) {
-        if (p.mx.neg)
-            k2_fused_scale_kernel<FMT, SITE, true, 32><<<grid, 256, smem, st>>>(map, p);
-        else
-            k2_fused_scale_kernel<FMT, SITE, false, 32><<<grid, 256, smem, st>>>(map, p);
-
-    } else {
-        if (p.mx.neg)
-            k2_fused_scale_kernel<FMT, SITE, true, 16><<<grid, 256, smem, st>>>(map, p);
-        else
-            k2_fused_scale_kernel<FMT, SITE, false, 16><<<grid, 256, smem, st>>>(map, p);
-    }
+    if (p.tile_h == 8)
+        k2_fused_scale_kernel<FMT, SITE, NEG, 8, ODD><<<grid, 256, smem, st>>>(map, p);
+    else if (p.tile_h == 32)
+        k2_fused_scale_kernel<FMT, SITE, NEG, 32, ODD><<<grid, 256, smem, st>>>(map, p);
+    else
+        k2_fused_scale_kernel<FMT, SITE, NEG, 16, ODD><<<grid, 256, smem, st>>>(map, p);
     return cudaGetLastError();
 }
 
-template <typename K>
-cudaError_t set_smem(K kernel, size_t bytes)
+template <int FMT, int SITE>
+cudaError_t launch_fused2(const CUtensorMap &map, const FusedScaleParams &p, dim3 grid, size_t smem, cudaStream_t st)
 {
-    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    const bool odd = (p.in_w | p.in_h) & 1;                // odd frames: the variant that repeats the last column / line
+    if (p.mx.neg)
+        return odd ? launch_fused4<FMT, SITE, true, true>(map, p, grid, smem, st) : launch_fused4<FMT, SITE, true, false>(map, p, grid, smem, st);
+    return odd ? launch_fused4<FMT, SITE, false, true>(map, p, grid, smem, st) : launch_fused4<FMT, SITE, false, false>(map, p, grid, smem, st);
+}
+
+// Lets a kernel ask for dynamic shared memory up to the device's opt-in limit less its own static arrays.
+template <typename K>
+cudaError_t set_smem(K kernel, size_t optin_bytes)
+{
+    cudaFuncAttributes a;
+    cudaError_t e = cudaFuncGetAttributes(&a, kernel);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(optin_bytes - a.sharedSizeBytes));
 }
 
 
@@ -586,13 +595,16 @@ size_t fused_scale_smem_bytes(int box_w, int box_h)
     return (size_t)box_w * box_h * 6 + (size_t)box_w * 2 + 16;
 }
 
-cudaError_t fused_scale_prepare(size_t smem_bytes)
+cudaError_t fused_scale_prepare(size_t optin_bytes)
 {
     cudaError_t e;
 #define B200VC_SET(F, S, N) \
-    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 8>, smem_bytes)) != cudaSuccess) return e; \
-    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 16>, smem_bytes)) != cudaSuccess) return e; \
-    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 32>, smem_bytes)) != cudaSuccess) return e;
+    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 8, false>, optin_bytes)) != cudaSuccess) return e; \
+    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 16, false>, optin_bytes)) != cudaSuccess) return e; \
+    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 32, false>, optin_bytes)) != cudaSuccess) return e; \
+    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 8, true>, optin_bytes)) != cudaSuccess) return e; \
+    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 16, true>, optin_bytes)) != cudaSuccess) return e; \
+    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 32, true>, optin_bytes)) != cudaSuccess) return e;
     B200VC_SET(0, 0, false) B200VC_SET(0, 0, true) B200VC_SET(0, 1, false) B200VC_SET(0, 1, true)
     B200VC_SET(1, 0, false) B200VC_SET(1, 0, true) B200VC_SET(1, 1, false) B200VC_SET(1, 1, true)
 #undef B200VC_SET

@@ -127,7 +127,7 @@ struct PlaneTileParams {
     int box2x2;
 };
 size_t plane_tile_smem_bytes(const PlaneTileParams &p, int fmt);
-cudaError_t plane_tile_prepare(size_t smem_bytes);
+cudaError_t plane_tile_prepare(size_t optin_bytes);   // once per device: dynamic shared memory up to the opt-in limit
 cudaError_t launch_plane_tile(const PlaneTileParams &p, int fmt, cudaStream_t st);
 
 constexpr int K1_TILE_W = 128;   // pixels per warp stripe (one LDG.128 per lane per line)
@@ -148,6 +148,6 @@ cudaError_t launch_fused_2x(const CUtensorMap &src_map, const Fused2xParams &p, 
                             cudaStream_t st);
 cudaError_t launch_plane_scale(const PlaneScaleParams &p, int fmt, cudaStream_t st);
 size_t fused_scale_smem_bytes(int box_w, int box_h);
-cudaError_t fused_scale_prepare(size_t smem_bytes);   // opt in to > 48 KB dynamic shared memory
+cudaError_t fused_scale_prepare(size_t optin_bytes);   // once per device: dynamic shared memory up to the opt-in limit
 
 }  // namespace b200vc

@@ -145,3 +145,21 @@ def test_8k_frame(orc):
     want = orc.convert(f, 0, 1, 0, 1, out_size=(w // 2, h // 2), threads=8)
     assert_planes_equal(plane_views(buf, off, pit, 0, w // 2, h // 2), plane_views(*want, 0, w // 2, h // 2), "8K -> 4K")
     conv.stop()
+
+
+def test_two_contexts_with_different_windows(orc):
+    """Two converters in one process share the kernels: negotiating the second (small window) must not
+    take shared memory away from the first (large window)."""
+    big, small = b200vc.Converter(0), b200vc.Converter(0)
+    try:
+        big.set_info(1920, 1080, 640, 360, matrix=1, range_=0, chroma_site=1)            # 3:1, ~30 KB window
+        small.set_info(64, 36, 48, 28, matrix=1, range_=0, chroma_site=1)                # a few KB
+        assert big.info().path == 1 and small.info().path == 1
+        for conv, (iw, ih, ow, oh) in ((big, (1920, 1080, 640, 360)), (small, (64, 36, 48, 28)), (big, (1920, 1080, 640, 360))):
+            frame = orc.synth("rand", iw, ih, 5)
+            buf, off, pit = conv.transform_frame(frame)
+            want, woff, wpit = orc.convert(frame, 0, 1, 0, 1, out_size=(ow, oh))
+            assert_planes_equal(plane_views(buf, off, pit, 0, ow, oh), plane_views(want, woff, wpit, 0, ow, oh), f"{iw}x{ih}")
+    finally:
+        big.stop()
+        small.stop()

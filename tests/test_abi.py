@@ -145,3 +145,22 @@ def test_damage_map_to_rectangles(orc):
     chk = (np.indices(dm.shape).sum(0) & 1).astype(np.uint8)
     got, need = b200vc.damage_rects(chk, w, h, max_rects=10)
     assert len(got) == 10 and need == int(chk.sum())
+
+
+def test_gstreamer_shim_parses_against_stub_headers():
+    """GStreamer is not installed here, so gst/gstb200convert.c has never met the real headers. This runs
+    it through gcc's front end against tests/gst_stub (a hand-written stand-in for the slice of the 1.x API
+    the shim uses) with implicit declarations and pointer mismatches as errors: it pins the shim's own C and
+    its calls into include/b200vc.h, not its conformance to GStreamer."""
+    import shutil
+    import subprocess
+    gcc = shutil.which("gcc")
+    if not gcc:
+        pytest.skip("no gcc")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([gcc, "-std=gnu11", "-fsyntax-only", "-Wall", "-Werror=implicit-function-declaration",
+                        "-Werror=incompatible-pointer-types", "-Werror=int-conversion",
+                        "-I" + os.path.join(root, "tests", "gst_stub"), "-I" + os.path.join(root, "include"),
+                        os.path.join(root, "docker-nvidia-glx-desktop_b200", "gst", "gstb200convert.c")],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]

@@ -22,6 +22,14 @@
 #define GST_TYPE_B200_CONVERT (gst_b200_convert_get_type())
 G_DECLARE_FINAL_TYPE(GstB200Convert, gst_b200_convert, GST, B200_CONVERT, GstVideoFilter)
 
+/* One frame in flight in one-frame-latency mode: both buffers stay mapped until the frame is collected. */
+typedef struct {
+    gboolean valid;
+    GstBuffer *in, *out;
+    GstVideoFrame in_frame, out_frame;
+    guint64 ticket;
+} GstB200Pending;
+
 struct _GstB200Convert {
     GstVideoFilter parent;
     b200vc_ctx *ctx;
@@ -29,6 +37,8 @@ struct _GstB200Convert {
     gint device_id;
     gboolean damage_map;
     gint n_bands;
+    gboolean one_frame_latency;   /* submit frame N, hand out frame N-1: its D2H overlaps frame N's H2D */
+    GstB200Pending pending;
 };
 
 /* ---- allocator over b200vc_host_alloc: buffers the copy engines reach without staging -------------
@@ -92,7 +102,7 @@ G_DEFINE_TYPE(GstB200Convert, gst_b200_convert, GST_TYPE_VIDEO_FILTER)
 GST_DEBUG_CATEGORY_STATIC(b200convert_debug);
 #define GST_CAT_DEFAULT b200convert_debug
 
-enum { PROP_0, PROP_DEVICE_ID, PROP_DAMAGE_MAP, PROP_N_BANDS };
+enum { PROP_0, PROP_DEVICE_ID, PROP_DAMAGE_MAP, PROP_N_BANDS, PROP_ONE_FRAME_LATENCY };
 
 static GstStaticPadTemplate sink_tmpl = GST_STATIC_PAD_TEMPLATE("sink", GST_PAD_SINK, GST_PAD_ALWAYS,
     GST_STATIC_CAPS("video/x-raw, format=(string){BGRx,BGRA,RGBx,RGBA,xRGB,ARGB,xBGR,ABGR}, width=(int)[2,16384], height=(int)[2,16384], "
@@ -159,6 +169,37 @@ static int matrix_of(const GstVideoInfo *i)
     }
 }
 
+/* One-frame-latency mode: waits for the frame in flight, releases its input and returns its output
+ * buffer (transfer full), or NULL if there is none or it failed. */
+static GstBuffer *gst_b200_convert_finish_pending(GstB200Convert *self)
+{
+    GstB200Pending *p = &self->pending;
+    GstBuffer *out;
+    int rc;
+    if (!p->valid)
+        return NULL;
+    rc = self->ctx ? b200vc_collect(self->ctx, p->ticket) : B200VC_ERR_NOT_NEGOTIATED;
+    gst_video_frame_unmap(&p->out_frame);
+    gst_video_frame_unmap(&p->in_frame);
+    gst_buffer_unref(p->in);
+    out = p->out;
+    p->in = p->out = NULL;
+    p->valid = FALSE;
+    if (rc != B200VC_OK) {
+        GST_ELEMENT_ERROR(self, LIBRARY, FAILED, ("b200vc_collect: %s", b200vc_status_string(rc)), ("%s", b200vc_last_error(self->ctx)));
+        gst_buffer_unref(out);
+        return NULL;
+    }
+    return out;
+}
+
+static void gst_b200_convert_drop_pending(GstB200Convert *self)
+{
+    GstBuffer *out = gst_b200_convert_finish_pending(self);
+    if (out)
+        gst_buffer_unref(out);
+}
+
 /* set_info: (re)build the converter for the negotiated caps. FALSE = not negotiated. */
 static gboolean
 gst_b200_convert_set_info(GstVideoFilter *filter, GstCaps *incaps, GstVideoInfo *in, GstCaps *outcaps, GstVideoInfo *out)
@@ -181,6 +222,8 @@ gst_b200_convert_set_info(GstVideoFilter *filter, GstCaps *incaps, GstVideoInfo 
     cfg.flags = (self->damage_map && cfg.in_w == cfg.out_w && cfg.in_h == cfg.out_h) ? B200VC_FLAG_DAMAGE_MAP : 0;
     cfg.flags |= B200VC_FLAG_REGISTER_HOST;           /* ximagesrc hands out a small pool of XShm images */
     cfg.n_bands = self->n_bands;
+    cfg.n_inflight = self->one_frame_latency ? 2 : 1;
+    gst_b200_convert_drop_pending(self);          /* normally gone already: the CAPS event pushed it */
     if (self->ctx) { b200vc_destroy(self->ctx); self->ctx = NULL; }
     int rc = b200vc_create(&cfg, &self->ctx);
     if (rc != B200VC_OK) {
@@ -219,6 +262,106 @@ gst_b200_convert_transform_frame(GstVideoFilter *filter, GstVideoFrame *in, GstV
         return GST_FLOW_ERROR;
     }
     return GST_FLOW_OK;
+}
+
+/* generate_output, one-frame-latency mode: the queued input is enqueued (H2D, kernel, D2H on the
+ * library's streams) and the call returns the frame before it, which has had a whole frame period to
+ * finish. Every output buffer carries its own input's timestamps (prepare_output_buffer copied them).
+ * Without the property this is the base class's synchronous path through transform_frame. */
+static GstFlowReturn gst_b200_convert_generate_output(GstBaseTransform *trans, GstBuffer **outbuf)
+{
+    GstB200Convert *self = GST_B200_CONVERT(trans);
+    GstVideoFilter *vf = (GstVideoFilter *)trans;
+    GstBaseTransformClass *bclass = GST_BASE_TRANSFORM_CLASS(gst_b200_convert_parent_class);
+    GstB200Pending next = { 0 };
+    GstFlowReturn ret;
+    b200vc_frame f = { 0 };
+    int rc;
+    if (!self->one_frame_latency)
+        return bclass->generate_output(trans, outbuf);
+    *outbuf = NULL;
+    next.in = trans->queued_buf;
+    if (next.in == NULL)                     /* second call of the chain loop: nothing more to give */
+        return GST_FLOW_OK;
+    trans->queued_buf = NULL;
+    if (!self->ctx) {
+        gst_buffer_unref(next.in);
+        return GST_FLOW_NOT_NEGOTIATED;
+    }
+    ret = bclass->prepare_output_buffer(trans, next.in, &next.out);
+    if (ret != GST_FLOW_OK || next.out == NULL) {
+        gst_buffer_unref(next.in);
+        return ret != GST_FLOW_OK ? ret : GST_FLOW_ERROR;
+    }
+    if (!gst_video_frame_map(&next.in_frame, &vf->in_info, next.in, GST_MAP_READ)) {
+        gst_buffer_unref(next.in);  gst_buffer_unref(next.out);
+        return GST_FLOW_ERROR;
+    }
+    if (!gst_video_frame_map(&next.out_frame, &vf->out_info, next.out, GST_MAP_WRITE)) {
+        gst_video_frame_unmap(&next.in_frame);
+        gst_buffer_unref(next.in);  gst_buffer_unref(next.out);
+        return GST_FLOW_ERROR;
+    }
+    f.bgrx = GST_VIDEO_FRAME_PLANE_DATA(&next.in_frame, 0);
+    f.in_pitch = (size_t)GST_VIDEO_FRAME_PLANE_STRIDE(&next.in_frame, 0);
+    for (guint i = 0; i < GST_VIDEO_FRAME_N_PLANES(&next.out_frame) && i < 3; i++) {
+        f.planes[i] = GST_VIDEO_FRAME_PLANE_DATA(&next.out_frame, i);
+        f.pitches[i] = (size_t)GST_VIDEO_FRAME_PLANE_STRIDE(&next.out_frame, i);
+    }
+    rc = b200vc_submit(self->ctx, &f, &next.ticket);
+    if (rc != B200VC_OK) {
+        GST_ELEMENT_ERROR(self, LIBRARY, FAILED, ("b200vc_submit: %s", b200vc_status_string(rc)), ("%s", b200vc_last_error(self->ctx)));
+        gst_video_frame_unmap(&next.out_frame);
+        gst_video_frame_unmap(&next.in_frame);
+        gst_buffer_unref(next.in);  gst_buffer_unref(next.out);
+        return GST_FLOW_ERROR;
+    }
+    next.valid = TRUE;
+    *outbuf = gst_b200_convert_finish_pending(self);      /* frame N-1, or NULL on the first call */
+    self->pending = next;
+    return GST_FLOW_OK;
+}
+
+/* The frame in flight must leave before anything that ends or changes the stream. */
+static gboolean gst_b200_convert_sink_event(GstBaseTransform *trans, GstEvent *event)
+{
+    GstB200Convert *self = GST_B200_CONVERT(trans);
+    GstBuffer *out;
+    switch (GST_EVENT_TYPE(event)) {
+    case GST_EVENT_EOS:
+    case GST_EVENT_CAPS:
+    case GST_EVENT_SEGMENT:
+        out = gst_b200_convert_finish_pending(self);
+        if (out)
+            gst_pad_push(trans->srcpad, out);
+        break;
+    case GST_EVENT_FLUSH_STOP:
+        gst_b200_convert_drop_pending(self);
+        break;
+    default:
+        break;
+    }
+    return GST_BASE_TRANSFORM_CLASS(gst_b200_convert_parent_class)->sink_event(trans, event);
+}
+
+/* The mode adds one frame period to the pipeline's latency. */
+static gboolean gst_b200_convert_query(GstBaseTransform *trans, GstPadDirection direction, GstQuery *query)
+{
+    GstB200Convert *self = GST_B200_CONVERT(trans);
+    GstVideoFilter *vf = (GstVideoFilter *)trans;
+    gboolean ok = GST_BASE_TRANSFORM_CLASS(gst_b200_convert_parent_class)->query(trans, direction, query);
+    if (ok && self->one_frame_latency && GST_QUERY_TYPE(query) == GST_QUERY_LATENCY && GST_VIDEO_INFO_FPS_N(&vf->in_info) > 0) {
+        gboolean live;
+        GstClockTime min, max;
+        const GstClockTime frame = gst_util_uint64_scale_int(GST_SECOND, GST_VIDEO_INFO_FPS_D(&vf->in_info),
+                                                             GST_VIDEO_INFO_FPS_N(&vf->in_info));
+        gst_query_parse_latency(query, &live, &min, &max);
+        min += frame;
+        if (max != GST_CLOCK_TIME_NONE)
+            max += frame;
+        gst_query_set_latency(query, live, min, max);
+    }
+    return ok;
 }
 
 /* A video buffer pool over the pinned allocator for `caps` (transfer full), or NULL. */
@@ -290,6 +433,7 @@ static gboolean gst_b200_convert_propose_allocation(GstBaseTransform *trans, Gst
 static void gst_b200_convert_finalize(GObject *obj)
 {
     GstB200Convert *self = GST_B200_CONVERT(obj);
+    gst_b200_convert_drop_pending(self);
     if (self->ctx) { b200vc_destroy(self->ctx); self->ctx = NULL; }
     gst_clear_object(&self->allocator);
     G_OBJECT_CLASS(gst_b200_convert_parent_class)->finalize(obj);
@@ -298,6 +442,7 @@ static void gst_b200_convert_finalize(GObject *obj)
 static gboolean gst_b200_convert_stop(GstBaseTransform *trans)
 {
     GstB200Convert *self = GST_B200_CONVERT(trans);
+    gst_b200_convert_drop_pending(self);
     if (self->ctx) { b200vc_destroy(self->ctx); self->ctx = NULL; }
     return TRUE;
 }
@@ -310,6 +455,7 @@ static void gst_b200_convert_set_property(GObject *obj, guint id, const GValue *
     case PROP_DEVICE_ID: self->device_id = g_value_get_int(v); break;
     case PROP_DAMAGE_MAP: self->damage_map = g_value_get_boolean(v); break;
     case PROP_N_BANDS: self->n_bands = g_value_get_int(v); break;
+    case PROP_ONE_FRAME_LATENCY: self->one_frame_latency = g_value_get_boolean(v); break;   /* read at the next negotiation */
     default: G_OBJECT_WARN_INVALID_PROPERTY_ID(obj, id, ps);
     }
     GST_OBJECT_UNLOCK(self);
@@ -322,6 +468,7 @@ static void gst_b200_convert_get_property(GObject *obj, guint id, GValue *v, GPa
     case PROP_DEVICE_ID: g_value_set_int(v, self->device_id); break;
     case PROP_DAMAGE_MAP: g_value_set_boolean(v, self->damage_map); break;
     case PROP_N_BANDS: g_value_set_int(v, self->n_bands); break;
+    case PROP_ONE_FRAME_LATENCY: g_value_set_boolean(v, self->one_frame_latency); break;
     default: G_OBJECT_WARN_INVALID_PROPERTY_ID(obj, id, ps);
     }
 }
@@ -338,6 +485,8 @@ static void gst_b200_convert_class_init(GstB200ConvertClass *klass)
     g_object_class_install_property(go, PROP_DEVICE_ID, g_param_spec_int("device-id", "Device", "CUDA device ordinal", 0, 63, 0, G_PARAM_READWRITE));
     g_object_class_install_property(go, PROP_DAMAGE_MAP, g_param_spec_boolean("damage-map", "Damage map", "Emit the 16x16 damage map", FALSE, G_PARAM_READWRITE));
     g_object_class_install_property(go, PROP_N_BANDS, g_param_spec_int("n-bands", "Bands", "Row bands a frame is pipelined in", 0, 64, 0, G_PARAM_READWRITE));
+    g_object_class_install_property(go, PROP_ONE_FRAME_LATENCY, g_param_spec_boolean("one-frame-latency", "One frame of latency",
+        "Return frame N-1 while frame N is in flight (copies of consecutive frames overlap)", FALSE, G_PARAM_READWRITE));
     gst_element_class_add_static_pad_template(el, &sink_tmpl);
     gst_element_class_add_static_pad_template(el, &src_tmpl);
     gst_element_class_set_static_metadata(el, "B200 BGRx converter/scaler", "Filter/Converter/Video/Scaler",
@@ -345,6 +494,9 @@ static void gst_b200_convert_class_init(GstB200ConvertClass *klass)
     bt->transform_caps = GST_DEBUG_FUNCPTR(gst_b200_convert_transform_caps);
     bt->fixate_caps = GST_DEBUG_FUNCPTR(gst_b200_convert_fixate_caps);
     bt->stop = GST_DEBUG_FUNCPTR(gst_b200_convert_stop);
+    bt->generate_output = GST_DEBUG_FUNCPTR(gst_b200_convert_generate_output);
+    bt->sink_event = GST_DEBUG_FUNCPTR(gst_b200_convert_sink_event);
+    bt->query = GST_DEBUG_FUNCPTR(gst_b200_convert_query);
     bt->decide_allocation = GST_DEBUG_FUNCPTR(gst_b200_convert_decide_allocation);
     bt->propose_allocation = GST_DEBUG_FUNCPTR(gst_b200_convert_propose_allocation);
     bt->passthrough_on_same_caps = FALSE;
@@ -360,6 +512,9 @@ static void gst_b200_convert_init(GstB200Convert *self)
     self->device_id = 0;
     self->damage_map = FALSE;
     self->n_bands = 0;
+    self->one_frame_latency = FALSE;
+    self->pending.valid = FALSE;
+    self->pending.in = self->pending.out = NULL;
 }
 
 static gboolean plugin_init(GstPlugin *plugin)

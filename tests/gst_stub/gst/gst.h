@@ -46,13 +46,26 @@ gpointer g_slice_alloc0(gsize n);  void g_slice_free1(gsize n, gpointer p);
 typedef struct _GstObject { GObject object; guint flags; } GstObject;
 typedef struct _GstCaps GstCaps;  typedef struct _GstStructure GstStructure;  typedef struct _GstPad GstPad;
 typedef struct _GstQuery GstQuery;  typedef struct _GstBuffer GstBuffer;  typedef struct _GstPlugin GstPlugin;
-typedef struct _GstBufferPool GstBufferPool;
+typedef struct _GstBufferPool GstBufferPool;  typedef struct _GstEvent { int type; } GstEvent;
+typedef uint64_t guint64;  typedef guint64 GstClockTime;
+#define GST_SECOND ((GstClockTime)1000000000)
+#define GST_CLOCK_TIME_NONE ((GstClockTime)-1)
+typedef enum { GST_EVENT_UNKNOWN, GST_EVENT_FLUSH_STOP, GST_EVENT_CAPS, GST_EVENT_SEGMENT, GST_EVENT_EOS } GstEventType;
+#define GST_EVENT_TYPE(e) ((GstEventType)(e)->type)
+typedef enum { GST_QUERY_UNKNOWN, GST_QUERY_LATENCY } GstQueryType;
+GstQueryType gst_stub_query_type(GstQuery *q);
+#define GST_QUERY_TYPE(q) gst_stub_query_type(q)
+void gst_query_parse_latency(GstQuery *q, gboolean *live, GstClockTime *min, GstClockTime *max);
+void gst_query_set_latency(GstQuery *q, gboolean live, GstClockTime min, GstClockTime max);
+guint64 gst_util_uint64_scale_int(guint64 val, gint num, gint denom);
+void gst_buffer_unref(GstBuffer *b);
 typedef struct _GstElement { GstObject object; } GstElement;
 typedef struct _GstElementClass { GObjectClass parent_class; } GstElementClass;
 typedef enum { GST_PAD_UNKNOWN, GST_PAD_SRC, GST_PAD_SINK } GstPadDirection;
 typedef enum { GST_PAD_ALWAYS } GstPadPresence;
 typedef enum { GST_FLOW_OK = 0, GST_FLOW_NOT_NEGOTIATED = -4, GST_FLOW_ERROR = -5 } GstFlowReturn;
 typedef enum { GST_CAPS_INTERSECT_ZIG_ZAG, GST_CAPS_INTERSECT_FIRST } GstCapsIntersectMode;
+GstFlowReturn gst_pad_push(GstPad *pad, GstBuffer *buffer);
 typedef enum { GST_MAP_READ = 1, GST_MAP_WRITE = 2 } GstMapFlags;
 typedef struct { const gchar *string; } GstStaticCaps;
 typedef struct { const gchar *name_template; GstPadDirection direction; GstPadPresence presence; GstStaticCaps static_caps; } GstStaticPadTemplate;
@@ -128,7 +141,7 @@ void gst_query_add_allocation_meta(GstQuery *query, GType api, const GstStructur
 gboolean gst_query_find_allocation_meta(GstQuery *query, GType api, guint *index);
 
 /* ---- base transform ------------------------------------------------------------------------------------ */
-typedef struct _GstBaseTransform { GstElement element; GstPad *sinkpad, *srcpad; } GstBaseTransform;
+typedef struct _GstBaseTransform { GstElement element; GstPad *sinkpad, *srcpad; GstBuffer *queued_buf; } GstBaseTransform;
 typedef struct _GstBaseTransformClass {
     GstElementClass parent_class;
     gboolean passthrough_on_same_caps;
@@ -136,6 +149,10 @@ typedef struct _GstBaseTransformClass {
     GstCaps *(*fixate_caps)(GstBaseTransform *, GstPadDirection, GstCaps *, GstCaps *);
     gboolean (*decide_allocation)(GstBaseTransform *, GstQuery *);
     gboolean (*propose_allocation)(GstBaseTransform *, GstQuery *, GstQuery *);
+    GstFlowReturn (*prepare_output_buffer)(GstBaseTransform *, GstBuffer *, GstBuffer **);
+    GstFlowReturn (*generate_output)(GstBaseTransform *, GstBuffer **);
+    gboolean (*sink_event)(GstBaseTransform *, GstEvent *);
+    gboolean (*query)(GstBaseTransform *, GstPadDirection, GstQuery *);
     gboolean (*start)(GstBaseTransform *);
     gboolean (*stop)(GstBaseTransform *);
 } GstBaseTransformClass;
@@ -153,12 +170,15 @@ typedef struct { GstVideoColorRange range; GstVideoColorMatrix matrix; int trans
 typedef struct _GstVideoInfo {
     GstVideoFormat format; gint width, height; gsize size; GstVideoChromaSite chroma_site; GstVideoColorimetry colorimetry;
     gint stride[4];
+    gint fps_n, fps_d;
 } GstVideoInfo;
 typedef struct _GstVideoFrame { GstVideoInfo info; GstBuffer *buffer; gpointer data[4]; gint n_planes; } GstVideoFrame;
 #define GST_VIDEO_INFO_FORMAT(i) ((i)->format)
 #define GST_VIDEO_INFO_WIDTH(i) ((i)->width)
 #define GST_VIDEO_INFO_HEIGHT(i) ((i)->height)
 #define GST_VIDEO_INFO_SIZE(i) ((i)->size)
+#define GST_VIDEO_INFO_FPS_N(i) ((i)->fps_n)
+#define GST_VIDEO_INFO_FPS_D(i) ((i)->fps_d)
 #define GST_VIDEO_FRAME_WIDTH(f) ((f)->info.width)
 #define GST_VIDEO_FRAME_HEIGHT(f) ((f)->info.height)
 #define GST_VIDEO_FRAME_N_PLANES(f) ((f)->n_planes)
@@ -167,9 +187,11 @@ typedef struct _GstVideoFrame { GstVideoInfo info; GstBuffer *buffer; gpointer d
 #define GST_VIDEO_META_API_TYPE ((GType)4)
 #define GST_BUFFER_POOL_OPTION_VIDEO_META "GstBufferPoolOptionVideoMeta"
 gboolean gst_video_info_from_caps(GstVideoInfo *info, const GstCaps *caps);
+gboolean gst_video_frame_map(GstVideoFrame *frame, const GstVideoInfo *info, GstBuffer *buffer, GstMapFlags flags);
+void gst_video_frame_unmap(GstVideoFrame *frame);
 GstBufferPool *gst_video_buffer_pool_new(void);
 gpointer gst_buffer_add_video_region_of_interest_meta(GstBuffer *buffer, const gchar *roi_type, guint x, guint y, guint w, guint h);
-typedef struct _GstVideoFilter { GstBaseTransform element; } GstVideoFilter;
+typedef struct _GstVideoFilter { GstBaseTransform element; gboolean negotiated; GstVideoInfo in_info, out_info; } GstVideoFilter;
 typedef struct _GstVideoFilterClass {
     GstBaseTransformClass parent_class;
     gboolean (*set_info)(GstVideoFilter *, GstCaps *, GstVideoInfo *, GstCaps *, GstVideoInfo *);

@@ -384,3 +384,33 @@ def test_zero_copy_out_mode(conv, orc):
     conv.stop()
     pin_in.free()
     pin_out.free()
+
+
+@pytest.mark.parametrize("scaled", [False, True])
+def test_one_frame_latency_call_order(conv, orc, scaled):
+    """The element's one-frame-latency mode: one session, frame N submitted before frame N-1 is
+    collected, each frame with its own input and output buffers (gst/gstb200convert.c generate_output)."""
+    w, h = 640, 360
+    ow, oh = (480, 270) if scaled else (w, h)
+    conv.set_info(w, h, ow, oh, matrix=1, range_=0, chroma_site=1, n_inflight=2)
+    total, off, pit = b200vc.default_layout(0, ow, oh)
+    n = 6
+    ins, outs = b200vc.PinnedBuffer(n * w * h * 4), b200vc.PinnedBuffer(n * total)
+    host, tickets = [], []
+    for k in range(n):
+        view = ins.array[k * w * h * 4:(k + 1) * w * h * 4].reshape(h, w * 4)
+        host.append(np.array(orc.synth("desk", w, h, k, out=view)))
+        f = conv.make_frame(view.ctypes.data, w * 4, outs.array.ctypes.data + k * total, off, pit, session=0)
+        tickets.append(conv.submit(f))
+        if k:
+            conv.collect(tickets[k - 1])
+            got = plane_views(outs.array[(k - 1) * total:k * total], off, pit, 0, ow, oh)
+            want, woff, wpit = orc.convert(host[k - 1], 0, 1, 0, 1, out_size=(ow, oh))
+            assert_planes_equal(got, plane_views(want, woff, wpit, 0, ow, oh), f"frame {k - 1}")
+    conv.collect(tickets[-1])
+    got = plane_views(outs.array[(n - 1) * total:n * total], off, pit, 0, ow, oh)
+    want, woff, wpit = orc.convert(host[-1], 0, 1, 0, 1, out_size=(ow, oh))
+    assert_planes_equal(got, plane_views(want, woff, wpit, 0, ow, oh), "last frame")
+    conv.stop()
+    ins.free()
+    outs.free()

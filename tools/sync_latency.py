@@ -36,3 +36,20 @@ for flags in (0, b200vc.FLAG_ZERO_COPY, b200vc.FLAG_ZERO_COPY_OUT):
     conv.stop()
     outs.free()
 conv.stop()
+
+# one session, one frame of latency (the element's one-frame-latency mode): submit N, collect N-1
+conv = b200vc.Converter(0)
+conv.set_info(W, H, matrix=0, range_=0, chroma_site=1, n_inflight=2)
+outs = b200vc.PinnedBuffer(2 * total)
+fr = [conv.make_frame(h_in.ptr + k * W * H * 4, W * 4, outs.ptr + (k % 2) * total, off, pit, session=0) for k in range(8)]
+prev = conv.submit(fr[0])
+n = 400
+t0 = time.perf_counter()
+for i in range(1, n + 1):
+    t = conv.submit(fr[i % 8])
+    conv.collect(prev)
+    prev = t
+conv.collect(prev)
+dt = time.perf_counter() - t0
+print(f"one session, submit N / collect N-1: {n / dt:8.1f} frames/s  {dt / n * 1e6:7.1f} us/frame", flush=True)
+conv.stop()

@@ -324,6 +324,16 @@ def run_gpu(args, rank: int, local_rank: int, world: int):
     for i in range(n_sync):
         conv.lib.b200vc_convert(conv.ctx, h_in.ptr + (i % RING) * IN_BYTES, W * 4, planes, pits, None)
     sync_fps = n_sync / (time.perf_counter() - t0)
+    # the same session with one frame of latency (submit N, collect N-1: the element's one-frame-latency mode)
+    lat_frames = [conv.make_frame(h_in.ptr + i * IN_BYTES, W * 4, h_out.ptr + i * OUT_BYTES, off, pit, session=0) for i in range(RING)]
+    prev_ticket = conv.submit(lat_frames[0])
+    t0 = time.perf_counter()
+    for i in range(1, n_sync + 1):
+        ticket = conv.submit(lat_frames[i % RING])
+        conv.collect(prev_ticket)
+        prev_ticket = ticket
+    conv.collect(prev_ticket)
+    latency_mode_fps = n_sync / (time.perf_counter() - t0)
 
     # PCIe ceiling for the e2e number: raw pinned copies of the same frames, both directions at once,
     # no kernel (what the link gives for this traffic pattern on this box)
@@ -372,7 +382,8 @@ def run_gpu(args, rank: int, local_rank: int, world: int):
                     "frac_of_pcie_ceiling": round(e2e_fps / world / pcie_fps, 4),
                     "frac_of_pcie_gen5_x16_raw_63GBs": round(e2e_fps / world * IN_BYTES / 63.02e9, 4),
                     "pcie_ceiling_how": "raw pinned H2D 8.3 MB + D2H 3.1 MB copies in flight together, no kernel, rank 0",
-                    "sync_single_session_fps": round(sync_fps, 1), "numa": numa},
+                    "sync_single_session_fps": round(sync_fps, 1),
+                    "one_frame_latency_single_session_fps": round(latency_mode_fps, 1), "numa": numa},
             "gpu_launches": gpu_launches,
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                          "frac": round(achieved / peak, 4), "traffic": committed_traffic(),

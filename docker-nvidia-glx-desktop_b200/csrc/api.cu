@@ -491,7 +491,7 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         p.out.p[0] += (size_t)row0 * out.pitch[0];
         p.out.p[1] += (size_t)(row0 / 2) * out.pitch[1];
         if (p.out.p[2]) p.out.p[2] += (size_t)(row0 / 2) * out.pitch[2];
-        p.w = g.in_w;  p.h = rows;  p.n_frames = n_frames;  p.mx = c->mx;
+        p.w = g.in_w;  p.h = rows;  p.n_frames = n_frames;  p.mx = c->mx;  p.stream_out = 1;
         CU_TRY(c, launch_convert(p, g.out_format, site, st));
         c->stats.kernel_launches += 1;
         return B200VC_OK;

@@ -39,6 +39,7 @@ struct ConvertParams {
     uint8_t *damage; long long damage_frame_stride; int mb_w;                  // K3 only
     int w, h;               // pixels covered by this launch (h = rows of the band, even)
     int n_frames;
+    int stream_out;         // 1: the planes are final output (streaming stores); 0: read again on the GPU (two-pass intermediate)
     Matrix mx;
 };
 

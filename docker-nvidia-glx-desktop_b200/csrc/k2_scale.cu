@@ -1,5 +1,4 @@
-// k2_scale.cu — K2: BGRx -> I420/NV12 with the bilinear downscale fused into the same pass, and
-// the general two-pass plane scaler (sm_100a).
+// k2_scale.cu — K2: BGRx -> I420/NV12 with the bilinear scale fused into the same pass (sm_100a).
 //
 // Replaces `videoconvert ! videoscale` (GstVideoScale -> GstVideoScaler 2-tap "lq" path) on the
 // reference's software-encoder fallback (/root/reference Dockerfile:467-471, README.md:21).
@@ -10,11 +9,17 @@
 //
 //   phase 0  one thread issues a TMA tiled load (cp.async.bulk.tensor.3d) of the tile's source
 //            window — the rows and columns its output pixels depend on, halo included; pixels
-//            outside the frame are zero-filled by the TMA unit and never consumed — and the CTA
-//            waits on an mbarrier for the bytes to land in shared memory
+//            outside the frame are zero-filled by the TMA unit — while every thread copies one word
+//            of the tile's host-made tap records into shared memory; the CTA then waits on an
+//            mbarrier for the window's bytes
 //   phase 1  convert the window: Y per pixel and the 4:2:0 (u,v) pair per 2x2 block, kept in
 //            shared memory (this is the "intermediate frame", tile-sized)
-//   phase 2  scale out of shared memory with host-built tap tables, store the output tile
+//   phase 2  scale out of shared memory (a lane owns an output column, all taps are dp4a weight
+//            words) into an output tile in shared memory
+//   phase 3  the tile leaves as 16-byte stores
+// (k2_fused_scale_kernel, any ratio whose window fits a TMA box). When the ratio is exactly 2:1,
+// k2_fused_2x_kernel does all of it in registers straight from the TMA tile. The file also holds the
+// gather form of the two-pass path's plane scaler (its tiled form is k2_plane_tile.cu).
 //
 // HBM roofline: algorithmic bytes per output frame = in_w*in_h*4 + out_w*out_h*1.5.
 #include "device_utils.cuh"

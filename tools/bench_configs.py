@@ -34,6 +34,8 @@ CONFIGS = [
     ("T 1440p->1080p 4:3 two-pass", 2560, 1440, 1920, 1080, 0, 1, 0, 1, b200vc.FLAG_FORCE_TWO_PASS, False),
     ("T 1080p->720p 3:2 two-pass", 1920, 1080, 1280, 720, 0, 1, 0, 1, b200vc.FLAG_FORCE_TWO_PASS, False),
     ("T 4K->720p 3:1 two-pass", 3840, 2160, 1280, 720, 0, 1, 0, 1, b200vc.FLAG_FORCE_TWO_PASS, False),
+    ("T 1080p->1536x864 1.25:1 two-pass", 1920, 1080, 1536, 864, 0, 1, 0, 1, b200vc.FLAG_FORCE_TWO_PASS, False),
+    ("T 720p->1080p 2:3 upscale two-pass", 1280, 720, 1920, 1080, 0, 1, 0, 1, b200vc.FLAG_FORCE_TWO_PASS, False),
 ]
 
 

@@ -31,7 +31,7 @@ FLAG_DAMAGE_MAP, FLAG_FORCE_TWO_PASS, FLAG_REGISTER_HOST, FLAG_FORCE_GENERIC_FUS
 # every symbol include/b200vc.h declares
 SYMBOLS = [
     "b200vc_default_colorimetry", "b200vc_default_layout", "b200vc_check_config", "b200vc_status_string",
-    "b200vc_version", "b200vc_create", "b200vc_destroy", "b200vc_last_error", "b200vc_get_info",
+    "b200vc_version", "b200vc_spec_string", "b200vc_create", "b200vc_destroy", "b200vc_last_error", "b200vc_get_info",
     "b200vc_get_stats", "b200vc_reset", "b200vc_convert", "b200vc_convert_batch", "b200vc_submit",
     "b200vc_collect", "b200vc_host_alloc", "b200vc_host_free", "b200vc_convert_device",
     "b200vc_convert_scale_device_static", "b200vc_damage_to_rects",
@@ -98,6 +98,7 @@ def load() -> C.CDLL:
     L.b200vc_check_config.argtypes = [C.POINTER(Config)]
     L.b200vc_status_string.argtypes = [i]
     L.b200vc_status_string.restype = C.c_char_p
+    L.b200vc_spec_string.restype = C.c_char_p
     L.b200vc_create.argtypes = [C.POINTER(Config), C.POINTER(vp)]
     L.b200vc_destroy.argtypes = [vp]
     L.b200vc_last_error.argtypes = [vp]

@@ -8,6 +8,7 @@
 // exists anywhere in this file: without a usable sm_100 device every call fails.
 #include "../../include/b200vc.h"
 #include "kernels.cuh"
+#include "host_tables.h"
 
 #include <cudaTypedefs.h>
 
@@ -123,80 +124,29 @@ bool aligned16(const void *p) { return ((uintptr_t)p & 15) == 0; }
 // negotiation must not shrink an earlier one's.
 size_t dyn_smem_cap(const b200vc_ctx *c) { return (size_t)c->prop.sharedMemPerBlockOptin - 8192; }
 
-// SURVEY A.2 table; rows Y,U,V of (cR, cG, cB, off). The oracle derives the same numbers from
-// Kr/Kb in double precision; tests compare the two.
-const int kMatrix[3][2][3][4] = {
-    { { { 66, 129, 25, 4096 }, { -38, -74, 112, 32768 }, { 112, -94, -18, 32768 } },      // 601 limited
-      { { 77, 150, 29, 0 }, { -43, -85, 128, 32768 }, { 128, -107, -21, 32768 } } },      // 601 full
-    { { { 47, 157, 16, 4096 }, { -26, -87, 112, 32768 }, { 112, -102, -10, 32768 } },     // 709 limited
-      { { 54, 183, 18, 0 }, { -29, -99, 128, 32768 }, { 128, -116, -12, 32768 } } },      // 709 full
-    { { { 58, 149, 13, 4096 }, { -31, -81, 112, 32768 }, { 112, -103, -9, 32768 } },      // 2020 limited
-      { { 67, 174, 15, 0 }, { -36, -92, 128, 32768 }, { 128, -118, -10, 32768 } } },      // 2020 full
-};
-
-// byte position of B, G, R in one pixel, per B200VC_IN_* (unpack_BGRA / _RGBA / _ARGB / _ABGR)
-const int kBytePos[4][3] = { { 0, 1, 2 }, { 2, 1, 0 }, { 3, 2, 1 }, { 1, 2, 3 } };
-
-uint32_t pack_coef_at(const int pos[3], int cb, int cg, int cr)
-{
-    return ((uint32_t)(cb & 0xff) << (8 * pos[0])) | ((uint32_t)(cg & 0xff) << (8 * pos[1])) |
-           ((uint32_t)(cr & 0xff) << (8 * pos[2]));
-}
-
-Matrix make_matrix(int matrix, int range, int in_format)
-{
-    const int (*m)[4] = kMatrix[matrix][range];
-    const int *pos = kBytePos[in_format];
-    auto pack_coef = [pos](int cb, int cg, int cr) { return pack_coef_at(pos, cb, cg, cr); };
-    Matrix r;
-    r.rgb_mask = pack_coef_at(pos, 0xff, 0xff, 0xff);
-    r.cy = pack_coef(m[0][2], m[0][1], m[0][0]);
-    r.oy = (uint32_t)m[0][3];
-    bool neg = false;
-    for (int row = 1; row < 3; row++)
-        for (int c = 0; c < 3; c++)
-            if (m[row][c] > 127) neg = true;
-    r.neg = neg ? 1 : 0;
-    if (!neg) {
-        r.cu = pack_coef(m[1][2], m[1][1], m[1][0]);  r.ou = (uint32_t)m[1][3];
-        r.cv = pack_coef(m[2][2], m[2][1], m[2][0]);  r.ov = (uint32_t)m[2][3];
-    } else {
-        r.cu = pack_coef(-m[1][2], -m[1][1], -m[1][0]);  r.ou = (uint32_t)(65535 - m[1][3]);
-        r.cv = pack_coef(-m[2][2], -m[2][1], -m[2][0]);  r.ov = (uint32_t)(65535 - m[2][3]);
-    }
-    return r;
-}
-
-// ---- scaler taps, integer arithmetic only -------------------------------------------
+// ---- scaler taps as tables; positions and spec constants from host_tables.h ------------
 void build_h_taps(int in_n, int out_n, std::vector<Tap> &t)
 {
-    long long inc = 0;
-    if (out_n > 1) {
-        inc = (((long long)(in_n - 1)) << 16) / (out_n - 1) - 1;
-        if (inc < 0) inc = 0;
-    }
+    const long long inc = scale_h_inc(in_n, out_n);
     t.resize(ru(out_n, 4));
     for (int x = 0; x < out_n; x++) {
-        long long p = (long long)x * inc;
-        int i = (int)(p >> 16), f = (int)((p >> 8) & 0xff);
-        int i0 = std::min(std::max(i, 0), in_n - 1), i1 = std::min(std::max(i + 1, 0), in_n - 1);
-        t[x] = (Tap)i0 | ((Tap)f << 16) | ((Tap)(i1 - i0) << 24);
+        int i, f;
+        scale_h_tap(inc, x, i, f);
+        const int i0 = clamp_index(i, in_n), i1 = clamp_index((long long)i + 1, in_n);
+        t[x] = make_tap(i0, f, i1 - i0);
     }
     for (size_t x = out_n; x < t.size(); x++) t[x] = t[out_n - 1];
 }
 
 void build_v_taps(int in_n, int out_n, std::vector<Tap> &t)
 {
-    const long long den = 2LL * out_n;
     t.resize(ru(out_n, 4));
     for (int y = 0; y < out_n; y++) {
-        long long num = (2LL * y + 1) * in_n - out_n;
-        long long i = num / den, rem = num - i * den;
-        if (rem < 0) { i -= 1; rem += den; }
-        int p1 = (int)((128 * rem + den) / (2 * den));
-        int i0 = (int)std::min<long long>(std::max<long long>(i, 0), in_n - 1);
-        int i1 = (int)std::min<long long>(std::max<long long>(i + 1, 0), in_n - 1);
-        t[y] = (Tap)i0 | ((Tap)p1 << 16) | ((Tap)(i1 - i0) << 24);
+        long long i;
+        int p1;
+        scale_v_tap(y, in_n, out_n, i, p1);
+        const int i0 = clamp_index(i, in_n), i1 = clamp_index(i + 1, in_n);
+        t[y] = make_tap(i0, p1, i1 - i0);
     }
     for (size_t y = out_n; y < t.size(); y++) t[y] = t[out_n - 1];
 }
@@ -205,13 +155,13 @@ void build_v_taps(int in_n, int out_n, std::vector<Tap> &t)
 void build_box_taps(int out_n, std::vector<Tap> &t)
 {
     t.resize(ru(out_n, 4));
-    for (int k = 0; k < out_n; k++) t[k] = (Tap)(2 * k) | ((Tap)1 << 24);
+    for (int k = 0; k < out_n; k++) t[k] = make_tap(2 * k, 0, 1);
     for (size_t k = out_n; k < t.size(); k++) t[k] = t[out_n - 1];
 }
 
-inline int tidx(Tap t) { return (int)(t & 0xffff); }
-inline int tstep(Tap t) { return (int)((t >> 24) & 1); }
-inline int tfrac(Tap t) { return (int)((t >> 16) & 0xff); }
+inline int tidx(Tap t) { return tap_idx(t); }
+inline int tstep(Tap t) { return tap_step(t); }
+inline int tfrac(Tap t) { return tap_frac(t); }
 
 // The general fused kernel's form of the tables (FusedTaps, kernels.cuh) as one blob of 32-bit words:
 // [tile_x pairs | tile_y | col_rec | row_rec], every section padded to a multiple of 4 words.
@@ -219,10 +169,7 @@ struct FusedTapBlob { std::vector<uint32_t> w; size_t tile_x, tile_y, col_rec, r
 
 uint32_t v_weights(Tap t)
 {
-    const int p1 = tstep(t) ? tfrac(t) : 0;          // clamped second line: all weight on the first
-    const int a = 256 - 4 * p1, b = 4 * p1;
-    const int a1 = std::min(a, 255), b1 = std::min(b, 255);
-    return (uint32_t)a1 | ((uint32_t)(a - a1) << 8) | ((uint32_t)b1 << 16) | ((uint32_t)(b - b1) << 24);
+    return v_weight_word(tstep(t) ? tfrac(t) : 0);   // clamped second line: all weight on the first
 }
 
 // Window origin of a tile column / tile row: the first source column (line) any of its taps reads,
@@ -361,22 +308,17 @@ void fused_box(const b200vc_config &c, const std::vector<Tap> &hy, const std::ve
 }
 
 // True when every tap of an (in_n -> out_n) scaler starts at 2k with the second tap at 2k+1 and,
-// for vertical taps, weighs both lines equally (p1 == 32): the pattern k2_fused_2x_kernel assumes.
+// for vertical taps, weighs both lines equally (p1 == half): the pattern k2_fused_2x_kernel assumes.
 bool taps_are_2to1(const std::vector<Tap> &t, int out_n, bool vertical)
 {
     for (int k = 0; k < out_n; k++) {
         if (tidx(t[k]) != 2 * k || tstep(t[k]) != 1) return false;
-        if (vertical && ((t[k] >> 16) & 0xff) != 32) return false;
+        if (vertical && tfrac(t[k]) != B200VC_SPEC_VTAP_HALF) return false;
     }
     return true;
 }
 
-uint32_t h_inc(int in_n, int out_n)
-{
-    if (out_n <= 1) return 0;
-    long long inc = (((long long)(in_n - 1)) << 16) / (out_n - 1) - 1;
-    return (uint32_t)(inc < 0 ? 0 : inc);
-}
+uint32_t h_inc(int in_n, int out_n) { return (uint32_t)scale_h_inc(in_n, out_n); }
 
 int check_config(const b200vc_config *c, std::string *why)
 {
@@ -680,7 +622,8 @@ int create_impl(b200vc_ctx *c)
         const bool fits = c->box_w <= 256 && c->box_h <= 256 &&
                           c->smem_bytes <= dyn_smem_cap(c);
         // (odd sizes run the general fused kernel; the exact-2:1 kernel needs multiples of 4, BOX even sizes)
-        c->path = (fits && !(g.flags & B200VC_FLAG_FORCE_TWO_PASS)) ? 1 : 2;
+        // (the fused kernels scale horizontally first; a build with the other order of the spec takes the two-pass path)
+        c->path = (fits && !(g.flags & B200VC_FLAG_FORCE_TWO_PASS) && B200VC_SPEC_SCALE_H_FIRST) ? 1 : 2;
         const bool exact2 = g.in_w == 2 * g.out_w && g.in_h == 2 * g.out_h && (g.in_w % 4) == 0 && (g.in_h % 4) == 0;
         c->fused2x = c->path == 1 && exact2 && !(g.flags & B200VC_FLAG_FORCE_GENERIC_FUSED) &&
                      (g.scale_mode == B200VC_SCALE_BOX_2X2 ||
@@ -975,6 +918,8 @@ extern "C" {
 
 int b200vc_version(void) { return B200VC_VERSION_MAJOR * 100 + B200VC_VERSION_MINOR; }
 
+const char *b200vc_spec_string(void) { return B200VC_SPEC_STRING; }
+
 const char *b200vc_status_string(int s)
 {
     switch (s) {
@@ -1236,6 +1181,11 @@ int b200vc_convert_device(b200vc_ctx *c, const b200vc_device_frames *d, void *cu
         (np == 3 && d->pitches[2] < cw))
         return fail(c, B200VC_ERR_INVALID_ARG, "a pitch is smaller than its row");
     if (d->n_frames > 1 && (d->in_frame_stride == 0 || d->out_frame_stride == 0))
+        return fail(c, B200VC_ERR_INVALID_ARG, "frame strides are required for n_frames > 1");
+    if (d->damage && d->n_frames > 1 && d->damage_frame_stride < (size_t)c->mb_w * c->mb_h)
+        return fail(c, B200VC_ERR_INVALID_ARG, "damage_frame_stride %zu is smaller than a map (%d bytes): the frames' maps would overlap",
+                    d->damage_frame_stride, c->mb_w * c->mb_h);
+    if (d->damage && d->prev && d->n_frames > 1 && d->prev_frame_stride == 0)
         return fail(c, B200VC_ERR_INVALID_ARG, "frame strides are required for n_frames > 1");
 
     CU_TRY(c, cudaSetDevice(g.device));

@@ -7,6 +7,7 @@
 
 #include <stdint.h>
 #include "kernels.cuh"
+#include "../../include/b200vc_spec.h"
 
 namespace b200vc {
 
@@ -81,6 +82,11 @@ __device__ __forceinline__ uint32_t chroma_pair(uint32_t pix, const Matrix &m)
 {
     uint32_t su = dp4a_us(pix, m.cu, m.ou);
     uint32_t sv = dp4a_us(pix, m.cv, m.ov);
+    if (B200VC_SPEC_MATRIX_ROUND && NEG) {
+        // with the rounding term a saturated primary reaches 65536 (negated: -1): clamp, i.e. 255
+        su = (uint32_t)max((int32_t)su, 0);
+        sv = (uint32_t)max((int32_t)sv, 0);
+    }
     uint32_t p = prmt(su, sv, 0x6521);      // bytes: su.1, su.2 (=0), sv.1, sv.2 (=0)
     return NEG ? (p ^ 0x00FF00FFu) : p;
 }

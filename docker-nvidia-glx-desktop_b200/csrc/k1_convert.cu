@@ -20,6 +20,7 @@
 //
 // HBM roofline: algorithmic bytes per pixel = 4 (read) + 1.5 (write) [+ 4 previous frame].
 #include "device_utils.cuh"
+#include "../../include/b200vc_spec.h"
 
 namespace b200vc {
 
@@ -79,8 +80,10 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
     // Right frame edge, cosited: the last chroma site (column w-2 of an even width, w-1 of an odd
     // one; w > 2) takes itself as right neighbour (FILT_1_3). (Jpeg siting needs no flag: the edge
     // loader duplicates an unpaired last pixel, and avg2(p, p) = p.)
-    const bool edge1 = SITE == 1 && p.w > 2 && remain <= 2;   // site at pixel 0
-    const bool edge3 = SITE == 1 && p.w > 2 && remain <= 4;   // site at pixel 2
+    // (B200VC_SPEC_COSITED_LAST_1_3 = 0: only an odd width's unpaired last pixel does; an even
+    // width's last site gets the plain 1-2-1 filter.)
+    const bool edge1 = SITE == 1 && p.w > 2 && remain <= (B200VC_SPEC_COSITED_LAST_1_3 ? 2 : 1);   // site at pixel 0
+    const bool edge3 = SITE == 1 && p.w > 2 && remain <= (B200VC_SPEC_COSITED_LAST_1_3 ? 4 : 3);   // site at pixel 2
 
     const uint8_t *src = p.src + (long long)frame * p.src_frame_stride + (long long)y0 * p.src_pitch + (long long)x * 4;
     const uint8_t *prv = DMG ? p.prev + (long long)frame * p.prev_frame_stride + (long long)y0 * p.prev_pitch + (long long)x * 4

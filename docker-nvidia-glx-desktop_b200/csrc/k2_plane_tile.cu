@@ -12,6 +12,7 @@
 // the structure measured on the general fused kernel (profiles/README.md).
 #include "device_utils.cuh"
 #include "kernels.cuh"
+#include "../../include/b200vc_spec.h"
 
 namespace b200vc {
 namespace {
@@ -57,6 +58,11 @@ __device__ __forceinline__ uint32_t tile_sample(const uint8_t *r0, int bwp, uint
     const uint8_t *r1 = r0 + bwp;
     if (box)
         return (uint32_t)(r0[0] + r0[1] + r1[0] + r1[1] + 2) << 6;
+    if (!B200VC_SPEC_SCALE_H_FIRST) {                    // vertical pass first (spec variant)
+        const uint32_t v0 = dp4a_uu(prmt(r0[0], r1[0], 0x4400), wv, 128u) >> 8;
+        const uint32_t v1 = dp4a_uu(prmt(r0[1], r1[1], 0x4400), wv, 128u) >> 8;
+        return dp4a_uu(prmt(v0, v1, 0x1400), wh, 0u);
+    }
     const uint32_t s0 = dp4a_uu(prmt(r0[0], r0[1], 0x1400), wh, 0u);
     const uint32_t s1 = dp4a_uu(prmt(r1[0], r1[1], 0x1400), wh, 0u);
     return dp4a_uu(prmt(s0, s1, 0x5511), wv, 128u);

@@ -23,16 +23,13 @@
 //
 // HBM roofline: algorithmic bytes per output frame = in_w*in_h*4 + out_w*out_h*1.5.
 #include "device_utils.cuh"
+#include "../../include/b200vc_spec.h"
 
 namespace b200vc {
 
 namespace {
 
 constexpr int TW = K2_TILE_W;
-
-__device__ __forceinline__ int tap_idx(Tap t) { return (int)(t & 0xffffu); }
-__device__ __forceinline__ int tap_frac(Tap t) { return (int)((t >> 16) & 0xffu); }
-__device__ __forceinline__ int tap_step(Tap t) { return (int)((t >> 24) & 1u); }
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p)
 {
@@ -116,8 +113,10 @@ __device__ __forceinline__ void convert_item(const uint32_t *s_src, uint8_t *s_y
                 }
             }
             // right neighbours: the frame's last even column (in_w - 2, in_w > 2) takes itself
-            const bool e0 = EDGE && in_w > 2 && ac + 4 * h == in_w - 2;
-            const bool e2 = EDGE && in_w > 2 && ac + 4 * h + 2 == in_w - 2;
+            // (B200VC_SPEC_COSITED_LAST_1_3 = 0: the plain 1-2-1 filter runs to the end; an odd frame's
+            // last pixel has been duplicated into the window by then, which is the same thing)
+            const bool e0 = EDGE && B200VC_SPEC_COSITED_LAST_1_3 && in_w > 2 && ac + 4 * h == in_w - 2;
+            const bool e2 = EDGE && B200VC_SPEC_COSITED_LAST_1_3 && in_w > 2 && ac + 4 * h + 2 == in_w - 2;
             c0 = avg2(filt121(la, pa0, e0 ? pa0 : pa1), filt121(lb, pb0, e0 ? pb0 : pb1));
             c1 = avg2(filt121(pa1, pa2, e2 ? pa2 : pa3), filt121(pb1, pb2, e2 ? pb2 : pb3));
             la = pa3;  lb = pb3;
@@ -379,7 +378,7 @@ k2_fused_2x_kernel(const __grid_constant__ CUtensorMap src_map, const Fused2xPar
             uint32_t l = __shfl_up_sync(0xffffffffu, q3, 1);
             if (lane == 0)                                 // tile halo column, or (frame column 0) itself
                 l = c > 0 ? chroma_pair<NEG>(s_src[warp * 4 + i][K2X_HALO - 1], m) : q0;
-            const uint32_t rr = (c + 4 == p.in_w) ? q2 : q3;   // last even column takes itself (FILT_1_3)
+            const uint32_t rr = (B200VC_SPEC_COSITED_LAST_1_3 && c + 4 == p.in_w) ? q2 : q3;   // last even column takes itself (FILT_1_3)
             h0[i] = filt121(l, q0, q1);
             h1[i] = filt121(q1, q2, rr);
         }
@@ -446,6 +445,19 @@ k2_fused_2x_kernel(const __grid_constant__ CUtensorMap src_map, const Fused2xPar
 // The intermediate was written by K1 a moment ago and is read out of L2. A thread owns four
 // consecutive output samples of one line of one plane; the two source lines ride in the two 16-bit
 // lanes of a word, so one multiply-add pair applies the horizontal tap to both.
+// vertical 2-tap on a word holding line 0's sample in byte 1 and line 1's in byte 3:
+// a + (((b-a)*p1 + half) >> bits) == (a*(one-p1) + b*p1 + half) >> bits, one dp4a
+__device__ __forceinline__ uint32_t scale_v2(uint32_t hs, int p1)
+{
+    constexpr int ONE = B200VC_SPEC_VTAP_ONE, HALF = B200VC_SPEC_VTAP_HALF, BITS = B200VC_SPEC_VTAP_BITS;
+    if (ONE < 256)                                            // weights fit a byte: bytes 1 and 3 as they are
+        return dp4a_uu(hs, ((uint32_t)(ONE - p1) << 8) | ((uint32_t)p1 << 24), (uint32_t)HALF) >> BITS;
+    // an 8-bit tap can be 256: each sample twice, the weight split over the two bytes
+    const int a = ONE - p1, b = p1, a1 = min(a, 255), b1 = min(b, 255);
+    const uint32_t w = (uint32_t)a1 << 8 | (uint32_t)(a - a1) | (uint32_t)b1 << 24 | (uint32_t)(b - b1) << 16;
+    return dp4a_uu(prmt(hs, hs, 0x3311), w, (uint32_t)HALF) >> BITS;
+}
+
 __device__ __forceinline__ uint32_t scale4(const uint8_t *r0, const uint8_t *r1, const uint4 th4, int p1, int box)
 {
     const Tap th[4] = { th4.x, th4.y, th4.z, th4.w };
@@ -461,9 +473,12 @@ __device__ __forceinline__ uint32_t scale4(const uint8_t *r0, const uint8_t *r1,
             const uint32_t q = w0 + w1;
             d = ((q & 0xffffu) + (q >> 16) + 2u) >> 2;
         } else {
-            // per lane the sum is < 65536 and its high byte is the scaled pixel; the vertical tap
-            // a + (((b-a)*p1 + 32) >> 6) == (a*(64-p1) + b*p1 + 32) >> 6 is one dp4a on bytes 1 and 3
-            d = dp4a_uu(w0 * (256u - f) + w1 * f, ((uint32_t)(64 - p1) << 8) | ((uint32_t)p1 << 24), 32u) >> 6;
+            if (B200VC_SPEC_SCALE_H_FIRST) {
+                // per lane the sum is < 65536 and its high byte is the horizontally scaled pixel
+                d = scale_v2(w0 * (256u - f) + w1 * f, p1);
+            } else {                                          // vertical pass first (spec variant)
+                d = (scale_v2(w0 << 8, p1) * (256u - f) + scale_v2(w1 << 8, p1) * f) >> 8;
+            }
         }
         out |= d << (8 * k);
     }
@@ -589,9 +604,6 @@ cudaError_t launch_fused_2x(const CUtensorMap &src_map, const Fused2xParams &p, 
         return site ? launch_2x2<0, 1>(src_map, p, box2x2, grid, st) : launch_2x2<0, 0>(src_map, p, box2x2, grid, st);
     return site ? launch_2x2<1, 1>(src_map, p, box2x2, grid, st) : launch_2x2<1, 0>(src_map, p, box2x2, grid, st);
 }
-
-namespace {
-}  // namespace
 
 size_t fused_scale_smem_bytes(int box_w, int box_h)
 {

@@ -43,9 +43,19 @@ struct ConvertParams {
     Matrix mx;
 };
 
-// Packed scaler tap: bits 0..15 first source index (clamped), bits 16..23 fraction (H: 0..255,
-// V: 0..64), bit 24 set when the second tap is index+1 (clear when clamped onto the first).
+// Packed scaler tap: bits 0..14 first source index (clamped), bit 15 set when the second tap is
+// index+1 (clear when clamped onto the first), bits 16..24 fraction (H: 0..255, V: 0..2^VTAP_BITS,
+// at most 256; include/b200vc_spec.h).
 typedef uint32_t Tap;
+#ifdef __CUDACC__
+#define B200VC_TAP_FN __host__ __device__ __forceinline__
+#else
+#define B200VC_TAP_FN inline
+#endif
+B200VC_TAP_FN Tap make_tap(int idx, int frac, int step) { return (Tap)idx | ((Tap)(step & 1) << 15) | ((Tap)frac << 16); }
+B200VC_TAP_FN int tap_idx(Tap t) { return (int)(t & 0x7fffu); }
+B200VC_TAP_FN int tap_step(Tap t) { return (int)((t >> 15) & 1u); }
+B200VC_TAP_FN int tap_frac(Tap t) { return (int)((t >> 16) & 0x1ffu); }
 
 struct ScaleTables {
     const Tap *hy, *vy;     // luma: out_w / out_h entries
@@ -62,8 +72,8 @@ struct ScaleTables {
 //                     32 x {offset of the first tap in a (u,v) line, 256-f, f, 0}
 //   row_rec[by][3*tile_h]: tile_h x {byte offset of the first line in the Y plane, wv}
 //                          tile_h/2 x {word offset of the first line in the (u,v) plane, wv}
-//       wv = wa1 | wa2<<8 | wb1<<16 | wb2<<24 with wa1+wa2 = 256-4*p1, wb1+wb2 = 4*p1:
-//       ([a,a,b,b] . wv + 128) >> 8 == (a*(64-p1) + b*p1 + 32) >> 6
+//       wv = wa1 | wa2<<8 | wb1<<16 | wb2<<24 (host_tables.h v_weight_word), for the 6-bit tap
+//       wa1+wa2 = 256-4*p1, wb1+wb2 = 4*p1: ([a,a,b,b] . wv + 128) >> 8 == (a*(64-p1) + b*p1 + 32) >> 6
 // Columns and rows past the frame edge repeat the last valid entry.
 struct FusedTaps {
     const int2 *tile_x;
@@ -104,12 +114,13 @@ struct PlaneScaleParams {
     int box2x2;
 };
 
-// Two-pass scale, pass 2, tiled form: 64 x 32 output tiles of one plane (NV12 chroma: of U and V
+// Two-pass scale, pass 2, tiled form: KPT_TILE_W x KPT_TILE_H (128 x 64) output tiles of one plane (NV12 chroma: of U and V
 // together), the source window staged in shared memory by coalesced 16-byte loads, taps ready-made in
 // per-tile records like FusedTaps. Kind 0 = luma plane, kind 1 = chroma planes.
 //   tile_x[bx] = window's first source column (multiple of 16), tile_y[by] = its first source line
-//   col_rec[bx][128]: 64 x byte offset of the first tap in a window line, 64 x (255-f) | 1<<8 | f<<16
-//   row_rec[by][64]:  32 x {byte offset of the first line in the window, wv}   (wv as in FusedTaps)
+//   col_rec[bx][2*KPT_TILE_W]: KPT_TILE_W x byte offset of the first tap in a window line,
+//                              KPT_TILE_W x (255-f) | 1<<8 | f<<16
+//   row_rec[by][2*KPT_TILE_H]: KPT_TILE_H x {byte offset of the first line in the window, wv}   (wv as in FusedTaps)
 constexpr int KPT_TILE_W = 128;
 constexpr int KPT_TILE_H = 64;
 struct PlaneTileKind {

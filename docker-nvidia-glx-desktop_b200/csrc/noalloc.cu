@@ -26,17 +26,17 @@
 // output; callers must order them.
 //
 // No cudaMalloc, cudaFree, cudaMallocHost or any other allocating routine is called here, and no
-// tap tables are needed: the scaler below computes its taps from the frame sizes in registers.
+// tap tables are needed: the scaler below computes its taps from the frame sizes in registers, with
+// the same functions (host_tables.h) the context-based path builds its tables from.
 #include "../../include/b200vc.h"
 #include "device_utils.cuh"
+#include "host_tables.h"
 
 #include <cstdarg>
 #include <cstdio>
 #include <mutex>
 
 using namespace b200vc;
-
-#define B200VC_STATIC_SCRATCH_BYTES 3133440   /* 1920 x 1088 x 1.5 */
 
 static __device__ __align__(256) uint8_t g_mid[B200VC_STATIC_SCRATCH_BYTES];
 
@@ -54,34 +54,37 @@ struct StaticScaleParams {
     int box2x2;
 };
 
-// SURVEY B.2 taps computed in place (same integer formulas the tap tables of api.cu hold).
+// SURVEY B.2 taps computed in place (scale_h_tap / scale_v_tap of host_tables.h, indices clamped).
 __device__ __forceinline__ void h_tap(long long inc, int x, int in_n, int &i0, int &i1, int &f)
 {
-    const long long p = (long long)x * inc;
-    const int i = (int)(p >> 16);
-    f = (int)((p >> 8) & 0xff);
-    i0 = min(max(i, 0), in_n - 1);
-    i1 = min(max(i + 1, 0), in_n - 1);
+    int i;
+    scale_h_tap(inc, x, i, f);
+    i0 = clamp_index(i, in_n);
+    i1 = clamp_index((long long)i + 1, in_n);
 }
 
 __device__ __forceinline__ void v_tap(int y, int in_n, int out_n, int &i0, int &i1, int &p1)
 {
-    const long long den = 2LL * out_n, num = (2LL * y + 1) * in_n - out_n;
-    long long i = num / den, rem = num - i * den;
-    if (rem < 0) { i -= 1; rem += den; }
-    p1 = (int)((128 * rem + den) / (2 * den));
-    i0 = (int)min(max(i, 0LL), (long long)in_n - 1);
-    i1 = (int)min(max(i + 1, 0LL), (long long)in_n - 1);
+    long long i;
+    scale_v_tap(y, in_n, out_n, i, p1);
+    i0 = clamp_index(i, in_n);
+    i1 = clamp_index(i + 1, in_n);
 }
+
+__device__ __forceinline__ int v2(int a, int b, int p1)
+{
+    return a + (((b - a) * p1 + B200VC_SPEC_VTAP_HALF) >> B200VC_SPEC_VTAP_BITS);
+}
+
+__device__ __forceinline__ int h2(int a, int b, int f) { return (a * (256 - f) + b * f) >> 8; }
 
 __device__ __forceinline__ int scale_px(const uint8_t *r0, const uint8_t *r1, int j0, int j1, int f, int p1, int box)
 {
     if (box)
         return (r0[j0] + r0[j0 + 1] + r1[j0] + r1[j0 + 1] + 2) >> 2;
-    const int a = (r0[j0] * (256 - f) + r0[j1] * f) >> 8;
-    const int b = (r1[j0] * (256 - f) + r1[j1] * f) >> 8;
-    const int d = a + (((b - a) * p1 + 32) >> 6);
-    return d < 0 ? 0 : (d > 255 ? 255 : d);
+    if (B200VC_SPEC_SCALE_H_FIRST)
+        return v2(h2(r0[j0], r0[j1], f), h2(r1[j0], r1[j1], f), p1);
+    return h2(v2(r0[j0], r1[j0], p1), v2(r0[j1], r1[j1], p1), f);
 }
 
 // Pass 2 on the static intermediate: one thread per 4 output samples of a row; rows 0..out_h-1 are
@@ -134,44 +137,6 @@ int report(char *buf, size_t len, int code, const char *fmt, ...)
         va_end(ap);
     }
     return code;
-}
-
-long long h_inc(int in_n, int out_n)
-{
-    if (out_n <= 1) return 0;
-    long long inc = (((long long)(in_n - 1)) << 16) / (out_n - 1) - 1;
-    return inc < 0 ? 0 : inc;
-}
-
-// Same numbers as the table in api.cu; kept here so that this file stands alone.
-Matrix static_matrix(int matrix, int range, int in_format)
-{
-    static const int pos_tab[4][3] = { { 0, 1, 2 }, { 2, 1, 0 }, { 3, 2, 1 }, { 1, 2, 3 } };   // byte of B, G, R
-    const int *pos = pos_tab[in_format];
-    static const int t[3][2][3][4] = {
-        { { { 66, 129, 25, 4096 }, { -38, -74, 112, 32768 }, { 112, -94, -18, 32768 } },
-          { { 77, 150, 29, 0 }, { -43, -85, 128, 32768 }, { 128, -107, -21, 32768 } } },
-        { { { 47, 157, 16, 4096 }, { -26, -87, 112, 32768 }, { 112, -102, -10, 32768 } },
-          { { 54, 183, 18, 0 }, { -29, -99, 128, 32768 }, { 128, -116, -12, 32768 } } },
-        { { { 58, 149, 13, 4096 }, { -31, -81, 112, 32768 }, { 112, -103, -9, 32768 } },
-          { { 67, 174, 15, 0 }, { -36, -92, 128, 32768 }, { 128, -118, -10, 32768 } } },
-    };
-    const int (*m)[4] = t[matrix][range];
-    auto pack = [pos](int cb, int cg, int cr) {
-        return ((uint32_t)(cb & 0xff) << (8 * pos[0])) | ((uint32_t)(cg & 0xff) << (8 * pos[1])) |
-               ((uint32_t)(cr & 0xff) << (8 * pos[2]));
-    };
-    Matrix r;
-    r.rgb_mask = pack(0xff, 0xff, 0xff);
-    r.cy = pack(m[0][2], m[0][1], m[0][0]);
-    r.oy = (uint32_t)m[0][3];
-    r.neg = range == B200VC_RANGE_FULL ? 1 : 0;      // the full-range rows hold the +128 coefficient
-    const int s = r.neg ? -1 : 1;
-    r.cu = pack(s * m[1][2], s * m[1][1], s * m[1][0]);
-    r.cv = pack(s * m[2][2], s * m[2][1], s * m[2][0]);
-    r.ou = (uint32_t)(r.neg ? 65535 - m[1][3] : m[1][3]);
-    r.ov = (uint32_t)(r.neg ? 65535 - m[2][3] : m[2][3]);
-    return r;
 }
 
 }  // namespace
@@ -244,7 +209,7 @@ extern "C" int b200vc_convert_scale_device_static(const b200vc_config *cfg, cons
 
     cudaStream_t st = (cudaStream_t)cuda_stream;
     const int site = cfg->chroma_site == B200VC_SITE_H_COSITED ? 1 : 0;
-    const Matrix mx = static_matrix(cfg->matrix, cfg->range, cfg->in_format);
+    const Matrix mx = make_matrix(cfg->matrix, cfg->range, cfg->in_format);
     for (int f = 0; f < d->n_frames; f++) {
         // pass 1: K1 at the source size into the static intermediate (always planar)
         ConvertParams p1 = {};
@@ -263,7 +228,7 @@ extern "C" int b200vc_convert_scale_device_static(const b200vc_config *cfg, cons
             p2.out.pitch[i] = i < np ? (long long)d->pitches[i] : 0;
         }
         p2.in_w = cfg->in_w;  p2.in_h = cfg->in_h;  p2.out_w = cfg->out_w;  p2.out_h = cfg->out_h;
-        p2.inc_y = h_inc(cfg->in_w, cfg->out_w);  p2.inc_c = h_inc(cfg->in_w / 2, cfg->out_w / 2);
+        p2.inc_y = scale_h_inc(cfg->in_w, cfg->out_w);  p2.inc_c = scale_h_inc(cfg->in_w / 2, cfg->out_w / 2);
         p2.box2x2 = cfg->scale_mode == B200VC_SCALE_BOX_2X2;
         const int rows = cfg->out_h + cfg->out_h / 2;
         dim3 grid(((cfg->out_w + 3) / 4 + 63) / 64, (rows + 3) / 4, 1);

@@ -160,6 +160,12 @@ int b200vc_damage_to_rects(const uint8_t *map, int frame_w, int frame_h, b200vc_
 const char *b200vc_status_string(int status);
 int b200vc_version(void);
 
+/* The values of include/b200vc_spec.h this library was built with, as one token ("m0c1h1b6r1"): the
+ * details of videoconvert/videoscale's arithmetic that SURVEY.md Appendix A/B could not verify against
+ * GStreamer (matrix rounding term, last column of the cosited filter, order of the scaler's passes,
+ * bits and rounding of its vertical tap). The oracle reports its own the same way; tests compare. */
+const char *b200vc_spec_string(void);
+
 /* ---- lifecycle ----------------------------------------------------------------------------- */
 
 /* GstBaseTransform::start + GstVideoFilter::set_info: build every CUDA resource for the

@@ -11,9 +11,10 @@ from __future__ import annotations
 import ctypes as C
 import os
 import subprocess
-import tempfile
 
 import numpy as np
+
+from . import spec as _spec
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SRCS = ["convert.c", "scale.c", "damage_synth.c"]
@@ -26,30 +27,43 @@ SCALE_GST_LQ, SCALE_BOX_2X2 = 0, 1
 IN_BGRX, IN_RGBX, IN_XRGB, IN_XBGR = 0, 1, 2, 3
 
 
-def build(native: bool = False, out_dir: str | None = None) -> str:
-    """Compile the oracle with gcc. native=True builds -march=native into a temp dir (used by the
-    timed CPU arm so the baseline gets the host's full ISA); otherwise oracle/_build/."""
+def build(native: bool = False, out_dir: str | None = None, spec: dict | None = None) -> str:
+    """Compile the oracle with gcc into oracle/_build/ (x86-64-v3: the file travels to the GPU box), or
+    with native=True into oracle/_build_native/ (-march=native, built on the box that runs it: the
+    timed CPU arm gets the host's full ISA). `spec` (default: include/b200vc_spec.h, then $B200VC_SPEC)
+    selects the values of the spec constants; other values than the header's build into a
+    subdirectory named after them."""
+    sp = _spec.current(spec)
     march = "native" if native else "x86-64-v3"
     if out_dir is None:
-        out_dir = tempfile.mkdtemp(prefix="b200vc_oracle_") if native else os.path.join(_HERE, "_build")
+        out_dir = os.path.join(_HERE, "_build_native" if native else "_build")
+        if not _spec.is_default(sp):
+            out_dir = os.path.join(out_dir, _spec.name(sp))
     os.makedirs(out_dir, exist_ok=True)
     out = os.path.join(out_dir, "liboracle.so")
     srcs = [os.path.join(_HERE, s) for s in _SRCS]
-    newest = max(os.path.getmtime(p) for p in srcs + [os.path.join(_HERE, "oracle.h")])
+    deps = srcs + [os.path.join(_HERE, "oracle.h"), os.path.join(os.path.dirname(_HERE), "include", "b200vc_spec.h")]
+    newest = max(os.path.getmtime(p) for p in deps)
     if os.path.exists(out) and os.path.getmtime(out) >= newest:
         return out
+    tmp = out + f".{os.getpid()}.tmp"                       # ranks of one job may build at the same time
     cmd = [os.environ.get("CC", "gcc"), "-O3", f"-march={march}", "-fPIC", "-std=c11", "-D_GNU_SOURCE",
-           "-shared", "-o", out] + srcs + ["-lm", "-lpthread"]
+           "-shared", "-o", tmp] + _spec.cflags(sp) + srcs + ["-lm", "-lpthread"]
     subprocess.run(cmd, check=True)
+    os.replace(tmp, out)
     return out
 
 
 class Oracle:
     """Thin typed wrapper over liboracle.so working on numpy uint8 arrays."""
 
-    def __init__(self, path: str | None = None, native: bool = False):
-        self.path = path or build(native=native)
+    def __init__(self, path: str | None = None, native: bool = False, spec: dict | None = None):
+        self.path = path or build(native=native, spec=spec)
         L = self.lib = C.CDLL(self.path)
+        L.orc_spec_string.restype = C.c_char_p
+        self.spec = _spec.current(spec)
+        if not path and L.orc_spec_string().decode() != _spec.name(self.spec):
+            raise RuntimeError(f"{self.path} was built as {L.orc_spec_string().decode()}, wanted {_spec.name(self.spec)}")
         u8p, sz, i = C.c_void_p, C.c_size_t, C.c_int
         pl, pi = C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)
         L.orc_build_matrix.argtypes = [i, i, C.POINTER(C.c_int32 * 12)]

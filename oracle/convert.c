@@ -9,6 +9,7 @@
  * run per output line pair, exactly the structure described in SURVEY A.1 / §8(a2-a5).
  */
 #include "oracle.h"
+#include "../include/b200vc_spec.h"   /* the unverified details of SURVEY A/B, one constant each */
 
 #include <math.h>
 #include <pthread.h>
@@ -40,9 +41,12 @@ void orc_build_matrix(int matrix, int range, orc_matrix *out)
     for (int r = 0; r < 3; r++) {
         for (int c = 0; c < 3; c++)
             out->m[r][c] = (int32_t)rint(256.0 * m[r][c] * scale[r] / 255.0);   /* SCALE = 8 */
-        out->m[r][3] = (int32_t)rint(256.0 * off[r]);
+        /* A.2 warning item: a rounding term, if upstream has one, is +128 on every offset */
+        out->m[r][3] = (int32_t)rint(256.0 * off[r]) + (B200VC_SPEC_MATRIX_ROUND ? 128 : 0);
     }
 }
+
+const char *orc_spec_string(void) { return B200VC_SPEC_STRING; }
 
 /* ---- A.5: default layout ------------------------------------------------------------------ */
 
@@ -89,10 +93,12 @@ static void unpack_line(const uint8_t *s, uint8_t *d, int w, int in_format)
 typedef struct {
     int64_t t_r[256], t_g[256], t_b[256];
     int64_t t_c;
+    orc_matrix mx;
 } matrix_tables;
 
 static void init_tables(const orc_matrix *mx, matrix_tables *t)
 {
+    t->mx = *mx;
     for (int i = 0; i < 256; i++) {
         int64_t r = 0, g = 0, b = 0;
         for (int j = 0; j < 3; j++) {
@@ -110,6 +116,19 @@ static void init_tables(const orc_matrix *mx, matrix_tables *t)
 /* video_converter_matrix8_table: ARGB -> AYUV in place, (sum) >> 8 with no rounding term. */
 static void matrix8_table(const matrix_tables *t, uint8_t *p, int w)
 {
+#if B200VC_SPEC_MATRIX_ROUND
+    /* with a rounding term a lane can reach 65536 (full-range U/V of a saturated primary) and would
+     * carry into its neighbour: evaluate the rows apart and clamp, as a clipping matrix stage would */
+    for (int i = 0; i < 4 * w; i += 4) {
+        const int r = p[i + 1], g = p[i + 2], b = p[i + 3];
+        for (int j = 0; j < 3; j++) {
+            int v = t->mx.m[j][0] * r + t->mx.m[j][1] * g + t->mx.m[j][2] * b + t->mx.m[j][3];
+            v = v < 0 ? 0 : (v > 65535 ? 65535 : v);
+            p[i + 1 + j] = (uint8_t)(v >> 8);
+        }
+    }
+    return;
+#endif
     for (int i = 0; i < 4 * w; i += 4) {
         int64_t x = t->t_r[p[i + 1]] + t->t_g[p[i + 2]] + t->t_b[p[i + 3]] + t->t_c;
         p[i + 1] = (uint8_t)(x >> (32 + 8));
@@ -138,7 +157,10 @@ static void chroma_down_h2_cs(uint8_t *p, int w)
         return;
     PU(0) = (uint8_t)((3 * PU(0) + PU(1) + 2) >> 2);
     PV(0) = (uint8_t)((3 * PV(0) + PV(1) + 2) >> 2);
-    for (i = 2; i < w - 2; i += 2) {
+    /* A.4 warning item: where the 1-2-1 loop stops. As recalled it stops before the last even column,
+     * which then ignores u[W-1]; the other candidate runs it while a right neighbour exists. */
+    const int stop = B200VC_SPEC_COSITED_LAST_1_3 ? w - 2 : w - 1;
+    for (i = 2; i < stop; i += 2) {
         PU(i) = (uint8_t)((PU(i - 1) + 2 * PU(i) + PU(i + 1) + 2) >> 2);
         PV(i) = (uint8_t)((PV(i - 1) + 2 * PV(i) + PV(i + 1) + 2) >> 2);
     }

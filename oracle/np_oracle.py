@@ -10,6 +10,11 @@ from __future__ import annotations
 
 import numpy as np
 
+from . import spec as _spec
+
+# the unverified details of SURVEY A/B (include/b200vc_spec.h, overridable through $B200VC_SPEC)
+SPEC = _spec.current()
+
 # (matrix, range) -> rows Y,U,V of (cR, cG, cB, off)
 MATRICES = {
     (0, 0): [(66, 129, 25, 4096), (-38, -74, 112, 32768), (112, -94, -18, 32768)],
@@ -36,6 +41,8 @@ def yuv444(frame: np.ndarray, matrix: int, rng: int, in_format: int = 0):
     out = []
     for cr, cg, cb, off in MATRICES[(matrix, rng)]:
         s = cr * r + cg * g + cb * b + off
+        if SPEC["MATRIX_ROUND"]:                      # A.2 warning item: +128, clamped like a clipping stage
+            s = np.clip(s + 128, 0, 65535)
         assert s.min() >= 0 and s.max() <= 65535
         out.append((s >> 8).astype(np.uint8))
     return out
@@ -56,7 +63,8 @@ def chroma_down(c: np.ndarray, site: int) -> np.ndarray:
     else:  # H_COSITED: h2_cs
         hz[:, 0] = (3 * c[:, 0] + c[:, 1] + 2) >> 2
         i = 2
-        while i < w - 2:
+        stop = w - 2 if SPEC["COSITED_LAST_1_3"] else w - 1      # A.4 warning item: where the 1-2-1 loop stops
+        while i < stop:
             hz[:, i // 2] = (c[:, i - 1] + 2 * c[:, i] + c[:, i + 1] + 2) >> 2
             i += 2
         if i < w:
@@ -88,7 +96,8 @@ def v_taps(in_h: int, out_h: int):
     num, den = (2 * y + 1) * in_h - out_h, 2 * out_h
     i = np.floor_divide(num, den)
     rem = num - i * den
-    return i, (128 * rem + den) // (2 * den)
+    one = 1 << SPEC["VTAP_BITS"]                                 # B.2 warning items: bits and rounding of the tap
+    return i, (2 * one * rem + (den if SPEC["VTAP_ROUND"] else 0)) // (2 * den)
 
 
 def scale_plane(src: np.ndarray, out_w: int, out_h: int, comps: int = 1, mode: int = 0) -> np.ndarray:
@@ -101,10 +110,17 @@ def scale_plane(src: np.ndarray, out_w: int, out_h: int, comps: int = 1, mode: i
     hi, hf = h_taps(in_w, out_w)
     i0, i1 = np.clip(hi, 0, in_w - 1), np.clip(hi + 1, 0, in_w - 1)
     f = hf[None, :, None]
-    hz = (s[:, i0] * (256 - f) + s[:, i1] * f) >> 8
     vi, vp = v_taps(in_h, out_h)
-    a, b = hz[np.clip(vi, 0, in_h - 1)], hz[np.clip(vi + 1, 0, in_h - 1)]
-    d = a + (((b - a) * vp[:, None, None] + 32) >> 6)
+    bits = SPEC["VTAP_BITS"]
+    half = 1 << (bits - 1)
+    if SPEC["SCALE_H_FIRST"]:                                    # B.2 warning item: order of the passes
+        hz = (s[:, i0] * (256 - f) + s[:, i1] * f) >> 8
+        a, b = hz[np.clip(vi, 0, in_h - 1)], hz[np.clip(vi + 1, 0, in_h - 1)]
+        d = a + (((b - a) * vp[:, None, None] + half) >> bits)
+    else:
+        a, b = s[np.clip(vi, 0, in_h - 1)], s[np.clip(vi + 1, 0, in_h - 1)]
+        vz = np.clip(a + (((b - a) * vp[:, None, None] + half) >> bits), 0, 255)
+        d = (vz[:, i0] * (256 - f) + vz[:, i1] * f) >> 8
     return np.clip(d, 0, 255).astype(np.uint8).reshape(out_h, out_w * comps)
 
 

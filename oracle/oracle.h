@@ -35,6 +35,9 @@ typedef struct {
     int32_t m[3][4];
 } orc_matrix;
 
+/* The values of include/b200vc_spec.h this oracle was built with ("m0c1h1b6r1"), see there. */
+const char *orc_spec_string(void);
+
 /* compute_matrix_to_YUV restated: double-precision build, x256, rint() per entry. */
 void orc_build_matrix(int matrix, int range, orc_matrix *out);
 

@@ -10,6 +10,7 @@
  * All tap arithmetic is integer so that every restatement of it agrees bit for bit.
  */
 #include "oracle.h"
+#include "../include/b200vc_spec.h"   /* the unverified details of SURVEY A/B, one constant each */
 
 #include <pthread.h>
 #include <stdlib.h>
@@ -31,7 +32,8 @@ void orc_scale_h_taps(int in_w, int out_w, int32_t *idx, int32_t *frac)
     }
 }
 
-/* B.2 vertical: centre-aligned, 6-bit tap: y' = (y+0.5)*in_h/out_h - 0.5, p1 = round(frac*64). */
+/* B.2 vertical: centre-aligned tap: y' = (y+0.5)*in_h/out_h - 0.5, p1 = round(frac * 2^bits) with
+ * bits = 6 as recalled (B200VC_SPEC_VTAP_BITS; B200VC_SPEC_VTAP_ROUND = 0 floors instead). */
 void orc_scale_v_taps(int in_h, int out_h, int32_t *idx, int32_t *p1)
 {
     const int64_t den = 2 * (int64_t)out_h;
@@ -44,7 +46,7 @@ void orc_scale_v_taps(int in_h, int out_h, int32_t *idx, int32_t *p1)
             rem += den;
         }
         idx[y] = (int32_t)i;
-        p1[y] = (int32_t)((128 * rem + den) / (2 * den));
+        p1[y] = (int32_t)((2 * (int64_t)B200VC_SPEC_VTAP_ONE * rem + (B200VC_SPEC_VTAP_ROUND ? den : 0)) / (2 * den));
     }
 }
 
@@ -99,6 +101,19 @@ int orc_scale_plane(const uint8_t *src, size_t src_pitch, int in_w, int in_h,
     orc_scale_h_taps(in_w, out_w, hi, hf);
     orc_scale_v_taps(in_h, out_h, vi, vp);
 
+#if !B200VC_SPEC_SCALE_H_FIRST
+    /* the other order of B.2: vertical 2-tap over the source lines first, horizontal after it */
+    uint8_t *lv = (uint8_t *)malloc((size_t)in_w * comps);
+    if (!lv) { free(hi); free(vi); free(la); free(lb); return -1; }
+    for (int y = 0; y < out_h; y++) {
+        const uint8_t *sa = src + (size_t)clampi(vi[y], 0, in_h - 1) * src_pitch;
+        const uint8_t *sb = src + (size_t)clampi(vi[y] + 1, 0, in_h - 1) * src_pitch;
+        for (int x = 0; x < in_w * comps; x++)
+            lv[x] = (uint8_t)clampi(sa[x] + (((sb[x] - sa[x]) * vp[y] + B200VC_SPEC_VTAP_HALF) >> B200VC_SPEC_VTAP_BITS), 0, 255);
+        scale_h_line(lv, in_w, dst + (size_t)y * dst_pitch, out_w, comps, hi, hf);
+    }
+    free(lv);
+#else
     int have_a = -1, have_b = -1;
     for (int y = 0; y < out_h; y++) {
         int ia = clampi(vi[y], 0, in_h - 1);
@@ -116,16 +131,17 @@ int orc_scale_plane(const uint8_t *src, size_t src_pitch, int in_w, int in_h,
             scale_h_line(src + (size_t)ib * src_pitch, in_w, lb, out_w, comps, hi, hf);
             have_b = ib;
         }
-        /* video_scale_v_2tap_u8 (lq): d = a + (((b-a)*p1 + 32) >> 6), saturated */
+        /* video_scale_v_2tap_u8 (lq): d = a + (((b-a)*p1 + half) >> bits), saturated. The ORC kernel
+         * does this in 16-bit lanes, which a 6- or 7-bit tap cannot overflow (255*128 + 64 < 32768);
+         * plain int here so that an 8-bit tap is evaluated as wider arithmetic would. */
         uint8_t *d = dst + (size_t)y * dst_pitch;
         int p1 = vp[y];
         for (int x = 0; x < out_w * comps; x++) {
-            int16_t diff = (int16_t)(lb[x] - la[x]);
-            int16_t t = (int16_t)((int16_t)(diff * p1 + 32) >> 6);
-            int v = la[x] + t;
-            d[x] = (uint8_t)clampi(v, 0, 255);
+            int t = ((lb[x] - la[x]) * p1 + B200VC_SPEC_VTAP_HALF) >> B200VC_SPEC_VTAP_BITS;
+            d[x] = (uint8_t)clampi(la[x] + t, 0, 255);
         }
     }
+#endif
     free(hi); free(vi); free(la); free(lb);
     return 0;
 }

@@ -5,6 +5,11 @@ to produce any, so these vectors are made from this repo's own spec: inputs come
 NumPy RNG, expected outputs from oracle/np_oracle.py (the plain-formula restatement of SURVEY
 Appendix A/B). They pin the restatement — the C oracle and the CUDA path must both reproduce them
 — not GStreamer itself. Re-run:  python tests/golden/make_golden.py
+
+vectors.npz holds inputs and the outputs under the default values of include/b200vc_spec.h (the
+unverified details of SURVEY A/B). `python tests/golden/make_golden.py variants` also writes, for every
+other candidate value (oracle/spec.py VARIANTS), vectors_<spec>.npz with the expected outputs of the
+same inputs under that value (outputs only: the inputs are those of vectors.npz).
 """
 import os
 import sys
@@ -36,6 +41,13 @@ CASES = [
 
 
 def main():
+    import subprocess
+    from oracle import spec as S
+    sp = S.current()
+    if len(sys.argv) > 1 and sys.argv[1] == "variants":
+        for ov in S.VARIANTS.values():                  # np_oracle reads the spec at import: one process each
+            subprocess.run([sys.executable, os.path.abspath(__file__)], env=dict(os.environ, B200VC_SPEC=S.env_text(ov)), check=True)
+        return
     rng = np.random.default_rng(20261106)
     out = {}
     for case in CASES:
@@ -55,7 +67,12 @@ def main():
     b[39, 69, 1] ^= 4    # G in the ragged corner MB (2,4)
     b[20, 50, 3] ^= 255  # x byte only: not damage
     out["damage/a"], out["damage/b"], out["damage/map"] = a, b, N.damage_map(b, a)
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "vectors.npz")
+    here = os.path.dirname(os.path.abspath(__file__))
+    if S.is_default(sp):
+        path = os.path.join(here, "vectors.npz")
+    else:
+        path = os.path.join(here, f"vectors_{S.name(sp)}.npz")
+        out = {k: v for k, v in out.items() if "/p" in k}
     np.savez_compressed(path, **out)
     print("wrote", path, os.path.getsize(path), "bytes;", len(CASES), "cases")
 

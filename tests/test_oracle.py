@@ -12,8 +12,14 @@ from hypothesis import given, settings, strategies as st
 
 from helpers import assert_planes_equal, plane_views
 from oracle import np_oracle as N
+from oracle import spec as S
 
+# The suite follows the values of include/b200vc_spec.h the oracle was built with ($B200VC_SPEC selects
+# others: tests/test_spec_variants.py runs this file once per candidate value of every unverified
+# detail). Inputs live in vectors.npz; a non-default spec has its expected outputs in vectors_<spec>.npz.
+SPEC = S.current()
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "vectors.npz")
+GOLDEN_OUT = GOLDEN if S.is_default(SPEC) else os.path.join(os.path.dirname(__file__), "golden", f"vectors_{S.name(SPEC)}.npz")
 
 # (R,G,B) -> (Y,U,V) for [601 limited, 601 full, 709 limited, 709 full]
 KNOWN = {
@@ -30,11 +36,18 @@ KNOWN_2020 = {(255, 255, 255): [(235, 128, 128), (255, 128, 128)], (255, 0, 0): 
               (0, 255, 0): [(164, 47, 25), (173, 36, 10)], (0, 0, 255): [(28, 239, 119), (14, 255, 118)]}
 
 
+def test_oracle_is_built_with_the_spec_under_test(orc):
+    assert orc.lib.orc_spec_string().decode() == S.name(SPEC)
+
+
 def test_matrix_table_matches_survey(orc):
     for (m, r), rows in N.MATRICES.items():
-        assert np.array_equal(orc.matrix(m, r), np.array(rows, np.int32))
+        want = np.array(rows, np.int32)
+        want[:, 3] += 128 if SPEC["MATRIX_ROUND"] else 0
+        assert np.array_equal(orc.matrix(m, r), want)
 
 
+@pytest.mark.skipif(SPEC["MATRIX_ROUND"] != 0, reason="SURVEY A.6 lists the answers of the truncating matrix stage")
 @pytest.mark.parametrize("site", [0, 1])
 @pytest.mark.parametrize("fmt", [0, 1])
 def test_known_answers_uniform_frames(orc, fmt, site):
@@ -55,14 +68,14 @@ def test_known_answers_uniform_frames(orc, fmt, site):
 
 
 def test_golden_vectors(orc):
-    z = np.load(GOLDEN)
+    z, zo = np.load(GOLDEN), np.load(GOLDEN_OUT)
     names = sorted({k.split("/")[0] for k in z.files if k.endswith("/cfg")})
     assert len(names) >= 15
     for name in names:
         iw, ih, ow, oh, fmt, mat, rg, site, mode, inf = [int(v) for v in z[name + "/cfg"]]
         frame = np.ascontiguousarray(z[name + "/in"])
         buf, off, pit = orc.convert(frame, fmt, mat, rg, site, out_size=(ow, oh), scale_mode=mode, in_format=inf)
-        want = [z[f"{name}/p{i}"] for i in range(2 if fmt else 3)]
+        want = [zo[f"{name}/p{i}"] for i in range(2 if fmt else 3)]
         assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), want, name)
     assert np.array_equal(orc.damage_map(np.ascontiguousarray(z["damage/b"]), np.ascontiguousarray(z["damage/a"])),
                           z["damage/map"])
@@ -75,7 +88,8 @@ def test_cosited_edges_by_hand(orc):
     frame[..., 0] = np.array([0, 40, 80, 120, 160, 200], np.uint8)  # B ramp
     y, u, v = N.yuv444(frame, 0, 1)
     u = u.astype(int)
-    h = [(3 * u[0, 0] + u[0, 1] + 2) >> 2, (u[0, 1] + 2 * u[0, 2] + u[0, 3] + 2) >> 2, (u[0, 3] + 3 * u[0, 4] + 2) >> 2]
+    last = (u[0, 3] + 3 * u[0, 4] + 2) >> 2 if SPEC["COSITED_LAST_1_3"] else (u[0, 3] + 2 * u[0, 4] + u[0, 5] + 2) >> 2
+    h = [(3 * u[0, 0] + u[0, 1] + 2) >> 2, (u[0, 1] + 2 * u[0, 2] + u[0, 3] + 2) >> 2, last]
     buf, off, pit = orc.convert(frame, 0, 0, 1, 1)
     pl = plane_views(buf, off, pit, 0, 6, 2)
     assert list(pl[1][0]) == h   # both lines equal, so the vertical mean is the identity
@@ -127,8 +141,12 @@ def test_scaler_taps_survey_b2(orc):
     assert np.array_equal(hf, (33 * np.arange(1920)) >> 8)
     hi, hf = orc.h_taps(1920, 960)    # inc = 131139
     assert np.array_equal(hi, 2 * np.arange(960)) and np.array_equal(hf, (67 * np.arange(960)) >> 8)
-    vi, vp = orc.v_taps(2160, 1080)   # exact 2:1 -> w = 0.5 -> p1 = 32 -> (a+b+1)>>1
-    assert np.array_equal(vi, 2 * np.arange(1080)) and (vp == 32).all()
+    vi, vp = orc.v_taps(2160, 1080)   # exact 2:1 -> w = 0.5 -> p1 = half (32 of 64) -> (a+b+1)>>1
+    assert np.array_equal(vi, 2 * np.arange(1080)) and (vp == (1 << (SPEC["VTAP_BITS"] - 1))).all()
+    vi, vp = orc.v_taps(3, 4)         # y' = -0.125, 0.625, 1.375, 2.125: rounded / floored at the spec's precision
+    one = 1 << SPEC["VTAP_BITS"]
+    fr = [0.875, 0.625, 0.375, 0.125]
+    assert list(vi) == [-1, 0, 1, 2] and list(vp) == [int(f * one + (0.5 if SPEC["VTAP_ROUND"] else 0)) for f in fr]
     for a, b in [(in_, out) for in_ in (7, 16, 33) for out in (2, 5, 16, 40)]:
         assert np.array_equal(orc.h_taps(a, b)[0], N.h_taps(a, b)[0])
         assert np.array_equal(orc.v_taps(a, b)[0], N.v_taps(a, b)[0])

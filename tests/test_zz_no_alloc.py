@@ -10,8 +10,10 @@ point takes the negotiated caps directly instead of a context.
 
 The check: through the C ABI, its output must equal, byte for byte (the tolerance every parity test
 here uses), what the existing context-based entry point b200vc_convert_device writes for the same
-device buffers — on two calls in a row with different geometry, so that whatever the first call
-left in the shared array would show up in the second. The file name sorts last on purpose: a run
+device buffers, and what the CPU oracle computes for the same frames — on calls in a row with
+different geometry, so that whatever one call left in the shared array would show up in the next.
+Where the box has a second GPU the same runs there too: every device holds its own copy of the
+array, whose address the library looks up on the first call made on that device. The file name sorts last on purpose: a run
 that stops at the first failure has then already run every other test. It passes on its own in a
 fresh process as well as after the rest of the suite.
 """
@@ -21,6 +23,7 @@ import numpy as np
 import pytest
 
 import b200vc
+from helpers import assert_planes_equal, plane_views
 
 pytestmark = pytest.mark.gpu
 
@@ -41,29 +44,39 @@ def _static(lib, cfg, df, stream=0):
     return rc, err.value.decode()
 
 
-def test_static_scratch_entry_point_matches_context_entry_point(lib):
+def _devices():
     import torch
-    torch.cuda.set_device(0)
-    gen = torch.Generator(device="cuda")
+    return [0, 1] if torch.cuda.device_count() > 1 else [0]
+
+
+@pytest.mark.parametrize("dev", [0, 1])
+def test_static_scratch_entry_point_matches_context_entry_point(lib, orc, dev):
+    import torch
+    if dev not in _devices():
+        pytest.skip("one GPU on this box")
+    torch.cuda.set_device(dev)
+    gen = torch.Generator(device=f"cuda:{dev}")
     gen.manual_seed(1234)
-    conv = b200vc.Converter(0)
-    # two calls in a row, different geometry, format and caps; the second is larger than the first
+    conv = b200vc.Converter(dev)
+    # calls in a row, different geometry, format and caps; the second is larger than the first
     cases = [(1280, 720, 640, 360, 0, 1, 0, 1, 0, 2),      # I420 bt709 limited mpeg2, 2 frames
              (1920, 1080, 1280, 720, 1, 0, 1, 0, 0, 1),    # NV12 bt601 full jpeg, 3:2
-             (640, 360, 320, 180, 0, 1, 0, 1, 1, 1)]       # BOX_2X2, smaller again: stale bytes beyond it
+             (640, 360, 320, 180, 0, 1, 0, 1, 1, 1),       # BOX_2X2, smaller again: stale bytes beyond it
+             (960, 540, 1280, 720, 0, 2, 0, 1, 0, 1),      # bt2020 limited, upscale
+             (1280, 720, 854, 480, 1, 2, 1, 0, 0, 1)]      # bt2020 full (the negated-matrix kernels), NV12
     # second round over the same cases: every kernel image is loaded by then, so the device's free
     # memory must not move across a call
     for rnd, (iw, ih, ow, oh, fmt, m, rg, site, mode, n) in [(r, c) for r in (0, 1) for c in cases]:
         total = b200vc.default_layout(fmt, ow, oh)[0]
-        d_in = torch.randint(0, 256, (n, iw * ih * 4), dtype=torch.uint8, device="cuda", generator=gen)
-        want = torch.zeros((n, total), dtype=torch.uint8, device="cuda")
-        got = torch.full((n, total), 0xA5, dtype=torch.uint8, device="cuda")
+        d_in = torch.randint(0, 256, (n, iw * ih * 4), dtype=torch.uint8, device=f"cuda:{dev}", generator=gen)
+        want = torch.zeros((n, total), dtype=torch.uint8, device=f"cuda:{dev}")
+        got = torch.full((n, total), 0xA5, dtype=torch.uint8, device=f"cuda:{dev}")
         # existing entry point (fused kernel where it applies) on a context
         conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=m, range_=rg, chroma_site=site, scale_mode=mode)
         conv.convert_device(_device_frames(d_in, want, iw, ih, ow, oh, fmt, n), 0)
         torch.cuda.synchronize()
         # new entry point: no context, nothing allocated between the two memory readings
-        cfg = b200vc.Config(0, iw, ih, ow, oh, fmt, m, rg, site, mode, 0, 0, 0, 0)
+        cfg = b200vc.Config(dev, iw, ih, ow, oh, fmt, m, rg, site, mode, 0, 0, 0, 0)
         df = _device_frames(d_in, got, iw, ih, ow, oh, fmt, n)
         free_before = torch.cuda.mem_get_info()[0]
         rc, msg = _static(lib, cfg, df)
@@ -73,7 +86,15 @@ def test_static_scratch_entry_point_matches_context_entry_point(lib):
             assert torch.cuda.mem_get_info()[0] == free_before, "the entry point changed the device's free memory"
         a, b = got.cpu().numpy(), want.cpu().numpy()
         assert np.array_equal(a, b), f"{iw}x{ih}->{ow}x{oh}: {int((a != b).sum())} bytes differ from b200vc_convert_device"
+        if rnd == 0:                 # and against the oracle itself, frame by frame
+            _, off, pit = b200vc.default_layout(fmt, ow, oh)
+            host_in = d_in.cpu().numpy()
+            for k in range(n):
+                obuf, ooff, opit = orc.convert(host_in[k].reshape(ih, iw, 4), fmt, m, rg, site, out_size=(ow, oh), scale_mode=mode)
+                assert_planes_equal(plane_views(a[k], off, pit, fmt, ow, oh), plane_views(obuf, ooff, opit, fmt, ow, oh),
+                                    f"device {dev} {iw}x{ih}->{ow}x{oh} frame {k} vs oracle")
     conv.stop()
+    torch.cuda.set_device(0)
 
 
 def test_static_scratch_limits_and_errors(lib):

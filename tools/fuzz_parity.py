@@ -1,6 +1,9 @@
 """Randomised parity sweep on the GPU: random geometries (odd and even, up- and down-scales), caps,
-sink formats and path flags, each compared byte for byte with the CPU oracle through the C ABI.
+sink formats and path flags, each compared byte for byte with the CPU oracle through the C ABI. Even-sized
+scaled cases whose source fits also go through the no-allocation entry point. Library and oracle must be
+built with the same values of include/b200vc_spec.h ($B200VC_LIB / $B200VC_SPEC select a variant).
   python tools/fuzz_parity.py [n_cases] [seed]"""
+import ctypes as C
 import os
 import sys
 
@@ -13,13 +16,38 @@ import oracle  # noqa: E402
 from helpers import plane_views  # noqa: E402
 
 
+def static_entry(lib, frame, iw, ih, ow, oh, fmt, m, rg, site, mode, inf):
+    """b200vc_convert_scale_device_static on device copies of the frame; returns the output frame (host)."""
+    import torch
+    total, off, pit = b200vc.default_layout(fmt, ow, oh)
+    d_in = torch.from_numpy(np.ascontiguousarray(frame)).cuda()
+    d_out = torch.zeros(total, dtype=torch.uint8, device="cuda")
+    df = b200vc.DeviceFrames()
+    df.bgrx, df.in_pitch, df.in_frame_stride = d_in.data_ptr(), iw * 4, iw * ih * 4
+    for i in range(2 if fmt else 3):
+        df.planes[i], df.pitches[i] = d_out.data_ptr() + off[i], pit[i]
+    df.out_frame_stride, df.n_frames = total, 1
+    cfg = b200vc.Config(0, iw, ih, ow, oh, fmt, m, rg, site, mode, 0, 0, 0, 0, inf)
+    err = C.create_string_buffer(512)
+    rc = lib.b200vc_convert_scale_device_static(C.byref(cfg), C.byref(df), None, err, len(err))
+    torch.cuda.synchronize()
+    if rc:
+        raise RuntimeError(f"static entry point: status {rc}: {err.value.decode()}")
+    return d_out.cpu().numpy()
+
+
 def main():
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 300
     seed = int(sys.argv[2]) if len(sys.argv) > 2 else 1
     rng = np.random.default_rng(seed)
     orc, conv = oracle.get(), b200vc.Converter(0)
+    lib_spec, orc_spec = conv.lib.b200vc_spec_string().decode(), orc.lib.orc_spec_string().decode()
+    if lib_spec != orc_spec:
+        print(f"library built as {lib_spec}, oracle as {orc_spec}: not comparable")
+        return 2
     bad = 0
     paths = {0: 0, 1: 0, 2: 0}
+    n_static = 0
     for case in range(n):
         iw, ih = int(rng.integers(2, 400)), int(rng.integers(2, 200))
         if rng.random() < 0.15:
@@ -60,13 +88,18 @@ def main():
             want = orc.convert(f, fmt, m, rg, site, out_size=(ow, oh), scale_mode=mode, in_format=inf)
             for a, b in zip(plane_views(buf, off, pit, fmt, ow, oh), plane_views(*want, fmt, ow, oh)):
                 ok = ok and np.array_equal(a, b)
+            if scaling and not ((iw | ih | ow | oh) & 1) and iw * ih * 3 // 2 <= 2_000_000 and rng.random() < 0.5:
+                got = static_entry(conv.lib, f, iw, ih, ow, oh, fmt, m, rg, site, mode, inf)
+                n_static += 1
+                for a, b in zip(plane_views(got, off, pit, fmt, ow, oh), plane_views(*want, fmt, ow, oh)):
+                    ok = ok and np.array_equal(a, b)
         except Exception as e:  # noqa: BLE001
             ok = False
             print("EXC", e)
         if not ok:
             bad += 1
             print("MISMATCH", dict(iw=iw, ih=ih, ow=ow, oh=oh, fmt=fmt, m=m, rg=rg, site=site, inf=inf, flags=flags, mode=mode), flush=True)
-    print(f"{n} cases, {bad} mismatches, paths used {paths}")
+    print(f"{n} cases, {bad} mismatches, paths used {paths}, no-allocation entry point {n_static}, spec {lib_spec}")
     conv.stop()
     return 1 if bad else 0
 

@@ -7,7 +7,11 @@
 // xgl.yml:10,120; README.md:182), so GPUs never talk: one libb200vc context per GPU, no collective.
 // Plain C++ over the C ABI; no Python, no torch.
 //
-//   session_bench [--gpus G] [--sessions S] [--seconds T] [--hz F] [--damage]
+//   session_bench [--gpus G] [--device D] [--sessions S] [--seconds T] [--hz F] [--damage]
+//                 [--in WxH] [--out WxH] [--nv12] [--matrix 0|1|2] [--full] [--wait-file PATH]
+// --hz 0 runs the ticks back to back (end-to-end throughput with no interpreter in the loop);
+// --device D puts a one-GPU run on device D (one process per GPU, the way bench.py's ranks use it);
+// --wait-file makes every worker start its first tick only once PATH exists (ranks start together).
 #include <algorithm>
 #include <atomic>
 #include <chrono>
@@ -18,6 +22,8 @@
 #include <string>
 #include <thread>
 #include <vector>
+
+#include <unistd.h>
 
 #include "b200vc.h"
 
@@ -40,19 +46,24 @@ static uint64_t splitmix64(uint64_t &s)
     return z ^ (z >> 31);
 }
 
-static void worker(int device, int sessions, double seconds, double hz, bool damage, GpuResult *res)
+struct Geometry { int W = 1920, H = 1080, OW = 1920, OH = 1080, fmt = B200VC_FMT_I420, matrix = -1, range = -1; };
+static std::string g_wait_file;
+
+static void worker(int device, int sessions, double seconds, double hz, bool damage, Geometry geo, GpuResult *res)
 {
     res->device = device;
-    const int W = 1920, H = 1080;
+    const int W = geo.W, H = geo.H;
     b200vc_config cfg;
     memset(&cfg, 0, sizeof cfg);
     cfg.device = device;
-    cfg.in_w = cfg.out_w = W;
-    cfg.in_h = cfg.out_h = H;
-    cfg.out_format = B200VC_FMT_I420;
-    b200vc_default_colorimetry(H, &cfg.matrix, &cfg.range, &cfg.chroma_site);
+    cfg.in_w = W;  cfg.in_h = H;
+    cfg.out_w = geo.OW;  cfg.out_h = geo.OH;
+    cfg.out_format = geo.fmt;
+    b200vc_default_colorimetry(geo.OH, &cfg.matrix, &cfg.range, &cfg.chroma_site);
+    if (geo.matrix >= 0) cfg.matrix = geo.matrix;
+    if (geo.range >= 0) cfg.range = geo.range;
     cfg.max_sessions = sessions;
-    cfg.n_inflight = sessions;
+    cfg.n_inflight = sessions < 64 ? sessions : 64;   // (the context keeps one slot per session anyway)
     cfg.flags = damage ? B200VC_FLAG_DAMAGE_MAP : 0;
     b200vc_ctx *ctx = nullptr;
     if ((res->rc = b200vc_create(&cfg, &ctx)) != B200VC_OK) {
@@ -60,7 +71,7 @@ static void worker(int device, int sessions, double seconds, double hz, bool dam
         return;
     }
     size_t off[3], pit[3];
-    const size_t out_bytes = b200vc_default_layout(cfg.out_format, W, H, off, pit);
+    const size_t out_bytes = b200vc_default_layout(cfg.out_format, geo.OW, geo.OH, off, pit);
     const size_t in_bytes = (size_t)W * H * 4, mb = (size_t)((W + 15) / 16) * ((H + 15) / 16);
     // two input frames per session (a desktop that changes a little every tick), pinned
     std::vector<uint8_t *> in(sessions * 2), out(sessions), dmg(sessions);
@@ -80,12 +91,15 @@ static void worker(int device, int sessions, double seconds, double hz, bool dam
         for (int y = 100; y < 124; y++) memset(in[s * 2 + 1] + ((size_t)y * W + 200 + 7 * s) * 4, 0xff, 16 * 4);   // a "cursor"
     }
     std::vector<b200vc_frame> frames(sessions);
-    const auto period = std::chrono::duration_cast<clk::duration>(std::chrono::duration<double>(1.0 / hz));
+    if (!g_wait_file.empty())
+        while (access(g_wait_file.c_str(), F_OK) != 0) std::this_thread::sleep_for(std::chrono::microseconds(200));
+    const bool paced = hz > 0;
+    const auto period = std::chrono::duration_cast<clk::duration>(std::chrono::duration<double>(paced ? 1.0 / hz : 0.0));
     const auto t_end = clk::now() + std::chrono::duration_cast<clk::duration>(std::chrono::duration<double>(seconds));
     auto next = clk::now();
     const auto t_run = next;
     for (uint64_t tick = 0; clk::now() < t_end; tick++) {
-        std::this_thread::sleep_until(next);
+        if (paced) std::this_thread::sleep_until(next);
         const auto t0 = clk::now();
         for (int s = 0; s < sessions; s++) {
             b200vc_frame &f = frames[s];
@@ -105,7 +119,7 @@ static void worker(int device, int sessions, double seconds, double hz, bool dam
         res->frames += sessions;
         res->ticks += 1;
         next += period;
-        if (clk::now() > next) { res->late_ticks += 1; next = clk::now(); }   // missed the period: resynchronise
+        if (paced && clk::now() > next) { res->late_ticks += 1; next = clk::now(); }   // missed the period: resynchronise
     }
     res->run_s = std::chrono::duration<double>(clk::now() - t_run).count();
     b200vc_destroy(ctx);
@@ -122,21 +136,29 @@ static float pct(std::vector<float> v, double q)
 
 int main(int argc, char **argv)
 {
-    int gpus = 1, sessions = 8;
+    int gpus = 1, sessions = 8, device0 = 0;
     double seconds = 5, hz = 60;
     bool damage = false;
+    Geometry geo;
     for (int i = 1; i < argc; i++) {
         if (!strcmp(argv[i], "--gpus") && i + 1 < argc) gpus = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--device") && i + 1 < argc) device0 = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--in") && i + 1 < argc) { if (sscanf(argv[++i], "%dx%d", &geo.W, &geo.H) != 2) return 2; geo.OW = geo.W; geo.OH = geo.H; }
+        else if (!strcmp(argv[i], "--out") && i + 1 < argc) { if (sscanf(argv[++i], "%dx%d", &geo.OW, &geo.OH) != 2) return 2; }
+        else if (!strcmp(argv[i], "--nv12")) geo.fmt = B200VC_FMT_NV12;
+        else if (!strcmp(argv[i], "--matrix") && i + 1 < argc) geo.matrix = atoi(argv[++i]);
+        else if (!strcmp(argv[i], "--full")) geo.range = B200VC_RANGE_FULL;
+        else if (!strcmp(argv[i], "--wait-file") && i + 1 < argc) g_wait_file = argv[++i];
         else if (!strcmp(argv[i], "--sessions") && i + 1 < argc) sessions = atoi(argv[++i]);
         else if (!strcmp(argv[i], "--seconds") && i + 1 < argc) seconds = atof(argv[++i]);
         else if (!strcmp(argv[i], "--hz") && i + 1 < argc) hz = atof(argv[++i]);
         else if (!strcmp(argv[i], "--damage")) damage = true;
-        else { fprintf(stderr, "usage: %s [--gpus G] [--sessions S] [--seconds T] [--hz F] [--damage]\n", argv[0]); return 2; }
+        else { fprintf(stderr, "usage: %s [--gpus G] [--device D] [--sessions S] [--seconds T] [--hz F] [--damage] [--in WxH] [--out WxH] [--nv12] [--matrix M] [--full] [--wait-file PATH]\n", argv[0]); return 2; }
     }
     std::vector<GpuResult> res(gpus);
     std::vector<std::thread> th;
     const auto t0 = clk::now();
-    for (int g = 0; g < gpus; g++) th.emplace_back(worker, g, sessions, seconds, hz, damage, &res[g]);
+    for (int g = 0; g < gpus; g++) th.emplace_back(worker, device0 + g, sessions, seconds, hz, damage, geo, &res[g]);
     for (auto &t : th) t.join();
     const double wall = std::chrono::duration<double>(clk::now() - t0).count();
     uint64_t frames = 0, late = 0, ticks = 0;
@@ -149,12 +171,14 @@ int main(int argc, char **argv)
         frames += r.frames;  late += r.late_ticks;  ticks += r.ticks;
         all.insert(all.end(), r.tick_ms.begin(), r.tick_ms.end());
     }
-    printf("{\"config\": \"C5: %d sessions x %d GPUs, 1080p BGRx->I420 at %.0f Hz%s\", \"sessions\": %d, \"frames\": %llu, "
+    printf("{\"config\": \"%d sessions x %d GPUs, %dx%d BGRx->%s %dx%d, %s%s\", \"sessions\": %d, \"frames\": %llu, "
            "\"wall_s\": %.2f, \"aggregate_fps\": %.1f, \"target_fps\": %.1f, \"ticks\": %llu, \"late_ticks\": %llu, "
            "\"tick_ms_p50\": %.3f, \"tick_ms_p99\": %.3f, \"tick_ms_max\": %.3f, \"tick_budget_ms\": %.3f, \"per_gpu_p99_ms\": [",
-           sessions, gpus, hz, damage ? ", damage map" : "", sessions * gpus, (unsigned long long)frames, wall, run_s > 0 ? frames / run_s : 0.0,
+           sessions, gpus, geo.W, geo.H, geo.fmt == B200VC_FMT_NV12 ? "NV12" : "I420", geo.OW, geo.OH,
+           hz > 0 ? (std::to_string((int)hz) + " Hz").c_str() : "back to back", damage ? ", damage map" : "",
+           sessions * gpus, (unsigned long long)frames, wall, run_s > 0 ? frames / run_s : 0.0,
            sessions * gpus * hz, (unsigned long long)ticks, (unsigned long long)late, pct(all, 0.5), pct(all, 0.99), pct(all, 0.9999),
-           1000.0 / hz);
+           hz > 0 ? 1000.0 / hz : 0.0);
     for (int g = 0; g < gpus; g++) printf("%s%.3f", g ? ", " : "", pct(res[g].tick_ms, 0.99));
     printf("]}\n");
     return rc;

@@ -63,7 +63,7 @@ def test_static_scratch_entry_point_matches_context_entry_point(lib, orc, dev):
              (1920, 1080, 1280, 720, 1, 0, 1, 0, 0, 1),    # NV12 bt601 full jpeg, 3:2
              (640, 360, 320, 180, 0, 1, 0, 1, 1, 1),       # BOX_2X2, smaller again: stale bytes beyond it
              (960, 540, 1280, 720, 0, 2, 0, 1, 0, 1),      # bt2020 limited, upscale
-             (1280, 720, 854, 480, 1, 2, 1, 0, 0, 1)]      # bt2020 full (the negated-matrix kernels), NV12
+             (1280, 720, 848, 480, 1, 2, 1, 0, 0, 1)]      # bt2020 full (the negated-matrix kernels), NV12
     # second round over the same cases: every kernel image is loaded by then, so the device's free
     # memory must not move across a call
     for rnd, (iw, ih, ow, oh, fmt, m, rg, site, mode, n) in [(r, c) for r in (0, 1) for c in cases]:

@@ -88,7 +88,8 @@ def main():
             want = orc.convert(f, fmt, m, rg, site, out_size=(ow, oh), scale_mode=mode, in_format=inf)
             for a, b in zip(plane_views(buf, off, pit, fmt, ow, oh), plane_views(*want, fmt, ow, oh)):
                 ok = ok and np.array_equal(a, b)
-            if scaling and not ((iw | ih | ow | oh) & 1) and iw * ih * 3 // 2 <= 2_000_000 and rng.random() < 0.5:
+            # (its device input needs a 16-byte row pitch: widths that are multiples of 4)
+            if scaling and not ((iw | ih | ow | oh) & 1) and iw % 4 == 0 and iw * ih * 3 // 2 <= 2_000_000 and rng.random() < 0.7:
                 got = static_entry(conv.lib, f, iw, ih, ow, oh, fmt, m, rg, site, mode, inf)
                 n_static += 1
                 for a, b in zip(plane_views(got, off, pit, fmt, ow, oh), plane_views(*want, fmt, ow, oh)):

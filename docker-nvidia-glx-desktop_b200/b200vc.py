@@ -27,12 +27,13 @@ SITE_NONE, SITE_H_COSITED = 0, 1
 SCALE_GST_LQ, SCALE_BOX_2X2 = 0, 1
 IN_BGRX, IN_RGBX, IN_XRGB, IN_XBGR = 0, 1, 2, 3
 FLAG_DAMAGE_MAP, FLAG_FORCE_TWO_PASS, FLAG_REGISTER_HOST, FLAG_FORCE_GENERIC_FUSED, FLAG_ZERO_COPY, FLAG_ZERO_COPY_OUT = 1, 2, 4, 8, 16, 32
+FLAG_ROW_GATE = 64
 
 # every symbol include/b200vc.h declares
 SYMBOLS = [
     "b200vc_default_colorimetry", "b200vc_default_layout", "b200vc_check_config", "b200vc_status_string",
     "b200vc_version", "b200vc_spec_string", "b200vc_create", "b200vc_destroy", "b200vc_last_error", "b200vc_get_info",
-    "b200vc_get_stats", "b200vc_reset", "b200vc_convert", "b200vc_convert_batch", "b200vc_submit",
+    "b200vc_get_stats", "b200vc_reset", "b200vc_convert", "b200vc_convert_session", "b200vc_convert_batch", "b200vc_submit",
     "b200vc_collect", "b200vc_host_alloc", "b200vc_host_free", "b200vc_convert_device",
     "b200vc_convert_scale_device_static", "b200vc_damage_to_rects",
 ]
@@ -107,6 +108,7 @@ def load() -> C.CDLL:
     L.b200vc_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.b200vc_reset.argtypes = [vp, i]
     L.b200vc_convert.argtypes = [vp, vp, sz, C.POINTER(vp), C.POINTER(sz), vp]
+    L.b200vc_convert_session.argtypes = [vp, i, vp, sz, C.POINTER(vp), C.POINTER(sz), vp]
     L.b200vc_convert_batch.argtypes = [vp, C.POINTER(Frame), i]
     L.b200vc_submit.argtypes = [vp, C.POINTER(Frame), C.POINTER(C.c_uint64)]
     L.b200vc_collect.argtypes = [vp, C.c_uint64]
@@ -220,7 +222,8 @@ class Converter:
         self._check(self.lib.b200vc_reset(self.ctx, session))
 
     # -- GstVideoFilter::transform_frame ---------------------------------------------------------
-    def transform_frame(self, frame: np.ndarray, out: np.ndarray | None = None, pitches=None, damage: bool = False):
+    def transform_frame(self, frame: np.ndarray, out: np.ndarray | None = None, pitches=None, damage: bool = False,
+                        session: int = 0):
         """frame: (h, w, 4) uint8 BGRx view (row stride free). Returns (buf, offsets, pitches[, map])."""
         if not self.ctx:
             raise B200vcError(ERR_NOT_NEGOTIATED, "set_info has not succeeded")
@@ -240,8 +243,8 @@ class Converter:
         planes = (C.c_void_p * 3)(*[out.ctypes.data + o for o in off])
         pits = (C.c_size_t * 3)(*pit)
         dmg = np.zeros(self.mb_shape, np.uint8) if damage else None
-        self._check(self.lib.b200vc_convert(self.ctx, frame.ctypes.data, frame.strides[0], planes, pits,
-                                            dmg.ctypes.data if damage else None))
+        self._check(self.lib.b200vc_convert_session(self.ctx, session, frame.ctypes.data, frame.strides[0], planes, pits,
+                                                    dmg.ctypes.data if damage else None))
         return (out, off, pit, dmg) if damage else (out, off, pit)
 
     def make_frame(self, in_ptr: int, in_pitch: int, out_ptr: int, off, pit, session: int = 0,

@@ -1,11 +1,18 @@
 // api.cu — the C ABI of libb200vc.so (include/b200vc.h) and the host runtime behind it:
-// negotiation checks, per-session device frames, pinned staging, the three-stream PCIe pipeline
-// (H2D / kernel / D2H with events), tap tables and TMA descriptors for the fused scaler.
+// negotiation checks, per-session device frames, pinned staging, the PCIe pipeline (copy streams,
+// kernel stream, events; row-gated kernels for the synchronous call), tap tables and TMA
+// descriptors for the fused scaler.
 //
 // Mirrors what GstVideoConvert/GstVideoScale do around gst_video_converter_frame on the
 // reference's x264enc fallback (/root/reference Dockerfile:467-471, README.md:21): set_info builds
 // the converter once, transform_frame runs it per buffer (b). No CPU fallback
 // exists anywhere in this file: without a usable sm_100 device every call fails.
+//
+// Locking. A context has one mutex. It is held while a call books a slot and enqueues work, and it
+// is released around everything that takes long on the host: waiting for a frame's completion
+// event, and copying pageable caller buffers to or from the pinned staging buffers. Session threads
+// sharing a context therefore overlap their waits and their staging copies; only the enqueueing is
+// serialised.
 #include "../../include/b200vc.h"
 #include "kernels.cuh"
 #include "host_tables.h"
@@ -13,6 +20,7 @@
 #include <cudaTypedefs.h>
 
 #include <algorithm>
+#include <condition_variable>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -26,6 +34,8 @@ namespace {
 
 thread_local std::string g_create_error;
 
+constexpr int kMaxChunks = 64;                 // row-gate flags per slot (n_bands <= 64)
+
 struct Session {
     uint8_t *d_in[2] = { nullptr, nullptr };   // ping-pong: current and previous frame stay in HBM
     int cur = 0;
@@ -34,20 +44,33 @@ struct Session {
     bool ev_valid = false;
 };
 
+// FREE -> SUBMITTING (booked, work still being enqueued: nobody may collect it) -> BUSY (its completion
+// event is recorded) -> COLLECTING (a thread waits for it with the mutex released) -> FREE
+enum SlotState { SLOT_FREE = 0, SLOT_SUBMITTING = 1, SLOT_BUSY = 2, SLOT_COLLECTING = 3 };
+
 struct Slot {
     uint8_t *d_out = nullptr;                 // device output frame (+ damage map at d_dmg)
     uint8_t *d_dmg = nullptr;
+    uint32_t *d_flags = nullptr;              // row gate: kMaxChunks flags + 1 time-out word, zero at create
+    uint32_t *h_flag_src = nullptr;           // pinned, mapped: word kMaxChunks is the gate's time-out word
+    uint32_t epoch = 0;
+    bool gated = false;                       // this frame ran row-gated: look at the time-out word when collecting
     uint8_t *h_in = nullptr;                  // pinned staging, allocated on first pageable frame
     uint8_t *h_out = nullptr;
+    uint8_t *h_map = nullptr;                 // pinned staging for a pageable damage map (damage contexts)
     cudaEvent_t done = nullptr;
-    bool busy = false;
+    int state = SLOT_FREE;
     uint64_t ticket = 0;
-    // deferred host copy out of h_out when the caller's planes are pageable
-    bool staged_out = false;
+    bool staged_out = false;                  // deferred host copy out of h_out (pageable planes)
+    bool staged_map = false;                  // deferred host copy out of h_map (pageable map)
     b200vc_frame frame;
 };
 
-struct HostReg { const void *base; size_t bytes; };
+struct HostReg { const uint8_t *base; size_t bytes; uint64_t last_use; };
+struct PtrKind { const void *p; int kind; const uint8_t *lo, *hi; };   // hi/lo: extent of the page-locked allocation
+struct MapEntry { const void *base; size_t pitch, fstride; int n_frames; CUtensorMap map; };
+
+typedef CUresult (*WriteValue32Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
 
 }  // namespace
 
@@ -58,11 +81,15 @@ struct b200vc_ctx {
     Matrix mx;
     cudaDeviceProp prop;
     cudaStream_t s_h2d = nullptr, s_k = nullptr, s_d2h = nullptr;
+    cudaStream_t s_up[4] = { nullptr, nullptr, nullptr, nullptr };   // row gate: chunks alternate over these (s_up[0] == s_h2d)
+    int n_up = 1;
+    bool auto_bands = false;                   // n_bands was left 0: chosen per frame
     std::vector<cudaEvent_t> ev_band_h2d, ev_band_k;
 
-    // device geometry (library-owned buffers: pitches padded so every row is 16-byte aligned)
+    // device geometry (library-owned buffers)
     size_t d_in_pitch = 0, d_in_size = 0;
     size_t d_off[3] = { 0, 0, 0 }, d_pitch[3] = { 0, 0, 0 }, d_out_size = 0;
+    bool out_compact = false;                  // device output frame = b200vc_default_layout: a contiguous caller frame leaves in one copy
     int mb_w = 0, mb_h = 0;
 
     std::vector<Session> sessions;
@@ -86,16 +113,25 @@ struct b200vc_ctx {
     uint8_t *d_mid = nullptr;                  // two-pass: full-size intermediate I420
     size_t mid_off[3] = { 0, 0, 0 }, mid_pitch[3] = { 0, 0, 0 }, mid_size = 0;
     int mid_frames = 0;
+    cudaEvent_t ev_mid = nullptr;              // last pass 2 that read d_mid, on whichever stream it ran
+    bool ev_mid_valid = false;
     PFN_cuTensorMapEncodeTiled_v12000 encode_tiled = nullptr;
+    std::vector<MapEntry> maps;                // tensor maps seen so far (a session has two input buffers)
+    size_t next_map = 0;
+    WriteValue32Fn write_value = nullptr;      // cuStreamWriteValue32, for the row gate's flags
 
-    std::vector<HostReg> registered;
+    std::vector<HostReg> registered;           // B200VC_FLAG_REGISTER_HOST: ranges this context page-locked
+    uint64_t reg_clock = 0;
+    PtrKind kinds[256] = {};                   // what cudaPointerGetAttributes said about recent caller pointers
     b200vc_stats stats;
     mutable std::mutex mu;
+    std::condition_variable cv;                // a slot left SLOT_COLLECTING
     std::string err;
 };
 
 namespace {
 
+typedef std::unique_lock<std::mutex> Lock;
 int fail(b200vc_ctx *c, int code, const char *fmt, ...)
 {
     char buf[512];
@@ -354,49 +390,161 @@ int check_config(const b200vc_config *c, std::string *why)
     return B200VC_OK;
 }
 
-// 1 = page-locked host memory (cudaMallocHost / cudaHostRegister), 0 = pageable host memory,
-// -1 = device or managed memory (belongs to b200vc_convert_device, not to the host entry points)
-int host_kind(const void *p)
+// What a caller pointer is: 1 = page-locked host memory (cudaMallocHost / cudaHostRegister), 0 = pageable
+// host memory, -1 = device or managed memory (belongs to b200vc_convert_device, not to the host entry
+// points). For page-locked memory also the extent [lo, hi) of the page-locked allocation it lies in: a
+// buffer is page-locked only if it lies in ONE such extent as a whole. (A buffer on the heap can begin and
+// end in pages its neighbours had locked while its middle is pageable; the copy engine refuses that.)
+typedef CUresult (*PointerGetAttributeFn)(void *, CUpointer_attribute, CUdeviceptr);
+
+PointerGetAttributeFn pointer_get_attribute()
 {
+    static PointerGetAttributeFn fn = [] {
+        void *f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuPointerGetAttribute", &f, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) {
+            cudaGetLastError();
+            f = nullptr;
+        }
+        return (PointerGetAttributeFn)f;
+    }();
+    return fn;
+}
+
+PtrKind classify_pointer(const void *p)
+{
+    PtrKind k = { p, 0, nullptr, nullptr };
     cudaPointerAttributes a;
     if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
         cudaGetLastError();
-        return 0;
+        return k;
     }
-    if (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) return -1;
-    return a.type == cudaMemoryTypeHost ? 1 : 0;
+    if (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) { k.kind = -1;  return k; }
+    if (a.type != cudaMemoryTypeHost) return k;
+    // extent of the page-locked allocation; without the driver's answer only the byte asked about is vouched for
+    k.kind = 1;
+    k.lo = (const uint8_t *)p;  k.hi = k.lo + 1;
+    if (PointerGetAttributeFn get = pointer_get_attribute()) {
+        CUdeviceptr start = 0;
+        size_t size = 0;
+        if (get(&start, CU_POINTER_ATTRIBUTE_RANGE_START_ADDR, (CUdeviceptr)(uintptr_t)p) == CUDA_SUCCESS &&
+            get(&size, CU_POINTER_ATTRIBUTE_RANGE_SIZE, (CUdeviceptr)(uintptr_t)p) == CUDA_SUCCESS && size) {
+            k.lo = (const uint8_t *)(uintptr_t)start;
+            k.hi = k.lo + size;
+        }
+    }
+    return k;
 }
 
-bool is_pinned(const void *p) { return host_kind(p) == 1; }
+// A session hands in the same few buffers frame after frame (an XShm pool, a buffer pool): the
+// driver is asked once per pointer, not five times per frame. A stale answer is harmless: cudaMemcpy
+// copes with either kind of host memory, and a mapping that is gone fails the zero-copy set-up,
+// which falls back to copies.
+const PtrKind &pointer_kind(b200vc_ctx *c, const void *p)
+{
+    PtrKind &k = c->kinds[((uintptr_t)p >> 4) % (sizeof c->kinds / sizeof c->kinds[0])];
+    if (k.p != p) k = classify_pointer(p);
+    return k;
+}
 
-int collect_slot(b200vc_ctx *c, Slot &s);
+int host_kind(b200vc_ctx *c, const void *p) { return pointer_kind(c, p).kind; }
 
-// Page-lock a caller buffer once (B200VC_FLAG_REGISTER_HOST); false = fall back to staging.
+// the whole buffer [p, p+bytes)
+int host_kind(b200vc_ctx *c, const void *p, size_t bytes)
+{
+    const PtrKind &k = pointer_kind(c, p);
+    if (k.kind != 1) return k.kind;
+    return ((const uint8_t *)p >= k.lo && (const uint8_t *)p + bytes <= k.hi) ? 1 : 0;
+}
+
+void forget_kinds(b200vc_ctx *c)
+{
+    for (PtrKind &k : c->kinds) k = { nullptr, 0, nullptr, nullptr };
+}
+
+// B200VC_FLAG_REGISTER_HOST: page-lock the caller's range [p, p+bytes) once, whole pages; false =
+// fall back to staging. At most kMaxRegistered ranges are kept; the least recently used one is
+// released (after the work in flight has drained) to make room.
+constexpr size_t kMaxRegistered = 16;
+
 bool ensure_registered(b200vc_ctx *c, const void *p, size_t bytes)
 {
-    for (const HostReg &r : c->registered)
-        if (p >= r.base && (const uint8_t *)p + bytes <= (const uint8_t *)r.base + r.bytes) return true;
-    if (c->registered.size() >= 64) return false;
-    if (cudaHostRegister(const_cast<void *>(p), bytes, cudaHostRegisterDefault) != cudaSuccess) {
+    const uint8_t *lo = (const uint8_t *)((uintptr_t)p & ~(uintptr_t)4095);
+    const uint8_t *hi = (const uint8_t *)(((uintptr_t)p + bytes + 4095) & ~(uintptr_t)4095);
+    for (HostReg &r : c->registered)
+        if (lo >= r.base && hi <= r.base + r.bytes) { r.last_use = ++c->reg_clock; return true; }
+    if (c->registered.size() >= kMaxRegistered) {
+        size_t victim = 0;
+        for (size_t i = 1; i < c->registered.size(); i++)
+            if (c->registered[i].last_use < c->registered[victim].last_use) victim = i;
+        cudaStreamSynchronize(c->s_h2d);  cudaStreamSynchronize(c->s_k);  cudaStreamSynchronize(c->s_d2h);
+        cudaHostUnregister(const_cast<uint8_t *>(c->registered[victim].base));
+        cudaGetLastError();
+        c->registered.erase(c->registered.begin() + victim);
+        forget_kinds(c);
+    }
+    cudaError_t e = cudaHostRegister(const_cast<uint8_t *>(lo), (size_t)(hi - lo), cudaHostRegisterDefault);
+    if (e == cudaErrorHostMemoryAlreadyRegistered) {
+        // Buffers that sit next to each other on the heap share their boundary pages, which an earlier
+        // range of ours already holds: merge — release every range of ours that touches this one and
+        // page-lock their union as one piece. (Pages someone else locked stay a failure: a range that is
+        // page-locked only in parts cannot be handed to the copy engine.)
+        cudaGetLastError();
+        bool merged = false;
+        for (size_t i = 0; i < c->registered.size();) {
+            const HostReg r = c->registered[i];
+            if (r.base < hi && lo < r.base + r.bytes) {
+                if (!merged) { cudaStreamSynchronize(c->s_h2d);  cudaStreamSynchronize(c->s_k);  cudaStreamSynchronize(c->s_d2h); }
+                merged = true;
+                cudaHostUnregister(const_cast<uint8_t *>(r.base));
+                cudaGetLastError();
+                lo = std::min(lo, r.base);
+                hi = std::max(hi, r.base + r.bytes);
+                c->registered.erase(c->registered.begin() + i);
+            } else {
+                i++;
+            }
+        }
+        if (merged) {
+            forget_kinds(c);
+            e = cudaHostRegister(const_cast<uint8_t *>(lo), (size_t)(hi - lo), cudaHostRegisterDefault);
+        }
+    }
+    if (e != cudaSuccess) {
         cudaGetLastError();
         return false;
     }
-    c->registered.push_back({ p, bytes });
+    c->registered.push_back({ lo, (size_t)(hi - lo), ++c->reg_clock });
+    forget_kinds(c);
     return true;
 }
 
-int make_tensor_map(b200vc_ctx *c, const void *base, size_t pitch, size_t frame_stride, int n_frames,
-                    CUtensorMap *map)
+// TMA descriptor of a source buffer. A session has two input buffers and a device ring is reused launch
+// after launch, so descriptors are kept (cuTensorMapEncodeTiled costs microseconds on the streaming thread).
+int get_tensor_map(b200vc_ctx *c, const void *base, size_t pitch, size_t frame_stride, int n_frames, const CUtensorMap **out)
 {
+    for (const MapEntry &m : c->maps)
+        if (m.base == base && m.pitch == pitch && m.fstride == frame_stride && m.n_frames == n_frames) { *out = &m.map; return B200VC_OK; }
+    MapEntry e;
+    e.base = base;  e.pitch = pitch;  e.fstride = frame_stride;  e.n_frames = n_frames;
     cuuint64_t dims[3] = { (cuuint64_t)c->cfg.in_w, (cuuint64_t)c->cfg.in_h, (cuuint64_t)n_frames };
     cuuint64_t strides[2] = { (cuuint64_t)pitch, (cuuint64_t)(frame_stride ? frame_stride : pitch * c->cfg.in_h) };
     cuuint32_t box[3] = { (cuuint32_t)c->box_w, (cuuint32_t)c->box_h, 1 };
     cuuint32_t estr[3] = { 1, 1, 1 };
-    CUresult r = c->encode_tiled(map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, const_cast<void *>(base), dims, strides,
+    CUresult r = c->encode_tiled(&e.map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, const_cast<void *>(base), dims, strides,
                                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS)
         return fail(c, B200VC_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    constexpr size_t kMaxMaps = 64;
+    if (c->maps.size() < kMaxMaps) {
+        c->maps.push_back(e);                  // (reserved at create: entries never move)
+        *out = &c->maps.back().map;
+    } else {
+        c->maps[c->next_map] = e;
+        *out = &c->maps[c->next_map].map;
+        c->next_map = (c->next_map + 1) % kMaxMaps;
+    }
     return B200VC_OK;
 }
 
@@ -411,12 +559,14 @@ PlaneSet plane_set(uint8_t *base, const size_t off[3], const size_t pitch[3], si
     return ps;
 }
 
+const RowGate kNoGate = { nullptr, 0, 0, nullptr };
+
 // Enqueue the kernels for n_frames frames on `st`. Input rows [row0,row0+rows) (unscaled path) or
-// whole frames (scaled paths).
+// whole frames (scaled paths). `gate` (one frame only): the frame is still arriving, see RowGate.
 int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_t src_fstride,
                     const uint8_t *d_prev, size_t prev_pitch, size_t prev_fstride,
                     const PlaneSet &out, uint8_t *d_dmg, size_t dmg_fstride,
-                    int row0, int rows, int n_frames, cudaStream_t st)
+                    int row0, int rows, int n_frames, const RowGate &gate, cudaStream_t st)
 {
     const b200vc_config &g = c->cfg;
     const int site = g.chroma_site == B200VC_SITE_H_COSITED ? 1 : 0;
@@ -433,21 +583,21 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         p.out.p[0] += (size_t)row0 * out.pitch[0];
         p.out.p[1] += (size_t)(row0 / 2) * out.pitch[1];
         if (p.out.p[2]) p.out.p[2] += (size_t)(row0 / 2) * out.pitch[2];
-        p.w = g.in_w;  p.h = rows;  p.n_frames = n_frames;  p.mx = c->mx;  p.stream_out = 1;
+        p.w = g.in_w;  p.h = rows;  p.n_frames = n_frames;  p.mx = c->mx;  p.stream_out = 1;  p.gate = gate;
         CU_TRY(c, launch_convert(p, g.out_format, site, st));
         c->stats.kernel_launches += 1;
         return B200VC_OK;
     }
     if (c->path == 1) {
-        CUtensorMap map;
-        int rc = make_tensor_map(c, d_src, src_pitch, src_fstride, n_frames, &map);
+        const CUtensorMap *map = nullptr;
+        int rc = get_tensor_map(c, d_src, src_pitch, src_fstride, n_frames, &map);
         if (rc) return rc;
         if (c->fused2x) {
             Fused2xParams q;
             memset(&q, 0, sizeof q);
             q.out = out;  q.in_w = g.in_w;  q.in_h = g.in_h;  q.inc_y = c->inc_y;  q.inc_c = c->inc_c;
-            q.n_frames = n_frames;  q.mx = c->mx;
-            CU_TRY(c, launch_fused_2x(map, q, g.out_format, site, g.scale_mode == B200VC_SCALE_BOX_2X2, st));
+            q.n_frames = n_frames;  q.mx = c->mx;  q.gate = gate;
+            CU_TRY(c, launch_fused_2x(*map, q, g.out_format, site, g.scale_mode == B200VC_SCALE_BOX_2X2, st));
             c->stats.kernel_launches += 1;
             return B200VC_OK;
         }
@@ -456,25 +606,28 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         p.out = out;  p.ft = c->ft;
         p.in_w = g.in_w;  p.in_h = g.in_h;  p.out_w = g.out_w;  p.out_h = g.out_h;
         p.box_w = c->box_w;  p.box_h = c->box_h;  p.tile_h = c->tile_h;  p.n_frames = n_frames;
-        p.box2x2 = g.scale_mode == B200VC_SCALE_BOX_2X2;  p.mx = c->mx;
+        p.box2x2 = g.scale_mode == B200VC_SCALE_BOX_2X2;  p.mx = c->mx;  p.gate = gate;
         // items per line pair of the window: 8-column items over box_w/4 groups, or one group fewer
         // when a tile's first group is pure halo
         const uint32_t groups_x = (uint32_t)c->box_w / 4;
         const uint32_t items_x = groups_x, items_x1 = std::max(groups_x - 1, 1u);
         p.inv_items_x = (65536u + items_x - 1) / items_x;
         p.inv_items_x1 = (65536u + items_x1 - 1) / items_x1;
-        CU_TRY(c, launch_fused_scale(map, p, g.out_format, site, st));
+        CU_TRY(c, launch_fused_scale(*map, p, g.out_format, site, st));
         c->stats.kernel_launches += 1;
         return B200VC_OK;
     }
-    // two-pass: K1 into the full-size intermediate (always planar), then the plane scaler
+    // two-pass: K1 into the full-size intermediate (always planar), then the plane scaler. The
+    // intermediate belongs to the context, the stream to the caller: whoever used it last, on whatever
+    // stream, must be done before pass 1 overwrites it.
+    if (c->ev_mid_valid) CU_TRY(c, cudaStreamWaitEvent(st, c->ev_mid, 0));
     for (int f0 = 0; f0 < n_frames; f0 += c->mid_frames) {
         const int nf = std::min(c->mid_frames, n_frames - f0);
         ConvertParams p;
         memset(&p, 0, sizeof p);
         p.src = d_src + (size_t)f0 * src_fstride;  p.src_pitch = (long long)src_pitch;  p.src_frame_stride = (long long)src_fstride;
         p.out = plane_set(c->d_mid, c->mid_off, c->mid_pitch, c->mid_size, B200VC_FMT_I420);
-        p.w = g.in_w;  p.h = g.in_h;  p.n_frames = nf;  p.mx = c->mx;
+        p.w = g.in_w;  p.h = g.in_h;  p.n_frames = nf;  p.mx = c->mx;  p.gate = gate;
         CU_TRY(c, launch_convert(p, B200VC_FMT_I420, site, st));
         if (c->plane_tiled) {
             PlaneTileParams t;
@@ -501,6 +654,8 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         CU_TRY(c, launch_plane_scale(q, g.out_format, st));
         c->stats.kernel_launches += 2;
     }
+    CU_TRY(c, cudaEventRecord(c->ev_mid, st));
+    c->ev_mid_valid = true;
     return B200VC_OK;
 }
 
@@ -508,21 +663,28 @@ void destroy_locked(b200vc_ctx *c)
 {
     cudaSetDevice(c->cfg.device);
     if (c->s_h2d) cudaStreamSynchronize(c->s_h2d);
+    for (int i = 1; i < 4; i++) if (c->s_up[i]) { cudaStreamSynchronize(c->s_up[i]);  cudaStreamDestroy(c->s_up[i]); }
     if (c->s_k) cudaStreamSynchronize(c->s_k);
     if (c->s_d2h) cudaStreamSynchronize(c->s_d2h);
+    if (c->ev_mid_valid) cudaEventSynchronize(c->ev_mid);     // a caller's stream may still be in pass 2
     for (Session &s : c->sessions) {
         cudaFree(s.d_in[0]);  cudaFree(s.d_in[1]);
         if (s.ev_kernel) cudaEventDestroy(s.ev_kernel);
     }
     for (Slot &s : c->slots) {
         cudaFree(s.d_out);
+        cudaFree(s.d_flags);
+        if (s.h_flag_src) cudaFreeHost(s.h_flag_src);
         if (s.h_in) cudaFreeHost(s.h_in);
         if (s.h_out) cudaFreeHost(s.h_out);
+        if (s.h_map) cudaFreeHost(s.h_map);
         if (s.done) cudaEventDestroy(s.done);
     }
     for (cudaEvent_t e : c->ev_band_h2d) cudaEventDestroy(e);
     for (cudaEvent_t e : c->ev_band_k) cudaEventDestroy(e);
-    for (const HostReg &r : c->registered) cudaHostUnregister(const_cast<void *>(r.base));
+    if (c->ev_mid) cudaEventDestroy(c->ev_mid);
+    // (a range the caller has unmapped meanwhile makes this fail; there is nothing left to release then)
+    for (const HostReg &r : c->registered) cudaHostUnregister(const_cast<uint8_t *>(r.base));
     cudaFree(c->d_taps);
     cudaFree(c->d_ftaps);
     cudaFree(c->d_ptaps);
@@ -553,27 +715,60 @@ int create_impl(b200vc_ctx *c)
     c->scaling = g.in_w != g.out_w || g.in_h != g.out_h;
     c->mb_w = (g.in_w + 15) / 16;
     c->mb_h = (g.in_h + 15) / 16;
+    c->maps.reserve(64);
 
     CU_TRY(c, cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));
     CU_TRY(c, cudaStreamCreateWithFlags(&c->s_k, cudaStreamNonBlocking));
     CU_TRY(c, cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking));
+    // Row-gated uploads alternate their chunks over two copy streams: consecutive copies of one stream
+    // leave the link idle for ~9 us between them, copies of different streams ~6 us (measured; more streams
+    // do not help further).
+    c->n_up = (g.flags & B200VC_FLAG_ROW_GATE) ? 2 : 1;
+    c->s_up[0] = c->s_h2d;
+    for (int i = 1; i < c->n_up; i++) CU_TRY(c, cudaStreamCreateWithFlags(&c->s_up[i], cudaStreamNonBlocking));
     c->ev_band_h2d.resize(g.n_bands);
     c->ev_band_k.resize(g.n_bands);
     for (int i = 0; i < g.n_bands; i++) {
         CU_TRY(c, cudaEventCreateWithFlags(&c->ev_band_h2d[i], cudaEventDisableTiming));
         CU_TRY(c, cudaEventCreateWithFlags(&c->ev_band_k[i], cudaEventDisableTiming));
     }
-
-    // library-owned device frames: rows padded to 256 bytes
-    c->d_in_pitch = ru((size_t)g.in_w * 4, 256);
-    c->d_in_size = c->d_in_pitch * g.in_h;
+    CU_TRY(c, cudaEventCreateWithFlags(&c->ev_mid, cudaEventDisableTiming));
     {
-        const size_t ch = (size_t)(g.out_h + 1) / 2, cw = (size_t)(g.out_w + 1) / 2;   // chroma lines / samples
-        const size_t yp = ru(g.out_w + 1, 256), cp = g.out_format == B200VC_FMT_NV12 ? yp : ru(cw, 256);
-        c->d_pitch[0] = yp;  c->d_pitch[1] = cp;  c->d_pitch[2] = g.out_format == B200VC_FMT_NV12 ? 0 : cp;
-        c->d_off[0] = 0;  c->d_off[1] = yp * g.out_h;
-        c->d_off[2] = g.out_format == B200VC_FMT_NV12 ? 0 : c->d_off[1] + cp * ch;
-        c->d_out_size = ru(c->d_off[1] + cp * ch * (g.out_format == B200VC_FMT_NV12 ? 1 : 2), 256);
+        // the row gate's flags are written by the copy stream itself where the driver offers that
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuStreamWriteValue32", &fn, cudaEnableDefault, &qres) == cudaSuccess && fn &&
+            qres == cudaDriverEntryPointSuccess)
+            c->write_value = (WriteValue32Fn)fn;
+        else
+            cudaGetLastError();
+    }
+
+    // Library-owned device frames. Input rows are as long as the caller's when that keeps them 16-byte
+    // aligned (a frame with the default pitch then arrives in one linear copy), else padded to 256 bytes.
+    c->d_in_pitch = ((size_t)g.in_w * 4) % 16 == 0 ? (size_t)g.in_w * 4 : ru((size_t)g.in_w * 4, 256);
+    c->d_in_size = ru(c->d_in_pitch * g.in_h, 256);
+    {
+        // Output frame: GstVideoInfo's default layout (b200vc_default_layout) when every pitch and plane
+        // offset of it is a multiple of 16 — 1080p, 1440p, 720p, 4K are — so that a caller frame laid out
+        // that way leaves in one linear copy; else rows padded to 256 bytes, copied plane by plane.
+        size_t off[3], pit[3];
+        const size_t total = b200vc_default_layout(g.out_format, g.out_w, g.out_h, off, pit);
+        const int np = g.out_format == B200VC_FMT_NV12 ? 2 : 3;
+        bool compact = total != 0;
+        for (int i = 0; i < np; i++) compact = compact && pit[i] % 16 == 0 && off[i] % 16 == 0;
+        c->out_compact = compact;
+        if (compact) {
+            for (int i = 0; i < 3; i++) { c->d_off[i] = i < np ? off[i] : 0;  c->d_pitch[i] = i < np ? pit[i] : 0; }
+            c->d_out_size = ru(total, 256);
+        } else {
+            const size_t ch = (size_t)(g.out_h + 1) / 2, cw = (size_t)(g.out_w + 1) / 2;   // chroma lines / samples
+            const size_t yp = ru(g.out_w + 1, 256), cp = g.out_format == B200VC_FMT_NV12 ? yp : ru(cw, 256);
+            c->d_pitch[0] = yp;  c->d_pitch[1] = cp;  c->d_pitch[2] = g.out_format == B200VC_FMT_NV12 ? 0 : cp;
+            c->d_off[0] = 0;  c->d_off[1] = yp * g.out_h;
+            c->d_off[2] = g.out_format == B200VC_FMT_NV12 ? 0 : c->d_off[1] + cp * ch;
+            c->d_out_size = ru(c->d_off[1] + cp * ch * (g.out_format == B200VC_FMT_NV12 ? 1 : 2), 256);
+        }
     }
     const size_t dmg_bytes = ru((size_t)c->mb_w * c->mb_h, 256);
 
@@ -587,6 +782,13 @@ int create_impl(b200vc_ctx *c)
     for (Slot &s : c->slots) {
         CU_TRY(c, cudaMalloc(&s.d_out, c->d_out_size + dmg_bytes));
         s.d_dmg = s.d_out + c->d_out_size;
+        CU_TRY(c, cudaMalloc(&s.d_flags, kMaxChunks * sizeof(uint32_t)));
+        CU_TRY(c, cudaMemset(s.d_flags, 0, kMaxChunks * sizeof(uint32_t)));
+        // pinned and mapped: the gate's time-out word (the last one), which a kernel writes over PCIe only
+        // if a wait gave up
+        CU_TRY(c, cudaHostAlloc(&s.h_flag_src, (kMaxChunks + 1) * sizeof(uint32_t), cudaHostAllocMapped));
+        memset(s.h_flag_src, 0, (kMaxChunks + 1) * sizeof(uint32_t));
+        if (g.flags & B200VC_FLAG_DAMAGE_MAP) CU_TRY(c, cudaMallocHost(&s.h_map, dmg_bytes));
         CU_TRY(c, cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
     }
 
@@ -700,6 +902,15 @@ void copy_rows(uint8_t *dst, size_t dpitch, const uint8_t *src, size_t spitch, s
     for (int r = 0; r < rows; r++) memcpy(dst + r * dpitch, src + r * spitch, bytes);
 }
 
+// One copy between host and device rows: linear when both sides are dense, 2-D otherwise.
+cudaError_t copy_rows_async(void *dst, size_t dpitch, const void *src, size_t spitch, size_t bytes, int rows,
+                            cudaMemcpyKind kind, cudaStream_t st)
+{
+    if (dpitch == bytes && spitch == bytes)
+        return cudaMemcpyAsync(dst, src, bytes * rows, kind, st);
+    return cudaMemcpy2DAsync(dst, dpitch, src, spitch, bytes, rows, kind, st);
+}
+
 int validate_frame(b200vc_ctx *c, const b200vc_frame *f)
 {
     const b200vc_config &g = c->cfg;
@@ -717,42 +928,207 @@ int validate_frame(b200vc_ctx *c, const b200vc_frame *f)
     return B200VC_OK;
 }
 
-// Enqueue one frame on the three streams. bands > 1 pipelines H2D / kernel / D2H inside the frame.
-int submit_locked(b200vc_ctx *c, const b200vc_frame *f, int bands, uint64_t *ticket)
+// Wait for a submitted frame and hand its slot back. The mutex is released while this thread waits
+// for the frame's completion event and while it copies staged output to pageable caller buffers, so
+// other sessions' threads submit and collect meanwhile; the slot stays SLOT_COLLECTING until done.
+int collect_slot(b200vc_ctx *c, Lock &lk, Slot &s)
+{
+    if (s.state == SLOT_FREE) return B200VC_OK;
+    if (s.state != SLOT_BUSY) {                           // another thread is on it: wait for that
+        const uint64_t t = s.ticket;
+        c->cv.wait(lk, [&] { return s.state == SLOT_FREE || s.state == SLOT_BUSY || s.ticket != t; });
+        if (s.state != SLOT_BUSY || s.ticket != t) return B200VC_OK;
+    }
+    s.state = SLOT_COLLECTING;
+    const b200vc_config &g = c->cfg;
+    lk.unlock();
+    const cudaError_t e = cudaEventSynchronize(s.done);
+    size_t staged = 0;
+    bool timed_out = false;
+    if (e == cudaSuccess) {
+        if (s.gated && s.h_flag_src[kMaxChunks]) { timed_out = true;  s.h_flag_src[kMaxChunks] = 0; }
+        if (s.staged_out) {
+            const int n_planes = g.out_format == B200VC_FMT_NV12 ? 2 : 3;
+            const size_t cs = (size_t)(g.out_w + 1) / 2;
+            const size_t rb[3] = { (size_t)g.out_w, g.out_format == B200VC_FMT_NV12 ? 2 * cs : cs, cs };
+            const int rows[3] = { g.out_h, (g.out_h + 1) / 2, (g.out_h + 1) / 2 };
+            for (int i = 0; i < n_planes; i++) {
+                copy_rows((uint8_t *)s.frame.planes[i], s.frame.pitches[i], s.h_out + c->d_off[i], c->d_pitch[i], rb[i], rows[i]);
+                staged += rb[i] * rows[i];
+            }
+        }
+        if (s.staged_map && s.frame.damage) {
+            memcpy(s.frame.damage, s.h_map, (size_t)c->mb_w * c->mb_h);
+            staged += (size_t)c->mb_w * c->mb_h;
+        }
+    }
+    lk.lock();
+    s.state = SLOT_FREE;
+    c->stats.staged_out_bytes += staged;
+    c->cv.notify_all();
+    if (e != cudaSuccess)
+        return fail(c, B200VC_ERR_CUDA, "waiting for a frame failed: %s", cudaGetErrorString(e));
+    if (timed_out)
+        return fail(c, B200VC_ERR_CUDA, "the row-gated kernel gave up waiting for its frame's copy (a host-to-device copy did not complete)");
+    return B200VC_OK;
+}
+
+int collect_ticket(b200vc_ctx *c, Lock &lk, uint64_t ticket)
+{
+    for (Slot &s : c->slots)
+        if (s.state != SLOT_FREE && s.ticket == ticket) return collect_slot(c, lk, s);
+    return B200VC_OK;   // already collected (its slot was reused or collected before)
+}
+
+// A free slot for a new frame, in ring order; with none free, the oldest frame in flight is collected
+// first (its owner's later collect finds it done).
+int acquire_slot(b200vc_ctx *c, Lock &lk, Slot **out)
+{
+    for (;;) {
+        const int n = (int)c->slots.size();
+        for (int i = 0; i < n; i++) {
+            Slot &s = c->slots[(c->next_slot + i) % n];
+            if (s.state == SLOT_FREE) {
+                c->next_slot = (c->next_slot + i + 1) % n;
+                *out = &s;
+                return B200VC_OK;
+            }
+        }
+        Slot *oldest = nullptr;
+        for (Slot &s : c->slots)
+            if (s.state == SLOT_BUSY && (!oldest || s.ticket < oldest->ticket)) oldest = &s;
+        if (oldest) {
+            const int rc = collect_slot(c, lk, *oldest);
+            if (rc) return rc;
+        } else {
+            c->cv.wait(lk);
+        }
+    }
+}
+
+void release_slot(b200vc_ctx *c, Slot &s)
+{
+    s.state = SLOT_FREE;
+    c->cv.notify_all();
+}
+
+// A frame's rows [row0, row0+rows) from the caller's buffer to the session's device frame on the copy
+// stream; pageable input goes through the slot's pinned staging buffer first (mutex released for that copy).
+int upload_rows(b200vc_ctx *c, Lock &lk, Slot &slot, const b200vc_frame *f, uint8_t *d_cur, bool in_pinned, int row0, int rows,
+                cudaStream_t st)
+{
+    const size_t row_bytes = (size_t)c->cfg.in_w * 4;
+    const uint8_t *hsrc = (const uint8_t *)f->bgrx + (size_t)row0 * f->in_pitch;
+    size_t hpitch = f->in_pitch;
+    if (!in_pinned) {
+        uint8_t *stage = slot.h_in + (size_t)row0 * row_bytes;
+        lk.unlock();
+        copy_rows(stage, row_bytes, hsrc, f->in_pitch, row_bytes, rows);
+        lk.lock();
+        hsrc = stage;
+        hpitch = row_bytes;
+        c->stats.staged_in_bytes += row_bytes * rows;
+    }
+    CU_TRY(c, copy_rows_async(d_cur + (size_t)row0 * c->d_in_pitch, c->d_in_pitch, hsrc, hpitch, row_bytes, rows,
+                              cudaMemcpyHostToDevice, st));
+    c->stats.h2d_bytes += row_bytes * rows;
+    return B200VC_OK;
+}
+
+// Device frame -> host on the D2H stream, rows [pr0, pr0+prs) of plane i counted in that plane's rows.
+int download_plane_rows(b200vc_ctx *c, Slot &slot, const b200vc_frame *f, bool out_pinned, int i, int pr0, int prs, size_t row_bytes)
+{
+    uint8_t *hdst = out_pinned ? (uint8_t *)f->planes[i] + (size_t)pr0 * f->pitches[i]
+                               : slot.h_out + c->d_off[i] + (size_t)pr0 * c->d_pitch[i];
+    const size_t hp = out_pinned ? f->pitches[i] : c->d_pitch[i];
+    CU_TRY(c, copy_rows_async(hdst, hp, slot.d_out + c->d_off[i] + (size_t)pr0 * c->d_pitch[i], c->d_pitch[i], row_bytes, prs,
+                              cudaMemcpyDeviceToHost, c->s_d2h));
+    c->stats.d2h_bytes += row_bytes * prs;
+    return B200VC_OK;
+}
+
+// Enqueue one frame. sync == false: the frame goes up whole, then the kernel, then the planes come
+// back (batches and submit/collect: consecutive frames overlap on the three streams). sync == true
+// (b200vc_convert, one frame, nothing to overlap with): on the unscaled path the frame goes up in bands
+// of rows, each band's kernel launch chained to its copy by an event, and with page-locked output the
+// kernels store the planes into the caller's buffers themselves, so that only the last band's work is
+// left when the transfer ends. Measured on B200 (tools/sync_latency.py, 1080p): every extra piece a
+// host-to-device copy is cut into costs 6-9 us of idle link, a whole frame's kernel only 6 us and its
+// planes 60 us by copy engine or 80 us as the kernel's own stores — so four bands with kernel stores is
+// the optimum (204 us; 233 us unpipelined; the link alone needs 153 us), two bands without them.
+// B200VC_FLAG_ROW_GATE replaces the launch per band by ONE launch whose stripes wait for their chunk's
+// flag (set by the copy stream behind each chunk); it reaches the scaled paths too, but the flag writes
+// make it slower than events on this machine (216 us at its best), so it is not the default.
+int submit_frame(b200vc_ctx *c, Lock &lk, const b200vc_frame *f, bool sync, uint64_t *ticket)
 {
     int rc = validate_frame(c, f);
     if (rc) return rc;
     const b200vc_config &g = c->cfg;
-    Slot &slot = c->slots[c->next_slot];
-    if (slot.busy && (rc = collect_slot(c, slot)) != 0) return rc;
-    c->next_slot = (c->next_slot + 1) % (int)c->slots.size();
-    Session &ss = c->sessions[f->session];
-
     const size_t row_bytes = (size_t)g.in_w * 4;
     const int n_planes = g.out_format == B200VC_FMT_NV12 ? 2 : 3;
     const size_t cs = (size_t)(g.out_w + 1) / 2;           // chroma samples per line
     const size_t out_row_bytes[3] = { (size_t)g.out_w, g.out_format == B200VC_FMT_NV12 ? 2 * cs : cs, cs };
     const int out_rows[3] = { g.out_h, (g.out_h + 1) / 2, (g.out_h + 1) / 2 };
+    const size_t map_bytes = (size_t)c->mb_w * c->mb_h;
 
     // where do the host sides live?
-    if (host_kind(f->bgrx) < 0 || host_kind(f->planes[0]) < 0)
+    if (host_kind(c, f->bgrx) < 0 || host_kind(c, f->planes[0]) < 0)
         return fail(c, B200VC_ERR_INVALID_ARG, "a device pointer was passed to a host-buffer entry point; "
                                                "frames already on the GPU go through b200vc_convert_device");
-    bool in_pinned = is_pinned(f->bgrx);
+    const size_t in_span = f->in_pitch * (g.in_h - 1) + row_bytes;
+    bool in_pinned = host_kind(c, f->bgrx, in_span) == 1;
     if (!in_pinned && (g.flags & B200VC_FLAG_REGISTER_HOST))
-        in_pinned = ensure_registered(c, f->bgrx, f->in_pitch * (g.in_h - 1) + row_bytes);
+        in_pinned = ensure_registered(c, f->bgrx, in_span);
     bool out_pinned = true;
-    for (int i = 0; i < n_planes; i++) {
-        bool pin = is_pinned(f->planes[i]);
-        if (!pin && (g.flags & B200VC_FLAG_REGISTER_HOST))
-            pin = ensure_registered(c, f->planes[i], f->pitches[i] * (out_rows[i] - 1) + out_row_bytes[i]);
-        out_pinned = out_pinned && pin;
+    for (int i = 0; i < n_planes; i++)
+        out_pinned = out_pinned && host_kind(c, f->planes[i], f->pitches[i] * (out_rows[i] - 1) + out_row_bytes[i]) == 1;
+    if (!out_pinned && (g.flags & B200VC_FLAG_REGISTER_HOST)) {
+        // the planes of one buffer share pages: page-lock the range they span as one piece when they are
+        // close together (one allocation), else plane by plane
+        const uint8_t *lo = (const uint8_t *)f->planes[0], *hi = lo;
+        size_t sum = 0;
+        for (int i = 0; i < n_planes; i++) {
+            const uint8_t *p = (const uint8_t *)f->planes[i];
+            const size_t bytes = f->pitches[i] * (out_rows[i] - 1) + out_row_bytes[i];
+            lo = std::min(lo, p);  hi = std::max(hi, p + bytes);  sum += bytes;
+        }
+        if ((size_t)(hi - lo) <= 2 * sum) {
+            out_pinned = ensure_registered(c, lo, (size_t)(hi - lo));
+        } else {
+            out_pinned = true;
+            for (int i = 0; i < n_planes; i++)
+                out_pinned = ensure_registered(c, f->planes[i], f->pitches[i] * (out_rows[i] - 1) + out_row_bytes[i]) && out_pinned;
+        }
     }
-    if (f->damage && !is_pinned(f->damage)) out_pinned = false;
-    if (!in_pinned && !slot.h_in) CU_TRY(c, cudaMallocHost(&slot.h_in, c->d_in_size));
-    if (!out_pinned && !slot.h_out) CU_TRY(c, cudaMallocHost(&slot.h_out, c->d_out_size + ru((size_t)c->mb_w * c->mb_h, 256)));
+    const bool map_pinned = !f->damage || host_kind(c, f->damage, map_bytes) == 1;
 
-    // zero-copy: K1 reads the page-locked frame over PCIe and writes the planes back itself
+    Slot *slot_p = nullptr;
+    if ((rc = acquire_slot(c, lk, &slot_p)) != 0) return rc;
+    Slot &slot = *slot_p;
+    if (!in_pinned && !slot.h_in) CU_TRY(c, cudaMallocHost(&slot.h_in, c->d_in_size));
+    if (!out_pinned && !slot.h_out) CU_TRY(c, cudaMallocHost(&slot.h_out, c->d_out_size));
+    slot.state = SLOT_SUBMITTING;
+    slot.ticket = c->next_ticket++;
+    slot.frame = *f;
+    slot.staged_out = false;
+    slot.staged_map = false;
+    slot.gated = false;
+    if (ticket) *ticket = slot.ticket;
+    // from here on an error hands the slot back
+#define SUBMIT_TRY(expr) do { int rc_ = (expr); if (rc_) { release_slot(c, slot); return rc_; } } while (0)
+#define SUBMIT_CU(call)                                                                                    \
+    do {                                                                                                   \
+        cudaError_t e_ = (call);                                                                           \
+        if (e_ != cudaSuccess) {                                                                           \
+            release_slot(c, slot);                                                                         \
+            return fail(c, e_ == cudaErrorMemoryAllocation ? B200VC_ERR_NOMEM : B200VC_ERR_CUDA,           \
+                        "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__);       \
+        }                                                                                                  \
+    } while (0)
+
+    Session &ss = c->sessions[f->session];
+
+    // B200VC_FLAG_ZERO_COPY: K1 reads the page-locked frame over PCIe and writes the planes back itself
     // (not on contexts that keep previous frames for the damage map: those need the frame in HBM)
     if ((g.flags & B200VC_FLAG_ZERO_COPY) && !(g.flags & B200VC_FLAG_DAMAGE_MAP) && c->path == 0 && in_pinned && out_pinned) {
         void *d_src = nullptr, *d_pl[3] = { nullptr, nullptr, nullptr };
@@ -765,30 +1141,29 @@ int submit_locked(b200vc_ctx *c, const b200vc_frame *f, int bands, uint64_t *tic
             PlaneSet zout;
             for (int i = 0; i < 3; i++) { zout.p[i] = (uint8_t *)d_pl[i];  zout.pitch[i] = i < n_planes ? (long long)f->pitches[i] : 0; }
             zout.frame_stride = 0;
-            rc = enqueue_kernels(c, (const uint8_t *)d_src, f->in_pitch, 0, nullptr, 0, 0, zout, nullptr, 0, 0, g.in_h, 1, c->s_k);
-            if (rc) return rc;
-            CU_TRY(c, cudaEventRecord(slot.done, c->s_k));
+            SUBMIT_TRY(enqueue_kernels(c, (const uint8_t *)d_src, f->in_pitch, 0, nullptr, 0, 0, zout, nullptr, 0, 0, g.in_h, 1, kNoGate, c->s_k));
+            SUBMIT_CU(cudaEventRecord(slot.done, c->s_k));
             c->stats.h2d_bytes += row_bytes * g.in_h;
             for (int i = 0; i < n_planes; i++) c->stats.d2h_bytes += out_row_bytes[i] * out_rows[i];
-            slot.busy = true;  slot.staged_out = false;  slot.frame = *f;  slot.ticket = c->next_ticket++;
-            if (ticket) *ticket = slot.ticket;
             c->stats.frames += 1;
+            slot.state = SLOT_BUSY;
+            c->cv.notify_all();
             return B200VC_OK;
         }
     }
 
-    if (c->path != 0 || bands < 1) bands = 1;
-    bands = std::min(bands, (int)c->ev_band_h2d.size());
-    bands = std::min(bands, std::max(1, c->mb_h));
+    const bool gated = sync && (g.flags & B200VC_FLAG_ROW_GATE) && c->write_value;   // (no stream write in the driver: bands)
 
     uint8_t *d_cur = ss.d_in[ss.cur];
     const uint8_t *d_prev = (f->damage && ss.have_prev) ? ss.d_in[ss.cur ^ 1] : nullptr;
     PlaneSet out = plane_set(slot.d_out, c->d_off, c->d_pitch, 0, g.out_format);
     uint8_t *d_dmg = slot.d_dmg;
 
-    // B200VC_FLAG_ZERO_COPY_OUT: kernels store planes (and map) into the caller's page-locked memory
+    // The kernels store planes (and map) straight into the caller's page-locked memory: on request
+    // (B200VC_FLAG_ZERO_COPY_OUT), and by itself for the row-gated unscaled call, whose 16-byte row-segment
+    // stores cross PCIe well and which has no later frame to hide a device-to-host copy behind.
     bool direct_out = false;
-    if ((g.flags & B200VC_FLAG_ZERO_COPY_OUT) && out_pinned) {
+    if (((g.flags & B200VC_FLAG_ZERO_COPY_OUT) || (sync && c->path == 0)) && out_pinned && map_pinned) {
         void *d_pl[3] = { nullptr, nullptr, nullptr }, *d_map = nullptr;
         bool ok = true;
         for (int i = 0; i < n_planes && ok; i++)
@@ -802,110 +1177,114 @@ int submit_locked(b200vc_ctx *c, const b200vc_frame *f, int bands, uint64_t *tic
         }
     }
 
-    // the copy engine must not overwrite a frame the previous kernel of this session still reads
-    if (ss.ev_valid) CU_TRY(c, cudaStreamWaitEvent(c->s_h2d, ss.ev_kernel, 0));
-    if (f->damage && !d_prev)
-        CU_TRY(c, cudaMemsetAsync(d_dmg, 1, (size_t)c->mb_w * c->mb_h, c->s_k));
+    // pieces of a synchronous frame: as negotiated, or (n_bands 0) what was measured best
+    const int want = !sync ? 1 : c->auto_bands ? (direct_out ? 4 : 2) : g.n_bands;
+    int bands = (sync && !gated && c->path == 0) ? want : 1;                      // launches chained by events
+    bands = std::min(bands, (int)c->ev_band_h2d.size());
+    bands = std::min(bands, std::max(1, c->mb_h));
 
-    const int mb_rows_per_band = (c->mb_h + bands - 1) / bands;
-    for (int b = 0; b < bands; b++) {
-        const int row0 = b * mb_rows_per_band * 16;
-        if (row0 >= g.in_h) break;
-        const int rows = std::min(mb_rows_per_band * 16, g.in_h - row0);
-        // host -> pinned (only for pageable input), then H2D
-        const uint8_t *hsrc = (const uint8_t *)f->bgrx + (size_t)row0 * f->in_pitch;
-        size_t hpitch = f->in_pitch;
-        if (!in_pinned) {
-            copy_rows(slot.h_in + (size_t)row0 * row_bytes, row_bytes, hsrc, f->in_pitch, row_bytes, rows);
-            hsrc = slot.h_in + (size_t)row0 * row_bytes;
-            hpitch = row_bytes;
-            c->stats.staged_in_bytes += row_bytes * rows;
+    // the copy engine must not overwrite a frame the previous kernel of this session still reads
+    if (ss.ev_valid) {
+        SUBMIT_CU(cudaStreamWaitEvent(c->s_h2d, ss.ev_kernel, 0));
+        for (int i = 1; i < c->n_up && gated; i++) SUBMIT_CU(cudaStreamWaitEvent(c->s_up[i], ss.ev_kernel, 0));
+    }
+    if (f->damage && !d_prev)
+        SUBMIT_CU(cudaMemsetAsync(d_dmg, 1, map_bytes, c->s_k));
+
+    if (gated) {
+        // ---- row gate: chunks of rows and their flags on the copy stream, then one launch ----------
+        int chunks = std::min(std::min(want, kMaxChunks), std::max(1, c->mb_h));
+        const int rpc = (int)ru((size_t)(g.in_h + chunks - 1) / chunks, 16);
+        chunks = (g.in_h + rpc - 1) / rpc;
+        if (++slot.epoch == 0) slot.epoch = 1;
+        slot.h_flag_src[kMaxChunks] = 0;
+        for (int k = 0; k < chunks; k++) {
+            const int row0 = k * rpc, rows = std::min(rpc, g.in_h - row0);
+            cudaStream_t up = c->s_up[k % c->n_up];
+            SUBMIT_TRY(upload_rows(c, lk, slot, f, d_cur, in_pinned, row0, rows, up));
+            // (a stream write carries a system-wide fence behind the copy before it; a small copy as the flag
+            // gives a running kernel no such ordering — tried, and it let stripes start early)
+            const CUresult r = c->write_value((CUstream)up, (CUdeviceptr)(uintptr_t)(slot.d_flags + k), slot.epoch, 0);
+            if (r != CUDA_SUCCESS) {
+                release_slot(c, slot);
+                return fail(c, B200VC_ERR_CUDA, "cuStreamWriteValue32 failed with CUresult %d", (int)r);
+            }
         }
-        CU_TRY(c, cudaMemcpy2DAsync(d_cur + (size_t)row0 * c->d_in_pitch, c->d_in_pitch, hsrc, hpitch, row_bytes, rows,
-                                    cudaMemcpyHostToDevice, c->s_h2d));
-        c->stats.h2d_bytes += row_bytes * rows;
-        if (c->path != 0) continue;      // scaled paths launch once, after the whole frame is up
-        CU_TRY(c, cudaEventRecord(c->ev_band_h2d[b], c->s_h2d));
-        CU_TRY(c, cudaStreamWaitEvent(c->s_k, c->ev_band_h2d[b], 0));
-        rc = enqueue_kernels(c, d_cur, c->d_in_pitch, 0, d_prev, c->d_in_pitch, 0, out, d_prev ? d_dmg : nullptr, 0,
-                             row0, rows, 1, c->s_k);
-        if (rc) return rc;
-        if (direct_out) {                               // the kernel's own stores are the D2H traffic
-            for (int i = 0; i < n_planes; i++) c->stats.d2h_bytes += out_row_bytes[i] * (i ? (rows + 1) / 2 : rows);
-            continue;
-        }
-        CU_TRY(c, cudaEventRecord(c->ev_band_k[b], c->s_k));
-        CU_TRY(c, cudaStreamWaitEvent(c->s_d2h, c->ev_band_k[b], 0));
-        // D2H of this band's rows of every plane
-        for (int i = 0; i < n_planes; i++) {
-            const int pr0 = i ? row0 / 2 : row0, prs = i ? (rows + 1) / 2 : rows;
-            uint8_t *hdst = out_pinned ? (uint8_t *)f->planes[i] + (size_t)pr0 * f->pitches[i]
-                                       : slot.h_out + c->d_off[i] + (size_t)pr0 * c->d_pitch[i];
-            const size_t hp = out_pinned ? f->pitches[i] : c->d_pitch[i];
-            CU_TRY(c, cudaMemcpy2DAsync(hdst, hp, slot.d_out + c->d_off[i] + (size_t)pr0 * c->d_pitch[i], c->d_pitch[i],
-                                        out_row_bytes[i], prs, cudaMemcpyDeviceToHost, c->s_d2h));
-            c->stats.d2h_bytes += out_row_bytes[i] * prs;
+        // every copy and every flag is in the queue: the kernel below cannot wait for one that never comes
+        void *d_timeout = nullptr;
+        SUBMIT_CU(cudaHostGetDevicePointer(&d_timeout, slot.h_flag_src + kMaxChunks, 0));
+        const RowGate gate = { slot.d_flags, slot.epoch, rpc, (uint32_t *)d_timeout };
+        slot.gated = true;
+        SUBMIT_TRY(enqueue_kernels(c, d_cur, c->d_in_pitch, 0, d_prev, c->d_in_pitch, 0, out, d_prev ? d_dmg : nullptr, 0,
+                                   0, g.in_h, 1, gate, c->s_k));
+    } else {
+        // ---- bands chained by events (one band: the whole frame) ---------------------------------------
+        const int mb_rows_per_band = (c->mb_h + bands - 1) / bands;
+        for (int b = 0; b < bands; b++) {
+            const int row0 = b * mb_rows_per_band * 16;
+            if (row0 >= g.in_h) break;
+            const int rows = std::min(mb_rows_per_band * 16, g.in_h - row0);
+            SUBMIT_TRY(upload_rows(c, lk, slot, f, d_cur, in_pinned, row0, rows, c->s_h2d));
+            SUBMIT_CU(cudaEventRecord(c->ev_band_h2d[b], c->s_h2d));
+            SUBMIT_CU(cudaStreamWaitEvent(c->s_k, c->ev_band_h2d[b], 0));
+            if (c->path != 0) {
+                SUBMIT_TRY(enqueue_kernels(c, d_cur, c->d_in_pitch, 0, nullptr, 0, 0, out, nullptr, 0, 0, g.in_h, 1, kNoGate, c->s_k));
+                break;
+            }
+            SUBMIT_TRY(enqueue_kernels(c, d_cur, c->d_in_pitch, 0, d_prev, c->d_in_pitch, 0, out, d_prev ? d_dmg : nullptr, 0,
+                                       row0, rows, 1, kNoGate, c->s_k));
+            if (direct_out || bands == 1) continue;
+            // this band's rows of every plane go back while the next band is still coming up
+            SUBMIT_CU(cudaEventRecord(c->ev_band_k[b], c->s_k));
+            SUBMIT_CU(cudaStreamWaitEvent(c->s_d2h, c->ev_band_k[b], 0));
+            for (int i = 0; i < n_planes; i++)
+                SUBMIT_TRY(download_plane_rows(c, slot, f, out_pinned, i, i ? row0 / 2 : row0, i ? (rows + 1) / 2 : rows, out_row_bytes[i]));
         }
     }
-    if (c->path != 0) {
-        CU_TRY(c, cudaEventRecord(c->ev_band_h2d[0], c->s_h2d));
-        CU_TRY(c, cudaStreamWaitEvent(c->s_k, c->ev_band_h2d[0], 0));
-        rc = enqueue_kernels(c, d_cur, c->d_in_pitch, 0, nullptr, 0, 0, out, nullptr, 0, 0, g.in_h, 1, c->s_k);
-        if (rc) return rc;
-        CU_TRY(c, cudaEventRecord(c->ev_band_k[0], c->s_k));
-        CU_TRY(c, cudaStreamWaitEvent(c->s_d2h, c->ev_band_k[0], 0));
-        for (int i = 0; i < n_planes && !direct_out; i++) {
-            uint8_t *hdst = out_pinned ? (uint8_t *)f->planes[i] : slot.h_out + c->d_off[i];
-            const size_t hp = out_pinned ? f->pitches[i] : c->d_pitch[i];
-            CU_TRY(c, cudaMemcpy2DAsync(hdst, hp, slot.d_out + c->d_off[i], c->d_pitch[i], out_row_bytes[i], out_rows[i],
-                                        cudaMemcpyDeviceToHost, c->s_d2h));
-            c->stats.d2h_bytes += out_row_bytes[i] * out_rows[i];
-        }
-    }
-    CU_TRY(c, cudaEventRecord(ss.ev_kernel, c->s_k));
+    SUBMIT_CU(cudaEventRecord(ss.ev_kernel, c->s_k));
     ss.ev_valid = true;
+
+    // ---- the planes (unless the kernels stored them into host memory, or the bands took them) and the map
+    SUBMIT_CU(cudaStreamWaitEvent(c->s_d2h, ss.ev_kernel, 0));      // "done" is recorded on the D2H stream
     if (direct_out) {
-        for (int i = 0; i < n_planes && c->path != 0; i++) c->stats.d2h_bytes += out_row_bytes[i] * out_rows[i];
-        if (f->damage) c->stats.d2h_bytes += (size_t)c->mb_w * c->mb_h;
-        CU_TRY(c, cudaStreamWaitEvent(c->s_d2h, ss.ev_kernel, 0));      // "done" is recorded on the D2H stream
-    } else if (f->damage) {
-        uint8_t *hdst = out_pinned ? f->damage : slot.h_out + c->d_out_size;
-        CU_TRY(c, cudaStreamWaitEvent(c->s_d2h, ss.ev_kernel, 0));
-        CU_TRY(c, cudaMemcpyAsync(hdst, slot.d_dmg, (size_t)c->mb_w * c->mb_h, cudaMemcpyDeviceToHost, c->s_d2h));
-        c->stats.d2h_bytes += (size_t)c->mb_w * c->mb_h;
+        for (int i = 0; i < n_planes; i++) c->stats.d2h_bytes += out_row_bytes[i] * out_rows[i];
+        if (f->damage) c->stats.d2h_bytes += map_bytes;
+    } else {
+        if (gated || bands == 1) {
+            // whole frame: one linear copy when the caller's frame is laid out like the device frame
+            bool same_layout = c->out_compact && out_pinned;
+            for (int i = 0; i < n_planes && same_layout; i++)
+                same_layout = f->pitches[i] == c->d_pitch[i] && (uint8_t *)f->planes[i] == (uint8_t *)f->planes[0] + c->d_off[i];
+            const size_t dense = c->d_off[n_planes - 1] + c->d_pitch[n_planes - 1] * (size_t)(out_rows[n_planes - 1] - 1) + out_row_bytes[n_planes - 1];
+            if (same_layout) {
+                SUBMIT_CU(cudaMemcpyAsync(f->planes[0], slot.d_out, dense, cudaMemcpyDeviceToHost, c->s_d2h));
+                c->stats.d2h_bytes += dense;
+            } else if (!out_pinned) {
+                SUBMIT_CU(cudaMemcpyAsync(slot.h_out, slot.d_out, dense, cudaMemcpyDeviceToHost, c->s_d2h));
+                c->stats.d2h_bytes += dense;
+            } else {
+                for (int i = 0; i < n_planes; i++)
+                    SUBMIT_TRY(download_plane_rows(c, slot, f, true, i, 0, out_rows[i], out_row_bytes[i]));
+            }
+        }
+        if (f->damage) {
+            SUBMIT_CU(cudaMemcpyAsync(map_pinned ? f->damage : slot.h_map, slot.d_dmg, map_bytes, cudaMemcpyDeviceToHost, c->s_d2h));
+            c->stats.d2h_bytes += map_bytes;
+        }
+        slot.staged_out = !out_pinned;
+        slot.staged_map = f->damage && !map_pinned;
     }
-    CU_TRY(c, cudaEventRecord(slot.done, c->s_d2h));
+    SUBMIT_CU(cudaEventRecord(slot.done, c->s_d2h));
+#undef SUBMIT_TRY
+#undef SUBMIT_CU
 
     if (g.flags & B200VC_FLAG_DAMAGE_MAP) {
         ss.cur ^= 1;               // this frame becomes the next one's "previous"; no copy
         ss.have_prev = true;
     }
-    slot.busy = true;
-    slot.staged_out = !out_pinned;
-    slot.frame = *f;
-    slot.ticket = c->next_ticket++;
-    if (ticket) *ticket = slot.ticket;
     c->stats.frames += 1;
-    return B200VC_OK;
-}
-
-int collect_slot(b200vc_ctx *c, Slot &s)
-{
-    if (!s.busy) return B200VC_OK;
-    CU_TRY(c, cudaEventSynchronize(s.done));
-    s.busy = false;
-    if (s.staged_out) {
-        const b200vc_config &g = c->cfg;
-        const int n_planes = g.out_format == B200VC_FMT_NV12 ? 2 : 3;
-        const size_t cs = (size_t)(g.out_w + 1) / 2;
-        const size_t rb[3] = { (size_t)g.out_w, g.out_format == B200VC_FMT_NV12 ? 2 * cs : cs, cs };
-        const int rows[3] = { g.out_h, (g.out_h + 1) / 2, (g.out_h + 1) / 2 };
-        for (int i = 0; i < n_planes; i++) {
-            copy_rows((uint8_t *)s.frame.planes[i], s.frame.pitches[i], s.h_out + c->d_off[i], c->d_pitch[i], rb[i], rows[i]);
-            c->stats.staged_out_bytes += rb[i] * rows[i];
-        }
-        if (s.frame.damage) memcpy(s.frame.damage, s.h_out + c->d_out_size, (size_t)c->mb_w * c->mb_h);
-    }
+    slot.state = SLOT_BUSY;
+    c->cv.notify_all();
     return B200VC_OK;
 }
 
@@ -1025,7 +1404,9 @@ int b200vc_create(const b200vc_config *cfg, b200vc_ctx **out)
     c->cfg = *cfg;
     if (c->cfg.max_sessions == 0) c->cfg.max_sessions = 1;
     if (c->cfg.n_inflight == 0) c->cfg.n_inflight = 3;
-    if (c->cfg.n_bands == 0) c->cfg.n_bands = 2;   // measured best for 1080p (tools/sync_latency.py)
+    // pieces of a synchronous convert: 0 = what was measured best for the frame at hand (submit_frame)
+    c->auto_bands = c->cfg.n_bands == 0;
+    if (c->auto_bands) c->cfg.n_bands = 4;
     memset(&c->stats, 0, sizeof c->stats);
     rc = create_impl(c);
     if (rc) {
@@ -1042,8 +1423,9 @@ int b200vc_destroy(b200vc_ctx *c)
 {
     if (!c) return B200VC_ERR_INVALID_ARG;
     {
-        std::lock_guard<std::mutex> lk(c->mu);
-        for (Slot &s : c->slots) collect_slot(c, s);
+        Lock lk(c->mu);
+        cudaSetDevice(c->cfg.device);
+        for (Slot &s : c->slots) collect_slot(c, lk, s);
         destroy_locked(c);
     }
     delete c;
@@ -1092,27 +1474,31 @@ int b200vc_reset(b200vc_ctx *c, int session)
 int b200vc_submit(b200vc_ctx *c, const b200vc_frame *f, uint64_t *ticket)
 {
     if (!c) return B200VC_ERR_NOT_NEGOTIATED;
-    std::lock_guard<std::mutex> lk(c->mu);
+    Lock lk(c->mu);
     CU_TRY(c, cudaSetDevice(c->cfg.device));
-    return submit_locked(c, f, 1, ticket);
+    return submit_frame(c, lk, f, false, ticket);
 }
 
 int b200vc_collect(b200vc_ctx *c, uint64_t ticket)
 {
     if (!c) return B200VC_ERR_NOT_NEGOTIATED;
-    std::lock_guard<std::mutex> lk(c->mu);
+    Lock lk(c->mu);
     CU_TRY(c, cudaSetDevice(c->cfg.device));
     if (ticket == 0 || ticket >= c->next_ticket) return fail(c, B200VC_ERR_BAD_TICKET, "ticket %llu was never issued", (unsigned long long)ticket);
-    for (Slot &s : c->slots)
-        if (s.busy && s.ticket == ticket) return collect_slot(c, s);
-    return B200VC_OK;   // already collected (its slot was reused or collected before)
+    return collect_ticket(c, lk, ticket);
 }
 
 int b200vc_convert(b200vc_ctx *c, const void *bgrx, size_t in_pitch, void *const planes[3], const size_t pitches[3],
                    uint8_t *damage)
 {
+    return b200vc_convert_session(c, 0, bgrx, in_pitch, planes, pitches, damage);
+}
+
+int b200vc_convert_session(b200vc_ctx *c, int session, const void *bgrx, size_t in_pitch, void *const planes[3],
+                           const size_t pitches[3], uint8_t *damage)
+{
     if (!c) return B200VC_ERR_NOT_NEGOTIATED;
-    std::lock_guard<std::mutex> lk(c->mu);
+    Lock lk(c->mu);
     if (!planes || !pitches) return fail(c, B200VC_ERR_INVALID_ARG, "planes/pitches is NULL");
     CU_TRY(c, cudaSetDevice(c->cfg.device));
     b200vc_frame f;
@@ -1120,25 +1506,25 @@ int b200vc_convert(b200vc_ctx *c, const void *bgrx, size_t in_pitch, void *const
     f.bgrx = bgrx;  f.in_pitch = in_pitch;
     const int np = c->cfg.out_format == B200VC_FMT_NV12 ? 2 : 3;
     for (int i = 0; i < np; i++) { f.planes[i] = planes[i];  f.pitches[i] = pitches[i]; }
-    f.damage = damage;  f.session = 0;
-    int rc = submit_locked(c, &f, c->cfg.n_bands, nullptr);
+    f.damage = damage;  f.session = session;
+    uint64_t ticket = 0;
+    int rc = submit_frame(c, lk, &f, true, &ticket);
     if (rc) return rc;
-    for (Slot &s : c->slots)
-        if ((rc = collect_slot(c, s)) != 0) return rc;
-    return B200VC_OK;
+    return collect_ticket(c, lk, ticket);          // this frame only: other sessions' frames stay in flight
 }
 
 int b200vc_convert_batch(b200vc_ctx *c, const b200vc_frame *frames, int n)
 {
     if (!c) return B200VC_ERR_NOT_NEGOTIATED;
-    std::lock_guard<std::mutex> lk(c->mu);
+    Lock lk(c->mu);
     if (!frames || n < 0) return fail(c, B200VC_ERR_INVALID_ARG, "frames is NULL or n < 0");
     CU_TRY(c, cudaSetDevice(c->cfg.device));
     int rc;
+    std::vector<uint64_t> tickets((size_t)n, 0);
     for (int i = 0; i < n; i++)
-        if ((rc = submit_locked(c, &frames[i], 1, nullptr)) != 0) return rc;
-    for (Slot &s : c->slots)
-        if ((rc = collect_slot(c, s)) != 0) return rc;
+        if ((rc = submit_frame(c, lk, &frames[i], false, &tickets[i])) != 0) return rc;
+    for (int i = 0; i < n; i++)
+        if ((rc = collect_ticket(c, lk, tickets[i])) != 0) return rc;
     return B200VC_OK;
 }
 
@@ -1203,7 +1589,7 @@ int b200vc_convert_device(b200vc_ctx *c, const b200vc_device_frames *d, void *cu
     }
     int rc = enqueue_kernels(c, (const uint8_t *)d->bgrx, d->in_pitch, d->in_frame_stride,
                              (const uint8_t *)d->prev, d->prev_pitch, d->prev_frame_stride, out,
-                             d->prev ? d->damage : nullptr, d->damage_frame_stride, 0, g.in_h, d->n_frames, st);
+                             d->prev ? d->damage : nullptr, d->damage_frame_stride, 0, g.in_h, d->n_frames, kNoGate, st);
     if (rc) return rc;
     c->stats.frames += d->n_frames;
     return B200VC_OK;

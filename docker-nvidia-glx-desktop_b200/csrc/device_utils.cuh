@@ -54,6 +54,74 @@ __device__ __forceinline__ uint32_t ldg_stream_u32(const void *p)
     return r;
 }
 
+// The same loads for a frame that is still being written while the kernel runs (row gate): ordinary
+// coherent loads ordered behind the gate's acquire, where .nc would assume memory that is read-only
+// for the kernel's lifetime.
+__device__ __forceinline__ uint4 ldg_live_v4(const void *p)
+{
+    uint4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+    return r;
+}
+
+__device__ __forceinline__ uint32_t ldg_live_u32(const void *p)
+{
+    uint32_t r;
+    asm volatile("ld.global.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p) : "memory");
+    return r;
+}
+
+__device__ __forceinline__ uint32_t ldg_live_u32_if(const void *p, bool pred)
+{
+    uint32_t r;
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %2, 0;\n\tmov.u32 %0, 0;\n\t"
+                 "@q ld.global.L1::no_allocate.u32 %0, [%1];\n\t}"
+                 : "=r"(r) : "l"(p), "r"((uint32_t)pred) : "memory");
+    return r;
+}
+
+// Row gate: wait until the chunk holding line `last_row` has arrived. Lane 0 of each warp spins (with
+// back-off, so that a thousand waiting warps do not hammer one L2 line); then every thread performs the
+// acquire itself, so that its own later loads are ordered behind it.
+__device__ __forceinline__ uint32_t gate_load(const uint32_t *f)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void gate_spin(const RowGate &g, const uint32_t *f)
+{
+    const long long t0 = clock64();
+    unsigned ns = 64;
+    while (gate_load(f) != g.epoch) {
+        __nanosleep(ns);
+        if (ns < 1024) ns *= 2;
+        if (clock64() - t0 > 6000000000LL) {          // ~3 s at 2 GHz: the copy is not coming
+            *g.timeout = 1u;
+            break;
+        }
+    }
+}
+
+// called by all 32 lanes of a warp
+__device__ __forceinline__ void gate_wait_warp(const RowGate &g, int last_row)
+{
+    const uint32_t *f = g.flags + last_row / g.rows;
+    if (__all_sync(0xffffffffu, gate_load(f) == g.epoch)) return;
+    if ((threadIdx.x & 31) == 0) gate_spin(g, f);
+    __syncwarp();
+    (void)gate_load(f);
+}
+
+// called by one thread (the one that issues a tile's TMA load)
+__device__ __forceinline__ void gate_wait_thread(const RowGate &g, int last_row)
+{
+    const uint32_t *f = g.flags + last_row / g.rows;
+    if (gate_load(f) != g.epoch) gate_spin(g, f);
+}
+
 // predicated 4-byte streaming load (no branch): 0 when pred is false
 __device__ __forceinline__ uint32_t ldg_stream_u32_if(const void *p, bool pred)
 {

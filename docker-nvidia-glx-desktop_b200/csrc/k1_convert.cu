@@ -58,9 +58,14 @@ __device__ __forceinline__ void store16(uint8_t *dst, const uint8_t *src, int va
         store_tail(dst, src, valid);
 }
 
-template <int FMT, int SITE, bool NEG, bool DMG, int HR, bool STREAM>
+// MODE 0: the planes are read again on the GPU (two-pass intermediate): plain stores. MODE 1: final
+// output: streaming stores. MODE 2: final output of a frame that is still arriving (row gate): every
+// stripe first waits for its lines, and the frame is read with coherent loads.
+template <int FMT, int SITE, bool NEG, bool DMG, int HR, int MODE>
 __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertParams p)
 {
+    constexpr bool STREAM = MODE != 0;
+    constexpr bool LIVE = MODE == 2;
     __shared__ __align__(16) WarpStage<HR> s_stage[WARPS];
     constexpr int PAIRS = HR / 2;
 
@@ -70,6 +75,7 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
     const int y0 = blockIdx.y * TH;
     const int frame = blockIdx.z;
     if (x0 >= p.w) return;                                 // warp-uniform: whole warp leaves
+    if (LIVE) gate_wait_warp(p.gate, min(y0 + TH, p.h) - 1);
 
     WarpStage<HR> &st = s_stage[warp];
     const Matrix &m = p.mx;
@@ -104,8 +110,8 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
         if (rows == HR && interior_x) {                    // warp-uniform: straight-line loads
 #pragma unroll
             for (int r = 0; r < HR; r++) {
-                px[r] = ldg_stream_v4(src);
-                hl[r] = SITE == 1 ? ldg_stream_u32_if(src - 4, halo) : 0;
+                px[r] = LIVE ? ldg_live_v4(src) : ldg_stream_v4(src);
+                hl[r] = SITE == 1 ? (LIVE ? ldg_live_u32_if(src - 4, halo) : ldg_stream_u32_if(src - 4, halo)) : 0;
                 if (DMG) {
                     const uint4 q = ldg_stream_v4(prv);
                     diff |= (px[r].x ^ q.x) | (px[r].y ^ q.y) | (px[r].z ^ q.z) | (px[r].w ^ q.w);
@@ -121,19 +127,19 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
                 if (r < rows) {
                     uint4 q = make_uint4(0, 0, 0, 0);
                     if (remain >= 4) {
-                        px[r] = ldg_stream_v4(src);
+                        px[r] = LIVE ? ldg_live_v4(src) : ldg_stream_v4(src);
                         if (DMG) q = ldg_stream_v4(prv);
                     } else if (remain > 0) {               // 1..3 pixels: odd widths and widths % 4 != 0
-                        px[r].x = ldg_stream_u32(src);
-                        if (remain > 1) px[r].y = ldg_stream_u32(src + 4);
-                        if (remain > 2) px[r].z = ldg_stream_u32(src + 8);
+                        px[r].x = LIVE ? ldg_live_u32(src) : ldg_stream_u32(src);
+                        if (remain > 1) px[r].y = LIVE ? ldg_live_u32(src + 4) : ldg_stream_u32(src + 4);
+                        if (remain > 2) px[r].z = LIVE ? ldg_live_u32(src + 8) : ldg_stream_u32(src + 8);
                         if (DMG) {
                             q.x = ldg_stream_u32(prv);
                             if (remain > 1) q.y = ldg_stream_u32(prv + 4);
                             if (remain > 2) q.z = ldg_stream_u32(prv + 8);
                         }
                     }
-                    if (SITE == 1) hl[r] = ldg_stream_u32_if(src - 4, halo);
+                    if (SITE == 1) hl[r] = LIVE ? ldg_live_u32_if(src - 4, halo) : ldg_stream_u32_if(src - 4, halo);
                     if (DMG) diff |= (px[r].x ^ q.x) | (px[r].y ^ q.y) | (px[r].z ^ q.z) | (px[r].w ^ q.w);
                     if (SITE == 0) {                       // odd width: the unpaired last pixel pairs with itself
                         if (remain == 1) px[r].y = px[r].x;
@@ -228,21 +234,22 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
 // 63-96 registers) runs at 0.99 of the copy roofline; 4 lines per step (48-56 registers) at 0.93-0.99.
 constexpr int K1_ROWS_PER_STEP = 8;
 
+template <int FMT, int SITE, bool NEG, bool DMG>
+cudaError_t launch4(const ConvertParams &p, dim3 grid, cudaStream_t st)
+{
+    if (p.gate.flags)
+        k1_convert_kernel<FMT, SITE, NEG, DMG, K1_ROWS_PER_STEP, 2><<<grid, WARPS * 32, 0, st>>>(p);
+    else if (p.stream_out)
+        k1_convert_kernel<FMT, SITE, NEG, DMG, K1_ROWS_PER_STEP, 1><<<grid, WARPS * 32, 0, st>>>(p);
+    else
+        k1_convert_kernel<FMT, SITE, NEG, DMG, K1_ROWS_PER_STEP, 0><<<grid, WARPS * 32, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
 template <int FMT, int SITE, bool NEG>
 cudaError_t launch3(const ConvertParams &p, dim3 grid, cudaStream_t st)
 {
-    if (p.prev && p.damage) {
-        if (p.stream_out)
-            k1_convert_kernel<FMT, SITE, NEG, true, K1_ROWS_PER_STEP, true><<<grid, WARPS * 32, 0, st>>>(p);
-        else
-            k1_convert_kernel<FMT, SITE, NEG, true, K1_ROWS_PER_STEP, false><<<grid, WARPS * 32, 0, st>>>(p);
-    } else {
-        if (p.stream_out)
-            k1_convert_kernel<FMT, SITE, NEG, false, K1_ROWS_PER_STEP, true><<<grid, WARPS * 32, 0, st>>>(p);
-        else
-            k1_convert_kernel<FMT, SITE, NEG, false, K1_ROWS_PER_STEP, false><<<grid, WARPS * 32, 0, st>>>(p);
-    }
-    return cudaGetLastError();
+    return (p.prev && p.damage) ? launch4<FMT, SITE, NEG, true>(p, grid, st) : launch4<FMT, SITE, NEG, false>(p, grid, st);
 }
 
 template <int FMT, int SITE>
@@ -255,7 +262,7 @@ cudaError_t launch2(const ConvertParams &p, dim3 grid, cudaStream_t st)
 
 cudaError_t launch_convert(const ConvertParams &p, int fmt, int site, cudaStream_t st)
 {
-    if (p.w <= 0 || p.h <= 0 || p.n_frames <= 0)
+    if (p.w <= 0 || p.h <= 0 || p.n_frames <= 0 || (p.gate.flags && (p.n_frames != 1 || p.gate.rows <= 0 || !p.gate.timeout)))
         return cudaErrorInvalidValue;
     dim3 grid((p.w + TW * WARPS - 1) / (TW * WARPS), (p.h + TH - 1) / TH, p.n_frames);
     if (fmt == 0)

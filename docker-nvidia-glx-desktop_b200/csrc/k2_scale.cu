@@ -152,8 +152,13 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
     // ---- phase 0: source window origin (host-made, per tile column / tile row), TMA load --------
     const int2 org_x = p.ft.tile_x[blockIdx.x];          // window's frame column (multiple of 4), kfirst
     const int sx0 = org_x.x, kfirst = org_x.y, sy0 = p.ft.tile_y[blockIdx.y];
-    if (tid == 0)
+    if (tid == 0) {
+        if (p.gate.flags) {                               // frame still arriving: wait for the window's last line
+            gate_wait_thread(p.gate, min(max(sy0 + bh, 1), p.in_h) - 1);
+            asm volatile("fence.proxy.async;" ::: "memory");
+        }
         issue_window_load(&s_bar, s_src, &src_map, sx0, sy0, frame, (uint32_t)bw * bh * 4);
+    }
     s_col[tid] = p.ft.col_rec[blockIdx.x * (4 * TW) + tid];               // 4 * TW == 256 == blockDim.x
     if (tid < 3 * TILE_H)
         s_row[tid] = p.ft.row_rec[blockIdx.y * (3 * TILE_H) + tid];
@@ -328,6 +333,10 @@ k2_fused_2x_kernel(const __grid_constant__ CUtensorMap src_map, const Fused2xPar
 #pragma unroll
         for (int t = 0; t < NT; t++) {
             if (ty0 + t * K2X_SRC_H < p.in_h) {
+                if (p.gate.flags) {                       // frame still arriving: wait for the tile's last line
+                    gate_wait_thread(p.gate, min(ty0 + (t + 1) * K2X_SRC_H, p.in_h) - 1);
+                    asm volatile("fence.proxy.async;" ::: "memory");
+                }
                 const uint32_t bar = smem_u32(&s_bar[t]);
                 asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
                              ::"r"(bar), "r"((uint32_t)sizeof(s_tiles[0])) : "memory");

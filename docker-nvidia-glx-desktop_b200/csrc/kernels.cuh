@@ -31,6 +31,19 @@ struct PlaneSet {
     long long frame_stride; // bytes between consecutive frames, same for every plane pointer
 };
 
+// Row gate of the synchronous host path (b200vc_convert): the kernel is launched while its frame is
+// still arriving over PCIe in chunks of `rows` lines; chunk k is complete once flags[k] == epoch (a
+// 32-bit word the copy stream writes behind the chunk's copy). A warp / CTA waits for the chunk that
+// holds the last line it reads, so conversion runs under the transfer and only the last chunk's work
+// is left when the transfer ends. flags == nullptr: no gate (the frame is resident). A wait that
+// sees nothing for seconds gives up, sets *timeout and lets the kernel end (the host reports it).
+struct RowGate {
+    const uint32_t *flags;
+    uint32_t epoch;
+    int rows;
+    uint32_t *timeout;
+};
+
 // K1 (+K3): convert a band of rows of n_frames frames.
 struct ConvertParams {
     const uint8_t *src;  long long src_pitch;  long long src_frame_stride;
@@ -40,6 +53,7 @@ struct ConvertParams {
     int w, h;               // pixels covered by this launch (h = rows of the band, even)
     int n_frames;
     int stream_out;         // 1: the planes are final output (streaming stores); 0: read again on the GPU (two-pass intermediate)
+    RowGate gate;           // n_frames == 1 only
     Matrix mx;
 };
 
@@ -92,6 +106,7 @@ struct FusedScaleParams {
     int box2x2;             // scale_mode == BOX_2X2
     uint32_t inv_items_x;   // ceil(65536 / items per line pair), for box_w/4 and box_w/4 - 1 groups:
     uint32_t inv_items_x1;  // tid / items_x without a division (exact for tid <= 256, up to 64 items)
+    RowGate gate;           // n_frames == 1 only
     Matrix mx;
 };
 
@@ -101,6 +116,7 @@ struct Fused2xParams {
     int in_w, in_h;         // in = 2 * out exactly; in_w % 4 == 0, in_h % 4 == 0
     uint32_t inc_y, inc_c;  // 16.16 horizontal steps of the luma / chroma plane scalers
     int n_frames;
+    RowGate gate;           // n_frames == 1 only
     Matrix mx;
 };
 

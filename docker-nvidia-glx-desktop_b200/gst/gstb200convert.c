@@ -28,16 +28,24 @@ typedef struct {
     GstBuffer *in, *out;
     GstVideoFrame in_frame, out_frame;
     guint64 ticket;
+    guint8 *map;                  /* which of the element's two damage maps this frame writes, or NULL */
 } GstB200Pending;
 
 struct _GstB200Convert {
     GstVideoFilter parent;
     b200vc_ctx *ctx;
     GstAllocator *allocator;      /* page-locked host memory (b200vc_host_alloc) for the output pool */
+    /* properties (object lock); read once per negotiation into the latched copies below */
     gint device_id;
     gboolean damage_map;
     gint n_bands;
     gboolean one_frame_latency;   /* submit frame N, hand out frame N-1: its D2H overlaps frame N's H2D */
+    gboolean register_host;       /* page-lock upstream's buffers on first sight (B200VC_FLAG_REGISTER_HOST) */
+    /* what the context in use was negotiated with: a property set in mid-stream takes effect at the next set_info */
+    gboolean cur_damage_map, cur_one_frame_latency;
+    gint frame_w, frame_h;
+    guint8 *maps[2];              /* page-locked damage maps (b200vc_host_alloc), one per frame that can be in flight */
+    guint next_map;
     GstB200Pending pending;
 };
 
@@ -45,7 +53,7 @@ struct _GstB200Convert {
  * Output buffers come from a GstVideoBufferPool configured with this allocator (decide_allocation), so
  * the planes x264enc reads are page-locked and the library copies device -> host straight into them.
  * The same allocator and a pool are offered upstream (propose_allocation); ximagesrc ignores the offer
- * (it wraps XShm images), which is what B200VC_FLAG_REGISTER_HOST is for. */
+ * (it wraps XShm images), which is what the register-host property (B200VC_FLAG_REGISTER_HOST) is for. */
 typedef struct { GstMemory mem; gpointer data; } GstB200PinnedMemory;
 typedef struct { GstAllocator parent; } GstB200PinnedAllocator;
 typedef struct { GstAllocatorClass parent_class; } GstB200PinnedAllocatorClass;
@@ -102,7 +110,7 @@ G_DEFINE_TYPE(GstB200Convert, gst_b200_convert, GST_TYPE_VIDEO_FILTER)
 GST_DEBUG_CATEGORY_STATIC(b200convert_debug);
 #define GST_CAT_DEFAULT b200convert_debug
 
-enum { PROP_0, PROP_DEVICE_ID, PROP_DAMAGE_MAP, PROP_N_BANDS, PROP_ONE_FRAME_LATENCY };
+enum { PROP_0, PROP_DEVICE_ID, PROP_DAMAGE_MAP, PROP_N_BANDS, PROP_ONE_FRAME_LATENCY, PROP_REGISTER_HOST };
 
 static GstStaticPadTemplate sink_tmpl = GST_STATIC_PAD_TEMPLATE("sink", GST_PAD_SINK, GST_PAD_ALWAYS,
     GST_STATIC_CAPS("video/x-raw, format=(string){BGRx,BGRA,RGBx,RGBA,xRGB,ARGB,xBGR,ABGR}, width=(int)[2,16384], height=(int)[2,16384], "
@@ -169,6 +177,23 @@ static int matrix_of(const GstVideoInfo *i)
     }
 }
 
+/* Dirty macroblocks travel downstream as regions of interest on the output buffer. */
+static void gst_b200_convert_attach_damage(GstB200Convert *self, GstBuffer *out, const guint8 *map)
+{
+    b200vc_rect rects[256];
+    int n = b200vc_damage_to_rects(map, self->frame_w, self->frame_h, rects, 256);
+    for (int i = 0; i < n && i < 256; i++)
+        gst_buffer_add_video_region_of_interest_meta(out, "damage", rects[i].x, rects[i].y, rects[i].w, rects[i].h);
+}
+
+static void gst_b200_convert_free_maps(GstB200Convert *self)
+{
+    for (int i = 0; i < 2; i++) {
+        if (self->maps[i]) b200vc_host_free(self->maps[i]);
+        self->maps[i] = NULL;
+    }
+}
+
 /* One-frame-latency mode: waits for the frame in flight, releases its input and returns its output
  * buffer (transfer full), or NULL if there is none or it failed. */
 static GstBuffer *gst_b200_convert_finish_pending(GstB200Convert *self)
@@ -183,7 +208,10 @@ static GstBuffer *gst_b200_convert_finish_pending(GstB200Convert *self)
     gst_video_frame_unmap(&p->in_frame);
     gst_buffer_unref(p->in);
     out = p->out;
+    if (rc == B200VC_OK && p->map)
+        gst_b200_convert_attach_damage(self, out, p->map);
     p->in = p->out = NULL;
+    p->map = NULL;
     p->valid = FALSE;
     if (rc != B200VC_OK) {
         GST_ELEMENT_ERROR(self, LIBRARY, FAILED, ("b200vc_collect: %s", b200vc_status_string(rc)), ("%s", b200vc_last_error(self->ctx)));
@@ -207,8 +235,15 @@ gst_b200_convert_set_info(GstVideoFilter *filter, GstCaps *incaps, GstVideoInfo 
     GstB200Convert *self = GST_B200_CONVERT(filter);
     b200vc_config cfg = { 0 };
     int m, r, s;
+    gboolean want_damage, want_register;
     b200vc_default_colorimetry(GST_VIDEO_INFO_HEIGHT(out), &m, &r, &s);
+    GST_OBJECT_LOCK(self);                       /* property setters run on application threads */
     cfg.device = self->device_id;
+    cfg.n_bands = self->n_bands;
+    want_damage = self->damage_map;
+    want_register = self->register_host;
+    self->cur_one_frame_latency = self->one_frame_latency;
+    GST_OBJECT_UNLOCK(self);
     cfg.in_w = GST_VIDEO_INFO_WIDTH(in);    cfg.in_h = GST_VIDEO_INFO_HEIGHT(in);
     cfg.out_w = GST_VIDEO_INFO_WIDTH(out);  cfg.out_h = GST_VIDEO_INFO_HEIGHT(out);
     cfg.in_format = in_format_of(in);
@@ -219,12 +254,30 @@ gst_b200_convert_set_info(GstVideoFilter *filter, GstCaps *incaps, GstVideoInfo 
               : (out->colorimetry.range == GST_VIDEO_COLOR_RANGE_0_255 ? B200VC_RANGE_FULL : B200VC_RANGE_LIMITED);
     cfg.chroma_site = out->chroma_site == GST_VIDEO_CHROMA_SITE_UNKNOWN ? s
                     : ((out->chroma_site & GST_VIDEO_CHROMA_SITE_H_COSITED) ? B200VC_SITE_H_COSITED : B200VC_SITE_NONE);
-    cfg.flags = (self->damage_map && cfg.in_w == cfg.out_w && cfg.in_h == cfg.out_h) ? B200VC_FLAG_DAMAGE_MAP : 0;
-    cfg.flags |= B200VC_FLAG_REGISTER_HOST;           /* ximagesrc hands out a small pool of XShm images */
-    cfg.n_bands = self->n_bands;
-    cfg.n_inflight = self->one_frame_latency ? 2 : 1;
+    self->cur_damage_map = want_damage && cfg.in_w == cfg.out_w && cfg.in_h == cfg.out_h;   /* the map exists on the unscaled path */
+    cfg.flags = self->cur_damage_map ? B200VC_FLAG_DAMAGE_MAP : 0;
+    /* Off by default: page-locking on first sight is for upstream buffers that come from a small long-lived
+     * pool (ximagesrc with XShm). Buffers malloc'd per frame would stay locked after they are freed, and an
+     * address handed out again would be copied from stale pages; those are staged through a pinned ring. */
+    if (want_register) cfg.flags |= B200VC_FLAG_REGISTER_HOST;
+    cfg.n_inflight = self->cur_one_frame_latency ? 2 : 1;
     gst_b200_convert_drop_pending(self);          /* normally gone already: the CAPS event pushed it */
     if (self->ctx) { b200vc_destroy(self->ctx); self->ctx = NULL; }
+    gst_b200_convert_free_maps(self);
+    self->frame_w = cfg.in_w;  self->frame_h = cfg.in_h;
+    if (self->cur_damage_map) {
+        /* page-locked maps, one per frame that can be in flight: a pageable map would be staged */
+        const size_t mb = (size_t)((cfg.in_w + 15) / 16) * ((cfg.in_h + 15) / 16);
+        for (int i = 0; i < 2; i++) {
+            void *p = NULL;
+            if (b200vc_host_alloc(mb, &p) != B200VC_OK) {
+                GST_ELEMENT_ERROR(self, RESOURCE, NO_SPACE_LEFT, ("page-locked damage map"), ("%s", b200vc_last_error(NULL)));
+                gst_b200_convert_free_maps(self);
+                return FALSE;
+            }
+            self->maps[i] = p;
+        }
+    }
     int rc = b200vc_create(&cfg, &self->ctx);
     if (rc != B200VC_OK) {
         GST_ELEMENT_ERROR(self, LIBRARY, INIT, ("b200vc_create: %s", b200vc_status_string(rc)), ("%s", b200vc_last_error(NULL)));
@@ -243,20 +296,11 @@ gst_b200_convert_transform_frame(GstVideoFilter *filter, GstVideoFrame *in, GstV
                         GST_VIDEO_FRAME_N_PLANES(out) > 2 ? GST_VIDEO_FRAME_PLANE_DATA(out, 2) : NULL };
     size_t pitches[3] = { (size_t)GST_VIDEO_FRAME_PLANE_STRIDE(out, 0), (size_t)GST_VIDEO_FRAME_PLANE_STRIDE(out, 1),
                           GST_VIDEO_FRAME_N_PLANES(out) > 2 ? (size_t)GST_VIDEO_FRAME_PLANE_STRIDE(out, 2) : 0 };
-    guint8 *map = NULL;
-    const gint fw = GST_VIDEO_FRAME_WIDTH(in), fh = GST_VIDEO_FRAME_HEIGHT(in);
-    if (self->damage_map && fw == GST_VIDEO_FRAME_WIDTH(out) && fh == GST_VIDEO_FRAME_HEIGHT(out))
-        map = g_malloc(((fw + 15) / 16) * ((fh + 15) / 16));
+    guint8 *map = self->cur_damage_map ? self->maps[0] : NULL;     /* as negotiated, not as the property reads now */
     int rc = b200vc_convert(self->ctx, GST_VIDEO_FRAME_PLANE_DATA(in, 0), (size_t)GST_VIDEO_FRAME_PLANE_STRIDE(in, 0),
                             planes, pitches, map);
-    if (rc == B200VC_OK && map) {
-        /* dirty macroblocks travel downstream as regions of interest */
-        b200vc_rect rects[256];
-        int n = b200vc_damage_to_rects(map, fw, fh, rects, 256);
-        for (int i = 0; i < n && i < 256; i++)
-            gst_buffer_add_video_region_of_interest_meta(out->buffer, "damage", rects[i].x, rects[i].y, rects[i].w, rects[i].h);
-    }
-    g_free(map);
+    if (rc == B200VC_OK && map)
+        gst_b200_convert_attach_damage(self, out->buffer, map);
     if (rc != B200VC_OK) {
         GST_ELEMENT_ERROR(self, LIBRARY, FAILED, ("b200vc_convert: %s", b200vc_status_string(rc)), ("%s", b200vc_last_error(self->ctx)));
         return GST_FLOW_ERROR;
@@ -277,7 +321,7 @@ static GstFlowReturn gst_b200_convert_generate_output(GstBaseTransform *trans, G
     GstFlowReturn ret;
     b200vc_frame f = { 0 };
     int rc;
-    if (!self->one_frame_latency)
+    if (!self->cur_one_frame_latency)
         return bclass->generate_output(trans, outbuf);
     *outbuf = NULL;
     next.in = trans->queued_buf;
@@ -307,6 +351,11 @@ static GstFlowReturn gst_b200_convert_generate_output(GstBaseTransform *trans, G
     for (guint i = 0; i < GST_VIDEO_FRAME_N_PLANES(&next.out_frame) && i < 3; i++) {
         f.planes[i] = GST_VIDEO_FRAME_PLANE_DATA(&next.out_frame, i);
         f.pitches[i] = (size_t)GST_VIDEO_FRAME_PLANE_STRIDE(&next.out_frame, i);
+    }
+    if (self->cur_damage_map) {                  /* frame N writes one map while frame N-1's is still being read */
+        next.map = self->maps[self->next_map];
+        self->next_map ^= 1;
+        f.damage = next.map;
     }
     rc = b200vc_submit(self->ctx, &f, &next.ticket);
     if (rc != B200VC_OK) {
@@ -350,7 +399,7 @@ static gboolean gst_b200_convert_query(GstBaseTransform *trans, GstPadDirection 
     GstB200Convert *self = GST_B200_CONVERT(trans);
     GstVideoFilter *vf = (GstVideoFilter *)trans;
     gboolean ok = GST_BASE_TRANSFORM_CLASS(gst_b200_convert_parent_class)->query(trans, direction, query);
-    if (ok && self->one_frame_latency && GST_QUERY_TYPE(query) == GST_QUERY_LATENCY && GST_VIDEO_INFO_FPS_N(&vf->in_info) > 0) {
+    if (ok && self->cur_one_frame_latency && GST_QUERY_TYPE(query) == GST_QUERY_LATENCY && GST_VIDEO_INFO_FPS_N(&vf->in_info) > 0) {
         gboolean live;
         GstClockTime min, max;
         const GstClockTime frame = gst_util_uint64_scale_int(GST_SECOND, GST_VIDEO_INFO_FPS_D(&vf->in_info),
@@ -435,6 +484,7 @@ static void gst_b200_convert_finalize(GObject *obj)
     GstB200Convert *self = GST_B200_CONVERT(obj);
     gst_b200_convert_drop_pending(self);
     if (self->ctx) { b200vc_destroy(self->ctx); self->ctx = NULL; }
+    gst_b200_convert_free_maps(self);
     gst_clear_object(&self->allocator);
     G_OBJECT_CLASS(gst_b200_convert_parent_class)->finalize(obj);
 }
@@ -444,6 +494,7 @@ static gboolean gst_b200_convert_stop(GstBaseTransform *trans)
     GstB200Convert *self = GST_B200_CONVERT(trans);
     gst_b200_convert_drop_pending(self);
     if (self->ctx) { b200vc_destroy(self->ctx); self->ctx = NULL; }
+    gst_b200_convert_free_maps(self);
     return TRUE;
 }
 
@@ -456,6 +507,7 @@ static void gst_b200_convert_set_property(GObject *obj, guint id, const GValue *
     case PROP_DAMAGE_MAP: self->damage_map = g_value_get_boolean(v); break;
     case PROP_N_BANDS: self->n_bands = g_value_get_int(v); break;
     case PROP_ONE_FRAME_LATENCY: self->one_frame_latency = g_value_get_boolean(v); break;   /* read at the next negotiation */
+    case PROP_REGISTER_HOST: self->register_host = g_value_get_boolean(v); break;
     default: G_OBJECT_WARN_INVALID_PROPERTY_ID(obj, id, ps);
     }
     GST_OBJECT_UNLOCK(self);
@@ -464,13 +516,16 @@ static void gst_b200_convert_set_property(GObject *obj, guint id, const GValue *
 static void gst_b200_convert_get_property(GObject *obj, guint id, GValue *v, GParamSpec *ps)
 {
     GstB200Convert *self = GST_B200_CONVERT(obj);
+    GST_OBJECT_LOCK(self);
     switch (id) {
     case PROP_DEVICE_ID: g_value_set_int(v, self->device_id); break;
     case PROP_DAMAGE_MAP: g_value_set_boolean(v, self->damage_map); break;
     case PROP_N_BANDS: g_value_set_int(v, self->n_bands); break;
     case PROP_ONE_FRAME_LATENCY: g_value_set_boolean(v, self->one_frame_latency); break;
+    case PROP_REGISTER_HOST: g_value_set_boolean(v, self->register_host); break;
     default: G_OBJECT_WARN_INVALID_PROPERTY_ID(obj, id, ps);
     }
+    GST_OBJECT_UNLOCK(self);
 }
 
 static void gst_b200_convert_class_init(GstB200ConvertClass *klass)
@@ -487,6 +542,9 @@ static void gst_b200_convert_class_init(GstB200ConvertClass *klass)
     g_object_class_install_property(go, PROP_N_BANDS, g_param_spec_int("n-bands", "Bands", "Row bands a frame is pipelined in", 0, 64, 0, G_PARAM_READWRITE));
     g_object_class_install_property(go, PROP_ONE_FRAME_LATENCY, g_param_spec_boolean("one-frame-latency", "One frame of latency",
         "Return frame N-1 while frame N is in flight (copies of consecutive frames overlap)", FALSE, G_PARAM_READWRITE));
+    g_object_class_install_property(go, PROP_REGISTER_HOST, g_param_spec_boolean("register-host", "Page-lock upstream buffers",
+        "Page-lock upstream's buffers on first sight instead of staging them; only for a small long-lived pool (ximagesrc XShm images)",
+        FALSE, G_PARAM_READWRITE));
     gst_element_class_add_static_pad_template(el, &sink_tmpl);
     gst_element_class_add_static_pad_template(el, &src_tmpl);
     gst_element_class_set_static_metadata(el, "B200 BGRx converter/scaler", "Filter/Converter/Video/Scaler",
@@ -513,7 +571,13 @@ static void gst_b200_convert_init(GstB200Convert *self)
     self->damage_map = FALSE;
     self->n_bands = 0;
     self->one_frame_latency = FALSE;
+    self->register_host = FALSE;
+    self->cur_damage_map = self->cur_one_frame_latency = FALSE;
+    self->frame_w = self->frame_h = 0;
+    self->maps[0] = self->maps[1] = NULL;
+    self->next_map = 0;
     self->pending.valid = FALSE;
+    self->pending.map = NULL;
     self->pending.in = self->pending.out = NULL;
 }
 

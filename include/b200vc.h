@@ -18,7 +18,13 @@
  * when no sm_100 device can be used.
  *
  * Threading: a context is internally locked; entry points may be called from any thread (the
- * GStreamer streaming thread is not ours), one frame stream per session index.
+ * GStreamer streaming thread is not ours), one frame stream per session index. The lock covers
+ * booking and enqueueing only: waits for a frame and copies of pageable buffers run outside it.
+ * b200vc_destroy must not run while another call on the context is in progress.
+ *
+ * b200vc_convert_device on the two-pass path (b200vc_info.path == 2) uses an intermediate frame that
+ * belongs to the context; calls on different streams are ordered against each other on the GPU by the
+ * library (each waits for the previous user of the intermediate), so they are safe but do not overlap.
  */
 #ifndef B200VC_H
 #define B200VC_H
@@ -72,8 +78,20 @@ enum { B200VC_IN_BGRX = 0, B200VC_IN_RGBX = 1, B200VC_IN_XRGB = 2, B200VC_IN_XBG
                                              (and the damage map) straight into host memory; the
                                              input still arrives through the copy engine. Saves the
                                              D2H copies and their per-band set-up cost            */
-#define B200VC_FLAG_REGISTER_HOST   0x4u  /* page-lock caller buffers on first sight (XShm pool)
-                                             instead of staging them through a pinned ring        */
+#define B200VC_FLAG_REGISTER_HOST   0x4u  /* page-lock caller buffers on first sight instead of
+                                             staging them through a pinned ring. For buffers that
+                                             come from a small, long-lived pool (ximagesrc's XShm
+                                             images): a range stays page-locked until 16 others
+                                             have been seen or the context is destroyed, so memory
+                                             that is freed and whose address is handed out again
+                                             for something else must NOT be used with this flag
+                                             (the GPU would still copy the old pages)             */
+#define B200VC_FLAG_ROW_GATE        0x40u /* b200vc_convert (the synchronous call) launches ONE
+                                             kernel while the frame is still crossing PCIe in
+                                             n_bands chunks; every stripe waits for the flag the
+                                             copy stream sets behind its chunk. Reaches the scaled
+                                             paths too. Measured slower than the default (a launch
+                                             per band, chained by events) on B200 hosts so far     */
 
 typedef struct b200vc_config {
     int32_t device;        /* CUDA device ordinal                                                  */
@@ -87,7 +105,8 @@ typedef struct b200vc_config {
     uint32_t flags;        /* B200VC_FLAG_*                                                        */
     int32_t max_sessions;  /* independent desktop sessions served by this context (>=1; 0 -> 1)   */
     int32_t n_inflight;    /* frames that may be in flight between submit and collect (0 -> 3)    */
-    int32_t n_bands;       /* row bands a single synchronous convert is pipelined in (0 -> 2)     */
+    int32_t n_bands;       /* bands of rows a synchronous convert is pipelined in (0 -> measured
+                              best: 4 when the kernels store into page-locked planes, else 2)      */
     int32_t in_format;     /* B200VC_IN_* (0 = BGRx)                                               */
 } b200vc_config;
 
@@ -189,10 +208,20 @@ int b200vc_reset(b200vc_ctx *ctx, int session);
 /* ---- the hot path, host buffers ------------------------------------------------------------ */
 
 /* GstVideoFilter::transform_frame -> gst_video_converter_frame: one frame of session 0,
- * synchronous; the planes are complete on return. H2D, kernel and D2H are pipelined over row
- * bands inside the call. damage may be NULL. */
+ * synchronous; the planes are complete on return. damage may be NULL. Inside the call (unscaled
+ * path) the frame goes to the GPU in n_bands bands of rows, each band's kernel launch chained to its
+ * copy, and with page-locked output the kernels store the planes into the caller's buffers
+ * themselves, so that when the last band has crossed PCIe only that band's work is left. The call
+ * waits for its own frame only; other sessions' frames stay in flight. */
 int b200vc_convert(b200vc_ctx *ctx, const void *bgrx, size_t in_pitch,
                    void *const planes[3], const size_t pitches[3], uint8_t *damage_or_null);
+
+/* The same for session `session` (0 .. max_sessions-1): what each of several elements sharing one
+ * context (one GPU, several desktop sessions) calls from its own streaming thread. The context's
+ * lock is held only while work is enqueued, not while a thread waits for its frame or copies
+ * pageable buffers, so the sessions' calls overlap. */
+int b200vc_convert_session(b200vc_ctx *ctx, int session, const void *bgrx, size_t in_pitch,
+                           void *const planes[3], const size_t pitches[3], uint8_t *damage_or_null);
 
 /* One tick of n sessions (config "64 sessions, 8 per GPU"): frames are pipelined against each
  * other (H2D of frame i+1 under kernel and D2H of frame i); all complete on return. */

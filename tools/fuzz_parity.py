@@ -69,10 +69,11 @@ def main():
         scaling = (ow, oh) != (iw, ih)
         flags = int(rng.choice([0, b200vc.FLAG_FORCE_TWO_PASS, b200vc.FLAG_FORCE_GENERIC_FUSED])) if scaling else \
             int(rng.choice([0, b200vc.FLAG_DAMAGE_MAP, b200vc.FLAG_ZERO_COPY, b200vc.FLAG_ZERO_COPY_OUT]))
+        flags |= int(rng.choice([0, b200vc.FLAG_ROW_GATE]))   # how the synchronous call pipelines
         f = rng.integers(0, 256, (ih, iw, 4), dtype=np.uint8)
         try:
             conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=m, range_=rg, chroma_site=site, scale_mode=mode, flags=flags,
-                          in_format=inf, n_bands=int(rng.integers(1, 5)))
+                          in_format=inf, n_bands=int(rng.integers(1, 10)))
             paths[conv.info().path] += 1
             if flags & b200vc.FLAG_DAMAGE_MAP:
                 g = f.copy()

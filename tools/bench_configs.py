@@ -10,6 +10,7 @@ sys.path[:0] = [ROOT, os.path.join(ROOT, "docker-nvidia-glx-desktop_b200")]
 import torch  # noqa: E402
 
 import b200vc  # noqa: E402
+from bench import ClockSampler  # noqa: E402  (every line carries the SM clock and throttle reasons sampled while it ran)
 
 PEAK = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(
     os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
@@ -44,6 +45,8 @@ def e2e(only):
     import ctypes as C
     import time
     conv = b200vc.Converter(0)
+    sampler = ClockSampler(0)
+    sampler.start()
     for name, iw, ih, ow, oh, fmt, m, rg, site, flags, damage in CONFIGS:
         if (only and only not in name) or "two-pass" in name or name.startswith("G "):
             continue
@@ -62,14 +65,17 @@ def e2e(only):
         for k in range(6):
             conv.lib.b200vc_convert_batch(conv.ctx, ticks[k & 1], ns)
         n = max(10, int(2e9 // (ns * in_b)))
+        sampler.mark(name)
         t0 = time.perf_counter()
         for k in range(n):
             rc = conv.lib.b200vc_convert_batch(conv.ctx, ticks[k & 1], ns)
             assert rc == 0
         dt = time.perf_counter() - t0
+        sampler.mark(None)
         fps = n * ns / dt
         print(json.dumps({"config": name, "e2e_fps": round(fps, 1), "h2d_GBs": round(fps * in_b / 1e9, 2),
-                          "d2h_GBs": round(fps * total / 1e9, 2), "frac_of_pcie_gen5_x16_raw_63GBs": round(fps * in_b / 63.02e9, 4)}), flush=True)
+                          "d2h_GBs": round(fps * total / 1e9, 2), "frac_of_pcie_gen5_x16_raw_63GBs": round(fps * in_b / 63.02e9, 4),
+                          "clocks": sampler.record(name)}), flush=True)
         conv.stop()
         h_in.free()
         h_out.free()
@@ -82,6 +88,8 @@ def main():
     only = sys.argv[2] if len(sys.argv) > 2 else None
     conv = b200vc.Converter(0)
     stream = torch.cuda.Stream()
+    sampler = ClockSampler(0)
+    sampler.start()
     for name, iw, ih, ow, oh, fmt, m, rg, site, flags, damage in CONFIGS:
         if only and only not in name:
             continue
@@ -106,12 +114,15 @@ def main():
         with torch.cuda.stream(stream):
             for _ in range(5):
                 conv.convert_device(df, stream.cuda_stream)
+            stream.synchronize()
+            sampler.mark(name)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(stream)
             for _ in range(reps):
                 conv.convert_device(df, stream.cuda_stream)
             e1.record(stream)
         stream.synchronize()
+        sampler.mark(None)
         sec = e0.elapsed_time(e1) / 1e3 / reps
         # single-frame launch (L2-resident, launch-latency bound), reported separately
         df.n_frames = 1
@@ -148,9 +159,11 @@ def main():
         print(json.dumps({"config": name, "per_frame_launch_ring_us": round(per * 1e6, 2) if per else None,
                           "per_frame_launch_ring_fps": round(1 / per, 1) if per else None, "ring_frames": n, "fps": round(n / sec, 1), "ms_per_launch": round(sec * 1e3, 4),
                           "algo_GBs": round(algo * n / sec / 1e9, 1), "frac_of_measured_peak": round(algo * n / sec / 1e9 / PEAK, 4),
-                          "single_frame_us": round(one * 1e6, 2), "path": inf.path, "box": [inf.box_w, inf.box_h]}), flush=True)
+                          "single_frame_us": round(one * 1e6, 2), "path": inf.path, "box": [inf.box_w, inf.box_h],
+                          "tile_h": inf.tile_h, "clocks": sampler.record(name)}), flush=True)
         del d_in, d_out, d_dmg
         torch.cuda.empty_cache()
+    sampler.finish()
     conv.stop()
 
 

@@ -264,7 +264,7 @@ def device_frames(b200vc, d_in, d_out, iw, ih, fmt, ow, oh, n):
     total, off, pit = b200vc.default_layout(fmt, ow, oh)
     df = b200vc.DeviceFrames()
     df.bgrx, df.in_pitch, df.in_frame_stride = d_in.data_ptr(), iw * 4, iw * ih * 4
-    for i in range(2 if fmt else 3):
+    for i in range(2 if fmt == 1 else 3):
         df.planes[i], df.pitches[i] = d_out.data_ptr() + off[i], pit[i]
     df.out_frame_stride, df.n_frames = total, n
     return df

@@ -20,12 +20,12 @@ LIB_PATH = os.environ.get("B200VC_LIB") or os.path.join(_HERE, "libb200vc.so")  
 
 OK = 0
 ERR_INVALID_ARG, ERR_UNSUPPORTED, ERR_NOT_NEGOTIATED, ERR_CUDA, ERR_NO_DEVICE, ERR_ALIGNMENT, ERR_NOMEM, ERR_BAD_TICKET = range(1, 9)
-FMT_I420, FMT_NV12 = 0, 1
+FMT_I420, FMT_NV12, FMT_Y42B, FMT_Y444 = 0, 1, 2, 3
 MATRIX_BT601, MATRIX_BT709, MATRIX_BT2020 = 0, 1, 2
 RANGE_LIMITED, RANGE_FULL = 0, 1
-SITE_NONE, SITE_H_COSITED = 0, 1
+SITE_NONE, SITE_H_COSITED, SITE_V_COSITED, SITE_ALT_LINE, SITE_COSITED, SITE_DV = 0, 1, 2, 4, 3, 7
 SCALE_GST_LQ, SCALE_BOX_2X2 = 0, 1
-IN_BGRX, IN_RGBX, IN_XRGB, IN_XBGR = 0, 1, 2, 3
+IN_BGRX, IN_RGBX, IN_XRGB, IN_XBGR, IN_RGB16, IN_BGR16 = 0, 1, 2, 3, 4, 5
 FLAG_DAMAGE_MAP, FLAG_FORCE_TWO_PASS, FLAG_REGISTER_HOST, FLAG_FORCE_GENERIC_FUSED, FLAG_ZERO_COPY, FLAG_ZERO_COPY_OUT = 1, 2, 4, 8, 16, 32
 FLAG_ROW_GATE = 64
 
@@ -224,7 +224,8 @@ class Converter:
     # -- GstVideoFilter::transform_frame ---------------------------------------------------------
     def transform_frame(self, frame: np.ndarray, out: np.ndarray | None = None, pitches=None, damage: bool = False,
                         session: int = 0):
-        """frame: (h, w, 4) uint8 BGRx view (row stride free). Returns (buf, offsets, pitches[, map])."""
+        """frame: (h, w, 4) uint8 pixels of the negotiated in_format ((h, w, 2) for RGB16/BGR16), row stride
+        free. Returns (buf, offsets, pitches[, map])."""
         if not self.ctx:
             raise B200vcError(ERR_NOT_NEGOTIATED, "set_info has not succeeded")
         g = self.cfg
@@ -232,7 +233,8 @@ class Converter:
             total, off, pit = self.out_layout()
         else:
             pit = list(pitches) + [0] * (3 - len(pitches))
-            rows = [g.out_h, (g.out_h + 1) // 2, (g.out_h + 1) // 2]
+            ch = g.out_h if g.out_format >= FMT_Y42B else (g.out_h + 1) // 2
+            rows = [g.out_h, ch, ch]
             off, total = [], 0
             for p in range(2 if g.out_format == FMT_NV12 else 3):
                 off.append(total)
@@ -252,7 +254,7 @@ class Converter:
         f = Frame()
         f.bgrx, f.in_pitch = in_ptr, in_pitch
         for i in range(3):
-            f.planes[i] = (out_ptr + off[i]) if (i < 2 or self.cfg.out_format == FMT_I420) else None
+            f.planes[i] = (out_ptr + off[i]) if (i < 2 or self.cfg.out_format != FMT_NV12) else None
             f.pitches[i] = pit[i]
         f.damage, f.session = damage_ptr, session
         return f

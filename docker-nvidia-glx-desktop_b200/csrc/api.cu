@@ -91,6 +91,13 @@ struct b200vc_ctx {
     size_t d_off[3] = { 0, 0, 0 }, d_pitch[3] = { 0, 0, 0 }, d_out_size = 0;
     bool out_compact = false;                  // device output frame = b200vc_default_layout: a contiguous caller frame leaves in one copy
     int mb_w = 0, mb_h = 0;
+    // by format: bytes of an input row; planes, bytes per row and rows of each output plane; chroma plane
+    // dimensions of the input-sized intermediate and of the output; lines per chroma line (band arithmetic)
+    size_t row_bytes = 0;
+    int n_planes = 3, vsub = 2;
+    size_t prow_bytes[3] = { 0, 0, 0 };
+    int prows[3] = { 0, 0, 0 };
+    int cw_in = 0, ch_in = 0, cw_out = 0, ch_out = 0;
 
     std::vector<Session> sessions;
     std::vector<Slot> slots;
@@ -223,7 +230,7 @@ inline int tile_org_y(const std::vector<Tap> &vy, const std::vector<Tap> &vc, in
 void build_fused_taps(const b200vc_config &c, const std::vector<Tap> &hy, const std::vector<Tap> &vy,
                       const std::vector<Tap> &hc, const std::vector<Tap> &vc, int tile_h, int box_w, FusedTapBlob &o)
 {
-    const int site = c.chroma_site == B200VC_SITE_H_COSITED ? 1 : 0;
+    const int site = (c.chroma_site & B200VC_SITE_H_COSITED) ? 1 : 0;
     const int tiles_x = (c.out_w + K2_TILE_W - 1) / K2_TILE_W, tiles_y = (c.out_h + tile_h - 1) / tile_h;
     const int cw_out = (c.out_w + 1) / 2, ch_out = (c.out_h + 1) / 2;          // odd frames: chroma planes round up
     auto pad4 = [&] { while (o.w.size() % 4) o.w.push_back(0u); };
@@ -325,7 +332,7 @@ void build_plane_tile_taps(const std::vector<Tap> &th, const std::vector<Tap> &t
 void fused_box(const b200vc_config &c, const std::vector<Tap> &hy, const std::vector<Tap> &vy,
                const std::vector<Tap> &hc, const std::vector<Tap> &vc, int tile_h, int &box_w, int &box_h)
 {
-    const int site = c.chroma_site == B200VC_SITE_H_COSITED ? 1 : 0;
+    const int site = (c.chroma_site & B200VC_SITE_H_COSITED) ? 1 : 0;
     box_w = box_h = 0;
     for (int x0 = 0; x0 < c.out_w; x0 += K2_TILE_W) {
         const int x1 = std::min(x0 + K2_TILE_W, c.out_w) - 1;
@@ -367,16 +374,16 @@ int check_config(const b200vc_config *c, std::string *why)
     if (c->scale_mode == B200VC_SCALE_BOX_2X2 && ((c->in_w | c->in_h | c->out_w | c->out_h) & 1) &&
         (c->in_w != c->out_w || c->in_h != c->out_h))
         return bad(B200VC_ERR_UNSUPPORTED, "BOX_2X2 needs even widths and heights");
-    if (c->out_format != B200VC_FMT_I420 && c->out_format != B200VC_FMT_NV12)
-        return bad(B200VC_ERR_UNSUPPORTED, "output format must be I420 or NV12");
-    if (c->in_format < B200VC_IN_BGRX || c->in_format > B200VC_IN_XBGR)
-        return bad(B200VC_ERR_UNSUPPORTED, "input format must be BGRx/BGRA, RGBx/RGBA, xRGB/ARGB or xBGR/ABGR");
+    if (c->out_format < B200VC_FMT_I420 || c->out_format > B200VC_FMT_Y444)
+        return bad(B200VC_ERR_UNSUPPORTED, "output format must be I420, NV12, Y42B or Y444");
+    if (c->in_format < B200VC_IN_BGRX || c->in_format > B200VC_IN_BGR16)
+        return bad(B200VC_ERR_UNSUPPORTED, "input format must be BGRx/BGRA, RGBx/RGBA, xRGB/ARGB, xBGR/ABGR, RGB16 or BGR16");
     if (c->matrix < B200VC_MATRIX_BT601 || c->matrix > B200VC_MATRIX_BT2020)
         return bad(B200VC_ERR_UNSUPPORTED, "colorimetry matrix must be bt601, bt709 or bt2020");
     if (c->range != B200VC_RANGE_LIMITED && c->range != B200VC_RANGE_FULL)
         return bad(B200VC_ERR_UNSUPPORTED, "range must be limited (16-235) or full (0-255)");
-    if (c->chroma_site != B200VC_SITE_NONE && c->chroma_site != B200VC_SITE_H_COSITED)
-        return bad(B200VC_ERR_UNSUPPORTED, "chroma-site must be none/jpeg or mpeg2 (h-cosited)");
+    if (c->chroma_site < 0 || c->chroma_site > B200VC_SITE_DV)
+        return bad(B200VC_ERR_UNSUPPORTED, "chroma-site must be a combination of h-cosited, v-cosited and alt-line (jpeg, mpeg2, cosited, dv)");
     if (c->scale_mode != B200VC_SCALE_GST_LQ && c->scale_mode != B200VC_SCALE_BOX_2X2)
         return bad(B200VC_ERR_UNSUPPORTED, "unknown scale mode");
     const bool scaling = c->in_w != c->out_w || c->in_h != c->out_h;
@@ -384,6 +391,8 @@ int check_config(const b200vc_config *c, std::string *why)
         return bad(B200VC_ERR_UNSUPPORTED, "BOX_2X2 needs an exact 2:1 downscale");
     if (scaling && (c->flags & B200VC_FLAG_DAMAGE_MAP))
         return bad(B200VC_ERR_UNSUPPORTED, "the damage map is produced on the unscaled path only");
+    if ((c->flags & B200VC_FLAG_DAMAGE_MAP) && c->out_format > B200VC_FMT_NV12)
+        return bad(B200VC_ERR_UNSUPPORTED, "the damage map is produced with I420 and NV12 output (what the encoders take)");
     if (c->max_sessions < 0 || c->max_sessions > 1024 || c->n_inflight < 0 || c->n_inflight > 64 ||
         c->n_bands < 0 || c->n_bands > 64)
         return bad(B200VC_ERR_INVALID_ARG, "max_sessions/n_inflight/n_bands out of range");
@@ -552,7 +561,7 @@ PlaneSet plane_set(uint8_t *base, const size_t off[3], const size_t pitch[3], si
 {
     PlaneSet ps;
     for (int i = 0; i < 3; i++) {
-        ps.p[i] = (fmt == B200VC_FMT_NV12 && i == 2) ? nullptr : base + off[i];
+        ps.p[i] = i < out_planes(fmt) ? base + off[i] : nullptr;
         ps.pitch[i] = (long long)pitch[i];
     }
     ps.frame_stride = (long long)frame_stride;
@@ -569,7 +578,7 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
                     int row0, int rows, int n_frames, const RowGate &gate, cudaStream_t st)
 {
     const b200vc_config &g = c->cfg;
-    const int site = g.chroma_site == B200VC_SITE_H_COSITED ? 1 : 0;
+    const int site = (g.chroma_site & B200VC_SITE_H_COSITED) ? 1 : 0;
     if (c->path == 0) {
         ConvertParams p;
         memset(&p, 0, sizeof p);
@@ -581,9 +590,10 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         p.mb_w = c->mb_w;
         p.out = out;
         p.out.p[0] += (size_t)row0 * out.pitch[0];
-        p.out.p[1] += (size_t)(row0 / 2) * out.pitch[1];
-        if (p.out.p[2]) p.out.p[2] += (size_t)(row0 / 2) * out.pitch[2];
+        p.out.p[1] += (size_t)(row0 / c->vsub) * out.pitch[1];
+        if (p.out.p[2]) p.out.p[2] += (size_t)(row0 / c->vsub) * out.pitch[2];
         p.w = g.in_w;  p.h = rows;  p.n_frames = n_frames;  p.mx = c->mx;  p.stream_out = 1;  p.gate = gate;
+        p.in16 = in_bytes_per_pixel(g.in_format) == 2;
         CU_TRY(c, launch_convert(p, g.out_format, site, st));
         c->stats.kernel_launches += 1;
         return B200VC_OK;
@@ -626,9 +636,12 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         ConvertParams p;
         memset(&p, 0, sizeof p);
         p.src = d_src + (size_t)f0 * src_fstride;  p.src_pitch = (long long)src_pitch;  p.src_frame_stride = (long long)src_fstride;
-        p.out = plane_set(c->d_mid, c->mid_off, c->mid_pitch, c->mid_size, B200VC_FMT_I420);
+        // (the intermediate has the output's chroma format, planar: NV12 is interleaved by pass 2)
+        const int mid_fmt = g.out_format == B200VC_FMT_NV12 ? B200VC_FMT_I420 : g.out_format;
+        p.out = plane_set(c->d_mid, c->mid_off, c->mid_pitch, c->mid_size, mid_fmt);
         p.w = g.in_w;  p.h = g.in_h;  p.n_frames = nf;  p.mx = c->mx;  p.gate = gate;
-        CU_TRY(c, launch_convert(p, B200VC_FMT_I420, site, st));
+        p.in16 = in_bytes_per_pixel(g.in_format) == 2;
+        CU_TRY(c, launch_convert(p, mid_fmt, site, st));
         if (c->plane_tiled) {
             PlaneTileParams t;
             memset(&t, 0, sizeof t);
@@ -638,7 +651,7 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
             for (int i = 0; i < 3; i++) if (t.out.p[i]) t.out.p[i] += (size_t)f0 * out.frame_stride;
             t.k[0] = c->pt[0];  t.k[1] = c->pt[1];
             t.n_frames = nf;  t.box2x2 = g.scale_mode == B200VC_SCALE_BOX_2X2;
-            CU_TRY(c, launch_plane_tile(t, g.out_format, st));
+            CU_TRY(c, launch_plane_tile(t, g.out_format == B200VC_FMT_NV12 ? 1 : 0, st));   // planar, or interleaving U and V
             c->stats.kernel_launches += 2;
             continue;
         }
@@ -650,8 +663,9 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         for (int i = 0; i < 3; i++) if (q.out.p[i]) q.out.p[i] += (size_t)f0 * out.frame_stride;
         q.tab = c->tab;
         q.in_w = g.in_w;  q.in_h = g.in_h;  q.out_w = g.out_w;  q.out_h = g.out_h;  q.n_frames = nf;
+        q.c_out_w = c->cw_out;  q.c_out_h = c->ch_out;
         q.box2x2 = g.scale_mode == B200VC_SCALE_BOX_2X2;
-        CU_TRY(c, launch_plane_scale(q, g.out_format, st));
+        CU_TRY(c, launch_plane_scale(q, g.out_format == B200VC_FMT_NV12 ? 1 : 0, st));
         c->stats.kernel_launches += 2;
     }
     CU_TRY(c, cudaEventRecord(c->ev_mid, st));
@@ -746,7 +760,15 @@ int create_impl(b200vc_ctx *c)
 
     // Library-owned device frames. Input rows are as long as the caller's when that keeps them 16-byte
     // aligned (a frame with the default pitch then arrives in one linear copy), else padded to 256 bytes.
-    c->d_in_pitch = ((size_t)g.in_w * 4) % 16 == 0 ? (size_t)g.in_w * 4 : ru((size_t)g.in_w * 4, 256);
+    c->row_bytes = (size_t)g.in_w * in_bytes_per_pixel(g.in_format);
+    c->n_planes = out_planes(g.out_format);
+    c->vsub = chroma_vsub(g.out_format);
+    chroma_dims(g.out_format, g.in_w, g.in_h, c->cw_in, c->ch_in);
+    chroma_dims(g.out_format, g.out_w, g.out_h, c->cw_out, c->ch_out);
+    c->prow_bytes[0] = (size_t)g.out_w;  c->prows[0] = g.out_h;
+    c->prow_bytes[1] = g.out_format == B200VC_FMT_NV12 ? 2 * (size_t)c->cw_out : (size_t)c->cw_out;  c->prows[1] = c->ch_out;
+    c->prow_bytes[2] = c->n_planes == 3 ? (size_t)c->cw_out : 0;  c->prows[2] = c->n_planes == 3 ? c->ch_out : 0;
+    c->d_in_pitch = c->row_bytes % 16 == 0 ? c->row_bytes : ru(c->row_bytes, 256);
     c->d_in_size = ru(c->d_in_pitch * g.in_h, 256);
     {
         // Output frame: GstVideoInfo's default layout (b200vc_default_layout) when every pitch and plane
@@ -754,7 +776,7 @@ int create_impl(b200vc_ctx *c)
         // that way leaves in one linear copy; else rows padded to 256 bytes, copied plane by plane.
         size_t off[3], pit[3];
         const size_t total = b200vc_default_layout(g.out_format, g.out_w, g.out_h, off, pit);
-        const int np = g.out_format == B200VC_FMT_NV12 ? 2 : 3;
+        const int np = c->n_planes;
         bool compact = total != 0;
         for (int i = 0; i < np; i++) compact = compact && pit[i] % 16 == 0 && off[i] % 16 == 0;
         c->out_compact = compact;
@@ -762,12 +784,12 @@ int create_impl(b200vc_ctx *c)
             for (int i = 0; i < 3; i++) { c->d_off[i] = i < np ? off[i] : 0;  c->d_pitch[i] = i < np ? pit[i] : 0; }
             c->d_out_size = ru(total, 256);
         } else {
-            const size_t ch = (size_t)(g.out_h + 1) / 2, cw = (size_t)(g.out_w + 1) / 2;   // chroma lines / samples
-            const size_t yp = ru(g.out_w + 1, 256), cp = g.out_format == B200VC_FMT_NV12 ? yp : ru(cw, 256);
-            c->d_pitch[0] = yp;  c->d_pitch[1] = cp;  c->d_pitch[2] = g.out_format == B200VC_FMT_NV12 ? 0 : cp;
+            const size_t ch = (size_t)c->ch_out;                                           // chroma lines
+            const size_t yp = ru(g.out_w + 1, 256), cp = ru(c->prow_bytes[1], 256);
+            c->d_pitch[0] = yp;  c->d_pitch[1] = cp;  c->d_pitch[2] = np == 3 ? cp : 0;
             c->d_off[0] = 0;  c->d_off[1] = yp * g.out_h;
-            c->d_off[2] = g.out_format == B200VC_FMT_NV12 ? 0 : c->d_off[1] + cp * ch;
-            c->d_out_size = ru(c->d_off[1] + cp * ch * (g.out_format == B200VC_FMT_NV12 ? 1 : 2), 256);
+            c->d_off[2] = np == 3 ? c->d_off[1] + cp * ch : 0;
+            c->d_out_size = ru(c->d_off[1] + cp * ch * (np == 3 ? 2 : 1), 256);
         }
     }
     const size_t dmg_bytes = ru((size_t)c->mb_w * c->mb_h, 256);
@@ -800,7 +822,7 @@ int create_impl(b200vc_ctx *c)
         } else {
             build_h_taps(g.in_w, g.out_w, hy);  build_v_taps(g.in_h, g.out_h, vy);
             // chroma planes of odd frames round up, like the intermediate frame's own layout
-            build_h_taps((g.in_w + 1) / 2, (g.out_w + 1) / 2, hc);  build_v_taps((g.in_h + 1) / 2, (g.out_h + 1) / 2, vc);
+            build_h_taps(c->cw_in, c->cw_out, hc);  build_v_taps(c->ch_in, c->ch_out, vc);
         }
         const size_t n = hy.size() + vy.size() + hc.size() + vc.size();       // every size a multiple of 4
         CU_TRY(c, cudaMalloc(&c->d_taps, n * sizeof(Tap)));
@@ -825,7 +847,9 @@ int create_impl(b200vc_ctx *c)
                           c->smem_bytes <= dyn_smem_cap(c);
         // (odd sizes run the general fused kernel; the exact-2:1 kernel needs multiples of 4, BOX even sizes)
         // (the fused kernels scale horizontally first; a build with the other order of the spec takes the two-pass path)
-        c->path = (fits && !(g.flags & B200VC_FLAG_FORCE_TWO_PASS) && B200VC_SPEC_SCALE_H_FIRST) ? 1 : 2;
+        // (and they read 4-byte pixels and make 4:2:0 planes; 16-bit input and Y42B/Y444 output take the two-pass path too)
+        const bool fusable = in_bytes_per_pixel(g.in_format) == 4 && g.out_format <= B200VC_FMT_NV12;
+        c->path = (fits && fusable && !(g.flags & B200VC_FLAG_FORCE_TWO_PASS) && B200VC_SPEC_SCALE_H_FIRST) ? 1 : 2;
         const bool exact2 = g.in_w == 2 * g.out_w && g.in_h == 2 * g.out_h && (g.in_w % 4) == 0 && (g.in_h % 4) == 0;
         c->fused2x = c->path == 1 && exact2 && !(g.flags & B200VC_FLAG_FORCE_GENERIC_FUSED) &&
                      (g.scale_mode == B200VC_SCALE_BOX_2X2 ||
@@ -857,7 +881,7 @@ int create_impl(b200vc_ctx *c)
             c->encode_tiled = (PFN_cuTensorMapEncodeTiled_v12000)fn;
             if (!c->fused2x) CU_TRY(c, fused_scale_prepare((size_t)c->prop.sharedMemPerBlockOptin));
         } else {
-            const size_t yp = ru(g.in_w + 1, 256), cp = ru((g.in_w + 1) / 2, 256), mch = (size_t)(g.in_h + 1) / 2;
+            const size_t yp = ru(g.in_w + 1, 256), cp = ru((size_t)c->cw_in, 256), mch = (size_t)c->ch_in;
             c->mid_pitch[0] = yp;  c->mid_pitch[1] = cp;  c->mid_pitch[2] = cp;
             c->mid_off[0] = 0;  c->mid_off[1] = yp * g.in_h;  c->mid_off[2] = c->mid_off[1] + cp * mch;
             c->mid_size = ru(c->mid_off[2] + cp * mch, 256);
@@ -868,11 +892,11 @@ int create_impl(b200vc_ctx *c)
             std::vector<uint32_t> w;
             size_t o0[4], o1[4];
             build_plane_tile_taps(hy, vy, g.in_h, g.out_w, g.out_h, c->pt[0], w, o0);
-            build_plane_tile_taps(hc, vc, (g.in_h + 1) / 2, (g.out_w + 1) / 2, (g.out_h + 1) / 2, c->pt[1], w, o1);
+            build_plane_tile_taps(hc, vc, c->ch_in, c->cw_out, c->ch_out, c->pt[1], w, o1);
             PlaneTileParams probe;
             memset(&probe, 0, sizeof probe);
             probe.k[0] = c->pt[0];  probe.k[1] = c->pt[1];
-            const size_t pt_smem = plane_tile_smem_bytes(probe, g.out_format);
+            const size_t pt_smem = plane_tile_smem_bytes(probe, g.out_format == B200VC_FMT_NV12 ? 1 : 0);
             if (pt_smem <= 64 * 1024) {
                 CU_TRY(c, cudaMalloc(&c->d_ptaps, w.size() * sizeof(uint32_t)));
                 CU_TRY(c, cudaMemcpy(c->d_ptaps, w.data(), w.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
@@ -914,15 +938,15 @@ cudaError_t copy_rows_async(void *dst, size_t dpitch, const void *src, size_t sp
 int validate_frame(b200vc_ctx *c, const b200vc_frame *f)
 {
     const b200vc_config &g = c->cfg;
-    if (!f || !f->bgrx || !f->planes[0] || !f->planes[1] || (g.out_format == B200VC_FMT_I420 && !f->planes[2]))
+    if (!f || !f->bgrx || !f->planes[0] || !f->planes[1] || (c->n_planes == 3 && !f->planes[2]))
         return fail(c, B200VC_ERR_INVALID_ARG, "frame, input or plane pointer is NULL");
     if (f->session < 0 || f->session >= g.max_sessions)
         return fail(c, B200VC_ERR_INVALID_ARG, "session %d out of range (max_sessions %d)", f->session, g.max_sessions);
-    if (f->in_pitch < (size_t)g.in_w * 4)
-        return fail(c, B200VC_ERR_INVALID_ARG, "input pitch %zu is smaller than a row (%d bytes)", f->in_pitch, g.in_w * 4);
-    const size_t cs = (size_t)(g.out_w + 1) / 2, cw = g.out_format == B200VC_FMT_NV12 ? 2 * cs : cs;
-    if (f->pitches[0] < (size_t)g.out_w || f->pitches[1] < cw || (g.out_format == B200VC_FMT_I420 && f->pitches[2] < cw))
-        return fail(c, B200VC_ERR_INVALID_ARG, "an output pitch is smaller than its row");
+    if (f->in_pitch < c->row_bytes)
+        return fail(c, B200VC_ERR_INVALID_ARG, "input pitch %zu is smaller than a row (%zu bytes)", f->in_pitch, c->row_bytes);
+    for (int i = 0; i < c->n_planes; i++)
+        if (f->pitches[i] < c->prow_bytes[i])
+            return fail(c, B200VC_ERR_INVALID_ARG, "an output pitch is smaller than its row");
     if (f->damage && !(g.flags & B200VC_FLAG_DAMAGE_MAP))
         return fail(c, B200VC_ERR_INVALID_ARG, "a damage map was requested but the context was created without B200VC_FLAG_DAMAGE_MAP");
     return B200VC_OK;
@@ -940,7 +964,6 @@ int collect_slot(b200vc_ctx *c, Lock &lk, Slot &s)
         if (s.state != SLOT_BUSY || s.ticket != t) return B200VC_OK;
     }
     s.state = SLOT_COLLECTING;
-    const b200vc_config &g = c->cfg;
     lk.unlock();
     const cudaError_t e = cudaEventSynchronize(s.done);
     size_t staged = 0;
@@ -948,13 +971,9 @@ int collect_slot(b200vc_ctx *c, Lock &lk, Slot &s)
     if (e == cudaSuccess) {
         if (s.gated && s.h_flag_src[kMaxChunks]) { timed_out = true;  s.h_flag_src[kMaxChunks] = 0; }
         if (s.staged_out) {
-            const int n_planes = g.out_format == B200VC_FMT_NV12 ? 2 : 3;
-            const size_t cs = (size_t)(g.out_w + 1) / 2;
-            const size_t rb[3] = { (size_t)g.out_w, g.out_format == B200VC_FMT_NV12 ? 2 * cs : cs, cs };
-            const int rows[3] = { g.out_h, (g.out_h + 1) / 2, (g.out_h + 1) / 2 };
-            for (int i = 0; i < n_planes; i++) {
-                copy_rows((uint8_t *)s.frame.planes[i], s.frame.pitches[i], s.h_out + c->d_off[i], c->d_pitch[i], rb[i], rows[i]);
-                staged += rb[i] * rows[i];
+            for (int i = 0; i < c->n_planes; i++) {
+                copy_rows((uint8_t *)s.frame.planes[i], s.frame.pitches[i], s.h_out + c->d_off[i], c->d_pitch[i], c->prow_bytes[i], c->prows[i]);
+                staged += c->prow_bytes[i] * c->prows[i];
             }
         }
         if (s.staged_map && s.frame.damage) {
@@ -1017,7 +1036,7 @@ void release_slot(b200vc_ctx *c, Slot &s)
 int upload_rows(b200vc_ctx *c, Lock &lk, Slot &slot, const b200vc_frame *f, uint8_t *d_cur, bool in_pinned, int row0, int rows,
                 cudaStream_t st)
 {
-    const size_t row_bytes = (size_t)c->cfg.in_w * 4;
+    const size_t row_bytes = c->row_bytes;
     const uint8_t *hsrc = (const uint8_t *)f->bgrx + (size_t)row0 * f->in_pitch;
     size_t hpitch = f->in_pitch;
     if (!in_pinned) {
@@ -1064,11 +1083,10 @@ int submit_frame(b200vc_ctx *c, Lock &lk, const b200vc_frame *f, bool sync, uint
     int rc = validate_frame(c, f);
     if (rc) return rc;
     const b200vc_config &g = c->cfg;
-    const size_t row_bytes = (size_t)g.in_w * 4;
-    const int n_planes = g.out_format == B200VC_FMT_NV12 ? 2 : 3;
-    const size_t cs = (size_t)(g.out_w + 1) / 2;           // chroma samples per line
-    const size_t out_row_bytes[3] = { (size_t)g.out_w, g.out_format == B200VC_FMT_NV12 ? 2 * cs : cs, cs };
-    const int out_rows[3] = { g.out_h, (g.out_h + 1) / 2, (g.out_h + 1) / 2 };
+    const size_t row_bytes = c->row_bytes;
+    const int n_planes = c->n_planes;
+    const size_t *out_row_bytes = c->prow_bytes;
+    const int *out_rows = c->prows;
     const size_t map_bytes = (size_t)c->mb_w * c->mb_h;
 
     // where do the host sides live?
@@ -1152,7 +1170,9 @@ int submit_frame(b200vc_ctx *c, Lock &lk, const b200vc_frame *f, bool sync, uint
         }
     }
 
-    const bool gated = sync && (g.flags & B200VC_FLAG_ROW_GATE) && c->write_value;   // (no stream write in the driver: bands)
+    // (no stream write in the driver: bands. The gated kernels read 4-byte pixels and make 4:2:0 planes.)
+    const bool gated = sync && (g.flags & B200VC_FLAG_ROW_GATE) && c->write_value &&
+                       in_bytes_per_pixel(g.in_format) == 4 && g.out_format <= B200VC_FMT_NV12;
 
     uint8_t *d_cur = ss.d_in[ss.cur];
     const uint8_t *d_prev = (f->damage && ss.have_prev) ? ss.d_in[ss.cur ^ 1] : nullptr;
@@ -1238,7 +1258,8 @@ int submit_frame(b200vc_ctx *c, Lock &lk, const b200vc_frame *f, bool sync, uint
             SUBMIT_CU(cudaEventRecord(c->ev_band_k[b], c->s_k));
             SUBMIT_CU(cudaStreamWaitEvent(c->s_d2h, c->ev_band_k[b], 0));
             for (int i = 0; i < n_planes; i++)
-                SUBMIT_TRY(download_plane_rows(c, slot, f, out_pinned, i, i ? row0 / 2 : row0, i ? (rows + 1) / 2 : rows, out_row_bytes[i]));
+                SUBMIT_TRY(download_plane_rows(c, slot, f, out_pinned, i, i ? row0 / c->vsub : row0,
+                                               i ? (rows + c->vsub - 1) / c->vsub : rows, out_row_bytes[i]));
         }
     }
     SUBMIT_CU(cudaEventRecord(ss.ev_kernel, c->s_k));
@@ -1335,6 +1356,17 @@ size_t b200vc_default_layout(int format, int w, int h, size_t offsets[3], size_t
     if (format == B200VC_FMT_NV12) {
         pitches[1] = yp;  offsets[2] = 0;  pitches[2] = 0;
         return offsets[1] + yp * (h2 / 2);
+    }
+    if (format == B200VC_FMT_Y42B) {                       // chroma halved horizontally only; heights as they are
+        const size_t cp = ru(w, 8) / 2;
+        pitches[1] = pitches[2] = cp;
+        offsets[1] = yp * h;  offsets[2] = offsets[1] + cp * h;
+        return offsets[2] + cp * h;
+    }
+    if (format == B200VC_FMT_Y444) {
+        pitches[1] = pitches[2] = yp;
+        offsets[1] = yp * h;  offsets[2] = 2 * yp * h;
+        return 3 * yp * h;
     }
     if (format != B200VC_FMT_I420) return 0;
     const size_t cp = ru(ru(w, 2) / 2, 4);
@@ -1504,8 +1536,7 @@ int b200vc_convert_session(b200vc_ctx *c, int session, const void *bgrx, size_t 
     b200vc_frame f;
     memset(&f, 0, sizeof f);
     f.bgrx = bgrx;  f.in_pitch = in_pitch;
-    const int np = c->cfg.out_format == B200VC_FMT_NV12 ? 2 : 3;
-    for (int i = 0; i < np; i++) { f.planes[i] = planes[i];  f.pitches[i] = pitches[i]; }
+    for (int i = 0; i < c->n_planes; i++) { f.planes[i] = planes[i];  f.pitches[i] = pitches[i]; }
     f.damage = damage;  f.session = session;
     uint64_t ticket = 0;
     int rc = submit_frame(c, lk, &f, true, &ticket);
@@ -1552,19 +1583,18 @@ int b200vc_convert_device(b200vc_ctx *c, const b200vc_device_frames *d, void *cu
     if (!c) return B200VC_ERR_NOT_NEGOTIATED;
     std::lock_guard<std::mutex> lk(c->mu);
     const b200vc_config &g = c->cfg;
-    if (!d || !d->bgrx || !d->planes[0] || !d->planes[1] || (g.out_format == B200VC_FMT_I420 && !d->planes[2]) || d->n_frames < 1)
+    if (!d || !d->bgrx || !d->planes[0] || !d->planes[1] || (c->n_planes == 3 && !d->planes[2]) || d->n_frames < 1)
         return fail(c, B200VC_ERR_INVALID_ARG, "device frame set is NULL, has a NULL plane or n_frames < 1");
     if (d->n_frames > 65535) return fail(c, B200VC_ERR_INVALID_ARG, "at most 65535 frames per launch");
     if (d->damage && (!(g.flags & B200VC_FLAG_DAMAGE_MAP) || c->path != 0))
         return fail(c, B200VC_ERR_INVALID_ARG, "a damage map was requested but the context was created without B200VC_FLAG_DAMAGE_MAP");
-    const int np = g.out_format == B200VC_FMT_NV12 ? 2 : 3;
+    const int np = c->n_planes;
     bool ok = aligned16(d->bgrx) && d->in_pitch % 16 == 0 && d->in_frame_stride % 16 == 0 && d->out_frame_stride % 16 == 0;
     for (int i = 0; i < np; i++) ok = ok && aligned16(d->planes[i]) && d->pitches[i] % 16 == 0;
     if (d->prev) ok = ok && aligned16(d->prev) && d->prev_pitch % 16 == 0 && d->prev_frame_stride % 16 == 0;
     if (!ok) return fail(c, B200VC_ERR_ALIGNMENT, "device pointers, pitches and frame strides must be multiples of 16 bytes");
-    const size_t cs2 = (size_t)(g.out_w + 1) / 2, cw = g.out_format == B200VC_FMT_NV12 ? 2 * cs2 : cs2;
-    if (d->in_pitch < (size_t)g.in_w * 4 || d->pitches[0] < (size_t)g.out_w || d->pitches[1] < cw ||
-        (np == 3 && d->pitches[2] < cw))
+    if (d->in_pitch < c->row_bytes || d->pitches[0] < c->prow_bytes[0] || d->pitches[1] < c->prow_bytes[1] ||
+        (np == 3 && d->pitches[2] < c->prow_bytes[2]))
         return fail(c, B200VC_ERR_INVALID_ARG, "a pitch is smaller than its row");
     if (d->n_frames > 1 && (d->in_frame_stride == 0 || d->out_frame_stride == 0))
         return fail(c, B200VC_ERR_INVALID_ARG, "frame strides are required for n_frames > 1");

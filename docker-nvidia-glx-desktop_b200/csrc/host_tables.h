@@ -31,11 +31,24 @@ inline const int (*matrix_rows(int matrix, int range))[4]
     return k[matrix][range];
 }
 
-// byte position of B, G, R in one pixel, per B200VC_IN_* (unpack_BGRA / _RGBA / _ARGB / _ABGR)
+// byte position of B, G, R in one pixel, per B200VC_IN_* (unpack_BGRA / _RGBA / _ARGB / _ABGR). The 16-bit
+// formats reach the matrix unpacked by the kernel into one word per pixel, low field in byte 0, high field in
+// byte 2: RGB16 then reads like BGRx, BGR16 like RGBx.
 inline const int *byte_pos(int in_format)
 {
-    static const int k[4][3] = { { 0, 1, 2 }, { 2, 1, 0 }, { 3, 2, 1 }, { 1, 2, 3 } };
+    static const int k[6][3] = { { 0, 1, 2 }, { 2, 1, 0 }, { 3, 2, 1 }, { 1, 2, 3 }, { 0, 1, 2 }, { 2, 1, 0 } };
     return k[in_format];
+}
+
+inline int in_bytes_per_pixel(int in_format) { return in_format >= B200VC_IN_RGB16 ? 2 : 4; }
+inline int out_planes(int fmt) { return fmt == B200VC_FMT_NV12 ? 2 : 3; }
+inline int chroma_vsub(int fmt) { return (fmt == B200VC_FMT_I420 || fmt == B200VC_FMT_NV12) ? 2 : 1; }   // lines per chroma line
+inline int chroma_hsub(int fmt) { return fmt == B200VC_FMT_Y444 ? 1 : 2; }                                 // pixels per chroma sample
+// samples per line and lines of one chroma plane of a w x h frame (odd sizes round up, video-info.c)
+inline void chroma_dims(int fmt, int w, int h, int &cw, int &ch)
+{
+    cw = chroma_hsub(fmt) == 2 ? (w + 1) / 2 : w;
+    ch = chroma_vsub(fmt) == 2 ? (h + 1) / 2 : h;
 }
 
 inline uint32_t pack_coef_at(const int pos[3], int cb, int cg, int cr)
@@ -52,7 +65,8 @@ inline Matrix make_matrix(int matrix, int range, int in_format)
     const int *pos = byte_pos(in_format);
     const int rnd = B200VC_SPEC_MATRIX_ROUND ? 128 : 0;
     Matrix r;
-    r.rgb_mask = pack_coef_at(pos, 0xff, 0xff, 0xff);
+    // (damage: the three colour bytes of a 4-byte pixel; every bit of a 16-bit one, compared before unpacking)
+    r.rgb_mask = in_bytes_per_pixel(in_format) == 2 ? 0xffffffffu : pack_coef_at(pos, 0xff, 0xff, 0xff);
     r.cy = pack_coef_at(pos, m[0][2], m[0][1], m[0][0]);
     r.oy = (uint32_t)(m[0][3] + rnd);
     bool neg = false;                      // a +128 coefficient does not fit a signed byte: evaluate negated

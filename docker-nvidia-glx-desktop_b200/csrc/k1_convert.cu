@@ -32,11 +32,37 @@ constexpr int WARPS = K1_WARPS_PER_CTA;  // 4
 constexpr uint32_t FULL = 0xffffffffu;
 
 // HR = lines a warp loads, converts and stores per step (4 or 8); a stripe takes 16 / HR steps.
-template <int HR>
+// FMT as in b200vc.h: 0 I420, 1 NV12 (one chroma row per line pair), 2 Y42B (one per line, half width),
+// 3 Y444 (one per line, full width).
+template <int HR, int FMT>
 struct WarpStage {
+    static constexpr int CROWS = FMT <= 1 ? HR / 2 : HR;
+    static constexpr int CBYTES = FMT == 3 ? 2 * TW : TW;
     uint8_t y[HR][TW];                   // HR x 128 B
-    uint8_t c[HR / 2][TW];               // I420: [0..63] U, [64..127] V; NV12: UVUV..
+    uint8_t c[CROWS][CBYTES];            // planar: U in the first half of a row, V in the second; NV12: UVUV..
 };
+
+// One 5-6-5 pixel (low 16 bits of v) as a 4-byte pixel: low field in byte 0, middle field in byte 1, high
+// field in byte 2 (RGB16 reads like BGRx then, BGR16 like RGBx), each widened to 8 bits the way video-format.c
+// unpacks them: high bits repeated into the low ones (B200VC_SPEC_UNPACK16_REPLICATE; 0: plain shift).
+__device__ __forceinline__ uint32_t unpack565(uint32_t v)
+{
+    uint32_t t = ((v & 0xF800u) << 8) | ((v & 0x07E0u) << 5) | ((v & 0x001Fu) << 3);
+    if (B200VC_SPEC_UNPACK16_REPLICATE) t |= ((t >> 5) & 0x00070007u) | ((t >> 6) & 0x00000300u);
+    return t;
+}
+
+__device__ __forceinline__ uint4 unpack565x4(uint2 raw)
+{
+    return make_uint4(unpack565(raw.x), unpack565(raw.x >> 16), unpack565(raw.y), unpack565(raw.y >> 16));
+}
+
+__device__ __forceinline__ uint32_t ldg_stream_u16(const void *p)
+{
+    uint16_t r;
+    asm volatile("ld.global.nc.L1::no_allocate.u16 %0, [%1];" : "=h"(r) : "l"(p));
+    return r;
+}
 
 __device__ __noinline__ void store_tail(uint8_t *dst, const uint8_t *src, int valid)
 {
@@ -61,13 +87,16 @@ __device__ __forceinline__ void store16(uint8_t *dst, const uint8_t *src, int va
 // MODE 0: the planes are read again on the GPU (two-pass intermediate): plain stores. MODE 1: final
 // output: streaming stores. MODE 2: final output of a frame that is still arriving (row gate): every
 // stripe first waits for its lines, and the frame is read with coherent loads.
-template <int FMT, int SITE, bool NEG, bool DMG, int HR, int MODE>
+// IN16: the source holds 2-byte 5-6-5 pixels (RGB16/BGR16), unpacked in registers right after the load.
+template <int FMT, int SITE, bool NEG, bool DMG, int HR, int MODE, bool IN16>
 __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertParams p)
 {
     constexpr bool STREAM = MODE != 0;
     constexpr bool LIVE = MODE == 2;
-    __shared__ __align__(16) WarpStage<HR> s_stage[WARPS];
+    static_assert(!(LIVE && IN16), "the row gate is built for 4-byte pixels");
+    __shared__ __align__(16) WarpStage<HR, FMT> s_stage[WARPS];
     constexpr int PAIRS = HR / 2;
+    constexpr int BPP = IN16 ? 2 : 4;
 
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -77,12 +106,12 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
     if (x0 >= p.w) return;                                 // warp-uniform: whole warp leaves
     if (LIVE) gate_wait_warp(p.gate, min(y0 + TH, p.h) - 1);
 
-    WarpStage<HR> &st = s_stage[warp];
+    WarpStage<HR, FMT> &st = s_stage[warp];
     const Matrix &m = p.mx;
     const int x = x0 + lane * 4;                           // first pixel of this thread
     const int remain = p.w - x;                            // pixels of this lane inside the frame: <= 0, 1..3, >= 4
     const bool interior_x = x0 + TW <= p.w;                // warp-uniform
-    const bool halo = SITE == 1 && lane == 0 && x0 > 0;    // lane 0 fetches the stripe's left neighbour
+    const bool halo = SITE == 1 && FMT != 3 && lane == 0 && x0 > 0;    // lane 0 fetches the stripe's left neighbour
     // Right frame edge, cosited: the last chroma site (column w-2 of an even width, w-1 of an odd
     // one; w > 2) takes itself as right neighbour (FILT_1_3). (Jpeg siting needs no flag: the edge
     // loader duplicates an unpaired last pixel, and avg2(p, p) = p.)
@@ -91,8 +120,8 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
     const bool edge1 = SITE == 1 && p.w > 2 && remain <= (B200VC_SPEC_COSITED_LAST_1_3 ? 2 : 1);   // site at pixel 0
     const bool edge3 = SITE == 1 && p.w > 2 && remain <= (B200VC_SPEC_COSITED_LAST_1_3 ? 4 : 3);   // site at pixel 2
 
-    const uint8_t *src = p.src + (long long)frame * p.src_frame_stride + (long long)y0 * p.src_pitch + (long long)x * 4;
-    const uint8_t *prv = DMG ? p.prev + (long long)frame * p.prev_frame_stride + (long long)y0 * p.prev_pitch + (long long)x * 4
+    const uint8_t *src = p.src + (long long)frame * p.src_frame_stride + (long long)y0 * p.src_pitch + (long long)x * BPP;
+    const uint8_t *prv = DMG ? p.prev + (long long)frame * p.prev_frame_stride + (long long)y0 * p.prev_pitch + (long long)x * BPP
                              : nullptr;
     const long long fo = (long long)frame * p.out.frame_stride;
     const int seg = lane & 7, gx = x0 + seg * 16;          // this lane's 16-byte segment in the store phase
@@ -110,12 +139,23 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
         if (rows == HR && interior_x) {                    // warp-uniform: straight-line loads
 #pragma unroll
             for (int r = 0; r < HR; r++) {
-                px[r] = LIVE ? ldg_live_v4(src) : ldg_stream_v4(src);
-                hl[r] = SITE == 1 ? (LIVE ? ldg_live_u32_if(src - 4, halo) : ldg_stream_u32_if(src - 4, halo)) : 0;
-                if (DMG) {
-                    const uint4 q = ldg_stream_v4(prv);
-                    diff |= (px[r].x ^ q.x) | (px[r].y ^ q.y) | (px[r].z ^ q.z) | (px[r].w ^ q.w);
-                    prv += p.prev_pitch;
+                if (IN16) {
+                    const uint2 raw = ldg_stream_v2(src);
+                    px[r] = unpack565x4(raw);
+                    hl[r] = (SITE == 1 && FMT != 3 && halo) ? unpack565(ldg_stream_u16(src - 2)) : 0;   // (lane 0 only: one short branch)
+                    if (DMG) {
+                        const uint2 q = ldg_stream_v2(prv);
+                        diff |= (raw.x ^ q.x) | (raw.y ^ q.y);
+                        prv += p.prev_pitch;
+                    }
+                } else {
+                    px[r] = LIVE ? ldg_live_v4(src) : ldg_stream_v4(src);
+                    hl[r] = (SITE == 1 && FMT != 3) ? (LIVE ? ldg_live_u32_if(src - 4, halo) : ldg_stream_u32_if(src - 4, halo)) : 0;
+                    if (DMG) {
+                        const uint4 q = ldg_stream_v4(prv);
+                        diff |= (px[r].x ^ q.x) | (px[r].y ^ q.y) | (px[r].z ^ q.z) | (px[r].w ^ q.w);
+                        prv += p.prev_pitch;
+                    }
                 }
                 src += p.src_pitch;
             }
@@ -124,7 +164,25 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
             for (int r = 0; r < HR; r++) {
                 px[r] = make_uint4(0, 0, 0, 0);            // pixels past the edge: never stored, never damage
                 hl[r] = 0;
-                if (r < rows) {
+                if (r < rows && IN16) {
+                    // pixel by pixel: 2-byte loads are always aligned; raw values side by side for the damage diff
+                    uint32_t v[4] = { 0, 0, 0, 0 }, q[4] = { 0, 0, 0, 0 };
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        if (i < remain) {
+                            v[i] = ldg_stream_u16(src + 2 * i);
+                            if (DMG) q[i] = ldg_stream_u16(prv + 2 * i);
+                        }
+                    }
+                    px[r] = make_uint4(remain > 0 ? unpack565(v[0]) : 0u, remain > 1 ? unpack565(v[1]) : 0u,
+                                       remain > 2 ? unpack565(v[2]) : 0u, remain > 3 ? unpack565(v[3]) : 0u);
+                    if (SITE == 1 && FMT != 3 && halo) hl[r] = unpack565(ldg_stream_u16(src - 2));
+                    if (DMG) diff |= (v[0] ^ q[0]) | (v[1] ^ q[1]) | (v[2] ^ q[2]) | (v[3] ^ q[3]);
+                    if (SITE == 0) {                       // odd width: the unpaired last pixel pairs with itself
+                        if (remain == 1) px[r].y = px[r].x;
+                        if (remain == 3) px[r].w = px[r].z;
+                    }
+                } else if (r < rows) {
                     uint4 q = make_uint4(0, 0, 0, 0);
                     if (remain >= 4) {
                         px[r] = LIVE ? ldg_live_v4(src) : ldg_stream_v4(src);
@@ -139,7 +197,7 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
                             if (remain > 2) q.z = ldg_stream_u32(prv + 8);
                         }
                     }
-                    if (SITE == 1) hl[r] = LIVE ? ldg_live_u32_if(src - 4, halo) : ldg_stream_u32_if(src - 4, halo);
+                    if (SITE == 1 && FMT != 3) hl[r] = LIVE ? ldg_live_u32_if(src - 4, halo) : ldg_stream_u32_if(src - 4, halo);
                     if (DMG) diff |= (px[r].x ^ q.x) | (px[r].y ^ q.y) | (px[r].z ^ q.z) | (px[r].w ^ q.w);
                     if (SITE == 0) {                       // odd width: the unpaired last pixel pairs with itself
                         if (remain == 1) px[r].y = px[r].x;
@@ -169,10 +227,19 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
             const uint32_t pa2 = chroma_pair<NEG>(a.z, m), pa3 = chroma_pair<NEG>(a.w, m);
             const uint32_t pb0 = chroma_pair<NEG>(b.x, m), pb1 = chroma_pair<NEG>(b.y, m);
             const uint32_t pb2 = chroma_pair<NEG>(b.z, m), pb3 = chroma_pair<NEG>(b.w, m);
-            uint32_t c0, c1;
+            if (FMT == 3) {
+                // 4:4:4: every pixel's u and v, planar: four u bytes and four v bytes per lane and line
+                *reinterpret_cast<uint32_t *>(&st.c[2 * k][lane * 4]) = prmt(prmt(pa0, pa1, 0x0040), prmt(pa2, pa3, 0x0040), 0x5410);
+                *reinterpret_cast<uint32_t *>(&st.c[2 * k][TW + lane * 4]) = prmt(prmt(pa0, pa1, 0x0062), prmt(pa2, pa3, 0x0062), 0x5410);
+                *reinterpret_cast<uint32_t *>(&st.c[2 * k + 1][lane * 4]) = prmt(prmt(pb0, pb1, 0x0040), prmt(pb2, pb3, 0x0040), 0x5410);
+                *reinterpret_cast<uint32_t *>(&st.c[2 * k + 1][TW + lane * 4]) = prmt(prmt(pb0, pb1, 0x0062), prmt(pb2, pb3, 0x0062), 0x5410);
+                continue;
+            }
+            // horizontal filter per line: two sites per lane (pixels 0 and 2)
+            uint32_t ha0, ha1, hb0, hb1;
             if (SITE == 0) {
-                c0 = avg2(avg2(pa0, pa1), avg2(pb0, pb1));
-                c1 = avg2(avg2(pa2, pa3), avg2(pb2, pb3));
+                ha0 = avg2(pa0, pa1);  ha1 = avg2(pa2, pa3);
+                hb0 = avg2(pb0, pb1);  hb1 = avg2(pb2, pb3);
             } else {
                 // left neighbour of pixel 0: previous lane's pixel 3, the stripe halo, or (column 0) itself
                 uint32_t la = __shfl_up_sync(FULL, pa3, 1);
@@ -183,9 +250,20 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
                 }
                 const uint32_t ra1 = edge1 ? pa0 : pa1, rb1 = edge1 ? pb0 : pb1;
                 const uint32_t ra3 = edge3 ? pa2 : pa3, rb3 = edge3 ? pb2 : pb3;
-                c0 = avg2(filt121(la, pa0, ra1), filt121(lb, pb0, rb1));
-                c1 = avg2(filt121(pa1, pa2, ra3), filt121(pb1, pb2, rb3));
+                ha0 = filt121(la, pa0, ra1);  ha1 = filt121(pa1, pa2, ra3);
+                hb0 = filt121(lb, pb0, rb1);  hb1 = filt121(pb1, pb2, rb3);
             }
+            if (FMT == 2) {
+                // 4:2:2: the horizontally filtered sites of each line are the samples
+                const uint32_t a = prmt(ha0, ha1, 0x6240), b = prmt(hb0, hb1, 0x6240);   // u0 u1 v0 v1
+                *reinterpret_cast<uint16_t *>(&st.c[2 * k][lane * 2]) = (uint16_t)(a & 0xffffu);
+                *reinterpret_cast<uint16_t *>(&st.c[2 * k][64 + lane * 2]) = (uint16_t)(a >> 16);
+                *reinterpret_cast<uint16_t *>(&st.c[2 * k + 1][lane * 2]) = (uint16_t)(b & 0xffffu);
+                *reinterpret_cast<uint16_t *>(&st.c[2 * k + 1][64 + lane * 2]) = (uint16_t)(b >> 16);
+                continue;
+            }
+            // 4:2:0: then the rounded mean of the two lines
+            const uint32_t c0 = avg2(ha0, hb0), c1 = avg2(ha1, hb1);
             if (FMT == 0) {
                 const uint32_t uuvv = prmt(c0, c1, 0x6240);                 // u0 u1 v0 v1
                 *reinterpret_cast<uint16_t *>(&st.c[k][lane * 2]) = (uint16_t)(uuvv & 0xffffu);
@@ -203,7 +281,7 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
             if (r < rows && gx < p.w)
                 store16(p.out.p[0] + fo + (long long)(yh + r) * p.out.pitch[0] + gx, &st.y[r][seg * 16], p.w - gx, STREAM);
         }
-        {
+        if (FMT <= 1) {
             const int r = lane >> 3;                       // chroma: HR/2 rows x 8 segments
             if (r < PAIRS && 2 * r < rows) {
                 const long long cy = (yh >> 1) + r;
@@ -215,6 +293,23 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
                 } else if (gx < 2 * cw) {
                     store16(p.out.p[1] + fo + cy * p.out.pitch[1] + gx, &st.c[r][seg * 16], 2 * cw - gx, STREAM);
                 }
+            }
+        } else if (FMT == 2) {
+            const int cw = (p.w + 1) >> 1;                 // Y42B: HR rows x (4 U + 4 V) segments
+            const int plane = 1 + (seg >> 2), cx = (x0 >> 1) + (seg & 3) * 16;
+#pragma unroll
+            for (int i = 0; i < HR / 4; i++) {
+                const int r = i * 4 + (lane >> 3);
+                if (r < rows && cx < cw)
+                    store16(p.out.p[plane] + fo + (long long)(yh + r) * p.out.pitch[plane] + cx, &st.c[r][seg * 16], cw - cx, STREAM);
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < HR / 2; i++) {             // Y444: HR rows x (8 U + 8 V) segments
+                const int idx = i * 32 + lane, r = idx >> 4, sg = idx & 15;
+                const int plane = 1 + (sg >> 3), cx = x0 + (sg & 7) * 16;
+                if (r < rows && cx < p.w)
+                    store16(p.out.p[plane] + fo + (long long)(yh + r) * p.out.pitch[plane] + cx, &st.c[r][sg * 16], p.w - cx, STREAM);
             }
         }
         __syncwarp();                                      // the stage is reused by the next step
@@ -237,19 +332,33 @@ constexpr int K1_ROWS_PER_STEP = 8;
 template <int FMT, int SITE, bool NEG, bool DMG>
 cudaError_t launch4(const ConvertParams &p, dim3 grid, cudaStream_t st)
 {
-    if (p.gate.flags)
-        k1_convert_kernel<FMT, SITE, NEG, DMG, K1_ROWS_PER_STEP, 2><<<grid, WARPS * 32, 0, st>>>(p);
-    else if (p.stream_out)
-        k1_convert_kernel<FMT, SITE, NEG, DMG, K1_ROWS_PER_STEP, 1><<<grid, WARPS * 32, 0, st>>>(p);
-    else
-        k1_convert_kernel<FMT, SITE, NEG, DMG, K1_ROWS_PER_STEP, 0><<<grid, WARPS * 32, 0, st>>>(p);
+    if (p.in16) {                                          // (no row gate for 2-byte pixels: launch_convert refuses it)
+        if (p.stream_out)
+            k1_convert_kernel<FMT, SITE, NEG, DMG, K1_ROWS_PER_STEP, 1, true><<<grid, WARPS * 32, 0, st>>>(p);
+        else
+            k1_convert_kernel<FMT, SITE, NEG, DMG, K1_ROWS_PER_STEP, 0, true><<<grid, WARPS * 32, 0, st>>>(p);
+    } else if (p.gate.flags) {
+        if constexpr (FMT <= 1)
+            k1_convert_kernel<FMT, SITE, NEG, DMG, K1_ROWS_PER_STEP, 2, false><<<grid, WARPS * 32, 0, st>>>(p);
+        else
+            return cudaErrorInvalidValue;                  // (the row gate serves the 4:2:0 formats)
+    } else if (p.stream_out) {
+        k1_convert_kernel<FMT, SITE, NEG, DMG, K1_ROWS_PER_STEP, 1, false><<<grid, WARPS * 32, 0, st>>>(p);
+    } else {
+        k1_convert_kernel<FMT, SITE, NEG, DMG, K1_ROWS_PER_STEP, 0, false><<<grid, WARPS * 32, 0, st>>>(p);
+    }
     return cudaGetLastError();
 }
 
 template <int FMT, int SITE, bool NEG>
 cudaError_t launch3(const ConvertParams &p, dim3 grid, cudaStream_t st)
 {
-    return (p.prev && p.damage) ? launch4<FMT, SITE, NEG, true>(p, grid, st) : launch4<FMT, SITE, NEG, false>(p, grid, st);
+    if constexpr (FMT <= 1) {
+        if (p.prev && p.damage) return launch4<FMT, SITE, NEG, true>(p, grid, st);
+    } else {
+        if (p.prev && p.damage) return cudaErrorInvalidValue;      // (the damage map goes with the 4:2:0 formats)
+    }
+    return launch4<FMT, SITE, NEG, false>(p, grid, st);
 }
 
 template <int FMT, int SITE>
@@ -262,12 +371,16 @@ cudaError_t launch2(const ConvertParams &p, dim3 grid, cudaStream_t st)
 
 cudaError_t launch_convert(const ConvertParams &p, int fmt, int site, cudaStream_t st)
 {
-    if (p.w <= 0 || p.h <= 0 || p.n_frames <= 0 || (p.gate.flags && (p.n_frames != 1 || p.gate.rows <= 0 || !p.gate.timeout)))
+    if (p.w <= 0 || p.h <= 0 || p.n_frames <= 0 || (p.gate.flags && (p.n_frames != 1 || p.gate.rows <= 0 || !p.gate.timeout || p.in16)))
         return cudaErrorInvalidValue;
     dim3 grid((p.w + TW * WARPS - 1) / (TW * WARPS), (p.h + TH - 1) / TH, p.n_frames);
-    if (fmt == 0)
-        return site ? launch2<0, 1>(p, grid, st) : launch2<0, 0>(p, grid, st);
-    return site ? launch2<1, 1>(p, grid, st) : launch2<1, 0>(p, grid, st);
+    switch (fmt) {
+    case 0: return site ? launch2<0, 1>(p, grid, st) : launch2<0, 0>(p, grid, st);
+    case 1: return site ? launch2<1, 1>(p, grid, st) : launch2<1, 0>(p, grid, st);
+    case 2: return site ? launch2<2, 1>(p, grid, st) : launch2<2, 0>(p, grid, st);
+    case 3: return launch2<3, 0>(p, grid, st);             // 4:4:4: no chroma filter, the site does not matter
+    default: return cudaErrorInvalidValue;
+    }
 }
 
 }  // namespace b200vc

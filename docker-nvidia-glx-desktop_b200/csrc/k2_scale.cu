@@ -501,7 +501,7 @@ __global__ void __launch_bounds__(128) k2_plane_scale_kernel(const PlaneScalePar
     const int row = blockIdx.y;
     const long long fi = (long long)blockIdx.z * p.src_frame_stride;
     const long long fo = (long long)blockIdx.z * p.out.frame_stride;
-    const int ch = (p.out_h + 1) >> 1, cw = (p.out_w + 1) >> 1;   // odd frames: chroma planes round up
+    const int ch = p.c_out_h, cw = p.c_out_w;             // by format; odd frames: chroma planes round up
 
     if (row < p.out_h) {                                   // luma line
         if (x >= p.out_w) return;
@@ -656,9 +656,9 @@ cudaError_t launch_plane_scale(const PlaneScaleParams &p, int fmt, cudaStream_t 
     if (p.out_w <= 0 || p.out_h <= 0 || p.n_frames <= 0)
         return cudaErrorInvalidValue;
     // one block row per output line: luma lines, then chroma lines (I420: U lines then V lines)
-    const int rows = p.out_h + (fmt == 0 ? 2 : 1) * ((p.out_h + 1) >> 1);
-    dim3 grid(((p.out_w + 3) / 4 + 127) / 128, rows, p.n_frames);
-    if (fmt == 0)
+    const int rows = p.out_h + (fmt != 1 ? 2 : 1) * p.c_out_h;
+    dim3 grid((((p.out_w > p.c_out_w ? p.out_w : p.c_out_w) + 3) / 4 + 127) / 128, rows, p.n_frames);
+    if (fmt != 1)
         k2_plane_scale_kernel<0><<<grid, 128, 0, st>>>(p);
     else
         k2_plane_scale_kernel<1><<<grid, 128, 0, st>>>(p);

@@ -53,6 +53,7 @@ struct ConvertParams {
     int w, h;               // pixels covered by this launch (h = rows of the band, even)
     int n_frames;
     int stream_out;         // 1: the planes are final output (streaming stores); 0: read again on the GPU (two-pass intermediate)
+    int in16;               // 1: 2-byte 5-6-5 pixels (RGB16/BGR16), unpacked in registers; src/prev pitches are in bytes as ever
     RowGate gate;           // n_frames == 1 only
     Matrix mx;
 };
@@ -126,6 +127,7 @@ struct PlaneScaleParams {
     PlaneSet out;
     ScaleTables tab;
     int in_w, in_h, out_w, out_h;
+    int c_out_w, c_out_h;   // samples per line / lines of a chroma plane of the output (by format)
     int n_frames;
     int box2x2;
 };

@@ -152,6 +152,9 @@ extern "C" int b200vc_convert_scale_device_static(const b200vc_config *cfg, cons
     if (cfg->in_w == cfg->out_w && cfg->in_h == cfg->out_h)
         return report(errbuf, errbuf_len, B200VC_ERR_UNSUPPORTED,
                       "no scaling requested: the unscaled path needs no scratch, use b200vc_convert_device");
+    if (cfg->out_format > B200VC_FMT_NV12 || cfg->in_format > B200VC_IN_XBGR)
+        return report(errbuf, errbuf_len, B200VC_ERR_UNSUPPORTED,
+                      "this entry point converts 4-byte pixels to I420 or NV12; other formats go through a context");
     if (cfg->flags & B200VC_FLAG_DAMAGE_MAP)
         return report(errbuf, errbuf_len, B200VC_ERR_UNSUPPORTED, "the damage map is produced on the unscaled path only");
     if ((cfg->in_w | cfg->in_h | cfg->out_w | cfg->out_h) & 1)
@@ -208,7 +211,7 @@ extern "C" int b200vc_convert_scale_device_static(const b200vc_config *cfg, cons
     }
 
     cudaStream_t st = (cudaStream_t)cuda_stream;
-    const int site = cfg->chroma_site == B200VC_SITE_H_COSITED ? 1 : 0;
+    const int site = (cfg->chroma_site & B200VC_SITE_H_COSITED) ? 1 : 0;
     const Matrix mx = make_matrix(cfg->matrix, cfg->range, cfg->in_format);
     for (int f = 0; f < d->n_frames; f++) {
         // pass 1: K1 at the source size into the static intermediate (always planar)

@@ -53,15 +53,28 @@ enum {
 };
 
 /* ---- negotiated caps, as plain enums ------------------------------------------------------- */
-enum { B200VC_FMT_I420 = 0, B200VC_FMT_NV12 = 1 };                  /* src pad format          */
+/* src pad format: 4:2:0 planar and semi-planar (what the reference's encoders take), and the planar
+ * 4:2:2 and 4:4:4 formats videoconvert also offers (chroma halved horizontally only / not at all) */
+enum { B200VC_FMT_I420 = 0, B200VC_FMT_NV12 = 1, B200VC_FMT_Y42B = 2, B200VC_FMT_Y444 = 3 };
 enum { B200VC_MATRIX_BT601 = 0, B200VC_MATRIX_BT709 = 1, B200VC_MATRIX_BT2020 = 2 };   /* colorimetry matrix */
 enum { B200VC_RANGE_LIMITED = 0, B200VC_RANGE_FULL = 1 };           /* colorimetry range       */
-enum { B200VC_SITE_NONE = 0 /* "jpeg" */, B200VC_SITE_H_COSITED = 1 /* "mpeg2" */ };
+/* chroma-site, as GstVideoChromaSite's flags: "jpeg"/none 0, "mpeg2" 1 (h-cosited), "cosited" 3 (h and v),
+ * "dv" 7 (cosited, alternate lines). The horizontal flag selects the 1-2-1 filter; the vertical step of
+ * videoconvert's 4:2:0 downsampling is the rounded mean of the two lines for every site (its v-cosited
+ * variants point at the same function upstream, as recalled: SURVEY A.4), and ALT_LINE only matters for
+ * interlaced video. So every value negotiates; bit 0 is what changes the output. */
+enum { B200VC_SITE_NONE = 0, B200VC_SITE_H_COSITED = 1, B200VC_SITE_V_COSITED = 2, B200VC_SITE_ALT_LINE = 4,
+       B200VC_SITE_COSITED = 3, B200VC_SITE_DV = 7 };
 enum { B200VC_SCALE_GST_LQ = 0 /* videoscale bilinear, SURVEY B.2 */, B200VC_SCALE_BOX_2X2 = 1 };
 /* sink pad format: byte order of one pixel in memory; x is a pad or alpha byte and never matters
  * (BGRA, RGBA, ARGB, ABGR negotiate as their x twins: I420/NV12 carry no alpha). BGRx is what
  * ximagesrc delivers at the reference's default depth 24 (Dockerfile:206, entrypoint.sh:102). */
-enum { B200VC_IN_BGRX = 0, B200VC_IN_RGBX = 1, B200VC_IN_XRGB = 2, B200VC_IN_XBGR = 3 };
+enum { B200VC_IN_BGRX = 0, B200VC_IN_RGBX = 1, B200VC_IN_XRGB = 2, B200VC_IN_XBGR = 3,
+       /* 16 bits per pixel, little endian, 5-6-5: what ximagesrc delivers at the reference's CDEPTH=16
+        * (Dockerfile:206, entrypoint.sh:102). RGB16: red in bits 11..15; BGR16: blue there. Unpacked to 8 bits
+        * per channel as video-format.c does (high bits repeated into the low ones, b200vc_spec.h). These run
+        * the conversion kernel; with scaling, the two-pass path. */
+       B200VC_IN_RGB16 = 4, B200VC_IN_BGR16 = 5 };
 
 /* flags */
 #define B200VC_FLAG_DAMAGE_MAP      0x1u  /* keep the previous frame per session and emit the map */
@@ -114,7 +127,8 @@ typedef struct b200vc_ctx b200vc_ctx;
 
 /* One frame crossing the boundary in host memory. Mirrors what transform_frame receives: the
  * mapped input GstVideoFrame (data[0], stride[0]) and the mapped output frame (data[p],
- * stride[p]); strides are always honoured. planes[2]/pitches[2] unused for NV12. */
+ * stride[p]); strides are always honoured. planes[2]/pitches[2] unused for NV12. The
+ * member is called bgrx after the reference's default format; it holds pixels of the negotiated in_format. */
 typedef struct b200vc_frame {
     const void *bgrx;
     size_t in_pitch;
@@ -179,7 +193,7 @@ int b200vc_damage_to_rects(const uint8_t *map, int frame_w, int frame_h, b200vc_
 const char *b200vc_status_string(int status);
 int b200vc_version(void);
 
-/* The values of include/b200vc_spec.h this library was built with, as one token ("m0c1h1b6r1"): the
+/* The values of include/b200vc_spec.h this library was built with, as one token ("m0c1h1b6r1u1"): the
  * details of videoconvert/videoscale's arithmetic that SURVEY.md Appendix A/B could not verify against
  * GStreamer (matrix rounding term, last column of the cosited filter, order of the scaler's passes,
  * bits and rounding of its vertical tap). The oracle reports its own the same way; tests compare. */

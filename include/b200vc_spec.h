@@ -54,6 +54,13 @@
 #define B200VC_SPEC_VTAP_ROUND 1
 #endif
 
+/* video-format.c — unpacking 5- and 6-bit channels (RGB16/BGR16 input) to 8 bits. 1: the high bits are
+ * repeated into the low ones, (v << 3) | (v >> 2) and (v << 2) | (v >> 4), so that full scale maps to 255
+ * (as recalled, the default). 0: plain shift (what GST_VIDEO_PACK_FLAG_TRUNCATE_RANGE selects). */
+#ifndef B200VC_SPEC_UNPACK16_REPLICATE
+#define B200VC_SPEC_UNPACK16_REPLICATE 1
+#endif
+
 #if B200VC_SPEC_VTAP_BITS != 6 && B200VC_SPEC_VTAP_BITS != 7 && B200VC_SPEC_VTAP_BITS != 8
 #error "B200VC_SPEC_VTAP_BITS must be 6, 7 or 8 (the kernels evaluate the tap as 8-bit dp4a weights)"
 #endif
@@ -61,12 +68,12 @@
 #define B200VC_SPEC_VTAP_ONE  (1 << B200VC_SPEC_VTAP_BITS)
 #define B200VC_SPEC_VTAP_HALF (1 << (B200VC_SPEC_VTAP_BITS - 1))
 
-/* "m0c1h1b6r1": the five values above in one token; b200vc_spec_string() and orc_spec_string()
+/* "m0c1h1b6r1u1": the values above in one token; b200vc_spec_string() and orc_spec_string()
  * return it so that a test can see that library and oracle were built from the same settings. */
 #define B200VC_SPEC_STR2(x) #x
 #define B200VC_SPEC_STR(x) B200VC_SPEC_STR2(x)
 #define B200VC_SPEC_STRING "m" B200VC_SPEC_STR(B200VC_SPEC_MATRIX_ROUND) "c" B200VC_SPEC_STR(B200VC_SPEC_COSITED_LAST_1_3) \
                            "h" B200VC_SPEC_STR(B200VC_SPEC_SCALE_H_FIRST) "b" B200VC_SPEC_STR(B200VC_SPEC_VTAP_BITS)       \
-                           "r" B200VC_SPEC_STR(B200VC_SPEC_VTAP_ROUND)
+                           "r" B200VC_SPEC_STR(B200VC_SPEC_VTAP_ROUND) "u" B200VC_SPEC_STR(B200VC_SPEC_UNPACK16_REPLICATE)
 
 #endif /* B200VC_SPEC_H */

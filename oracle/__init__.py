@@ -19,12 +19,12 @@ from . import spec as _spec
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SRCS = ["convert.c", "scale.c", "damage_synth.c"]
 
-FMT_I420, FMT_NV12 = 0, 1
+FMT_I420, FMT_NV12, FMT_Y42B, FMT_Y444 = 0, 1, 2, 3
 MATRIX_BT601, MATRIX_BT709, MATRIX_BT2020 = 0, 1, 2
 RANGE_LIMITED, RANGE_FULL = 0, 1
 SITE_NONE, SITE_H_COSITED = 0, 1
 SCALE_GST_LQ, SCALE_BOX_2X2 = 0, 1
-IN_BGRX, IN_RGBX, IN_XRGB, IN_XBGR = 0, 1, 2, 3
+IN_BGRX, IN_RGBX, IN_XRGB, IN_XBGR, IN_RGB16, IN_BGR16 = 0, 1, 2, 3, 4, 5
 
 
 def build(native: bool = False, out_dir: str | None = None, spec: dict | None = None) -> str:
@@ -109,9 +109,10 @@ class Oracle:
             total, off, pit = self.default_layout(fmt, w, h)
         else:
             pit = list(pitches) + [0] * (3 - len(pitches))
-            rows = [h, (h + 1) // 2, (h + 1) // 2]
+            ch = h if fmt >= FMT_Y42B else (h + 1) // 2
+            rows = [h, ch, ch]
             off, total = [], 0
-            for p in range(3 if fmt == FMT_I420 else 2):
+            for p in range(2 if fmt == FMT_NV12 else 3):
                 off.append(total)
                 total += pit[p] * rows[p]
             off += [0] * (3 - len(off))
@@ -122,9 +123,11 @@ class Oracle:
 
     def convert(self, frame: np.ndarray, fmt=FMT_I420, matrix=MATRIX_BT601, rng=RANGE_LIMITED,
                 site=SITE_NONE, out_size=None, scale_mode=SCALE_GST_LQ, pitches=None, threads=1, in_format=IN_BGRX):
-        """frame: (h, w, 4) uint8 BGRx (may be a strided view). Returns (buf, offsets, pitches)."""
+        """frame: (h, w, 4) uint8 pixels, or (h, w, 2) for the 16-bit formats (may be a strided view).
+        Returns (buf, offsets, pitches)."""
         h, w = frame.shape[:2]
-        assert frame.dtype == np.uint8 and frame.shape[2] == 4 and frame.strides[2] == 1 and frame.strides[1] == 4
+        bpp = 2 if in_format >= IN_RGB16 else 4
+        assert frame.dtype == np.uint8 and frame.shape[2] == bpp and frame.strides[2] == 1 and frame.strides[1] == bpp
         ow, oh = out_size if out_size else (w, h)
         buf, off, pit, ptrs, pits = self._planes(fmt, ow, oh, pitches)
         rc = self.lib.orc_convert_scale_mt_ex(frame.ctypes.data, frame.strides[0], in_format, w, h, ow, oh, fmt, matrix,

@@ -58,6 +58,17 @@ size_t orc_default_layout(int format, int w, int h, size_t offsets[3], size_t pi
     size_t ypitch = (size_t)RU4(w);
     offsets[0] = 0;
     pitches[0] = ypitch;
+    if (format == ORC_FMT_Y42B) {          /* fill_planes: stride[1] = RU8(w)/2, heights as they are */
+        size_t cp = (size_t)(((w + 7) & ~7) / 2);
+        offsets[1] = ypitch * (size_t)h;  pitches[1] = cp;
+        offsets[2] = offsets[1] + cp * (size_t)h;  pitches[2] = cp;
+        return offsets[2] + cp * (size_t)h;
+    }
+    if (format == ORC_FMT_Y444) {
+        offsets[1] = ypitch * (size_t)h;  pitches[1] = ypitch;
+        offsets[2] = 2 * ypitch * (size_t)h;  pitches[2] = ypitch;
+        return 3 * ypitch * (size_t)h;
+    }
     if (format == ORC_FMT_NV12) {
         offsets[1] = ypitch * (size_t)RU2(h);
         pitches[1] = ypitch;
@@ -79,6 +90,22 @@ size_t orc_default_layout(int format, int w, int h, size_t offsets[3], size_t pi
  * (A forced to 0xff like the x-format unpacks; it is dropped again by the pack stage). */
 static void unpack_line(const uint8_t *s, uint8_t *d, int w, int in_format)
 {
+    if (in_format == ORC_IN_RGB16 || in_format == ORC_IN_BGR16) {
+        /* unpack_RGB16 / unpack_BGR16: little-endian 5-6-5, widened to 8 bits with the high bits repeated
+         * into the low ones (video_orc_unpack_RGB16; _trunc, a plain shift, under TRUNCATE_RANGE — the
+         * B200VC_SPEC_UNPACK16_REPLICATE constant) */
+        for (int i = 0; i < w; i++) {
+            const unsigned v = s[2 * i] | ((unsigned)s[2 * i + 1] << 8);
+            unsigned hi = v >> 11, g = (v >> 5) & 63, lo = v & 31;
+            unsigned hi8 = hi << 3, g8 = g << 2, lo8 = lo << 3;
+            if (B200VC_SPEC_UNPACK16_REPLICATE) { hi8 |= hi >> 2;  g8 |= g >> 4;  lo8 |= lo >> 2; }
+            d[4 * i + 0] = 0xff;
+            d[4 * i + 1] = (uint8_t)(in_format == ORC_IN_RGB16 ? hi8 : lo8);
+            d[4 * i + 2] = (uint8_t)g8;
+            d[4 * i + 3] = (uint8_t)(in_format == ORC_IN_RGB16 ? lo8 : hi8);
+        }
+        return;
+    }
     static const int pos[4][3] = { { 2, 1, 0 }, { 0, 1, 2 }, { 1, 2, 3 }, { 3, 2, 1 } };   /* byte of R, G, B */
     const int pr = pos[in_format][0], pg = pos[in_format][1], pb = pos[in_format][2];
     for (int i = 0; i < w; i++) {
@@ -171,9 +198,18 @@ static void chroma_down_h2_cs(uint8_t *p, int w)
 }
 
 /* video_chroma_down_v2_u8: horizontal on each line first, then rounded vertical mean into l0. */
+/* 4:2:2 (Y42B): horizontal only, every line */
+static void chroma_down_h(uint8_t *l, int w, int site)
+{
+    if (site & ORC_SITE_H_COSITED)
+        chroma_down_h2_cs(l, w);
+    else
+        chroma_down_h2(l, w);
+}
+
 static void chroma_down_v2(uint8_t *l0, uint8_t *l1, int w, int site)
 {
-    if (site == ORC_SITE_H_COSITED) {
+    if (site & ORC_SITE_H_COSITED) {
         chroma_down_h2_cs(l0, w);
         chroma_down_h2_cs(l1, w);
     } else {
@@ -202,6 +238,15 @@ static void pack_uv_planar(const uint8_t *p, uint8_t *u, uint8_t *v, int w)
     }
 }
 
+/* pack_Y444: U and V of every pixel */
+static void pack_uv_full(const uint8_t *p, uint8_t *u, uint8_t *v, int w)
+{
+    for (int i = 0; i < w; i++) {
+        u[i] = p[4 * i + 2];
+        v[i] = p[4 * i + 3];
+    }
+}
+
 static void pack_uv_interleaved(const uint8_t *p, uint8_t *uv, int w)
 {
     for (int i = 0; i < (w + 1) / 2; i++) {
@@ -217,15 +262,15 @@ static int convert_rows_ex(const uint8_t *bgrx, size_t in_pitch, int in_format, 
                            uint8_t *const planes[3], const size_t pitches[3],
                            int row0, int row1)
 {
-    if (in_format < ORC_IN_BGRX || in_format > ORC_IN_XBGR || matrix < ORC_MATRIX_BT601 || matrix > ORC_MATRIX_BT2020)
+    if (in_format < ORC_IN_BGRX || in_format > ORC_IN_BGR16 || matrix < ORC_MATRIX_BT601 || matrix > ORC_MATRIX_BT2020)
         return -1;
     if (!bgrx || !planes || !pitches || w < 2 || h < 2)
         return -1;
     if (row0 < 0 || row1 > h || row0 > row1 || (row0 & 1) || ((row1 & 1) && row1 != h))
         return -1;
-    if (format != ORC_FMT_I420 && format != ORC_FMT_NV12)
+    if (format < ORC_FMT_I420 || format > ORC_FMT_Y444)
         return -1;
-    if (site != ORC_SITE_NONE && site != ORC_SITE_H_COSITED)
+    if (site < 0 || site > 7)
         return -1;
 
     orc_matrix mx;
@@ -249,6 +294,20 @@ static int convert_rows_ex(const uint8_t *bgrx, size_t in_pitch, int in_format, 
         pack_y(l0, planes[0] + (size_t)y * pitches[0], w);
         if (y1 != y)
             pack_y(l1, planes[0] + (size_t)y1 * pitches[0], w);
+        if (format == ORC_FMT_Y444 || format == ORC_FMT_Y42B) {
+            /* no vertical subsampling: each line on its own (4:2:2: horizontal filter first) */
+            for (int k = 0; k < (y1 != y ? 2 : 1); k++) {
+                uint8_t *l = k ? l1 : l0;
+                const size_t yy = (size_t)(k ? y1 : y);
+                if (format == ORC_FMT_Y444) {
+                    pack_uv_full(l, planes[1] + yy * pitches[1], planes[2] + yy * pitches[2], w);
+                } else {
+                    chroma_down_h(l, w, site);
+                    pack_uv_planar(l, planes[1] + yy * pitches[1], planes[2] + yy * pitches[2], w);
+                }
+            }
+            continue;
+        }
         chroma_down_v2(l0, l1, w, site);
         if (format == ORC_FMT_NV12)
             pack_uv_interleaved(l0, planes[1] + (size_t)(y / 2) * pitches[1], w);

@@ -20,8 +20,9 @@ int orc_damage_map(const uint8_t *cur, size_t cur_pitch, const uint8_t *prev, si
 int orc_damage_map_ex(const uint8_t *cur, size_t cur_pitch, const uint8_t *prev, size_t prev_pitch,
                       int in_format, int w, int h, uint8_t *map)
 {
-    if (!cur || !map || w < 1 || h < 1 || in_format < ORC_IN_BGRX || in_format > ORC_IN_XBGR)
+    if (!cur || !map || w < 1 || h < 1 || in_format < ORC_IN_BGRX || in_format > ORC_IN_BGR16)
         return -1;
+    const int bpp16 = in_format >= ORC_IN_RGB16;          /* 2-byte pixels: every bit is colour */
     const int c0 = (in_format == ORC_IN_XRGB || in_format == ORC_IN_XBGR) ? 1 : 0;   /* first colour byte */
     const int mb_w = (w + 15) / 16, mb_h = (h + 15) / 16;
     if (!prev) {
@@ -33,6 +34,11 @@ int orc_damage_map_ex(const uint8_t *cur, size_t cur_pitch, const uint8_t *prev,
         const uint8_t *a = cur + (size_t)y * cur_pitch;
         const uint8_t *b = prev + (size_t)y * prev_pitch;
         for (int x = 0; x < w; x++) {
+            if (bpp16) {
+                if (a[2 * x] != b[2 * x] || a[2 * x + 1] != b[2 * x + 1])
+                    map[(y / 16) * mb_w + (x / 16)] = 1;
+                continue;
+            }
             /* the x byte cannot change the converted output, so it is not damage */
             if (a[4 * x + c0] != b[4 * x + c0] || a[4 * x + c0 + 1] != b[4 * x + c0 + 1] ||
                 a[4 * x + c0 + 2] != b[4 * x + c0 + 2])

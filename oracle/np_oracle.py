@@ -32,8 +32,24 @@ MATRICES = {
 CHANNELS = {0: (2, 1, 0), 1: (0, 1, 2), 2: (1, 2, 3), 3: (3, 2, 1)}
 
 
+def unpack16(frame: np.ndarray, in_format: int) -> np.ndarray:
+    """(h,w,2) little-endian 5-6-5 pixels (4 RGB16: red in the top bits; 5 BGR16: blue there) -> (h,w,4) BGRx,
+    each channel widened to 8 bits by repeating its high bits (or by a plain shift, SPEC UNPACK16_REPLICATE)."""
+    v = frame[..., 0].astype(np.uint32) | (frame[..., 1].astype(np.uint32) << 8)
+    hi, g, lo = v >> 11, (v >> 5) & 63, v & 31
+    hi8, g8, lo8 = hi << 3, g << 2, lo << 3
+    if SPEC["UNPACK16_REPLICATE"]:
+        hi8, g8, lo8 = hi8 | (hi >> 2), g8 | (g >> 4), lo8 | (lo >> 2)
+    r, b = (hi8, lo8) if in_format == 4 else (lo8, hi8)
+    out = np.zeros(frame.shape[:2] + (4,), np.uint8)
+    out[..., 0], out[..., 1], out[..., 2], out[..., 3] = b, g8, r, 0xFF
+    return out
+
+
 def yuv444(frame: np.ndarray, matrix: int, rng: int, in_format: int = 0):
     """(h,w,4) pixels -> three (h,w) uint8 arrays, (c.RGB + off) >> 8 with no rounding term."""
+    if in_format >= 4:
+        frame, in_format = unpack16(frame, in_format), 0
     ir, ig, ib = CHANNELS[in_format]
     b = frame[..., ib].astype(np.int32)
     g = frame[..., ig].astype(np.int32)
@@ -48,10 +64,12 @@ def yuv444(frame: np.ndarray, matrix: int, rng: int, in_format: int = 0):
     return out
 
 
-def chroma_down(c: np.ndarray, site: int) -> np.ndarray:
+def chroma_down(c: np.ndarray, site: int, vertical: bool = True) -> np.ndarray:
     """(h,w) 4:4:4 chroma -> (ceil(h/2),ceil(w/2)): horizontal (rounded) on each line, then vertical
     (rounded). Odd widths: the last pixel is a site of its own; odd heights: the last line pairs with
-    itself."""
+    itself. vertical=False (4:2:2): the horizontal step alone. Of the chroma-site flags only H_COSITED
+    (bit 0) matters."""
+    site &= 1
     h, w = c.shape
     c = c.astype(np.int32)
     n = (w + 1) // 2
@@ -69,6 +87,8 @@ def chroma_down(c: np.ndarray, site: int) -> np.ndarray:
             i += 2
         if i < w:
             hz[:, i // 2] = (c[:, i - 1] + 3 * c[:, i] + 2) >> 2
+    if not vertical:
+        return hz.astype(np.uint8)
     if h & 1:
         hz = np.concatenate([hz, hz[-1:]], axis=0)
     return ((hz[0::2] + hz[1::2] + 1) >> 1).astype(np.uint8)
@@ -77,6 +97,10 @@ def chroma_down(c: np.ndarray, site: int) -> np.ndarray:
 def convert(frame: np.ndarray, fmt: int, matrix: int, rng: int, site: int, in_format: int = 0):
     """Returns (Y, U, V) planes for I420 or (Y, UV) for NV12 at the input size."""
     y, u, v = yuv444(frame, matrix, rng, in_format)
+    if fmt == 3:                                   # Y444
+        return y, u, v
+    if fmt == 2:                                   # Y42B
+        return y, chroma_down(u, site, vertical=False), chroma_down(v, site, vertical=False)
     u2, v2 = chroma_down(u, site), chroma_down(v, site)
     if fmt == 1:
         uv = np.empty((u2.shape[0], u2.shape[1] * 2), np.uint8)
@@ -129,7 +153,8 @@ def convert_scale(frame, out_w, out_h, fmt, matrix, rng, site, mode=0, in_format
     if out_w == frame.shape[1] and out_h == frame.shape[0]:
         return planes
     out = [scale_plane(planes[0], out_w, out_h, 1, mode)]
-    ocw, och = (out_w + 1) // 2, (out_h + 1) // 2      # chroma planes of odd frames round up
+    ocw = out_w if fmt == 3 else (out_w + 1) // 2        # chroma planes of odd frames round up
+    och = out_h if fmt >= 2 else (out_h + 1) // 2
     if fmt == 1:
         out.append(scale_plane(planes[1], ocw, och, 2, mode))
     else:
@@ -143,7 +168,7 @@ def damage_map(cur: np.ndarray, prev: np.ndarray | None, in_format: int = 0) -> 
     mh, mw = (h + 15) // 16, (w + 15) // 16
     if prev is None:
         return np.ones((mh, mw), np.uint8)
-    ch = list(CHANNELS[in_format])
+    ch = [0, 1] if in_format >= 4 else list(CHANNELS[in_format])     # 16-bit pixels: both bytes
     diff = np.any(cur[..., ch] != prev[..., ch], axis=2)
     pad = np.zeros((mh * 16, mw * 16), bool)
     pad[:h, :w] = diff

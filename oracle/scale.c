@@ -162,7 +162,8 @@ static int convert_scale_impl(const uint8_t *bgrx, size_t in_pitch, int in_forma
     if (scale_mode == ORC_SCALE_BOX_2X2 && ((in_w | in_h | out_w | out_h) & 1))
         return -1;
     /* odd sizes: the chroma planes of both frames round up (video-info.c), and are scaled as such */
-    const int icw = (in_w + 1) / 2, ich = (in_h + 1) / 2, ocw = (out_w + 1) / 2, och = (out_h + 1) / 2;
+    const int hs = format == ORC_FMT_Y444 ? 1 : 2, vs = (format == ORC_FMT_I420 || format == ORC_FMT_NV12) ? 2 : 1;
+    const int icw = (in_w + hs - 1) / hs, ich = (in_h + vs - 1) / vs, ocw = (out_w + hs - 1) / hs, och = (out_h + vs - 1) / vs;
 
     /* stage 1: videoconvert at input size into a default-layout intermediate frame */
     size_t off[3], pit[3];

@@ -37,6 +37,13 @@ CASES = [
     ("odd_709l_i420_mpeg2", 37, 21, 37, 21, 0, 1, 0, 1, 0),
     ("odd_601f_nv12_jpeg", 35, 19, 35, 19, 1, 0, 1, 0, 0),
     ("odd_scale_709l_i420", 71, 39, 36, 21, 0, 1, 0, 1, 0),
+    # round 2 (appended: the cases above keep their random inputs)
+    ("y42b_709l_mpeg2", 38, 20, 38, 20, 2, 1, 0, 1, 0),
+    ("y444_601f", 37, 21, 37, 21, 3, 0, 1, 0, 0),
+    ("y42b_scale_odd", 71, 39, 36, 21, 2, 1, 0, 1, 0),
+    ("rgb16_709l_i420_mpeg2", 38, 20, 38, 20, 0, 1, 0, 1, 0, 4),
+    ("bgr16_601f_nv12_scale", 64, 36, 40, 24, 1, 0, 1, 0, 0, 5),
+    ("site_cosited_i420", 36, 20, 36, 20, 0, 1, 0, 3, 0),
 ]
 
 
@@ -53,7 +60,7 @@ def main():
     for case in CASES:
         name, iw, ih, ow, oh, fmt, mat, rg, site, mode = case[:10]
         inf = case[10] if len(case) > 10 else 0
-        frame = rng.integers(0, 256, size=(ih, iw, 4), dtype=np.uint8)
+        frame = rng.integers(0, 256, size=(ih, iw, 2 if inf >= 4 else 4), dtype=np.uint8)
         planes = N.convert_scale(frame, ow, oh, fmt, mat, rg, site, mode, inf)
         out[name + "/in"] = frame
         out[name + "/cfg"] = np.array([iw, ih, ow, oh, fmt, mat, rg, site, mode, inf], np.int32)

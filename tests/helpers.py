@@ -8,8 +8,10 @@ def plane_views(buf, off, pit, fmt, w, h):
     if fmt == 1:
         uv = np.ndarray(((h + 1) // 2, 2 * ((w + 1) // 2)), np.uint8, buffer=buf, offset=off[1], strides=(pit[1], 1))
         return [y, uv]
-    u = np.ndarray(((h + 1) // 2, (w + 1) // 2), np.uint8, buffer=buf, offset=off[1], strides=(pit[1], 1))
-    v = np.ndarray(((h + 1) // 2, (w + 1) // 2), np.uint8, buffer=buf, offset=off[2], strides=(pit[2], 1))
+    ch = h if fmt >= 2 else (h + 1) // 2               # Y42B, Y444: a chroma line per line
+    cw = w if fmt == 3 else (w + 1) // 2               # Y444: a chroma sample per pixel
+    u = np.ndarray((ch, cw), np.uint8, buffer=buf, offset=off[1], strides=(pit[1], 1))
+    v = np.ndarray((ch, cw), np.uint8, buffer=buf, offset=off[2], strides=(pit[2], 1))
     return [y, u, v]
 
 

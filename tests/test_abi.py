@@ -53,7 +53,8 @@ def test_default_colorimetry_by_height():
     assert b200vc.default_colorimetry(480)[2] == b200vc.SITE_NONE
 
 
-@pytest.mark.parametrize("fmt,w,h", [(0, 1920, 1080), (1, 2560, 1440), (0, 1366, 768), (1, 1366, 768), (0, 2, 2)])
+@pytest.mark.parametrize("fmt,w,h", [(0, 1920, 1080), (1, 2560, 1440), (0, 1366, 768), (1, 1366, 768), (0, 2, 2),
+                                     (2, 1920, 1080), (3, 1920, 1080), (2, 1366, 767), (3, 1365, 767)])
 def test_default_layout_matches_oracle(orc, fmt, w, h):
     assert b200vc.default_layout(fmt, w, h) == orc.default_layout(fmt, w, h)
 
@@ -69,14 +70,18 @@ def test_caps_acceptance(lib):
     ok = [_cfg(), _cfg(out_format=1, matrix=1, range=1, chroma_site=1, in_w=2560, in_h=1440, out_w=2560, out_h=1440),
           _cfg(in_w=3840, in_h=2160), _cfg(in_w=3840, in_h=2160, scale_mode=1), _cfg(flags=b200vc.FLAG_DAMAGE_MAP),
           _cfg(in_w=1366, in_h=768, out_w=1366, out_h=768), _cfg(max_sessions=8, n_inflight=4), _cfg(in_format=3),
-          _cfg(in_w=1365, in_h=767, out_w=1365, out_h=767), _cfg(in_w=3841, in_h=2161)]
+          _cfg(in_w=1365, in_h=767, out_w=1365, out_h=767), _cfg(in_w=3841, in_h=2161),
+          _cfg(chroma_site=3), _cfg(chroma_site=7), _cfg(chroma_site=2),      # cosited, dv, v-cosited: all negotiate
+          _cfg(out_format=2), _cfg(out_format=3, in_w=3840, in_h=2160),       # Y42B, Y444 (scaled: two-pass)
+          _cfg(in_format=4), _cfg(in_format=5, flags=b200vc.FLAG_DAMAGE_MAP)]  # RGB16, BGR16 (CDEPTH=16)
     for c in ok:
         assert lib.b200vc_check_config(C.byref(c)) == b200vc.OK
     refused = [(_cfg(in_w=3842, in_h=2162, out_w=1921, out_h=1081, scale_mode=1), b200vc.ERR_UNSUPPORTED),   # BOX, odd
-               (_cfg(out_format=2), b200vc.ERR_UNSUPPORTED),               # not I420/NV12
-               (_cfg(in_format=4), b200vc.ERR_UNSUPPORTED),                # not a 4-byte RGB order
+               (_cfg(out_format=4), b200vc.ERR_UNSUPPORTED),               # not I420/NV12/Y42B/Y444
+               (_cfg(in_format=6), b200vc.ERR_UNSUPPORTED),                # not one of the six sink formats
                (_cfg(matrix=3), b200vc.ERR_UNSUPPORTED),                   # not bt601/bt709/bt2020
-               (_cfg(chroma_site=3), b200vc.ERR_UNSUPPORTED),              # v-cosited not offered
+               (_cfg(chroma_site=8), b200vc.ERR_UNSUPPORTED),              # not a combination of the site flags
+               (_cfg(out_format=3, flags=b200vc.FLAG_DAMAGE_MAP), b200vc.ERR_UNSUPPORTED),   # the map goes with 4:2:0 output
                (_cfg(in_w=3840, in_h=2160, out_w=1280, out_h=720, scale_mode=1), b200vc.ERR_UNSUPPORTED),
                (_cfg(in_w=3840, in_h=2160, flags=b200vc.FLAG_DAMAGE_MAP), b200vc.ERR_UNSUPPORTED),
                (_cfg(in_w=0), b200vc.ERR_INVALID_ARG), (_cfg(max_sessions=-1), b200vc.ERR_INVALID_ARG),

@@ -82,7 +82,7 @@ def test_golden_vectors_on_gpu(conv):
         conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=mat, range_=rg, chroma_site=site, scale_mode=mode,
                       in_format=inf)
         buf, off, pit = conv.transform_frame(np.ascontiguousarray(z[name + "/in"]))
-        want = [z[f"{name}/p{i}"] for i in range(2 if fmt else 3)]
+        want = [z[f"{name}/p{i}"] for i in range(2 if fmt == 1 else 3)]
         assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), want, name)
     conv.set_info(70, 40, flags=b200vc.FLAG_DAMAGE_MAP)
     conv.transform_frame(np.ascontiguousarray(z["damage/a"]), damage=True)

@@ -75,7 +75,7 @@ def test_golden_vectors(orc):
         iw, ih, ow, oh, fmt, mat, rg, site, mode, inf = [int(v) for v in z[name + "/cfg"]]
         frame = np.ascontiguousarray(z[name + "/in"])
         buf, off, pit = orc.convert(frame, fmt, mat, rg, site, out_size=(ow, oh), scale_mode=mode, in_format=inf)
-        want = [zo[f"{name}/p{i}"] for i in range(2 if fmt else 3)]
+        want = [zo[f"{name}/p{i}"] for i in range(2 if fmt == 1 else 3)]
         assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), want, name)
     assert np.array_equal(orc.damage_map(np.ascontiguousarray(z["damage/b"]), np.ascontiguousarray(z["damage/a"])),
                           z["damage/map"])
@@ -107,6 +107,43 @@ def test_c_equals_numpy_convert(orc, size):
                     buf, off, pit = orc.convert(frame, fmt, m, rg, site)
                     assert_planes_equal(plane_views(buf, off, pit, fmt, w, h), list(N.convert(frame, fmt, m, rg, site)),
                                         f"{kind} {size} fmt{fmt} m{m} r{rg} s{site}")
+
+
+@pytest.mark.parametrize("size", [(2, 2), (6, 4), (130, 18), (131, 35), (640, 360)])
+def test_c_equals_numpy_more_formats(orc, size):
+    """Y42B and Y444 output, RGB16/BGR16 input, every chroma-site value (only its h-cosited bit matters)."""
+    w, h = size
+    rng = np.random.default_rng(w * 1000 + h)
+    f4 = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+    f2 = rng.integers(0, 256, (h, w, 2), dtype=np.uint8)
+    for fmt in (0, 1, 2, 3):
+        for inf, frame in ((0, f4), (4, f2), (5, f2)):
+            for site in (0, 1, 2, 3, 7):
+                buf, off, pit = orc.convert(frame, fmt, 1, 1, site, in_format=inf)
+                assert_planes_equal(plane_views(buf, off, pit, fmt, w, h), list(N.convert(frame, fmt, 1, 1, site, inf)),
+                                    f"{size} fmt{fmt} in{inf} site{site}")
+            if w >= 6:
+                ow, oh = max(2, w * 2 // 3), max(2, h * 3 // 4)
+                buf, off, pit = orc.convert(frame, fmt, 0, 0, 1, out_size=(ow, oh), in_format=inf)
+                assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), list(N.convert_scale(frame, ow, oh, fmt, 0, 0, 1, 0, inf)),
+                                    f"{size} scaled fmt{fmt} in{inf}")
+    # site flags other than h-cosited change nothing
+    a = orc.convert(f4, 0, 1, 0, 1)[0]
+    assert np.array_equal(a, orc.convert(f4, 0, 1, 0, 3)[0]) and np.array_equal(a, orc.convert(f4, 0, 1, 0, 7)[0])
+    assert np.array_equal(orc.convert(f4, 0, 1, 0, 0)[0], orc.convert(f4, 0, 1, 0, 2)[0])
+
+
+def test_unpack16_known_answers(orc):
+    """5-6-5 full scale is white, zero is black, and a lone top bit lands where bit replication puts it."""
+    def px(v):
+        return np.array([[[v & 255, v >> 8]] * 4] * 2, np.uint8)
+    y = lambda v, inf: int(plane_views(*orc.convert(px(v), 3, 0, 1, 0, in_format=inf), 3, 4, 2)[0][0, 0])   # noqa: E731  bt601 full: Y of grey = grey
+    rep = SPEC["UNPACK16_REPLICATE"]
+    assert y(0xFFFF, 4) == (255 if rep else 250) and y(0, 4) == 0
+    bgrx = N.unpack16(px(0x8410), 4)[0, 0]                 # r5 = 16, g6 = 32, b5 = 16
+    assert list(bgrx[:3]) == ([132, 130, 132] if rep else [128, 128, 128])
+    assert list(N.unpack16(px(0xF800), 4)[0, 0][:3]) == [0, 0, 255 if rep else 248]      # RGB16: top field is red
+    assert list(N.unpack16(px(0xF800), 5)[0, 0][:3]) == [255 if rep else 248, 0, 0]      # BGR16: top field is blue
 
 
 def test_threads_and_pitch_do_not_change_results(orc):
@@ -159,6 +196,8 @@ def test_default_layout_survey_a5(orc):
     total, off, pit = orc.default_layout(1, 2560, 1440)
     assert (total, off[:2], pit[:2]) == (5529600, [0, 3686400], [2560, 2560])
     assert orc.default_layout(0, 1366, 768)[2] == [1368, 684, 684]
+    assert orc.default_layout(2, 1920, 1080) == (4147200, [0, 2073600, 3110400], [1920, 960, 960])     # Y42B
+    assert orc.default_layout(3, 1920, 1080) == (6220800, [0, 2073600, 4147200], [1920, 1920, 1920])   # Y444
 
 
 def test_damage_map_properties(orc):

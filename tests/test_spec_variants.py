@@ -32,7 +32,7 @@ def _env(ov):
 
 def test_variants_cover_every_spec_constant():
     d = S.header_defaults()
-    assert set(d) == set(S.KEYS) and S.name(d) == "m0c1h1b6r1"
+    assert set(d) == set(S.KEYS) and S.name(d) == "m0c1h1b6r1u1"
     flipped = set()
     for ov in S.VARIANTS.values():
         flipped |= {k for k, v in ov.items() if v != d[k]}

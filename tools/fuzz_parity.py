@@ -24,7 +24,7 @@ def static_entry(lib, frame, iw, ih, ow, oh, fmt, m, rg, site, mode, inf):
     d_out = torch.zeros(total, dtype=torch.uint8, device="cuda")
     df = b200vc.DeviceFrames()
     df.bgrx, df.in_pitch, df.in_frame_stride = d_in.data_ptr(), iw * 4, iw * ih * 4
-    for i in range(2 if fmt else 3):
+    for i in range(2 if fmt == 1 else 3):
         df.planes[i], df.pitches[i] = d_out.data_ptr() + off[i], pit[i]
     df.out_frame_stride, df.n_frames = total, 1
     cfg = b200vc.Config(0, iw, ih, ow, oh, fmt, m, rg, site, mode, 0, 0, 0, 0, inf)
@@ -64,13 +64,17 @@ def main():
             ow = max(2, int(iw * rng.uniform(0.3, 1.6)))
             oh = max(2, int(ih * rng.uniform(0.3, 1.6)))
         fmt, m, rg, site, inf = (int(rng.integers(0, 2)) for _ in range(5))
-        inf = int(rng.integers(0, 4))
+        inf = int(rng.integers(0, 6))                       # four 4-byte orders, RGB16, BGR16
         m = int(rng.integers(0, 3))
+        if rng.random() < 0.3:
+            fmt = int(rng.integers(2, 4))                   # Y42B, Y444
+        if rng.random() < 0.3:
+            site = int(rng.choice([2, 3, 7]))               # v-cosited, cosited, dv
         scaling = (ow, oh) != (iw, ih)
         flags = int(rng.choice([0, b200vc.FLAG_FORCE_TWO_PASS, b200vc.FLAG_FORCE_GENERIC_FUSED])) if scaling else \
-            int(rng.choice([0, b200vc.FLAG_DAMAGE_MAP, b200vc.FLAG_ZERO_COPY, b200vc.FLAG_ZERO_COPY_OUT]))
+            int(rng.choice([0, b200vc.FLAG_DAMAGE_MAP if fmt <= 1 else 0, b200vc.FLAG_ZERO_COPY, b200vc.FLAG_ZERO_COPY_OUT]))
         flags |= int(rng.choice([0, b200vc.FLAG_ROW_GATE]))   # how the synchronous call pipelines
-        f = rng.integers(0, 256, (ih, iw, 4), dtype=np.uint8)
+        f = rng.integers(0, 256, (ih, iw, 2 if inf >= 4 else 4), dtype=np.uint8)
         try:
             conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=m, range_=rg, chroma_site=site, scale_mode=mode, flags=flags,
                           in_format=inf, n_bands=int(rng.integers(1, 10)))
@@ -78,7 +82,7 @@ def main():
             if flags & b200vc.FLAG_DAMAGE_MAP:
                 g = f.copy()
                 for _ in range(3):
-                    g[rng.integers(0, ih), rng.integers(0, iw), rng.integers(0, 4)] ^= 0x40
+                    g[rng.integers(0, ih), rng.integers(0, iw), rng.integers(0, g.shape[2])] ^= 0x40
                 conv.transform_frame(f, damage=True)
                 buf, off, pit, dm = conv.transform_frame(g, damage=True)
                 ok = np.array_equal(dm, orc.damage_map(g, f, inf))
@@ -90,7 +94,7 @@ def main():
             for a, b in zip(plane_views(buf, off, pit, fmt, ow, oh), plane_views(*want, fmt, ow, oh)):
                 ok = ok and np.array_equal(a, b)
             # (its device input needs a 16-byte row pitch: widths that are multiples of 4)
-            if scaling and not ((iw | ih | ow | oh) & 1) and iw % 4 == 0 and iw * ih * 3 // 2 <= 2_000_000 and rng.random() < 0.7:
+            if scaling and fmt <= 1 and inf <= 3 and not ((iw | ih | ow | oh) & 1) and iw % 4 == 0 and iw * ih * 3 // 2 <= 2_000_000 and rng.random() < 0.7:
                 got = static_entry(conv.lib, f, iw, ih, ow, oh, fmt, m, rg, site, mode, inf)
                 n_static += 1
                 for a, b in zip(plane_views(got, off, pit, fmt, ow, oh), plane_views(*want, fmt, ow, oh)):

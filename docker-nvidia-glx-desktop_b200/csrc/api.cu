@@ -818,7 +818,7 @@ int create_impl(b200vc_ctx *c)
         std::vector<Tap> hy, vy, hc, vc;
         if (g.scale_mode == B200VC_SCALE_BOX_2X2) {
             build_box_taps(g.out_w, hy);  build_box_taps(g.out_h, vy);
-            build_box_taps(g.out_w / 2, hc);  build_box_taps(g.out_h / 2, vc);   // BOX: even sizes only
+            build_box_taps(c->cw_out, hc);  build_box_taps(c->ch_out, vc);       // BOX: even sizes only; chroma planes by format
         } else {
             build_h_taps(g.in_w, g.out_w, hy);  build_v_taps(g.in_h, g.out_h, vy);
             // chroma planes of odd frames round up, like the intermediate frame's own layout

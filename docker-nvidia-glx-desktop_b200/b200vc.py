@@ -31,7 +31,7 @@ FLAG_ROW_GATE = 64
 
 # every symbol include/b200vc.h declares
 SYMBOLS = [
-    "b200vc_default_colorimetry", "b200vc_default_layout", "b200vc_check_config", "b200vc_status_string",
+    "b200vc_default_colorimetry", "b200vc_default_layout", "b200vc_fit_borders", "b200vc_check_config", "b200vc_status_string",
     "b200vc_version", "b200vc_spec_string", "b200vc_create", "b200vc_destroy", "b200vc_last_error", "b200vc_get_info",
     "b200vc_get_stats", "b200vc_reset", "b200vc_convert", "b200vc_convert_session", "b200vc_convert_batch", "b200vc_submit",
     "b200vc_collect", "b200vc_host_alloc", "b200vc_host_free", "b200vc_convert_device",
@@ -44,7 +44,8 @@ class Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("in_w", C.c_int32), ("in_h", C.c_int32), ("out_w", C.c_int32),
                 ("out_h", C.c_int32), ("out_format", C.c_int32), ("matrix", C.c_int32), ("range", C.c_int32),
                 ("chroma_site", C.c_int32), ("scale_mode", C.c_int32), ("flags", C.c_uint32),
-                ("max_sessions", C.c_int32), ("n_inflight", C.c_int32), ("n_bands", C.c_int32), ("in_format", C.c_int32)]
+                ("max_sessions", C.c_int32), ("n_inflight", C.c_int32), ("n_bands", C.c_int32), ("in_format", C.c_int32),
+                ("content_x", C.c_int32), ("content_y", C.c_int32), ("content_w", C.c_int32), ("content_h", C.c_int32)]
 
 
 class Frame(C.Structure):
@@ -96,6 +97,7 @@ def load() -> C.CDLL:
     L.b200vc_default_colorimetry.argtypes = [i, C.POINTER(i), C.POINTER(i), C.POINTER(i)]
     L.b200vc_default_layout.argtypes = [i, i, i, C.POINTER(sz), C.POINTER(sz)]
     L.b200vc_default_layout.restype = sz
+    L.b200vc_fit_borders.argtypes = [i] * 8 + [C.POINTER(i)] * 4
     L.b200vc_check_config.argtypes = [C.POINTER(Config)]
     L.b200vc_status_string.argtypes = [i]
     L.b200vc_status_string.restype = C.c_char_p
@@ -133,6 +135,15 @@ def default_layout(fmt: int, w: int, h: int):
     off, pit = (C.c_size_t * 3)(), (C.c_size_t * 3)()
     total = load().b200vc_default_layout(fmt, w, h, off, pit)
     return int(total), [int(x) for x in off], [int(x) for x in pit]
+
+
+def fit_borders(in_w: int, in_h: int, out_w: int, out_h: int, in_par=(1, 1), out_par=(1, 1)):
+    """videoscale add-borders: (x, y, w, h) of the picture inside the out_w x out_h frame."""
+    v = [C.c_int() for _ in range(4)]
+    rc = load().b200vc_fit_borders(in_w, in_h, in_par[0], in_par[1], out_w, out_h, out_par[0], out_par[1], *[C.byref(a) for a in v])
+    if rc:
+        raise B200vcError(rc, "bad sizes or pixel-aspect-ratios")
+    return tuple(a.value for a in v)
 
 
 def damage_rects(dmg: np.ndarray, frame_w: int, frame_h: int, max_rects: int = 4096):
@@ -181,7 +192,8 @@ class Converter:
     def set_info(self, in_w: int, in_h: int, out_w: int | None = None, out_h: int | None = None,
                  out_format: int = FMT_I420, matrix: int | None = None, range_: int | None = None,
                  chroma_site: int | None = None, scale_mode: int = SCALE_GST_LQ, flags: int = 0,
-                 max_sessions: int = 1, n_inflight: int = 0, n_bands: int = 0, in_format: int = IN_BGRX) -> None:
+                 max_sessions: int = 1, n_inflight: int = 0, n_bands: int = 0, in_format: int = IN_BGRX,
+                 content: tuple | None = None) -> None:
         out_w, out_h = out_w or in_w, out_h or in_h
         if matrix is None or range_ is None or chroma_site is None:
             dm, dr, ds = default_colorimetry(out_h)   # caps left colorimetry open: defaults by height
@@ -190,7 +202,7 @@ class Converter:
             chroma_site = ds if chroma_site is None else chroma_site
         self.stop()
         cfg = Config(self.device, in_w, in_h, out_w, out_h, out_format, matrix, range_, chroma_site, scale_mode,
-                     flags, max_sessions, n_inflight, n_bands, in_format)
+                     flags, max_sessions, n_inflight, n_bands, in_format, *(content or (0, 0, 0, 0)))
         ctx = C.c_void_p()
         rc = self.lib.b200vc_create(C.byref(cfg), C.byref(ctx))
         if rc:

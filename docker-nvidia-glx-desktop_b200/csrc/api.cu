@@ -76,6 +76,10 @@ typedef CUresult (*WriteValue32Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned i
 
 struct b200vc_ctx {
     b200vc_config cfg;
+    b200vc_config kcfg;                        // cfg as the scaler sees it: out_w x out_h = the picture's rectangle (add-borders)
+    bool borders = false;                      // the picture does not fill the output frame
+    int cont_x = 0, cont_y = 0;                // where it sits
+    int ccw = 0, cch = 0;                      // its chroma plane's samples per line / lines
     bool scaling = false;
     int path = 0;                              // 0 convert, 1 fused scale, 2 two-pass scale
     Matrix mx;
@@ -372,7 +376,7 @@ int check_config(const b200vc_config *c, std::string *why)
     if (c->in_w > 16384 || c->in_h > 16384 || c->out_w > 16384 || c->out_h > 16384)
         return bad(B200VC_ERR_UNSUPPORTED, "width/height above 16384");
     if (c->scale_mode == B200VC_SCALE_BOX_2X2 && ((c->in_w | c->in_h | c->out_w | c->out_h) & 1) &&
-        (c->in_w != c->out_w || c->in_h != c->out_h))
+        (c->in_w != c->out_w || c->in_h != c->out_h || c->content_w))
         return bad(B200VC_ERR_UNSUPPORTED, "BOX_2X2 needs even widths and heights");
     if (c->out_format < B200VC_FMT_I420 || c->out_format > B200VC_FMT_Y444)
         return bad(B200VC_ERR_UNSUPPORTED, "output format must be I420, NV12, Y42B or Y444");
@@ -386,8 +390,17 @@ int check_config(const b200vc_config *c, std::string *why)
         return bad(B200VC_ERR_UNSUPPORTED, "chroma-site must be a combination of h-cosited, v-cosited and alt-line (jpeg, mpeg2, cosited, dv)");
     if (c->scale_mode != B200VC_SCALE_GST_LQ && c->scale_mode != B200VC_SCALE_BOX_2X2)
         return bad(B200VC_ERR_UNSUPPORTED, "unknown scale mode");
-    const bool scaling = c->in_w != c->out_w || c->in_h != c->out_h;
-    if (scaling && c->scale_mode == B200VC_SCALE_BOX_2X2 && (c->in_w != 2 * c->out_w || c->in_h != 2 * c->out_h))
+    int pw = c->out_w, ph = c->out_h;                      // the picture inside the output frame (add-borders)
+    if (c->content_x || c->content_y || c->content_w || c->content_h) {
+        if (c->content_x < 0 || c->content_y < 0 || c->content_w < 2 || c->content_h < 2 ||
+            c->content_x + c->content_w > c->out_w || c->content_y + c->content_h > c->out_h)
+            return bad(B200VC_ERR_INVALID_ARG, "the content rectangle does not lie inside the output frame");
+        if ((c->content_x | c->content_y | c->content_w | c->content_h) & 1)
+            return bad(B200VC_ERR_UNSUPPORTED, "the content rectangle's position and size must be even");
+        pw = c->content_w;  ph = c->content_h;
+    }
+    const bool scaling = c->in_w != pw || c->in_h != ph;
+    if (scaling && c->scale_mode == B200VC_SCALE_BOX_2X2 && (c->in_w != 2 * pw || c->in_h != 2 * ph))
         return bad(B200VC_ERR_UNSUPPORTED, "BOX_2X2 needs an exact 2:1 downscale");
     if (scaling && (c->flags & B200VC_FLAG_DAMAGE_MAP))
         return bad(B200VC_ERR_UNSUPPORTED, "the damage map is produced on the unscaled path only");
@@ -568,16 +581,46 @@ PlaneSet plane_set(uint8_t *base, const size_t off[3], const size_t pitch[3], si
     return ps;
 }
 
+// add-borders: black (in the output's colorimetry: the matrix's answer to RGB 0,0,0) everywhere outside the
+// picture's rectangle of n_frames output frames.
+int fill_borders(b200vc_ctx *c, const PlaneSet &out, int n_frames, cudaStream_t st)
+{
+    const b200vc_config &g = c->cfg;
+    const int (*m)[4] = matrix_rows(g.matrix, g.range);
+    const int rnd = B200VC_SPEC_MATRIX_ROUND ? 128 : 0;
+    const int nv12 = g.out_format == B200VC_FMT_NV12 ? 2 : 1, hs = chroma_hsub(g.out_format);
+    BorderParams b;
+    memset(&b, 0, sizeof b);
+    b.out = out;  b.n_planes = c->n_planes;  b.n_frames = n_frames;
+    for (int i = 0; i < c->n_planes; i++) {
+        b.w[i] = (int)c->prow_bytes[i];  b.h[i] = c->prows[i];
+        b.val[i] = (uint32_t)((m[i ? 1 : 0][3] + rnd) >> 8);
+        b.cx[i] = i ? c->cont_x / hs * nv12 : c->cont_x;
+        b.cy[i] = i ? c->cont_y / c->vsub : c->cont_y;
+        b.cw[i] = i ? c->ccw * nv12 : c->kcfg.out_w;
+        b.ch[i] = i ? c->cch : c->kcfg.out_h;
+    }
+    CU_TRY(c, launch_border_fill(b, st));
+    c->stats.kernel_launches += 1;
+    return B200VC_OK;
+}
+
 const RowGate kNoGate = { nullptr, 0, 0, nullptr };
 
 // Enqueue the kernels for n_frames frames on `st`. Input rows [row0,row0+rows) (unscaled path) or
 // whole frames (scaled paths). `gate` (one frame only): the frame is still arriving, see RowGate.
 int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_t src_fstride,
                     const uint8_t *d_prev, size_t prev_pitch, size_t prev_fstride,
-                    const PlaneSet &out, uint8_t *d_dmg, size_t dmg_fstride,
+                    const PlaneSet &out_frame, uint8_t *d_dmg, size_t dmg_fstride,
                     int row0, int rows, int n_frames, const RowGate &gate, cudaStream_t st)
 {
-    const b200vc_config &g = c->cfg;
+    const b200vc_config &g = c->kcfg;                  // output size = the picture's rectangle inside the frame
+    PlaneSet out = out_frame;
+    if (c->borders) {                                  // whose origin is where the planes start, for the kernels
+        const int cx = c->cont_x / chroma_hsub(g.out_format) * (g.out_format == B200VC_FMT_NV12 ? 2 : 1);
+        out.p[0] += (long long)c->cont_y * out.pitch[0] + c->cont_x;
+        for (int i = 1; i < c->n_planes; i++) out.p[i] += (long long)(c->cont_y / c->vsub) * out.pitch[i] + cx;
+    }
     const int site = (g.chroma_site & B200VC_SITE_H_COSITED) ? 1 : 0;
     if (c->path == 0) {
         ConvertParams p;
@@ -726,7 +769,14 @@ int create_impl(b200vc_ctx *c)
                     g.device, c->prop.name, c->prop.major, c->prop.minor);
 
     c->mx = make_matrix(g.matrix, g.range, g.in_format);
-    c->scaling = g.in_w != g.out_w || g.in_h != g.out_h;
+    c->kcfg = g;
+    if (g.content_w) {
+        c->kcfg.out_w = g.content_w;  c->kcfg.out_h = g.content_h;
+        c->cont_x = g.content_x;  c->cont_y = g.content_y;
+        c->borders = g.content_w != g.out_w || g.content_h != g.out_h;
+    }
+    chroma_dims(g.out_format, c->kcfg.out_w, c->kcfg.out_h, c->ccw, c->cch);
+    c->scaling = g.in_w != c->kcfg.out_w || g.in_h != c->kcfg.out_h;
     c->mb_w = (g.in_w + 15) / 16;
     c->mb_h = (g.in_h + 15) / 16;
     c->maps.reserve(64);
@@ -812,17 +862,24 @@ int create_impl(b200vc_ctx *c)
         memset(s.h_flag_src, 0, (kMaxChunks + 1) * sizeof(uint32_t));
         if (g.flags & B200VC_FLAG_DAMAGE_MAP) CU_TRY(c, cudaMallocHost(&s.h_map, dmg_bytes));
         CU_TRY(c, cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+        // add-borders: the library's own output frames get their black border once; the kernels only ever
+        // write the picture's rectangle, and every download carries the whole frame
+        if (c->borders) {
+            int rc = fill_borders(c, plane_set(s.d_out, c->d_off, c->d_pitch, 0, g.out_format), 1, nullptr);
+            if (rc) return rc;
+        }
     }
 
     if (c->scaling) {
+        const b200vc_config &k = c->kcfg;              // the scaler's geometry: source -> the picture's rectangle
         std::vector<Tap> hy, vy, hc, vc;
         if (g.scale_mode == B200VC_SCALE_BOX_2X2) {
-            build_box_taps(g.out_w, hy);  build_box_taps(g.out_h, vy);
-            build_box_taps(c->cw_out, hc);  build_box_taps(c->ch_out, vc);       // BOX: even sizes only; chroma planes by format
+            build_box_taps(k.out_w, hy);  build_box_taps(k.out_h, vy);
+            build_box_taps(c->ccw, hc);  build_box_taps(c->cch, vc);       // BOX: even sizes only; chroma planes by format
         } else {
-            build_h_taps(g.in_w, g.out_w, hy);  build_v_taps(g.in_h, g.out_h, vy);
+            build_h_taps(g.in_w, k.out_w, hy);  build_v_taps(g.in_h, k.out_h, vy);
             // chroma planes of odd frames round up, like the intermediate frame's own layout
-            build_h_taps(c->cw_in, c->cw_out, hc);  build_v_taps(c->ch_in, c->ch_out, vc);
+            build_h_taps(c->cw_in, c->ccw, hc);  build_v_taps(c->ch_in, c->cch, vc);
         }
         const size_t n = hy.size() + vy.size() + hc.size() + vc.size();       // every size a multiple of 4
         CU_TRY(c, cudaMalloc(&c->d_taps, n * sizeof(Tap)));
@@ -838,7 +895,7 @@ int create_impl(b200vc_ctx *c)
         // 16 -> 32 rows); a window too large for 6 resident CTAs no longer hides its TMA wait
         // (4K -> 720p: 0.78 of the roofline with 8 rows, 0.67 with 16, 0.37 with 32).
         for (c->tile_h = 32; ; c->tile_h /= 2) {
-            fused_box(g, hy, vy, hc, vc, c->tile_h, c->box_w, c->box_h);
+            fused_box(k, hy, vy, hc, vc, c->tile_h, c->box_w, c->box_h);
             c->smem_bytes = fused_scale_smem_bytes(c->box_w, c->box_h);
             if (c->tile_h == 8 || c->smem_bytes + 4096 <= (size_t)c->prop.sharedMemPerMultiprocessor / 6)
                 break;
@@ -850,21 +907,21 @@ int create_impl(b200vc_ctx *c)
         // (and they read 4-byte pixels and make 4:2:0 planes; 16-bit input and Y42B/Y444 output take the two-pass path too)
         const bool fusable = in_bytes_per_pixel(g.in_format) == 4 && g.out_format <= B200VC_FMT_NV12;
         c->path = (fits && fusable && !(g.flags & B200VC_FLAG_FORCE_TWO_PASS) && B200VC_SPEC_SCALE_H_FIRST) ? 1 : 2;
-        const bool exact2 = g.in_w == 2 * g.out_w && g.in_h == 2 * g.out_h && (g.in_w % 4) == 0 && (g.in_h % 4) == 0;
+        const bool exact2 = g.in_w == 2 * k.out_w && g.in_h == 2 * k.out_h && (g.in_w % 4) == 0 && (g.in_h % 4) == 0;
         c->fused2x = c->path == 1 && exact2 && !(g.flags & B200VC_FLAG_FORCE_GENERIC_FUSED) &&
                      (g.scale_mode == B200VC_SCALE_BOX_2X2 ||
-                      (taps_are_2to1(hy, g.out_w, false) && taps_are_2to1(vy, g.out_h, true) &&
-                       taps_are_2to1(hc, g.out_w / 2, false) && taps_are_2to1(vc, g.out_h / 2, true)));
+                      (taps_are_2to1(hy, k.out_w, false) && taps_are_2to1(vy, k.out_h, true) &&
+                       taps_are_2to1(hc, k.out_w / 2, false) && taps_are_2to1(vc, k.out_h / 2, true)));
         if (c->fused2x) {
             c->box_w = K2X_SRC_W + K2X_HALO;
             c->box_h = K2X_SRC_H;
             c->smem_bytes = (size_t)c->box_w * c->box_h * 4;
-            c->inc_y = h_inc(g.in_w, g.out_w);
-            c->inc_c = h_inc(g.in_w / 2, g.out_w / 2);
+            c->inc_y = h_inc(g.in_w, k.out_w);
+            c->inc_c = h_inc(g.in_w / 2, k.out_w / 2);
         }
         if (c->path == 1 && !c->fused2x) {
             FusedTapBlob blob;
-            build_fused_taps(g, hy, vy, hc, vc, c->tile_h, c->box_w, blob);
+            build_fused_taps(k, hy, vy, hc, vc, c->tile_h, c->box_w, blob);
             CU_TRY(c, cudaMalloc(&c->d_ftaps, blob.w.size() * sizeof(uint32_t)));
             CU_TRY(c, cudaMemcpy(c->d_ftaps, blob.w.data(), blob.w.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
             c->ft.tile_x = reinterpret_cast<const int2 *>(c->d_ftaps + blob.tile_x);
@@ -891,8 +948,8 @@ int create_impl(b200vc_ctx *c)
             // about 8:1); larger ratios keep the gather kernel
             std::vector<uint32_t> w;
             size_t o0[4], o1[4];
-            build_plane_tile_taps(hy, vy, g.in_h, g.out_w, g.out_h, c->pt[0], w, o0);
-            build_plane_tile_taps(hc, vc, c->ch_in, c->cw_out, c->ch_out, c->pt[1], w, o1);
+            build_plane_tile_taps(hy, vy, g.in_h, k.out_w, k.out_h, c->pt[0], w, o0);
+            build_plane_tile_taps(hc, vc, c->ch_in, c->ccw, c->cch, c->pt[1], w, o1);
             PlaneTileParams probe;
             memset(&probe, 0, sizeof probe);
             probe.k[0] = c->pt[0];  probe.k[1] = c->pt[1];
@@ -1148,7 +1205,7 @@ int submit_frame(b200vc_ctx *c, Lock &lk, const b200vc_frame *f, bool sync, uint
 
     // B200VC_FLAG_ZERO_COPY: K1 reads the page-locked frame over PCIe and writes the planes back itself
     // (not on contexts that keep previous frames for the damage map: those need the frame in HBM)
-    if ((g.flags & B200VC_FLAG_ZERO_COPY) && !(g.flags & B200VC_FLAG_DAMAGE_MAP) && c->path == 0 && in_pinned && out_pinned) {
+    if ((g.flags & B200VC_FLAG_ZERO_COPY) && !(g.flags & B200VC_FLAG_DAMAGE_MAP) && c->path == 0 && in_pinned && out_pinned && !c->borders) {
         void *d_src = nullptr, *d_pl[3] = { nullptr, nullptr, nullptr };
         bool ok = cudaHostGetDevicePointer(&d_src, const_cast<void *>(f->bgrx), 0) == cudaSuccess;
         for (int i = 0; i < n_planes && ok; i++) ok = cudaHostGetDevicePointer(&d_pl[i], f->planes[i], 0) == cudaSuccess;
@@ -1183,7 +1240,9 @@ int submit_frame(b200vc_ctx *c, Lock &lk, const b200vc_frame *f, bool sync, uint
     // (B200VC_FLAG_ZERO_COPY_OUT), and by itself for the row-gated unscaled call, whose 16-byte row-segment
     // stores cross PCIe well and which has no later frame to hide a device-to-host copy behind.
     bool direct_out = false;
-    if (((g.flags & B200VC_FLAG_ZERO_COPY_OUT) || (sync && c->path == 0)) && out_pinned && map_pinned) {
+    // (Not with add-borders: the caller's buffer would need its border painted every frame; the library's
+    // own frames carry theirs from set-up, and the download takes the whole frame.)
+    if (((g.flags & B200VC_FLAG_ZERO_COPY_OUT) || (sync && c->path == 0)) && out_pinned && map_pinned && !c->borders) {
         void *d_pl[3] = { nullptr, nullptr, nullptr }, *d_map = nullptr;
         bool ok = true;
         for (int i = 0; i < n_planes && ok; i++)
@@ -1202,6 +1261,7 @@ int submit_frame(b200vc_ctx *c, Lock &lk, const b200vc_frame *f, bool sync, uint
     int bands = (sync && !gated && c->path == 0) ? want : 1;                      // launches chained by events
     bands = std::min(bands, (int)c->ev_band_h2d.size());
     bands = std::min(bands, std::max(1, c->mb_h));
+    if (c->borders) bands = 1;                         // (the download is the whole frame, border included)
 
     // the copy engine must not overwrite a frame the previous kernel of this session still reads
     if (ss.ev_valid) {
@@ -1373,6 +1433,30 @@ size_t b200vc_default_layout(int format, int w, int h, size_t offsets[3], size_t
     pitches[1] = pitches[2] = cp;
     offsets[2] = offsets[1] + cp * (h2 / 2);
     return offsets[2] + cp * (h2 / 2);
+}
+
+int b200vc_fit_borders(int in_w, int in_h, int in_par_n, int in_par_d, int out_w, int out_h, int out_par_n, int out_par_d,
+                       int *x, int *y, int *w, int *h)
+{
+    if (in_w < 1 || in_h < 1 || out_w < 2 || out_h < 2 || in_par_n < 1 || in_par_d < 1 || out_par_n < 1 || out_par_d < 1 ||
+        !x || !y || !w || !h)
+        return B200VC_ERR_INVALID_ARG;
+    // gstvideoscale.c set_info, add-borders: the source's display aspect ratio in output pixels is num : den
+    const unsigned long long num = (unsigned long long)in_w * in_par_n * out_par_d, den = (unsigned long long)in_h * in_par_d * out_par_n;
+    *x = *y = 0;  *w = out_w;  *h = out_h;
+    if (num * out_h == den * out_w) return B200VC_OK;                    // same shape: no border
+    const unsigned long long to_h = (unsigned long long)out_w * den / num;
+    if (to_h <= (unsigned long long)out_h) {                             // bars above and below
+        *h = std::max(2, (int)to_h & ~1);
+        *y = ((out_h - *h) / 2) & ~1;
+        *w = out_w & ~1;                                                 // (an odd frame keeps its last column as border)
+    } else {
+        *h = out_h & ~1;                                                             // bars left and right
+        const unsigned long long to_w = (unsigned long long)out_h * num / den;
+        *w = std::max(2, (int)std::min<unsigned long long>(to_w, (unsigned long long)out_w) & ~1);
+        *x = ((out_w - *w) / 2) & ~1;
+    }
+    return B200VC_OK;
 }
 
 int b200vc_damage_to_rects(const uint8_t *map, int frame_w, int frame_h, b200vc_rect *rects, int max_rects)
@@ -1616,6 +1700,10 @@ int b200vc_convert_device(b200vc_ctx *c, const b200vc_device_frames *d, void *cu
         } else {
             CU_TRY(c, cudaMemsetAsync(d->damage, 1, (size_t)c->mb_w * c->mb_h * d->n_frames, st));
         }
+    }
+    if (c->borders) {                                  // the caller's frames: their border is painted with every call
+        int rcb = fill_borders(c, out, d->n_frames, st);
+        if (rcb) return rcb;
     }
     int rc = enqueue_kernels(c, (const uint8_t *)d->bgrx, d->in_pitch, d->in_frame_stride,
                              (const uint8_t *)d->prev, d->prev_pitch, d->prev_frame_stride, out,

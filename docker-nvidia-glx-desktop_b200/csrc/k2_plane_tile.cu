@@ -11,6 +11,8 @@
 // byte gathers are free of bank conflicts, and the tile leaves through shared memory as 16-byte stores —
 // the structure measured on the general fused kernel (profiles/README.md).
 #include "device_utils.cuh"
+
+#include <algorithm>
 #include "kernels.cuh"
 #include "../../include/b200vc_spec.h"
 
@@ -143,6 +145,42 @@ __global__ void __launch_bounds__(256) k2_plane_tile_kernel(const PlaneTileParam
 }
 
 }  // namespace
+
+namespace {
+
+// add-borders: a thread looks at 16 bytes of one row of one plane and writes what lies outside the picture
+__global__ void __launch_bounds__(256) border_fill_kernel(const BorderParams p)
+{
+    const int pl = blockIdx.y, frame = blockIdx.z;
+    if (pl >= p.n_planes) return;
+    const int chunks = (p.w[pl] + 15) >> 4;
+    const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+    const int row = (int)(idx / chunks), x0 = (int)(idx % chunks) * 16;
+    if (row >= p.h[pl]) return;
+    uint8_t *dst = p.out.p[pl] + (long long)frame * p.out.frame_stride + (long long)row * p.out.pitch[pl];
+    const bool row_inside = row >= p.cy[pl] && row < p.cy[pl] + p.ch[pl];
+    const int x1 = min(x0 + 16, p.w[pl]);
+    const uint32_t v = p.val[pl] * 0x01010101u;
+    if ((!row_inside || x1 <= p.cx[pl] || x0 >= p.cx[pl] + p.cw[pl]) && x1 - x0 == 16 && ((p.out.pitch[pl] | (uintptr_t)p.out.p[pl]) & 15) == 0 &&
+        (p.out.frame_stride & 15) == 0) {
+        *reinterpret_cast<uint4 *>(dst + x0) = make_uint4(v, v, v, v);
+        return;
+    }
+    for (int x = x0; x < x1; x++)
+        if (!row_inside || x < p.cx[pl] || x >= p.cx[pl] + p.cw[pl]) dst[x] = (uint8_t)v;
+}
+
+}  // namespace
+
+cudaError_t launch_border_fill(const BorderParams &p, cudaStream_t st)
+{
+    if (p.n_planes < 1 || p.n_planes > 3 || p.n_frames < 1) return cudaErrorInvalidValue;
+    long long most = 0;
+    for (int i = 0; i < p.n_planes; i++) most = std::max(most, (long long)((p.w[i] + 15) >> 4) * p.h[i]);
+    dim3 grid((unsigned)((most + 255) / 256), p.n_planes, p.n_frames);
+    border_fill_kernel<<<grid, 256, 0, st>>>(p);
+    return cudaGetLastError();
+}
 
 size_t plane_tile_smem_bytes(const PlaneTileParams &p, int fmt)
 {

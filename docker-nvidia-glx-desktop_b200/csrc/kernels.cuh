@@ -170,6 +170,18 @@ constexpr int K2X_SRC_H = 32;
 constexpr int K2X_TILES_PER_CTA = 2;   // exact-2:1 kernel: tiles per CTA (the later loads hide behind the first tile's work)
 constexpr int K2X_HALO = 4;      // columns loaded left of the tile (TMA boxes start 16-byte aligned)
 
+// add-borders: fill everything of n_frames output frames that lies outside the picture's rectangle with
+// black (val[i] = the byte for plane i). w/h: bytes per row and rows of each plane; cx/cy/cw/ch: the
+// picture's rectangle in each plane, in bytes and rows.
+struct BorderParams {
+    PlaneSet out;
+    int n_planes, n_frames;
+    int w[3], h[3];
+    int cx[3], cy[3], cw[3], ch[3];
+    uint32_t val[3];
+};
+cudaError_t launch_border_fill(const BorderParams &p, cudaStream_t st);
+
 // Launchers return the cudaError_t of the launch. fmt/site as in b200vc.h.
 cudaError_t launch_convert(const ConvertParams &p, int fmt, int site, cudaStream_t st);
 cudaError_t launch_fused_scale(const CUtensorMap &src_map, const FusedScaleParams &p, int fmt, int site,

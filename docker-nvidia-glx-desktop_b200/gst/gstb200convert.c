@@ -113,10 +113,10 @@ GST_DEBUG_CATEGORY_STATIC(b200convert_debug);
 enum { PROP_0, PROP_DEVICE_ID, PROP_DAMAGE_MAP, PROP_N_BANDS, PROP_ONE_FRAME_LATENCY, PROP_REGISTER_HOST };
 
 static GstStaticPadTemplate sink_tmpl = GST_STATIC_PAD_TEMPLATE("sink", GST_PAD_SINK, GST_PAD_ALWAYS,
-    GST_STATIC_CAPS("video/x-raw, format=(string){BGRx,BGRA,RGBx,RGBA,xRGB,ARGB,xBGR,ABGR}, width=(int)[2,16384], height=(int)[2,16384], "
+    GST_STATIC_CAPS("video/x-raw, format=(string){BGRx,BGRA,RGBx,RGBA,xRGB,ARGB,xBGR,ABGR,RGB16,BGR16}, width=(int)[2,16384], height=(int)[2,16384], "
                     "framerate=(fraction)[0/1,2147483647/1]"));
 static GstStaticPadTemplate src_tmpl = GST_STATIC_PAD_TEMPLATE("src", GST_PAD_SRC, GST_PAD_ALWAYS,
-    GST_STATIC_CAPS("video/x-raw, format=(string){I420,NV12}, width=(int)[2,16384], height=(int)[2,16384], "
+    GST_STATIC_CAPS("video/x-raw, format=(string){I420,NV12,Y42B,Y444}, width=(int)[2,16384], height=(int)[2,16384], "
                     "framerate=(fraction)[0/1,2147483647/1]"));
 
 /* transform_caps: what videoconvert and videoscale do combined — drop format, colorimetry and
@@ -155,6 +155,13 @@ gst_b200_convert_fixate_caps(GstBaseTransform *trans, GstPadDirection direction,
     if (gst_structure_get_int(in, "width", &w)) gst_structure_fixate_field_nearest_int(out, "width", w);
     if (gst_structure_get_int(in, "height", &h)) gst_structure_fixate_field_nearest_int(out, "height", h);
     if (direction == GST_PAD_SINK) gst_structure_fixate_field_string(out, "format", "I420");
+    /* pixel-aspect-ratio: keep the input's where the other side leaves it open (what videoscale prefers); a
+     * different fixed one is honoured, and set_info then letterboxes (add-borders) */
+    if (gst_structure_has_field(out, "pixel-aspect-ratio")) {
+        gint pn = 1, pd = 1;
+        gst_structure_get_fraction(in, "pixel-aspect-ratio", &pn, &pd);
+        gst_structure_fixate_field_nearest_fraction(out, "pixel-aspect-ratio", pn, pd);
+    }
     return gst_caps_fixate(othercaps);
 }
 
@@ -164,6 +171,8 @@ static int in_format_of(const GstVideoInfo *i)
     case GST_VIDEO_FORMAT_RGBx: case GST_VIDEO_FORMAT_RGBA: return B200VC_IN_RGBX;
     case GST_VIDEO_FORMAT_xRGB: case GST_VIDEO_FORMAT_ARGB: return B200VC_IN_XRGB;
     case GST_VIDEO_FORMAT_xBGR: case GST_VIDEO_FORMAT_ABGR: return B200VC_IN_XBGR;
+    case GST_VIDEO_FORMAT_RGB16: return B200VC_IN_RGB16;      /* ximagesrc at CDEPTH=16 */
+    case GST_VIDEO_FORMAT_BGR16: return B200VC_IN_BGR16;
     default: return B200VC_IN_BGRX;   /* BGRx, BGRA: what ximagesrc delivers at depth 24/32 */
     }
 }
@@ -247,14 +256,28 @@ gst_b200_convert_set_info(GstVideoFilter *filter, GstCaps *incaps, GstVideoInfo 
     cfg.in_w = GST_VIDEO_INFO_WIDTH(in);    cfg.in_h = GST_VIDEO_INFO_HEIGHT(in);
     cfg.out_w = GST_VIDEO_INFO_WIDTH(out);  cfg.out_h = GST_VIDEO_INFO_HEIGHT(out);
     cfg.in_format = in_format_of(in);
-    cfg.out_format = GST_VIDEO_INFO_FORMAT(out) == GST_VIDEO_FORMAT_NV12 ? B200VC_FMT_NV12 : B200VC_FMT_I420;
+    /* videoscale add-borders (its default): keep the display aspect ratio, black bars around the picture */
+    if (b200vc_fit_borders(cfg.in_w, cfg.in_h, GST_VIDEO_INFO_PAR_N(in), GST_VIDEO_INFO_PAR_D(in), cfg.out_w, cfg.out_h,
+                           GST_VIDEO_INFO_PAR_N(out), GST_VIDEO_INFO_PAR_D(out), &cfg.content_x, &cfg.content_y,
+                           &cfg.content_w, &cfg.content_h) != B200VC_OK ||
+        (cfg.content_w == cfg.out_w && cfg.content_h == cfg.out_h))
+        cfg.content_x = cfg.content_y = cfg.content_w = cfg.content_h = 0;
+    switch (GST_VIDEO_INFO_FORMAT(out)) {
+    case GST_VIDEO_FORMAT_NV12: cfg.out_format = B200VC_FMT_NV12; break;
+    case GST_VIDEO_FORMAT_Y42B: cfg.out_format = B200VC_FMT_Y42B; break;
+    case GST_VIDEO_FORMAT_Y444: cfg.out_format = B200VC_FMT_Y444; break;
+    default: cfg.out_format = B200VC_FMT_I420; break;
+    }
     /* honour the caps, do not assume */
     cfg.matrix = out->colorimetry.matrix == GST_VIDEO_COLOR_MATRIX_UNKNOWN ? m : matrix_of(out);
     cfg.range = out->colorimetry.range == GST_VIDEO_COLOR_RANGE_UNKNOWN ? r
               : (out->colorimetry.range == GST_VIDEO_COLOR_RANGE_0_255 ? B200VC_RANGE_FULL : B200VC_RANGE_LIMITED);
     cfg.chroma_site = out->chroma_site == GST_VIDEO_CHROMA_SITE_UNKNOWN ? s
-                    : ((out->chroma_site & GST_VIDEO_CHROMA_SITE_H_COSITED) ? B200VC_SITE_H_COSITED : B200VC_SITE_NONE);
-    self->cur_damage_map = want_damage && cfg.in_w == cfg.out_w && cfg.in_h == cfg.out_h;   /* the map exists on the unscaled path */
+                    : (((out->chroma_site & GST_VIDEO_CHROMA_SITE_H_COSITED) ? B200VC_SITE_H_COSITED : 0) |
+                       ((out->chroma_site & GST_VIDEO_CHROMA_SITE_V_COSITED) ? B200VC_SITE_V_COSITED : 0) |
+                       ((out->chroma_site & GST_VIDEO_CHROMA_SITE_ALT_LINE) ? B200VC_SITE_ALT_LINE : 0));
+    self->cur_damage_map = want_damage && cfg.in_w == (cfg.content_w ? cfg.content_w : cfg.out_w) &&
+                           cfg.in_h == (cfg.content_h ? cfg.content_h : cfg.out_h);          /* the map exists on the unscaled path */
     cfg.flags = self->cur_damage_map ? B200VC_FLAG_DAMAGE_MAP : 0;
     /* Off by default: page-locking on first sight is for upstream buffers that come from a small long-lived
      * pool (ximagesrc with XShm). Buffers malloc'd per frame would stay locked after they are freed, and an

@@ -37,7 +37,7 @@ extern "C" {
 #endif
 
 #define B200VC_VERSION_MAJOR 0
-#define B200VC_VERSION_MINOR 1
+#define B200VC_VERSION_MINOR 2
 
 /* ---- status codes ------------------------------------------------------------------------- */
 enum {
@@ -121,6 +121,11 @@ typedef struct b200vc_config {
     int32_t n_bands;       /* bands of rows a synchronous convert is pipelined in (0 -> measured
                               best: 4 when the kernels store into page-locked planes, else 2)      */
     int32_t in_format;     /* B200VC_IN_* (0 = BGRx)                                               */
+    /* videoscale add-borders: where the scaled picture sits inside the out_w x out_h frame when the
+     * display aspect ratios of the two sides differ (letterbox / pillarbox; b200vc_fit_borders computes
+     * it from the pixel-aspect-ratios the way videoscale's set_info does). The rest of the frame is
+     * black in the output's colorimetry. All four 0 = the picture fills the frame. x, y, w, h even. */
+    int32_t content_x, content_y, content_w, content_h;
 } b200vc_config;
 
 typedef struct b200vc_ctx b200vc_ctx;
@@ -178,6 +183,14 @@ int b200vc_default_colorimetry(int out_h, int *matrix, int *range, int *chroma_s
 
 /* video-info.c default strides/offsets for I420/NV12. Returns the frame size. */
 size_t b200vc_default_layout(int format, int w, int h, size_t offsets[3], size_t pitches[3]);
+
+/* GstVideoScale::set_info with add-borders=true (its default): the rectangle of the out_w x out_h frame
+ * the picture is scaled into so that its display aspect ratio (width x par_n : height x par_d) is kept,
+ * centred, the rest being border. Sizes are rounded down to even and positions to even (4:2:0 chroma
+ * sites; videoconvert aligns the position the same way, the size it leaves odd — a deviation, noted in
+ * DESIGN.md). Equal aspect ratios give the whole frame. */
+int b200vc_fit_borders(int in_w, int in_h, int in_par_n, int in_par_d, int out_w, int out_h, int out_par_n, int out_par_d,
+                       int *x, int *y, int *w, int *h);
 
 /* transform_caps/set_caps acceptance test: B200VC_OK, or the reason the caps are refused. */
 int b200vc_check_config(const b200vc_config *cfg);

@@ -122,7 +122,8 @@ class Oracle:
         return buf, off, pit, ptrs, pits
 
     def convert(self, frame: np.ndarray, fmt=FMT_I420, matrix=MATRIX_BT601, rng=RANGE_LIMITED,
-                site=SITE_NONE, out_size=None, scale_mode=SCALE_GST_LQ, pitches=None, threads=1, in_format=IN_BGRX):
+                site=SITE_NONE, out_size=None, scale_mode=SCALE_GST_LQ, pitches=None, threads=1, in_format=IN_BGRX,
+                content=None):
         """frame: (h, w, 4) uint8 pixels, or (h, w, 2) for the 16-bit formats (may be a strided view).
         Returns (buf, offsets, pitches)."""
         h, w = frame.shape[:2]
@@ -130,6 +131,22 @@ class Oracle:
         assert frame.dtype == np.uint8 and frame.shape[2] == bpp and frame.strides[2] == 1 and frame.strides[1] == bpp
         ow, oh = out_size if out_size else (w, h)
         buf, off, pit, ptrs, pits = self._planes(fmt, ow, oh, pitches)
+        if content and tuple(content) != (0, 0, ow, oh):
+            # videoscale add-borders (gst_video_converter with a destination rectangle and fill-border): the
+            # frame is black in the output's colorimetry — the matrix's answer to RGB 0,0,0 — and the picture is
+            # converted and scaled into its rectangle (plane pointers moved to the rectangle's origin)
+            cx, cy, cw, ch = content
+            hs, vs = (1 if fmt == FMT_Y444 else 2), (2 if fmt <= FMT_NV12 else 1)
+            black = self.matrix(matrix, rng)[:, 3] >> 8
+            rows = [oh, oh if fmt >= FMT_Y42B else (oh + 1) // 2]
+            buf[off[0]:off[0] + pit[0] * rows[0]] = black[0]
+            for p in range(1, 2 if fmt == FMT_NV12 else 3):
+                buf[off[p]:off[p] + pit[p] * rows[1]] = black[1]
+            shifted = [buf.ctypes.data + off[0] + cy * pit[0] + cx]
+            for p in range(1, 2 if fmt == FMT_NV12 else 3):
+                shifted.append(buf.ctypes.data + off[p] + (cy // vs) * pit[p] + (cx // hs) * (2 if fmt == FMT_NV12 else 1))
+            ptrs = (C.c_void_p * 3)(*(shifted + [None] * (3 - len(shifted))))
+            ow, oh = cw, ch
         rc = self.lib.orc_convert_scale_mt_ex(frame.ctypes.data, frame.strides[0], in_format, w, h, ow, oh, fmt, matrix,
                                               rng, site, scale_mode, ptrs, pits, threads)
         if rc:

@@ -163,6 +163,30 @@ def convert_scale(frame, out_w, out_h, fmt, matrix, rng, site, mode=0, in_format
     return tuple(out)
 
 
+def convert_scale_borders(frame, out_w, out_h, content, fmt, matrix, rng, site, mode=0, in_format=0):
+    """videoscale add-borders: the picture converted and scaled into the rectangle content = (x, y, w, h) of an
+    out_w x out_h frame that is otherwise black in the output's colorimetry ((off) >> 8 of the matrix rows)."""
+    cx, cy, cw, ch = content
+    pic = convert_scale(frame, cw, ch, fmt, matrix, rng, site, mode, in_format)
+    rows = MATRICES[(matrix, rng)]
+    rnd = 128 if SPEC["MATRIX_ROUND"] else 0
+    by, bc = (rows[0][3] + rnd) >> 8, (rows[1][3] + rnd) >> 8
+    hs, vs = (1 if fmt == 3 else 2), (2 if fmt <= 1 else 1)
+    ocw, och = (out_w + hs - 1) // hs, (out_h + vs - 1) // vs
+    y = np.full((out_h, out_w), by, np.uint8)
+    y[cy:cy + ch, cx:cx + cw] = pic[0]
+    if fmt == 1:
+        uv = np.full((och, 2 * ocw), bc, np.uint8)
+        uv[cy // 2:cy // 2 + pic[1].shape[0], cx:cx + pic[1].shape[1]] = pic[1]
+        return y, uv
+    out = [y]
+    for p in pic[1:]:
+        c = np.full((och, ocw), bc, np.uint8)
+        c[cy // vs:cy // vs + p.shape[0], cx // hs:cx // hs + p.shape[1]] = p
+        out.append(c)
+    return tuple(out)
+
+
 def damage_map(cur: np.ndarray, prev: np.ndarray | None, in_format: int = 0) -> np.ndarray:
     h, w = cur.shape[:2]
     mh, mw = (h + 15) // 16, (w + 15) // 16

@@ -98,6 +98,8 @@ gboolean gst_structure_has_field(const GstStructure *, const gchar *);
 gboolean gst_structure_get_int(const GstStructure *, const gchar *, gint *);
 gboolean gst_structure_fixate_field_nearest_int(GstStructure *, const gchar *, gint);
 gboolean gst_structure_fixate_field_string(GstStructure *, const gchar *, const gchar *);
+gboolean gst_structure_get_fraction(const GstStructure *, const gchar *, gint *, gint *);
+gboolean gst_structure_fixate_field_nearest_fraction(GstStructure *, const gchar *, gint, gint);
 GstCaps *gst_pad_get_pad_template_caps(GstPad *);
 void gst_element_class_add_static_pad_template(GstElementClass *, GstStaticPadTemplate *);
 void gst_element_class_set_static_metadata(GstElementClass *, const gchar *, const gchar *, const gchar *, const gchar *);
@@ -161,22 +163,27 @@ typedef struct _GstBaseTransformClass {
 /* ---- video --------------------------------------------------------------------------------------------- */
 typedef enum { GST_VIDEO_FORMAT_UNKNOWN, GST_VIDEO_FORMAT_I420 = 2, GST_VIDEO_FORMAT_RGBx = 7, GST_VIDEO_FORMAT_BGRx,
                GST_VIDEO_FORMAT_xRGB, GST_VIDEO_FORMAT_xBGR, GST_VIDEO_FORMAT_RGBA, GST_VIDEO_FORMAT_BGRA,
-               GST_VIDEO_FORMAT_ARGB, GST_VIDEO_FORMAT_ABGR, GST_VIDEO_FORMAT_NV12 = 23 } GstVideoFormat;
+               GST_VIDEO_FORMAT_ARGB, GST_VIDEO_FORMAT_ABGR, GST_VIDEO_FORMAT_Y42B = 19, GST_VIDEO_FORMAT_Y444 = 20,
+               GST_VIDEO_FORMAT_NV12 = 23, GST_VIDEO_FORMAT_RGB16 = 29, GST_VIDEO_FORMAT_BGR16 = 30 } GstVideoFormat;
 typedef enum { GST_VIDEO_COLOR_RANGE_UNKNOWN, GST_VIDEO_COLOR_RANGE_0_255, GST_VIDEO_COLOR_RANGE_16_235 } GstVideoColorRange;
 typedef enum { GST_VIDEO_COLOR_MATRIX_UNKNOWN, GST_VIDEO_COLOR_MATRIX_RGB, GST_VIDEO_COLOR_MATRIX_FCC, GST_VIDEO_COLOR_MATRIX_BT709,
                GST_VIDEO_COLOR_MATRIX_BT601, GST_VIDEO_COLOR_MATRIX_SMPTE240M, GST_VIDEO_COLOR_MATRIX_BT2020 } GstVideoColorMatrix;
-typedef enum { GST_VIDEO_CHROMA_SITE_UNKNOWN = 0, GST_VIDEO_CHROMA_SITE_NONE = 1, GST_VIDEO_CHROMA_SITE_H_COSITED = 2 } GstVideoChromaSite;
+typedef enum { GST_VIDEO_CHROMA_SITE_UNKNOWN = 0, GST_VIDEO_CHROMA_SITE_NONE = 1, GST_VIDEO_CHROMA_SITE_H_COSITED = 2,
+               GST_VIDEO_CHROMA_SITE_V_COSITED = 4, GST_VIDEO_CHROMA_SITE_ALT_LINE = 8 } GstVideoChromaSite;
 typedef struct { GstVideoColorRange range; GstVideoColorMatrix matrix; int transfer, primaries; } GstVideoColorimetry;
 typedef struct _GstVideoInfo {
     GstVideoFormat format; gint width, height; gsize size; GstVideoChromaSite chroma_site; GstVideoColorimetry colorimetry;
     gint stride[4];
     gint fps_n, fps_d;
+    gint par_n, par_d;
 } GstVideoInfo;
 typedef struct _GstVideoFrame { GstVideoInfo info; GstBuffer *buffer; gpointer data[4]; gint n_planes; } GstVideoFrame;
 #define GST_VIDEO_INFO_FORMAT(i) ((i)->format)
 #define GST_VIDEO_INFO_WIDTH(i) ((i)->width)
 #define GST_VIDEO_INFO_HEIGHT(i) ((i)->height)
 #define GST_VIDEO_INFO_SIZE(i) ((i)->size)
+#define GST_VIDEO_INFO_PAR_N(i) ((i)->par_n)
+#define GST_VIDEO_INFO_PAR_D(i) ((i)->par_d)
 #define GST_VIDEO_INFO_FPS_N(i) ((i)->fps_n)
 #define GST_VIDEO_INFO_FPS_D(i) ((i)->fps_d)
 #define GST_VIDEO_FRAME_WIDTH(f) ((f)->info.width)

@@ -30,7 +30,7 @@ def test_header_and_library_agree(lib):
 
 def test_struct_sizes_match_the_header():
     # the header's structs, laid out by hand (LP64): catches a drifting ctypes mirror
-    assert C.sizeof(b200vc.Config) == 15 * 4
+    assert C.sizeof(b200vc.Config) == 19 * 4
     assert C.sizeof(b200vc.Frame) == 8 + 8 + 24 + 24 + 8 + 4 + 4
     assert C.sizeof(b200vc.DeviceFrames) == 3 * 8 + 3 * 8 + 24 + 24 + 8 + 8 + 8 + 4 + 4
     assert C.sizeof(b200vc.Stats) == 6 * 8
@@ -38,7 +38,7 @@ def test_struct_sizes_match_the_header():
 
 
 def test_version_and_status_strings(lib):
-    assert lib.b200vc_version() == 1
+    assert lib.b200vc_version() == 2
     assert lib.b200vc_status_string(0) == b"ok"
     assert b"sm_100" in lib.b200vc_status_string(b200vc.ERR_NO_DEVICE)
 
@@ -61,7 +61,8 @@ def test_default_layout_matches_oracle(orc, fmt, w, h):
 
 def _cfg(**kw):
     base = dict(device=0, in_w=1920, in_h=1080, out_w=1920, out_h=1080, out_format=0, matrix=0, range=0,
-                chroma_site=0, scale_mode=0, flags=0, max_sessions=1, n_inflight=0, n_bands=0, in_format=0)
+                chroma_site=0, scale_mode=0, flags=0, max_sessions=1, n_inflight=0, n_bands=0, in_format=0,
+                content_x=0, content_y=0, content_w=0, content_h=0)
     base.update(kw)
     return b200vc.Config(**base)
 
@@ -90,6 +91,34 @@ def test_caps_acceptance(lib):
         assert lib.b200vc_check_config(C.byref(c)) == want
         assert lib.b200vc_last_error(None)          # a reason is always given
     assert lib.b200vc_check_config(None) == b200vc.ERR_INVALID_ARG
+
+
+def test_fit_borders_like_videoscale_add_borders():
+    # 16:9 into 5:4: bars above and below
+    assert b200vc.fit_borders(1920, 1080, 1280, 1024) == (0, 152, 1280, 720)
+    # 4:3 into 16:9: bars left and right
+    assert b200vc.fit_borders(1024, 768, 1920, 1080) == (240, 0, 1440, 1080)
+    # same shape (any scale): the whole frame
+    assert b200vc.fit_borders(3840, 2160, 1920, 1080) == (0, 0, 1920, 1080)
+    # anamorphic source (PAR 4:3 on 1440x1080 = 16:9 display) into square-pixel 1280x720: fills it
+    assert b200vc.fit_borders(1440, 1080, 1280, 720, in_par=(4, 3)) == (0, 0, 1280, 720)
+    # and into a 4:3 frame of square pixels: letterboxed; sizes and positions come out even
+    x, y, w, h = b200vc.fit_borders(1440, 1080, 1024, 768, in_par=(4, 3))
+    assert (x, w) == (0, 1024) and h == 576 and y == 96
+    x, y, w, h = b200vc.fit_borders(1366, 768, 1001, 700)
+    assert x % 2 == 0 and y % 2 == 0 and w % 2 == 0 and h % 2 == 0 and x + w <= 1001 and y + h <= 700
+
+
+def test_content_rectangle_checks(lib):
+    ok = _cfg(in_w=1920, in_h=1080, out_w=1280, out_h=1024, content_x=0, content_y=152, content_w=1280, content_h=720)
+    assert lib.b200vc_check_config(C.byref(ok)) == b200vc.OK
+    # unscaled picture inside a bigger frame, with the damage map: the scaler is not involved
+    ok = _cfg(in_w=1280, in_h=720, out_w=1280, out_h=1024, content_y=152, content_w=1280, content_h=720, flags=b200vc.FLAG_DAMAGE_MAP)
+    assert lib.b200vc_check_config(C.byref(ok)) == b200vc.OK
+    for bad, want in [(_cfg(out_w=1280, out_h=1024, content_y=400, content_w=1280, content_h=720), b200vc.ERR_INVALID_ARG),   # sticks out
+                      (_cfg(out_w=1280, out_h=1024, content_x=1, content_w=1278, content_h=720), b200vc.ERR_UNSUPPORTED),     # odd position
+                      (_cfg(out_w=1280, out_h=1024, content_w=1280, content_h=0), b200vc.ERR_INVALID_ARG)]:
+        assert lib.b200vc_check_config(C.byref(bad)) == want
 
 
 def test_calls_before_negotiation_fail(lib):

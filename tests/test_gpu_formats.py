@@ -133,3 +133,52 @@ def test_device_entry_point_and_batches_with_new_formats(conv, orc):
     assert conv.stats().d2h_bytes == n * total
     pin_in.free()
     pin_out.free()
+
+
+@pytest.mark.parametrize("geo", [(1920, 1080, 1280, 1024), (1024, 768, 1920, 1080), (1280, 720, 1280, 1024), (3840, 2160, 1920, 1200),
+                                 (640, 360, 322, 200)])
+def test_add_borders(conv, orc, geo):
+    """videoscale add-borders: the picture keeps its display aspect ratio inside the output frame (b200vc_fit_borders), the
+    rest is black in the output's colorimetry. Unscaled-in-a-bigger-frame, fused and two-pass paths, all four output formats;
+    synchronous call with pageable and with page-locked buffers, and the device entry point."""
+    import torch
+    iw, ih, ow, oh = geo
+    content = b200vc.fit_borders(iw, ih, ow, oh)
+    assert content != (0, 0, ow, oh)
+    frame = orc.synth("rand", iw, ih, 44)
+    for fmt, m, rg, site, flags in [(0, 1, 0, 1, 0), (1, 0, 1, 0, 0), (2, 1, 0, 1, 0), (3, 2, 1, 0, 0), (0, 0, 0, 1, b200vc.FLAG_FORCE_TWO_PASS)]:
+        scaled = (iw, ih) != content[2:]
+        conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=m, range_=rg, chroma_site=site, flags=flags if scaled else 0, content=content)
+        obuf, ooff, opit = orc.convert(frame, fmt, m, rg, site, out_size=(ow, oh), content=content)
+        want = plane_views(obuf, ooff, opit, fmt, ow, oh)
+        buf, off, pit = conv.transform_frame(frame)
+        assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), want, f"{geo} fmt{fmt} pageable")
+        total = b200vc.default_layout(fmt, ow, oh)[0]
+        pin_in, pin_out = b200vc.PinnedBuffer(iw * ih * 4), b200vc.PinnedBuffer(total)
+        pin_in.array[:] = frame.reshape(-1)
+        pin_out.array[:] = 0x5A                               # a recycled buffer: the border must be painted
+        buf, off, pit = conv.transform_frame(pin_in.array.reshape(ih, iw, 4), out=pin_out.array)
+        assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), want, f"{geo} fmt{fmt} pinned")
+        if all(p % 16 == 0 for p in pit[:2 if fmt == 1 else 3]) and all(o % 16 == 0 for o in off[:2 if fmt == 1 else 3]) and total % 16 == 0:
+            d_in = torch.from_numpy(np.stack([frame.reshape(-1)] * 2)).cuda()
+            d_out = torch.full((2, total), 0x5A, dtype=torch.uint8, device="cuda")
+            df = b200vc.DeviceFrames()
+            df.bgrx, df.in_pitch, df.in_frame_stride = d_in.data_ptr(), iw * 4, iw * ih * 4
+            for i in range(2 if fmt == 1 else 3):
+                df.planes[i], df.pitches[i] = d_out.data_ptr() + off[i], pit[i]
+            df.out_frame_stride, df.n_frames = total, 2
+            conv.convert_device(df, 0)
+            torch.cuda.synchronize()
+            got = d_out.cpu().numpy()
+            for k in range(2):
+                assert_planes_equal(plane_views(got[k], off, pit, fmt, ow, oh), want, f"{geo} fmt{fmt} device frame {k}")
+        pin_in.free()
+        pin_out.free()
+    # the border is black: Y 16 (limited range), chroma 128
+    conv.set_info(iw, ih, ow, oh, matrix=1, range_=0, chroma_site=1, content=content)
+    buf, off, pit = conv.transform_frame(frame)
+    y, u, v = plane_views(buf, off, pit, 0, ow, oh)
+    cx, cy, cw, ch = content
+    mask = np.ones((oh, ow), bool)
+    mask[cy:cy + ch, cx:cx + cw] = False
+    assert (y[mask] == 16).all() and (u[0 if cy else slice(None), 0] == 128).all()

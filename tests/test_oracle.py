@@ -133,6 +133,18 @@ def test_c_equals_numpy_more_formats(orc, size):
     assert np.array_equal(orc.convert(f4, 0, 1, 0, 0)[0], orc.convert(f4, 0, 1, 0, 2)[0])
 
 
+@pytest.mark.parametrize("geo", [(64, 36, 40, 32, (0, 4, 40, 22)), (40, 30, 64, 36, (8, 0, 48, 36)), (36, 20, 48, 30, (6, 4, 36, 20))])
+def test_c_equals_numpy_borders(orc, geo):
+    """add-borders: the picture in a rectangle of the frame, black around it (scaled and unscaled, every format)."""
+    iw, ih, ow, oh, content = geo
+    frame = np.random.default_rng(iw).integers(0, 256, (ih, iw, 4), dtype=np.uint8)
+    for fmt in (0, 1, 2, 3):
+        for m, rg in ((1, 0), (0, 1)):
+            buf, off, pit = orc.convert(frame, fmt, m, rg, 1, out_size=(ow, oh), content=content)
+            assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh),
+                                list(N.convert_scale_borders(frame, ow, oh, content, fmt, m, rg, 1)), f"{geo} fmt{fmt}")
+
+
 def test_unpack16_known_answers(orc):
     """5-6-5 full scale is white, zero is black, and a lone top bit lands where bit replication puts it."""
     def px(v):

@@ -74,10 +74,17 @@ def main():
         flags = int(rng.choice([0, b200vc.FLAG_FORCE_TWO_PASS, b200vc.FLAG_FORCE_GENERIC_FUSED])) if scaling else \
             int(rng.choice([0, b200vc.FLAG_DAMAGE_MAP if fmt <= 1 else 0, b200vc.FLAG_ZERO_COPY, b200vc.FLAG_ZERO_COPY_OUT]))
         flags |= int(rng.choice([0, b200vc.FLAG_ROW_GATE]))   # how the synchronous call pipelines
+        content = None
+        if rng.random() < 0.15 and ow >= 8 and oh >= 8 and mode == 0:       # add-borders: the picture in a rectangle of the frame
+            cw, ch = int(rng.integers(1, ow // 2 + 1)) * 2, int(rng.integers(1, oh // 2 + 1)) * 2
+            content = (int(rng.integers(0, (ow - cw) // 2 + 1)) * 2, int(rng.integers(0, (oh - ch) // 2 + 1)) * 2, cw, ch)
+            scaling = (cw, ch) != (iw, ih)
+            if scaling:
+                flags = int(rng.choice([0, b200vc.FLAG_FORCE_TWO_PASS, b200vc.FLAG_FORCE_GENERIC_FUSED])) | (flags & b200vc.FLAG_ROW_GATE)
         f = rng.integers(0, 256, (ih, iw, 2 if inf >= 4 else 4), dtype=np.uint8)
         try:
             conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=m, range_=rg, chroma_site=site, scale_mode=mode, flags=flags,
-                          in_format=inf, n_bands=int(rng.integers(1, 10)))
+                          in_format=inf, n_bands=int(rng.integers(1, 10)), content=content)
             paths[conv.info().path] += 1
             if flags & b200vc.FLAG_DAMAGE_MAP:
                 g = f.copy()
@@ -90,11 +97,11 @@ def main():
             else:
                 buf, off, pit = conv.transform_frame(f)
                 ok = True
-            want = orc.convert(f, fmt, m, rg, site, out_size=(ow, oh), scale_mode=mode, in_format=inf)
+            want = orc.convert(f, fmt, m, rg, site, out_size=(ow, oh), scale_mode=mode, in_format=inf, content=content)
             for a, b in zip(plane_views(buf, off, pit, fmt, ow, oh), plane_views(*want, fmt, ow, oh)):
                 ok = ok and np.array_equal(a, b)
             # (its device input needs a 16-byte row pitch: widths that are multiples of 4)
-            if scaling and fmt <= 1 and inf <= 3 and not ((iw | ih | ow | oh) & 1) and iw % 4 == 0 and iw * ih * 3 // 2 <= 2_000_000 and rng.random() < 0.7:
+            if scaling and content is None and fmt <= 1 and inf <= 3 and not ((iw | ih | ow | oh) & 1) and iw % 4 == 0 and iw * ih * 3 // 2 <= 2_000_000 and rng.random() < 0.7:
                 got = static_entry(conv.lib, f, iw, ih, ow, oh, fmt, m, rg, site, mode, inf)
                 n_static += 1
                 for a, b in zip(plane_views(got, off, pit, fmt, ow, oh), plane_views(*want, fmt, ow, oh)):
@@ -104,7 +111,7 @@ def main():
             print("EXC", e)
         if not ok:
             bad += 1
-            print("MISMATCH", dict(iw=iw, ih=ih, ow=ow, oh=oh, fmt=fmt, m=m, rg=rg, site=site, inf=inf, flags=flags, mode=mode), flush=True)
+            print("MISMATCH", dict(iw=iw, ih=ih, ow=ow, oh=oh, fmt=fmt, m=m, rg=rg, site=site, inf=inf, flags=flags, mode=mode, content=content), flush=True)
     print(f"{n} cases, {bad} mismatches, paths used {paths}, no-allocation entry point {n_static}, spec {lib_spec}")
     conv.stop()
     return 1 if bad else 0

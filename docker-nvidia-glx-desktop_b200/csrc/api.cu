@@ -570,6 +570,14 @@ int get_tensor_map(b200vc_ctx *c, const void *base, size_t pitch, size_t frame_s
     return B200VC_OK;
 }
 
+void set_alignment(PlaneSet &ps)
+{
+    uintptr_t bits = (uintptr_t)ps.frame_stride;
+    for (int i = 0; i < 3; i++)
+        if (ps.p[i]) bits |= (uintptr_t)ps.p[i] | (uintptr_t)ps.pitch[i];
+    ps.aligned16 = (bits & 15) == 0;
+}
+
 PlaneSet plane_set(uint8_t *base, const size_t off[3], const size_t pitch[3], size_t frame_stride, int fmt)
 {
     PlaneSet ps;
@@ -578,6 +586,7 @@ PlaneSet plane_set(uint8_t *base, const size_t off[3], const size_t pitch[3], si
         ps.pitch[i] = (long long)pitch[i];
     }
     ps.frame_stride = (long long)frame_stride;
+    set_alignment(ps);
     return ps;
 }
 
@@ -621,6 +630,7 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         out.p[0] += (long long)c->cont_y * out.pitch[0] + c->cont_x;
         for (int i = 1; i < c->n_planes; i++) out.p[i] += (long long)(c->cont_y / c->vsub) * out.pitch[i] + cx;
     }
+    set_alignment(out);
     const int site = (g.chroma_site & B200VC_SITE_H_COSITED) ? 1 : 0;
     if (c->path == 0) {
         ConvertParams p;
@@ -706,7 +716,7 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         for (int i = 0; i < 3; i++) if (q.out.p[i]) q.out.p[i] += (size_t)f0 * out.frame_stride;
         q.tab = c->tab;
         q.in_w = g.in_w;  q.in_h = g.in_h;  q.out_w = g.out_w;  q.out_h = g.out_h;  q.n_frames = nf;
-        q.c_out_w = c->cw_out;  q.c_out_h = c->ch_out;
+        q.c_out_w = c->ccw;  q.c_out_h = c->cch;             // (of the picture, not of a bordered frame)
         q.box2x2 = g.scale_mode == B200VC_SCALE_BOX_2X2;
         CU_TRY(c, launch_plane_scale(q, g.out_format == B200VC_FMT_NV12 ? 1 : 0, st));
         c->stats.kernel_launches += 2;

@@ -73,15 +73,15 @@ __device__ __noinline__ void store_tail(uint8_t *dst, const uint8_t *src, int va
 // Output that nothing on the GPU reads again goes out with the streaming hint (st.global.cs): measured
 // +2-4 % on every K1 variant (the planes stop displacing the input stream in L2). The intermediate frame of
 // the two-pass path is read back by pass 2 and keeps plain stores.
-__device__ __forceinline__ void store16(uint8_t *dst, const uint8_t *src, int valid, bool streaming)
+__device__ __forceinline__ void store16(uint8_t *dst, const uint8_t *src, int valid, bool streaming, bool vec)
 {
-    if (valid >= 16) {
+    if (valid >= 16 && vec) {
         if (streaming)
             __stcs(reinterpret_cast<uint4 *>(dst), *reinterpret_cast<const uint4 *>(src));
         else
             *reinterpret_cast<uint4 *>(dst) = *reinterpret_cast<const uint4 *>(src);
     } else
-        store_tail(dst, src, valid);
+        store_tail(dst, src, min(valid, 16));
 }
 
 // MODE 0: the planes are read again on the GPU (two-pass intermediate): plain stores. MODE 1: final
@@ -125,6 +125,7 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
                              : nullptr;
     const long long fo = (long long)frame * p.out.frame_stride;
     const int seg = lane & 7, gx = x0 + seg * 16;          // this lane's 16-byte segment in the store phase
+    const bool vec = p.out.aligned16 != 0;
     uint32_t diff = 0;
 
 #pragma unroll 1
@@ -279,7 +280,7 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
         for (int i = 0; i < HR / 4; i++) {                // Y: HR rows x 8 segments
             const int r = i * 4 + (lane >> 3);
             if (r < rows && gx < p.w)
-                store16(p.out.p[0] + fo + (long long)(yh + r) * p.out.pitch[0] + gx, &st.y[r][seg * 16], p.w - gx, STREAM);
+                store16(p.out.p[0] + fo + (long long)(yh + r) * p.out.pitch[0] + gx, &st.y[r][seg * 16], p.w - gx, STREAM, vec);
         }
         if (FMT <= 1) {
             const int r = lane >> 3;                       // chroma: HR/2 rows x 8 segments
@@ -289,9 +290,9 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
                 if (FMT == 0) {
                     const int plane = 1 + (seg >> 2), cx = (x0 >> 1) + (seg & 3) * 16;
                     if (cx < cw)
-                        store16(p.out.p[plane] + fo + cy * p.out.pitch[plane] + cx, &st.c[r][seg * 16], cw - cx, STREAM);
+                        store16(p.out.p[plane] + fo + cy * p.out.pitch[plane] + cx, &st.c[r][seg * 16], cw - cx, STREAM, vec);
                 } else if (gx < 2 * cw) {
-                    store16(p.out.p[1] + fo + cy * p.out.pitch[1] + gx, &st.c[r][seg * 16], 2 * cw - gx, STREAM);
+                    store16(p.out.p[1] + fo + cy * p.out.pitch[1] + gx, &st.c[r][seg * 16], 2 * cw - gx, STREAM, vec);
                 }
             }
         } else if (FMT == 2) {
@@ -301,7 +302,7 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
             for (int i = 0; i < HR / 4; i++) {
                 const int r = i * 4 + (lane >> 3);
                 if (r < rows && cx < cw)
-                    store16(p.out.p[plane] + fo + (long long)(yh + r) * p.out.pitch[plane] + cx, &st.c[r][seg * 16], cw - cx, STREAM);
+                    store16(p.out.p[plane] + fo + (long long)(yh + r) * p.out.pitch[plane] + cx, &st.c[r][seg * 16], cw - cx, STREAM, vec);
             }
         } else {
 #pragma unroll
@@ -309,7 +310,7 @@ __global__ void __launch_bounds__(WARPS * 32) k1_convert_kernel(const ConvertPar
                 const int idx = i * 32 + lane, r = idx >> 4, sg = idx & 15;
                 const int plane = 1 + (sg >> 3), cx = x0 + (sg & 7) * 16;
                 if (r < rows && cx < p.w)
-                    store16(p.out.p[plane] + fo + (long long)(yh + r) * p.out.pitch[plane] + cx, &st.c[r][sg * 16], p.w - cx, STREAM);
+                    store16(p.out.p[plane] + fo + (long long)(yh + r) * p.out.pitch[plane] + cx, &st.c[r][sg * 16], p.w - cx, STREAM, vec);
             }
         }
         __syncwarp();                                      // the stage is reused by the next step

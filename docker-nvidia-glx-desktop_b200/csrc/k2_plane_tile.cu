@@ -136,10 +136,10 @@ __global__ void __launch_bounds__(256) k2_plane_tile_kernel(const PlaneTileParam
         const int n = valid - q * 16;
         const uint8_t *src = s_out + r * row_bytes + q * 16;
         uint8_t *dst = plane + (long long)(y0 + r) * p.out.pitch[pl] + q * 16;
-        if (n >= 16) {
+        if (n >= 16 && p.out.aligned16) {
             *reinterpret_cast<uint4 *>(dst) = *reinterpret_cast<const uint4 *>(src);
         } else {
-            for (int i = 0; i < n; i++) dst[i] = src[i];
+            for (int i = 0; i < min(n, 16); i++) dst[i] = src[i];
         }
     }
 }

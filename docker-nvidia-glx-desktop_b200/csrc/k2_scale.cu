@@ -294,10 +294,10 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
             dst = p.out.p[1] + fo + (long long)((y0 >> 1) + r) * p.out.pitch[1] + xb;
         }
         if (row_ok) {
-            if (n >= 16) {
+            if (n >= 16 && p.out.aligned16) {
                 *reinterpret_cast<uint4 *>(dst) = *reinterpret_cast<const uint4 *>(src);
             } else {
-                for (int k = 0; k < n; k++) dst[k] = src[k];
+                for (int k = 0; k < min(n, 16); k++) dst[k] = src[k];
             }
         }
     }
@@ -510,10 +510,10 @@ __global__ void __launch_bounds__(128) k2_plane_scale_kernel(const PlaneScalePar
         const uint8_t *r1 = r0 + (long long)tap_step(tv) * p.src_pitch[0];
         const uint32_t out = scale4(r0, r1, *reinterpret_cast<const uint4 *>(p.tab.hy + x), tap_frac(tv), p.box2x2);
         uint8_t *dst = p.out.p[0] + fo + (long long)row * p.out.pitch[0] + x;
-        if (x + 4 <= p.out_w) {
+        if (x + 4 <= p.out_w && p.out.aligned16) {
             *reinterpret_cast<uint32_t *>(dst) = out;
         } else {
-            for (int k = 0; k < p.out_w - x; k++) dst[k] = (uint8_t)(out >> (8 * k));
+            for (int k = 0; k < min(4, p.out_w - x); k++) dst[k] = (uint8_t)(out >> (8 * k));
         }
         return;
     }
@@ -525,10 +525,10 @@ __global__ void __launch_bounds__(128) k2_plane_scale_kernel(const PlaneScalePar
         const uint8_t *r1 = r0 + (long long)tap_step(tv) * p.src_pitch[pl];
         const uint32_t out = scale4(r0, r1, *reinterpret_cast<const uint4 *>(p.tab.hc + x), tap_frac(tv), p.box2x2);
         uint8_t *dst = p.out.p[pl] + fo + (long long)cy * p.out.pitch[pl] + x;
-        if (x + 4 <= cw) {
+        if (x + 4 <= cw && p.out.aligned16) {
             *reinterpret_cast<uint32_t *>(dst) = out;
         } else {
-            for (int k = 0; k < cw - x; k++) dst[k] = (uint8_t)(out >> (8 * k));
+            for (int k = 0; k < min(4, cw - x); k++) dst[k] = (uint8_t)(out >> (8 * k));
         }
     } else {                                               // NV12: U and V of four samples, interleaved
         const int cy = row - p.out_h;
@@ -544,11 +544,11 @@ __global__ void __launch_bounds__(128) k2_plane_scale_kernel(const PlaneScalePar
         }
         const uint32_t lo = prmt(o[0], o[1], 0x5140), hi = prmt(o[0], o[1], 0x7362);   // u0 v0 u1 v1 | u2 v2 u3 v3
         uint8_t *dst = p.out.p[1] + fo + (long long)cy * p.out.pitch[1] + 2 * x;
-        if (x + 4 <= cw) {
+        if (x + 4 <= cw && p.out.aligned16) {
             *reinterpret_cast<uint2 *>(dst) = make_uint2(lo, hi);
         } else {
             const unsigned long long both = (unsigned long long)lo | ((unsigned long long)hi << 32);
-            for (int k = 0; k < 2 * (cw - x); k++) dst[k] = (uint8_t)(both >> (8 * k));
+            for (int k = 0; k < 2 * min(4, cw - x); k++) dst[k] = (uint8_t)(both >> (8 * k));
         }
     }
 }

@@ -29,6 +29,8 @@ struct PlaneSet {
     uint8_t *p[3];          // Y,U,V (I420) or Y,UV (NV12)
     long long pitch[3];
     long long frame_stride; // bytes between consecutive frames, same for every plane pointer
+    int aligned16;          // every plane pointer, pitch and the frame stride are multiples of 16: rows may leave as
+                            // 16-byte stores (a picture placed at an odd multiple of 8 inside a bordered frame may not)
 };
 
 // Row gate of the synchronous host path (b200vc_convert): the kernel is launched while its frame is

@@ -222,6 +222,7 @@ extern "C" int b200vc_convert_scale_device_static(const b200vc_config *cfg, cons
         p1.src_pitch = (long long)d->in_pitch;
         p1.out.p[0] = mid;  p1.out.p[1] = mid + yp * cfg->in_h;  p1.out.p[2] = p1.out.p[1] + cp * (cfg->in_h / 2);
         p1.out.pitch[0] = (long long)yp;  p1.out.pitch[1] = p1.out.pitch[2] = (long long)cp;
+        p1.out.aligned16 = 1;                        // the scratch array and its 16-byte-padded rows
         p1.w = cfg->in_w;  p1.h = cfg->in_h;  p1.n_frames = 1;  p1.mx = mx;
         if ((e = launch_convert(p1, B200VC_FMT_I420, site, st)) != cudaSuccess)
             return report(errbuf, errbuf_len, B200VC_ERR_CUDA, "launching the conversion kernel failed: %s", cudaGetErrorString(e));

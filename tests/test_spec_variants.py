@@ -75,3 +75,16 @@ def test_gpu_parity_under_variant(variant):
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "fuzz_parity.py"), "90", "777"],
                        env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "0 mismatches" in r.stdout and f"spec {S.name(sp)}" in r.stdout, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+@pytest.mark.parametrize("variant", ["vtap8", "cosited121"])
+def test_gst_validate_names_the_setting(variant):
+    """tools/gst_validate.py with an oracle variant standing in for GStreamer: every differing case is matched to
+    that variant's constant, and the summary names the default to edit."""
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "gst_validate.py"), "--stand-in", variant, "--quick"],
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 1, r.stdout[-2000:] + r.stderr[-2000:]
+    diffs = [line for line in r.stdout.splitlines() if line.startswith("DIFF")]
+    assert diffs and all(variant in line for line in diffs)
+    key, val = next(iter(S.VARIANTS[variant].items()))
+    assert f"#define B200VC_SPEC_{key} {val}" in r.stdout

@@ -218,6 +218,13 @@ def host_cores() -> int:
         return os.cpu_count() or 1
 
 
+def bench_config():
+    """The `config` object of both arms (the reference arm runs a bounded sample of it, described in its cpu_baseline)."""
+    return {"workload": WORKLOAD, "frames_per_step": FRAMES_PER_STEP, "sessions_per_gpu": SESSIONS,
+            "ring_frames": RING, "launches_per_step": LAUNCHES_PER_STEP, "partition": "sessions by GPU, no collective",
+            "l2": f"inputs larger than L2: ring of {RING} frames = {RING * ALGO_BYTES_PER_FRAME / 1e6:.0f} MB in+out per launch"}
+
+
 def run_reference(args, rank: int):
     if rank != 0:
         return
@@ -227,7 +234,7 @@ def run_reference(args, rank: int):
         "impl": "reference", "metric": METRIC, "value": round(fps, 2), "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frames_per_step": 2 * cores},
+        "config": bench_config(),
         "cpu_baseline": {"value": round(fps, 2), "unit": "frames/s", "cores": cores, "kind": "port",
                          "sample": f"{2 * cores * args.steps} frames ({2 * cores} per step) of the same 1080p workload, "
                                    f"{cores} threads each converting whole frames; CPU restatement of videoconvert, "
@@ -347,26 +354,68 @@ def run_session_bench(local_rank: int, sessions: int, seconds: float, hz: float,
 
 
 def paced_run(job: Job, rank: int, local_rank: int, sessions: int, seconds: float, hz: float, extra=()):
-    """All ranks start their harness together (a file rank 0 creates after a barrier releases them)."""
+    """All ranks start their harness together (a file rank 0 creates after a barrier releases them). A rank whose
+    harness fails still walks through every barrier and reduction, so that the ranks fail together, not one by one."""
     gate = os.path.join(tempfile.gettempdir(), f"b200vc_gate_{os.environ.get('MASTER_PORT', '0')}_{sessions}_{int(hz)}_{int(time.time()) // 600}")
     if rank == 0 and os.path.exists(gate):
         os.unlink(gate)
     job.barrier()
-    proc = run_session_bench(local_rank, sessions, seconds, hz, gate, extra)
+    proc, err = None, ""
+    try:
+        proc = run_session_bench(local_rank, sessions, seconds, hz, gate, extra)
+    except Exception as e:  # noqa: BLE001
+        err = f"{type(e).__name__}: {e}"
     time.sleep(1.0)                              # contexts and pinned buffers are set up behind the gate
     job.barrier()
     if rank == 0:
         open(gate, "w").close()
-    out, err = proc.communicate(timeout=seconds + 120)
+    d = {"frames": 0, "ticks": 0, "late_ticks": 0, "aggregate_fps": 0.0, "tick_ms_p50": 0.0, "tick_ms_p99": 0.0, "tick_ms_max": 0.0}
+    if proc is not None:
+        try:
+            out, perr = proc.communicate(timeout=seconds + 120)
+            if proc.returncode != 0:
+                err = f"session_bench exit {proc.returncode}: {perr[-300:]}"
+            else:
+                d = json.loads(out.strip().splitlines()[-1])
+        except Exception as e:  # noqa: BLE001
+            proc.kill()
+            err = f"{type(e).__name__}: {e}"
     job.barrier()
     if rank == 0 and os.path.exists(gate):
         os.unlink(gate)
-    if proc.returncode != 0:
-        raise RuntimeError(f"session_bench failed on rank {rank}: {err[-500:]}")
-    d = json.loads(out.strip().splitlines()[-1])
-    return {"frames": job.reduce(d["frames"], "sum"), "ticks": job.reduce(d["ticks"], "sum"),
-            "late_ticks": job.reduce(d["late_ticks"], "sum"), "fps": job.reduce(d["aggregate_fps"], "sum"),
-            "p50_ms": job.reduce(d["tick_ms_p50"]), "p99_ms": job.reduce(d["tick_ms_p99"]), "max_ms": job.reduce(d["tick_ms_max"])}
+    res = {"frames": job.reduce(d["frames"], "sum"), "ticks": job.reduce(d["ticks"], "sum"),
+           "late_ticks": job.reduce(d["late_ticks"], "sum"), "fps": job.reduce(d["aggregate_fps"], "sum"),
+           "p50_ms": job.reduce(d["tick_ms_p50"]), "p99_ms": job.reduce(d["tick_ms_p99"]), "max_ms": job.reduce(d["tick_ms_max"])}
+    if job.reduce(1.0 if err else 0.0, "sum") > 0:
+        raise RuntimeError(err or "session_bench failed on another rank")
+    return res
+
+
+def ensure_harness(job: "Job", rank: int):
+    """harness/session_bench travels with the tree; if it is missing, rank 0 builds it (gcc is on the box)."""
+    if rank == 0 and not os.path.exists(SESSION_BENCH):
+        subprocess.run(["make", "-C", PKG, "harness/session_bench"], capture_output=True)
+    job.barrier()
+
+
+def c5_record(job: "Job", rank: int, local_rank: int, world: int):
+    """C5 in real time: 8 sessions per GPU at 60 Hz for 5 s, then as many as still miss no tick."""
+    base = paced_run(job, rank, local_rank, SESSIONS, 5.0, 60, ("--damage",))
+    c5 = {"workload": f"C5: {SESSIONS} sessions per GPU x {world} GPU(s), 1080p BGRx->I420 + damage map, paced at 60 Hz for 5 s, "
+                      "harness/session_bench over the C ABI (one process per GPU, started together)",
+          "sessions": SESSIONS * world, "target_fps": 60.0 * SESSIONS * world, "delivered_fps": round(base["fps"], 1),
+          "ticks": int(base["ticks"]), "late_ticks": int(base["late_ticks"]), "tick_ms_p50": round(base["p50_ms"], 3),
+          "tick_ms_p99": round(base["p99_ms"], 3), "tick_ms_max": round(base["max_ms"], 3), "tick_budget_ms": round(1000 / 60, 3)}
+    best, sweep = (SESSIONS if base["late_ticks"] == 0 else 0), []
+    for s in (16, 24, 32, 48, 64, 80, 96):
+        r = paced_run(job, rank, local_rank, s, 1.5, 60, ("--damage",))
+        sweep.append({"sessions_per_gpu": s, "late_ticks": int(r["late_ticks"]), "tick_ms_p99": round(r["p99_ms"], 3), "delivered_fps": round(r["fps"], 1)})
+        if r["late_ticks"] > 0:
+            break
+        best = s
+    c5["max_sessions_per_gpu_without_a_late_tick"] = best
+    c5["sweep"] = sweep
+    return c5
 
 
 def run_gpu(args, rank: int, local_rank: int, world: int):
@@ -482,7 +531,11 @@ def run_gpu(args, rank: int, local_rank: int, world: int):
 
     # ---- the same e2e loop without an interpreter: native harness, ticks back to back ----------------
     sampler.mark("c1_native")
-    native = paced_run(job, rank, local_rank, SESSIONS, 2.0, 0)
+    ensure_harness(job, rank)
+    try:
+        native = paced_run(job, rank, local_rank, SESSIONS, 2.0, 0)
+    except Exception as e:  # noqa: BLE001 — the harness is an extra; the headline must not die with it
+        native = {"fps": 0.0, "error": f"{type(e).__name__}: {e}"[:200]}
     sampler.mark(None)
 
     # ---- BASELINE configs C2, C3, C4 -------------------------------------------------------------------
@@ -562,21 +615,10 @@ def run_gpu(args, rank: int, local_rank: int, world: int):
 
     # ---- C5: 8 sessions per GPU at 60 Hz, then as many as still miss no tick ---------------------------
     sampler.mark("c5")
-    base = paced_run(job, rank, local_rank, SESSIONS, 5.0, 60, ("--damage",))
-    c5 = {"workload": f"C5: {SESSIONS} sessions per GPU x {world} GPU(s), 1080p BGRx->I420 + damage map, paced at 60 Hz for 5 s, "
-                      "harness/session_bench over the C ABI (one process per GPU, started together)",
-          "sessions": SESSIONS * world, "target_fps": 60.0 * SESSIONS * world, "delivered_fps": round(base["fps"], 1),
-          "ticks": int(base["ticks"]), "late_ticks": int(base["late_ticks"]), "tick_ms_p50": round(base["p50_ms"], 3),
-          "tick_ms_p99": round(base["p99_ms"], 3), "tick_ms_max": round(base["max_ms"], 3), "tick_budget_ms": round(1000 / 60, 3)}
-    best, sweep = (SESSIONS if base["late_ticks"] == 0 else 0), []
-    for s in (16, 24, 32, 48, 64, 80, 96):
-        r = paced_run(job, rank, local_rank, s, 1.5, 60, ("--damage",))
-        sweep.append({"sessions_per_gpu": s, "late_ticks": int(r["late_ticks"]), "tick_ms_p99": round(r["p99_ms"], 3), "delivered_fps": round(r["fps"], 1)})
-        if r["late_ticks"] > 0:
-            break
-        best = s
-    c5["max_sessions_per_gpu_without_a_late_tick"] = best
-    c5["sweep"] = sweep
+    try:
+        c5 = c5_record(job, rank, local_rank, world)
+    except Exception as e:  # noqa: BLE001
+        c5 = {"unavailable": f"{type(e).__name__}: {e}"[:300]}
     sampler.mark(None)
     sampler.finish()
 
@@ -593,9 +635,7 @@ def run_gpu(args, rank: int, local_rank: int, world: int):
             "metric": METRIC, "value": round(value, 1), "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": warm, "ms_per_step": round(k_seconds / args.steps * 1e3, 4),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "frames_per_step": FRAMES_PER_STEP, "sessions_per_gpu": SESSIONS,
-                       "ring_frames": RING, "launches_per_step": LAUNCHES_PER_STEP, "partition": "sessions by GPU, no collective",
-                       "l2": f"inputs larger than L2: ring of {RING} frames = {RING * ALGO_BYTES_PER_FRAME / 1e6:.0f} MB in+out per launch"},
+            "config": bench_config(),
             "e2e": {"value": round(e2e_fps, 1), "unit": "frames/s",
                     "h2d_bytes_per_step": int((st1.h2d_bytes - st0.h2d_bytes) // args.steps),
                     "d2h_bytes_per_step": int((st1.d2h_bytes - st0.d2h_bytes) // args.steps),
@@ -609,7 +649,7 @@ def run_gpu(args, rank: int, local_rank: int, world: int):
                     "pcie": pcie,
                     "host_cpu_seconds": {"max_rank": round(e_cpu_max, 3), "all_ranks": round(e_cpu_sum, 3), "wall": round(e_seconds, 3),
                                          "host_cores": host_cores()},
-                    "native_harness_fps": round(native["fps"], 1),
+                    "native_harness_fps": round(native["fps"], 1), **({"native_harness_error": native["error"]} if "error" in native else {}),
                     "native_harness_how": "harness/session_bench --hz 0: the same 8-session ticks back to back from C++, one process per GPU",
                     "sync_single_session_fps": round(sync_fps * world, 1), "sync_single_session_fps_per_gpu": round(sync_fps, 1),
                     "one_frame_latency_single_session_fps_per_gpu": round(latency_mode_fps, 1), "numa": numa},

@@ -24,7 +24,7 @@ FMT_I420, FMT_NV12, FMT_Y42B, FMT_Y444 = 0, 1, 2, 3
 MATRIX_BT601, MATRIX_BT709, MATRIX_BT2020 = 0, 1, 2
 RANGE_LIMITED, RANGE_FULL = 0, 1
 SITE_NONE, SITE_H_COSITED, SITE_V_COSITED, SITE_ALT_LINE, SITE_COSITED, SITE_DV = 0, 1, 2, 4, 3, 7
-SCALE_GST_LQ, SCALE_BOX_2X2 = 0, 1
+SCALE_GST_LQ, SCALE_BOX_2X2, SCALE_NEAREST = 0, 1, 2
 IN_BGRX, IN_RGBX, IN_XRGB, IN_XBGR, IN_RGB16, IN_BGR16 = 0, 1, 2, 3, 4, 5
 FLAG_DAMAGE_MAP, FLAG_FORCE_TWO_PASS, FLAG_REGISTER_HOST, FLAG_FORCE_GENERIC_FUSED, FLAG_ZERO_COPY, FLAG_ZERO_COPY_OUT = 1, 2, 4, 8, 16, 32
 FLAG_ROW_GATE = 64

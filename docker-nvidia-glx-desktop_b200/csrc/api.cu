@@ -198,6 +198,18 @@ void build_v_taps(int in_n, int out_n, std::vector<Tap> &t)
     for (size_t y = out_n; y < t.size(); y++) t[y] = t[out_n - 1];
 }
 
+// method=nearest as taps: all the weight on one sample (fraction 0; the second tap exists so that the kernels,
+// which always read two, stay inside the plane).
+void build_nearest_taps(int in_n, int out_n, std::vector<Tap> &t)
+{
+    t.resize(ru(out_n, 4));
+    for (int x = 0; x < out_n; x++) {
+        const int i0 = clamp_index(scale_nearest_index(x, in_n, out_n), in_n), i1 = clamp_index((long long)i0 + 1, in_n);
+        t[x] = make_tap(i0, 0, i1 - i0);
+    }
+    for (size_t x = out_n; x < t.size(); x++) t[x] = t[out_n - 1];
+}
+
 // BOX_2X2 reuses the tables as plain index maps: entry k = source index 2k.
 void build_box_taps(int out_n, std::vector<Tap> &t)
 {
@@ -388,8 +400,8 @@ int check_config(const b200vc_config *c, std::string *why)
         return bad(B200VC_ERR_UNSUPPORTED, "range must be limited (16-235) or full (0-255)");
     if (c->chroma_site < 0 || c->chroma_site > B200VC_SITE_DV)
         return bad(B200VC_ERR_UNSUPPORTED, "chroma-site must be a combination of h-cosited, v-cosited and alt-line (jpeg, mpeg2, cosited, dv)");
-    if (c->scale_mode != B200VC_SCALE_GST_LQ && c->scale_mode != B200VC_SCALE_BOX_2X2)
-        return bad(B200VC_ERR_UNSUPPORTED, "unknown scale mode");
+    if (c->scale_mode < B200VC_SCALE_GST_LQ || c->scale_mode > B200VC_SCALE_NEAREST)
+        return bad(B200VC_ERR_UNSUPPORTED, "scale method must be bilinear, nearest (or the 2x2 box)");
     int pw = c->out_w, ph = c->out_h;                      // the picture inside the output frame (add-borders)
     if (c->content_x || c->content_y || c->content_w || c->content_h) {
         if (c->content_x < 0 || c->content_y < 0 || c->content_w < 2 || c->content_h < 2 ||
@@ -886,6 +898,9 @@ int create_impl(b200vc_ctx *c)
         if (g.scale_mode == B200VC_SCALE_BOX_2X2) {
             build_box_taps(k.out_w, hy);  build_box_taps(k.out_h, vy);
             build_box_taps(c->ccw, hc);  build_box_taps(c->cch, vc);       // BOX: even sizes only; chroma planes by format
+        } else if (g.scale_mode == B200VC_SCALE_NEAREST) {
+            build_nearest_taps(g.in_w, k.out_w, hy);  build_nearest_taps(g.in_h, k.out_h, vy);
+            build_nearest_taps(c->cw_in, c->ccw, hc);  build_nearest_taps(c->ch_in, c->cch, vc);
         } else {
             build_h_taps(g.in_w, k.out_w, hy);  build_v_taps(g.in_h, k.out_h, vy);
             // chroma planes of odd frames round up, like the intermediate frame's own layout

@@ -111,6 +111,13 @@ B200VC_HD void scale_v_tap(int y, int in_n, int out_n, long long &i, int &p1)
     p1 = (int)((2LL * B200VC_SPEC_VTAP_ONE * rem + (B200VC_SPEC_VTAP_ROUND ? den : 0)) / (2 * den));
 }
 
+// method=nearest: the source index of output sample x (B200VC_SPEC_NEAREST_CENTRE)
+B200VC_HD int scale_nearest_index(int x, int in_n, int out_n)
+{
+    if (B200VC_SPEC_NEAREST_CENTRE) return (int)(((2LL * x + 1) * in_n) / (2LL * out_n));
+    return (int)(((long long)x * scale_h_inc(in_n, out_n)) >> 16);
+}
+
 B200VC_HD int clamp_index(long long i, int n) { return (int)(i < 0 ? 0 : (i > n - 1 ? n - 1 : i)); }
 
 // The vertical tap as dp4a weights against [a,a,b,b] (the two lines' samples, each twice):

@@ -155,6 +155,8 @@ extern "C" int b200vc_convert_scale_device_static(const b200vc_config *cfg, cons
     if (cfg->out_format > B200VC_FMT_NV12 || cfg->in_format > B200VC_IN_XBGR)
         return report(errbuf, errbuf_len, B200VC_ERR_UNSUPPORTED,
                       "this entry point converts 4-byte pixels to I420 or NV12; other formats go through a context");
+    if (cfg->scale_mode == B200VC_SCALE_NEAREST)
+        return report(errbuf, errbuf_len, B200VC_ERR_UNSUPPORTED, "method=nearest goes through a context");
     if (cfg->content_w || cfg->content_h || cfg->content_x || cfg->content_y)
         return report(errbuf, errbuf_len, B200VC_ERR_UNSUPPORTED, "borders (a content rectangle) go through a context");
     if (cfg->flags & B200VC_FLAG_DAMAGE_MAP)

@@ -41,6 +41,7 @@ struct _GstB200Convert {
     gint n_bands;
     gboolean one_frame_latency;   /* submit frame N, hand out frame N-1: its D2H overlaps frame N's H2D */
     gboolean register_host;       /* page-lock upstream's buffers on first sight (B200VC_FLAG_REGISTER_HOST) */
+    gint method;                  /* videoscale's method property: 0 nearest, 1 bilinear (its default); others are not offered */
     /* what the context in use was negotiated with: a property set in mid-stream takes effect at the next set_info */
     gboolean cur_damage_map, cur_one_frame_latency;
     gint frame_w, frame_h;
@@ -110,7 +111,7 @@ G_DEFINE_TYPE(GstB200Convert, gst_b200_convert, GST_TYPE_VIDEO_FILTER)
 GST_DEBUG_CATEGORY_STATIC(b200convert_debug);
 #define GST_CAT_DEFAULT b200convert_debug
 
-enum { PROP_0, PROP_DEVICE_ID, PROP_DAMAGE_MAP, PROP_N_BANDS, PROP_ONE_FRAME_LATENCY, PROP_REGISTER_HOST };
+enum { PROP_0, PROP_DEVICE_ID, PROP_DAMAGE_MAP, PROP_N_BANDS, PROP_ONE_FRAME_LATENCY, PROP_REGISTER_HOST, PROP_METHOD };
 
 static GstStaticPadTemplate sink_tmpl = GST_STATIC_PAD_TEMPLATE("sink", GST_PAD_SINK, GST_PAD_ALWAYS,
     GST_STATIC_CAPS("video/x-raw, format=(string){BGRx,BGRA,RGBx,RGBA,xRGB,ARGB,xBGR,ABGR,RGB16,BGR16}, width=(int)[2,16384], height=(int)[2,16384], "
@@ -251,6 +252,7 @@ gst_b200_convert_set_info(GstVideoFilter *filter, GstCaps *incaps, GstVideoInfo 
     cfg.n_bands = self->n_bands;
     want_damage = self->damage_map;
     want_register = self->register_host;
+    cfg.scale_mode = self->method == 0 ? B200VC_SCALE_NEAREST : B200VC_SCALE_GST_LQ;
     self->cur_one_frame_latency = self->one_frame_latency;
     GST_OBJECT_UNLOCK(self);
     cfg.in_w = GST_VIDEO_INFO_WIDTH(in);    cfg.in_h = GST_VIDEO_INFO_HEIGHT(in);
@@ -531,6 +533,7 @@ static void gst_b200_convert_set_property(GObject *obj, guint id, const GValue *
     case PROP_N_BANDS: self->n_bands = g_value_get_int(v); break;
     case PROP_ONE_FRAME_LATENCY: self->one_frame_latency = g_value_get_boolean(v); break;   /* read at the next negotiation */
     case PROP_REGISTER_HOST: self->register_host = g_value_get_boolean(v); break;
+    case PROP_METHOD: self->method = g_value_get_int(v); break;
     default: G_OBJECT_WARN_INVALID_PROPERTY_ID(obj, id, ps);
     }
     GST_OBJECT_UNLOCK(self);
@@ -546,6 +549,7 @@ static void gst_b200_convert_get_property(GObject *obj, guint id, GValue *v, GPa
     case PROP_N_BANDS: g_value_set_int(v, self->n_bands); break;
     case PROP_ONE_FRAME_LATENCY: g_value_set_boolean(v, self->one_frame_latency); break;
     case PROP_REGISTER_HOST: g_value_set_boolean(v, self->register_host); break;
+    case PROP_METHOD: g_value_set_int(v, self->method); break;
     default: G_OBJECT_WARN_INVALID_PROPERTY_ID(obj, id, ps);
     }
     GST_OBJECT_UNLOCK(self);
@@ -568,6 +572,8 @@ static void gst_b200_convert_class_init(GstB200ConvertClass *klass)
     g_object_class_install_property(go, PROP_REGISTER_HOST, g_param_spec_boolean("register-host", "Page-lock upstream buffers",
         "Page-lock upstream's buffers on first sight instead of staging them; only for a small long-lived pool (ximagesrc XShm images)",
         FALSE, G_PARAM_READWRITE));
+    g_object_class_install_property(go, PROP_METHOD, g_param_spec_int("method", "Scale method",
+        "videoscale's method: 0 nearest-neighbour, 1 bilinear (2-tap)", 0, 1, 1, G_PARAM_READWRITE));
     gst_element_class_add_static_pad_template(el, &sink_tmpl);
     gst_element_class_add_static_pad_template(el, &src_tmpl);
     gst_element_class_set_static_metadata(el, "B200 BGRx converter/scaler", "Filter/Converter/Video/Scaler",
@@ -595,6 +601,7 @@ static void gst_b200_convert_init(GstB200Convert *self)
     self->n_bands = 0;
     self->one_frame_latency = FALSE;
     self->register_host = FALSE;
+    self->method = 1;
     self->cur_damage_map = self->cur_one_frame_latency = FALSE;
     self->frame_w = self->frame_h = 0;
     self->maps[0] = self->maps[1] = NULL;

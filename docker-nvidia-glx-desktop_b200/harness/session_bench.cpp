@@ -91,6 +91,23 @@ static void worker(int device, int sessions, double seconds, double hz, bool dam
         for (int y = 100; y < 124; y++) memset(in[s * 2 + 1] + ((size_t)y * W + 200 + 7 * s) * 4, 0xff, 16 * 4);   // a "cursor"
     }
     std::vector<b200vc_frame> frames(sessions);
+    // two untimed ticks: kernel images loaded, staging and flags touched, before the clock starts (a session has
+    // been running for a while when its 60 Hz budget matters)
+    for (int warm = 0; warm < 2; warm++) {
+        for (int s = 0; s < sessions; s++) {
+            b200vc_frame &f = frames[s];
+            memset(&f, 0, sizeof f);
+            f.bgrx = in[s * 2 + (warm & 1)];
+            f.in_pitch = (size_t)W * 4;
+            for (int p = 0; p < 3; p++) { f.planes[p] = out[s] + off[p]; f.pitches[p] = pit[p]; }
+            f.damage = damage ? dmg[s] : nullptr;
+            f.session = s;
+        }
+        if ((res->rc = b200vc_convert_batch(ctx, frames.data(), sessions)) != B200VC_OK) {
+            res->err = b200vc_last_error(ctx);
+            return;
+        }
+    }
     if (!g_wait_file.empty())
         while (access(g_wait_file.c_str(), F_OK) != 0) std::this_thread::sleep_for(std::chrono::microseconds(200));
     const bool paced = hz > 0;

@@ -65,7 +65,10 @@ enum { B200VC_RANGE_LIMITED = 0, B200VC_RANGE_FULL = 1 };           /* colorimet
  * interlaced video. So every value negotiates; bit 0 is what changes the output. */
 enum { B200VC_SITE_NONE = 0, B200VC_SITE_H_COSITED = 1, B200VC_SITE_V_COSITED = 2, B200VC_SITE_ALT_LINE = 4,
        B200VC_SITE_COSITED = 3, B200VC_SITE_DV = 7 };
-enum { B200VC_SCALE_GST_LQ = 0 /* videoscale bilinear, SURVEY B.2 */, B200VC_SCALE_BOX_2X2 = 1 };
+/* videoscale method: 0 = bilinear (its default), 2 = nearest-neighbour (method=nearest: the sample
+ * under the centre of the output pixel; b200vc_spec.h holds the alignment convention). 1 is not a videoscale
+ * method: the plain rounded 2x2 mean, kept as the survey's alternative reading of an exact 2:1 downscale. */
+enum { B200VC_SCALE_GST_LQ = 0, B200VC_SCALE_BOX_2X2 = 1, B200VC_SCALE_NEAREST = 2 };
 /* sink pad format: byte order of one pixel in memory; x is a pad or alpha byte and never matters
  * (BGRA, RGBA, ARGB, ABGR negotiate as their x twins: I420/NV12 carry no alpha). BGRx is what
  * ximagesrc delivers at the reference's default depth 24 (Dockerfile:206, entrypoint.sh:102). */
@@ -206,7 +209,7 @@ int b200vc_damage_to_rects(const uint8_t *map, int frame_w, int frame_h, b200vc_
 const char *b200vc_status_string(int status);
 int b200vc_version(void);
 
-/* The values of include/b200vc_spec.h this library was built with, as one token ("m0c1h1b6r1u1"): the
+/* The values of include/b200vc_spec.h this library was built with, as one token ("m0c1h1b6r1u1n1"): the
  * details of videoconvert/videoscale's arithmetic that SURVEY.md Appendix A/B could not verify against
  * GStreamer (matrix rounding term, last column of the cosited filter, order of the scaler's passes,
  * bits and rounding of its vertical tap). The oracle reports its own the same way; tests compare. */

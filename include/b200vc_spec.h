@@ -61,6 +61,14 @@
 #define B200VC_SPEC_UNPACK16_REPLICATE 1
 #endif
 
+/* videoscale method=nearest — which source sample an output sample takes. 1: the one under the output
+ * pixel's centre, floor((x + 0.5) * in / out), both directions (the resampler's centre alignment, as
+ * recalled). 0: edge-aligned, the bilinear path's 16.16 step without its fraction, (x * inc) >> 16, horizontally
+ * and vertically alike. */
+#ifndef B200VC_SPEC_NEAREST_CENTRE
+#define B200VC_SPEC_NEAREST_CENTRE 1
+#endif
+
 #if B200VC_SPEC_VTAP_BITS != 6 && B200VC_SPEC_VTAP_BITS != 7 && B200VC_SPEC_VTAP_BITS != 8
 #error "B200VC_SPEC_VTAP_BITS must be 6, 7 or 8 (the kernels evaluate the tap as 8-bit dp4a weights)"
 #endif
@@ -68,12 +76,13 @@
 #define B200VC_SPEC_VTAP_ONE  (1 << B200VC_SPEC_VTAP_BITS)
 #define B200VC_SPEC_VTAP_HALF (1 << (B200VC_SPEC_VTAP_BITS - 1))
 
-/* "m0c1h1b6r1u1": the values above in one token; b200vc_spec_string() and orc_spec_string()
+/* "m0c1h1b6r1u1n1": the values above in one token; b200vc_spec_string() and orc_spec_string()
  * return it so that a test can see that library and oracle were built from the same settings. */
 #define B200VC_SPEC_STR2(x) #x
 #define B200VC_SPEC_STR(x) B200VC_SPEC_STR2(x)
 #define B200VC_SPEC_STRING "m" B200VC_SPEC_STR(B200VC_SPEC_MATRIX_ROUND) "c" B200VC_SPEC_STR(B200VC_SPEC_COSITED_LAST_1_3) \
                            "h" B200VC_SPEC_STR(B200VC_SPEC_SCALE_H_FIRST) "b" B200VC_SPEC_STR(B200VC_SPEC_VTAP_BITS)       \
-                           "r" B200VC_SPEC_STR(B200VC_SPEC_VTAP_ROUND) "u" B200VC_SPEC_STR(B200VC_SPEC_UNPACK16_REPLICATE)
+                           "r" B200VC_SPEC_STR(B200VC_SPEC_VTAP_ROUND) "u" B200VC_SPEC_STR(B200VC_SPEC_UNPACK16_REPLICATE) \
+                           "n" B200VC_SPEC_STR(B200VC_SPEC_NEAREST_CENTRE)
 
 #endif /* B200VC_SPEC_H */

@@ -131,6 +131,14 @@ def scale_plane(src: np.ndarray, out_w: int, out_h: int, comps: int = 1, mode: i
         assert in_w == 2 * out_w and in_h == 2 * out_h
         d = (s[0::2, 0::2] + s[0::2, 1::2] + s[1::2, 0::2] + s[1::2, 1::2] + 2) >> 2
         return d.astype(np.uint8).reshape(out_h, out_w * comps)
+    if mode == 2:                                                # method=nearest: one source sample per output sample
+        def idx(n_in, n_out):
+            k = np.arange(n_out, dtype=np.int64)
+            if SPEC["NEAREST_CENTRE"]:
+                return np.clip(((2 * k + 1) * n_in) // (2 * n_out), 0, n_in - 1)
+            inc = max(0, ((n_in - 1) << 16) // (n_out - 1) - 1) if n_out > 1 else 0
+            return np.clip((k * inc) >> 16, 0, n_in - 1)
+        return s[idx(in_h, out_h)][:, idx(in_w, out_w)].astype(np.uint8).reshape(out_h, out_w * comps)
     hi, hf = h_taps(in_w, out_w)
     i0, i1 = np.clip(hi, 0, in_w - 1), np.clip(hi + 1, 0, in_w - 1)
     f = hf[None, :, None]

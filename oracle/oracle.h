@@ -27,7 +27,7 @@ enum { ORC_MATRIX_BT601 = 0, ORC_MATRIX_BT709 = 1, ORC_MATRIX_BT2020 = 2 };
 enum { ORC_RANGE_LIMITED = 0, ORC_RANGE_FULL = 1 };
 /* GstVideoChromaSite flags; only H_COSITED changes videoconvert's output (see b200vc.h) */
 enum { ORC_SITE_NONE = 0 /* "jpeg" */, ORC_SITE_H_COSITED = 1 /* "mpeg2" */, ORC_SITE_V_COSITED = 2, ORC_SITE_ALT_LINE = 4 };
-enum { ORC_SCALE_GST_LQ = 0, ORC_SCALE_BOX_2X2 = 1 };
+enum { ORC_SCALE_GST_LQ = 0, ORC_SCALE_BOX_2X2 = 1, ORC_SCALE_NEAREST = 2 /* videoscale method=nearest */ };
 /* input byte orders: unpack_BGRA, unpack_RGBA, unpack_ARGB, unpack_ABGR (alpha/pad byte ignored) */
 enum { ORC_IN_BGRX = 0, ORC_IN_RGBX = 1, ORC_IN_XRGB = 2, ORC_IN_XBGR = 3,
        ORC_IN_RGB16 = 4, ORC_IN_BGR16 = 5 /* unpack_RGB16 / unpack_BGR16: 2 bytes per pixel, 5-6-5, little endian */ };
@@ -37,7 +37,7 @@ typedef struct {
     int32_t m[3][4];
 } orc_matrix;
 
-/* The values of include/b200vc_spec.h this oracle was built with ("m0c1h1b6r1u1"), see there. */
+/* The values of include/b200vc_spec.h this oracle was built with ("m0c1h1b6r1u1n1"), see there. */
 const char *orc_spec_string(void);
 
 /* compute_matrix_to_YUV restated: double-precision build, x256, rint() per entry. */

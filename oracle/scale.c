@@ -86,6 +86,27 @@ int orc_scale_plane(const uint8_t *src, size_t src_pitch, int in_w, int in_h,
         }
         return 0;
     }
+    if (scale_mode == ORC_SCALE_NEAREST) {
+        /* method=nearest (video_scale_h_near_u8 / v_near): one source sample per output sample, the one under the
+         * output pixel's centre — or, the other candidate, at the bilinear path's edge-aligned 16.16 position
+         * (B200VC_SPEC_NEAREST_CENTRE) */
+        for (int y = 0; y < out_h; y++) {
+            int64_t inc_v = out_h > 1 ? (((int64_t)(in_h - 1)) << 16) / (out_h - 1) - 1 : 0;
+            int sy = B200VC_SPEC_NEAREST_CENTRE ? (int)(((2 * (int64_t)y + 1) * in_h) / (2 * (int64_t)out_h))
+                                                : (int)(((int64_t)y * (inc_v < 0 ? 0 : inc_v)) >> 16);
+            const uint8_t *s = src + (size_t)clampi(sy, 0, in_h - 1) * src_pitch;
+            uint8_t *d = dst + (size_t)y * dst_pitch;
+            int64_t inc_h = out_w > 1 ? (((int64_t)(in_w - 1)) << 16) / (out_w - 1) - 1 : 0;
+            for (int x = 0; x < out_w; x++) {
+                int sx = B200VC_SPEC_NEAREST_CENTRE ? (int)(((2 * (int64_t)x + 1) * in_w) / (2 * (int64_t)out_w))
+                                                    : (int)(((int64_t)x * (inc_h < 0 ? 0 : inc_h)) >> 16);
+                sx = clampi(sx, 0, in_w - 1);
+                for (int c = 0; c < comps; c++)
+                    d[x * comps + c] = s[sx * comps + c];
+            }
+        }
+        return 0;
+    }
     if (scale_mode != ORC_SCALE_GST_LQ)
         return -1;
 

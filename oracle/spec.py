@@ -17,7 +17,7 @@ import os
 import re
 
 _HEADER = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "b200vc_spec.h")
-KEYS = ["MATRIX_ROUND", "COSITED_LAST_1_3", "SCALE_H_FIRST", "VTAP_BITS", "VTAP_ROUND", "UNPACK16_REPLICATE"]
+KEYS = ["MATRIX_ROUND", "COSITED_LAST_1_3", "SCALE_H_FIRST", "VTAP_BITS", "VTAP_ROUND", "UNPACK16_REPLICATE", "NEAREST_CENTRE"]
 
 # the other candidate value of every warning item of SURVEY A/B, plus the pair (8-bit tap, floored)
 VARIANTS = {
@@ -28,6 +28,7 @@ VARIANTS = {
     "cosited121": {"COSITED_LAST_1_3": 0},
     "vfirst": {"SCALE_H_FIRST": 0},
     "unpack16trunc": {"UNPACK16_REPLICATE": 0},
+    "nearestedge": {"NEAREST_CENTRE": 0},
 }
 
 
@@ -70,7 +71,7 @@ def current(overrides: dict[str, int] | None = None) -> dict[str, int]:
 
 def name(spec: dict[str, int]) -> str:
     """The token b200vc_spec_string() / orc_spec_string() return for these values."""
-    return "m%dc%dh%db%dr%du%d" % tuple(spec[k] for k in KEYS)
+    return "m%dc%dh%db%dr%du%dn%d" % tuple(spec[k] for k in KEYS)
 
 
 def cflags(spec: dict[str, int]) -> list[str]:

@@ -44,6 +44,8 @@ CASES = [
     ("rgb16_709l_i420_mpeg2", 38, 20, 38, 20, 0, 1, 0, 1, 0, 4),
     ("bgr16_601f_nv12_scale", 64, 36, 40, 24, 1, 0, 1, 0, 0, 5),
     ("site_cosited_i420", 36, 20, 36, 20, 0, 1, 0, 3, 0),
+    ("nearest_3to2_709l_i420", 96, 48, 64, 32, 0, 1, 0, 1, 2),
+    ("nearest_up_odd_601f_nv12", 35, 19, 50, 31, 1, 0, 1, 0, 2),
 ]
 
 

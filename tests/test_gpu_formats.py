@@ -8,7 +8,8 @@ import b200vc
 from helpers import assert_planes_equal, plane_views
 
 pytestmark = pytest.mark.gpu
-GOLDEN_NEW = ["y42b_709l_mpeg2", "y444_601f", "y42b_scale_odd", "rgb16_709l_i420_mpeg2", "bgr16_601f_nv12_scale", "site_cosited_i420"]
+GOLDEN_NEW = ["y42b_709l_mpeg2", "y444_601f", "y42b_scale_odd", "rgb16_709l_i420_mpeg2", "bgr16_601f_nv12_scale", "site_cosited_i420",
+              "nearest_3to2_709l_i420", "nearest_up_odd_601f_nv12"]
 
 
 @pytest.fixture(scope="module")
@@ -182,3 +183,18 @@ def test_add_borders(conv, orc, geo):
     mask = np.ones((oh, ow), bool)
     mask[cy:cy + ch, cx:cx + cw] = False
     assert (y[mask] == 16).all() and (u[0 if cy else slice(None), 0] == 128).all()
+
+
+@pytest.mark.parametrize("geo", [(3840, 2160, 1920, 1080), (1920, 1080, 1280, 720), (1280, 720, 1920, 1080), (131, 35, 65, 17), (1920, 1080, 320, 180),
+                                 (640, 360, 641, 361)])
+def test_method_nearest(conv, orc, geo):
+    """videoscale method=nearest: the same kernels with all the weight on one tap — fused (the general kernel, also at
+    exactly 2:1), two-pass and every output format."""
+    iw, ih, ow, oh = geo
+    frame = orc.synth("rand", iw, ih, 51)
+    for fmt, flags in [(0, 0), (1, 0), (0, b200vc.FLAG_FORCE_TWO_PASS), (2, 0), (3, 0)]:
+        conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=1, range_=0, chroma_site=1, scale_mode=b200vc.SCALE_NEAREST, flags=flags)
+        assert conv.info().fused_2to1 == 0
+        buf, off, pit = conv.transform_frame(frame)
+        obuf, ooff, opit = orc.convert(frame, fmt, 1, 0, 1, out_size=(ow, oh), scale_mode=2)
+        assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), plane_views(obuf, ooff, opit, fmt, ow, oh), f"{geo} fmt{fmt} flags{flags}")

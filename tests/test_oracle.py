@@ -176,7 +176,7 @@ def test_c_equals_numpy_scale(orc, geo):
     iw, ih, ow, oh = geo
     frame = orc.synth("rand", iw, ih, 5)
     for fmt in (0, 1):
-        for mode in (0, 1):
+        for mode in (0, 1, 2):                      # bilinear, 2x2 box, nearest
             if mode == 1 and (iw != 2 * ow or ih != 2 * oh):
                 continue
             buf, off, pit = orc.convert(frame, fmt, 1, 0, 1, out_size=(ow, oh), scale_mode=mode)
@@ -200,6 +200,19 @@ def test_scaler_taps_survey_b2(orc):
         assert np.array_equal(orc.h_taps(a, b)[0], N.h_taps(a, b)[0])
         assert np.array_equal(orc.v_taps(a, b)[0], N.v_taps(a, b)[0])
         assert np.array_equal(orc.v_taps(a, b)[1], N.v_taps(a, b)[1])
+
+
+def test_nearest_by_hand(orc):
+    """method=nearest on a ramp: the sample under each output pixel's centre (or at the edge-aligned position)."""
+    plane = np.tile(np.arange(12, dtype=np.uint8) * 10, (4, 1))
+    out = orc.scale_plane(plane, 5, 2, scale_mode=2)
+    if SPEC["NEAREST_CENTRE"]:
+        want = [int((2 * x + 1) * 12 // 10) * 10 for x in range(5)]          # floor((x + 0.5) * 12 / 5)
+    else:
+        inc = ((12 - 1) << 16) // (5 - 1) - 1
+        want = [((x * inc) >> 16) * 10 for x in range(5)]
+    assert list(out[0]) == want and list(out[1]) == want
+    assert np.array_equal(out, N.scale_plane(plane, 5, 2, 1, 2))
 
 
 def test_default_layout_survey_a5(orc):

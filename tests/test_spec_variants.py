@@ -32,7 +32,7 @@ def _env(ov):
 
 def test_variants_cover_every_spec_constant():
     d = S.header_defaults()
-    assert set(d) == set(S.KEYS) and S.name(d) == "m0c1h1b6r1u1"
+    assert set(d) == set(S.KEYS) and S.name(d) == "m0c1h1b6r1u1n1"
     flipped = set()
     for ov in S.VARIANTS.values():
         flipped |= {k for k, v in ov.items() if v != d[k]}
@@ -66,6 +66,15 @@ def test_variants_change_the_output_they_should(orc):
         assert not np.array_equal(got, base_s if scaled else base_u), variant
         if scaled:    # and leaves the unscaled conversion alone
             assert np.array_equal(o.convert(frame, 0, 1, 1, 1)[0], base_u), variant
+    # the two constants that only certain caps reach: 5-6-5 input, method=nearest
+    f16 = np.random.default_rng(3).integers(0, 256, (48, 96, 2), dtype=np.uint8)
+    o = oracle.Oracle(spec=S.VARIANTS["unpack16trunc"])
+    assert not np.array_equal(o.convert(f16, 0, 1, 1, 1, in_format=4)[0], orc.convert(f16, 0, 1, 1, 1, in_format=4)[0])
+    assert np.array_equal(o.convert(frame, 0, 1, 0, 1, out_size=(72, 36))[0], base_s)
+    o = oracle.Oracle(spec=S.VARIANTS["nearestedge"])
+    assert not np.array_equal(o.convert(frame, 0, 1, 0, 1, out_size=(72, 36), scale_mode=2)[0],
+                              orc.convert(frame, 0, 1, 0, 1, out_size=(72, 36), scale_mode=2)[0])
+    assert np.array_equal(o.convert(frame, 0, 1, 0, 1, out_size=(72, 36))[0], base_s)
 
 
 @pytest.mark.gpu

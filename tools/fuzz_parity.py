@@ -63,6 +63,8 @@ def main():
         else:
             ow = max(2, int(iw * rng.uniform(0.3, 1.6)))
             oh = max(2, int(ih * rng.uniform(0.3, 1.6)))
+            if rng.random() < 0.2:
+                mode = 2                                     # videoscale method=nearest
         fmt, m, rg, site, inf = (int(rng.integers(0, 2)) for _ in range(5))
         inf = int(rng.integers(0, 6))                       # four 4-byte orders, RGB16, BGR16
         m = int(rng.integers(0, 3))
@@ -101,7 +103,7 @@ def main():
             for a, b in zip(plane_views(buf, off, pit, fmt, ow, oh), plane_views(*want, fmt, ow, oh)):
                 ok = ok and np.array_equal(a, b)
             # (its device input needs a 16-byte row pitch: widths that are multiples of 4)
-            if scaling and content is None and fmt <= 1 and inf <= 3 and not ((iw | ih | ow | oh) & 1) and iw % 4 == 0 and iw * ih * 3 // 2 <= 2_000_000 and rng.random() < 0.7:
+            if scaling and content is None and mode != 2 and fmt <= 1 and inf <= 3 and not ((iw | ih | ow | oh) & 1) and iw % 4 == 0 and iw * ih * 3 // 2 <= 2_000_000 and rng.random() < 0.7:
                 got = static_entry(conv.lib, f, iw, ih, ow, oh, fmt, m, rg, site, mode, inf)
                 n_static += 1
                 for a, b in zip(plane_views(got, off, pit, fmt, ow, oh), plane_views(*want, fmt, ow, oh)):

@@ -114,6 +114,7 @@ struct b200vc_ctx {
     uint32_t *d_ftaps = nullptr;               // the general fused kernel's per-tile tap records
     FusedTaps ft = { nullptr, nullptr, nullptr, nullptr };
     int tile_h = K2_TILE_H;
+    bool pair_luma = false;
     uint32_t *d_ptaps = nullptr;               // tiled plane scaler's records (two-pass path)
     PlaneTileKind pt[2] = {};
     bool plane_tiled = false;                  // two-pass path: pass 2 is the tiled kernel, not the gather kernel
@@ -243,8 +244,40 @@ inline int tile_org_y(const std::vector<Tap> &vy, const std::vector<Tap> &vc, in
     return std::min(tidx(vy[y0]), 2 * tidx(vc[y0 >> 1])) & ~1;
 }
 
+// The part of its window a tile's taps reach, as phase 1 of the general fused kernel walks it: the
+// window's first frame column (16-byte aligned), whether its first 4-column group is pure halo, and
+// the number of groups after that / the first frame line (even) and the number of line pairs.
+struct FusedSpanX { int sx, kfirst, groups; };
+struct FusedSpanY { int sy, pairs; };
+inline FusedSpanX fused_span_x(const b200vc_config &c, const std::vector<Tap> &hy, const std::vector<Tap> &hc, int x0, int site)
+{
+    const int x1 = std::min(x0 + K2_TILE_W, c.out_w) - 1;
+    const int sx = tile_org_x(hy, hc, x0, site);
+    const int first = std::min(tidx(hy[x0]), 2 * tidx(hc[x0 >> 1]));
+    const int last = std::max(tidx(hy[x1]) + tstep(hy[x1]), 2 * (tidx(hc[x1 >> 1]) + tstep(hc[x1 >> 1])) + 1);
+    const int kfirst = std::min(first - sx, 4) >> 2;
+    return { sx, kfirst, (last - sx) / 4 + 1 - kfirst };
+}
+inline FusedSpanY fused_span_y(const b200vc_config &c, const std::vector<Tap> &vy, const std::vector<Tap> &vc, int y0, int tile_h)
+{
+    const int y1 = std::min(y0 + tile_h, c.out_h) - 1;
+    const int sy = tile_org_y(vy, vc, y0);
+    const int last = std::max(tidx(vy[y1]) + tstep(vy[y1]), 2 * (tidx(vc[y1 >> 1]) + tstep(vc[y1 >> 1])) + 1);
+    return { sy, (last - sy) / 2 + 1 };
+}
+
+// True when the two taps of every output column pair (2l, 2l+1) lie within 4 bytes of the pair's first
+// tap, which is what the kernel's paired form of the luma pass needs (any ratio up to 2).
+bool luma_pairs_fit(const b200vc_config &c, const std::vector<Tap> &hy)
+{
+    for (int x = 0; x + 1 < c.out_w; x += 2)
+        if (tidx(hy[x + 1]) - tidx(hy[x]) > 2 || tidx(hy[x + 1]) < tidx(hy[x])) return false;
+    return true;
+}
+
 void build_fused_taps(const b200vc_config &c, const std::vector<Tap> &hy, const std::vector<Tap> &vy,
-                      const std::vector<Tap> &hc, const std::vector<Tap> &vc, int tile_h, int box_w, FusedTapBlob &o)
+                      const std::vector<Tap> &hc, const std::vector<Tap> &vc, int tile_h, int box_w, bool pair_luma,
+                      FusedTapBlob &o)
 {
     const int site = (c.chroma_site & B200VC_SITE_H_COSITED) ? 1 : 0;
     const int tiles_x = (c.out_w + K2_TILE_W - 1) / K2_TILE_W, tiles_y = (c.out_h + tile_h - 1) / tile_h;
@@ -253,29 +286,42 @@ void build_fused_taps(const b200vc_config &c, const std::vector<Tap> &hy, const 
     o.w.clear();
     o.tile_x = o.w.size();
     for (int bx = 0; bx < tiles_x; bx++) {
-        const int x0 = bx * K2_TILE_W, sx = tile_org_x(hy, hc, x0, site);
-        const int first = std::min(tidx(hy[x0]), 2 * tidx(hc[x0 >> 1]));
-        o.w.push_back((uint32_t)sx);
-        o.w.push_back((uint32_t)(std::min(first - sx, 4) >> 2));               // first 4 columns halo only
+        const FusedSpanX sp = fused_span_x(c, hy, hc, bx * K2_TILE_W, site);
+        o.w.push_back((uint32_t)sp.sx);
+        o.w.push_back((uint32_t)sp.kfirst);
     }
     pad4();
     o.tile_y = o.w.size();
-    for (int by = 0; by < tiles_y; by++) o.w.push_back((uint32_t)tile_org_y(vy, vc, by * tile_h));
+    for (int by = 0; by < tiles_y; by++) {
+        const FusedSpanY sp = fused_span_y(c, vy, vc, by * tile_h, tile_h);
+        o.w.push_back((uint32_t)sp.sy);
+        o.w.push_back((uint32_t)sp.pairs);
+    }
     pad4();
     o.col_rec = o.w.size();
     for (int bx = 0; bx < tiles_x; bx++) {
         const int x0 = bx * K2_TILE_W, sx = tile_org_x(hy, hc, x0, site);
-        for (int k = 0; k < K2_TILE_W; k++)
-            o.w.push_back((uint32_t)(tidx(hy[std::min(x0 + k, c.out_w - 1)]) - sx));
-        for (int k = 0; k < K2_TILE_W; k++) {
-            const Tap t = hy[std::min(x0 + k, c.out_w - 1)];
+        auto h_weights = [](Tap t) {
             const uint32_t f = tstep(t) ? (uint32_t)tfrac(t) : 0u;
-            o.w.push_back((255u - f) | (1u << 8) | (f << 16));
+            return (255u - f) | (1u << 8) | (f << 16);
+        };
+        if (pair_luma) {
+            for (int l = 0; l < K2_TILE_W / 2; l++) {
+                const Tap t0 = hy[std::min(x0 + 2 * l, c.out_w - 1)], t1 = hy[std::min(x0 + 2 * l + 1, c.out_w - 1)];
+                const uint32_t o0 = (uint32_t)(tidx(t0) - sx), d = (uint32_t)(tidx(t1) - tidx(t0));
+                o.w.push_back((o0 & ~3u) | ((8u * (o0 & 3u)) << 16));
+                o.w.push_back(d | (d << 4) | ((d + 1u) << 8) | (3u << 12));
+                o.w.push_back(h_weights(t0));  o.w.push_back(h_weights(t1));
+            }
+        } else {
+            for (int k = 0; k < K2_TILE_W; k++)
+                o.w.push_back((uint32_t)(tidx(hy[std::min(x0 + k, c.out_w - 1)]) - sx));
+            for (int k = 0; k < K2_TILE_W; k++)
+                o.w.push_back(h_weights(hy[std::min(x0 + k, c.out_w - 1)]));
         }
         for (int k = 0; k < K2_TILE_W / 2; k++) {
             const Tap t = hc[std::min(x0 / 2 + k, cw_out - 1)];
-            const uint32_t f = tstep(t) ? (uint32_t)tfrac(t) : 0u;
-            o.w.push_back((uint32_t)(tidx(t) - sx / 2));  o.w.push_back(256u - f);  o.w.push_back(f);  o.w.push_back(0u);
+            o.w.push_back((uint32_t)(2 * (tidx(t) - sx / 2)));  o.w.push_back(h_weights(t));  o.w.push_back(0u);  o.w.push_back(0u);
         }
     }
     o.row_rec = o.w.size();
@@ -287,7 +333,7 @@ void build_fused_taps(const b200vc_config &c, const std::vector<Tap> &hy, const 
         }
         for (int k = 0; k < tile_h / 2; k++) {
             const Tap t = vc[std::min(y0 / 2 + k, ch_out - 1)];
-            o.w.push_back((uint32_t)((tidx(t) - sy / 2) * (box_w / 2)));  o.w.push_back(v_weights(t));
+            o.w.push_back((uint32_t)((tidx(t) - sy / 2) * box_w));  o.w.push_back(v_weights(t));
         }
     }
 }
@@ -351,19 +397,36 @@ void fused_box(const b200vc_config &c, const std::vector<Tap> &hy, const std::ve
     const int site = (c.chroma_site & B200VC_SITE_H_COSITED) ? 1 : 0;
     box_w = box_h = 0;
     for (int x0 = 0; x0 < c.out_w; x0 += K2_TILE_W) {
-        const int x1 = std::min(x0 + K2_TILE_W, c.out_w) - 1;
-        int sx = tile_org_x(hy, hc, x0, site);                                   // 16-byte aligned box start
-        int last = std::max(tidx(hy[x1]) + tstep(hy[x1]), 2 * (tidx(hc[x1 >> 1]) + tstep(hc[x1 >> 1])) + 1);
-        box_w = std::max(box_w, last - sx + 1);
+        const FusedSpanX sp = fused_span_x(c, hy, hc, x0, site);
+        box_w = std::max(box_w, 4 * (sp.kfirst + sp.groups));
     }
-    for (int y0 = 0; y0 < c.out_h; y0 += tile_h) {
-        const int y1 = std::min(y0 + tile_h, c.out_h) - 1;
-        int sy = tile_org_y(vy, vc, y0);
-        int last = std::max(tidx(vy[y1]) + tstep(vy[y1]), 2 * (tidx(vc[y1 >> 1]) + tstep(vc[y1 >> 1])) + 1);
-        box_h = std::max(box_h, last - sy + 1);
+    for (int y0 = 0; y0 < c.out_h; y0 += tile_h)
+        box_h = std::max(box_h, 2 * fused_span_y(c, vy, vc, y0, tile_h).pairs);
+}
+
+// Issue slots the general fused kernel spends on one frame with tiles of tile_h rows, in warp
+// instructions (the kernel is issue-bound; counts per phase from its ncu source page,
+// profiles/r2_general_scaler_experiments.md): set-up per tile, phase 1 per sweep of the 256 threads down
+// the window (items of 4 columns x 2 lines, 256 / groups line pairs at a time), phase 2 per row of luma /
+// chroma, phase 3 per sweep of the tile's 16-byte chunks. What the choice of tile_h changes is mostly how
+// full phase 1's last sweep is.
+double fused_frame_cost(const b200vc_config &c, const std::vector<Tap> &hy, const std::vector<Tap> &vy,
+                        const std::vector<Tap> &hc, const std::vector<Tap> &vc, int tile_h)
+{
+    const int site = (c.chroma_site & B200VC_SITE_H_COSITED) ? 1 : 0;
+    int box_w, box_h;
+    fused_box(c, hy, vy, hc, vc, tile_h, box_w, box_h);
+    std::vector<int> gx, py;
+    for (int x0 = 0; x0 < c.out_w; x0 += K2_TILE_W) gx.push_back(box_w / 4 - fused_span_x(c, hy, hc, x0, site).kfirst);
+    for (int y0 = 0; y0 < c.out_h; y0 += tile_h) py.push_back(fused_span_y(c, vy, vc, y0, tile_h).pairs);
+    double sweeps = 0;                                     // 256 / g line pairs per sweep
+    for (int g : gx) {
+        if (g > 64) return 1e30;                           // (a window the kernel does not take anyway)
+        for (int p : py) sweeps += (p + 256 / g - 1) / (256 / g);
     }
-    box_w = (int)ru(box_w, 4);
-    box_h = (int)ru(box_h, 2);
+    const double tiles = (double)gx.size() * py.size();
+    const double per_tile = 550.0 + 8.0 * 15 * ((tile_h + 3) / 4) + 8.0 * 27 * ((tile_h / 2 + 7) / 8) + 8.0 * 30 * ((tile_h * 6 + 255) / 256);
+    return tiles * per_tile + sweeps * 8.0 * 90;
 }
 
 // True when every tap of an (in_n -> out_n) scaler starts at 2k with the second tap at 2k+1 and,
@@ -681,9 +744,9 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         p.out = out;  p.ft = c->ft;
         p.in_w = g.in_w;  p.in_h = g.in_h;  p.out_w = g.out_w;  p.out_h = g.out_h;
         p.box_w = c->box_w;  p.box_h = c->box_h;  p.tile_h = c->tile_h;  p.n_frames = n_frames;
-        p.box2x2 = g.scale_mode == B200VC_SCALE_BOX_2X2;  p.mx = c->mx;  p.gate = gate;
-        // items per line pair of the window: 8-column items over box_w/4 groups, or one group fewer
-        // when a tile's first group is pure halo
+        p.box2x2 = g.scale_mode == B200VC_SCALE_BOX_2X2;  p.pair_luma = c->pair_luma ? 1 : 0;  p.mx = c->mx;  p.gate = gate;
+        // items per line pair of the window: the box's 4-column groups, or one group fewer when a
+        // tile's first group is pure halo
         const uint32_t groups_x = (uint32_t)c->box_w / 4;
         const uint32_t items_x = groups_x, items_x1 = std::max(groups_x - 1, 1u);
         p.inv_items_x = (65536u + items_x - 1) / items_x;
@@ -914,16 +977,27 @@ int create_impl(b200vc_ctx *c)
         c->tab.hc = d;  CU_TRY(c, cudaMemcpy(d, hc.data(), hc.size() * sizeof(Tap), cudaMemcpyHostToDevice));  d += hc.size();
         c->tab.vc = d;  CU_TRY(c, cudaMemcpy(d, vc.data(), vc.size() * sizeof(Tap), cudaMemcpyHostToDevice));
 
-        // Output rows per tile of the general fused kernel: the tallest of 32, 16, 8 whose window
-        // leaves room for 6 CTAs per SM. Tall tiles amortise the per-tile set-up, the halo lines and
-        // the rounding of phase 1's work to whole warps (measured: 4:3 and 3:2 gain 13-22 % from
-        // 16 -> 32 rows); a window too large for 6 resident CTAs no longer hides its TMA wait
-        // (4K -> 720p: 0.78 of the roofline with 8 rows, 0.67 with 16, 0.37 with 32).
-        for (c->tile_h = 32; ; c->tile_h /= 2) {
+        // Output rows per tile of the general fused kernel: the height of 8, 16, 24, 32 (one
+        // instantiation each) that costs the fewest issue slots per frame (fused_frame_cost) among
+        // those whose window leaves room for 6 CTAs per SM. Tall tiles amortise the per-tile set-up and the halo lines; the height decides
+        // how full the last sweep of phase 1 over the window is (4:3 with 32 rows: 529 items, three
+        // sweeps of 256 threads; with 30 rows: 506, two); a window too large for 6 resident CTAs no
+        // longer hides its TMA wait (4K -> 720p: 0.78 of the roofline with 8 rows, 0.67 with 16, 0.37 with 32).
+        {
+            int best = 8;
+            double best_cost = 0;
+            const char *force = getenv("B200VC_TILE_H");                       // measurements only
+            for (int th = 8; th <= K2_MAX_TILE_H; th += 8) {
+                int bw, bh;
+                fused_box(k, hy, vy, hc, vc, th, bw, bh);
+                if (th > 8 && fused_scale_smem_bytes(bw, bh) + 4096 > (size_t)c->prop.sharedMemPerMultiprocessor / 6) break;
+                const double cost = fused_frame_cost(k, hy, vy, hc, vc, th);
+                if (th == 8 || cost < best_cost) { best = th;  best_cost = cost; }
+            }
+            if (force && atoi(force) >= 8 && atoi(force) <= K2_MAX_TILE_H && !(atoi(force) & 7)) best = atoi(force);
+            c->tile_h = best;
             fused_box(k, hy, vy, hc, vc, c->tile_h, c->box_w, c->box_h);
             c->smem_bytes = fused_scale_smem_bytes(c->box_w, c->box_h);
-            if (c->tile_h == 8 || c->smem_bytes + 4096 <= (size_t)c->prop.sharedMemPerMultiprocessor / 6)
-                break;
         }
         const bool fits = c->box_w <= 256 && c->box_h <= 256 &&
                           c->smem_bytes <= dyn_smem_cap(c);
@@ -946,11 +1020,12 @@ int create_impl(b200vc_ctx *c)
         }
         if (c->path == 1 && !c->fused2x) {
             FusedTapBlob blob;
-            build_fused_taps(k, hy, vy, hc, vc, c->tile_h, c->box_w, blob);
+            c->pair_luma = g.scale_mode != B200VC_SCALE_BOX_2X2 && luma_pairs_fit(k, hy);
+            build_fused_taps(k, hy, vy, hc, vc, c->tile_h, c->box_w, c->pair_luma, blob);
             CU_TRY(c, cudaMalloc(&c->d_ftaps, blob.w.size() * sizeof(uint32_t)));
             CU_TRY(c, cudaMemcpy(c->d_ftaps, blob.w.data(), blob.w.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
             c->ft.tile_x = reinterpret_cast<const int2 *>(c->d_ftaps + blob.tile_x);
-            c->ft.tile_y = reinterpret_cast<const int *>(c->d_ftaps + blob.tile_y);
+            c->ft.tile_y = reinterpret_cast<const int2 *>(c->d_ftaps + blob.tile_y);
             c->ft.col_rec = c->d_ftaps + blob.col_rec;
             c->ft.row_rec = c->d_ftaps + blob.row_rec;
         }

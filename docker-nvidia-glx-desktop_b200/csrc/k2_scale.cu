@@ -72,57 +72,73 @@ __device__ __forceinline__ void repeat_last_column_and_line(uint32_t *s_src, int
             if (!(fixx && c == dupx)) s_src[dupy * bw + c] = s_src[(dupy - 1) * bw + c];
 }
 
-// Phase 1 of the general fused kernel: one item = 8 columns x 2 lines of the window (two 4-column
-// groups; `two` false: only the first), BGRx in s_src -> Y bytes in s_yf and filtered, vertically
-// averaged (u,v) pairs in s_cf. kx = first group's index in the line pair, sx0 = window's frame column.
+// Phase 1 of the general fused kernel: one item = 4 columns x 2 lines of the window, BGRx at ra (second
+// line bw words on) -> Y bytes at ya and two filtered, vertically averaged (u,v) byte pairs at cf. `left`: the
+// group has a left chroma neighbour in the window (not frame column 0, not the window's first group);
+// e0 / e2: its first / second even column is the frame's last one (B200VC_SPEC_COSITED_LAST_1_3).
 template <int SITE, bool NEG, bool EDGE>
-__device__ __forceinline__ void convert_item(const uint32_t *s_src, uint8_t *s_yf, uint32_t *s_cf, int bw, int kx, int ky,
-                                             int sx0, int in_w, bool two, const Matrix &m)
+__device__ __forceinline__ void convert_item(const uint32_t *ra, uint8_t *ya, uint8_t *cf, int bw, bool left, bool e0, bool e2,
+                                             const Matrix &m)
 {
-    const uint32_t *ra = s_src + (2 * ky) * bw + 4 * kx, *rb = ra + bw;
-    uint8_t *ya = s_yf + (2 * ky) * bw + 4 * kx;
-    uint32_t *cf = s_cf + ky * (bw >> 1) + 2 * kx;
-    const int ac = sx0 + 4 * kx;                          // frame column of pixel 0 (multiple of 4)
-    uint32_t la = 0, lb = 0;                              // left chroma neighbours of the group
-#pragma unroll
-    for (int h = 0; h < 2; h++) {
-        if (h == 1 && !two) break;
-        const uint4 a = *reinterpret_cast<const uint4 *>(ra + 4 * h);
-        const uint4 b = *reinterpret_cast<const uint4 *>(rb + 4 * h);
-        *reinterpret_cast<uint32_t *>(ya + 4 * h) =
-            pack_luma4(luma_sum(a.x, m), luma_sum(a.y, m), luma_sum(a.z, m), luma_sum(a.w, m));
-        *reinterpret_cast<uint32_t *>(ya + bw + 4 * h) =
-            pack_luma4(luma_sum(b.x, m), luma_sum(b.y, m), luma_sum(b.z, m), luma_sum(b.w, m));
+    const uint32_t *rb = ra + bw;
+    const uint4 a = *reinterpret_cast<const uint4 *>(ra);
+    const uint4 b = *reinterpret_cast<const uint4 *>(rb);
+    *reinterpret_cast<uint32_t *>(ya) = pack_luma4(luma_sum(a.x, m), luma_sum(a.y, m), luma_sum(a.z, m), luma_sum(a.w, m));
+    *reinterpret_cast<uint32_t *>(ya + bw) = pack_luma4(luma_sum(b.x, m), luma_sum(b.y, m), luma_sum(b.z, m), luma_sum(b.w, m));
 
-        const uint32_t pa0 = chroma_pair<NEG>(a.x, m), pa1 = chroma_pair<NEG>(a.y, m);
-        const uint32_t pa2 = chroma_pair<NEG>(a.z, m), pa3 = chroma_pair<NEG>(a.w, m);
-        const uint32_t pb0 = chroma_pair<NEG>(b.x, m), pb1 = chroma_pair<NEG>(b.y, m);
-        const uint32_t pb2 = chroma_pair<NEG>(b.z, m), pb3 = chroma_pair<NEG>(b.w, m);
-        uint32_t c0, c1;
-        if (SITE == 0) {
-            c0 = avg2(avg2(pa0, pa1), avg2(pb0, pb1));
-            c1 = avg2(avg2(pa2, pa3), avg2(pb2, pb3));
-        } else {
-            if (h == 0) {
-                // frame column 0 takes itself; the window's first group has no left neighbour (its
-                // first chroma column is halo and is never consumed)
-                la = pa0;  lb = pb0;
-                if (ac != 0 && kx > 0) {
-                    la = chroma_pair<NEG>(ra[-1], m);
-                    lb = chroma_pair<NEG>(rb[-1], m);
-                }
-            }
-            // right neighbours: the frame's last even column (in_w - 2, in_w > 2) takes itself
-            // (B200VC_SPEC_COSITED_LAST_1_3 = 0: the plain 1-2-1 filter runs to the end; an odd frame's
-            // last pixel has been duplicated into the window by then, which is the same thing)
-            const bool e0 = EDGE && B200VC_SPEC_COSITED_LAST_1_3 && in_w > 2 && ac + 4 * h == in_w - 2;
-            const bool e2 = EDGE && B200VC_SPEC_COSITED_LAST_1_3 && in_w > 2 && ac + 4 * h + 2 == in_w - 2;
-            c0 = avg2(filt121(la, pa0, e0 ? pa0 : pa1), filt121(lb, pb0, e0 ? pb0 : pb1));
-            c1 = avg2(filt121(pa1, pa2, e2 ? pa2 : pa3), filt121(pb1, pb2, e2 ? pb2 : pb3));
-            la = pa3;  lb = pb3;
+    const uint32_t pa0 = chroma_pair<NEG>(a.x, m), pa1 = chroma_pair<NEG>(a.y, m);
+    const uint32_t pa2 = chroma_pair<NEG>(a.z, m), pa3 = chroma_pair<NEG>(a.w, m);
+    const uint32_t pb0 = chroma_pair<NEG>(b.x, m), pb1 = chroma_pair<NEG>(b.y, m);
+    const uint32_t pb2 = chroma_pair<NEG>(b.z, m), pb3 = chroma_pair<NEG>(b.w, m);
+    uint32_t c0, c1;
+    if (SITE == 0) {
+        c0 = avg2(avg2(pa0, pa1), avg2(pb0, pb1));
+        c1 = avg2(avg2(pa2, pa3), avg2(pb2, pb3));
+    } else {
+        // frame column 0 takes itself; the window's first group has no left neighbour (its first
+        // chroma column is halo and is never consumed)
+        uint32_t la = pa0, lb = pb0;
+        if (left) {
+            la = chroma_pair<NEG>(ra[-1], m);
+            lb = chroma_pair<NEG>(rb[-1], m);
         }
-        *reinterpret_cast<uint2 *>(cf + 2 * h) = make_uint2(c0, c1);
+        // right neighbours: the frame's last even column (in_w - 2, in_w > 2) takes itself
+        // (B200VC_SPEC_COSITED_LAST_1_3 = 0: the plain 1-2-1 filter runs to the end; an odd frame's
+        // last pixel has been duplicated into the window by then, which is the same thing)
+        c0 = avg2(filt121(la, pa0, (EDGE && e0) ? pa0 : pa1), filt121(lb, pb0, (EDGE && e0) ? pb0 : pb1));
+        c1 = avg2(filt121(pa1, pa2, (EDGE && e2) ? pa2 : pa3), filt121(pb1, pb2, (EDGE && e2) ? pb2 : pb3));
     }
+    *reinterpret_cast<uint32_t *>(cf) = prmt(c0, c1, 0x6420);              // u0 v0 u1 v1
+}
+
+// Phase 2 helpers of the general fused kernel. A line's horizontal pass leaves two samples (still with
+// their 8 fraction bits) whose high bytes are packed into bytes 0 and 1 of one word; the vertical tap
+// then takes [A,A,B,B] from the words of the two lines (v_weight_word, host_tables.h).
+//
+// luma, two adjacent output columns per lane: their four taps lie within 4 bytes of the first tap
+// (step <= 2), which one funnel shift of two aligned words brings into a register
+__device__ __forceinline__ uint32_t h_pass_luma_pair(const uint8_t *line, uint32_t sh, uint32_t sel1, uint32_t wh0, uint32_t wh1)
+{
+    const uint32_t w0 = *reinterpret_cast<const uint32_t *>(line), w1 = *reinterpret_cast<const uint32_t *>(line + 4);
+    const uint32_t v = __funnelshift_r(w0, w1, sh);                        // bytes i0 .. i0 + 3 of the line
+    const uint32_t s0 = dp4a_uu(prmt(v, 0u, 0x3100), wh0, 0u);             // [a,a,b,_] . (255-f, 1, f, 0)
+    const uint32_t s1 = dp4a_uu(prmt(v, 0u, sel1), wh1, 0u);
+    return prmt(s0, s1, 0x0051);
+}
+
+// chroma, one (u,v) sample per lane: the plane holds u,v byte pairs, the two taps are two 16-bit loads
+__device__ __forceinline__ uint32_t h_pass_chroma(const uint8_t *smp, uint32_t wh)
+{
+    const uint32_t lo = *reinterpret_cast<const uint16_t *>(smp), hi = *reinterpret_cast<const uint16_t *>(smp + 2);
+    const uint32_t su = dp4a_uu(prmt(lo, hi, 0x2400), wh, 0u);             // [u0,u0,u1,0]
+    const uint32_t sv = dp4a_uu(prmt(lo, hi, 0x2511), wh, 0u);             // [v0,v0,v1,0]
+    return prmt(su, sv, 0x0051);
+}
+
+__device__ __forceinline__ uint32_t v_pass_pair(uint32_t top, uint32_t bot, uint32_t wv)
+{
+    const uint32_t d0 = dp4a_uu(prmt(top, bot, 0x4400), wv, 128u), d1 = dp4a_uu(prmt(top, bot, 0x5511), wv, 128u);
+    return prmt(d0, d1, 0x0051);                                           // the two samples in bytes 0 and 1
 }
 
 template <int FMT, int SITE, bool NEG, int TILE_H, bool ODD>
@@ -133,31 +149,29 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
     __shared__ __align__(8) uint64_t s_bar;
     // this tile's taps, ready to use (FusedTaps): copied from the host-made records while the TMA
     // load is in flight
-    __shared__ __align__(16) uint32_t s_col[4 * TW];           // hyo[TW] | hyw[TW] | hc[TW/2] quads
+    __shared__ __align__(16) uint32_t s_col[4 * TW];           // luma records (two forms, FusedTaps) | hc[TW/2] quads
     __shared__ __align__(8) uint32_t s_row[3 * TILE_H];        // vy[TILE_H] pairs | vc[TILE_H/2] pairs
     __shared__ __align__(16) uint8_t s_out[TW * TILE_H * 3 / 2];   // output tile: Y, then U and V (or UV) tiles
-    const uint32_t *s_hyo = s_col, *s_hyw = s_col + TW;
     const uint4 *s_hc = reinterpret_cast<const uint4 *>(s_col + 2 * TW);
     const uint2 *s_vy = reinterpret_cast<const uint2 *>(s_row), *s_vc = s_vy + TILE_H;
 
     const int bw = p.box_w, bh = p.box_h;
     uint32_t *s_src = reinterpret_cast<uint32_t *>(smem);                 // [bh][bw] pixels
     uint8_t *s_yf = smem + (size_t)bw * bh * 4;                           // [bh][bw] luma
-    uint32_t *s_cf = reinterpret_cast<uint32_t *>(s_yf + (size_t)bw * bh); // [bh/2][bw/2] (u,v) pairs
+    uint8_t *s_cf = s_yf + (size_t)bw * bh;                               // [bh/2][bw/2] (u,v) byte pairs
 
     const int tid = threadIdx.x;
-    const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TILE_H;
-    const int frame = blockIdx.z;
 
     // ---- phase 0: source window origin (host-made, per tile column / tile row), TMA load --------
     const int2 org_x = p.ft.tile_x[blockIdx.x];          // window's frame column (multiple of 4), kfirst
-    const int sx0 = org_x.x, kfirst = org_x.y, sy0 = p.ft.tile_y[blockIdx.y];
+    const int2 org_y = p.ft.tile_y[blockIdx.y];          // window's frame line (even), line pairs in use
+    const int sx0 = org_x.x, kfirst = org_x.y, sy0 = org_y.x;
     if (tid == 0) {
         if (p.gate.flags) {                               // frame still arriving: wait for the window's last line
             gate_wait_thread(p.gate, min(max(sy0 + bh, 1), p.in_h) - 1);
             asm volatile("fence.proxy.async;" ::: "memory");
         }
-        issue_window_load(&s_bar, s_src, &src_map, sx0, sy0, frame, (uint32_t)bw * bh * 4);
+        issue_window_load(&s_bar, s_src, &src_map, sx0, sy0, (int)blockIdx.z, (uint32_t)bw * bh * 4);
     }
     s_col[tid] = p.ft.col_rec[blockIdx.x * (4 * TW) + tid];               // 4 * TW == 256 == blockDim.x
     if (tid < 3 * TILE_H)
@@ -180,28 +194,38 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
     // the cosited filter gives it l + 3c, the vertical mean pairs the line with itself — SURVEY A.4.
     // The TMA unit zero-filled those cells; after this, phase 1 needs no special case.)
     if (ODD) {                                         // instantiated apart: even frames pay nothing
-        repeat_last_column_and_line(s_src, bw, bh, p.in_w - sx0, p.in_h - p.ft.tile_y[blockIdx.y], p.in_w & 1, p.in_h & 1, tid);
+        repeat_last_column_and_line(s_src, bw, bh, p.in_w - sx0, p.in_h - sy0, p.in_w & 1, p.in_h & 1, tid);
         __syncthreads();
     }
 
-    // ---- phase 1: convert the window (8 columns x 2 lines per item, as two halves) ---------------
-    // Items are walked without divisions (host-made reciprocal for the start, increments after); a
-    // first 4-column group that holds nothing but halo is skipped. The second half takes its left
-    // chroma neighbours from the first half's registers. Only tiles whose window reaches the frame's
-    // last column pay for the right-edge rule of the cosited filter (uniform branch).
+    // ---- phase 1: convert the window (4 columns x 2 lines per item) ---------------------------------
+    // A thread keeps its 4-column group and walks down the window: the 256 threads form a block of
+    // (groups per line pair) x (256 / groups) items that sweeps the window top to bottom, so everything
+    // but three addresses is loop-invariant (no divisions: host-made reciprocal of the group count).
+    // Only the line pairs this tile's taps reach are converted (the box is the tallest window of any
+    // tile), and a first group that holds nothing but halo is skipped. Only tiles whose window reaches
+    // the frame's last column pay for the right-edge rule of the cosited filter (uniform branch).
     {
-        const int items_x = (bw >> 2) - kfirst, n_items = items_x * (bh >> 1);   // 4-column groups
+        const int items_x = (bw >> 2) - kfirst, pairs = org_y.y;
         const uint32_t inv = kfirst ? p.inv_items_x1 : p.inv_items_x;
-        int ky = (int)(((uint32_t)tid * inv) >> 16), kxr = tid - ky * items_x;
-        const int dky = (int)((256u * inv) >> 16), dkx = 256 - dky * items_x;
-        const bool redge = SITE != 0 && sx0 + bw >= p.in_w;
-        for (int it = tid; it < n_items; it += 256, kxr += dkx, ky += dky) {
-            if (kxr >= items_x) { kxr -= items_x; ky++; }
-            const int kx = kxr + kfirst;
-            if (redge)
-                convert_item<SITE, NEG, true>(s_src, s_yf, s_cf, bw, kx, ky, sx0, p.in_w, false, p.mx);
-            else
-                convert_item<SITE, NEG, false>(s_src, s_yf, s_cf, bw, kx, ky, sx0, p.in_w, false, p.mx);
+        const int rps = (int)((256u * inv) >> 16);                          // line pairs per sweep: 256 / items_x
+        const int ky0 = (int)(((uint32_t)tid * inv) >> 16), kx = tid - ky0 * items_x + kfirst;
+        if (ky0 < rps) {
+            const int ac = sx0 + 4 * kx;                                    // frame column of the group (multiple of 4)
+            const bool left = SITE != 0 && ac != 0 && kx > 0;
+            const bool redge = SITE != 0 && B200VC_SPEC_COSITED_LAST_1_3 && p.in_w > 2 && sx0 + bw >= p.in_w;
+            const bool e0 = redge && ac == p.in_w - 2, e2 = redge && ac + 2 == p.in_w - 2;
+            const int o = 2 * ky0 * bw + 4 * kx, step = rps * bw;
+            const uint32_t *ra = s_src + o;
+            uint8_t *ya = s_yf + o;
+            uint8_t *cf = s_cf + ky0 * bw + 4 * kx;                         // two (u,v) byte pairs per item
+            if (redge) {
+                for (int ky = ky0; ky < pairs; ky += rps, ra += 2 * step, ya += 2 * step, cf += step)
+                    convert_item<SITE, NEG, true>(ra, ya, cf, bw, left, e0, e2, p.mx);
+            } else {
+                for (int ky = ky0; ky < pairs; ky += rps, ra += 2 * step, ya += 2 * step, cf += step)
+                    convert_item<SITE, NEG, false>(ra, ya, cf, bw, left, false, false, p.mx);
+            }
         }
     }
     __syncthreads();
@@ -209,21 +233,41 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
     // ---- phase 2: scale out of the planes into an output tile in shared memory ----------------
     // Taps come ready to use (FusedTaps, staged above as offsets into the planes): nothing is decoded
     // here. Both taps are always read (a clamped one has weight 0; the byte or line after the window
-    // is inside this CTA's shared memory, see fused_scale_smem_bytes). A warp covers 32 consecutive
-    // output columns of one row at a time: its byte loads fall into at most 32 consecutive words
-    // (ratio < 4), free of bank conflicts, and the row's vertical tap is a uniform load. Every sample of
-    // the tile is computed (the staged taps of columns and rows past the frame edge are clamped copies);
-    // the frame edge is applied when the tile is stored.
+    // is inside this CTA's shared memory, see fused_scale_smem_bytes). Every sample of the tile is
+    // computed (the staged taps of columns and rows past the frame edge are clamped copies); the frame
+    // edge is applied when the tile is stored. A warp works on whole rows (the row's vertical tap is a
+    // broadcast load). Round 1's form of this phase (four byte loads and a byte store per luma sample)
+    // kept the LSU data pipe at 89 % (profiles/r1_k2general_4to3_ncu_full_raw_v4.csv); word loads shared
+    // by a lane's two columns halve that. Keeping the lower line's horizontal pass for the next row, which
+    // at ratios below 2 usually starts on it, saves loads but costs more issue slots in branches than
+    // it saves in arithmetic (measured, profiles/r2_general_scaler_experiments.md) and is not done.
     const int lane = tid & 31, wrp = tid >> 5;
-    {
-        // luma: one output column x 4 rows per thread
-        constexpr int RPT = TILE_H / 4;           // rows per thread: 8 warps = 2 column halves x 4 row groups
+    if (p.pair_luma) {
+        // luma: two adjacent output columns per lane, rows wrp * RPW ...
+        constexpr int RPW = TILE_H / 8;
+        const uint4 rec = reinterpret_cast<const uint4 *>(s_col)[lane];   // {window byte of the first word | shift << 16, sel1, wh0, wh1}
+        const uint8_t *col = s_yf + (rec.x & 0xffffu);
+        const uint32_t sh = rec.x >> 16;
+        uint16_t *dst = reinterpret_cast<uint16_t *>(s_out) + wrp * RPW * (TW / 2) + lane;
+#pragma unroll
+        for (int k = 0; k < RPW; k++) {
+            const uint2 tv = s_vy[wrp * RPW + k]; // {byte offset of the upper line, vertical weights}
+            const uint8_t *l0 = col + (int)tv.x;
+            const uint32_t top = h_pass_luma_pair(l0, sh, rec.y, rec.z, rec.w);
+            const uint32_t bot = h_pass_luma_pair(l0 + bw, sh, rec.y, rec.z, rec.w);
+            dst[k * (TW / 2)] = (uint16_t)v_pass_pair(top, bot, tv.y);
+        }
+    } else {
+        // luma, any step (ratios above 2, BOX): one output column x TILE_H/4 rows per thread, 8 warps =
+        // 2 column halves x 4 row groups; byte loads
+        const uint32_t *s_hyo = s_col, *s_hyw = s_col + TW;
+        constexpr int RPT = TILE_H / 4;
         const int c = (wrp & 1) * 32 + lane, rb = (wrp >> 1) * RPT;
         const uint32_t wh = s_hyw[c];
         const uint8_t *col = s_yf + (int)s_hyo[c];
 #pragma unroll
-        for (int k = 0; k < RPT; k++) {
-            const uint2 tv = s_vy[rb + k];
+        for (int r = rb; r < rb + RPT; r++) {
+            const uint2 tv = s_vy[r];
             const uint8_t *r0 = col + (int)tv.x, *r1 = r0 + bw;
             uint32_t d;
             if (p.box2x2) {
@@ -235,41 +279,43 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
                 const uint32_t s1 = dp4a_uu(prmt(r1[0], r1[1], 0x1400), wh, 0u);
                 d = dp4a_uu(prmt(s0, s1, 0x5511), tv.y, 128u);
             }
-            s_out[(rb + k) * TW + c] = (uint8_t)(d >> 8);
+            s_out[r * TW + c] = (uint8_t)(d >> 8);
         }
     }
     {
-        // chroma: one (u,v) sample per thread and row, warp w does chroma rows w, w + 8, ...
-        const uint4 th = s_hc[lane];
-        const int cw = bw >> 1;
+        // chroma: one (u,v) sample per lane, warp w does chroma rows w * CPW ... (while there are rows)
+        constexpr int CPW = (TILE_H / 2 + 7) / 8;
+        const uint4 th = s_hc[lane];              // {byte offset of the first tap in a (u,v) line, wh, -, -}
+        const uint8_t *col = s_cf + (int)th.x;
         uint8_t *oc = s_out + TW * TILE_H;
 #pragma unroll
-        for (int r = wrp; r < TILE_H / 2; r += 8) {
+        for (int r = wrp * CPW; r < wrp * CPW + CPW; r++) {
+            if (r >= TILE_H / 2) break;
             const uint2 tv = s_vc[r];
-            const uint32_t *r0 = s_cf + (int)th.x + (int)tv.x, *r1 = r0 + cw;
-            uint32_t uv;                              // u in byte 1, v in byte 3
+            const uint8_t *l0 = col + (int)tv.x;
+            uint32_t uv;                          // u in byte 0, v in byte 1
             if (p.box2x2) {
-                uv = (((r0[0] + r0[1] + r1[0] + r1[1] + 0x00020002u) >> 2) & LANES8) << 8;
+                const uint32_t a0 = *reinterpret_cast<const uint16_t *>(l0), a1 = *reinterpret_cast<const uint16_t *>(l0 + 2);
+                const uint32_t b0 = *reinterpret_cast<const uint16_t *>(l0 + bw), b1 = *reinterpret_cast<const uint16_t *>(l0 + bw + 2);
+                const uint32_t q = (a0 & 0xffu) + (a1 & 0xffu) + (b0 & 0xffu) + (b1 & 0xffu) + 2u;          // u
+                const uint32_t w = (a0 >> 8) + (a1 >> 8) + (b0 >> 8) + (b1 >> 8) + 2u;                      // v
+                uv = (q >> 2) | ((w >> 2) << 8);
             } else {
-                // both lanes at once: each lane's weighted sum is <= 255*256, its high byte the sample
-                const uint32_t ha = r0[0] * th.y + r0[1] * th.z;
-                const uint32_t hb = r1[0] * th.y + r1[1] * th.z;
-                const uint32_t du = dp4a_uu(prmt(ha, hb, 0x5511), tv.y, 128u);
-                const uint32_t dv = dp4a_uu(prmt(ha, hb, 0x7733), tv.y, 128u);
-                uv = prmt(du, dv, 0x5010);            // du.0, du.1, dv.0, dv.1
+                uv = v_pass_pair(h_pass_chroma(l0, th.y), h_pass_chroma(l0 + bw, th.y), tv.y);
             }
             if (FMT == 0) {
-                oc[r * (TW / 2) + lane] = (uint8_t)(uv >> 8);                            // U tile, then V tile
-                oc[(TW / 2) * (TILE_H / 2) + r * (TW / 2) + lane] = (uint8_t)(uv >> 24);
+                oc[r * (TW / 2) + lane] = (uint8_t)uv;                                   // U tile, then V tile
+                oc[(TW / 2) * (TILE_H / 2) + r * (TW / 2) + lane] = (uint8_t)(uv >> 8);
             } else {
-                reinterpret_cast<uint16_t *>(oc)[r * (TW / 2) + lane] = (uint16_t)prmt(uv, 0, 0x4431);   // u, v
+                reinterpret_cast<uint16_t *>(oc)[r * (TW / 2) + lane] = (uint16_t)uv;    // u, v
             }
         }
     }
     __syncthreads();
 
     // ---- phase 3: the tile leaves as 16-byte stores (4 chunks per luma row, 4 per chroma row pair) --
-    const long long fo = (long long)frame * p.out.frame_stride;
+    const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TILE_H;
+    const long long fo = (long long)blockIdx.z * p.out.frame_stride;
 #pragma unroll
     for (int c = tid; c < TILE_H * 6; c += 256) {
         const uint8_t *src = s_out + c * 16;
@@ -283,7 +329,7 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
             dst = p.out.p[0] + fo + (long long)(y0 + r) * p.out.pitch[0] + xb;
         } else if (FMT == 0) {
             const int i = c - TILE_H * 4;
-            const int pl = i / TILE_H, r = (i >> 1) & (TILE_H / 2 - 1), xb = (x0 >> 1) + (c & 1) * 16;
+            const int pl = i / TILE_H, r = (i - pl * TILE_H) >> 1, xb = (x0 >> 1) + (c & 1) * 16;
             row_ok = (y0 >> 1) + r < ((p.out_h + 1) >> 1);
             n = ((p.out_w + 1) >> 1) - xb;
             dst = p.out.p[1 + pl] + fo + (long long)((y0 >> 1) + r) * p.out.pitch[1 + pl] + xb;
@@ -556,12 +602,13 @@ __global__ void __launch_bounds__(128) k2_plane_scale_kernel(const PlaneScalePar
 template <int FMT, int SITE, bool NEG, bool ODD>
 cudaError_t launch_fused4(const CUtensorMap &map, const FusedScaleParams &p, dim3 grid, size_t smem, cudaStream_t st)
 {
-    if (p.tile_h == 8)
-        k2_fused_scale_kernel<FMT, SITE, NEG, 8, ODD><<<grid, 256, smem, st>>>(map, p);
-    else if (p.tile_h == 32)
-        k2_fused_scale_kernel<FMT, SITE, NEG, 32, ODD><<<grid, 256, smem, st>>>(map, p);
-    else
-        k2_fused_scale_kernel<FMT, SITE, NEG, 16, ODD><<<grid, 256, smem, st>>>(map, p);
+    switch (p.tile_h) {                                   // K2_TILE_HEIGHTS
+    case 8:  k2_fused_scale_kernel<FMT, SITE, NEG, 8, ODD><<<grid, 256, smem, st>>>(map, p);  break;
+    case 16: k2_fused_scale_kernel<FMT, SITE, NEG, 16, ODD><<<grid, 256, smem, st>>>(map, p);  break;
+    case 24: k2_fused_scale_kernel<FMT, SITE, NEG, 24, ODD><<<grid, 256, smem, st>>>(map, p);  break;
+    case 32: k2_fused_scale_kernel<FMT, SITE, NEG, 32, ODD><<<grid, 256, smem, st>>>(map, p);  break;
+    default: return cudaErrorInvalidValue;
+    }
     return cudaGetLastError();
 }
 
@@ -616,24 +663,23 @@ cudaError_t launch_fused_2x(const CUtensorMap &src_map, const Fused2xParams &p, 
 
 size_t fused_scale_smem_bytes(int box_w, int box_h)
 {
-    // source pixels + Y plane + (u,v) plane, and one spare chroma line: a clamped second tap still
-    // reads index+1 (with weight 0), which for the last chroma line lies just behind the plane
-    return (size_t)box_w * box_h * 6 + (size_t)box_w * 2 + 16;
+    // source pixels (4 bytes) + Y plane (1) + (u,v) plane (a byte pair per 2x2 pixels), and one spare
+    // chroma line: a clamped second tap still reads index+1 (with weight 0), which for the last chroma
+    // line lies just behind the plane
+    return (size_t)box_w * box_h * 11 / 2 + (size_t)box_w * 2 + 16;
 }
 
 cudaError_t fused_scale_prepare(size_t optin_bytes)
 {
     cudaError_t e;
-#define B200VC_SET(F, S, N) \
-    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 8, false>, optin_bytes)) != cudaSuccess) return e; \
-    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 16, false>, optin_bytes)) != cudaSuccess) return e; \
-    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 32, false>, optin_bytes)) != cudaSuccess) return e; \
-    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 8, true>, optin_bytes)) != cudaSuccess) return e; \
-    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 16, true>, optin_bytes)) != cudaSuccess) return e; \
-    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, 32, true>, optin_bytes)) != cudaSuccess) return e;
+#define B200VC_SET1(F, S, N, H) \
+    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, H, false>, optin_bytes)) != cudaSuccess) return e; \
+    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, H, true>, optin_bytes)) != cudaSuccess) return e;
+#define B200VC_SET(F, S, N) B200VC_SET1(F, S, N, 8) B200VC_SET1(F, S, N, 16) B200VC_SET1(F, S, N, 24) B200VC_SET1(F, S, N, 32)
     B200VC_SET(0, 0, false) B200VC_SET(0, 0, true) B200VC_SET(0, 1, false) B200VC_SET(0, 1, true)
     B200VC_SET(1, 0, false) B200VC_SET(1, 0, true) B200VC_SET(1, 1, false) B200VC_SET(1, 1, true)
 #undef B200VC_SET
+#undef B200VC_SET1
     return cudaSuccess;
 }
 
@@ -642,7 +688,7 @@ cudaError_t launch_fused_scale(const CUtensorMap &src_map, const FusedScaleParam
 {
     if (p.out_w <= 0 || p.out_h <= 0 || p.n_frames <= 0)
         return cudaErrorInvalidValue;
-    if (p.tile_h != 8 && p.tile_h != 16 && p.tile_h != 32)
+    if (p.tile_h < 8 || p.tile_h > K2_MAX_TILE_H || (p.tile_h & 7))
         return cudaErrorInvalidValue;
     dim3 grid((p.out_w + TW - 1) / TW, (p.out_h + p.tile_h - 1) / p.tile_h, p.n_frames);
     const size_t smem = fused_scale_smem_bytes(p.box_w, p.box_h);

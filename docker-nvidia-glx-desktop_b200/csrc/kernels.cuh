@@ -83,18 +83,23 @@ struct ScaleTables {
 // column and one per tile row (host-made, api.cu build_fused_taps). Indices are offsets into the
 // tile's source window; a clamped second tap (step 0) has weight 0, so the kernel always reads index+1.
 //   tile_x[bx] = {window's first frame column (multiple of 4, may be -4), 1 if its first 4 columns
-//                 are pure halo}, tile_y[by] = window's first frame line (even)
-//   col_rec[bx][256]: 64 x hyo (byte offset of the first tap in a Y line of the window)
+//                 are pure halo}
+//   tile_y[by] = {window's first frame line (even), line pairs the tile's taps reach}
+//   col_rec[bx][256], luma part, pair_luma == 0:
+//                     64 x hyo (byte offset of the first tap in a Y line of the window)
 //                     64 x hyw = (255-f) | 1<<8 | f<<16 : [a,a,b,_] . hyw = a*(256-f) + b*f
-//                     32 x {offset of the first tap in a (u,v) line, 256-f, f, 0}
+//                   pair_luma == 1 (every column pair's taps lie within 4 bytes of the first):
+//                     32 x {(hyo of column 2l) & ~3 | 8 * (hyo & 3) << 16, selector of column 2l+1's
+//                           [a,a,b,_] in the 4 bytes from column 2l's first tap, hyw of 2l, hyw of 2l+1}
+//                   chroma part: 32 x {byte offset of the first tap in a (u,v) line, hyw, 0, 0}
 //   row_rec[by][3*tile_h]: tile_h x {byte offset of the first line in the Y plane, wv}
-//                          tile_h/2 x {word offset of the first line in the (u,v) plane, wv}
+//                          tile_h/2 x {byte offset of the first line in the (u,v) plane, wv}
 //       wv = wa1 | wa2<<8 | wb1<<16 | wb2<<24 (host_tables.h v_weight_word), for the 6-bit tap
 //       wa1+wa2 = 256-4*p1, wb1+wb2 = 4*p1: ([a,a,b,b] . wv + 128) >> 8 == (a*(64-p1) + b*p1 + 32) >> 6
 // Columns and rows past the frame edge repeat the last valid entry.
 struct FusedTaps {
     const int2 *tile_x;
-    const int *tile_y;
+    const int2 *tile_y;
     const uint32_t *col_rec, *row_rec;
 };
 
@@ -104,9 +109,10 @@ struct FusedScaleParams {
     FusedTaps ft;
     int in_w, in_h, out_w, out_h;
     int box_w, box_h;       // source window per tile (pixels); box_w % 4 == 0, box_h even
-    int tile_h;             // output rows per tile: 32, 16 or 8 (the tallest whose window leaves 6 CTAs per SM)
+    int tile_h;             // output rows per tile: 8, 16, 24 or 32 (the cheapest per frame, api.cu fused_frame_cost)
     int n_frames;
     int box2x2;             // scale_mode == BOX_2X2
+    int pair_luma;          // form of the luma column records (FusedTaps); never with box2x2
     uint32_t inv_items_x;   // ceil(65536 / items per line pair), for box_w/4 and box_w/4 - 1 groups:
     uint32_t inv_items_x1;  // tid / items_x without a division (exact for tid <= 256, up to 64 items)
     RowGate gate;           // n_frames == 1 only
@@ -167,6 +173,7 @@ constexpr int K1_TILE_H = 16;    // one macroblock row per warp stripe
 constexpr int K1_WARPS_PER_CTA = 4;
 constexpr int K2_TILE_W = 64;    // output pixels per CTA tile
 constexpr int K2_TILE_H = 16;    // exact-2:1 kernel; the general kernel's is FusedScaleParams::tile_h
+constexpr int K2_MAX_TILE_H = 32;
 constexpr int K2X_SRC_W = 128;   // exact-2:1 kernel: source tile per CTA (8 warps x 4 lines, 32 lanes x 4 pixels)
 constexpr int K2X_SRC_H = 32;
 constexpr int K2X_TILES_PER_CTA = 2;   // exact-2:1 kernel: tiles per CTA (the later loads hide behind the first tile's work)

@@ -123,17 +123,30 @@ def test_odd_sizes_with_scaling(conv, orc, geo, two_pass):
                             f"{geo} fmt{fmt} two_pass={two_pass}")
 
 
-@pytest.mark.parametrize("geo,flags,tile_h", [((2560, 1440, 1920, 1080), 0, 32),
-                                              ((3840, 2160, 1920, 1080), b200vc.FLAG_FORCE_GENERIC_FUSED, 16),
-                                              ((3840, 2160, 1280, 720), 0, 8)])
-def test_general_kernel_tile_heights(conv, orc, geo, flags, tile_h):
-    """The general fused kernel picks 32-, 16- or 8-row tiles by window size; each height is its own
-    instantiation, so each is checked at the geometry that selects it (bars: every fraction occurs)."""
+@pytest.mark.parametrize("geo,flags", [((2560, 1440, 1920, 1080), 0),
+                                       ((3840, 2160, 1920, 1080), b200vc.FLAG_FORCE_GENERIC_FUSED),
+                                       ((3840, 2160, 1280, 720), 0),
+                                       ((1280, 720, 1920, 1080), 0)])
+def test_general_kernel_tile_heights(conv, orc, geo, flags, monkeypatch):
+    """The general fused kernel is instantiated for tiles of 8, 16, 24 and 32 rows; the library picks the
+    cheapest for the geometry. The pick and every forced height (B200VC_TILE_H, read by set_info) must
+    give the oracle's frame (bars: every fraction occurs)."""
     iw, ih, ow, oh = geo
     frame = orc.synth("bars", iw, ih, 4)
-    for fmt, site in [(0, 1), (1, 0)]:
-        conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=1, range_=0, chroma_site=site, flags=flags)
-        inf = conv.info()
-        assert inf.path == 1 and inf.fused_2to1 == 0 and inf.tile_h == tile_h
-        buf, off, pit = conv.transform_frame(frame)
-        assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), _want(orc, frame, ow, oh, fmt, 1, 0, site), f"{geo} fmt{fmt}")
+    want = {}
+    for force in (None, 8, 16, 24, 32):
+        if force is None:
+            monkeypatch.delenv("B200VC_TILE_H", raising=False)
+        else:
+            monkeypatch.setenv("B200VC_TILE_H", str(force))
+        for fmt, site in [(0, 1), (1, 0)]:
+            conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=1, range_=0, chroma_site=site, flags=flags)
+            inf = conv.info()
+            assert inf.path == 1 and inf.fused_2to1 == 0 and inf.tile_h in (8, 16, 24, 32)
+            if force is not None and inf.tile_h != force:
+                continue                                    # (a window too large for that height: the library fell back)
+            if (fmt, site) not in want:
+                want[(fmt, site)] = _want(orc, frame, ow, oh, fmt, 1, 0, site)
+            buf, off, pit = conv.transform_frame(frame)
+            assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), want[(fmt, site)], f"{geo} fmt{fmt} tile_h {inf.tile_h}")
+    monkeypatch.delenv("B200VC_TILE_H", raising=False)

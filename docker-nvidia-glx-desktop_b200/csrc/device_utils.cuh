@@ -173,4 +173,15 @@ __device__ __forceinline__ uint32_t filt121(uint32_t l, uint32_t c, uint32_t r)
     return ((l + 2u * c + r + 0x00020002u) >> 2) & LANES8;
 }
 
+// The same two without the final mask: the u lane's top bits hold the bits the shift dragged out of the
+// v lane (the v lane is exact). For callers that add a masked operand and use bytes 0 and 2 only.
+__device__ __forceinline__ uint32_t avg2_raw(uint32_t a, uint32_t b)
+{
+    return (a + b + 0x00010001u) >> 1;
+}
+__device__ __forceinline__ uint32_t filt121_raw(uint32_t l, uint32_t c, uint32_t r)
+{
+    return (l + 2u * c + r + 0x00020002u) >> 2;
+}
+
 }  // namespace b200vc

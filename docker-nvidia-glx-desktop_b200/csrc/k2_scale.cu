@@ -90,10 +90,14 @@ __device__ __forceinline__ void convert_item(const uint32_t *ra, uint8_t *ya, ui
     const uint32_t pa2 = chroma_pair<NEG>(a.z, m), pa3 = chroma_pair<NEG>(a.w, m);
     const uint32_t pb0 = chroma_pair<NEG>(b.x, m), pb1 = chroma_pair<NEG>(b.y, m);
     const uint32_t pb2 = chroma_pair<NEG>(b.z, m), pb3 = chroma_pair<NEG>(b.w, m);
+    // The 2x16-bit lane results below keep whatever the shifts drag from the v lane into the top bits
+    // of the u lane wherever it cannot reach a byte that is used: one operand of the vertical mean is
+    // masked (so the sum cannot carry into the v lane), the other and the mean itself are not, because
+    // only bytes 0 and 2 of the mean are stored.
     uint32_t c0, c1;
     if (SITE == 0) {
-        c0 = avg2(avg2(pa0, pa1), avg2(pb0, pb1));
-        c1 = avg2(avg2(pa2, pa3), avg2(pb2, pb3));
+        c0 = (avg2_raw(pa0, pa1) + avg2(pb0, pb1) + 0x00010001u) >> 1;
+        c1 = (avg2_raw(pa2, pa3) + avg2(pb2, pb3) + 0x00010001u) >> 1;
     } else {
         // frame column 0 takes itself; the window's first group has no left neighbour (its first
         // chroma column is halo and is never consumed)
@@ -105,8 +109,8 @@ __device__ __forceinline__ void convert_item(const uint32_t *ra, uint8_t *ya, ui
         // right neighbours: the frame's last even column (in_w - 2, in_w > 2) takes itself
         // (B200VC_SPEC_COSITED_LAST_1_3 = 0: the plain 1-2-1 filter runs to the end; an odd frame's
         // last pixel has been duplicated into the window by then, which is the same thing)
-        c0 = avg2(filt121(la, pa0, (EDGE && e0) ? pa0 : pa1), filt121(lb, pb0, (EDGE && e0) ? pb0 : pb1));
-        c1 = avg2(filt121(pa1, pa2, (EDGE && e2) ? pa2 : pa3), filt121(pb1, pb2, (EDGE && e2) ? pb2 : pb3));
+        c0 = (filt121_raw(la, pa0, (EDGE && e0) ? pa0 : pa1) + filt121(lb, pb0, (EDGE && e0) ? pb0 : pb1) + 0x00010001u) >> 1;
+        c1 = (filt121_raw(pa1, pa2, (EDGE && e2) ? pa2 : pa3) + filt121(pb1, pb2, (EDGE && e2) ? pb2 : pb3) + 0x00010001u) >> 1;
     }
     *reinterpret_cast<uint32_t *>(cf) = prmt(c0, c1, 0x6420);              // u0 v0 u1 v1
 }
@@ -219,10 +223,14 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
             const uint32_t *ra = s_src + o;
             uint8_t *ya = s_yf + o;
             uint8_t *cf = s_cf + ky0 * bw + 4 * kx;                         // two (u,v) byte pairs per item
+            // (not unrolled: the unrolled form computes its trip count with a division, per warp and tile
+            // more than an item's worth of instructions)
             if (redge) {
+#pragma unroll 1
                 for (int ky = ky0; ky < pairs; ky += rps, ra += 2 * step, ya += 2 * step, cf += step)
                     convert_item<SITE, NEG, true>(ra, ya, cf, bw, left, e0, e2, p.mx);
             } else {
+#pragma unroll 1
                 for (int ky = ky0; ky < pairs; ky += rps, ra += 2 * step, ya += 2 * step, cf += step)
                     convert_item<SITE, NEG, false>(ra, ya, cf, bw, left, false, false, p.mx);
             }

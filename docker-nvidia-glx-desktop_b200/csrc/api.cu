@@ -170,7 +170,6 @@ bool aligned16(const void *p) { return ((uintptr_t)p & 15) == 0; }
 // its static arrays. The kernels' function attribute is set to the device limit (*_prepare), never to one
 // geometry's need: the kernels are shared by every context of the process, and a later, smaller
 // negotiation must not shrink an earlier one's.
-size_t dyn_smem_cap(const b200vc_ctx *c) { return (size_t)c->prop.sharedMemPerBlockOptin - 8192; }
 
 // ---- scaler taps as tables; positions and spec constants from host_tables.h ------------
 void build_h_taps(int in_n, int out_n, std::vector<Tap> &t)
@@ -405,28 +404,33 @@ void fused_box(const b200vc_config &c, const std::vector<Tap> &hy, const std::ve
 }
 
 // Issue slots the general fused kernel spends on one frame with tiles of tile_h rows, in warp
-// instructions (the kernel is issue-bound; counts per phase from its ncu source page,
-// profiles/r2_general_scaler_experiments.md): set-up per tile, phase 1 per sweep of the 256 threads down
-// the window (items of 4 columns x 2 lines, 256 / groups line pairs at a time), phase 2 per row of luma /
-// chroma, phase 3 per sweep of the tile's 16-byte chunks. What the choice of tile_h changes is mostly how
-// full phase 1's last sweep is.
+// instructions (the kernel is issue-bound; counts per phase from its ncu source page joined with the
+// line table, tools/ncu_phases.py, profiles/r2_general_scaler_experiments.md): per tile and warp a fixed
+// part (set-up, the prologues of the phases), phase 1 per warp with work in each sweep of the 256
+// threads down the window (items of 4 columns x 2 lines, 256 / groups line pairs at a time), phase 2
+// per row of luma / chroma, phase 3 per sweep over the tile's 16-byte chunks. Tall tiles amortise the
+// fixed part and the halo lines, and the height decides how full phase 1's last sweep is.
 double fused_frame_cost(const b200vc_config &c, const std::vector<Tap> &hy, const std::vector<Tap> &vy,
                         const std::vector<Tap> &hc, const std::vector<Tap> &vc, int tile_h)
 {
     const int site = (c.chroma_site & B200VC_SITE_H_COSITED) ? 1 : 0;
     int box_w, box_h;
     fused_box(c, hy, vy, hc, vc, tile_h, box_w, box_h);
+    if (box_w > 256 || box_h > 256) return 1e30;           // (a window the kernel does not take)
     std::vector<int> gx, py;
     for (int x0 = 0; x0 < c.out_w; x0 += K2_TILE_W) gx.push_back(box_w / 4 - fused_span_x(c, hy, hc, x0, site).kfirst);
     for (int y0 = 0; y0 < c.out_h; y0 += tile_h) py.push_back(fused_span_y(c, vy, vc, y0, tile_h).pairs);
-    double sweeps = 0;                                     // 256 / g line pairs per sweep
+    double phase1 = 0;
     for (int g : gx) {
-        if (g > 64) return 1e30;                           // (a window the kernel does not take anyway)
-        for (int p : py) sweeps += (p + 256 / g - 1) / (256 / g);
+        const int rps = 256 / g;                           // line pairs per sweep
+        for (int p : py)
+            for (int done = 0; done < p; done += rps)
+                phase1 += 90.0 * ((g * std::min(rps, p - done) + 31) / 32);
     }
     const double tiles = (double)gx.size() * py.size();
-    const double per_tile = 550.0 + 8.0 * 15 * ((tile_h + 3) / 4) + 8.0 * 27 * ((tile_h / 2 + 7) / 8) + 8.0 * 30 * ((tile_h * 6 + 255) / 256);
-    return tiles * per_tile + sweeps * 8.0 * 90;
+    const double per_tile = 8.0 * (65 + 45 + 28 + 15) + 8.0 * 23 * (tile_h / 8) + 8.0 * 22 * ((tile_h / 2 + 7) / 8) +
+                            8.0 * 30 * ((tile_h * 6 + 255) / 256);
+    return tiles * per_tile + phase1;
 }
 
 // True when every tap of an (in_n -> out_n) scaler starts at 2k with the second tap at 2k+1 and,
@@ -977,30 +981,40 @@ int create_impl(b200vc_ctx *c)
         c->tab.hc = d;  CU_TRY(c, cudaMemcpy(d, hc.data(), hc.size() * sizeof(Tap), cudaMemcpyHostToDevice));  d += hc.size();
         c->tab.vc = d;  CU_TRY(c, cudaMemcpy(d, vc.data(), vc.size() * sizeof(Tap), cudaMemcpyHostToDevice));
 
-        // Output rows per tile of the general fused kernel: the height of 8, 16, 24, 32 (one
-        // instantiation each) that costs the fewest issue slots per frame (fused_frame_cost) among
-        // those whose window leaves room for 6 CTAs per SM. Tall tiles amortise the per-tile set-up and the halo lines; the height decides
-        // how full the last sweep of phase 1 over the window is (4:3 with 32 rows: 529 items, three
-        // sweeps of 256 threads; with 30 rows: 506, two); a window too large for 6 resident CTAs no
-        // longer hides its TMA wait (4K -> 720p: 0.78 of the roofline with 8 rows, 0.67 with 16, 0.37 with 32).
+        // Output rows per tile of the general fused kernel: the height (one instantiation each) that
+        // costs the fewest issue slots per frame (fused_frame_cost) among those whose window leaves room
+        // for 5 CTAs per SM. With fewer the TMA waits and the barriers between the phases are no longer
+        // hidden, and that outweighs what the count promises (measured, tools/run_general.sh with forced
+        // heights: 3:2 with 48 rows, 4 CTAs: 0.66 of the roofline against 0.72 with 32 rows, 7 CTAs;
+        // 4K -> 720p: 0.81 with 16 rows, 0.58 with 24, 0.39 with 48; the 2:3 upscale, whose window is
+        // small: 0.32 with 32 rows, 0.40 with 64, 0.41 with 96).
         {
-            int best = 8;
-            double best_cost = 0;
-            const char *force = getenv("B200VC_TILE_H");                       // measurements only
-            for (int th = 8; th <= K2_MAX_TILE_H; th += 8) {
+            static const int heights[] = { 8, 16, 32, 48, 64, 96, 128 };       // K2_TILE_HEIGHTS, k2_scale.cu
+            auto ctas_per_sm = [&](int th) {
                 int bw, bh;
                 fused_box(k, hy, vy, hc, vc, th, bw, bh);
-                if (th > 8 && fused_scale_smem_bytes(bw, bh) + 4096 > (size_t)c->prop.sharedMemPerMultiprocessor / 6) break;
+                const size_t cta = fused_scale_smem_bytes(bw, bh) + fused_scale_static_bytes(th);
+                if (bw > 256 || bh > 256 || cta > (size_t)c->prop.sharedMemPerBlockOptin) return 0;
+                return (int)std::min<size_t>(8, (size_t)c->prop.sharedMemPerMultiprocessor / (cta + 1024));
+            };
+            auto usable = [&](int th) { return ctas_per_sm(th) > 0; };
+            int best = 8;
+            double best_cost = 0;
+            for (int th : heights) {
+                if (th > 8 && ctas_per_sm(th) < 5) continue;
                 const double cost = fused_frame_cost(k, hy, vy, hc, vc, th);
                 if (th == 8 || cost < best_cost) { best = th;  best_cost = cost; }
             }
-            if (force && atoi(force) >= 8 && atoi(force) <= K2_MAX_TILE_H && !(atoi(force) & 7)) best = atoi(force);
+            const char *force = getenv("B200VC_TILE_H");                       // measurements and tests only
+            if (force)
+                for (int th : heights)
+                    if (atoi(force) == th && usable(th)) best = th;
             c->tile_h = best;
             fused_box(k, hy, vy, hc, vc, c->tile_h, c->box_w, c->box_h);
             c->smem_bytes = fused_scale_smem_bytes(c->box_w, c->box_h);
         }
         const bool fits = c->box_w <= 256 && c->box_h <= 256 &&
-                          c->smem_bytes <= dyn_smem_cap(c);
+                          c->smem_bytes + fused_scale_static_bytes(c->tile_h) <= (size_t)c->prop.sharedMemPerBlockOptin;
         // (odd sizes run the general fused kernel; the exact-2:1 kernel needs multiples of 4, BOX even sizes)
         // (the fused kernels scale horizontally first; a build with the other order of the spec takes the two-pass path)
         // (and they read 4-byte pixels and make 4:2:0 planes; 16-bit input and Y42B/Y444 output take the two-pass path too)

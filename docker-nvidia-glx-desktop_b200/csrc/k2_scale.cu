@@ -115,34 +115,33 @@ __device__ __forceinline__ void convert_item(const uint32_t *ra, uint8_t *ya, ui
     *reinterpret_cast<uint32_t *>(cf) = prmt(c0, c1, 0x6420);              // u0 v0 u1 v1
 }
 
-// Phase 2 helpers of the general fused kernel. A line's horizontal pass leaves two samples (still with
-// their 8 fraction bits) whose high bytes are packed into bytes 0 and 1 of one word; the vertical tap
-// then takes [A,A,B,B] from the words of the two lines (v_weight_word, host_tables.h).
+// Phase 2 helpers of the general fused kernel. A line's horizontal pass leaves two samples that still
+// carry their 8 fraction bits (the sample is byte 1 of each sum); the vertical tap takes [A,A,B,B] from
+// the sums of the two lines (v_weight_word, host_tables.h) and leaves the result in byte 1 again.
 //
 // luma, two adjacent output columns per lane: their four taps lie within 4 bytes of the first tap
 // (step <= 2), which one funnel shift of two aligned words brings into a register
-__device__ __forceinline__ uint32_t h_pass_luma_pair(const uint8_t *line, uint32_t sh, uint32_t sel1, uint32_t wh0, uint32_t wh1)
+__device__ __forceinline__ uint2 h_pass_luma_pair(const uint8_t *line, uint32_t sh, uint32_t sel1, uint32_t wh0, uint32_t wh1)
 {
     const uint32_t w0 = *reinterpret_cast<const uint32_t *>(line), w1 = *reinterpret_cast<const uint32_t *>(line + 4);
     const uint32_t v = __funnelshift_r(w0, w1, sh);                        // bytes i0 .. i0 + 3 of the line
-    const uint32_t s0 = dp4a_uu(prmt(v, 0u, 0x3100), wh0, 0u);             // [a,a,b,_] . (255-f, 1, f, 0)
-    const uint32_t s1 = dp4a_uu(prmt(v, 0u, sel1), wh1, 0u);
-    return prmt(s0, s1, 0x0051);
+    return make_uint2(dp4a_uu(prmt(v, 0u, 0x3100), wh0, 0u),               // [a,a,b,_] . (255-f, 1, f, 0)
+                      dp4a_uu(prmt(v, 0u, sel1), wh1, 0u));
 }
 
 // chroma, one (u,v) sample per lane: the plane holds u,v byte pairs, the two taps are two 16-bit loads
-__device__ __forceinline__ uint32_t h_pass_chroma(const uint8_t *smp, uint32_t wh)
+__device__ __forceinline__ uint2 h_pass_chroma(const uint8_t *smp, uint32_t wh)
 {
     const uint32_t lo = *reinterpret_cast<const uint16_t *>(smp), hi = *reinterpret_cast<const uint16_t *>(smp + 2);
-    const uint32_t su = dp4a_uu(prmt(lo, hi, 0x2400), wh, 0u);             // [u0,u0,u1,0]
-    const uint32_t sv = dp4a_uu(prmt(lo, hi, 0x2511), wh, 0u);             // [v0,v0,v1,0]
-    return prmt(su, sv, 0x0051);
+    return make_uint2(dp4a_uu(prmt(lo, hi, 0x2400), wh, 0u),               // [u0,u0,u1,0]
+                      dp4a_uu(prmt(lo, hi, 0x2511), wh, 0u));              // [v0,v0,v1,0]
 }
 
-__device__ __forceinline__ uint32_t v_pass_pair(uint32_t top, uint32_t bot, uint32_t wv)
+// vertical tap on the two lines' sums of both samples; the samples land in bytes 0 and 1
+__device__ __forceinline__ uint32_t v_pass_pair(uint2 top, uint2 bot, uint32_t wv)
 {
-    const uint32_t d0 = dp4a_uu(prmt(top, bot, 0x4400), wv, 128u), d1 = dp4a_uu(prmt(top, bot, 0x5511), wv, 128u);
-    return prmt(d0, d1, 0x0051);                                           // the two samples in bytes 0 and 1
+    const uint32_t d0 = dp4a_uu(prmt(top.x, bot.x, 0x5511), wv, 128u), d1 = dp4a_uu(prmt(top.y, bot.y, 0x5511), wv, 128u);
+    return prmt(d0, d1, 0x0051);
 }
 
 template <int FMT, int SITE, bool NEG, int TILE_H, bool ODD>
@@ -178,8 +177,9 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
         issue_window_load(&s_bar, s_src, &src_map, sx0, sy0, (int)blockIdx.z, (uint32_t)bw * bh * 4);
     }
     s_col[tid] = p.ft.col_rec[blockIdx.x * (4 * TW) + tid];               // 4 * TW == 256 == blockDim.x
-    if (tid < 3 * TILE_H)
-        s_row[tid] = p.ft.row_rec[blockIdx.y * (3 * TILE_H) + tid];
+#pragma unroll
+    for (int i = tid; i < 3 * TILE_H; i += 256)
+        s_row[i] = p.ft.row_rec[blockIdx.y * (3 * TILE_H) + i];
     __syncthreads();
     {
         const uint32_t bar = smem_u32(&s_bar);
@@ -257,12 +257,12 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
         const uint8_t *col = s_yf + (rec.x & 0xffffu);
         const uint32_t sh = rec.x >> 16;
         uint16_t *dst = reinterpret_cast<uint16_t *>(s_out) + wrp * RPW * (TW / 2) + lane;
-#pragma unroll
+#pragma unroll(RPW < 4 ? RPW : 4)
         for (int k = 0; k < RPW; k++) {
             const uint2 tv = s_vy[wrp * RPW + k]; // {byte offset of the upper line, vertical weights}
             const uint8_t *l0 = col + (int)tv.x;
-            const uint32_t top = h_pass_luma_pair(l0, sh, rec.y, rec.z, rec.w);
-            const uint32_t bot = h_pass_luma_pair(l0 + bw, sh, rec.y, rec.z, rec.w);
+            const uint2 top = h_pass_luma_pair(l0, sh, rec.y, rec.z, rec.w);
+            const uint2 bot = h_pass_luma_pair(l0 + bw, sh, rec.y, rec.z, rec.w);
             dst[k * (TW / 2)] = (uint16_t)v_pass_pair(top, bot, tv.y);
         }
     } else {
@@ -296,7 +296,7 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
         const uint4 th = s_hc[lane];              // {byte offset of the first tap in a (u,v) line, wh, -, -}
         const uint8_t *col = s_cf + (int)th.x;
         uint8_t *oc = s_out + TW * TILE_H;
-#pragma unroll
+#pragma unroll(CPW < 4 ? CPW : 4)
         for (int r = wrp * CPW; r < wrp * CPW + CPW; r++) {
             if (r >= TILE_H / 2) break;
             const uint2 tv = s_vc[r];
@@ -613,8 +613,11 @@ cudaError_t launch_fused4(const CUtensorMap &map, const FusedScaleParams &p, dim
     switch (p.tile_h) {                                   // K2_TILE_HEIGHTS
     case 8:  k2_fused_scale_kernel<FMT, SITE, NEG, 8, ODD><<<grid, 256, smem, st>>>(map, p);  break;
     case 16: k2_fused_scale_kernel<FMT, SITE, NEG, 16, ODD><<<grid, 256, smem, st>>>(map, p);  break;
-    case 24: k2_fused_scale_kernel<FMT, SITE, NEG, 24, ODD><<<grid, 256, smem, st>>>(map, p);  break;
     case 32: k2_fused_scale_kernel<FMT, SITE, NEG, 32, ODD><<<grid, 256, smem, st>>>(map, p);  break;
+    case 48: k2_fused_scale_kernel<FMT, SITE, NEG, 48, ODD><<<grid, 256, smem, st>>>(map, p);  break;
+    case 64: k2_fused_scale_kernel<FMT, SITE, NEG, 64, ODD><<<grid, 256, smem, st>>>(map, p);  break;
+    case 96: k2_fused_scale_kernel<FMT, SITE, NEG, 96, ODD><<<grid, 256, smem, st>>>(map, p);  break;
+    case 128: k2_fused_scale_kernel<FMT, SITE, NEG, 128, ODD><<<grid, 256, smem, st>>>(map, p);  break;
     default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();
@@ -677,13 +680,20 @@ size_t fused_scale_smem_bytes(int box_w, int box_h)
     return (size_t)box_w * box_h * 11 / 2 + (size_t)box_w * 2 + 16;
 }
 
+// the kernel's static shared memory for tiles of tile_h rows: output tile, tap records, mbarrier
+size_t fused_scale_static_bytes(int tile_h)
+{
+    return (size_t)TW * tile_h * 3 / 2 + 12 * (size_t)tile_h + 4 * 4 * TW + 16 + 256;      // (+ alignment gaps)
+}
+
 cudaError_t fused_scale_prepare(size_t optin_bytes)
 {
     cudaError_t e;
 #define B200VC_SET1(F, S, N, H) \
     if ((e = set_smem(k2_fused_scale_kernel<F, S, N, H, false>, optin_bytes)) != cudaSuccess) return e; \
     if ((e = set_smem(k2_fused_scale_kernel<F, S, N, H, true>, optin_bytes)) != cudaSuccess) return e;
-#define B200VC_SET(F, S, N) B200VC_SET1(F, S, N, 8) B200VC_SET1(F, S, N, 16) B200VC_SET1(F, S, N, 24) B200VC_SET1(F, S, N, 32)
+#define B200VC_SET(F, S, N) B200VC_SET1(F, S, N, 8) B200VC_SET1(F, S, N, 16) B200VC_SET1(F, S, N, 32) B200VC_SET1(F, S, N, 48) \
+    B200VC_SET1(F, S, N, 64) B200VC_SET1(F, S, N, 96) B200VC_SET1(F, S, N, 128)
     B200VC_SET(0, 0, false) B200VC_SET(0, 0, true) B200VC_SET(0, 1, false) B200VC_SET(0, 1, true)
     B200VC_SET(1, 0, false) B200VC_SET(1, 0, true) B200VC_SET(1, 1, false) B200VC_SET(1, 1, true)
 #undef B200VC_SET
@@ -697,6 +707,8 @@ cudaError_t launch_fused_scale(const CUtensorMap &src_map, const FusedScaleParam
     if (p.out_w <= 0 || p.out_h <= 0 || p.n_frames <= 0)
         return cudaErrorInvalidValue;
     if (p.tile_h < 8 || p.tile_h > K2_MAX_TILE_H || (p.tile_h & 7))
+        return cudaErrorInvalidValue;
+    if (p.box_h > 256 || p.box_w > 256)                    // TMA box limit; and phase 1 divides by up to 64 groups
         return cudaErrorInvalidValue;
     dim3 grid((p.out_w + TW - 1) / TW, (p.out_h + p.tile_h - 1) / p.tile_h, p.n_frames);
     const size_t smem = fused_scale_smem_bytes(p.box_w, p.box_h);

@@ -987,9 +987,9 @@ int create_impl(b200vc_ctx *c)
         // hidden, and that outweighs what the count promises (measured, tools/run_general.sh with forced
         // heights: 3:2 with 48 rows, 4 CTAs: 0.66 of the roofline against 0.72 with 32 rows, 7 CTAs;
         // 4K -> 720p: 0.81 with 16 rows, 0.58 with 24, 0.39 with 48; the 2:3 upscale, whose window is
-        // small: 0.32 with 32 rows, 0.40 with 64, 0.41 with 96).
+        // small: 0.32 with 32 rows, 0.40 with 64, 0.41 with 96 — not worth an instantiation of its own).
         {
-            static const int heights[] = { 8, 16, 32, 48, 64, 96, 128 };       // K2_TILE_HEIGHTS, k2_scale.cu
+            static const int heights[] = { 8, 16, 32, 48, 64 };       // K2_TILE_HEIGHTS, k2_scale.cu
             auto ctas_per_sm = [&](int th) {
                 int bw, bh;
                 fused_box(k, hy, vy, hc, vc, th, bw, bh);

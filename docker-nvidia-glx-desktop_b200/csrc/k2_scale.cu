@@ -616,8 +616,6 @@ cudaError_t launch_fused4(const CUtensorMap &map, const FusedScaleParams &p, dim
     case 32: k2_fused_scale_kernel<FMT, SITE, NEG, 32, ODD><<<grid, 256, smem, st>>>(map, p);  break;
     case 48: k2_fused_scale_kernel<FMT, SITE, NEG, 48, ODD><<<grid, 256, smem, st>>>(map, p);  break;
     case 64: k2_fused_scale_kernel<FMT, SITE, NEG, 64, ODD><<<grid, 256, smem, st>>>(map, p);  break;
-    case 96: k2_fused_scale_kernel<FMT, SITE, NEG, 96, ODD><<<grid, 256, smem, st>>>(map, p);  break;
-    case 128: k2_fused_scale_kernel<FMT, SITE, NEG, 128, ODD><<<grid, 256, smem, st>>>(map, p);  break;
     default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();
@@ -693,7 +691,7 @@ cudaError_t fused_scale_prepare(size_t optin_bytes)
     if ((e = set_smem(k2_fused_scale_kernel<F, S, N, H, false>, optin_bytes)) != cudaSuccess) return e; \
     if ((e = set_smem(k2_fused_scale_kernel<F, S, N, H, true>, optin_bytes)) != cudaSuccess) return e;
 #define B200VC_SET(F, S, N) B200VC_SET1(F, S, N, 8) B200VC_SET1(F, S, N, 16) B200VC_SET1(F, S, N, 32) B200VC_SET1(F, S, N, 48) \
-    B200VC_SET1(F, S, N, 64) B200VC_SET1(F, S, N, 96) B200VC_SET1(F, S, N, 128)
+    B200VC_SET1(F, S, N, 64)
     B200VC_SET(0, 0, false) B200VC_SET(0, 0, true) B200VC_SET(0, 1, false) B200VC_SET(0, 1, true)
     B200VC_SET(1, 0, false) B200VC_SET(1, 0, true) B200VC_SET(1, 1, false) B200VC_SET(1, 1, true)
 #undef B200VC_SET

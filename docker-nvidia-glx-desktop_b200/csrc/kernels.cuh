@@ -109,7 +109,7 @@ struct FusedScaleParams {
     FusedTaps ft;
     int in_w, in_h, out_w, out_h;
     int box_w, box_h;       // source window per tile (pixels); box_w % 4 == 0, box_h even
-    int tile_h;             // output rows per tile: 8, 16, 32, 48, 64, 96 or 128 (the cheapest per frame, api.cu fused_frame_cost)
+    int tile_h;             // output rows per tile: 8, 16, 32, 48 or 64 (the cheapest per frame, api.cu fused_frame_cost)
     int n_frames;
     int box2x2;             // scale_mode == BOX_2X2
     int pair_luma;          // form of the luma column records (FusedTaps); never with box2x2
@@ -173,7 +173,7 @@ constexpr int K1_TILE_H = 16;    // one macroblock row per warp stripe
 constexpr int K1_WARPS_PER_CTA = 4;
 constexpr int K2_TILE_W = 64;    // output pixels per CTA tile
 constexpr int K2_TILE_H = 16;    // exact-2:1 kernel; the general kernel's is FusedScaleParams::tile_h
-constexpr int K2_MAX_TILE_H = 128;
+constexpr int K2_MAX_TILE_H = 64;
 constexpr int K2X_SRC_W = 128;   // exact-2:1 kernel: source tile per CTA (8 warps x 4 lines, 32 lanes x 4 pixels)
 constexpr int K2X_SRC_H = 32;
 constexpr int K2X_TILES_PER_CTA = 2;   // exact-2:1 kernel: tiles per CTA (the later loads hide behind the first tile's work)

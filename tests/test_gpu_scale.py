@@ -128,13 +128,13 @@ def test_odd_sizes_with_scaling(conv, orc, geo, two_pass):
                                        ((3840, 2160, 1280, 720), 0),
                                        ((1280, 720, 1920, 1080), 0)])
 def test_general_kernel_tile_heights(conv, orc, geo, flags, monkeypatch):
-    """The general fused kernel is instantiated for tiles of 8 to 128 rows; the library picks the cheapest
+    """The general fused kernel is instantiated for tiles of 8 to 64 rows; the library picks the cheapest
     for the geometry. The pick and every forced height (B200VC_TILE_H, read by set_info; a height whose
     window does not fit falls back to the pick) must give the oracle's frame (bars: every fraction occurs)."""
     iw, ih, ow, oh = geo
     frame = orc.synth("bars", iw, ih, 4)
     want = {}
-    for force in (None, 8, 16, 32, 48, 64, 96, 128):
+    for force in (None, 8, 16, 32, 48, 64):
         if force is None:
             monkeypatch.delenv("B200VC_TILE_H", raising=False)
         else:
@@ -142,7 +142,7 @@ def test_general_kernel_tile_heights(conv, orc, geo, flags, monkeypatch):
         for fmt, site in [(0, 1), (1, 0)]:
             conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=1, range_=0, chroma_site=site, flags=flags)
             inf = conv.info()
-            assert inf.path == 1 and inf.fused_2to1 == 0 and inf.tile_h in (8, 16, 32, 48, 64, 96, 128)
+            assert inf.path == 1 and inf.fused_2to1 == 0 and inf.tile_h in (8, 16, 32, 48, 64)
             if force is not None and inf.tile_h != force:
                 continue                                    # (a window too large for that height: the library fell back)
             if (fmt, site) not in want:

@@ -14,7 +14,7 @@ for pat in \
   'k1_convert_kernelILi3ELi0ELb0ELb0ELi8ELi1ELb1E|K1 <Y444, 5-6-5 input>' \
   'k1_convert_kernelILi2ELi1ELb0ELb0ELi8ELi1ELb0E|K1 <Y42B,mpeg2>' \
   'k2_fused_2x_kernelILi0ELi1ELb0ELb0E|K2 exact 2:1 fused <I420,mpeg2>: config C3' \
-  'k2_fused_scale_kernelILi0ELi1ELb0ELi32ELb0E|K2 general fused <I420,mpeg2,32-row tiles>' \
+  'k2_fused_scale_kernelILi0ELi1ELb0ELi48ELb0E|K2 general fused <I420,mpeg2,48-row tiles>' \
   'k2_fused_scale_kernelILi0ELi1ELb0ELi8ELb1E|K2 general fused <I420,mpeg2,8-row tiles,odd frames>' \
   'k2_plane_tile_kernelILi0E|two-pass, pass 2, tiled plane scaler <planar>' \
   'k2_plane_tile_kernelILi1E|two-pass, pass 2, tiled plane scaler <NV12>' \

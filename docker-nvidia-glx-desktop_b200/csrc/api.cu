@@ -69,6 +69,8 @@ struct Slot {
 struct HostReg { const uint8_t *base; size_t bytes; uint64_t last_use; };
 struct PtrKind { const void *p; int kind; const uint8_t *lo, *hi; };   // hi/lo: extent of the page-locked allocation
 struct MapEntry { const void *base; size_t pitch, fstride; int n_frames; CUtensorMap map; };
+// the output planes' maps of the general fused kernel; usable: planes in device memory, everything 16-byte aligned
+struct OutMapEntry { PlaneSet planes; int n_frames; bool usable; FusedOutMaps maps; };
 
 typedef CUresult (*WriteValue32Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
 
@@ -115,6 +117,7 @@ struct b200vc_ctx {
     FusedTaps ft = { nullptr, nullptr, nullptr, nullptr };
     int tile_h = K2_TILE_H;
     bool pair_luma = false;
+    bool no_tma_out = false;
     uint32_t *d_ptaps = nullptr;               // tiled plane scaler's records (two-pass path)
     PlaneTileKind pt[2] = {};
     bool plane_tiled = false;                  // two-pass path: pass 2 is the tiled kernel, not the gather kernel
@@ -129,6 +132,8 @@ struct b200vc_ctx {
     bool ev_mid_valid = false;
     PFN_cuTensorMapEncodeTiled_v12000 encode_tiled = nullptr;
     std::vector<MapEntry> maps;                // tensor maps seen so far (a session has two input buffers)
+    std::vector<OutMapEntry> out_maps;         // and of output planes (general fused kernel)
+    size_t next_out_map = 0;
     size_t next_map = 0;
     WriteValue32Fn write_value = nullptr;      // cuStreamWriteValue32, for the row gate's flags
 
@@ -649,6 +654,54 @@ int get_tensor_map(b200vc_ctx *c, const void *base, size_t pitch, size_t frame_s
     return B200VC_OK;
 }
 
+// TMA descriptors of the output planes (general fused kernel). Kept like the sources': a session's planes
+// are the same few buffers launch after launch. `usable` false: the kernel stores the tile itself.
+const OutMapEntry *get_out_maps(b200vc_ctx *c, const PlaneSet &out, int n_frames)
+{
+    for (const OutMapEntry &m : c->out_maps)
+        if (m.n_frames == n_frames && m.planes.frame_stride == out.frame_stride && m.planes.p[0] == out.p[0] && m.planes.p[1] == out.p[1] &&
+            m.planes.p[2] == out.p[2] && m.planes.pitch[0] == out.pitch[0] && m.planes.pitch[1] == out.pitch[1] && m.planes.pitch[2] == out.pitch[2])
+            return &m;
+    const b200vc_config &g = c->kcfg;
+    OutMapEntry e;
+    memset(&e, 0, sizeof e);
+    e.planes = out;  e.n_frames = n_frames;
+    cudaPointerAttributes a;
+    // (the unit clips a tile at the plane's last line exactly but at its last column in units of 16 bytes —
+    // measured: a 94-byte row got 96 — so rows must be whole multiples of 16 bytes: 1080p, 720p, 1440p, 1536x864 are)
+    e.usable = out.aligned16 && c->encode_tiled && g.out_format <= B200VC_FMT_NV12 && g.out_w % 16 == 0 &&
+               (g.out_format == B200VC_FMT_NV12 || (g.out_w / 2) % 16 == 0);
+    if (e.usable && (cudaPointerGetAttributes(&a, out.p[0]) != cudaSuccess || a.type != cudaMemoryTypeDevice)) {
+        cudaGetLastError();
+        e.usable = false;                      // (mapped host memory: the kernel's own stores are what was measured there)
+    }
+    if (e.usable) {
+        const int cw = (g.out_w + 1) / 2, ch = (g.out_h + 1) / 2, nv12 = g.out_format == B200VC_FMT_NV12;
+        auto encode = [&](CUtensorMap *m, uint8_t *base, size_t pitch, int w, int h, int bw, int bh) {
+            cuuint64_t dims[3] = { (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)n_frames };
+            cuuint64_t strides[2] = { (cuuint64_t)pitch, (cuuint64_t)(out.frame_stride ? out.frame_stride : ru(pitch * h, 16)) };
+            cuuint32_t box[3] = { (cuuint32_t)bw, (cuuint32_t)bh, 1 };
+            cuuint32_t estr[3] = { 1, 1, 1 };
+            return c->encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                   CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+        };
+        e.usable = encode(&e.maps.y, out.p[0], out.pitch[0], g.out_w, g.out_h, K2_TILE_W, c->tile_h);
+        if (e.usable && nv12) e.usable = encode(&e.maps.c1, out.p[1], out.pitch[1], 2 * cw, ch, K2_TILE_W, c->tile_h / 2);
+        if (e.usable && !nv12)
+            e.usable = encode(&e.maps.c1, out.p[1], out.pitch[1], cw, ch, K2_TILE_W / 2, c->tile_h / 2) &&
+                       encode(&e.maps.c2, out.p[2], out.pitch[2], cw, ch, K2_TILE_W / 2, c->tile_h / 2);
+    }
+    constexpr size_t kMaxMaps = 64;
+    if (c->out_maps.size() < kMaxMaps) {
+        c->out_maps.push_back(e);              // (reserved at create: entries never move)
+        return &c->out_maps.back();
+    }
+    c->out_maps[c->next_out_map] = e;
+    const OutMapEntry *r = &c->out_maps[c->next_out_map];
+    c->next_out_map = (c->next_out_map + 1) % kMaxMaps;
+    return r;
+}
+
 void set_alignment(PlaneSet &ps)
 {
     uintptr_t bits = (uintptr_t)ps.frame_stride;
@@ -755,7 +808,9 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         const uint32_t items_x = groups_x, items_x1 = std::max(groups_x - 1, 1u);
         p.inv_items_x = (65536u + items_x - 1) / items_x;
         p.inv_items_x1 = (65536u + items_x1 - 1) / items_x1;
-        CU_TRY(c, launch_fused_scale(*map, p, g.out_format, site, st));
+        const OutMapEntry *om = get_out_maps(c, out, n_frames);
+        p.tma_out = om->usable && !c->no_tma_out;
+        CU_TRY(c, launch_fused_scale(*map, om->maps, p, g.out_format, site, st));
         c->stats.kernel_launches += 1;
         return B200VC_OK;
     }
@@ -869,6 +924,8 @@ int create_impl(b200vc_ctx *c)
     c->mb_w = (g.in_w + 15) / 16;
     c->mb_h = (g.in_h + 15) / 16;
     c->maps.reserve(64);
+    c->out_maps.reserve(64);
+    c->no_tma_out = getenv("B200VC_NO_TMA_STORE") != nullptr;          // measurements and tests only
 
     CU_TRY(c, cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));
     CU_TRY(c, cudaStreamCreateWithFlags(&c->s_k, cudaStreamNonBlocking));

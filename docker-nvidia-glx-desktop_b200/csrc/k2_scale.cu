@@ -58,6 +58,27 @@ __device__ __noinline__ void issue_window_load(uint64_t *s_bar, void *dst, const
         : "memory");
 }
 
+// The general fused kernel's output tile, shared memory -> the planes, as TMA tiled stores by one thread
+// (out of line for the same reason). The caller has made the tile visible to the async proxy. The thread
+// waits until the unit has read the tile: shared memory must outlive the reads.
+__device__ __noinline__ void store_tile(const FusedOutMaps *om, const uint8_t *s_out, int fmt, int tile_h, int x0, int y0, int z)
+{
+    const uint32_t sy = smem_u32(s_out), sc1 = sy + TW * tile_h, sc2 = sc1 + (TW / 2) * (tile_h / 2);
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%1, %2, %3}], [%4];"
+                 ::"l"(reinterpret_cast<uint64_t>(&om->y)), "r"(x0), "r"(y0), "r"(z), "r"(sy) : "memory");
+    if (fmt == 0) {
+        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%1, %2, %3}], [%4];"
+                     ::"l"(reinterpret_cast<uint64_t>(&om->c1)), "r"(x0 >> 1), "r"(y0 >> 1), "r"(z), "r"(sc1) : "memory");
+        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%1, %2, %3}], [%4];"
+                     ::"l"(reinterpret_cast<uint64_t>(&om->c2)), "r"(x0 >> 1), "r"(y0 >> 1), "r"(z), "r"(sc2) : "memory");
+    } else {
+        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%1, %2, %3}], [%4];"
+                     ::"l"(reinterpret_cast<uint64_t>(&om->c1)), "r"(x0), "r"(y0 >> 1), "r"(z), "r"(sc1) : "memory");
+    }
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
 // Odd frames, edge tiles of the general fused kernel: window column dupx / line dupy (the ones just past
 // the frame, zero-filled by the TMA unit) become copies of the column / line before them.
 __device__ __forceinline__ void repeat_last_column_and_line(uint32_t *s_src, int bw, int bh, int dupx, int dupy, int odd_w,
@@ -146,7 +167,8 @@ __device__ __forceinline__ uint32_t v_pass_pair(uint2 top, uint2 bot, uint32_t w
 
 template <int FMT, int SITE, bool NEG, int TILE_H, bool ODD>
 __global__ void __launch_bounds__(256, 8)
-k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedScaleParams p)
+k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const __grid_constant__ FusedOutMaps out_maps,
+                      const FusedScaleParams p)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t s_bar;
@@ -154,7 +176,7 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
     // load is in flight
     __shared__ __align__(16) uint32_t s_col[4 * TW];           // luma records (two forms, FusedTaps) | hc[TW/2] quads
     __shared__ __align__(8) uint32_t s_row[3 * TILE_H];        // vy[TILE_H] pairs | vc[TILE_H/2] pairs
-    __shared__ __align__(16) uint8_t s_out[TW * TILE_H * 3 / 2];   // output tile: Y, then U and V (or UV) tiles
+    __shared__ __align__(128) uint8_t s_out[TW * TILE_H * 3 / 2];  // output tile: Y, then U and V (or UV) tiles
     const uint4 *s_hc = reinterpret_cast<const uint4 *>(s_col + 2 * TW);
     const uint2 *s_vy = reinterpret_cast<const uint2 *>(s_row), *s_vc = s_vy + TILE_H;
 
@@ -319,9 +341,18 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const FusedSc
             }
         }
     }
+    // ---- phase 3: the tile leaves --------------------------------------------------------------------
+    // by TMA stores where the planes allow it (device memory, every pitch a multiple of 16): one thread
+    // issues them, the unit clips tiles that overhang the frame. Otherwise as 16-byte stores, 4 chunks
+    // per luma row, 4 per chroma row pair.
+    if (p.tma_out) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // this thread's part of the tile, for the TMA unit
+        __syncthreads();
+        if (tid == 0)
+            store_tile(&out_maps, s_out, FMT, TILE_H, (int)blockIdx.x * TW, (int)blockIdx.y * TILE_H, (int)blockIdx.z);
+        return;
+    }
     __syncthreads();
-
-    // ---- phase 3: the tile leaves as 16-byte stores (4 chunks per luma row, 4 per chroma row pair) --
     const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TILE_H;
     const long long fo = (long long)blockIdx.z * p.out.frame_stride;
 #pragma unroll
@@ -608,26 +639,26 @@ __global__ void __launch_bounds__(128) k2_plane_scale_kernel(const PlaneScalePar
 }
 
 template <int FMT, int SITE, bool NEG, bool ODD>
-cudaError_t launch_fused4(const CUtensorMap &map, const FusedScaleParams &p, dim3 grid, size_t smem, cudaStream_t st)
+cudaError_t launch_fused4(const CUtensorMap &map, const FusedOutMaps &om, const FusedScaleParams &p, dim3 grid, size_t smem, cudaStream_t st)
 {
     switch (p.tile_h) {                                   // K2_TILE_HEIGHTS
-    case 8:  k2_fused_scale_kernel<FMT, SITE, NEG, 8, ODD><<<grid, 256, smem, st>>>(map, p);  break;
-    case 16: k2_fused_scale_kernel<FMT, SITE, NEG, 16, ODD><<<grid, 256, smem, st>>>(map, p);  break;
-    case 32: k2_fused_scale_kernel<FMT, SITE, NEG, 32, ODD><<<grid, 256, smem, st>>>(map, p);  break;
-    case 48: k2_fused_scale_kernel<FMT, SITE, NEG, 48, ODD><<<grid, 256, smem, st>>>(map, p);  break;
-    case 64: k2_fused_scale_kernel<FMT, SITE, NEG, 64, ODD><<<grid, 256, smem, st>>>(map, p);  break;
+    case 8:  k2_fused_scale_kernel<FMT, SITE, NEG, 8, ODD><<<grid, 256, smem, st>>>(map, om, p);  break;
+    case 16: k2_fused_scale_kernel<FMT, SITE, NEG, 16, ODD><<<grid, 256, smem, st>>>(map, om, p);  break;
+    case 32: k2_fused_scale_kernel<FMT, SITE, NEG, 32, ODD><<<grid, 256, smem, st>>>(map, om, p);  break;
+    case 48: k2_fused_scale_kernel<FMT, SITE, NEG, 48, ODD><<<grid, 256, smem, st>>>(map, om, p);  break;
+    case 64: k2_fused_scale_kernel<FMT, SITE, NEG, 64, ODD><<<grid, 256, smem, st>>>(map, om, p);  break;
     default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();
 }
 
 template <int FMT, int SITE>
-cudaError_t launch_fused2(const CUtensorMap &map, const FusedScaleParams &p, dim3 grid, size_t smem, cudaStream_t st)
+cudaError_t launch_fused2(const CUtensorMap &map, const FusedOutMaps &om, const FusedScaleParams &p, dim3 grid, size_t smem, cudaStream_t st)
 {
     const bool odd = (p.in_w | p.in_h) & 1;                // odd frames: the variant that repeats the last column / line
     if (p.mx.neg)
-        return odd ? launch_fused4<FMT, SITE, true, true>(map, p, grid, smem, st) : launch_fused4<FMT, SITE, true, false>(map, p, grid, smem, st);
-    return odd ? launch_fused4<FMT, SITE, false, true>(map, p, grid, smem, st) : launch_fused4<FMT, SITE, false, false>(map, p, grid, smem, st);
+        return odd ? launch_fused4<FMT, SITE, true, true>(map, om, p, grid, smem, st) : launch_fused4<FMT, SITE, true, false>(map, om, p, grid, smem, st);
+    return odd ? launch_fused4<FMT, SITE, false, true>(map, om, p, grid, smem, st) : launch_fused4<FMT, SITE, false, false>(map, om, p, grid, smem, st);
 }
 
 // Lets a kernel ask for dynamic shared memory up to the device's opt-in limit less its own static arrays.
@@ -699,7 +730,7 @@ cudaError_t fused_scale_prepare(size_t optin_bytes)
     return cudaSuccess;
 }
 
-cudaError_t launch_fused_scale(const CUtensorMap &src_map, const FusedScaleParams &p, int fmt, int site,
+cudaError_t launch_fused_scale(const CUtensorMap &src_map, const FusedOutMaps &out_maps, const FusedScaleParams &p, int fmt, int site,
                                cudaStream_t st)
 {
     if (p.out_w <= 0 || p.out_h <= 0 || p.n_frames <= 0)
@@ -711,8 +742,8 @@ cudaError_t launch_fused_scale(const CUtensorMap &src_map, const FusedScaleParam
     dim3 grid((p.out_w + TW - 1) / TW, (p.out_h + p.tile_h - 1) / p.tile_h, p.n_frames);
     const size_t smem = fused_scale_smem_bytes(p.box_w, p.box_h);
     if (fmt == 0)
-        return site ? launch_fused2<0, 1>(src_map, p, grid, smem, st) : launch_fused2<0, 0>(src_map, p, grid, smem, st);
-    return site ? launch_fused2<1, 1>(src_map, p, grid, smem, st) : launch_fused2<1, 0>(src_map, p, grid, smem, st);
+        return site ? launch_fused2<0, 1>(src_map, out_maps, p, grid, smem, st) : launch_fused2<0, 0>(src_map, out_maps, p, grid, smem, st);
+    return site ? launch_fused2<1, 1>(src_map, out_maps, p, grid, smem, st) : launch_fused2<1, 0>(src_map, out_maps, p, grid, smem, st);
 }
 
 cudaError_t launch_plane_scale(const PlaneScaleParams &p, int fmt, cudaStream_t st)

@@ -103,6 +103,11 @@ struct FusedTaps {
     const uint32_t *col_rec, *row_rec;
 };
 
+// Tensor maps of the output planes (Y; U and V, or UV), for the general fused kernel's tile stores: boxes
+// of 64 x tile_h, 32 x tile_h/2 (I420) or 64 x tile_h/2 bytes (NV12), UINT8 elements, dims = the plane's
+// samples, so tiles that overhang the frame are clipped by the TMA unit.
+struct FusedOutMaps { CUtensorMap y, c1, c2; };
+
 // K2 fused: TMA-staged source window -> convert -> chroma down -> 2-tap scale, one pass.
 struct FusedScaleParams {
     PlaneSet out;
@@ -113,6 +118,7 @@ struct FusedScaleParams {
     int n_frames;
     int box2x2;             // scale_mode == BOX_2X2
     int pair_luma;          // form of the luma column records (FusedTaps); never with box2x2
+    int tma_out;            // the tile leaves by TMA stores through FusedOutMaps (planes in device memory, 16-byte pitches)
     uint32_t inv_items_x;   // ceil(65536 / items per line pair), for box_w/4 and box_w/4 - 1 groups:
     uint32_t inv_items_x1;  // tid / items_x without a division (exact for tid <= 256, up to 64 items)
     RowGate gate;           // n_frames == 1 only
@@ -193,7 +199,7 @@ cudaError_t launch_border_fill(const BorderParams &p, cudaStream_t st);
 
 // Launchers return the cudaError_t of the launch. fmt/site as in b200vc.h.
 cudaError_t launch_convert(const ConvertParams &p, int fmt, int site, cudaStream_t st);
-cudaError_t launch_fused_scale(const CUtensorMap &src_map, const FusedScaleParams &p, int fmt, int site,
+cudaError_t launch_fused_scale(const CUtensorMap &src_map, const FusedOutMaps &out_maps, const FusedScaleParams &p, int fmt, int site,
                                cudaStream_t st);
 cudaError_t launch_fused_2x(const CUtensorMap &src_map, const Fused2xParams &p, int fmt, int site, int box2x2,
                             cudaStream_t st);

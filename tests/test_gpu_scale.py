@@ -150,3 +150,27 @@ def test_general_kernel_tile_heights(conv, orc, geo, flags, monkeypatch):
             buf, off, pit = conv.transform_frame(frame)
             assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), want[(fmt, site)], f"{geo} fmt{fmt} tile_h {inf.tile_h}")
     monkeypatch.delenv("B200VC_TILE_H", raising=False)
+
+
+@pytest.mark.parametrize("geo", [(1920, 1080, 1312, 730), (2560, 1440, 1920, 1080), (1280, 720, 1920, 1080)])
+def test_general_kernel_tile_stores(conv, orc, geo, monkeypatch):
+    """The general fused kernel hands its output tile to the TMA unit when the planes lie in device memory and
+    every pitch is a multiple of 16, and stores it itself otherwise (B200VC_NO_TMA_STORE, read by set_info,
+    forces that). Both must give the oracle's frame, tiles overhanging the right and bottom edges included
+    (1312x730: 20.5 tile columns, rows that end inside a tile; all rows multiples of 16 bytes — the unit clips
+    columns in units of 16 bytes, so other widths keep the kernel's own stores; the add-borders cases of
+    test_gpu_formats.py and the fuzz run are what would show a store reaching past the picture)."""
+    iw, ih, ow, oh = geo
+    frame = orc.synth("bars", iw, ih, 5)
+    for fmt, site in [(0, 1), (1, 0)]:
+        want = _want(orc, frame, ow, oh, fmt, 1, 0, site)
+        for off_switch in (False, True):
+            if off_switch:
+                monkeypatch.setenv("B200VC_NO_TMA_STORE", "1")
+            else:
+                monkeypatch.delenv("B200VC_NO_TMA_STORE", raising=False)
+            conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=1, range_=0, chroma_site=site)
+            assert conv.info().path == 1
+            buf, off, pit = conv.transform_frame(frame)
+            assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), want, f"{geo} fmt{fmt} tma stores off={off_switch}")
+    monkeypatch.delenv("B200VC_NO_TMA_STORE", raising=False)

@@ -9,9 +9,8 @@
 //
 //   phase 0  one thread issues a TMA tiled load (cp.async.bulk.tensor.3d) of the tile's source
 //            window — the rows and columns its output pixels depend on, halo included; pixels
-//            outside the frame are zero-filled by the TMA unit — while every thread copies one word
-//            of the tile's host-made tap records into shared memory; the CTA then waits on an
-//            mbarrier for the window's bytes
+//            outside the frame are zero-filled by the TMA unit — and bulk copies of the tile's
+//            host-made tap records; the CTA then waits on one mbarrier for all the bytes
 //   phase 1  convert the window: Y per pixel and the 4:2:0 (u,v) pair per 2x2 block, kept in
 //            shared memory (this is the "intermediate frame", tile-sized)
 //   phase 2  scale out of shared memory (a lane owns an output column, all taps are dp4a weight
@@ -41,21 +40,31 @@ __device__ __forceinline__ uint32_t smem_u32(const void *p)
 // video_scale_v_2tap_u8 (lq): a + (((b-a)*p1 + 32) >> 6), which equals (a*(64-p1) + b*p1 + 32) >> 6
 // (no clamp needed for 0 <= p1 <= 64) and is evaluated as one dp4a on the lanes' high bytes.
 
-// mbarrier init + TMA tiled load of the tile's source window, by one thread. Kept out of line: inlined,
-// the sequence's uniform-datapath instructions are stepped through by all eight warps (~40 issue slots
-// each); as a call only the calling warp pays.
-__device__ __noinline__ void issue_window_load(uint64_t *s_bar, void *dst, const CUtensorMap *map, int x, int y, int z,
-                                               uint32_t bytes)
+// mbarrier init + TMA tiled load of the tile's source window + bulk copies of the tile's tap records (one
+// per tile column, one per tile row; both 16-byte multiples at 16-byte aligned addresses), all completing
+// on the one mbarrier, by one thread. Kept out of line: inlined, the sequence's uniform-datapath
+// instructions are stepped through by all eight warps (~40 issue slots each); as a call only the calling
+// warp pays.
+struct TileLoad {
+    void *window;  const CUtensorMap *map;  int x, y, z;  uint32_t window_bytes;
+    void *col_dst;  const void *col_src;  uint32_t col_bytes;
+    void *row_dst;  const void *row_src;  uint32_t row_bytes;
+};
+__device__ __noinline__ void issue_tile_load(uint64_t *s_bar, const TileLoad t)
 {
     const uint32_t bar = smem_u32(s_bar);
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(t.window_bytes + t.col_bytes + t.row_bytes) : "memory");
     asm volatile(
         "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
         " [%0], [%1, {%2, %3, %4}], [%5];"
-        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(x), "r"(y), "r"(z), "r"(bar)
+        ::"r"(smem_u32(t.window)), "l"(reinterpret_cast<uint64_t>(t.map)), "r"(t.x), "r"(t.y), "r"(t.z), "r"(bar)
         : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(t.col_dst)), "l"(reinterpret_cast<uint64_t>(t.col_src)), "r"(t.col_bytes), "r"(bar) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(t.row_dst)), "l"(reinterpret_cast<uint64_t>(t.row_src)), "r"(t.row_bytes), "r"(bar) : "memory");
 }
 
 // The general fused kernel's output tile, shared memory -> the planes, as TMA tiled stores by one thread
@@ -172,10 +181,10 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const __grid_
 {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t s_bar;
-    // this tile's taps, ready to use (FusedTaps): copied from the host-made records while the TMA
-    // load is in flight
+    // this tile's taps, ready to use (FusedTaps): bulk copies of the host-made records, in flight with the
+    // window's TMA load and completing on the same mbarrier
     __shared__ __align__(16) uint32_t s_col[4 * TW];           // luma records (two forms, FusedTaps) | hc[TW/2] quads
-    __shared__ __align__(8) uint32_t s_row[3 * TILE_H];        // vy[TILE_H] pairs | vc[TILE_H/2] pairs
+    __shared__ __align__(16) uint32_t s_row[3 * TILE_H];       // vy[TILE_H] pairs | vc[TILE_H/2] pairs
     __shared__ __align__(128) uint8_t s_out[TW * TILE_H * 3 / 2];  // output tile: Y, then U and V (or UV) tiles
     const uint4 *s_hc = reinterpret_cast<const uint4 *>(s_col + 2 * TW);
     const uint2 *s_vy = reinterpret_cast<const uint2 *>(s_row), *s_vc = s_vy + TILE_H;
@@ -196,13 +205,13 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const __grid_
             gate_wait_thread(p.gate, min(max(sy0 + bh, 1), p.in_h) - 1);
             asm volatile("fence.proxy.async;" ::: "memory");
         }
-        issue_window_load(&s_bar, s_src, &src_map, sx0, sy0, (int)blockIdx.z, (uint32_t)bw * bh * 4);
+        TileLoad t;
+        t.window = s_src;  t.map = &src_map;  t.x = sx0;  t.y = sy0;  t.z = (int)blockIdx.z;  t.window_bytes = (uint32_t)bw * bh * 4;
+        t.col_dst = s_col;  t.col_src = p.ft.col_rec + blockIdx.x * (4 * TW);  t.col_bytes = 4 * TW * 4;
+        t.row_dst = s_row;  t.row_src = p.ft.row_rec + blockIdx.y * (3 * TILE_H);  t.row_bytes = 3 * TILE_H * 4;
+        issue_tile_load(&s_bar, t);
     }
-    s_col[tid] = p.ft.col_rec[blockIdx.x * (4 * TW) + tid];               // 4 * TW == 256 == blockDim.x
-#pragma unroll
-    for (int i = tid; i < 3 * TILE_H; i += 256)
-        s_row[i] = p.ft.row_rec[blockIdx.y * (3 * TILE_H) + i];
-    __syncthreads();
+    __syncthreads();                                       // (the mbarrier exists)
     {
         const uint32_t bar = smem_u32(&s_bar);
         uint32_t done = 0;

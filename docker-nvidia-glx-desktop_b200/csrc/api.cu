@@ -801,6 +801,7 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         p.out = out;  p.ft = c->ft;
         p.in_w = g.in_w;  p.in_h = g.in_h;  p.out_w = g.out_w;  p.out_h = g.out_h;
         p.box_w = c->box_w;  p.box_h = c->box_h;  p.tile_h = c->tile_h;  p.n_frames = n_frames;
+        p.planes_off = (int)fused_scale_planes_off(c->box_w, c->box_h, c->tile_h);
         p.box2x2 = g.scale_mode == B200VC_SCALE_BOX_2X2;  p.pair_luma = c->pair_luma ? 1 : 0;  p.mx = c->mx;  p.gate = gate;
         // items per line pair of the window: the box's 4-column groups, or one group fewer when a
         // tile's first group is pure halo
@@ -1050,7 +1051,7 @@ int create_impl(b200vc_ctx *c)
             auto ctas_per_sm = [&](int th) {
                 int bw, bh;
                 fused_box(k, hy, vy, hc, vc, th, bw, bh);
-                const size_t cta = fused_scale_smem_bytes(bw, bh) + fused_scale_static_bytes(th);
+                const size_t cta = fused_scale_smem_bytes(bw, bh, th) + fused_scale_static_bytes(th);
                 if (bw > 256 || bh > 256 || cta > (size_t)c->prop.sharedMemPerBlockOptin) return 0;
                 return (int)std::min<size_t>(8, (size_t)c->prop.sharedMemPerMultiprocessor / (cta + 1024));
             };
@@ -1068,7 +1069,7 @@ int create_impl(b200vc_ctx *c)
                     if (atoi(force) == th && usable(th)) best = th;
             c->tile_h = best;
             fused_box(k, hy, vy, hc, vc, c->tile_h, c->box_w, c->box_h);
-            c->smem_bytes = fused_scale_smem_bytes(c->box_w, c->box_h);
+            c->smem_bytes = fused_scale_smem_bytes(c->box_w, c->box_h, c->tile_h);
         }
         const bool fits = c->box_w <= 256 && c->box_h <= 256 &&
                           c->smem_bytes + fused_scale_static_bytes(c->tile_h) <= (size_t)c->prop.sharedMemPerBlockOptin;

@@ -185,14 +185,15 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const __grid_
     // window's TMA load and completing on the same mbarrier
     __shared__ __align__(16) uint32_t s_col[4 * TW];           // luma records (two forms, FusedTaps) | hc[TW/2] quads
     __shared__ __align__(16) uint32_t s_row[3 * TILE_H];       // vy[TILE_H] pairs | vc[TILE_H/2] pairs
-    __shared__ __align__(128) uint8_t s_out[TW * TILE_H * 3 / 2];  // output tile: Y, then U and V (or UV) tiles
     const uint4 *s_hc = reinterpret_cast<const uint4 *>(s_col + 2 * TW);
     const uint2 *s_vy = reinterpret_cast<const uint2 *>(s_row), *s_vc = s_vy + TILE_H;
 
     const int bw = p.box_w, bh = p.box_h;
     uint32_t *s_src = reinterpret_cast<uint32_t *>(smem);                 // [bh][bw] pixels
-    uint8_t *s_yf = smem + (size_t)bw * bh * 4;                           // [bh][bw] luma
-    uint8_t *s_cf = s_yf + (size_t)bw * bh;                               // [bh/2][bw/2] (u,v) byte pairs
+    uint8_t *s_out = smem;                                                // output tile: Y, then U and V (or UV) tiles; written
+                                                                          // in phase 2, when the pixels are dead
+    uint8_t *s_yf = smem + p.planes_off;                                  // [bh][bw] luma: after the larger of the two
+    uint8_t *s_cf = s_yf + bw * bh;                                       // [bh/2][bw/2] (u,v) byte pairs
 
     const int tid = threadIdx.x;
 
@@ -710,18 +711,26 @@ cudaError_t launch_fused_2x(const CUtensorMap &src_map, const Fused2xParams &p, 
     return site ? launch_2x2<1, 1>(src_map, p, box2x2, grid, st) : launch_2x2<1, 0>(src_map, p, box2x2, grid, st);
 }
 
-size_t fused_scale_smem_bytes(int box_w, int box_h)
+// offset of the Y plane in the kernel's dynamic shared memory: behind the window's pixels and behind
+// the output tile, which takes the pixels' place in phase 2 (an upscale's window can be the smaller one)
+size_t fused_scale_planes_off(int box_w, int box_h, int tile_h)
+{
+    const size_t window = (size_t)box_w * box_h * 4, tile = (size_t)TW * tile_h * 3 / 2;
+    return ((window > tile ? window : tile) + 15) & ~(size_t)15;
+}
+
+size_t fused_scale_smem_bytes(int box_w, int box_h, int tile_h)
 {
     // source pixels (4 bytes) + Y plane (1) + (u,v) plane (a byte pair per 2x2 pixels), and one spare
     // chroma line: a clamped second tap still reads index+1 (with weight 0), which for the last chroma
     // line lies just behind the plane
-    return (size_t)box_w * box_h * 11 / 2 + (size_t)box_w * 2 + 16;
+    return fused_scale_planes_off(box_w, box_h, tile_h) + (size_t)box_w * box_h * 3 / 2 + (size_t)box_w * 2 + 16;
 }
 
-// the kernel's static shared memory for tiles of tile_h rows: output tile, tap records, mbarrier
+// the kernel's static shared memory for tiles of tile_h rows: tap records, mbarrier
 size_t fused_scale_static_bytes(int tile_h)
 {
-    return (size_t)TW * tile_h * 3 / 2 + 12 * (size_t)tile_h + 4 * 4 * TW + 16 + 256;      // (+ alignment gaps)
+    return 12 * (size_t)tile_h + 4 * 4 * TW + 16 + 64;      // (+ alignment gaps)
 }
 
 cudaError_t fused_scale_prepare(size_t optin_bytes)
@@ -749,7 +758,9 @@ cudaError_t launch_fused_scale(const CUtensorMap &src_map, const FusedOutMaps &o
     if (p.box_h > 256 || p.box_w > 256)                    // TMA box limit; and phase 1 divides by up to 64 groups
         return cudaErrorInvalidValue;
     dim3 grid((p.out_w + TW - 1) / TW, (p.out_h + p.tile_h - 1) / p.tile_h, p.n_frames);
-    const size_t smem = fused_scale_smem_bytes(p.box_w, p.box_h);
+    const size_t smem = fused_scale_smem_bytes(p.box_w, p.box_h, p.tile_h);
+    if ((size_t)p.planes_off != fused_scale_planes_off(p.box_w, p.box_h, p.tile_h))
+        return cudaErrorInvalidValue;
     if (fmt == 0)
         return site ? launch_fused2<0, 1>(src_map, out_maps, p, grid, smem, st) : launch_fused2<0, 0>(src_map, out_maps, p, grid, smem, st);
     return site ? launch_fused2<1, 1>(src_map, out_maps, p, grid, smem, st) : launch_fused2<1, 0>(src_map, out_maps, p, grid, smem, st);

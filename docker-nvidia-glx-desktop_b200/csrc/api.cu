@@ -1041,11 +1041,13 @@ int create_impl(b200vc_ctx *c)
 
         // Output rows per tile of the general fused kernel: the height (one instantiation each) that
         // costs the fewest issue slots per frame (fused_frame_cost) among those whose window leaves room
-        // for 5 CTAs per SM. With fewer the TMA waits and the barriers between the phases are no longer
-        // hidden, and that outweighs what the count promises (measured, tools/run_general.sh with forced
-        // heights: 3:2 with 48 rows, 4 CTAs: 0.66 of the roofline against 0.72 with 32 rows, 7 CTAs;
-        // 4K -> 720p: 0.81 with 16 rows, 0.58 with 24, 0.39 with 48; the 2:3 upscale, whose window is
-        // small: 0.32 with 32 rows, 0.40 with 64, 0.41 with 96 — not worth an instantiation of its own).
+        // for 6 CTAs per SM. With fewer the TMA waits and the barriers between the phases are no longer
+        // hidden, and that outweighs what the count promises. Measured with forced heights
+        // (tools/run_general.sh, fraction of the HBM roofline at 16 / 32 / 48 / 64 rows; CTAs per SM in
+        // brackets): 4K -> 1440p 0.61 / 0.82 [8] / 0.81 [5] / 0.79; 1440p -> 1080p 0.53 / 0.72 [8] / 0.76 [6] / 0.71 [4];
+        // 1080p -> 1536x864 0.51 / 0.70 / 0.75 [7] / 0.72 [5]; 4K -> 1080p 0.84 [8] / 0.83 [4] / 0.78 / 0.66;
+        // 4K -> 720p 0.85 (8 rows) / 0.86 (16) [4] / 0.66 (32); the 2:3 upscale, whose window is small,
+        // 0.26 / 0.38 / 0.42 / 0.46 [8].
         {
             static const int heights[] = { 8, 16, 32, 48, 64 };       // K2_TILE_HEIGHTS, k2_scale.cu
             auto ctas_per_sm = [&](int th) {
@@ -1059,7 +1061,7 @@ int create_impl(b200vc_ctx *c)
             int best = 8;
             double best_cost = 0;
             for (int th : heights) {
-                if (th > 8 && ctas_per_sm(th) < 5) continue;
+                if (th > 8 && ctas_per_sm(th) < 6) continue;
                 const double cost = fused_frame_cost(k, hy, vy, hc, vc, th);
                 if (th == 8 || cost < best_cost) { best = th;  best_cost = cost; }
             }

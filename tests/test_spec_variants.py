@@ -86,7 +86,7 @@ def test_gpu_parity_under_variant(variant):
     assert r.returncode == 0 and "0 mismatches" in r.stdout and f"spec {S.name(sp)}" in r.stdout, r.stdout[-3000:] + r.stderr[-2000:]
 
 
-@pytest.mark.parametrize("variant", ["vtap8", "cosited121"])
+@pytest.mark.parametrize("variant", ["vtap8", "cosited121", "nearestedge"])
 def test_gst_validate_names_the_setting(variant):
     """tools/gst_validate.py with an oracle variant standing in for GStreamer: every differing case is matched to
     that variant's constant, and the summary names the default to edit."""

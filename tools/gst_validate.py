@@ -57,13 +57,13 @@ def colorimetry(matrix: int, rng: int) -> str:
     return f"{r}:{m}:0:0"                 # transfer and primaries unknown: no gamma/primaries conversion
 
 
-def gst_convert(gst: str, frame: np.ndarray, inf: int, fmt: int, matrix: int, rng: int, site: int, out_size, tmp: str):
+def gst_convert(gst: str, frame: np.ndarray, inf: int, fmt: int, matrix: int, rng: int, site: int, out_size, tmp: str, mode: int = 0):
     h, w = frame.shape[:2]
     ow, oh = out_size
     src, dst = os.path.join(tmp, "in.raw"), os.path.join(tmp, "out.raw")
     np.ascontiguousarray(frame).tofile(src)
     site_s = "mpeg2" if site == 1 else "jpeg"
-    scale = ["!", "videoscale", "method=bilinear"] if (ow, oh) != (w, h) else []
+    scale = ["!", "videoscale", "method=nearest-neighbour" if mode == 2 else "method=bilinear"] if (ow, oh) != (w, h) else []
     cmd = [gst, "-q", "filesrc", f"location={src}", "!", "rawvideoparse", f"format={IN_FMT[inf]}", f"width={w}",
            f"height={h}", "framerate=1/1", "!", "videoconvert", "n-threads=1", *scale, "!",
            f"video/x-raw,format={OUT_FMT[fmt]},width={ow},height={oh},colorimetry={colorimetry(matrix, rng)},chroma-site={site_s}",
@@ -74,11 +74,11 @@ def gst_convert(gst: str, frame: np.ndarray, inf: int, fmt: int, matrix: int, rn
     return np.fromfile(dst, np.uint8)
 
 
-def which_setting(variants: dict, got: np.ndarray, frame, fmt, matrix, rng, site, out_size, inf):
+def which_setting(variants: dict, got: np.ndarray, frame, fmt, matrix, rng, site, out_size, inf, mode=0):
     """Names of the spec variants whose oracle reproduces `got` for this case."""
     hits = []
     for name, o in variants.items():
-        want = o.convert(frame, fmt, matrix, rng, site, out_size=out_size, in_format=inf)[0]
+        want = o.convert(frame, fmt, matrix, rng, site, out_size=out_size, in_format=inf, scale_mode=mode)[0]
         if want.size == got.size and np.array_equal(want, got):
             hits.append(name)
     return hits
@@ -119,23 +119,26 @@ def main():
                                  (640, 360, 1280, 720, "B.2 scaler, upscale"), (641, 361, 320, 180, "scaler, odd source")]:
         for kind in ("rand", "bars"):
             cases.append((kind, w, h, ow, oh, 0, 0, 1, 0, 1, what))
+    cases = [c + (0,) for c in cases]                      # scale mode: bilinear
+    for (w, h, ow, oh) in [(1920, 1080, 1280, 720), (640, 360, 1280, 720), (641, 361, 320, 180)]:
+        cases.append(("rand", w, h, ow, oh, 0, 0, 1, 0, 1, "videoscale method=nearest-neighbour (sample position)", 2))
     if args.quick:
         cases = [c for c in cases if c[1] <= 642]
     bad = 0
     selected: dict[str, int] = {}
-    for (kind, w, h, ow, oh, inf, fmt, matrix, rng, site, what) in cases:
+    for (kind, w, h, ow, oh, inf, fmt, matrix, rng, site, what, mode) in cases:
         if kind == "rand16":
             frame = np.random.default_rng(w + inf).integers(0, 256, (h, w, 2), dtype=np.uint8)
         else:
             frame = orc.synth(kind, w, h, 3)
-        want, off, pit = orc.convert(frame, fmt, matrix, rng, site, out_size=(ow, oh), in_format=inf)
+        want, off, pit = orc.convert(frame, fmt, matrix, rng, site, out_size=(ow, oh), in_format=inf, scale_mode=mode)
         try:
             if stand_in:
-                got = stand_in.convert(frame, fmt, matrix, rng, site, out_size=(ow, oh), in_format=inf)[0]
+                got = stand_in.convert(frame, fmt, matrix, rng, site, out_size=(ow, oh), in_format=inf, scale_mode=mode)[0]
             else:
-                got = gst_convert(gst, frame, inf, fmt, matrix, rng, site, (ow, oh), tmp)
+                got = gst_convert(gst, frame, inf, fmt, matrix, rng, site, (ow, oh), tmp, mode)
         except Exception as e:  # noqa: BLE001
-            print(f"ERROR {kind} {w}x{h}->{ow}x{oh} in{inf} {OUT_FMT[fmt]} {MATRIX[matrix]} r{rng} s{site}: {e}")
+            print(f"ERROR {kind} {w}x{h}->{ow}x{oh} in{inf} {OUT_FMT[fmt]} {MATRIX[matrix]} r{rng} s{site} mode{mode}: {e}")
             bad += 1
             continue
         ok = got.size == want.size and np.array_equal(got, want)
@@ -147,12 +150,12 @@ def main():
                 detail = "; ".join(f"{names[i]}: {int((a != b).sum())} bytes differ, max |d| {int(np.abs(a.astype(int) - b).max())}"
                                    for i, (a, b) in enumerate(zip(plane_views(got, off, pit, fmt, ow, oh),
                                                                   plane_views(want, off, pit, fmt, ow, oh))))
-            hits = which_setting(variants, got, frame, fmt, matrix, rng, site, (ow, oh), inf)
+            hits = which_setting(variants, got, frame, fmt, matrix, rng, site, (ow, oh), inf, mode)
             for name in hits:
                 selected[name] = selected.get(name, 0) + 1
             verdict = ("matches the spec variant(s) " + ", ".join(f"{n} ({S.env_text(S.VARIANTS[n])})" for n in hits)) if hits else \
                 "matches no single-constant variant"
-            print(f"DIFF  {kind} {w}x{h}->{ow}x{oh} in{inf} {OUT_FMT[fmt]} {MATRIX[matrix]} r{rng} s{site} [{what}]: {detail}; {verdict}")
+            print(f"DIFF  {kind} {w}x{h}->{ow}x{oh} in{inf} {OUT_FMT[fmt]} {MATRIX[matrix]} r{rng} s{site} mode{mode} [{what}]: {detail}; {verdict}")
     print(f"{len(cases)} cases, {bad} differ from GStreamer" + ("" if bad else ": the oracle is pinned for these caps"))
     if selected:
         print("settings that explain differing cases (edit these defaults in include/b200vc_spec.h, rebuild, run again):")

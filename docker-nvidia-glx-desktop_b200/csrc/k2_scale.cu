@@ -13,9 +13,11 @@
 //            host-made tap records; the CTA then waits on one mbarrier for all the bytes
 //   phase 1  convert the window: Y per pixel and the 4:2:0 (u,v) pair per 2x2 block, kept in
 //            shared memory (this is the "intermediate frame", tile-sized)
-//   phase 2  scale out of shared memory (a lane owns an output column, all taps are dp4a weight
-//            words) into an output tile in shared memory
-//   phase 3  the tile leaves as 16-byte stores
+//   phase 2  scale out of shared memory (a lane owns two adjacent output columns of luma or one
+//            (u,v) sample, word loads, all taps are dp4a weight words) into an output tile, which
+//            takes the place of the window's pixels in shared memory
+//   phase 3  the tile leaves by TMA stores (device planes whose rows and pitches are multiples of
+//            16 bytes) or as 16-byte stores
 // (k2_fused_scale_kernel, any ratio whose window fits a TMA box). When the ratio is exactly 2:1,
 // k2_fused_2x_kernel does all of it in registers straight from the TMA tile. The file also holds the
 // gather form of the two-pass path's plane scaler (its tiled form is k2_plane_tile.cu).

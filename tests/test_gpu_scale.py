@@ -174,3 +174,36 @@ def test_general_kernel_tile_stores(conv, orc, geo, monkeypatch):
             buf, off, pit = conv.transform_frame(frame)
             assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), want, f"{geo} fmt{fmt} tma stores off={off_switch}")
     monkeypatch.delenv("B200VC_NO_TMA_STORE", raising=False)
+
+
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_general_kernel_device_batch(conv, orc, fmt, monkeypatch):
+    """Several frames in one launch of the general fused kernel on the device entry point, planes in GstVideoInfo's
+    default layout (rows and pitches multiples of 16: the tiles leave by TMA stores through 3-D maps whose third
+    dimension is the frame), and the same with the kernel's own stores."""
+    import torch
+    iw, ih, ow, oh, n = 1920, 1080, 1280, 720, 3
+    total, off, pit = b200vc.default_layout(fmt, ow, oh)
+    host = np.stack([orc.synth("rand", iw, ih, 80 + i) for i in range(n)])
+    want = [_want(orc, host[i], ow, oh, fmt, 1, 0, 1) for i in range(n)]
+    d_in = torch.from_numpy(host.reshape(n, -1)).cuda()
+    for off_switch in (False, True):
+        if off_switch:
+            monkeypatch.setenv("B200VC_NO_TMA_STORE", "1")
+        else:
+            monkeypatch.delenv("B200VC_NO_TMA_STORE", raising=False)
+        d_out = torch.full((n, total), 0x5A, dtype=torch.uint8, device="cuda")
+        conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=1, range_=0, chroma_site=1, max_sessions=2)
+        inf = conv.info()
+        assert inf.path == 1 and inf.fused_2to1 == 0
+        df = b200vc.DeviceFrames()
+        df.bgrx, df.in_pitch, df.in_frame_stride = d_in.data_ptr(), iw * 4, iw * ih * 4
+        for i in range(2 if fmt == 1 else 3):
+            df.planes[i], df.pitches[i] = d_out.data_ptr() + off[i], pit[i]
+        df.out_frame_stride, df.n_frames = total, n
+        conv.convert_device(df, 0)
+        torch.cuda.synchronize()
+        got = d_out.cpu().numpy()
+        for i in range(n):
+            assert_planes_equal(plane_views(got[i], off, pit, fmt, ow, oh), want[i], f"frame {i} fmt{fmt} tma stores off={off_switch}")
+    monkeypatch.delenv("B200VC_NO_TMA_STORE", raising=False)

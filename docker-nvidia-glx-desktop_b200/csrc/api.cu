@@ -239,9 +239,10 @@ uint32_t v_weights(Tap t)
 // Window origin of a tile column / tile row: the first source column (line) any of its taps reads,
 // the cosited chroma filter's left neighbour included, rounded down to what the TMA box (16-byte
 // aligned start) and the 2x2 chroma sites need.
-inline int tile_org_x(const std::vector<Tap> &hy, const std::vector<Tap> &hc, int x0, int site)
+inline int tile_org_x(const b200vc_config &c, const std::vector<Tap> &hy, const std::vector<Tap> &hc, int x0, int site)
 {
-    return std::min(tidx(hy[x0]), 2 * tidx(hc[x0 >> 1]) - site) & ~3;
+    const int align = 16 / in_bytes_per_pixel(c.in_format);              // pixels per 16 bytes: 4, or 8 (5-6-5)
+    return std::min(tidx(hy[x0]), 2 * tidx(hc[x0 >> 1]) - site) & ~(align - 1);
 }
 inline int tile_org_y(const std::vector<Tap> &vy, const std::vector<Tap> &vc, int y0)
 {
@@ -256,7 +257,7 @@ struct FusedSpanY { int sy, pairs; };
 inline FusedSpanX fused_span_x(const b200vc_config &c, const std::vector<Tap> &hy, const std::vector<Tap> &hc, int x0, int site)
 {
     const int x1 = std::min(x0 + K2_TILE_W, c.out_w) - 1;
-    const int sx = tile_org_x(hy, hc, x0, site);
+    const int sx = tile_org_x(c, hy, hc, x0, site);
     const int first = std::min(tidx(hy[x0]), 2 * tidx(hc[x0 >> 1]));
     const int last = std::max(tidx(hy[x1]) + tstep(hy[x1]), 2 * (tidx(hc[x1 >> 1]) + tstep(hc[x1 >> 1])) + 1);
     const int kfirst = std::min(first - sx, 4) >> 2;
@@ -304,7 +305,7 @@ void build_fused_taps(const b200vc_config &c, const std::vector<Tap> &hy, const 
     pad4();
     o.col_rec = o.w.size();
     for (int bx = 0; bx < tiles_x; bx++) {
-        const int x0 = bx * K2_TILE_W, sx = tile_org_x(hy, hc, x0, site);
+        const int x0 = bx * K2_TILE_W, sx = tile_org_x(c, hy, hc, x0, site);
         auto h_weights = [](Tap t) {
             const uint32_t f = tstep(t) ? (uint32_t)tfrac(t) : 0u;
             return (255u - f) | (1u << 8) | (f << 16);
@@ -406,6 +407,7 @@ void fused_box(const b200vc_config &c, const std::vector<Tap> &hy, const std::ve
     }
     for (int y0 = 0; y0 < c.out_h; y0 += tile_h)
         box_h = std::max(box_h, 2 * fused_span_y(c, vy, vc, y0, tile_h).pairs);
+    box_w = (int)ru((size_t)box_w, 16 / in_bytes_per_pixel(c.in_format));   // a box line is a multiple of 16 bytes
 }
 
 // Issue slots the general fused kernel spends on one frame with tiles of tile_h rows, in warp
@@ -637,7 +639,8 @@ int get_tensor_map(b200vc_ctx *c, const void *base, size_t pitch, size_t frame_s
     cuuint64_t strides[2] = { (cuuint64_t)pitch, (cuuint64_t)(frame_stride ? frame_stride : pitch * c->cfg.in_h) };
     cuuint32_t box[3] = { (cuuint32_t)c->box_w, (cuuint32_t)c->box_h, 1 };
     cuuint32_t estr[3] = { 1, 1, 1 };
-    CUresult r = c->encode_tiled(&e.map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, const_cast<void *>(base), dims, strides,
+    const bool in16 = in_bytes_per_pixel(c->cfg.in_format) == 2;
+    CUresult r = c->encode_tiled(&e.map, in16 ? CU_TENSOR_MAP_DATA_TYPE_UINT16 : CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, const_cast<void *>(base), dims, strides,
                                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS)
@@ -801,7 +804,8 @@ int enqueue_kernels(b200vc_ctx *c, const uint8_t *d_src, size_t src_pitch, size_
         p.out = out;  p.ft = c->ft;
         p.in_w = g.in_w;  p.in_h = g.in_h;  p.out_w = g.out_w;  p.out_h = g.out_h;
         p.box_w = c->box_w;  p.box_h = c->box_h;  p.tile_h = c->tile_h;  p.n_frames = n_frames;
-        p.planes_off = (int)fused_scale_planes_off(c->box_w, c->box_h, c->tile_h);
+        p.in16 = in_bytes_per_pixel(g.in_format) == 2;
+        p.planes_off = (int)fused_scale_planes_off(c->box_w, c->box_h, c->tile_h, in_bytes_per_pixel(g.in_format));
         p.box2x2 = g.scale_mode == B200VC_SCALE_BOX_2X2;  p.pair_luma = c->pair_luma ? 1 : 0;  p.mx = c->mx;  p.gate = gate;
         // items per line pair of the window: the box's 4-column groups, or one group fewer when a
         // tile's first group is pure halo
@@ -1053,7 +1057,7 @@ int create_impl(b200vc_ctx *c)
             auto ctas_per_sm = [&](int th) {
                 int bw, bh;
                 fused_box(k, hy, vy, hc, vc, th, bw, bh);
-                const size_t cta = fused_scale_smem_bytes(bw, bh, th) + fused_scale_static_bytes(th);
+                const size_t cta = fused_scale_smem_bytes(bw, bh, th, in_bytes_per_pixel(k.in_format)) + fused_scale_static_bytes(th);
                 if (bw > 256 || bh > 256 || cta > (size_t)c->prop.sharedMemPerBlockOptin) return 0;
                 return (int)std::min<size_t>(8, (size_t)c->prop.sharedMemPerMultiprocessor / (cta + 1024));
             };
@@ -1071,17 +1075,18 @@ int create_impl(b200vc_ctx *c)
                     if (atoi(force) == th && usable(th)) best = th;
             c->tile_h = best;
             fused_box(k, hy, vy, hc, vc, c->tile_h, c->box_w, c->box_h);
-            c->smem_bytes = fused_scale_smem_bytes(c->box_w, c->box_h, c->tile_h);
+            c->smem_bytes = fused_scale_smem_bytes(c->box_w, c->box_h, c->tile_h, in_bytes_per_pixel(k.in_format));
         }
         const bool fits = c->box_w <= 256 && c->box_h <= 256 &&
                           c->smem_bytes + fused_scale_static_bytes(c->tile_h) <= (size_t)c->prop.sharedMemPerBlockOptin;
         // (odd sizes run the general fused kernel; the exact-2:1 kernel needs multiples of 4, BOX even sizes)
         // (the fused kernels scale horizontally first; a build with the other order of the spec takes the two-pass path)
-        // (and they read 4-byte pixels and make 4:2:0 planes; 16-bit input and Y42B/Y444 output take the two-pass path too)
-        const bool fusable = in_bytes_per_pixel(g.in_format) == 4 && g.out_format <= B200VC_FMT_NV12;
+        // (and they make 4:2:0 planes: Y42B/Y444 output takes the two-pass path too; 5-6-5 input is unpacked in the
+        // general fused kernel's phase 1, the exact-2:1 kernel reads 4-byte pixels only)
+        const bool fusable = g.out_format <= B200VC_FMT_NV12;
         c->path = (fits && fusable && !(g.flags & B200VC_FLAG_FORCE_TWO_PASS) && B200VC_SPEC_SCALE_H_FIRST) ? 1 : 2;
         const bool exact2 = g.in_w == 2 * k.out_w && g.in_h == 2 * k.out_h && (g.in_w % 4) == 0 && (g.in_h % 4) == 0;
-        c->fused2x = c->path == 1 && exact2 && !(g.flags & B200VC_FLAG_FORCE_GENERIC_FUSED) &&
+        c->fused2x = c->path == 1 && exact2 && !(g.flags & B200VC_FLAG_FORCE_GENERIC_FUSED) && in_bytes_per_pixel(g.in_format) == 4 &&
                      (g.scale_mode == B200VC_SCALE_BOX_2X2 ||
                       (taps_are_2to1(hy, k.out_w, false) && taps_are_2to1(vy, k.out_h, true) &&
                        taps_are_2to1(hc, k.out_w / 2, false) && taps_are_2to1(vc, k.out_h / 2, true)));

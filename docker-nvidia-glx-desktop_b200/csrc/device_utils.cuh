@@ -184,4 +184,19 @@ __device__ __forceinline__ uint32_t filt121_raw(uint32_t l, uint32_t c, uint32_t
     return (l + 2u * c + r + 0x00020002u) >> 2;
 }
 
+// One 5-6-5 pixel (low 16 bits of v) as a 4-byte pixel: low field in byte 0, middle field in byte 1, high
+// field in byte 2 (RGB16 reads like BGRx then, BGR16 like RGBx), each widened to 8 bits the way video-format.c
+// unpacks them: high bits repeated into the low ones (B200VC_SPEC_UNPACK16_REPLICATE; 0: plain shift).
+__device__ __forceinline__ uint32_t unpack565(uint32_t v)
+{
+    uint32_t t = ((v & 0xF800u) << 8) | ((v & 0x07E0u) << 5) | ((v & 0x001Fu) << 3);
+    if (B200VC_SPEC_UNPACK16_REPLICATE) t |= ((t >> 5) & 0x00070007u) | ((t >> 6) & 0x00000300u);
+    return t;
+}
+
+__device__ __forceinline__ uint4 unpack565x4(uint2 raw)
+{
+    return make_uint4(unpack565(raw.x), unpack565(raw.x >> 16), unpack565(raw.y), unpack565(raw.y >> 16));
+}
+
 }  // namespace b200vc

@@ -42,21 +42,6 @@ struct WarpStage {
     uint8_t c[CROWS][CBYTES];            // planar: U in the first half of a row, V in the second; NV12: UVUV..
 };
 
-// One 5-6-5 pixel (low 16 bits of v) as a 4-byte pixel: low field in byte 0, middle field in byte 1, high
-// field in byte 2 (RGB16 reads like BGRx then, BGR16 like RGBx), each widened to 8 bits the way video-format.c
-// unpacks them: high bits repeated into the low ones (B200VC_SPEC_UNPACK16_REPLICATE; 0: plain shift).
-__device__ __forceinline__ uint32_t unpack565(uint32_t v)
-{
-    uint32_t t = ((v & 0xF800u) << 8) | ((v & 0x07E0u) << 5) | ((v & 0x001Fu) << 3);
-    if (B200VC_SPEC_UNPACK16_REPLICATE) t |= ((t >> 5) & 0x00070007u) | ((t >> 6) & 0x00000300u);
-    return t;
-}
-
-__device__ __forceinline__ uint4 unpack565x4(uint2 raw)
-{
-    return make_uint4(unpack565(raw.x), unpack565(raw.x >> 16), unpack565(raw.y), unpack565(raw.y >> 16));
-}
-
 __device__ __forceinline__ uint32_t ldg_stream_u16(const void *p)
 {
     uint16_t r;

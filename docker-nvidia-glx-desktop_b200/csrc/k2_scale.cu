@@ -24,6 +24,8 @@
 //
 // HBM roofline: algorithmic bytes per output frame = in_w*in_h*4 + out_w*out_h*1.5.
 #include "device_utils.cuh"
+
+#include <type_traits>
 #include "../../include/b200vc_spec.h"
 
 namespace b200vc {
@@ -92,7 +94,8 @@ __device__ __noinline__ void store_tile(const FusedOutMaps *om, const uint8_t *s
 
 // Odd frames, edge tiles of the general fused kernel: window column dupx / line dupy (the ones just past
 // the frame, zero-filled by the TMA unit) become copies of the column / line before them.
-__device__ __forceinline__ void repeat_last_column_and_line(uint32_t *s_src, int bw, int bh, int dupx, int dupy, int odd_w,
+template <typename PX>
+__device__ __forceinline__ void repeat_last_column_and_line(PX *s_src, int bw, int bh, int dupx, int dupy, int odd_w,
                                                          int odd_h, int tid)
 {
     const bool fixx = odd_w && dupx > 0 && dupx < bw, fixy = odd_h && dupy > 0 && dupy < bh;
@@ -104,17 +107,23 @@ __device__ __forceinline__ void repeat_last_column_and_line(uint32_t *s_src, int
             if (!(fixx && c == dupx)) s_src[dupy * bw + c] = s_src[(dupy - 1) * bw + c];
 }
 
-// Phase 1 of the general fused kernel: one item = 4 columns x 2 lines of the window, BGRx at ra (second
-// line bw words on) -> Y bytes at ya and two filtered, vertically averaged (u,v) byte pairs at cf. `left`: the
-// group has a left chroma neighbour in the window (not frame column 0, not the window's first group);
-// e0 / e2: its first / second even column is the frame's last one (B200VC_SPEC_COSITED_LAST_1_3).
-template <int SITE, bool NEG, bool EDGE>
-__device__ __forceinline__ void convert_item(const uint32_t *ra, uint8_t *ya, uint8_t *cf, int bw, bool left, bool e0, bool e2,
+// Phase 1 of the general fused kernel: one item = 4 columns x 2 lines of the window, pixels at ra (second
+// line bw pixels on; PX = uint32_t: 4-byte pixels, uint16_t: 5-6-5 pixels, unpacked here) -> Y bytes at ya and
+// two filtered, vertically averaged (u,v) byte pairs at cf. `left`: the group has a left chroma neighbour in
+// the window (not frame column 0, not the window's first group); e0 / e2: its first / second even column is
+// the frame's last one (B200VC_SPEC_COSITED_LAST_1_3).
+__device__ __forceinline__ uint4 load_px4(const uint32_t *p) { return *reinterpret_cast<const uint4 *>(p); }
+__device__ __forceinline__ uint4 load_px4(const uint16_t *p) { return unpack565x4(*reinterpret_cast<const uint2 *>(p)); }
+__device__ __forceinline__ uint32_t load_px(const uint32_t *p) { return *p; }
+__device__ __forceinline__ uint32_t load_px(const uint16_t *p) { return unpack565(*p); }
+
+template <int SITE, bool NEG, bool EDGE, typename PX>
+__device__ __forceinline__ void convert_item(const PX *ra, uint8_t *ya, uint8_t *cf, int bw, bool left, bool e0, bool e2,
                                              const Matrix &m)
 {
-    const uint32_t *rb = ra + bw;
-    const uint4 a = *reinterpret_cast<const uint4 *>(ra);
-    const uint4 b = *reinterpret_cast<const uint4 *>(rb);
+    const PX *rb = ra + bw;
+    const uint4 a = load_px4(ra);
+    const uint4 b = load_px4(rb);
     *reinterpret_cast<uint32_t *>(ya) = pack_luma4(luma_sum(a.x, m), luma_sum(a.y, m), luma_sum(a.z, m), luma_sum(a.w, m));
     *reinterpret_cast<uint32_t *>(ya + bw) = pack_luma4(luma_sum(b.x, m), luma_sum(b.y, m), luma_sum(b.z, m), luma_sum(b.w, m));
 
@@ -135,8 +144,8 @@ __device__ __forceinline__ void convert_item(const uint32_t *ra, uint8_t *ya, ui
         // chroma column is halo and is never consumed)
         uint32_t la = pa0, lb = pb0;
         if (left) {
-            la = chroma_pair<NEG>(ra[-1], m);
-            lb = chroma_pair<NEG>(rb[-1], m);
+            la = chroma_pair<NEG>(load_px(ra - 1), m);
+            lb = chroma_pair<NEG>(load_px(rb - 1), m);
         }
         // right neighbours: the frame's last even column (in_w - 2, in_w > 2) takes itself
         // (B200VC_SPEC_COSITED_LAST_1_3 = 0: the plain 1-2-1 filter runs to the end; an odd frame's
@@ -176,7 +185,7 @@ __device__ __forceinline__ uint32_t v_pass_pair(uint2 top, uint2 bot, uint32_t w
     return prmt(d0, d1, 0x0051);
 }
 
-template <int FMT, int SITE, bool NEG, int TILE_H, bool ODD>
+template <int FMT, int SITE, bool NEG, int TILE_H, bool ODD, bool IN16>
 __global__ void __launch_bounds__(256, 8)
 k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const __grid_constant__ FusedOutMaps out_maps,
                       const FusedScaleParams p)
@@ -191,7 +200,8 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const __grid_
     const uint2 *s_vy = reinterpret_cast<const uint2 *>(s_row), *s_vc = s_vy + TILE_H;
 
     const int bw = p.box_w, bh = p.box_h;
-    uint32_t *s_src = reinterpret_cast<uint32_t *>(smem);                 // [bh][bw] pixels
+    using PX = typename std::conditional<IN16, uint16_t, uint32_t>::type;
+    PX *s_src = reinterpret_cast<PX *>(smem);                             // [bh][bw] pixels (4-byte, or 5-6-5)
     uint8_t *s_out = smem;                                                // output tile: Y, then U and V (or UV) tiles; written
                                                                           // in phase 2, when the pixels are dead
     uint8_t *s_yf = smem + p.planes_off;                                  // [bh][bw] luma: after the larger of the two
@@ -209,7 +219,7 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const __grid_
             asm volatile("fence.proxy.async;" ::: "memory");
         }
         TileLoad t;
-        t.window = s_src;  t.map = &src_map;  t.x = sx0;  t.y = sy0;  t.z = (int)blockIdx.z;  t.window_bytes = (uint32_t)bw * bh * 4;
+        t.window = s_src;  t.map = &src_map;  t.x = sx0;  t.y = sy0;  t.z = (int)blockIdx.z;  t.window_bytes = (uint32_t)bw * bh * (uint32_t)sizeof(PX);
         t.col_dst = s_col;  t.col_src = p.ft.col_rec + blockIdx.x * (4 * TW);  t.col_bytes = 4 * TW * 4;
         t.row_dst = s_row;  t.row_src = p.ft.row_rec + blockIdx.y * (3 * TILE_H);  t.row_bytes = 3 * TILE_H * 4;
         issue_tile_load(&s_bar, t);
@@ -254,7 +264,7 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const __grid_
             const bool redge = SITE != 0 && B200VC_SPEC_COSITED_LAST_1_3 && p.in_w > 2 && sx0 + bw >= p.in_w;
             const bool e0 = redge && ac == p.in_w - 2, e2 = redge && ac + 2 == p.in_w - 2;
             const int o = 2 * ky0 * bw + 4 * kx, step = rps * bw;
-            const uint32_t *ra = s_src + o;
+            const PX *ra = s_src + o;
             uint8_t *ya = s_yf + o;
             uint8_t *cf = s_cf + ky0 * bw + 4 * kx;                         // two (u,v) byte pairs per item
             // (not unrolled: the unrolled form computes its trip count with a division, per warp and tile
@@ -262,11 +272,11 @@ k2_fused_scale_kernel(const __grid_constant__ CUtensorMap src_map, const __grid_
             if (redge) {
 #pragma unroll 1
                 for (int ky = ky0; ky < pairs; ky += rps, ra += 2 * step, ya += 2 * step, cf += step)
-                    convert_item<SITE, NEG, true>(ra, ya, cf, bw, left, e0, e2, p.mx);
+                    convert_item<SITE, NEG, true, PX>(ra, ya, cf, bw, left, e0, e2, p.mx);
             } else {
 #pragma unroll 1
                 for (int ky = ky0; ky < pairs; ky += rps, ra += 2 * step, ya += 2 * step, cf += step)
-                    convert_item<SITE, NEG, false>(ra, ya, cf, bw, left, false, false, p.mx);
+                    convert_item<SITE, NEG, false, PX>(ra, ya, cf, bw, left, false, false, p.mx);
             }
         }
     }
@@ -650,18 +660,25 @@ __global__ void __launch_bounds__(128) k2_plane_scale_kernel(const PlaneScalePar
     }
 }
 
-template <int FMT, int SITE, bool NEG, bool ODD>
-cudaError_t launch_fused4(const CUtensorMap &map, const FusedOutMaps &om, const FusedScaleParams &p, dim3 grid, size_t smem, cudaStream_t st)
+template <int FMT, int SITE, bool NEG, bool ODD, bool IN16>
+cudaError_t launch_fused5(const CUtensorMap &map, const FusedOutMaps &om, const FusedScaleParams &p, dim3 grid, size_t smem, cudaStream_t st)
 {
     switch (p.tile_h) {                                   // K2_TILE_HEIGHTS
-    case 8:  k2_fused_scale_kernel<FMT, SITE, NEG, 8, ODD><<<grid, 256, smem, st>>>(map, om, p);  break;
-    case 16: k2_fused_scale_kernel<FMT, SITE, NEG, 16, ODD><<<grid, 256, smem, st>>>(map, om, p);  break;
-    case 32: k2_fused_scale_kernel<FMT, SITE, NEG, 32, ODD><<<grid, 256, smem, st>>>(map, om, p);  break;
-    case 48: k2_fused_scale_kernel<FMT, SITE, NEG, 48, ODD><<<grid, 256, smem, st>>>(map, om, p);  break;
-    case 64: k2_fused_scale_kernel<FMT, SITE, NEG, 64, ODD><<<grid, 256, smem, st>>>(map, om, p);  break;
+    case 8:  k2_fused_scale_kernel<FMT, SITE, NEG, 8, ODD, IN16><<<grid, 256, smem, st>>>(map, om, p);  break;
+    case 16: k2_fused_scale_kernel<FMT, SITE, NEG, 16, ODD, IN16><<<grid, 256, smem, st>>>(map, om, p);  break;
+    case 32: k2_fused_scale_kernel<FMT, SITE, NEG, 32, ODD, IN16><<<grid, 256, smem, st>>>(map, om, p);  break;
+    case 48: k2_fused_scale_kernel<FMT, SITE, NEG, 48, ODD, IN16><<<grid, 256, smem, st>>>(map, om, p);  break;
+    case 64: k2_fused_scale_kernel<FMT, SITE, NEG, 64, ODD, IN16><<<grid, 256, smem, st>>>(map, om, p);  break;
     default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();
+}
+
+template <int FMT, int SITE, bool NEG, bool ODD>
+cudaError_t launch_fused4(const CUtensorMap &map, const FusedOutMaps &om, const FusedScaleParams &p, dim3 grid, size_t smem, cudaStream_t st)
+{
+    return p.in16 ? launch_fused5<FMT, SITE, NEG, ODD, true>(map, om, p, grid, smem, st)
+                  : launch_fused5<FMT, SITE, NEG, ODD, false>(map, om, p, grid, smem, st);
 }
 
 template <int FMT, int SITE>
@@ -715,18 +732,18 @@ cudaError_t launch_fused_2x(const CUtensorMap &src_map, const Fused2xParams &p, 
 
 // offset of the Y plane in the kernel's dynamic shared memory: behind the window's pixels and behind
 // the output tile, which takes the pixels' place in phase 2 (an upscale's window can be the smaller one)
-size_t fused_scale_planes_off(int box_w, int box_h, int tile_h)
+size_t fused_scale_planes_off(int box_w, int box_h, int tile_h, int px_bytes)
 {
-    const size_t window = (size_t)box_w * box_h * 4, tile = (size_t)TW * tile_h * 3 / 2;
+    const size_t window = (size_t)box_w * box_h * px_bytes, tile = (size_t)TW * tile_h * 3 / 2;
     return ((window > tile ? window : tile) + 15) & ~(size_t)15;
 }
 
-size_t fused_scale_smem_bytes(int box_w, int box_h, int tile_h)
+size_t fused_scale_smem_bytes(int box_w, int box_h, int tile_h, int px_bytes)
 {
     // source pixels (4 bytes) + Y plane (1) + (u,v) plane (a byte pair per 2x2 pixels), and one spare
     // chroma line: a clamped second tap still reads index+1 (with weight 0), which for the last chroma
     // line lies just behind the plane
-    return fused_scale_planes_off(box_w, box_h, tile_h) + (size_t)box_w * box_h * 3 / 2 + (size_t)box_w * 2 + 16;
+    return fused_scale_planes_off(box_w, box_h, tile_h, px_bytes) + (size_t)box_w * box_h * 3 / 2 + (size_t)box_w * 2 + 16;
 }
 
 // the kernel's static shared memory for tiles of tile_h rows: tap records, mbarrier
@@ -739,8 +756,10 @@ cudaError_t fused_scale_prepare(size_t optin_bytes)
 {
     cudaError_t e;
 #define B200VC_SET1(F, S, N, H) \
-    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, H, false>, optin_bytes)) != cudaSuccess) return e; \
-    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, H, true>, optin_bytes)) != cudaSuccess) return e;
+    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, H, false, false>, optin_bytes)) != cudaSuccess) return e; \
+    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, H, true, false>, optin_bytes)) != cudaSuccess) return e; \
+    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, H, false, true>, optin_bytes)) != cudaSuccess) return e; \
+    if ((e = set_smem(k2_fused_scale_kernel<F, S, N, H, true, true>, optin_bytes)) != cudaSuccess) return e;
 #define B200VC_SET(F, S, N) B200VC_SET1(F, S, N, 8) B200VC_SET1(F, S, N, 16) B200VC_SET1(F, S, N, 32) B200VC_SET1(F, S, N, 48) \
     B200VC_SET1(F, S, N, 64)
     B200VC_SET(0, 0, false) B200VC_SET(0, 0, true) B200VC_SET(0, 1, false) B200VC_SET(0, 1, true)
@@ -760,8 +779,11 @@ cudaError_t launch_fused_scale(const CUtensorMap &src_map, const FusedOutMaps &o
     if (p.box_h > 256 || p.box_w > 256)                    // TMA box limit; and phase 1 divides by up to 64 groups
         return cudaErrorInvalidValue;
     dim3 grid((p.out_w + TW - 1) / TW, (p.out_h + p.tile_h - 1) / p.tile_h, p.n_frames);
-    const size_t smem = fused_scale_smem_bytes(p.box_w, p.box_h, p.tile_h);
-    if ((size_t)p.planes_off != fused_scale_planes_off(p.box_w, p.box_h, p.tile_h))
+    const int px_bytes = p.in16 ? 2 : 4;
+    if ((p.box_w * px_bytes) & 15)                         // a TMA box line is a multiple of 16 bytes
+        return cudaErrorInvalidValue;
+    const size_t smem = fused_scale_smem_bytes(p.box_w, p.box_h, p.tile_h, px_bytes);
+    if ((size_t)p.planes_off != fused_scale_planes_off(p.box_w, p.box_h, p.tile_h, px_bytes))
         return cudaErrorInvalidValue;
     if (fmt == 0)
         return site ? launch_fused2<0, 1>(src_map, out_maps, p, grid, smem, st) : launch_fused2<0, 0>(src_map, out_maps, p, grid, smem, st);

@@ -113,12 +113,13 @@ struct FusedScaleParams {
     PlaneSet out;
     FusedTaps ft;
     int in_w, in_h, out_w, out_h;
-    int box_w, box_h;       // source window per tile (pixels); box_w % 4 == 0, box_h even
+    int box_w, box_h;       // source window per tile (pixels); a line of it a multiple of 16 bytes, box_h even
     int tile_h;             // output rows per tile: 8, 16, 32, 48 or 64 (the cheapest per frame, api.cu fused_frame_cost)
     int n_frames;
     int box2x2;             // scale_mode == BOX_2X2
     int pair_luma;          // form of the luma column records (FusedTaps); never with box2x2
-    int planes_off;         // fused_scale_planes_off(box_w, box_h, tile_h)
+    int in16;               // 5-6-5 input pixels (2 bytes; box_w % 8 == 0), unpacked in phase 1
+    int planes_off;         // fused_scale_planes_off(box_w, box_h, tile_h, bytes per pixel)
     int tma_out;            // the tile leaves by TMA stores through FusedOutMaps (planes in device memory, 16-byte pitches)
     uint32_t inv_items_x;   // ceil(65536 / items per line pair), for box_w/4 and box_w/4 - 1 groups:
     uint32_t inv_items_x1;  // tid / items_x without a division (exact for tid <= 256, up to 64 items)
@@ -205,8 +206,8 @@ cudaError_t launch_fused_scale(const CUtensorMap &src_map, const FusedOutMaps &o
 cudaError_t launch_fused_2x(const CUtensorMap &src_map, const Fused2xParams &p, int fmt, int site, int box2x2,
                             cudaStream_t st);
 cudaError_t launch_plane_scale(const PlaneScaleParams &p, int fmt, cudaStream_t st);
-size_t fused_scale_smem_bytes(int box_w, int box_h, int tile_h);
-size_t fused_scale_planes_off(int box_w, int box_h, int tile_h);
+size_t fused_scale_smem_bytes(int box_w, int box_h, int tile_h, int px_bytes);
+size_t fused_scale_planes_off(int box_w, int box_h, int tile_h, int px_bytes);
 size_t fused_scale_static_bytes(int tile_h);
 cudaError_t fused_scale_prepare(size_t optin_bytes);   // once per device: dynamic shared memory up to the opt-in limit
 

@@ -83,17 +83,22 @@ def test_chroma_sites_with_vertical_cositing_negotiate(conv, orc, site):
 
 @pytest.mark.parametrize("geo", [(1920, 1080, 1280, 720), (1280, 720, 1920, 1080), (640, 360, 320, 180), (133, 37, 65, 20), (1920, 1080, 320, 180)])
 def test_new_formats_scaled(conv, orc, geo):
-    """Y42B/Y444 output and 16-bit input with scaling: convert at the source size, scale every plane (two-pass path;
-    the intermediate and the plane scaler follow the output format's chroma geometry)."""
+    """Y42B/Y444 output and 16-bit input with scaling: convert at the source size, scale every plane. Y42B/Y444 take
+    the two-pass path (the intermediate and the plane scaler follow the output format's chroma geometry); 5-6-5 input
+    to I420/NV12 is unpacked inside the general fused kernel (the 6:1 geometry's window exceeds a TMA box: two-pass),
+    and both ways are checked for it."""
     iw, ih, ow, oh = geo
     rng = np.random.default_rng(iw + oh)
     f4 = orc.synth("rand", iw, ih, 30)
     f2 = rng.integers(0, 256, (ih, iw, 2), dtype=np.uint8)
     for fmt, inf, frame in [(2, 0, f4), (3, 0, f4), (0, 4, f2), (1, 5, f2), (3, 4, f2), (2, 5, f2)]:
-        conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=1, range_=0, chroma_site=1, in_format=inf)
-        assert conv.info().path == 2
-        buf, off, pit = conv.transform_frame(frame)
-        assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), _want(orc, frame, fmt, 1, 0, 1, inf, (ow, oh)), f"{geo} fmt{fmt} in{inf}")
+        want = _want(orc, frame, fmt, 1, 0, 1, inf, (ow, oh))
+        for flags in ((0, b200vc.FLAG_FORCE_TWO_PASS) if fmt <= 1 else (0,)):
+            conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=1, range_=0, chroma_site=1, in_format=inf, flags=flags)
+            fused = fmt <= 1 and not flags and iw < 6 * ow
+            assert conv.info().path == (1 if fused else 2) and conv.info().fused_2to1 == 0
+            buf, off, pit = conv.transform_frame(frame)
+            assert_planes_equal(plane_views(buf, off, pit, fmt, ow, oh), want, f"{geo} fmt{fmt} in{inf} flags{flags}")
 
 
 def test_new_golden_vectors_on_gpu(conv):

@@ -31,6 +31,10 @@ CONFIGS = [
     ("G 4K->720p 3:1", 3840, 2160, 1280, 720, 0, 1, 0, 1, 0, False),
     ("G 1080p->1536x864 1.25:1", 1920, 1080, 1536, 864, 0, 1, 0, 1, 0, False),
     ("G 720p->1080p 2:3 upscale", 1280, 720, 1920, 1080, 0, 1, 0, 1, 0, False),
+    # 5-6-5 input (CDEPTH=16): 2 bytes per pixel, unpacked in the general fused kernel (name ends in "rgb16")
+    ("G 1440p->1080p 4:3 rgb16", 2560, 1440, 1920, 1080, 0, 1, 0, 1, 0, False),
+    ("G 1080p->720p 3:2 rgb16", 1920, 1080, 1280, 720, 0, 1, 0, 1, 0, False),
+    ("T 1440p->1080p 4:3 rgb16 two-pass", 2560, 1440, 1920, 1080, 0, 1, 0, 1, b200vc.FLAG_FORCE_TWO_PASS, False),
     ("T 4K->1440p 3:2 two-pass", 3840, 2160, 2560, 1440, 0, 1, 0, 1, b200vc.FLAG_FORCE_TWO_PASS, False),
     ("T 1440p->1080p 4:3 two-pass", 2560, 1440, 1920, 1080, 0, 1, 0, 1, b200vc.FLAG_FORCE_TWO_PASS, False),
     ("T 1080p->720p 3:2 two-pass", 1920, 1080, 1280, 720, 0, 1, 0, 1, b200vc.FLAG_FORCE_TWO_PASS, False),
@@ -93,22 +97,23 @@ def main():
     for name, iw, ih, ow, oh, fmt, m, rg, site, flags, damage in CONFIGS:
         if only and only not in name:
             continue
-        in_b, (total, off, pit) = iw * ih * 4, b200vc.default_layout(fmt, ow, oh)
+        bpp, in_format = (2, b200vc.IN_RGB16) if "rgb16" in name else (4, b200vc.IN_BGRX)
+        in_b, (total, off, pit) = iw * ih * bpp, b200vc.default_layout(fmt, ow, oh)
         n = max(8, min(64, int(600e6 // in_b)))                 # ring >= ~600 MB of input
-        conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=m, range_=rg, chroma_site=site, flags=flags, max_sessions=8)
+        conv.set_info(iw, ih, ow, oh, out_format=fmt, matrix=m, range_=rg, chroma_site=site, flags=flags, max_sessions=8, in_format=in_format)
         d_in = torch.randint(0, 256, (n, in_b), dtype=torch.uint8, device="cuda")
         d_out = torch.zeros((n, total), dtype=torch.uint8, device="cuda")
         mb = ((iw + 15) // 16) * ((ih + 15) // 16)
         d_dmg = torch.zeros((n, mb), dtype=torch.uint8, device="cuda")
         df = b200vc.DeviceFrames()
-        df.bgrx, df.in_pitch, df.in_frame_stride = d_in.data_ptr(), iw * 4, in_b
+        df.bgrx, df.in_pitch, df.in_frame_stride = d_in.data_ptr(), iw * bpp, in_b
         for i in range(3):
             df.planes[i], df.pitches[i] = d_out.data_ptr() + off[i], pit[i]
         df.out_frame_stride, df.n_frames = total, n
         algo = in_b + total
         if damage:
             d_prev = torch.roll(d_in, 1, 0).contiguous()
-            df.prev, df.prev_pitch, df.prev_frame_stride = d_prev.data_ptr(), iw * 4, in_b
+            df.prev, df.prev_pitch, df.prev_frame_stride = d_prev.data_ptr(), iw * bpp, in_b
             df.damage, df.damage_frame_stride = d_dmg.data_ptr(), mb
             algo += in_b + mb
         with torch.cuda.stream(stream):
@@ -141,7 +146,7 @@ def main():
             frames_df = []
             for i in range(n):
                 d1 = b200vc.DeviceFrames()
-                d1.bgrx, d1.in_pitch, d1.in_frame_stride = d_in.data_ptr() + i * in_b, iw * 4, in_b
+                d1.bgrx, d1.in_pitch, d1.in_frame_stride = d_in.data_ptr() + i * in_b, iw * bpp, in_b
                 for k in range(3):
                     d1.planes[k], d1.pitches[k] = d_out.data_ptr() + i * total + off[k], pit[k]
                 d1.out_frame_stride, d1.n_frames = total, 1

@@ -194,9 +194,26 @@ __device__ __forceinline__ uint32_t unpack565(uint32_t v)
     return t;
 }
 
+// Two 5-6-5 pixels (the halves of w) at once, on 2x16-bit lanes: a 5-bit field f widened with its high bits
+// repeated is (f << 3) | (f >> 2) = (33 * f) >> 2, a 6-bit one (65 * f) >> 4 (no carry between the lanes: 33 * 31
+// and 65 * 63 fit 16 bits); the shifts drag the upper lane's low bits into the top of the lower lane, where no
+// byte is taken from — except into byte 3 of the first pixel, the unused x byte, whose matrix coefficient is 0.
+__device__ __forceinline__ uint2 unpack565x2(uint32_t w)
+{
+    uint32_t lo = w & 0x001F001Fu, mid = (w >> 5) & 0x003F003Fu, hi = (w >> 11) & 0x001F001Fu;
+    if (B200VC_SPEC_UNPACK16_REPLICATE) {
+        lo = (lo * 33u) >> 2;  mid = (mid * 65u) >> 4;  hi = (hi * 33u) >> 2;
+    } else {
+        lo <<= 3;  mid <<= 2;  hi <<= 3;
+    }
+    const uint32_t lm = prmt(lo, mid, 0x6240);                       // lo0 mid0 lo1 mid1
+    return make_uint2(prmt(lm, hi, 0x5410), prmt(lm, hi, 0x7632));   // {lo, mid, hi, x} of each pixel
+}
+
 __device__ __forceinline__ uint4 unpack565x4(uint2 raw)
 {
-    return make_uint4(unpack565(raw.x), unpack565(raw.x >> 16), unpack565(raw.y), unpack565(raw.y >> 16));
+    const uint2 a = unpack565x2(raw.x), b = unpack565x2(raw.y);
+    return make_uint4(a.x, a.y, b.x, b.y);
 }
 
 }  // namespace b200vc

@@ -118,6 +118,7 @@ struct b200vc_ctx {
     int tile_h = K2_TILE_H;
     bool pair_luma = false;
     bool no_tma_out = false;
+    bool equal_bands = false;                  // B200VC_EQUAL_BANDS: the synchronous call's bands all the same size (measurements only)
     uint32_t *d_ptaps = nullptr;               // tiled plane scaler's records (two-pass path)
     PlaneTileKind pt[2] = {};
     bool plane_tiled = false;                  // two-pass path: pass 2 is the tiled kernel, not the gather kernel
@@ -931,6 +932,7 @@ int create_impl(b200vc_ctx *c)
     c->maps.reserve(64);
     c->out_maps.reserve(64);
     c->no_tma_out = getenv("B200VC_NO_TMA_STORE") != nullptr;          // measurements and tests only
+    c->equal_bands = getenv("B200VC_EQUAL_BANDS") != nullptr;
 
     CU_TRY(c, cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));
     CU_TRY(c, cudaStreamCreateWithFlags(&c->s_k, cudaStreamNonBlocking));
@@ -1478,11 +1480,18 @@ int submit_frame(b200vc_ctx *c, Lock &lk, const b200vc_frame *f, bool sync, uint
                                    0, g.in_h, 1, gate, c->s_k));
     } else {
         // ---- bands chained by events (one band: the whole frame) ---------------------------------------
-        const int mb_rows_per_band = (c->mb_h + bands - 1) / bands;
-        for (int b = 0; b < bands; b++) {
-            const int row0 = b * mb_rows_per_band * 16;
-            if (row0 >= g.in_h) break;
-            const int rows = std::min(mb_rows_per_band * 16, g.in_h - row0);
+        // Each band is half the one before it (36, 18, 9, 5 macroblock rows of 1080p's 68): what the call
+        // waits for after the last byte has come up is the last band's kernel and its way back, so that band
+        // is small, and a band's way back (less than half the bytes of its way up) still fits under the
+        // upload of the next one. Measured against equal bands: profiles/r2_sync_latency_v2.txt.
+        int mb_left = c->mb_h, mb_row0 = 0;
+        for (int b = 0; b < bands && mb_left > 0; b++) {
+            const int shares_left = (1 << std::min(bands - b, 16)) - 1;          // 2^(bands-b) - 1
+            const int mb_rows = (c->equal_bands || bands > 8) ? (mb_left + (bands - b) - 1) / (bands - b)
+                                               : std::max(1, (int)(((long long)mb_left << (bands - b - 1)) + shares_left - 1) / shares_left);
+            const int row0 = mb_row0 * 16;
+            const int rows = std::min(mb_rows * 16, g.in_h - row0);
+            mb_row0 += mb_rows;  mb_left -= mb_rows;
             SUBMIT_TRY(upload_rows(c, lk, slot, f, d_cur, in_pinned, row0, rows, c->s_h2d));
             SUBMIT_CU(cudaEventRecord(c->ev_band_h2d[b], c->s_h2d));
             SUBMIT_CU(cudaStreamWaitEvent(c->s_k, c->ev_band_h2d[b], 0));

@@ -14,7 +14,7 @@ conv = b200vc.Converter(0)
 NAMES = {0: "bands chained by events, kernel stores", b200vc.FLAG_ROW_GATE: "row gate (flags by stream write)",
          b200vc.FLAG_ZERO_COPY: "kernel reads and writes host"}
 for flags in NAMES:
-    for bands in (1, 2, 4, 8, 16, 32):
+    for bands in (1, 2, 3, 4, 5, 6, 8, 16, 32):
         conv.set_info(W, H, matrix=0, range_=0, chroma_site=1, n_bands=bands, flags=flags)
         for i in range(20):
             conv.lib.b200vc_convert(conv.ctx, h_in.ptr + (i % 8) * W * H * 4, W * 4, planes, pits, None)

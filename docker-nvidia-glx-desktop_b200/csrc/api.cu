@@ -348,7 +348,7 @@ void build_fused_taps(const b200vc_config &c, const std::vector<Tap> &hy, const 
 // in_w x in_h -> out_w x out_h through the taps th (horizontal) and tv (vertical). Returns the blob
 // [tile_x | tile_y | col_rec | row_rec] (sections padded to 4 words) and fills everything of `k` but
 // the pointers; `off` receives the sections' word offsets.
-void build_plane_tile_taps(const std::vector<Tap> &th, const std::vector<Tap> &tv, int in_h, int out_w, int out_h,
+void build_plane_tile_taps(const std::vector<Tap> &th, const std::vector<Tap> &tv, int in_h, int out_w, int out_h, bool allow_pair,
                            PlaneTileKind &k, std::vector<uint32_t> &w, size_t off[4])
 {
     const int tiles_x = (out_w + KPT_TILE_W - 1) / KPT_TILE_W, tiles_y = (out_h + KPT_TILE_H - 1) / KPT_TILE_H;
@@ -375,14 +375,29 @@ void build_plane_tile_taps(const std::vector<Tap> &th, const std::vector<Tap> &t
     for (int v : sy) w.push_back((uint32_t)v);
     pad4();
     off[2] = w.size();
+    // the paired form (two adjacent columns per lane) when every pair's taps lie within 4 bytes of the pair's first
+    // (not in box mode and not with the vertical-first variant of the spec: the kernel's byte-load form handles those)
+    k.pair = allow_pair ? 1 : 0;
+    for (int x = 0; x + 1 < out_w; x += 2)
+        if (tidx(th[x + 1]) - tidx(th[x]) > 2 || tidx(th[x + 1]) < tidx(th[x])) k.pair = 0;
+    auto h_weights = [](Tap t) {
+        const uint32_t f = tstep(t) ? (uint32_t)tfrac(t) : 0u;
+        return (255u - f) | (1u << 8) | (f << 16);
+    };
     for (int bx = 0; bx < tiles_x; bx++) {
         const int x0 = bx * KPT_TILE_W;
-        for (int i = 0; i < KPT_TILE_W; i++) w.push_back((uint32_t)(tidx(th[std::min(x0 + i, out_w - 1)]) - sx[bx]));
-        for (int i = 0; i < KPT_TILE_W; i++) {
-            const Tap t = th[std::min(x0 + i, out_w - 1)];
-            const uint32_t f = tstep(t) ? (uint32_t)tfrac(t) : 0u;
-            w.push_back((255u - f) | (1u << 8) | (f << 16));
+        if (k.pair) {
+            for (int l = 0; l < KPT_TILE_W / 2; l++) {
+                const Tap t0 = th[std::min(x0 + 2 * l, out_w - 1)], t1 = th[std::min(x0 + 2 * l + 1, out_w - 1)];
+                const uint32_t o0 = (uint32_t)(tidx(t0) - sx[bx]), d = (uint32_t)(tidx(t1) - tidx(t0));
+                w.push_back((o0 & ~3u) | ((8u * (o0 & 3u)) << 16));
+                w.push_back(d | (d << 4) | ((d + 1u) << 8) | (3u << 12));
+                w.push_back(h_weights(t0));  w.push_back(h_weights(t1));
+            }
+            continue;
         }
+        for (int i = 0; i < KPT_TILE_W; i++) w.push_back((uint32_t)(tidx(th[std::min(x0 + i, out_w - 1)]) - sx[bx]));
+        for (int i = 0; i < KPT_TILE_W; i++) w.push_back(h_weights(th[std::min(x0 + i, out_w - 1)]));
     }
     off[3] = w.size();
     for (int by = 0; by < tiles_y; by++) {
@@ -1129,8 +1144,9 @@ int create_impl(b200vc_ctx *c)
             // about 8:1); larger ratios keep the gather kernel
             std::vector<uint32_t> w;
             size_t o0[4], o1[4];
-            build_plane_tile_taps(hy, vy, g.in_h, k.out_w, k.out_h, c->pt[0], w, o0);
-            build_plane_tile_taps(hc, vc, c->ch_in, c->ccw, c->cch, c->pt[1], w, o1);
+            const bool allow_pair = g.scale_mode != B200VC_SCALE_BOX_2X2 && B200VC_SPEC_SCALE_H_FIRST;
+            build_plane_tile_taps(hy, vy, g.in_h, k.out_w, k.out_h, allow_pair, c->pt[0], w, o0);
+            build_plane_tile_taps(hc, vc, c->ch_in, c->ccw, c->cch, allow_pair, c->pt[1], w, o1);
             PlaneTileParams probe;
             memset(&probe, 0, sizeof probe);
             probe.k[0] = c->pt[0];  probe.k[1] = c->pt[1];

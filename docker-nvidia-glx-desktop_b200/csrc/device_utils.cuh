@@ -216,4 +216,33 @@ __device__ __forceinline__ uint4 unpack565x4(uint2 raw)
     return make_uint4(a.x, a.y, b.x, b.y);
 }
 
+// Scaler helpers (phase 2 of the general fused kernel, the tiled plane scaler of the two-pass path). A line's horizontal pass leaves two samples that still
+// carry their 8 fraction bits (the sample is byte 1 of each sum); the vertical tap takes [A,A,B,B] from
+// the sums of the two lines (v_weight_word, host_tables.h) and leaves the result in byte 1 again.
+//
+// luma, two adjacent output columns per lane: their four taps lie within 4 bytes of the first tap
+// (step <= 2), which one funnel shift of two aligned words brings into a register
+__device__ __forceinline__ uint2 h_pass_luma_pair(const uint8_t *line, uint32_t sh, uint32_t sel1, uint32_t wh0, uint32_t wh1)
+{
+    const uint32_t w0 = *reinterpret_cast<const uint32_t *>(line), w1 = *reinterpret_cast<const uint32_t *>(line + 4);
+    const uint32_t v = __funnelshift_r(w0, w1, sh);                        // bytes i0 .. i0 + 3 of the line
+    return make_uint2(dp4a_uu(prmt(v, 0u, 0x3100), wh0, 0u),               // [a,a,b,_] . (255-f, 1, f, 0)
+                      dp4a_uu(prmt(v, 0u, sel1), wh1, 0u));
+}
+
+// chroma, one (u,v) sample per lane: the plane holds u,v byte pairs, the two taps are two 16-bit loads
+__device__ __forceinline__ uint2 h_pass_chroma(const uint8_t *smp, uint32_t wh)
+{
+    const uint32_t lo = *reinterpret_cast<const uint16_t *>(smp), hi = *reinterpret_cast<const uint16_t *>(smp + 2);
+    return make_uint2(dp4a_uu(prmt(lo, hi, 0x2400), wh, 0u),               // [u0,u0,u1,0]
+                      dp4a_uu(prmt(lo, hi, 0x2511), wh, 0u));              // [v0,v0,v1,0]
+}
+
+// vertical tap on the two lines' sums of both samples; the samples land in bytes 0 and 1
+__device__ __forceinline__ uint32_t v_pass_pair(uint2 top, uint2 bot, uint32_t wv)
+{
+    const uint32_t d0 = dp4a_uu(prmt(top.x, bot.x, 0x5511), wv, 128u), d1 = dp4a_uu(prmt(top.y, bot.y, 0x5511), wv, 128u);
+    return prmt(d0, d1, 0x0051);
+}
+
 }  // namespace b200vc

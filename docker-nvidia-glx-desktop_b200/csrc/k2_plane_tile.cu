@@ -74,7 +74,7 @@ template <int FMT>
 __global__ void __launch_bounds__(256) k2_plane_tile_kernel(const PlaneTileParams p)
 {
     extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ uint32_t s_col[2 * TW];                       // offsets[TW] | horizontal weight words[TW]
+    __shared__ __align__(16) uint32_t s_col[2 * TW];         // offsets[TW] | horizontal weight words[TW], or TW/2 pair records
     __shared__ __align__(8) uint2 s_row[TH];                 // {line offset in the window, vertical weight word}
     __shared__ __align__(16) uint8_t s_out[TW * TH * 2];     // output tile (NV12 chroma: 128-byte rows)
 
@@ -105,8 +105,30 @@ __global__ void __launch_bounds__(256) k2_plane_tile_kernel(const PlaneTileParam
         load_window(smem + win_bytes, p.src[2] + fi, p.src_pitch[2], sx, sy, bwp, bh, k.src_h, tid);
     __syncthreads();
 
-    // ---- scale: one output column x RPT rows per thread ------------------------------------------------
-    {
+    // ---- scale -------------------------------------------------------------------------------------------
+    // Two adjacent output columns per lane where every pair's taps lie within 4 bytes (ratios up to 2; the form
+    // the general fused kernel's phase 2 took in round 2: word loads and a funnel shift instead of byte loads,
+    // a quarter of the shared-memory wavefronts); a warp is half a tile row wide, TH/4 rows per thread.
+    if (k.pair && !p.box2x2 && B200VC_SPEC_SCALE_H_FIRST) {
+        const int cg = wrp & 1, rb = (wrp >> 1) * (TH / 4);
+        const uint4 rec = reinterpret_cast<const uint4 *>(s_col)[cg * 32 + lane];
+        const uint8_t *col = smem + (rec.x & 0xffffu);
+        const uint32_t sh = rec.x >> 16;
+#pragma unroll 4
+        for (int i = 0; i < TH / 4; i++) {
+            const uint2 tv = s_row[rb + i];
+            const uint8_t *l0 = col + tv.x;
+            const uint32_t d = v_pass_pair(h_pass_luma_pair(l0, sh, rec.y, rec.z, rec.w), h_pass_luma_pair(l0 + bwp, sh, rec.y, rec.z, rec.w), tv.y);
+            if (both) {
+                const uint8_t *m0 = l0 + win_bytes;
+                const uint32_t e = v_pass_pair(h_pass_luma_pair(m0, sh, rec.y, rec.z, rec.w), h_pass_luma_pair(m0 + bwp, sh, rec.y, rec.z, rec.w), tv.y);
+                reinterpret_cast<uint32_t *>(s_out)[(rb + i) * (TW / 2) + cg * 32 + lane] = prmt(d, e, 0x5140);   // u0 v0 u1 v1
+            } else {
+                reinterpret_cast<uint16_t *>(s_out)[(rb + i) * (TW / 2) + cg * 32 + lane] = (uint16_t)d;
+            }
+        }
+    } else {
+        // one output column x RPT rows per thread, byte loads (ratios above 2, box mode, the vertical-first variant)
         const int c = (wrp % CG) * 32 + lane, rb = (wrp / CG) * RPT;
         const uint32_t wh = s_col[TW + c];
         const uint8_t *col = smem + s_col[c];

@@ -164,6 +164,7 @@ struct PlaneTileKind {
     int bwp, bh;            // window pitch in shared memory (bytes, multiple of 16) and lines (without the spare one)
     int src_h;              // lines of the source plane (window lines past the last one repeat it)
     int out_w, out_h;       // samples of the output plane
+    int pair;               // col_rec in the paired form (two adjacent columns per lane, as FusedTaps' luma records)
 };
 struct PlaneTileParams {
     const uint8_t *src[3]; long long src_pitch[3]; long long src_frame_stride;

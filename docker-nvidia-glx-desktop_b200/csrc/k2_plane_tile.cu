@@ -7,9 +7,10 @@
 //
 // A CTA makes a 64 x 32 tile of one output plane (for NV12 chroma: of U and V, interleaved on the way
 // out). Its source window is copied into shared memory with coalesced 16-byte loads, taps come ready-made
-// from host-built per-tile records (PlaneTileKind, kernels.cuh), a lane owns one output column so the
-// byte gathers are free of bank conflicts, and the tile leaves through shared memory as 16-byte stores —
-// the structure measured on the general fused kernel (profiles/README.md).
+// from host-built per-tile records (PlaneTileKind, kernels.cuh), a lane owns two adjacent output columns
+// (word loads; or one column and byte gathers free of bank conflicts where a pair's taps do not fit 4 bytes),
+// and the tile leaves through shared memory as 16-byte stores — the structure measured on the general
+// fused kernel (profiles/README.md).
 #include "device_utils.cuh"
 
 #include <algorithm>

@@ -5,7 +5,7 @@
 // box, B200VC_FLAG_FORCE_TWO_PASS); the gather kernel in k2_scale.cu stays as the fallback for windows
 // that do not fit shared memory.
 //
-// A CTA makes a 64 x 32 tile of one output plane (for NV12 chroma: of U and V, interleaved on the way
+// A CTA makes a 128 x 64 tile of one output plane (for NV12 chroma: of U and V, interleaved on the way
 // out). Its source window is copied into shared memory with coalesced 16-byte loads, taps come ready-made
 // from host-built per-tile records (PlaneTileKind, kernels.cuh), a lane owns two adjacent output columns
 // (word loads; or one column and byte gathers free of bank conflicts where a pair's taps do not fit 4 bytes),

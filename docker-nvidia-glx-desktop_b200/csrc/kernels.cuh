@@ -154,6 +154,7 @@ struct PlaneScaleParams {
 //   tile_x[bx] = window's first source column (multiple of 16), tile_y[by] = its first source line
 //   col_rec[bx][2*KPT_TILE_W]: KPT_TILE_W x byte offset of the first tap in a window line,
 //                              KPT_TILE_W x (255-f) | 1<<8 | f<<16
+//                          or, pair == 1: KPT_TILE_W/2 x the four words of FusedTaps' paired luma records
 //   row_rec[by][2*KPT_TILE_H]: KPT_TILE_H x {byte offset of the first line in the window, wv}   (wv as in FusedTaps)
 constexpr int KPT_TILE_W = 128;
 constexpr int KPT_TILE_H = 64;
